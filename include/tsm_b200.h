@@ -1,0 +1,166 @@
+/* tsm_b200.h -- C ABI of libtsm_b200.so: the B200 (sm_100a) kernels behind the tianshou_marl
+ * on-policy multi-agent hot path (rollout collection -> replay-buffer add/sample -> GAE ->
+ * PPO minibatch update).
+ *
+ * The reference (eric-downes/tianshou_marl) is pure Python and has no FFI; the entry points
+ * below are what a ctypes binding for this path binds.  Each one cites
+ * the reference function it replaces (file:line relative to the reference checkout).
+ *
+ * Conventions
+ *  - extern "C", plain pointers and sizes, no torch / C++ types.
+ *  - Every pointer is a DEVICE pointer unless its name starts with h_ .
+ *  - The caller owns every buffer; the library allocates nothing.  Scratch space is passed in
+ *    explicitly and sized by the matching *_workspace_bytes() query.
+ *  - Every call is asynchronous on `stream` (a cudaStream_t passed as void*; NULL = default
+ *    stream).  Calls on one stream are ordered; a handle/struct is not thread-safe.
+ *  - Return 0 on success, a negative tsm_status otherwise; tsm_last_error() gives the message
+ *    of the calling thread's last failure.  No C++ exception crosses the boundary.
+ *  - Row flattening: row r = env * n_agents + agent.  One sub-buffer per row.
+ *    Indices exchanged with the caller are numbered ENV-MAJOR like the reference
+ *    (flat = r * size + t, vecbuf.py:33-37 / manager.py:26-51); storage inside the device
+ *    buffer is TIME-MAJOR ([t][r]) so that one vector step is one contiguous write.
+ */
+#ifndef TSM_B200_H
+#define TSM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TSM_ABI_VERSION 1
+
+typedef void* tsm_stream_t; /* cudaStream_t */
+
+typedef enum {
+    TSM_OK = 0,
+    TSM_ERR_INVALID = -1,   /* bad argument (maps to ValueError) */
+    TSM_ERR_CUDA = -2,      /* CUDA runtime error (maps to RuntimeError) */
+    TSM_ERR_WORKSPACE = -3, /* workspace too small */
+    TSM_ERR_UNSUPPORTED = -4
+} tsm_status;
+
+int tsm_abi_version(void);
+const char* tsm_last_error(void);
+/* sm count / compute capability of `device`; any out pointer may be NULL. */
+int tsm_device_info(int device, int* h_sm_count, int* h_cc_major, int* h_cc_minor);
+
+/* =========================================================================================
+ * K3  GAE / discounted returns
+ * replaces  Algorithm.compute_episodic_return   tianshou/algorithm/algorithm_base.py:651-717
+ *           Algorithm.value_mask                tianshou/algorithm/algorithm_base.py:631-649
+ *           _gae (numba)                        tianshou/algorithm/algorithm_base.py:1079-1134
+ *           episode_mc_return_to_go (numba)     tianshou/algorithm/algorithm_base.py:1137-1151
+ *
+ *   v_next_i <- v_next_i * !terminated_i                      (value mask, :709)
+ *   end_i     = terminated_i | truncated_i | force_end_i | ((i+1) % seg_len == 0 if seg_len>0)
+ *   delta_i   = rew_i + gamma * v_next_i - v_s_i              (float64, :1128)
+ *   g_i       = delta_i + (1-end_i) * gamma*lam * g_{i+1}     (float64, :1129-1133), g_n = 0
+ *   adv_i = g_i ; ret_i = g_i + v_s_i                         (:715)
+ * The recurrence runs over the whole flat vector exactly like the reference; segment breaks
+ * come only from `end`.  State is carried in float64; I/O dtypes are selected by the flags.
+ * ========================================================================================= */
+
+/* Flat 1-D vector in the reference's batch order (one-pass segmented reverse scan with
+ * decoupled look-back).  io_is_f64 selects the dtype of v_s, v_next, rew, adv_out and ret_out:
+ * 0 = float32 (device-resident rollouts), 1 = float64 (the reference's numpy path, where numba
+ * promotes everything to float64).  v_s may be NULL (treated as 0; MC return-to-go), v_next
+ * may be NULL (0).  force_end may be NULL.  seg_len <= 0 disables the periodic break. */
+size_t tsm_gae_flat_workspace_bytes(int64_t n);
+int tsm_gae_flat(const void* v_s, const void* v_next, const void* rew, int io_is_f64,
+                 const uint8_t* terminated, const uint8_t* truncated, const uint8_t* force_end,
+                 int64_t n, int64_t seg_len, double gamma, double lam,
+                 void* adv_out, void* ret_out,
+                 void* workspace, size_t workspace_bytes, tsm_stream_t stream);
+
+/* Time-major device-buffer layout: arrays are [size][n_rows]; row r holds `len` valid slots
+ * starting at ring slot `start` (time order (start + j) % size, j < len); the last one is
+ * forced to `end` (= buffer.unfinished_index(), algorithm_base.py:712-713).  One thread per
+ * row, serial in t like the reference, coalesced across rows.  Outputs are [size][n_rows]. */
+int tsm_gae_tm(const float* v_s, const float* v_next, const float* rew,
+               const uint8_t* terminated, const uint8_t* truncated,
+               int64_t size, int64_t n_rows, int64_t start, int64_t len,
+               double gamma, double lam, float* adv_out, float* ret_out, tsm_stream_t stream);
+
+/* =========================================================================================
+ * K2  Device ring buffer (VectorReplayBuffer)
+ * replaces  ReplayBufferManager.add             tianshou/data/buffer/manager.py:131-193
+ *           ReplayBuffer._update_state_pre_add  tianshou/data/buffer/buffer_base.py:355-410
+ *           ReplayBufferManager.sample_indices  tianshou/data/buffer/manager.py:195-229
+ *           ReplayBuffer.sample_indices         tianshou/data/buffer/buffer_base.py:495-531
+ *           _prev_index / _next_index (numba)   tianshou/data/buffer/manager.py:306-358
+ *           ReplayBufferManager.unfinished_index tianshou/data/buffer/manager.py:85-91
+ *           ReplayBufferManager.reset           tianshou/data/buffer/manager.py:70-75
+ *           ReplayBuffer.__getitem__ (gather)   tianshou/data/buffer/buffer_base.py:591-635
+ * All integer results are bit-exact with the reference.
+ * ========================================================================================= */
+typedef struct tsm_buf {
+    int64_t n_bufs;  /* R sub-buffers (rows) */
+    int64_t size;    /* slots per sub-buffer = ceil(total_size / n_bufs), vecbuf.py:35 */
+    int64_t obs_dim; /* O (flattened) */
+    /* per-sub-buffer counters, length n_bufs (buffer_base.py:103-106, manager.py:48-50) */
+    int64_t* ins;        /* _insertion_idx */
+    int64_t* sz;         /* _size  (== manager._lengths) */
+    int64_t* last_index; /* manager.last_index, env-major flat */
+    int64_t* ep_len;     /* _ep_len */
+    int64_t* ep_start;   /* _ep_start_idx (local to the sub-buffer) */
+    double* ep_ret;      /* _ep_return */
+    /* payload, time-major: scalars [size][n_bufs], obs [size][n_bufs][obs_dim] */
+    float* obs;
+    float* obs_next;
+    int32_t* act;
+    float* rew;
+    uint8_t* terminated;
+    uint8_t* truncated;
+    uint8_t* done;
+    float* logp;  /* optional policy output stored per step (may be NULL) */
+    float* value; /* optional critic output stored per step (may be NULL) */
+} tsm_buf;
+
+/* zero the counters (keep_statistics != 0 keeps ep_ret / ep_len, buffer_base.py:292-298). */
+int tsm_buf_reset(const tsm_buf* buf, int keep_statistics, tsm_stream_t stream);
+
+/* add n rows. buffer_ids NULL = arange(n_bufs) (then n must equal n_bufs).  Payload inputs are
+ * [n] / [n][obs_dim] row-major; obs_next / logp / value may be NULL (then not stored).
+ * Outputs (each may be NULL): idx_out = env-major flat slot written, ep_ret_out / ep_len_out =
+ * episode return / length if the row finished an episode else 0, ep_start_out = env-major
+ * flat start slot of the row's current episode.  buffer_ids must be unique within one call. */
+int tsm_buf_add(const tsm_buf* buf, const float* obs, const int32_t* act, const float* rew,
+                const uint8_t* terminated, const uint8_t* truncated, const float* obs_next,
+                const float* logp, const float* value,
+                const int64_t* buffer_ids, int64_t n,
+                int64_t* idx_out, double* ep_ret_out, int64_t* ep_len_out, int64_t* ep_start_out,
+                tsm_stream_t stream);
+
+/* sample_indices(0): every valid index, sub-buffer by sub-buffer, each in time order
+ * ([ins..sz) ++ [0..ins)).  `out` must hold n_bufs*size entries; the number written is stored
+ * to *count_out (device int64).  workspace: tsm_buf_indices_workspace_bytes(n_bufs). */
+size_t tsm_buf_indices_workspace_bytes(int64_t n_bufs);
+int tsm_buf_indices_all(const tsm_buf* buf, int64_t* out, int64_t* count_out,
+                        void* workspace, size_t workspace_bytes, tsm_stream_t stream);
+
+/* prev / next for n env-major indices (taken modulo maxsize like manager.py:313,340). */
+int tsm_buf_prev(const tsm_buf* buf, const int64_t* idx, int64_t n, int64_t* out, tsm_stream_t stream);
+int tsm_buf_next(const tsm_buf* buf, const int64_t* idx, int64_t n, int64_t* out, tsm_stream_t stream);
+
+/* unfinished_index(): last written slot of every sub-buffer whose done flag is false, in
+ * sub-buffer order.  out holds up to n_bufs entries; *count_out (device) = number written. */
+int tsm_buf_unfinished(const tsm_buf* buf, int64_t* out, int64_t* count_out,
+                       void* workspace, size_t workspace_bytes, tsm_stream_t stream);
+
+/* gather rows by env-major index into contiguous [n] / [n][obs_dim] outputs (any out may be
+ * NULL).  `extra_in` are optional extra time-major float arrays ([size][n_bufs], e.g. adv,
+ * returns) gathered into extra_out[k]. */
+int tsm_buf_gather(const tsm_buf* buf, const int64_t* idx, int64_t n,
+                   float* obs_out, float* obs_next_out, int32_t* act_out, float* rew_out,
+                   uint8_t* term_out, uint8_t* trunc_out, uint8_t* done_out,
+                   float* logp_out, float* value_out,
+                   const float* const* h_extra_in, float* const* h_extra_out, int n_extra,
+                   tsm_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TSM_B200_H */

@@ -1,0 +1,108 @@
+"""ctypes binding of libtsm_b200.so (C ABI: include/tsm_b200.h).
+
+The product path has NO CPU fallback: if the shared library is missing or a kernel call
+fails, this module raises.  Build it with `python -c "import __graft_entry__ as g; g.build()"`
+or `make -C tianshou_marl_b200/csrc`.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libtsm_b200.so")
+
+c_i64, c_i32, c_f64, c_vp, c_sz = C.c_int64, C.c_int, C.c_double, C.c_void_p, C.c_size_t
+
+
+class TsmError(RuntimeError):
+    pass
+
+
+class TsmBuf(C.Structure):
+    """struct tsm_buf (include/tsm_b200.h)."""
+
+    _fields_ = [
+        ("n_bufs", c_i64), ("size", c_i64), ("obs_dim", c_i64),
+        ("ins", c_vp), ("sz", c_vp), ("last_index", c_vp), ("ep_len", c_vp), ("ep_start", c_vp), ("ep_ret", c_vp),
+        ("obs", c_vp), ("obs_next", c_vp), ("act", c_vp), ("rew", c_vp),
+        ("terminated", c_vp), ("truncated", c_vp), ("done", c_vp), ("logp", c_vp), ("value", c_vp),
+    ]
+
+
+_SIGS = {
+    "tsm_abi_version": (c_i32, []),
+    "tsm_last_error": (C.c_char_p, []),
+    "tsm_device_info": (c_i32, [c_i32, c_vp, c_vp, c_vp]),
+    "tsm_gae_flat_workspace_bytes": (c_sz, [c_i64]),
+    "tsm_gae_flat": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_i64, c_i64, c_f64, c_f64,
+                             c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "tsm_gae_tm": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_f64, c_f64, c_vp, c_vp, c_vp]),
+    "tsm_buf_reset": (c_i32, [c_vp, c_i32, c_vp]),
+    "tsm_buf_add": (c_i32, [c_vp] * 10 + [c_i64] + [c_vp] * 5),
+    "tsm_buf_indices_workspace_bytes": (c_sz, [c_i64]),
+    "tsm_buf_indices_all": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "tsm_buf_prev": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_vp]),
+    "tsm_buf_next": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_vp]),
+    "tsm_buf_unfinished": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "tsm_buf_gather": (c_i32, [c_vp, c_vp, c_i64] + [c_vp] * 9 + [c_vp, c_vp, c_i32, c_vp]),
+}
+
+_lib = None
+
+
+def exported_symbols() -> list[str]:
+    """Names include/tsm_b200.h declares (kept in sync by tests/test_abi.py)."""
+    return list(_SIGS)
+
+
+def build(verbose: bool = False) -> str:
+    """Compile the library in-tree with nvcc for sm_100a (cross-compiles without a GPU)."""
+    r = subprocess.run(["make", "-C", os.path.join(_HERE, "csrc"), "-j8"], capture_output=True, text=True)
+    if verbose or r.returncode != 0:
+        print(r.stdout[-4000:], r.stderr[-4000:])
+    if r.returncode != 0:
+        raise TsmError("building libtsm_b200.so failed")
+    return LIB_PATH
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise TsmError(
+                f"{LIB_PATH} is missing: the CUDA extension is required (no CPU fallback). "
+                "Build it with `make -C tianshou_marl_b200/csrc` or __graft_entry__.build()."
+            )
+        l = C.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGS.items():
+            fn = getattr(l, name)  # AttributeError if the .so lacks a declared symbol
+            fn.restype, fn.argtypes = res, args
+        if l.tsm_abi_version() != 1:
+            raise TsmError("libtsm_b200.so ABI version mismatch")
+        _lib = l
+    return _lib
+
+
+def check(rc: int) -> None:
+    """Translate a tsm_status into the reference's exception types."""
+    if rc == 0:
+        return
+    msg = lib().tsm_last_error().decode(errors="replace")
+    if rc == -1:
+        raise ValueError(msg)
+    raise TsmError(f"tsm error {rc}: {msg}")
+
+
+def ptr(t) -> int | None:
+    """Device/host pointer of a torch tensor (None -> NULL)."""
+    if t is None:
+        return None
+    return t.data_ptr()
+
+
+def stream_ptr() -> int:
+    import torch
+
+    return torch.cuda.current_stream().cuda_stream

@@ -1,0 +1,3 @@
+from .returns import compute_episodic_return, episode_mc_return_to_go, gae_flat, gae_time_major
+
+__all__ = ["compute_episodic_return", "episode_mc_return_to_go", "gae_flat", "gae_time_major"]

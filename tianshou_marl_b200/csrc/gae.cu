@@ -1,0 +1,317 @@
+// gae.cu -- K3: GAE / discounted returns as a segmented reverse scan (sm_100a).
+//
+// Replaces tianshou/algorithm/algorithm_base.py:651-717 (compute_episodic_return),
+// :631-649 (value_mask), :1079-1134 (_gae), :1137-1151 (episode_mc_return_to_go).
+//
+// Two layouts:
+//  * tsm_gae_flat : the reference's flat 1-D batch order.  One pass over HBM: every CTA scans
+//    a tile of TILE elements (blocked, ITEMS contiguous elements per thread), composes the
+//    affine maps g -> delta + c*g with warp shuffles, and obtains its carry from the tile to
+//    its right by decoupled look-back.  Because c == 0 at every episode end, a tile that
+//    contains any end flag publishes its inclusive value immediately, so the look-back depth
+//    is 1 for MPE-like data and the scan never serialises.
+//  * tsm_gae_tm   : the device buffer's time-major [t][row] layout.  One thread per row walks
+//    t backwards exactly like the reference's serial loop; rows are adjacent across lanes so
+//    every load/store is a fully coalesced 128-byte line.
+// Both carry the recurrence in float64 (numba computes in float64) and round once on store.
+#include "common.cuh"
+
+namespace tsm {
+namespace gae {
+
+constexpr int THREADS = 256;
+constexpr int ITEMS = 8;  // contiguous elements per thread
+constexpr int TILE = THREADS * ITEMS;
+constexpr int WARPS = THREADS / 32;
+
+// tile status for decoupled look-back
+constexpr int ST_EMPTY = 0, ST_AGG = 1, ST_INCL = 2;
+struct __align__(32) TileState {
+    double a;     // aggregate multiplier            (valid once status >= ST_AGG, never rewritten)
+    double b;     // aggregate offset                (valid once status >= ST_AGG, never rewritten)
+    double incl;  // g at the tile's first element   (valid once status == ST_INCL)
+    int status;
+    int pad;
+};
+
+struct Map {
+    double a, b;  // g_out = b + a * g_in
+};
+__device__ __forceinline__ Map compose(const Map& l, const Map& r) {
+    // apply r first (it is to the right), then l
+    return Map{l.a * r.a, fma(l.a, r.b, l.b)};
+}
+
+template <typename T>
+__device__ __forceinline__ void load_items(const T* __restrict__ p, int64_t base, int64_t n, T (&out)[ITEMS], T fill) {
+    // base is a multiple of ITEMS; fast path when the whole chunk is in range and aligned
+    constexpr int BYTES = sizeof(T) * ITEMS;
+    if (p == nullptr) {
+#pragma unroll
+        for (int e = 0; e < ITEMS; ++e) out[e] = fill;
+        return;
+    }
+    if (base + ITEMS <= n && (reinterpret_cast<uintptr_t>(p + base) % (BYTES >= 16 ? 16 : BYTES)) == 0) {
+        if constexpr (BYTES >= 16) {
+            const uint4* q = reinterpret_cast<const uint4*>(p + base);
+            uint4* o = reinterpret_cast<uint4*>(out);
+#pragma unroll
+            for (int k = 0; k < BYTES / 16; ++k) o[k] = q[k];
+        } else {  // 8 bytes (uint8 flags, ITEMS == 8)
+            *reinterpret_cast<uint2*>(out) = *reinterpret_cast<const uint2*>(p + base);
+        }
+    } else {
+#pragma unroll
+        for (int e = 0; e < ITEMS; ++e) out[e] = (base + e < n) ? p[base + e] : fill;
+    }
+}
+
+template <typename T>
+__device__ __forceinline__ void store_items(T* __restrict__ p, int64_t base, int64_t n, const T (&v)[ITEMS]) {
+    constexpr int BYTES = sizeof(T) * ITEMS;
+    if (base + ITEMS <= n && (reinterpret_cast<uintptr_t>(p + base) % 16) == 0) {
+        uint4* q = reinterpret_cast<uint4*>(p + base);
+        const uint4* o = reinterpret_cast<const uint4*>(v);
+#pragma unroll
+        for (int k = 0; k < BYTES / 16; ++k) q[k] = o[k];
+    } else {
+#pragma unroll
+        for (int e = 0; e < ITEMS; ++e)
+            if (base + e < n) p[base + e] = v[e];
+    }
+}
+
+// T in {float,double}: dtype of v_s, v_next, rew and of both outputs (float64 = the numpy path
+// of the reference, float32 = device-resident rollouts); the carry is float64 either way
+template <typename T>
+__global__ void __launch_bounds__(THREADS) gae_flat_kernel(
+    const T* __restrict__ v_s, const T* __restrict__ v_next, const T* __restrict__ rew,
+    const uint8_t* __restrict__ term, const uint8_t* __restrict__ trunc, const uint8_t* __restrict__ force_end,
+    int64_t n, int64_t seg_len, double gamma, double gl, T* __restrict__ adv_out, T* __restrict__ ret_out,
+    unsigned int* __restrict__ tile_counter, TileState* __restrict__ tiles, int num_tiles) {
+    __shared__ int s_tile;
+    __shared__ Map s_warp[WARPS];
+    __shared__ double s_carry;
+
+    // tiles are handed out right-to-left in launch order, so a tile only ever waits on tiles
+    // that already started (forward progress without co-residency assumptions)
+    if (threadIdx.x == 0) s_tile = num_tiles - 1 - (int)atomicAdd(tile_counter, 1u);
+    __syncthreads();
+    const int tile = s_tile;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t base = (int64_t)tile * TILE + (int64_t)threadIdx.x * ITEMS;
+
+    T vs[ITEMS], vn[ITEMS], rw[ITEMS];
+    uint8_t te[ITEMS], tr[ITEMS], fe[ITEMS];
+    load_items<T>(v_s, base, n, vs, (T)0);
+    load_items<T>(v_next, base, n, vn, (T)0);
+    load_items<T>(rew, base, n, rw, (T)0);
+    load_items<uint8_t>(term, base, n, te, (uint8_t)0);
+    load_items<uint8_t>(trunc, base, n, tr, (uint8_t)0);
+    load_items<uint8_t>(force_end, base, n, fe, (uint8_t)0);
+
+    // per element: delta (float64, unfused like numba) and c in {0, gamma*lambda}
+    double delta[ITEMS];
+    bool endf[ITEMS];
+#pragma unroll
+    for (int e = 0; e < ITEMS; ++e) {
+        const int64_t i = base + e;
+        double vnm = te[e] ? 0.0 : (double)vn[e];                                   // value_mask, :709
+        delta[e] = __dadd_rn(__dadd_rn((double)rw[e], __dmul_rn(vnm, gamma)), -(double)vs[e]);  // :1128
+        bool en = (te[e] | tr[e] | fe[e]) != 0;
+        if (seg_len > 0 && ((i + 1) % seg_len) == 0) en = true;
+        if (i >= n) { en = true; delta[e] = 0.0; }
+        endf[e] = en;
+    }
+    // pass 1: thread aggregate  g_first = B + A * g_in
+    Map m{1.0, 0.0};
+#pragma unroll
+    for (int e = ITEMS - 1; e >= 0; --e) {
+        double c = endf[e] ? 0.0 : gl;
+        m.b = __dadd_rn(delta[e], __dmul_rn(c, m.b));  // same rounding as the serial loop
+        m.a = c * m.a;
+    }
+    // warp inclusive suffix scan of maps (Hillis-Steele with shfl_down)
+    Map incl = m;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        Map r{__shfl_down_sync(0xffffffffu, incl.a, d), __shfl_down_sync(0xffffffffu, incl.b, d)};
+        if (lane + d < 32) incl = compose(incl, r);
+    }
+    Map excl{__shfl_down_sync(0xffffffffu, incl.a, 1), __shfl_down_sync(0xffffffffu, incl.b, 1)};
+    if (lane == 31) excl = Map{1.0, 0.0};
+    if (lane == 0) s_warp[warp] = incl;
+    __syncthreads();
+
+    if (threadIdx.x == 0) {
+        Map blk{1.0, 0.0};
+#pragma unroll
+        for (int w = WARPS - 1; w >= 0; --w) blk = compose(s_warp[w], blk);
+        double carry = 0.0;
+        if (tile == num_tiles - 1 || blk.a == 0.0) {
+            // no dependence on the right neighbour for the published value
+            if (tile == num_tiles - 1) carry = 0.0;
+            TileState* me = &tiles[tile];
+            me->incl = blk.b;  // a == 0 or g_n == 0: inclusive value is just b
+            __threadfence();
+            atomicExch(&me->status, ST_INCL);
+        } else {
+            TileState* me = &tiles[tile];
+            me->a = blk.a;
+            me->b = blk.b;
+            __threadfence();
+            atomicExch(&me->status, ST_AGG);
+        }
+        if (tile != num_tiles - 1) {
+            // decoupled look-back over tiles to the right
+            Map run{1.0, 0.0};
+            int j = tile + 1;
+            while (true) {
+                if (j >= num_tiles) { carry = run.b; break; }
+                volatile TileState* t = &tiles[j];
+                int st;
+                while ((st = atomicAdd((int*)&t->status, 0)) == ST_EMPTY) { __nanosleep(20); }
+                __threadfence();
+                if (st == ST_INCL) { carry = fma(run.a, t->incl, run.b); break; }
+                run = compose(run, Map{t->a, t->b});
+                if (run.a == 0.0) { carry = run.b; break; }
+                ++j;
+            }
+            if (blk.a != 0.0) {
+                TileState* me = &tiles[tile];
+                me->incl = fma(blk.a, carry, blk.b);
+                __threadfence();
+                atomicExch(&me->status, ST_INCL);
+            }
+        }
+        s_carry = carry;
+    }
+    __syncthreads();
+
+    // carry into this warp = maps of the warps to its right applied to the tile carry
+    double g = s_carry;
+    for (int w = WARPS - 1; w > warp; --w) g = fma(s_warp[w].a, g, s_warp[w].b);
+    g = fma(excl.a, g, excl.b);  // carry into this thread
+
+    // pass 2: the reference's serial recurrence with the true carry (:1131-1133)
+    T adv[ITEMS], ret[ITEMS];
+#pragma unroll
+    for (int e = ITEMS - 1; e >= 0; --e) {
+        double c = endf[e] ? 0.0 : gl;
+        g = __dadd_rn(delta[e], __dmul_rn(c, g));
+        adv[e] = (T)g;
+        ret[e] = (T)__dadd_rn(g, (double)vs[e]);  // :715
+    }
+    if (adv_out) store_items<T>(adv_out, base, n, adv);
+    if (ret_out) store_items<T>(ret_out, base, n, ret);
+}
+
+// ---------------------------------------------------------------------------------------------
+// time-major: one thread per row, serial over t (bit-exact float64 recurrence of the reference)
+constexpr int TM_THREADS = 128;
+constexpr int TM_UNROLL = 8;
+
+__global__ void __launch_bounds__(TM_THREADS) gae_tm_kernel(
+    const float* __restrict__ v_s, const float* __restrict__ v_next, const float* __restrict__ rew,
+    const uint8_t* __restrict__ term, const uint8_t* __restrict__ trunc, int64_t size, int64_t R, int64_t start,
+    int64_t len, double gamma, double gl, float* __restrict__ adv_out, float* __restrict__ ret_out) {
+    const int64_t r = (int64_t)blockIdx.x * TM_THREADS + threadIdx.x;
+    if (r >= R) return;
+    double g = 0.0;
+    int64_t j = len - 1;
+    int64_t tj = (start + j) % size;  // ring slot of element j; walks backwards with one wrap
+    // main loop: TM_UNROLL independent loads in flight per array, then the dependent chain
+    while (j >= 0) {
+        float a_vs[TM_UNROLL], a_vn[TM_UNROLL], a_rw[TM_UNROLL];
+        uint8_t a_te[TM_UNROLL], a_tr[TM_UNROLL];
+        int64_t off[TM_UNROLL];
+#pragma unroll
+        for (int u = 0; u < TM_UNROLL; ++u) {
+            int64_t jj = j - u;
+            bool ok = jj >= 0;  // ok implies u <= j < size, so a single wrap is enough
+            int64_t t = tj - u;
+            if (t < 0) t += size;
+            off[u] = ok ? t * R + r : r;
+            a_vs[u] = (ok && v_s) ? v_s[off[u]] : 0.f;
+            a_vn[u] = (ok && v_next) ? v_next[off[u]] : 0.f;
+            a_rw[u] = ok ? rew[off[u]] : 0.f;
+            a_te[u] = ok ? term[off[u]] : (uint8_t)0;
+            a_tr[u] = ok ? trunc[off[u]] : (uint8_t)0;
+        }
+#pragma unroll
+        for (int u = 0; u < TM_UNROLL; ++u) {
+            int64_t jj = j - u;
+            if (jj < 0) break;
+            double vnm = a_te[u] ? 0.0 : (double)a_vn[u];
+            double delta = __dadd_rn(__dadd_rn((double)a_rw[u], __dmul_rn(vnm, gamma)), -(double)a_vs[u]);
+            bool en = (a_te[u] | a_tr[u]) != 0 || jj == len - 1;
+            double c = en ? 0.0 : gl;
+            g = __dadd_rn(delta, __dmul_rn(c, g));
+            if (adv_out) adv_out[off[u]] = (float)g;
+            if (ret_out) ret_out[off[u]] = (float)__dadd_rn(g, (double)a_vs[u]);
+        }
+        j -= TM_UNROLL;
+        tj -= TM_UNROLL;
+        if (tj < 0) tj = ((tj % size) + size) % size;
+    }
+}
+
+}  // namespace gae
+}  // namespace tsm
+
+using namespace tsm;
+using namespace tsm::gae;
+
+extern "C" size_t tsm_gae_flat_workspace_bytes(int64_t n) {
+    if (n < 0) n = 0;
+    int64_t tiles = ceil_div(n, TILE);
+    return 64 + (size_t)tiles * sizeof(TileState);
+}
+
+extern "C" int tsm_gae_flat(const void* v_s, const void* v_next, const void* rew, int io_is_f64,
+                            const uint8_t* terminated, const uint8_t* truncated, const uint8_t* force_end,
+                            int64_t n, int64_t seg_len, double gamma, double lam, void* adv_out, void* ret_out,
+                            void* workspace, size_t workspace_bytes, tsm_stream_t stream) {
+    TSM_REQUIRE(n >= 0, "n >= 0");
+    if (n == 0) return TSM_OK;
+    TSM_REQUIRE(rew != nullptr, "rew != NULL");
+    TSM_REQUIRE(terminated != nullptr && truncated != nullptr, "terminated/truncated != NULL");
+    TSM_REQUIRE(adv_out != nullptr || ret_out != nullptr, "an output pointer");
+    TSM_REQUIRE(n / TILE < (int64_t)INT32_MAX, "n too large");
+    if (workspace == nullptr || workspace_bytes < tsm_gae_flat_workspace_bytes(n))
+        return fail(TSM_ERR_WORKSPACE, "%s: workspace too small (need %lld bytes)", __func__,
+                    (long long)tsm_gae_flat_workspace_bytes(n));
+    TSM_REQUIRE((reinterpret_cast<uintptr_t>(workspace) % 32) == 0, "workspace 32-byte aligned");
+    cudaStream_t s = as_stream(stream);
+    const int num_tiles = (int)ceil_div(n, TILE);
+    TSM_CUDA(cudaMemsetAsync(workspace, 0, tsm_gae_flat_workspace_bytes(n), s));
+    unsigned int* counter = reinterpret_cast<unsigned int*>(workspace);
+    TileState* tiles = reinterpret_cast<TileState*>(reinterpret_cast<char*>(workspace) + 64);
+    const double gl = gamma * lam;
+    if (io_is_f64)
+        gae_flat_kernel<double><<<num_tiles, THREADS, 0, s>>>(
+            (const double*)v_s, (const double*)v_next, (const double*)rew, terminated, truncated, force_end, n, seg_len,
+            gamma, gl, (double*)adv_out, (double*)ret_out, counter, tiles, num_tiles);
+    else
+        gae_flat_kernel<float><<<num_tiles, THREADS, 0, s>>>(
+            (const float*)v_s, (const float*)v_next, (const float*)rew, terminated, truncated, force_end, n, seg_len,
+            gamma, gl, (float*)adv_out, (float*)ret_out, counter, tiles, num_tiles);
+    TSM_LAUNCH_CHECK();
+    return TSM_OK;
+}
+
+extern "C" int tsm_gae_tm(const float* v_s, const float* v_next, const float* rew, const uint8_t* terminated,
+                          const uint8_t* truncated, int64_t size, int64_t n_rows, int64_t start, int64_t len,
+                          double gamma, double lam, float* adv_out, float* ret_out, tsm_stream_t stream) {
+    TSM_REQUIRE(size > 0 && n_rows >= 0, "size > 0, n_rows >= 0");
+    TSM_REQUIRE(len >= 0 && len <= size && start >= 0 && start < size, "0 <= len <= size, 0 <= start < size");
+    if (n_rows == 0 || len == 0) return TSM_OK;
+    TSM_REQUIRE(rew && terminated && truncated, "rew/terminated/truncated != NULL");
+    TSM_REQUIRE(adv_out != nullptr || ret_out != nullptr, "an output pointer");
+    const int64_t blocks = ceil_div(n_rows, TM_THREADS);
+    TSM_REQUIRE(blocks < (int64_t)INT32_MAX, "n_rows too large");
+    gae_tm_kernel<<<(unsigned)blocks, TM_THREADS, 0, as_stream(stream)>>>(
+        v_s, v_next, rew, terminated, truncated, size, n_rows, start, len, gamma, gamma * lam, adv_out, ret_out);
+    TSM_LAUNCH_CHECK();
+    return TSM_OK;
+}
