@@ -160,6 +160,55 @@ int tsm_buf_gather(const tsm_buf* buf, const int64_t* idx, int64_t n,
                    const float* const* h_extra_in, float* const* h_extra_out, int n_extra,
                    tsm_stream_t stream);
 
+
+/* =========================================================================================
+ * K1  Batched MPE (simple_spread / simple_tag) step, reset, observe, reward
+ * replaces  BaseVectorEnv.step / reset          tianshou/env/venvs.py:237-322, :195-235
+ *           DummyEnvWorker.send                 tianshou/env/worker/dummy.py:37-41
+ *           (wrappers) PettingZooEnv.step/reset tianshou/env/pettingzoo_env.py:38-120
+ *                      EnhancedPettingZooEnv    tianshou/env/enhanced_pettingzoo_env.py:90-222
+ *           and the third-party simulator they drive: pettingzoo 1.24.2
+ *           mpe/_mpe_utils/core.py (World.step), _mpe_utils/simple_env.py, scenarios/
+ *           simple_spread.py, simple_tag.py  (not in the reference tree; parity unpinned).
+ * One group of G lanes (G = 4..32, chosen from n_agents) simulates one environment; lanes
+ * exchange positions with warp shuffles.  State is SoA per field, float2-vectorised:
+ * pos/vel are [n_envs * n_agents] (row order), lm is [n_envs * n_landmarks].
+ * ========================================================================================= */
+#define TSM_MPE_SPREAD 0
+#define TSM_MPE_TAG 1
+typedef struct tsm_mpe {
+    int32_t scenario;      /* TSM_MPE_SPREAD / TSM_MPE_TAG */
+    int32_t n_agents;      /* A (tag: adversaries first, then good agents) */
+    int32_t n_landmarks;   /* L */
+    int32_t n_adversaries; /* tag only */
+    int32_t obs_dim;       /* spread 6A; tag 4 + 2L + 2(A-1) + 2*n_good (good agents zero-padded) */
+    int32_t max_cycles;    /* truncation horizon (25) */
+    int32_t pos_first;     /* 1: p += v*dt before the velocity update (pettingzoo 1.24) ; 0: after */
+    float local_ratio;     /* spread: reward = global*(1-lr) + local*lr */
+    int64_t n_envs;
+    uint64_t seed;         /* Philox key for reset draws */
+    float* pos;            /* float2 [n_envs*A] */
+    float* vel;            /* float2 [n_envs*A] */
+    float* lm;             /* float2 [n_envs*L] */
+    int32_t* steps;        /* [n_envs] cycles since reset */
+    int64_t* episode;      /* [n_envs] number of resets so far (Philox counter) */
+} tsm_mpe;
+
+/* reset n envs (env_ids NULL = envs 0..n-1 in order; then n must be n_envs).  init_pos NULL =
+ * draw U(-1,1)^2 agents / landmarks (tag landmarks U(-0.9,0.9)^2) from Philox keyed by
+ * (seed, env, episode); else float [n][A+L][2].  obs_out (may be NULL): [n*A][obs_dim]. */
+int tsm_mpe_reset(const tsm_mpe* env, const int64_t* env_ids, int64_t n, const float* init_pos,
+                  float* obs_out, tsm_stream_t stream);
+
+/* one world step for all envs.  act [n_envs*A] in 0..4.  Outputs are row-ordered:
+ * obs_next [R][obs_dim], rew [R], terminated [R] (always 0), truncated [R].
+ * autoreset != 0: envs that truncate are re-drawn (Philox) inside the same launch and
+ * obs_carry [R][obs_dim] receives the observation the NEXT step must act on (reset obs for
+ * done envs, obs_next otherwise) -- collector.py:935,1028.  obs_carry may be NULL. */
+int tsm_mpe_step(const tsm_mpe* env, const int32_t* act, float* obs_next, float* rew,
+                 uint8_t* terminated, uint8_t* truncated, int autoreset, float* obs_carry,
+                 tsm_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -31,6 +31,17 @@ class TsmBuf(C.Structure):
     ]
 
 
+class TsmMpe(C.Structure):
+    """struct tsm_mpe (include/tsm_b200.h)."""
+
+    _fields_ = [
+        ("scenario", C.c_int32), ("n_agents", C.c_int32), ("n_landmarks", C.c_int32), ("n_adversaries", C.c_int32),
+        ("obs_dim", C.c_int32), ("max_cycles", C.c_int32), ("pos_first", C.c_int32), ("local_ratio", C.c_float),
+        ("n_envs", c_i64), ("seed", C.c_uint64),
+        ("pos", c_vp), ("vel", c_vp), ("lm", c_vp), ("steps", c_vp), ("episode", c_vp),
+    ]
+
+
 _SIGS = {
     "tsm_abi_version": (c_i32, []),
     "tsm_last_error": (C.c_char_p, []),
@@ -46,6 +57,8 @@ _SIGS = {
     "tsm_buf_prev": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_vp]),
     "tsm_buf_next": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_vp]),
     "tsm_buf_unfinished": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "tsm_mpe_reset": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_vp, c_vp]),
+    "tsm_mpe_step": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
     "tsm_buf_gather": (c_i32, [c_vp, c_vp, c_i64] + [c_vp] * 9 + [c_vp, c_vp, c_i32, c_vp]),
 }
 
