@@ -1,0 +1,275 @@
+#!/usr/bin/env python
+"""bench.py -- the contract bench of the hot path (see DESIGN.md "Measurement").
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --gpus N --steps K ...  # CPU arm (oracle port, host cores)
+
+A "step" is one pass of the hot path over one batch of synthetic input: collect T vector steps
+of `simple_spread_v3` over E environments per GPU (policy forward -> MPE world step -> replay
+buffer add), GAE over the collected [T, E*A] block, and the PPO minibatch update (`repeat`
+epochs).  Metric (BASELINE.json): agent-steps/s, whole job.  One process per GPU; environments
+shard across ranks with no data-path collective during collect/GAE (scaling: weak); the PPO
+update all-reduces the flat gradient over NCCL.
+
+Nothing here reads /root/reference.  oracle/ is executed only by the `cpu_baseline` leg and
+by `--impl reference`.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "agent-steps/sec collect+PPO update, simple_spread"
+UNIT = "agent-steps/s"
+GAE_BYTES_PER_ELT = 22  # read v_s 4 + v_next 4 + rew 4 + term 1 + trunc 1, write adv 4 + ret 4
+
+
+def parse() -> argparse.Namespace:
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=5)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    p.add_argument("--envs", type=int, default=65536, help="environments per GPU (C2: 65536)")
+    p.add_argument("--agents", type=int, default=3)
+    p.add_argument("--horizon", type=int, default=128, help="T: vector steps per collect")
+    p.add_argument("--batch-size", type=int, default=65536)
+    p.add_argument("--repeat", type=int, default=4)
+    p.add_argument("--hidden", type=int, default=64)
+    p.add_argument("--no-update", action="store_true", help="collect + GAE only")
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--cpu-envs", type=int, default=2048, help="reference arm: environments in the bounded sample")
+    p.add_argument("--cpu-horizon", type=int, default=32)
+    return p.parse_args()
+
+
+# ------------------------------------------------------------------------------------------
+# clocks sampler (B200_PROFILING.md "clocks DURING the timed region")
+class Clocks:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int) -> None:
+        self.index, self.rows, self._stop, self._th = index, [], threading.Event(), None
+
+    def _run(self) -> None:
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def __enter__(self) -> "Clocks":
+        self._th = threading.Thread(target=self._run, daemon=True)
+        self._th.start()
+        return self
+
+    def __exit__(self, *a) -> None:
+        self._stop.set()
+        if self._th:
+            self._th.join(timeout=6)
+
+    def summary(self) -> dict:
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+# ------------------------------------------------------------------------------------------
+# CPU arm: the oracle port (numpy / C restatement of the reference path) on the host cores
+def cpu_arm(args: argparse.Namespace, steps: int, warmup: int) -> dict:
+    """One 'step' = collect T_s vector steps over E_s simple_spread worlds (random-uniform
+    policy stand-in is NOT used: the policy MLP runs in torch fp32 on the CPU like the reference's
+    Net), buffer add state machine, GAE (serial float64 loop like numba `_gae`), PPO update."""
+    import torch
+
+    from oracle import gae as ogae
+    from oracle.gae import _clib
+
+    torch.set_num_threads(os.cpu_count() or 1)
+    lib = _clib()
+    E, A, T = args.cpu_envs, args.agents, args.cpu_horizon
+    R, O = E * A, 6 * A
+    rng = np.random.default_rng(0)
+    pos = rng.uniform(-1, 1, (E, 2 * A, 2))
+    vel = np.zeros((E, A, 2))
+    obs = np.zeros((R, O), np.float32)
+    rew = np.zeros(R)
+    ins, sz, ep_len, ep_start, last, lens = (np.zeros(R, np.int64) for _ in range(6))
+    ep_ret = np.zeros(R)
+    outs = [np.zeros(R, np.int64), np.zeros(R), np.zeros(R, np.int64), np.zeros(R, np.int64)]
+    store = {"obs": np.zeros((R * T, O), np.float32), "obs_next": np.zeros((R * T, O), np.float32),
+             "act": np.zeros(R * T, np.int64), "rew": np.zeros(R * T), "done": np.zeros(R * T, bool)}
+    try:
+        from oracle import ppo as oppo
+    except ImportError:
+        oppo = None
+    net = oppo.make_net(O, args.hidden, 5, seed=0) if (oppo is not None and not args.no_update) else None
+    P = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+
+    def one_step() -> None:
+        ins[:] = 0
+        sz[:] = 0
+        cur = obs.copy()
+        for t in range(T):
+            if net is not None:
+                act = oppo.act(net, cur)
+            else:
+                act = rng.integers(0, 5, R)
+            a32 = act.astype(np.int32)
+            lib.orc_mpe_spread_step(P(pos), P(vel), P(a32), C.c_int64(E), C.c_int(A), C.c_double(0.5), C.c_int(1), P(obs), P(rew))
+            done = np.full(R, (t + 1) % 25 == 0, np.uint8)
+            lib.orc_buf_add(P(ins), P(sz), P(ep_ret), P(ep_len), P(ep_start), P(last), P(lens), C.c_int64(T), None,
+                            P(rew), P(done), C.c_int64(R), *(P(o) for o in outs))
+            slot = outs[0]
+            store["obs"][slot] = cur
+            store["obs_next"][slot] = obs
+            store["act"][slot] = act
+            store["rew"][slot] = rew
+            store["done"][slot] = done.astype(bool)
+            cur = obs.copy()
+            if done[0]:
+                pos[:] = rng.uniform(-1, 1, pos.shape)
+                vel[:] = 0
+        B = R * T
+        if net is not None:
+            v_s, v_n = oppo.values(net, store["obs"]), oppo.values(net, store["obs_next"])
+        else:
+            v_s, v_n = np.zeros(B), np.zeros(B)
+        end = store["done"].copy()
+        end[T - 1::T] = True
+        adv = ogae.gae(v_s.astype(np.float64), v_n.astype(np.float64), store["rew"], end, 0.99, 0.95)
+        if net is not None:
+            oppo.update(net, store, adv, adv + v_s, batch_size=max(256, args.batch_size * R // (args.envs * A)), repeat=args.repeat)
+
+    for _ in range(warmup):
+        one_step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one_step()
+    dt = (time.perf_counter() - t0) / steps
+    return {"value": R * T / dt, "ms_per_step": dt * 1e3, "cores": os.cpu_count() or 1,
+            "sample": f"simple_spread E={E} A={A} T={T} per step, {'collect+GAE+PPO update' if net is not None else 'collect(random actions)+GAE'}, "
+                      f"oracle port (C/OpenMP MPE step + buffer add, serial f64 GAE, torch-fp32 CPU MLP)"}
+
+
+def reference_main(args: argparse.Namespace) -> None:
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    r = cpu_arm(args, max(1, args.steps), max(0, args.warmup))
+    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"C2 simple_spread_v3 A={args.agents}, bounded CPU sample: {r['sample']}"},
+            "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]},
+            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------
+def main() -> None:
+    args = parse()
+    if args.impl == "reference":
+        reference_main(args)
+        return
+    import torch
+    import torch.distributed as dist
+
+    from tianshou_marl_b200 import _lib
+    from tianshou_marl_b200.bench_workload import Workload
+
+    rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    _lib.lib()
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+
+    wl = Workload(args, rank, world)
+
+    def barrier() -> None:
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing ("value") ----
+    for _ in range(max(args.warmup, 3)):
+        wl.step()
+    barrier()
+    wl.reset_timers()
+    with Clocks(local) as clk:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            wl.step(timed=True)
+        e1.record()
+        barrier()
+    ms = e0.elapsed_time(e1) / args.steps
+    if world > 1:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    stages = wl.stage_ms(args.steps)
+    launches = wl.launches_per_step * args.steps
+
+    # ---- end to end through the public API with host round trips ("e2e") ----
+    for _ in range(2):
+        wl.step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(args.steps):
+        wl.step_e2e()
+    e1.record()
+    barrier()
+    ms_e2e = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3) / args.steps
+    if world > 1:
+        t = torch.tensor([ms_e2e], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_e2e = float(t.item())
+
+    if rank == 0:
+        units = wl.agent_steps_per_step * world
+        roof = wl.roofline(stages, hbm_peak, peak_src)
+        line = {"metric": METRIC, "value": units / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": wl.dtype, "data": "synthetic", "config": wl.config(),
+                "clocks": clk.summary(), "gpu_launches": launches,
+                "e2e": {"value": units / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
+                        "h2d_bytes_per_step": wl.h2d_bytes, "d2h_bytes_per_step": wl.d2h_bytes},
+                "stages_ms": stages, "roofline": roof}
+        if not args.no_cpu_baseline and world == 1:
+            r = cpu_arm(args, 1, 1)
+            line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -209,6 +209,14 @@ int tsm_mpe_step(const tsm_mpe* env, const int32_t* act, float* obs_next, float*
                  uint8_t* terminated, uint8_t* truncated, int autoreset, float* obs_carry,
                  tsm_stream_t stream);
 
+/* =========================================================================================
+ * Policy side of the rollout
+ * ========================================================================================= */
+/* uniform random actions in [0, n_act) for n rows: the collector's `random=True` branch
+ * (tianshou/data/collector.py:711-726).  Philox4x32-10, counter (row, step), key (seed, 'ACT!');
+ * act = mulhi(x0, n_act).  Restated by oracle/philox.py. */
+int tsm_random_actions(int32_t* act, int64_t n, int n_act, uint64_t seed, uint64_t step, tsm_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

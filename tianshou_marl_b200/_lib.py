@@ -59,6 +59,7 @@ _SIGS = {
     "tsm_buf_unfinished": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
     "tsm_mpe_reset": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_vp, c_vp]),
     "tsm_mpe_step": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
+    "tsm_random_actions": (c_i32, [c_vp, c_i64, c_i32, C.c_uint64, C.c_uint64, c_vp]),
     "tsm_buf_gather": (c_i32, [c_vp, c_vp, c_i64] + [c_vp] * 9 + [c_vp, c_vp, c_i32, c_vp]),
 }
 
