@@ -217,6 +217,101 @@ int tsm_mpe_step(const tsm_mpe* env, const int32_t* act, float* obs_next, float*
  * act = mulhi(x0, n_act).  Restated by oracle/philox.py. */
 int tsm_random_actions(int32_t* act, int64_t n, int n_act, uint64_t seed, uint64_t step, tsm_stream_t stream);
 
+/* =========================================================================================
+ * K4/K5/K6  actor-critic MLP, fused PPO minibatch, fused clip + Adam
+ * replaces  MLP.forward / Net.forward            tianshou/utils/net/common.py:173-181, :343-369
+ *           DiscreteActor / DiscreteCritic       tianshou/utils/net/discrete.py:67-89, :116-124
+ *           ProbabilisticActorPolicy.forward     tianshou/algorithm/modelfree/reinforce.py:167-192
+ *           _add_returns_and_advantages (critic) tianshou/algorithm/modelfree/a2c.py:113-127
+ *           PPO._preprocess_batch (logp_old)     tianshou/algorithm/modelfree/ppo.py:146-162
+ *           PPO._update_with_batch               tianshou/algorithm/modelfree/ppo.py:164-224
+ *           Batch.split (minibatch order)        tianshou/data/batch.py:1209-1226
+ *           Algorithm.Optimizer.step             tianshou/algorithm/algorithm_base.py:485-498
+ *           AdamOptimizerFactory defaults        tianshou/algorithm/optim.py:89-110
+ * Net shape: in_dim -> hidden -> hidden -> out_dim, ReLU, hidden in {64,128}.  Flat float32
+ * parameter layout (torch.nn.Linear convention weight[out][in]):
+ *     W1[H][in] b1[H] W2[H][H] b2[H] W3[out][H] b3[out]
+ * Head outputs 0..n_act-1 are action logits (Categorical(logits=...)); output `value_index`
+ * (>= n_act, or -1 for none) is the state value.  The shared actor-critic of the reference's PPO
+ * setup (one Net trunk, DiscreteActor.last + DiscreteCritic.last) is out_dim = n_act + 1.
+ * ========================================================================================= */
+typedef struct tsm_net {
+    int32_t in_dim, hidden, out_dim, n_act, value_index, _pad;
+    int64_t n_params;   /* == tsm_net_param_count(in_dim, hidden, out_dim) */
+    float* params;      /* [n_params] */
+    float* grads;       /* [n_params] accumulated by tsm_ppo_minibatch, zeroed by tsm_adam_step */
+    float* adam_m;      /* [n_params] exp_avg */
+    float* adam_v;      /* [n_params] exp_avg_sq */
+    int64_t* adam_step; /* [1] device step counter */
+} tsm_net;
+
+int64_t tsm_net_param_count(int in_dim, int hidden, int out_dim);
+
+/* Forward over n rows of x ([.][in_dim] float32; `rows` optionally gathers x rows, and with
+ * scatter != 0 results are written at those row ids instead of 0..n-1).
+ *   mode 0: raw head outputs -> out [n][out_dim]            (critic(obs), a2c.py:122-124)
+ *   mode 1: sample act ~ Categorical(logits) by inverse CDF on one Philox uniform keyed by
+ *           (seed, 'ACT!'), counter (row id, counter)        (reinforce.py:185-189, dist.sample())
+ *   mode 2: act = argmax logits                              (dist.mode, deterministic_eval)
+ *   mode 3: evaluate the given act                           (dist.log_prob(act), ppo.py:157-161)
+ * modes 1-3 write logp [n] (log-prob of act), optional value [n] (needs value_index >= 0),
+ * optional entropy [n], and optional logits -> out [n][n_act]. */
+int tsm_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int64_t n, int mode, int scatter,
+                    uint64_t seed, uint64_t counter, float* out, int32_t* act, float* logp, float* value,
+                    float* entropy, tsm_stream_t stream);
+
+/* The update batch, addressed in place inside the time-major device buffer ([size][n_rows]
+ * arrays, obs [size][n_rows][in_dim]).  Batch position p (0 <= p < B, the order of
+ * buffer.sample(0), manager.py:212-229) maps to a storage slot either through an explicit list
+ * of env-major buffer indices (`indices`, parity mode: indices[order[p]] drawn by numpy) or in
+ * closed form for a lock-step rollout: q = perm(p), row = q / len, slot = (start + q % len) % size
+ * with perm the keyed Feistel permutation of [0, perm_n) (perm_n = 0: identity). */
+typedef struct tsm_ppo_batch {
+    const float* obs;
+    const int32_t* act;
+    const float* adv;
+    const float* ret;
+    const float* logp_old;
+    const float* v_old;      /* only read when value_clip */
+    const int64_t* indices;  /* optional [B] env-major buffer indices */
+    int64_t size, n_rows, start, len;
+    uint64_t perm_key;
+    int64_t perm_n;
+} tsm_ppo_batch;
+
+typedef struct tsm_ppo_cfg {
+    float eps_clip;   /* ppo.py:25 (0.2) */
+    float dual_clip;  /* <= 0: off (ppo.py:26) */
+    float vf_coef;    /* a2c.py (0.5) */
+    float ent_coef;   /* a2c.py (0.01) */
+    int32_t value_clip;
+    int32_t adv_norm; /* advantage_normalization (ppo.py:184-186) */
+} tsm_ppo_cfg;
+
+/* per-minibatch {mean, 1/(std_unbiased + eps)} of adv: mb_bounds (device) [n_minibatches+1]
+ * batch positions; stats_out [n_minibatches][2]. */
+int tsm_ppo_adv_stats(const tsm_ppo_batch* batch, const int64_t* mb_bounds, int64_t n_minibatches, float eps,
+                      float* stats_out, tsm_stream_t stream);
+
+/* forward + clipped-surrogate / value / entropy loss + backward over batch positions
+ * [mb_start, mb_start + mb_len); parameter gradients are ADDED into net->grads.
+ * loss_sums (device, may be NULL) [3] += {sum_i clip_loss_i, sum_i vf_i, sum_i entropy_i}. */
+int tsm_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, int64_t mb_start,
+                      int64_t mb_len, const float* mb_stats, double* loss_sums, tsm_stream_t stream);
+
+/* g <- grads * grad_scale; optional global-norm clip (max_grad_norm > 0: g *= min(1, max/(|g|+1e-6)));
+ * torch.optim.Adam step (no weight decay, no amsgrad); grads zeroed; *adam_step += 1.
+ * grad_norm_out (device, may be NULL) receives |g| before clipping. */
+int tsm_adam_step(const tsm_net* net, float lr, float beta1, float beta2, float eps, float max_grad_norm,
+                  float grad_scale, float* grad_norm_out, tsm_stream_t stream);
+
+/* one epoch on one GPU: for each minibatch m: tsm_ppo_minibatch then tsm_adam_step.
+ * h_mb_bounds is a HOST array [n_minibatches+1]; mb_stats [n_minibatches][2] and loss_sums
+ * [n_minibatches][4] are device arrays (either may be NULL). */
+int tsm_ppo_epoch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, const int64_t* h_mb_bounds,
+                  int64_t n_minibatches, const float* mb_stats, float lr, float beta1, float beta2, float eps,
+                  float max_grad_norm, double* loss_sums, tsm_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -45,3 +45,49 @@ def u01(x) -> np.ndarray:
 STREAM_RESET = 0x52455345  # 'RESE'  key1 for env reset draws
 STREAM_ACT = 0x41435421  # 'ACT!'  key1 for action sampling draws
 STREAM_PERM = 0x5045524D  # 'PERM'  key1 for minibatch permutation keys
+
+
+# ----------------------------------------------------------------------------------------------
+# keyed Feistel permutation of [0, n) (csrc/feistel.cuh), restated for tests
+def _mix32(x: np.ndarray) -> np.ndarray:
+    x = x.astype(np.uint32)
+    with np.errstate(over="ignore"):
+        x = x ^ (x >> np.uint32(16))
+        x = x * np.uint32(0x7FEB352D)
+        x = x ^ (x >> np.uint32(15))
+        x = x * np.uint32(0x846CA68B)
+        x = x ^ (x >> np.uint32(16))
+    return x
+
+
+def feistel_bits(n: int) -> int:
+    bits = 2
+    while bits < 62 and (1 << bits) < n:
+        bits += 1
+    return bits
+
+
+def feistel_permute(x, n: int, key: int, rounds: int = 6) -> np.ndarray:
+    """Alternating unbalanced Feistel network over ceil(log2 n) bits with cycle walking."""
+    x = np.asarray(x, dtype=np.uint64).copy()
+    bits = feistel_bits(n)
+    a = bits >> 1
+    b = bits - a
+    mask_a, mask_b = np.uint32((1 << a) - 1), np.uint32((1 << b) - 1)
+    k0, k1 = np.uint32(key & 0xFFFFFFFF), np.uint32((key >> 32) & 0xFFFFFFFF)
+    todo = np.ones(x.shape, bool)
+    while todo.any():
+        v = x[todo]
+        lo = (v & np.uint64(int(mask_a))).astype(np.uint32)
+        hi = ((v >> np.uint64(a)) & np.uint64(int(mask_b))).astype(np.uint32)
+        for r in range(rounds):
+            with np.errstate(over="ignore"):
+                kr = _mix32(np.asarray(k0 + np.uint32(0x9E3779B9) * np.uint32(r + 1), dtype=np.uint32)) ^ k1
+            if r & 1:
+                lo = lo ^ (_mix32(hi ^ kr) & mask_a)
+            else:
+                hi = hi ^ (_mix32(lo ^ kr) & mask_b)
+        v = (hi.astype(np.uint64) << np.uint64(a)) | lo.astype(np.uint64)
+        x[todo] = v
+        todo[todo] = v >= np.uint64(n)
+    return x.astype(np.int64)

@@ -1,0 +1,127 @@
+"""More golden fixtures from the UNMODIFIED reference (imported through oracle/shims):
+`ppo` -- PPO._preprocess_batch + _update_with_batch + Optimizer.step on synthetic rollouts.
+See make_golden.py for how to run.  Never runs on the GPU box."""
+from __future__ import annotations
+
+import numpy as np
+
+from make_golden import save  # noqa: E402  (also sets sys.path for the reference + shims)
+
+
+def _ref_ppo(O: int, H: int, nA: int, seed: int, softmax_probs: bool, **ppo_kw):
+    import gymnasium as gym
+    import torch
+    from tianshou.algorithm import PPO
+    from tianshou.algorithm.modelfree.reinforce import DiscreteActorPolicy
+    from tianshou.algorithm.optim import AdamOptimizerFactory
+    from tianshou.utils.net.common import ActorCritic, Net
+    from tianshou.utils.net.discrete import DiscreteActor, DiscreteCritic
+
+    torch.manual_seed(seed)
+    net = Net(state_shape=(O,), hidden_sizes=[H, H])
+    actor = DiscreteActor(preprocess_net=net, action_shape=nA, softmax_output=softmax_probs)
+    critic = DiscreteCritic(preprocess_net=net)
+    ac = ActorCritic(actor, critic)
+    for m in ac.modules():  # test/discrete/test_ppo_discrete.py:101-105
+        if isinstance(m, torch.nn.Linear):
+            torch.nn.init.orthogonal_(m.weight)
+            torch.nn.init.normal_(m.bias, std=0.1)  # non-zero so that bias paths are exercised
+    if softmax_probs:
+        policy = DiscreteActorPolicy(actor=actor, dist_fn=torch.distributions.Categorical, action_space=gym.spaces.Discrete(nA))
+    else:
+        policy = DiscreteActorPolicy(actor=actor, action_space=gym.spaces.Discrete(nA))
+    lr = ppo_kw.pop("lr", 3e-4)
+    alg = PPO(policy=policy, critic=critic, optim=AdamOptimizerFactory(lr=lr), **ppo_kw)
+    return alg, ac
+
+
+def _flat_params(ac) -> dict[str, np.ndarray]:
+    sd = {k: v.detach().cpu().numpy().copy() for k, v in ac.state_dict().items()}
+    # shared trunk appears under actor.preprocess.* and critic.preprocess.* (same tensors)
+    pick = lambda suffix, root: next(v for k, v in sd.items() if k.startswith(root) and k.endswith(suffix))  # noqa: E731
+    return {
+        "W1": pick("model.model.0.weight", "actor.preprocess"), "b1": pick("model.model.0.bias", "actor.preprocess"),
+        "W2": pick("model.model.2.weight", "actor.preprocess"), "b2": pick("model.model.2.bias", "actor.preprocess"),
+        "Wa": pick("last.model.0.weight", "actor"), "ba": pick("last.model.0.bias", "actor"),
+        "Wv": pick("last.model.0.weight", "critic"), "bv": pick("last.model.0.bias", "critic"),
+    }
+
+
+def gen_ppo() -> None:
+    import torch
+    from tianshou.data import Batch, VectorReplayBuffer
+    from tianshou.data.stats import SequenceSummaryStats
+    from tianshou.utils.torch_utils import policy_within_training_step, torch_train_mode
+
+    out: dict[str, np.ndarray] = {}
+    cases = [
+        # R rows, T steps, O, H, nA, batch_size, repeat, probs-parameterisation, PPO kwargs
+        dict(R=24, T=16, O=18, H=64, nA=5, bs=128, repeat=2, probs=False, kw=dict()),
+        dict(R=12, T=25, O=18, H=64, nA=5, bs=64, repeat=3, probs=False,
+             kw=dict(max_grad_norm=0.5, value_clip=True, dual_clip=3.0, advantage_normalization=False, lr=1e-3)),
+        dict(R=8, T=13, O=16, H=64, nA=5, bs=40, repeat=2, probs=True, kw=dict(max_grad_norm=0.5, ent_coef=0.05, vf_coef=0.25)),
+        dict(R=6, T=12, O=60, H=128, nA=5, bs=36, repeat=2, probs=False, kw=dict(max_grad_norm=1.0, eps_clip=0.1)),
+    ]
+    for ci, c in enumerate(cases):
+        R, T, O, H, nA = c["R"], c["T"], c["O"], c["H"], c["nA"]
+        rng = np.random.default_rng(100 + ci)
+        alg, ac = _ref_ppo(O, H, nA, seed=ci, softmax_probs=c["probs"], **dict(c["kw"]))
+        pre = f"p{ci}_"
+        for k, v in _flat_params(ac).items():
+            out[pre + k] = v
+        buf = VectorReplayBuffer(R * T, R)
+        obs = rng.normal(size=(R, O)).astype(np.float32)
+        store = {k: [] for k in ("obs", "act", "rew", "term", "trunc", "obs_next")}
+        for t in range(T):
+            act = rng.integers(0, nA, R)
+            rew = rng.normal(size=R).astype(np.float32).astype(np.float64)  # f32-representable rewards
+            trunc = np.full(R, (t + 1) % 5 == 0) & (rng.random(R) < 0.9)
+            term = (rng.random(R) < 0.05) & ~trunc
+            obs_next = (obs + rng.normal(size=(R, O)) * 0.3).astype(np.float32)
+            buf.add(Batch(obs=obs, act=act, rew=rew, terminated=term, truncated=trunc, obs_next=obs_next, info={}))
+            for k, v in zip(store, (obs, act, rew, term, trunc, obs_next)):
+                store[k].append(np.array(v))
+            done = term | trunc
+            obs = np.where(done[:, None], rng.normal(size=(R, O)).astype(np.float32), obs_next)
+        for k, v in store.items():
+            out[pre + k] = np.stack(v)  # [T][R]...
+        # one deterministic forward with the INITIAL weights for the policy-forward check
+        with torch.no_grad():
+            x = torch.from_numpy(store["obs"][0])
+            logits, _ = alg.policy.actor(x)
+            out[pre + "fwd_actor_out"] = logits.numpy().copy()
+            out[pre + "fwd_value"] = alg.critic(x).flatten().numpy().copy()
+        seqs: list[list[float]] = []
+        orig = SequenceSummaryStats.from_sequence.__func__
+
+        def spy(cls, seq, _orig=orig, _seqs=seqs):
+            _seqs.append([float(x) for x in seq])
+            return _orig(cls, seq)
+
+        SequenceSummaryStats.from_sequence = classmethod(spy)
+        try:
+            np.random.seed(7 + ci)
+            with policy_within_training_step(alg.policy):
+                batch, indices = buf.sample(0)
+                batch = alg._preprocess_batch(batch, buf, indices)
+                out[pre + "indices"] = np.asarray(indices)
+                for k in ("v_s", "returns", "adv", "logp_old"):
+                    out[pre + k] = batch[k].detach().cpu().numpy().copy()
+                with torch_train_mode(alg):
+                    stats = alg._update_with_batch(batch, c["bs"], c["repeat"])
+        finally:
+            SequenceSummaryStats.from_sequence = classmethod(orig)
+        out[pre + "loss_seq"], out[pre + "clip_seq"], out[pre + "vf_seq"], out[pre + "ent_seq"] = (np.array(s) for s in seqs[:4])
+        out[pre + "gradient_steps"] = np.array(stats.gradient_steps)
+        for k, v in _flat_params(ac).items():
+            out[pre + "after_" + k] = v
+        kw = c["kw"]
+        out[pre + "cfg"] = np.array([R, T, O, H, nA, c["bs"], c["repeat"], int(c["probs"]), 7 + ci], np.int64)
+        out[pre + "hyper"] = np.array([kw.get("eps_clip", 0.2), kw.get("dual_clip") or 0.0, kw.get("vf_coef", 0.5), kw.get("ent_coef", 0.01),
+                                       float(kw.get("value_clip", False)), float(kw.get("advantage_normalization", True)),
+                                       kw.get("max_grad_norm") or 0.0, kw.get("lr", 3e-4), 0.99, 0.95])
+    out["n_cases"] = np.array(len(cases))
+    save("ppo.npz", **out)
+
+
+GENS = {"ppo": gen_ppo}

@@ -1,0 +1,36 @@
+"""Pins oracle/ppo.py (torch-fp32 restatement) to fixtures recorded from the reference PPO
+(tests/golden/ppo.npz <- tests/golden/make_golden_more.py).  Tolerances: fp32 reductions in a
+different association order -> rtol 2e-5 on values, 1e-4 on losses, 2e-5 abs on parameters."""
+import numpy as np
+import pytest
+
+from oracle import ppo as oppo
+from _ppo_golden import load_case
+
+
+@pytest.mark.parametrize("ci", [0, 1, 2, 3])
+def test_oracle_matches_reference_ppo(golden, ci):
+    c = load_case(golden("ppo.npz"), ci)
+    net = oppo.Net(c["W1"], c["b1"], c["W2"], c["b2"], c["W3"], c["b3"], c["nA"])
+    f = c["flat"]
+    # forward pin (actor output is probabilities when the reference ran softmax_output=True)
+    import torch
+
+    with torch.no_grad():
+        logits, value = net.forward(torch.from_numpy(c["obs"][0]))
+        a_out = torch.softmax(logits, -1) if c["probs"] else logits
+    assert np.allclose(a_out.numpy(), c["fwd_actor_out"], rtol=1e-5, atol=1e-6)
+    assert np.allclose(value.numpy(), c["fwd_value"], rtol=1e-5, atol=1e-6)
+    v_s, ret, adv, logp_old = oppo.preprocess(net, f["obs"], f["obs_next"], f["act"], f["rew"], f["term"], f["trunc"], c["indices"],
+                                              c["unfinished"], c["gamma"], c["lam"], c["probs"])
+    assert np.allclose(v_s, c["v_s"], rtol=2e-5, atol=2e-6)
+    assert np.allclose(ret, c["returns"], rtol=2e-5, atol=2e-5)
+    assert np.allclose(adv, c["adv"], rtol=2e-5, atol=2e-5)
+    assert np.allclose(logp_old, c["logp_old"], rtol=2e-5, atol=2e-6)
+    log = oppo.update_with_orders(net, f["obs"], f["act"], c["adv"], c["returns"], c["logp_old"], c["v_s"], c["cfg"], c["orders"],
+                                  c["bs"], c["lr"], c["max_norm"], c["probs"])
+    assert len(log["loss"]) == len(c["loss_seq"])
+    for k, ref in (("loss", "loss_seq"), ("clip", "clip_seq"), ("vf", "vf_seq"), ("ent", "ent_seq")):
+        assert np.allclose(log[k], c[ref], rtol=1e-4, atol=1e-5), (k, np.abs(np.array(log[k]) - c[ref]).max())
+    for k, p in zip(("W1", "b1", "W2", "b2", "W3", "b3"), net.p):
+        assert np.allclose(p.detach().numpy(), c["after_" + k], rtol=0, atol=2e-5), (k, np.abs(p.detach().numpy() - c["after_" + k]).max())

@@ -42,6 +42,36 @@ class TsmMpe(C.Structure):
     ]
 
 
+class TsmNet(C.Structure):
+    """struct tsm_net (include/tsm_b200.h)."""
+
+    _fields_ = [
+        ("in_dim", C.c_int32), ("hidden", C.c_int32), ("out_dim", C.c_int32), ("n_act", C.c_int32),
+        ("value_index", C.c_int32), ("_pad", C.c_int32), ("n_params", c_i64),
+        ("params", c_vp), ("grads", c_vp), ("adam_m", c_vp), ("adam_v", c_vp), ("adam_step", c_vp),
+    ]
+
+
+class TsmPpoBatch(C.Structure):
+    """struct tsm_ppo_batch (include/tsm_b200.h)."""
+
+    _fields_ = [
+        ("obs", c_vp), ("act", c_vp), ("adv", c_vp), ("ret", c_vp), ("logp_old", c_vp), ("v_old", c_vp), ("indices", c_vp),
+        ("size", c_i64), ("n_rows", c_i64), ("start", c_i64), ("len", c_i64), ("perm_key", C.c_uint64), ("perm_n", c_i64),
+    ]
+
+
+class TsmPpoCfg(C.Structure):
+    """struct tsm_ppo_cfg (include/tsm_b200.h)."""
+
+    _fields_ = [
+        ("eps_clip", C.c_float), ("dual_clip", C.c_float), ("vf_coef", C.c_float), ("ent_coef", C.c_float),
+        ("value_clip", C.c_int32), ("adv_norm", C.c_int32),
+    ]
+
+
+c_f32, c_u64 = C.c_float, C.c_uint64
+
 _SIGS = {
     "tsm_abi_version": (c_i32, []),
     "tsm_last_error": (C.c_char_p, []),
@@ -60,6 +90,12 @@ _SIGS = {
     "tsm_mpe_reset": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_vp, c_vp]),
     "tsm_mpe_step": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
     "tsm_random_actions": (c_i32, [c_vp, c_i64, c_i32, C.c_uint64, C.c_uint64, c_vp]),
+    "tsm_net_param_count": (c_i64, [c_i32, c_i32, c_i32]),
+    "tsm_net_forward": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_u64, c_u64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "tsm_ppo_adv_stats": (c_i32, [c_vp, c_vp, c_i64, c_f32, c_vp, c_vp]),
+    "tsm_ppo_minibatch": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i64, c_vp, c_vp, c_vp]),
+    "tsm_adam_step": (c_i32, [c_vp, c_f32, c_f32, c_f32, c_f32, c_f32, c_f32, c_vp, c_vp]),
+    "tsm_ppo_epoch": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_f32, c_f32, c_f32, c_f32, c_f32, c_vp, c_vp]),
     "tsm_buf_gather": (c_i32, [c_vp, c_vp, c_i64] + [c_vp] * 9 + [c_vp, c_vp, c_i32, c_vp]),
 }
 
@@ -106,6 +142,8 @@ def check(rc: int) -> None:
     msg = lib().tsm_last_error().decode(errors="replace")
     if rc == -1:
         raise ValueError(msg)
+    if rc == -4:
+        raise NotImplementedError(msg)
     raise TsmError(f"tsm error {rc}: {msg}")
 
 

@@ -1,0 +1,302 @@
+"""PPO on the device (K4/K5/K6): drop-in for the reference's on-policy update path
+
+    OnPolicyAlgorithm.update            tianshou/algorithm/algorithm_base.py:852-863
+    Algorithm._update                   tianshou/algorithm/algorithm_base.py:584-629
+    PPO._preprocess_batch               tianshou/algorithm/modelfree/ppo.py:146-162
+    A2C-base._add_returns_and_advantages tianshou/algorithm/modelfree/a2c.py:113-151
+    PPO._update_with_batch              tianshou/algorithm/modelfree/ppo.py:164-224
+    Algorithm.Optimizer.step            tianshou/algorithm/algorithm_base.py:485-498
+    DiscreteActorPolicy / ProbabilisticActorPolicy.forward   reinforce.py:167-215
+
+All arithmetic runs in libtsm_b200 (csrc/mlp.cu, gae.cu); this module orders the launches.
+The update batch is never gathered: kernels address the time-major device buffer in place.
+
+Minibatch order: `minibatch_order="numpy"` draws np.random.permutation(B) per epoch from the
+global numpy RNG exactly like Batch.split (batch.py:1219) -- bit-exact minibatch index lists;
+`"device"` (default) uses the keyed Feistel permutation evaluated inside the kernels (no index
+arrays, different but equally uniform order).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import time
+from dataclasses import dataclass
+from typing import Any
+
+import numpy as np
+import torch
+
+from .. import _lib
+from ..data.batch import Batch
+from ..utils.net import ActorCriticNet
+from ..utils.stats import A2CTrainingStats, SequenceSummaryStats
+from .returns import gae_flat, gae_time_major
+
+
+@dataclass
+class AdamOptimizerFactory:
+    """tianshou/algorithm/optim.py:89-110 (defaults lr 1e-3, betas (0.9, 0.999), eps 1e-8, no weight decay)."""
+
+    lr: float = 1e-3
+    betas: tuple[float, float] = (0.9, 0.999)
+    eps: float = 1e-8
+    weight_decay: float = 0.0
+
+    def __post_init__(self) -> None:
+        if self.weight_decay != 0.0:
+            raise NotImplementedError("weight_decay != 0 is not on this path")
+
+
+class DiscreteActorPolicy:
+    """reinforce.py:195-247 / :167-192: logits -> Categorical -> sample (or mode when
+    deterministic_eval and not within a training step).  One fused kernel per call."""
+
+    def __init__(self, *, actor: ActorCriticNet, action_space: Any = None, observation_space: Any = None,
+                 deterministic_eval: bool = False, seed: int = 0, **kwargs: Any) -> None:
+        self.actor = actor
+        self.action_space, self.observation_space = action_space, observation_space
+        self.deterministic_eval = deterministic_eval
+        self.is_within_training_step = False
+        self.training = False
+        self.seed = int(seed)
+        self._counter = 0
+
+    def train(self, mode: bool = True) -> "DiscreteActorPolicy":
+        self.training = mode
+        return self
+
+    def eval(self) -> "DiscreteActorPolicy":
+        return self.train(False)
+
+    def map_action(self, act: Any) -> Any:
+        return act  # identity for Discrete (algorithm_base.py:255-288)
+
+    def forward(self, batch: Any, state: Any = None, **kwargs: Any) -> Batch:
+        obs = batch.obs if hasattr(batch, "obs") else batch["obs"]
+        if isinstance(obs, Batch):
+            obs = obs["obs"]
+        if not (isinstance(obs, torch.Tensor) and obs.is_cuda):
+            obs = torch.as_tensor(np.ascontiguousarray(obs), dtype=torch.float32, device=self.actor.device)
+        obs = obs.to(torch.float32).contiguous()
+        mode = "mode" if (self.deterministic_eval and not self.is_within_training_step) else "sample"
+        o = self.actor.forward(obs, mode=mode, seed=self.seed, counter=self._counter, want_logits=True)
+        self._counter += 1
+        out = Batch()
+        out.__dict__.update(logits=o["logits"], act=o["act"].to(torch.int64), state=None, logp=o["logp"])
+        if "value" in o:
+            out.__dict__["value"] = o["value"]
+        out.__dict__["dist"] = torch.distributions.Categorical(logits=o["logits"]) if kwargs.get("want_dist") else None
+        return out
+
+    __call__ = forward
+
+
+class PPO:
+    def __init__(self, *, policy: DiscreteActorPolicy, critic: ActorCriticNet | None = None,
+                 optim: AdamOptimizerFactory | None = None, eps_clip: float = 0.2, dual_clip: float | None = None,
+                 value_clip: bool = False, advantage_normalization: bool = True, recompute_advantage: bool = False,
+                 vf_coef: float = 0.5, ent_coef: float = 0.01, max_grad_norm: float | None = None, gae_lambda: float = 0.95,
+                 max_batchsize: int = 256, gamma: float = 0.99, return_scaling: bool = False,
+                 minibatch_order: str = "device", reuse_rollout_policy_outputs: bool = False, seed: int = 0) -> None:
+        assert dual_clip is None or dual_clip > 1.0, f"Dual-clip PPO parameter should greater than 1.0 but got {dual_clip}"  # ppo.py
+        assert 0.0 <= gamma <= 1.0 and 0.0 <= gae_lambda <= 1.0
+        if return_scaling:
+            raise NotImplementedError("return_scaling (RunningMeanStd) is a next-tier row, not built yet")
+        if critic is not None and critic is not policy.actor:
+            raise NotImplementedError("separate critic network: use the CTDE path")
+        if policy.actor.value_index < 0:
+            raise ValueError("the shared actor-critic net needs a value head (with_value=True)")
+        if minibatch_order not in ("device", "numpy"):
+            raise ValueError("minibatch_order must be 'device' or 'numpy'")
+        self.policy, self.net = policy, policy.actor
+        self.critic = self.net
+        self.optim = optim or AdamOptimizerFactory()
+        self.eps_clip, self.dual_clip, self.value_clip = eps_clip, dual_clip, value_clip
+        self.advantage_normalization, self.recompute_adv = advantage_normalization, recompute_advantage
+        self.vf_coef, self.ent_coef, self.max_grad_norm = vf_coef, ent_coef, max_grad_norm
+        self.gae_lambda, self.gamma, self.max_batchsize = gae_lambda, gamma, max_batchsize
+        self.minibatch_order = minibatch_order
+        self.reuse_rollout = reuse_rollout_policy_outputs
+        self._eps = 1e-8
+        self._epoch_counter = 0
+        self._seed = seed
+        self.training = False
+        self._cfg = _lib.TsmPpoCfg(eps_clip=eps_clip, dual_clip=dual_clip or 0.0, vf_coef=vf_coef, ent_coef=ent_coef,
+                                   value_clip=int(value_clip), adv_norm=int(advantage_normalization))
+        self._work: dict[str, torch.Tensor] = {}
+        self.last_profile: dict[str, float] = {}
+
+    # nn.Module-like surface the reference's trainer / collector touch
+    def train(self, mode: bool = True) -> "PPO":
+        self.training = mode
+        return self
+
+    def eval(self) -> "PPO":
+        return self.train(False)
+
+    def __call__(self, batch: Any, state: Any = None, **kw: Any) -> Batch:
+        return self.policy(batch, state, **kw)
+
+    def state_dict(self) -> dict[str, Any]:
+        """algorithm_base.py:521-541: module parameters + optimizer states under `_optimizers`."""
+        n = self.net
+        return {"policy.actor.flat": n.flat.detach().clone(),
+                "_optimizers": [{"exp_avg": n.adam_m.clone(), "exp_avg_sq": n.adam_v.clone(), "step": n.adam_step.clone()}]}
+
+    def load_state_dict(self, sd: dict[str, Any]) -> None:
+        n = self.net
+        with torch.no_grad():
+            n.flat.copy_(sd["policy.actor.flat"])
+            if sd.get("_optimizers"):
+                o = sd["_optimizers"][0]
+                n.adam_m.copy_(o["exp_avg"]); n.adam_v.copy_(o["exp_avg_sq"]); n.adam_step.copy_(o["step"])
+
+    # -- helpers ------------------------------------------------------------------------------
+    def _buf(self, name: str, shape: tuple[int, ...], dtype: torch.dtype = torch.float32) -> torch.Tensor:
+        t = self._work.get(name)
+        if t is None or tuple(t.shape) != tuple(shape) or t.dtype != dtype:
+            t = torch.empty(shape, dtype=dtype, device=self.net.device)
+            self._work[name] = t
+        return t
+
+    @staticmethod
+    def split_bounds(length: int, size: int | None) -> list[int]:
+        """Batch.split(size, merge_last=True) boundaries (batch.py:1209-1226)."""
+        if size is None or size <= 0 or size == -1:
+            size = length
+        merge = length % size > 0
+        b = [0]
+        for idx in range(0, length, size):
+            if merge and idx + size + size >= length:
+                b.append(length)
+                break
+            b.append(min(idx + size, length))
+        return b
+
+    # -- the update ---------------------------------------------------------------------------
+    def update(self, buffer: Any, batch_size: int | None, repeat: int) -> A2CTrainingStats:
+        if not self.policy.is_within_training_step:
+            raise RuntimeError(
+                f"update() was called outside of a training step as signalled by {self.policy.is_within_training_step=} "
+                "If you want to update the policy without a Trainer, you will have to manage the above-mentioned flag yourself.")
+        if buffer is None:
+            return A2CTrainingStats(*(SequenceSummaryStats.from_sequence([]) for _ in range(4)))
+        t0 = time.time()
+        net, L, P, S = self.net, _lib.lib(), _lib.ptr, _lib.stream_ptr()
+        st = buffer._store
+        size, R, O = buffer._size, buffer.buffer_num, net.in_dim
+        lock_len = buffer._lockstep_len
+        lockstep = lock_len is not None and lock_len > 0
+        obs_all = st["obs"].view(size * R, O)
+        v_s = self._buf("v_s", (size, R))
+        v_n = self._buf("v_n", (size, R))
+        logp = self._buf("logp_old", (size, R))
+        adv = self._buf("adv", (size, R))
+        ret = self._buf("ret", (size, R))
+        # ---- _add_returns_and_advantages (a2c.py:113-151): critic(obs), critic(obs_next) ----
+        if self.reuse_rollout and "value" in st and "logp" in st:
+            raise NotImplementedError("reuse_rollout_policy_outputs is wired by the fused collector")
+        net.forward(obs_all, mode="raw", out={"value": v_s.view(-1)})
+        net.forward(st["obs_next"].view(size * R, O), mode="raw", out={"value": v_n.view(-1)})
+        if lockstep:
+            start = buffer._lockstep_ins if lock_len == size else 0
+            B = lock_len * R
+            gae_time_major(v_s, v_n, st["rew"], st["terminated"], st["truncated"], start, lock_len, self.gamma, self.gae_lambda, adv, ret)
+            idx_all = None
+        else:
+            idx_all = buffer._all_indices_device()
+            B = int(idx_all.numel())
+            if B == 0:
+                return A2CTrainingStats(*(SequenceSummaryStats.from_sequence([]) for _ in range(4)))
+            slot = (idx_all % size) * R + idx_all // size
+            g = lambda t: t.view(-1)[slot]  # noqa: E731
+            unf = buffer._unfinished_device()
+            mask = torch.zeros(buffer.maxsize, dtype=torch.uint8, device=net.device)
+            mask[unf] = 1
+            r_f, a_f = gae_flat(g(v_s), g(v_n), g(st["rew"]), g(st["terminated"]), g(st["truncated"]), mask[idx_all], 0,
+                                self.gamma, self.gae_lambda)
+            adv.view(-1)[slot] = a_f
+            ret.view(-1)[slot] = r_f
+            start, lock_len = 0, size
+        # ---- logp_old (ppo.py:157-161) ----
+        net.forward(obs_all, mode="eval", act=st["act"].view(-1), out={"logp": logp.view(-1), "value": self._buf("scratch_v", (size * R,))})
+        # ---- minibatch loop (ppo.py:173-216) ----
+        bounds = self.split_bounds(B, batch_size)
+        n_mb = len(bounds) - 1
+        bounds_dev = torch.tensor(bounds, dtype=torch.int64, device=net.device)
+        h_bounds = (C.c_int64 * len(bounds))(*bounds)
+        stats = self._buf("mb_stats", (repeat * n_mb, 2))
+        sums = self._buf("loss_sums", (repeat * n_mb, 4), torch.float64)
+        sums.zero_()
+        pb = _lib.TsmPpoBatch(obs=P(st["obs"]), act=P(st["act"]), adv=P(adv), ret=P(ret), logp_old=P(logp), v_old=P(v_s),
+                              indices=None, size=size, n_rows=R, start=start, len=lock_len, perm_key=0, perm_n=0)
+        world = torch.distributed.get_world_size() if torch.distributed.is_available() and torch.distributed.is_initialized() else 1
+        o = self.optim
+        mgn = float(self.max_grad_norm) if self.max_grad_norm else 0.0
+        keep = []  # keep explicit index tensors alive until the stream has consumed them
+        for ep in range(repeat):
+            if self.recompute_adv and ep > 0:
+                raise NotImplementedError("recompute_advantage is a next-tier row, not built yet")
+            if self.minibatch_order == "numpy":
+                order = torch.as_tensor(np.random.permutation(B), device=net.device)  # batch.py:1219
+                explicit = order if idx_all is None and start == 0 and lock_len == size else (
+                    idx_all[order] if idx_all is not None else self._lockstep_indices(order, start, lock_len, size))
+            elif idx_all is not None:
+                gen = torch.Generator(device=net.device).manual_seed(self._seed * 1000003 + self._epoch_counter)
+                explicit = idx_all[torch.randperm(B, device=net.device, generator=gen)]
+            else:
+                explicit = None
+            if explicit is not None:
+                keep.append(explicit)
+                pb.indices, pb.perm_n = P(explicit), 0
+            else:
+                pb.indices, pb.perm_n = None, B
+                pb.perm_key = (self._seed * 0x9E3779B97F4A7C15 + self._epoch_counter * 0xD1B54A32D192ED03 + 0x632BE59BD9B4E019) & (2**64 - 1)
+            self._epoch_counter += 1
+            st_ep, sums_ep = stats[ep * n_mb:], sums[ep * n_mb:]
+            if self.advantage_normalization:
+                _lib.check(L.tsm_ppo_adv_stats(C.byref(pb), P(bounds_dev), n_mb, self._eps, P(st_ep), S))
+            if world == 1:
+                _lib.check(L.tsm_ppo_epoch(net.desc, C.byref(pb), C.byref(self._cfg), h_bounds, n_mb,
+                                           P(st_ep) if self.advantage_normalization else None, o.lr, o.betas[0], o.betas[1], o.eps,
+                                           mgn, P(sums_ep), S))
+            else:
+                for m in range(n_mb):
+                    _lib.check(L.tsm_ppo_minibatch(net.desc, C.byref(pb), C.byref(self._cfg), bounds[m], bounds[m + 1] - bounds[m],
+                                                   P(st_ep[m:]) if self.advantage_normalization else None, P(sums_ep[m:]), S))
+                    torch.distributed.all_reduce(net.grads)  # NCCL sum over ranks
+                    _lib.check(L.tsm_adam_step(net.desc, o.lr, o.betas[0], o.betas[1], o.eps, mgn, 1.0 / world, None, S))
+        # ---- stats: one device -> host copy for the whole update (the reference does 4 .item() per minibatch) ----
+        h = sums.cpu().numpy()
+        n_per = np.tile(np.diff(np.asarray(bounds)), repeat).astype(np.float64)
+        clip_l, vf_l, ent_l = h[:, 0] / n_per, h[:, 1] / n_per, h[:, 2] / n_per
+        loss = clip_l + self.vf_coef * vf_l - self.ent_coef * ent_l
+        del keep
+        out = A2CTrainingStats(loss=SequenceSummaryStats.from_sequence(loss), actor_loss=SequenceSummaryStats.from_sequence(clip_l),
+                               vf_loss=SequenceSummaryStats.from_sequence(vf_l), ent_loss=SequenceSummaryStats.from_sequence(ent_l),
+                               gradient_steps=repeat * n_mb)
+        out.train_time = time.time() - t0
+        self.last_sequences = {"loss": loss, "clip": clip_l, "vf": vf_l, "ent": ent_l}
+        return out
+
+    @staticmethod
+    def _lockstep_indices(order: torch.Tensor, start: int, length: int, size: int) -> torch.Tensor:
+        """batch position -> env-major buffer index for a lock-step ring view."""
+        row, j = order // length, order % length
+        return row * size + (start + j) % size
+
+
+def ppo_smoke() -> None:
+    """Used by __graft_entry__.smoke(): one tiny PPO minibatch update vs the torch-fp32 oracle."""
+    from oracle import ppo as oppo  # checker only (smoke is test infrastructure)
+
+    torch.manual_seed(0)
+    R, T, O, nA = 16, 8, 18, 5
+    onet = oppo.make_net(O, 64, nA, seed=1)
+    net = ActorCriticNet(O, 64, nA).load_arrays(*[p.detach().numpy() for p in onet.p])
+    obs = torch.randn(T * R, O, device="cuda")
+    o = net.forward(obs, mode="sample", seed=3, counter=0, want_logits=True)
+    with torch.no_grad():
+        lg, v = onet.forward(obs.cpu())
+    assert torch.allclose(o["logits"].cpu(), lg, rtol=1e-4, atol=1e-5), "policy forward mismatch"
+    assert torch.allclose(o["value"].cpu(), v, rtol=1e-4, atol=1e-5), "value forward mismatch"

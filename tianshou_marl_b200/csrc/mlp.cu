@@ -1,0 +1,918 @@
+// mlp.cu -- K4/K5/K6 (fp32 CUDA-core path): actor-critic MLP forward, fused PPO
+// forward+loss+backward over a minibatch, fused grad-norm-clip + Adam (sm_100a).
+//
+// Replaces, for nets of the shape  in -> H -> H -> out  with ReLU (H in {64,128}),
+//   tianshou/utils/net/common.py:90-181,286-369 (MLP / Net forward),
+//   tianshou/utils/net/discrete.py:67-89,116-124 (DiscreteActor / DiscreteCritic heads),
+//   tianshou/algorithm/modelfree/reinforce.py:167-192 (ProbabilisticActorPolicy.forward: dist + sample),
+//   tianshou/algorithm/modelfree/ppo.py:157-161 (logp_old), :179-216 (clipped-surrogate minibatch loss),
+//   tianshou/algorithm/algorithm_base.py:485-498 (Optimizer.step: zero_grad, backward, clip_grad_norm_, Adam),
+//   tianshou/algorithm/optim.py:89-110 (Adam hyper-parameters).
+//
+// This file is the exact-fp32 path (parity mode, and the checker for the tcgen05 path in
+// mlp_tc.cu).  A CTA owns a tile of TM rows; activations live in shared memory TRANSPOSED
+// ([feature][row], leading dimension TM+4) so that both the layer GEMMs (k = feature) and the
+// weight-gradient GEMMs (k = row) read 16-byte vectors without bank conflicts.  Weight
+// gradients accumulate in registers across all tiles of a (persistent) CTA and are added to
+// the flat gradient buffer once per CTA.
+//
+// Flat parameter layout (float32, torch.nn.Linear convention weight[out][in]):
+//   W1[H][IN] b1[H] W2[H][H] b2[H] W3[OUT][H] b3[OUT]
+// For the shared actor-critic OUT = n_act + 1: rows 0..n_act-1 of W3 are the
+// actor head (DiscreteActor.last), row n_act is the critic head (DiscreteCritic.last).
+#include <algorithm>
+#include "common.cuh"
+#include "philox.cuh"
+#include "feistel.cuh"
+
+namespace tsm {
+namespace mlp {
+
+constexpr int THREADS = 256;
+constexpr int OUTP = 8;  // head width padded to 8 (OUT <= 8)
+
+template <int H>
+struct Cfg {
+    static constexpr int TM = (H == 64) ? 128 : 64;  // rows per tile
+    static constexpr int LD = TM + 4;                // leading dim of transposed activation tiles
+    static constexpr int LDW = H + 4;                // leading dim of W2 / W3 (torch layout) in smem
+    static constexpr int RC = TM / 64;               // row chunks of 4 per thread in the layer GEMMs
+    static constexpr int CC = H / 64;                // col chunks of 4 per thread
+};
+
+struct Offsets {
+    int64_t w1, b1, w2, b2, w3, b3, total;
+};
+__host__ __device__ inline Offsets offsets(int in_dim, int H, int out_dim) {
+    Offsets o;
+    o.w1 = 0;
+    o.b1 = (int64_t)H * in_dim;
+    o.w2 = o.b1 + H;
+    o.b2 = o.w2 + (int64_t)H * H;
+    o.w3 = o.b2 + H;
+    o.b3 = o.w3 + (int64_t)out_dim * H;
+    o.total = o.b3 + out_dim;
+    return o;
+}
+
+template <int H>
+struct Smem {
+    // all offsets in floats
+    int xrows;  // 16 * ceil(in/16): rows of sXT (zero beyond in_dim)
+    int w1t, w2, w3, b1, b2, b3, xt, h1t, h2t, dot, slot, red, total;
+    __host__ __device__ Smem(int in_dim) {
+        using C = Cfg<H>;
+        xrows = (in_dim + 15) / 16 * 16;
+        int p = 0;
+        w1t = p; p += xrows * H;
+        w2 = p;  p += H * C::LDW;
+        w3 = p;  p += OUTP * C::LDW;
+        b1 = p;  p += H;
+        b2 = p;  p += H;
+        b3 = p;  p += OUTP;
+        xt = p;  p += xrows * C::LD;
+        h1t = p; p += H * C::LD;
+        h2t = p; p += H * C::LD;
+        dot = p; p += OUTP * C::LD;      // head outputs [TM][OUTP] (forward) / dOut^T [OUTP][LD] (backward)
+        slot = p; p += 2 * C::TM;        // int64 storage slot per tile row
+        red = p; p += 64;
+        total = p;
+    }
+};
+
+// ---------------------------------------------------------------------------------------------
+// where batch position p lives in the time-major device buffer
+struct BatchView {
+    const int64_t* indices;  // explicit env-major buffer indices per position (may be NULL)
+    int64_t size, n_rows;    // ring: slots per row, rows
+    int64_t start, len;      // lock-step view: row r holds `len` valid slots from ring slot `start`
+    uint64_t perm_key;       // Feistel key of the minibatch permutation
+    int64_t perm_n;          // domain of the permutation (0 = identity)
+};
+__device__ __forceinline__ int64_t slot_of(const BatchView& b, int64_t p) {
+    if (b.indices) {
+        const int64_t i = b.indices[p];
+        const int64_t row = i / b.size, t = i - row * b.size;
+        return t * b.n_rows + row;
+    }
+    const int64_t q = b.perm_n > 0 ? (int64_t)feistel_permute((uint64_t)p, (uint64_t)b.perm_n, b.perm_key) : p;
+    const int64_t row = q / b.len, j = q - row * b.len;
+    int64_t t = b.start + j;
+    if (t >= b.size) t -= b.size;
+    return t * b.n_rows + row;
+}
+
+// ---------------------------------------------------------------------------------------------
+template <int H>
+__device__ __forceinline__ void load_weights(float* smem, const Smem<H>& L, const float* __restrict__ params, int in_dim,
+                                             int out_dim) {
+    using C = Cfg<H>;
+    const Offsets o = offsets(in_dim, H, out_dim);
+    for (int i = threadIdx.x; i < L.xrows * H; i += THREADS) {  // sW1T[k][j] = W1[j][k]
+        const int k = i / H, j = i - k * H;
+        smem[L.w1t + i] = k < in_dim ? params[o.w1 + (int64_t)j * in_dim + k] : 0.f;
+    }
+    for (int i = threadIdx.x; i < H * H; i += THREADS) {
+        const int r = i / H, c = i - r * H;
+        smem[L.w2 + r * C::LDW + c] = params[o.w2 + i];
+    }
+    for (int i = threadIdx.x; i < OUTP * H; i += THREADS) {
+        const int r = i / H, c = i - r * H;
+        smem[L.w3 + r * C::LDW + c] = r < out_dim ? params[o.w3 + (int64_t)r * H + c] : 0.f;
+    }
+    for (int i = threadIdx.x; i < H; i += THREADS) {
+        smem[L.b1 + i] = params[o.b1 + i];
+        smem[L.b2 + i] = params[o.b2 + i];
+    }
+    if (threadIdx.x < OUTP) smem[L.b3 + threadIdx.x] = threadIdx.x < out_dim ? params[o.b3 + threadIdx.x] : 0.f;
+}
+
+// gather TM rows of x (row-major [.][in_dim]) into sXT[k][row]; rows >= n_valid are zero
+template <int H>
+__device__ __forceinline__ void load_x_tile(float* smem, const Smem<H>& L, const float* __restrict__ x, int in_dim,
+                                            int n_valid) {
+    using C = Cfg<H>;
+    const int64_t* sSlot = reinterpret_cast<const int64_t*>(smem + L.slot);
+    float* sXT = smem + L.xt;
+    if ((in_dim & 1) == 0 && (reinterpret_cast<uintptr_t>(x) & 7) == 0) {
+        const int nv = in_dim >> 1;
+        for (int i = threadIdx.x; i < C::TM * nv; i += THREADS) {
+            const int r = i / nv, v = i - r * nv;
+            float2 val = make_float2(0.f, 0.f);
+            if (r < n_valid) val = *reinterpret_cast<const float2*>(x + sSlot[r] * in_dim + 2 * v);
+            sXT[(2 * v) * C::LD + r] = val.x;
+            sXT[(2 * v + 1) * C::LD + r] = val.y;
+        }
+    } else {
+        for (int i = threadIdx.x; i < C::TM * in_dim; i += THREADS) {
+            const int r = i / in_dim, k = i - r * in_dim;
+            sXT[k * C::LD + r] = r < n_valid ? x[sSlot[r] * in_dim + k] : 0.f;
+        }
+    }
+}
+
+// acc[rc][cc][i][j] = sum_k A^T[k][row] * W(k, col);  row = rc*64 + rg*4 + i, col = cc*64 + cg*4 + j
+// WT: W stored [k][col] (ld = ldw, 16-byte vector loads); else W stored [col][k] (torch layout, scalar loads)
+template <int H, bool WT>
+__device__ __forceinline__ void tile_gemm(const float* __restrict__ sAT, const float* __restrict__ sW, int ldw, int K,
+                                          float (&acc)[Cfg<H>::RC][Cfg<H>::CC][4][4]) {
+    using C = Cfg<H>;
+    const int rg = threadIdx.x & 15, cg = threadIdx.x >> 4;
+#pragma unroll
+    for (int rc = 0; rc < C::RC; ++rc)
+#pragma unroll
+        for (int cc = 0; cc < C::CC; ++cc)
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[rc][cc][i][j] = 0.f;
+#pragma unroll 2
+    for (int k = 0; k < K; ++k) {
+        float a[C::RC][4], w[C::CC][4];
+#pragma unroll
+        for (int rc = 0; rc < C::RC; ++rc) {
+            const float4 t = *reinterpret_cast<const float4*>(sAT + k * C::LD + rc * 64 + rg * 4);
+            a[rc][0] = t.x; a[rc][1] = t.y; a[rc][2] = t.z; a[rc][3] = t.w;
+        }
+#pragma unroll
+        for (int cc = 0; cc < C::CC; ++cc) {
+            if constexpr (WT) {
+                const float4 t = *reinterpret_cast<const float4*>(sW + k * ldw + cc * 64 + cg * 4);
+                w[cc][0] = t.x; w[cc][1] = t.y; w[cc][2] = t.z; w[cc][3] = t.w;
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) w[cc][j] = sW[(cc * 64 + cg * 4 + j) * ldw + k];
+            }
+        }
+#pragma unroll
+        for (int rc = 0; rc < C::RC; ++rc)
+#pragma unroll
+            for (int cc = 0; cc < C::CC; ++cc)
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) acc[rc][cc][i][j] = fmaf(a[rc][i], w[cc][j], acc[rc][cc][i][j]);
+    }
+}
+
+// out^T[col][row] = relu(acc + bias[col])
+template <int H>
+__device__ __forceinline__ void store_relu(const float (&acc)[Cfg<H>::RC][Cfg<H>::CC][4][4], const float* __restrict__ sBias,
+                                           float* __restrict__ sOT) {
+    using C = Cfg<H>;
+    const int rg = threadIdx.x & 15, cg = threadIdx.x >> 4;
+#pragma unroll
+    for (int rc = 0; rc < C::RC; ++rc)
+#pragma unroll
+        for (int cc = 0; cc < C::CC; ++cc)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int col = cc * 64 + cg * 4 + j;
+                const float b = sBias[col];
+                float4 v;
+                v.x = fmaxf(acc[rc][cc][0][j] + b, 0.f);
+                v.y = fmaxf(acc[rc][cc][1][j] + b, 0.f);
+                v.z = fmaxf(acc[rc][cc][2][j] + b, 0.f);
+                v.w = fmaxf(acc[rc][cc][3][j] + b, 0.f);
+                *reinterpret_cast<float4*>(sOT + col * C::LD + rc * 64 + rg * 4) = v;
+            }
+}
+
+// in place: sHT[col][row] = (sHT[col][row] > 0) ? acc : 0     (ReLU backward on the stored activation)
+template <int H>
+__device__ __forceinline__ void store_masked(const float (&acc)[Cfg<H>::RC][Cfg<H>::CC][4][4], float* __restrict__ sHT) {
+    using C = Cfg<H>;
+    const int rg = threadIdx.x & 15, cg = threadIdx.x >> 4;
+#pragma unroll
+    for (int rc = 0; rc < C::RC; ++rc)
+#pragma unroll
+        for (int cc = 0; cc < C::CC; ++cc)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                float4* p = reinterpret_cast<float4*>(sHT + (cc * 64 + cg * 4 + j) * C::LD + rc * 64 + rg * 4);
+                const float4 h = *p;
+                float4 v;
+                v.x = h.x > 0.f ? acc[rc][cc][0][j] : 0.f;
+                v.y = h.y > 0.f ? acc[rc][cc][1][j] : 0.f;
+                v.z = h.z > 0.f ? acc[rc][cc][2][j] : 0.f;
+                v.w = h.w > 0.f ? acc[rc][cc][3][j] : 0.f;
+                *p = v;
+            }
+}
+
+// head: sOut[row][o] = b3[o] + sum_k H2^T[k][row] * W3[o][k]
+template <int H>
+__device__ __forceinline__ void head_forward(const float* __restrict__ smem, const Smem<H>& L, float* __restrict__ sOut) {
+    using C = Cfg<H>;
+    constexpr int OPT = OUTP * C::TM / THREADS;  // outputs per thread (4 at TM=128, 2 at TM=64)
+    const int row = threadIdx.x % C::TM, og = threadIdx.x / C::TM;
+    float o[OPT];
+#pragma unroll
+    for (int q = 0; q < OPT; ++q) o[q] = smem[L.b3 + og * OPT + q];
+    const float* sH2T = smem + L.h2t;
+    const float* sW3 = smem + L.w3;
+#pragma unroll 4
+    for (int k = 0; k < H; ++k) {
+        const float a = sH2T[k * C::LD + row];
+#pragma unroll
+        for (int q = 0; q < OPT; ++q) o[q] = fmaf(a, sW3[(og * OPT + q) * C::LDW + k], o[q]);
+    }
+#pragma unroll
+    for (int q = 0; q < OPT; ++q) sOut[row * OUTP + og * OPT + q] = o[q];
+}
+
+// the two hidden layers + head for the tile currently in sXT
+template <int H>
+__device__ __forceinline__ void forward_tile(float* smem, const Smem<H>& L, int in_dim) {
+    using C = Cfg<H>;
+    float acc[C::RC][C::CC][4][4];
+    tile_gemm<H, true>(smem + L.xt, smem + L.w1t, H, in_dim, acc);
+    store_relu<H>(acc, smem + L.b1, smem + L.h1t);
+    __syncthreads();
+    tile_gemm<H, false>(smem + L.h1t, smem + L.w2, C::LDW, H, acc);
+    store_relu<H>(acc, smem + L.b2, smem + L.h2t);
+    __syncthreads();
+    head_forward<H>(smem, L, smem + L.dot);
+    __syncthreads();
+}
+
+// softmax pieces of one row
+struct Soft {
+    float logp[OUTP];
+    float p[OUTP];
+    float ent;
+};
+__device__ __forceinline__ Soft softmax_row(const float* z, int n_act) {
+    Soft s;
+    float m = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < OUTP; ++j)
+        if (j < n_act) m = fmaxf(m, z[j]);
+    float sum = 0.f;
+#pragma unroll
+    for (int j = 0; j < OUTP; ++j) {
+        s.p[j] = j < n_act ? expf(z[j] - m) : 0.f;
+        sum += s.p[j];
+    }
+    const float lse = logf(sum);
+    s.ent = 0.f;
+#pragma unroll
+    for (int j = 0; j < OUTP; ++j) {
+        s.logp[j] = j < n_act ? (z[j] - m) - lse : 0.f;
+        s.p[j] = j < n_act ? s.p[j] / sum : 0.f;
+        if (j < n_act) s.ent -= s.p[j] * s.logp[j];
+    }
+    return s;
+}
+
+// ---------------------------------------------------------------------------------------------
+// forward kernel.  mode: 0 raw outputs [n][out_dim]; 1 sample action (Philox inverse-CDF);
+// 2 arg-max action (dist.mode, deterministic_eval); 3 evaluate given actions (log_prob).
+struct FwdArgs {
+    const float* params;
+    const float* x;          // [.][in_dim] rows addressed through `rows` (NULL = identity)
+    const int64_t* rows;     // optional gather list of x rows (also the scatter target when scatter != 0)
+    int64_t n;
+    int in_dim, out_dim, n_act, value_index, mode, scatter;
+    uint64_t seed, counter;
+    float* out;              // mode 0: [n][out_dim]
+    int32_t* act;            // modes 1,2: written; mode 3: read
+    float* logp;             // [n]
+    float* value;            // [n] (if value_index >= 0)
+    float* entropy;          // [n] optional
+};
+
+template <int H>
+__global__ void __launch_bounds__(THREADS) forward_kernel(FwdArgs a) {
+    using C = Cfg<H>;
+    extern __shared__ __align__(16) float smem[];
+    const Smem<H> L(a.in_dim);
+    load_weights<H>(smem, L, a.params, a.in_dim, a.out_dim);
+    int64_t* sSlot = reinterpret_cast<int64_t*>(smem + L.slot);
+    const int64_t n_tiles = (a.n + C::TM - 1) / C::TM;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int64_t base = tile * C::TM;
+        const int n_valid = (int)min((int64_t)C::TM, a.n - base);
+        __syncthreads();  // previous tile fully consumed (and weights visible on the first pass)
+        if (threadIdx.x < C::TM) sSlot[threadIdx.x] = threadIdx.x < n_valid ? (a.rows ? a.rows[base + threadIdx.x] : base + threadIdx.x) : 0;
+        __syncthreads();
+        load_x_tile<H>(smem, L, a.x, a.in_dim, n_valid);
+        __syncthreads();
+        forward_tile<H>(smem, L, a.in_dim);
+        if (threadIdx.x < n_valid) {
+            const int r = threadIdx.x;
+            const int64_t dst = (a.scatter && a.rows) ? sSlot[r] : base + r;
+            float z[OUTP];
+            const float4 z0 = *reinterpret_cast<const float4*>(smem + L.dot + r * OUTP);
+            const float4 z1 = *reinterpret_cast<const float4*>(smem + L.dot + r * OUTP + 4);
+            z[0] = z0.x; z[1] = z0.y; z[2] = z0.z; z[3] = z0.w; z[4] = z1.x; z[5] = z1.y; z[6] = z1.z; z[7] = z1.w;
+            if (a.value && a.value_index >= 0) {
+                float v = 0.f;
+#pragma unroll
+                for (int j = 0; j < OUTP; ++j)
+                    if (j == a.value_index) v = z[j];
+                a.value[dst] = v;
+            }
+            if (a.mode == 0) {
+                if (a.out) {
+#pragma unroll
+                    for (int j = 0; j < OUTP; ++j)
+                        if (j < a.out_dim) a.out[dst * a.out_dim + j] = z[j];
+                }
+            } else {
+                const Soft s = softmax_row(z, a.n_act);
+                int act = 0;
+                if (a.mode == 1) {
+                    const Philox4 rnd = philox4x32((uint32_t)dst, (uint32_t)((uint64_t)dst >> 32), (uint32_t)a.counter,
+                                                   (uint32_t)(a.counter >> 32), (uint32_t)a.seed, (uint32_t)(a.seed >> 32) ^ STREAM_ACT);
+                    const float u = u01(rnd.x);
+                    float c = 0.f;
+                    act = a.n_act - 1;
+                    bool found = false;
+#pragma unroll
+                    for (int j = 0; j < OUTP; ++j) {
+                        if (j < a.n_act) {
+                            c += s.p[j];
+                            if (!found && u < c) { act = j; found = true; }
+                        }
+                    }
+                } else if (a.mode == 2) {
+                    float best = -INFINITY;
+#pragma unroll
+                    for (int j = 0; j < OUTP; ++j)
+                        if (j < a.n_act && z[j] > best) { best = z[j]; act = j; }
+                } else {
+                    act = a.act[dst];
+                }
+                float lp = 0.f;
+#pragma unroll
+                for (int j = 0; j < OUTP; ++j)
+                    if (j == act) lp = s.logp[j];
+                if (a.mode != 3 && a.act) a.act[dst] = act;
+                if (a.logp) a.logp[dst] = lp;
+                if (a.entropy) a.entropy[dst] = s.ent;
+                if (a.out) {
+#pragma unroll
+                    for (int j = 0; j < OUTP; ++j)
+                        if (j < a.n_act) a.out[dst * a.n_act + j] = z[j];
+                }
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// G[i][j] += sum_k P^T[i][k] * Q^T[j][k] over the TM rows of the tile; i = ig + 16*ii, j = jg + 16*jj
+template <int H, int NI, int NJ>
+__device__ __forceinline__ void wgrad(const float* __restrict__ sPT, const float* __restrict__ sQT, float (&g)[NI][NJ]) {
+    using C = Cfg<H>;
+    const int ig = threadIdx.x & 15, jg = threadIdx.x >> 4;
+#pragma unroll 2
+    for (int k = 0; k < C::TM; k += 4) {
+        float4 p[NI], q[NJ];
+#pragma unroll
+        for (int ii = 0; ii < NI; ++ii) p[ii] = *reinterpret_cast<const float4*>(sPT + (ig + 16 * ii) * C::LD + k);
+#pragma unroll
+        for (int jj = 0; jj < NJ; ++jj) q[jj] = *reinterpret_cast<const float4*>(sQT + (jg + 16 * jj) * C::LD + k);
+#pragma unroll
+        for (int ii = 0; ii < NI; ++ii)
+#pragma unroll
+            for (int jj = 0; jj < NJ; ++jj) {
+                float s = g[ii][jj];
+                s = fmaf(p[ii].x, q[jj].x, s);
+                s = fmaf(p[ii].y, q[jj].y, s);
+                s = fmaf(p[ii].z, q[jj].z, s);
+                s = fmaf(p[ii].w, q[jj].w, s);
+                g[ii][jj] = s;
+            }
+    }
+}
+
+struct PpoCfg {
+    float eps_clip, dual_clip, vf_coef, ent_coef;
+    int value_clip, adv_norm;
+};
+
+struct PpoArgs {
+    const float* params;
+    float* grads;           // flat, accumulated with atomics
+    const float* obs;       // time-major [size][n_rows][in_dim]
+    const int32_t* act;     // [size][n_rows]
+    const float* adv;
+    const float* ret;
+    const float* logp_old;
+    const float* v_old;     // only for value_clip
+    BatchView view;
+    int64_t mb_start, mb_len;  // batch positions [mb_start, mb_start + mb_len)
+    const float* mb_stats;     // {mean, 1/(std+eps)} of adv over this minibatch (device) or NULL
+    PpoCfg cfg;
+    int in_dim, out_dim, n_act, value_index;
+    double* loss_sums;         // [4]: sum clip_loss_i, sum vf_i, sum ent_i, count  (device, accumulated)
+};
+
+template <int H, int XJ>
+__global__ void __launch_bounds__(THREADS) ppo_minibatch_kernel(PpoArgs a) {
+    using C = Cfg<H>;
+    extern __shared__ __align__(16) float smem[];
+    const Smem<H> L(a.in_dim);
+    load_weights<H>(smem, L, a.params, a.in_dim, a.out_dim);
+    int64_t* sSlot = reinterpret_cast<int64_t*>(smem + L.slot);
+    float* sDOT = smem + L.dot;
+    for (int i = threadIdx.x; i < (L.xrows - a.in_dim) * C::LD; i += THREADS) smem[L.xt + a.in_dim * C::LD + i] = 0.f;
+    constexpr int NI = H / 16;
+    float g2[NI][NI], g1[NI][XJ];
+    float g3[H / 32];
+    float gb1 = 0.f, gb2 = 0.f, gb3 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NI; ++i) {
+#pragma unroll
+        for (int j = 0; j < NI; ++j) g2[i][j] = 0.f;
+#pragma unroll
+        for (int j = 0; j < XJ; ++j) g1[i][j] = 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < H / 32; ++j) g3[j] = 0.f;
+    double l_clip = 0.0, l_vf = 0.0, l_ent = 0.0;
+    const float inv_n = 1.0f / (float)a.mb_len;
+    float mean = 0.f, rstd = 1.f;
+    if (a.cfg.adv_norm && a.mb_stats) { mean = a.mb_stats[0]; rstd = a.mb_stats[1]; }
+
+    const int64_t n_tiles = (a.mb_len + C::TM - 1) / C::TM;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int64_t base = a.mb_start + tile * C::TM;
+        const int n_valid = (int)min((int64_t)C::TM, a.mb_start + a.mb_len - base);
+        __syncthreads();
+        if (threadIdx.x < C::TM) sSlot[threadIdx.x] = threadIdx.x < n_valid ? slot_of(a.view, base + threadIdx.x) : 0;
+        __syncthreads();
+        load_x_tile<H>(smem, L, a.obs, a.in_dim, n_valid);
+        __syncthreads();
+        forward_tile<H>(smem, L, a.in_dim);
+        // ---- per-row loss and d(loss)/d(head outputs) (ppo.py:181-211) ----
+        float dz[OUTP];
+#pragma unroll
+        for (int j = 0; j < OUTP; ++j) dz[j] = 0.f;
+        if (threadIdx.x < n_valid) {
+            const int r = threadIdx.x;
+            const int64_t s = sSlot[r];
+            float z[OUTP];
+            const float4 z0 = *reinterpret_cast<const float4*>(sDOT + r * OUTP);
+            const float4 z1 = *reinterpret_cast<const float4*>(sDOT + r * OUTP + 4);
+            z[0] = z0.x; z[1] = z0.y; z[2] = z0.z; z[3] = z0.w; z[4] = z1.x; z[5] = z1.y; z[6] = z1.z; z[7] = z1.w;
+            if (a.n_act > 0) {
+                const Soft sm = softmax_row(z, a.n_act);
+                const int act = a.act[s];
+                float lp = 0.f;
+#pragma unroll
+                for (int j = 0; j < OUTP; ++j)
+                    if (j == act) lp = sm.logp[j];
+                float advn = a.adv[s];
+                if (a.cfg.adv_norm) advn = (advn - mean) * rstd;
+                const float ratio = expf(lp - a.logp_old[s]);
+                const float lo = 1.f - a.cfg.eps_clip, hi = 1.f + a.cfg.eps_clip;
+                const float s1 = ratio * advn, s2 = fminf(fmaxf(ratio, lo), hi) * advn;
+                const bool inside = ratio >= lo && ratio <= hi;
+                float clip1 = fminf(s1, s2);
+                float g_ratio = (inside || s1 < s2) ? advn : 0.f;  // d min(s1,s2) / d ratio
+                float li = -clip1;
+                if (a.cfg.dual_clip > 0.f && advn < 0.f) {
+                    const float c2 = a.cfg.dual_clip * advn;
+                    if (c2 > clip1) { li = -c2; g_ratio = 0.f; }
+                }
+                l_clip += (double)li;
+                l_ent += (double)sm.ent;
+                const float dlp = -g_ratio * ratio * inv_n;  // d loss / d logp(act)
+                const float ec = a.cfg.ent_coef * inv_n;
+#pragma unroll
+                for (int j = 0; j < OUTP; ++j)
+                    if (j < a.n_act)
+                        dz[j] = dlp * ((j == act ? 1.f : 0.f) - sm.p[j]) + ec * sm.p[j] * (sm.logp[j] + sm.ent);
+            }
+            if (a.value_index >= 0) {
+                float v = 0.f;
+#pragma unroll
+                for (int j = 0; j < OUTP; ++j)
+                    if (j == a.value_index) v = z[j];
+                const float ret = a.ret[s];
+                float vf = (ret - v) * (ret - v), dv = 2.f * (v - ret);
+                if (a.cfg.value_clip) {
+                    const float vo = a.v_old[s];
+                    const float d = v - vo;
+                    const float vc = vo + fminf(fmaxf(d, -a.cfg.eps_clip), a.cfg.eps_clip);
+                    const float vf2 = (ret - vc) * (ret - vc);
+                    if (vf2 > vf) {
+                        vf = vf2;
+                        dv = (d >= -a.cfg.eps_clip && d <= a.cfg.eps_clip) ? 2.f * (vc - ret) : 0.f;
+                    }
+                }
+                l_vf += (double)vf;
+                const float dvs = a.cfg.vf_coef * inv_n * dv;
+#pragma unroll
+                for (int j = 0; j < OUTP; ++j)
+                    if (j == a.value_index) dz[j] = dvs;
+            }
+        }
+        __syncthreads();  // every thread has read its head outputs before the region is reused as dOut^T
+        if (threadIdx.x < C::TM) {
+#pragma unroll
+            for (int j = 0; j < OUTP; ++j) sDOT[j * C::LD + threadIdx.x] = dz[j];
+        }
+        __syncthreads();
+        // ---- head gradients: dW3[o][j] += sum_row dOut[row][o] * H2[row][j];  db3[o] ----
+        {
+            const int o = threadIdx.x & 7, jq = threadIdx.x >> 3;
+            float b3 = 0.f;
+#pragma unroll 2
+            for (int k = 0; k < C::TM; k += 4) {
+                const float4 p = *reinterpret_cast<const float4*>(sDOT + o * C::LD + k);
+#pragma unroll
+                for (int jj = 0; jj < H / 32; ++jj) {
+                    const float4 q = *reinterpret_cast<const float4*>(smem + L.h2t + (jq + 32 * jj) * C::LD + k);
+                    g3[jj] = fmaf(p.x, q.x, fmaf(p.y, q.y, fmaf(p.z, q.z, fmaf(p.w, q.w, g3[jj]))));
+                }
+                b3 += (p.x + p.y) + (p.z + p.w);
+            }
+            if (jq == 0) gb3 += b3;
+        }
+        __syncthreads();
+        // ---- D2 = relu'(H2) * (dOut . W3), in place over H2 ----
+        float acc[C::RC][C::CC][4][4];
+        tile_gemm<H, true>(sDOT, smem + L.w3, C::LDW, OUTP, acc);
+        store_masked<H>(acc, smem + L.h2t);
+        __syncthreads();
+        // ---- dW2[i][j] += sum_row D2[row][i] * H1[row][j];  db2[i] ----
+        wgrad<H, NI, NI>(smem + L.h2t, smem + L.h1t, g2);
+        if (threadIdx.x < H) {
+            float s = 0.f;
+            for (int k = 0; k < C::TM; k += 4) {
+                const float4 p = *reinterpret_cast<const float4*>(smem + L.h2t + threadIdx.x * C::LD + k);
+                s += (p.x + p.y) + (p.z + p.w);
+            }
+            gb2 += s;
+        }
+        __syncthreads();
+        // ---- D1 = relu'(H1) * (D2 . W2), in place over H1 ----
+        tile_gemm<H, true>(smem + L.h2t, smem + L.w2, C::LDW, H, acc);
+        store_masked<H>(acc, smem + L.h1t);
+        __syncthreads();
+        // ---- dW1[i][j] += sum_row D1[row][i] * X[row][j];  db1[i] ----
+        wgrad<H, NI, XJ>(smem + L.h1t, smem + L.xt, g1);
+        if (threadIdx.x < H) {
+            float s = 0.f;
+            for (int k = 0; k < C::TM; k += 4) {
+                const float4 p = *reinterpret_cast<const float4*>(smem + L.h1t + threadIdx.x * C::LD + k);
+                s += (p.x + p.y) + (p.z + p.w);
+            }
+            gb1 += s;
+        }
+    }
+    // ---- flush this CTA's gradient partials ----
+    const Offsets o = offsets(a.in_dim, H, a.out_dim);
+    {
+        const int ig = threadIdx.x & 15, jg = threadIdx.x >> 4;
+#pragma unroll
+        for (int ii = 0; ii < NI; ++ii) {
+            const int i = ig + 16 * ii;
+#pragma unroll
+            for (int jj = 0; jj < NI; ++jj) atomicAdd(a.grads + o.w2 + (int64_t)i * H + jg + 16 * jj, g2[ii][jj]);
+#pragma unroll
+            for (int jj = 0; jj < XJ; ++jj) {
+                const int j = jg + 16 * jj;
+                if (j < a.in_dim) atomicAdd(a.grads + o.w1 + (int64_t)i * a.in_dim + j, g1[ii][jj]);
+            }
+        }
+        const int oo = threadIdx.x & 7, jq = threadIdx.x >> 3;
+        if (oo < a.out_dim) {
+#pragma unroll
+            for (int jj = 0; jj < H / 32; ++jj) atomicAdd(a.grads + o.w3 + (int64_t)oo * H + jq + 32 * jj, g3[jj]);
+            if (jq == 0) atomicAdd(a.grads + o.b3 + oo, gb3);
+        }
+        if (threadIdx.x < H) {
+            atomicAdd(a.grads + o.b1 + threadIdx.x, gb1);
+            atomicAdd(a.grads + o.b2 + threadIdx.x, gb2);
+        }
+    }
+    // ---- loss sums: warp shuffle -> shared -> one atomic per CTA ----
+    if (a.loss_sums) {
+        __syncthreads();
+        double* sRed = reinterpret_cast<double*>(smem + L.slot);  // reuse (TM int64 >= 8*3 doubles)
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            l_clip += __shfl_down_sync(0xffffffffu, l_clip, d);
+            l_vf += __shfl_down_sync(0xffffffffu, l_vf, d);
+            l_ent += __shfl_down_sync(0xffffffffu, l_ent, d);
+        }
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        if (lane == 0) { sRed[warp * 3] = l_clip; sRed[warp * 3 + 1] = l_vf; sRed[warp * 3 + 2] = l_ent; }
+        __syncthreads();
+        if (threadIdx.x < 3) {
+            double s = 0.0;
+            for (int w = 0; w < THREADS / 32; ++w) s += sRed[w * 3 + threadIdx.x];
+            atomicAdd(a.loss_sums + threadIdx.x, s);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// mean and 1/(std_unbiased + eps) of adv over each minibatch (ppo.py:184-186), one CTA each
+__global__ void __launch_bounds__(THREADS) adv_stats_kernel(const float* __restrict__ adv, BatchView view,
+                                                           const int64_t* __restrict__ mb_bounds, float eps,
+                                                           float* __restrict__ stats) {
+    const int64_t s0 = mb_bounds[blockIdx.x], s1 = mb_bounds[blockIdx.x + 1];
+    double sum = 0.0, sq = 0.0;
+    for (int64_t p = s0 + threadIdx.x; p < s1; p += THREADS) {
+        const double v = (double)adv[slot_of(view, p)];
+        sum += v;
+        sq += v * v;
+    }
+    __shared__ double sh[2][THREADS / 32];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        sum += __shfl_down_sync(0xffffffffu, sum, d);
+        sq += __shfl_down_sync(0xffffffffu, sq, d);
+    }
+    if ((threadIdx.x & 31) == 0) { sh[0][threadIdx.x >> 5] = sum; sh[1][threadIdx.x >> 5] = sq; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0.0, b = 0.0;
+        for (int w = 0; w < THREADS / 32; ++w) { a += sh[0][w]; b += sh[1][w]; }
+        const double n = (double)(s1 - s0);
+        const double mean = n > 0 ? a / n : 0.0;
+        double var = n > 1 ? (b - n * mean * mean) / (n - 1.0) : NAN;  // torch.std of one element is nan
+        if (var < 0.0) var = 0.0;
+        stats[2 * blockIdx.x] = (float)mean;
+        stats[2 * blockIdx.x + 1] = (float)(1.0 / (sqrt(var) + (double)eps));
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// one CTA: global grad-norm clip (torch.nn.utils.clip_grad_norm_) + torch.optim.Adam step; zeroes grads
+constexpr int ADAM_THREADS = 1024;
+__global__ void __launch_bounds__(ADAM_THREADS) adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
+                                                           float* __restrict__ v, int64_t* __restrict__ step, int64_t n, float lr,
+                                                           float beta1, float beta2, float eps, float max_norm, float grad_scale,
+                                                           float* __restrict__ gnorm_out) {
+    __shared__ float sh[ADAM_THREADS / 32];
+    __shared__ float s_coef;
+    float coef = grad_scale;
+    if (max_norm > 0.f || gnorm_out) {
+        float sq = 0.f;
+        for (int64_t i = threadIdx.x; i < n; i += ADAM_THREADS) {
+            const float x = g[i] * grad_scale;
+            sq = fmaf(x, x, sq);
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) sq += __shfl_down_sync(0xffffffffu, sq, d);
+        if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = sq;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float t = 0.f;
+            for (int w = 0; w < ADAM_THREADS / 32; ++w) t += sh[w];
+            const float norm = sqrtf(t);
+            if (gnorm_out) *gnorm_out = norm;
+            float c = 1.f;
+            if (max_norm > 0.f) c = fminf(max_norm / (norm + 1e-6f), 1.f);
+            s_coef = c * grad_scale;
+        }
+        __syncthreads();
+        coef = s_coef;
+    }
+    const int64_t t = *step + 1;
+    const float bc1 = (float)(1.0 - pow((double)beta1, (double)t));
+    const float bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, (double)t));
+    const float step_size = lr / bc1;
+    for (int64_t i = threadIdx.x; i < n; i += ADAM_THREADS) {
+        const float gi = g[i] * coef;
+        const float mi = m[i] + (gi - m[i]) * (1.f - beta1);         // exp_avg.lerp_(grad, 1 - beta1)
+        const float vi = fmaf(gi * gi, 1.f - beta2, v[i] * beta2);   // mul_(beta2).addcmul_(g, g, 1 - beta2)
+        const float denom = sqrtf(vi) / bc2_sqrt + eps;
+        p[i] = p[i] - step_size * (mi / denom);
+        m[i] = mi;
+        v[i] = vi;
+        g[i] = 0.f;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) *step = t;
+}
+
+}  // namespace mlp
+}  // namespace tsm
+
+using namespace tsm;
+using namespace tsm::mlp;
+
+static int check_net(const tsm_net* n, const char* fn) {
+    if (!n) return fail(TSM_ERR_INVALID, "%s: net is NULL", fn);
+    if (n->hidden != 64 && n->hidden != 128) return fail(TSM_ERR_UNSUPPORTED, "%s: hidden must be 64 or 128", fn);
+    if (n->in_dim < 1 || n->in_dim > 64) return fail(TSM_ERR_UNSUPPORTED, "%s: in_dim must be in 1..64 on the fp32 path", fn);
+    if (n->out_dim < 1 || n->out_dim > OUTP) return fail(TSM_ERR_UNSUPPORTED, "%s: out_dim must be in 1..8", fn);
+    if (n->n_act < 0 || n->n_act > n->out_dim) return fail(TSM_ERR_INVALID, "%s: 0 <= n_act <= out_dim", fn);
+    if (n->value_index >= n->out_dim) return fail(TSM_ERR_INVALID, "%s: value_index < out_dim", fn);
+    if (n->value_index >= 0 && n->value_index < n->n_act) return fail(TSM_ERR_INVALID, "%s: value_index must not alias a logit", fn);
+    if (!n->params) return fail(TSM_ERR_INVALID, "%s: params is NULL", fn);
+    if (n->n_params != offsets(n->in_dim, n->hidden, n->out_dim).total)
+        return fail(TSM_ERR_INVALID, "%s: n_params does not match the layout (want %lld)", fn,
+                    (long long)offsets(n->in_dim, n->hidden, n->out_dim).total);
+    return TSM_OK;
+}
+
+template <int H>
+static size_t smem_bytes(int in_dim) {
+    return (size_t)Smem<H>(in_dim).total * sizeof(float);
+}
+
+template <typename K>
+static int prep_kernel(K kernel, size_t smem, int* ctas_per_sm) {
+    TSM_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 0;
+    TSM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, THREADS, smem));
+    if (occ < 1) return fail(TSM_ERR_UNSUPPORTED, "%s: kernel does not fit on an SM", __func__);
+    *ctas_per_sm = occ;
+    return TSM_OK;
+}
+
+extern "C" int64_t tsm_net_param_count(int in_dim, int hidden, int out_dim) { return offsets(in_dim, hidden, out_dim).total; }
+
+extern "C" int tsm_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int64_t n, int mode, int scatter,
+                               uint64_t seed, uint64_t counter, float* out, int32_t* act, float* logp, float* value,
+                               float* entropy, tsm_stream_t stream) {
+    int rc = check_net(net, __func__);
+    if (rc) return rc;
+    TSM_REQUIRE(n >= 0 && mode >= 0 && mode <= 3, "n >= 0, 0 <= mode <= 3");
+    if (n == 0) return TSM_OK;
+    TSM_REQUIRE(x != nullptr, "x != NULL");
+    TSM_REQUIRE(mode == 0 || net->n_act > 0, "sampling / evaluation needs n_act > 0");
+    TSM_REQUIRE(mode != 3 || act != nullptr, "mode 3 (evaluate) needs act");
+    FwdArgs a{};
+    a.params = net->params; a.x = x; a.rows = rows; a.n = n;
+    a.in_dim = net->in_dim; a.out_dim = net->out_dim; a.n_act = net->n_act; a.value_index = net->value_index;
+    a.mode = mode; a.scatter = scatter; a.seed = seed; a.counter = counter;
+    a.out = out; a.act = act; a.logp = logp; a.value = value; a.entropy = entropy;
+    cudaStream_t s = as_stream(stream);
+    int occ = 1;
+    if (net->hidden == 64) {
+        const size_t sm = smem_bytes<64>(net->in_dim);
+        rc = prep_kernel(forward_kernel<64>, sm, &occ);
+        if (rc) return rc;
+        const int64_t tiles = ceil_div(n, Cfg<64>::TM);
+        const unsigned grid = (unsigned)std::min<int64_t>(tiles, (int64_t)sm_count() * occ);
+        forward_kernel<64><<<grid, THREADS, sm, s>>>(a);
+    } else {
+        const size_t sm = smem_bytes<128>(net->in_dim);
+        rc = prep_kernel(forward_kernel<128>, sm, &occ);
+        if (rc) return rc;
+        const int64_t tiles = ceil_div(n, Cfg<128>::TM);
+        const unsigned grid = (unsigned)std::min<int64_t>(tiles, (int64_t)sm_count() * occ);
+        forward_kernel<128><<<grid, THREADS, sm, s>>>(a);
+    }
+    TSM_LAUNCH_CHECK();
+    return TSM_OK;
+}
+
+static BatchView make_view(const tsm_ppo_batch* b) {
+    BatchView v{};
+    v.indices = b->indices; v.size = b->size; v.n_rows = b->n_rows; v.start = b->start; v.len = b->len;
+    v.perm_key = b->perm_key; v.perm_n = b->perm_n;
+    return v;
+}
+
+static int check_batch(const tsm_ppo_batch* b, const char* fn) {
+    if (!b) return fail(TSM_ERR_INVALID, "%s: batch is NULL", fn);
+    if (b->size <= 0 || b->n_rows <= 0) return fail(TSM_ERR_INVALID, "%s: size and n_rows must be > 0", fn);
+    if (!b->indices && (b->len <= 0 || b->len > b->size || b->start < 0 || b->start >= b->size))
+        return fail(TSM_ERR_INVALID, "%s: need 0 < len <= size and 0 <= start < size", fn);
+    if (b->perm_n < 0 || (!b->indices && b->perm_n > 0 && b->perm_n != b->len * b->n_rows))
+        return fail(TSM_ERR_INVALID, "%s: perm_n must be 0 or len * n_rows", fn);
+    return TSM_OK;
+}
+
+extern "C" int tsm_ppo_adv_stats(const tsm_ppo_batch* batch, const int64_t* mb_bounds, int64_t n_minibatches, float eps,
+                                 float* stats_out, tsm_stream_t stream) {
+    int rc = check_batch(batch, __func__);
+    if (rc) return rc;
+    TSM_REQUIRE(n_minibatches >= 0, "n_minibatches >= 0");
+    if (n_minibatches == 0) return TSM_OK;
+    TSM_REQUIRE(batch->adv && mb_bounds && stats_out, "adv / mb_bounds / stats_out != NULL");
+    adv_stats_kernel<<<(unsigned)n_minibatches, THREADS, 0, as_stream(stream)>>>(batch->adv, make_view(batch), mb_bounds, eps,
+                                                                                stats_out);
+    TSM_LAUNCH_CHECK();
+    return TSM_OK;
+}
+
+template <int H>
+static int launch_ppo(const PpoArgs& a, cudaStream_t s) {
+    const size_t sm = smem_bytes<H>(a.in_dim);
+    const int xj = (a.in_dim + 15) / 16;
+    int occ = 1, rc = 0;
+    const int64_t tiles = ceil_div(a.mb_len, Cfg<H>::TM);
+#define TSM_PPO_CASE(XJ)                                                                   \
+    case XJ: {                                                                             \
+        rc = prep_kernel(ppo_minibatch_kernel<H, XJ>, sm, &occ);                            \
+        if (rc) return rc;                                                                 \
+        const unsigned grid = (unsigned)std::min<int64_t>(tiles, (int64_t)sm_count() * occ); \
+        ppo_minibatch_kernel<H, XJ><<<grid, THREADS, sm, s>>>(a);                           \
+        break;                                                                             \
+    }
+    switch (xj) {
+        TSM_PPO_CASE(1)
+        TSM_PPO_CASE(2)
+        TSM_PPO_CASE(3)
+        TSM_PPO_CASE(4)
+        default: return fail(TSM_ERR_UNSUPPORTED, "%s: in_dim > 64", __func__);
+    }
+#undef TSM_PPO_CASE
+    TSM_LAUNCH_CHECK();
+    return TSM_OK;
+}
+
+extern "C" int tsm_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, int64_t mb_start,
+                                 int64_t mb_len, const float* mb_stats, double* loss_sums, tsm_stream_t stream) {
+    int rc = check_net(net, __func__);
+    if (rc) return rc;
+    rc = check_batch(batch, __func__);
+    if (rc) return rc;
+    TSM_REQUIRE(cfg != nullptr, "cfg != NULL");
+    TSM_REQUIRE(net->grads != nullptr, "net.grads != NULL");
+    TSM_REQUIRE(mb_start >= 0 && mb_len >= 0, "mb_start, mb_len >= 0");
+    if (mb_len == 0) return TSM_OK;
+    TSM_REQUIRE(batch->obs != nullptr, "batch.obs != NULL");
+    TSM_REQUIRE(net->n_act == 0 || (batch->act && batch->adv && batch->logp_old), "policy loss needs act / adv / logp_old");
+    TSM_REQUIRE(net->value_index < 0 || batch->ret, "value loss needs ret");
+    TSM_REQUIRE(!cfg->value_clip || batch->v_old, "value_clip needs v_old");
+    TSM_REQUIRE(!cfg->adv_norm || mb_stats, "advantage normalisation needs mb_stats");
+    PpoArgs a{};
+    a.params = net->params; a.grads = net->grads;
+    a.obs = batch->obs; a.act = batch->act; a.adv = batch->adv; a.ret = batch->ret; a.logp_old = batch->logp_old; a.v_old = batch->v_old;
+    a.view = make_view(batch);
+    a.mb_start = mb_start; a.mb_len = mb_len; a.mb_stats = mb_stats;
+    a.cfg.eps_clip = cfg->eps_clip; a.cfg.dual_clip = cfg->dual_clip; a.cfg.vf_coef = cfg->vf_coef; a.cfg.ent_coef = cfg->ent_coef;
+    a.cfg.value_clip = cfg->value_clip; a.cfg.adv_norm = cfg->adv_norm;
+    a.in_dim = net->in_dim; a.out_dim = net->out_dim; a.n_act = net->n_act; a.value_index = net->value_index;
+    a.loss_sums = loss_sums;
+    return net->hidden == 64 ? launch_ppo<64>(a, as_stream(stream)) : launch_ppo<128>(a, as_stream(stream));
+}
+
+extern "C" int tsm_adam_step(const tsm_net* net, float lr, float beta1, float beta2, float eps, float max_grad_norm,
+                             float grad_scale, float* grad_norm_out, tsm_stream_t stream) {
+    TSM_REQUIRE(net != nullptr, "net != NULL");
+    TSM_REQUIRE(net->params && net->grads && net->adam_m && net->adam_v && net->adam_step, "params/grads/adam state != NULL");
+    TSM_REQUIRE(net->n_params > 0, "n_params > 0");
+    adam_kernel<<<1, ADAM_THREADS, 0, as_stream(stream)>>>(net->params, net->grads, net->adam_m, net->adam_v, net->adam_step,
+                                                          net->n_params, lr, beta1, beta2, eps, max_grad_norm, grad_scale,
+                                                          grad_norm_out);
+    TSM_LAUNCH_CHECK();
+    return TSM_OK;
+}
+
+extern "C" int tsm_ppo_epoch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, const int64_t* h_mb_bounds,
+                             int64_t n_minibatches, const float* mb_stats, float lr, float beta1, float beta2, float eps,
+                             float max_grad_norm, double* loss_sums, tsm_stream_t stream) {
+    TSM_REQUIRE(h_mb_bounds != nullptr && n_minibatches >= 0, "h_mb_bounds != NULL");
+    for (int64_t m = 0; m < n_minibatches; ++m) {
+        int rc = tsm_ppo_minibatch(net, batch, cfg, h_mb_bounds[m], h_mb_bounds[m + 1] - h_mb_bounds[m],
+                                   mb_stats ? mb_stats + 2 * m : nullptr, loss_sums ? loss_sums + 4 * m : nullptr, stream);
+        if (rc) return rc;
+        rc = tsm_adam_step(net, lr, beta1, beta2, eps, max_grad_norm, 1.0f, nullptr, stream);
+        if (rc) return rc;
+    }
+    return TSM_OK;
+}

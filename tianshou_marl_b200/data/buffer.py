@@ -69,6 +69,7 @@ class VectorReplayBuffer:
         self._count = torch.zeros(1, **i64)
         self._desc = _lib.TsmBuf()
         self._lockstep_len: int | None = 0  # host-known common length while every add was a full lock-step add
+        self._lockstep_ins = 0  # host-known common insertion index in lock-step use
         self._refresh_desc()
 
     # -- plumbing -----------------------------------------------------------------------------
@@ -126,6 +127,7 @@ class VectorReplayBuffer:
     def reset(self, keep_statistics: bool = False) -> None:
         _lib.check(_lib.lib().tsm_buf_reset(C.byref(self._desc), int(keep_statistics), _lib.stream_ptr()))
         self._lockstep_len = 0
+        self._lockstep_ins = 0
 
     def update(self, buffer: Any) -> np.ndarray:
         """manager.py:127-129."""
@@ -177,6 +179,7 @@ class VectorReplayBuffer:
             P(ids_t), n, P(idx), P(ep_ret), P(ep_len), P(ep_start), _lib.stream_ptr()))
         if buffer_ids is None and self._lockstep_len is not None:
             self._lockstep_len = min(self._lockstep_len + 1, self._size)
+            self._lockstep_ins = (self._lockstep_ins + 1) % self._size
         else:
             self._lockstep_len = None
         return self._out(idx, host), self._out(ep_ret, host), self._out(ep_len, host), self._out(ep_start, host)

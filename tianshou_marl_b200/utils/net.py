@@ -1,0 +1,140 @@
+"""Actor-critic MLP whose parameters live in ONE flat float32 device buffer consumed by the
+libtsm_b200 kernels (csrc/mlp.cu).
+
+Stands where the reference builds  Net(state_shape, hidden_sizes=[H, H])  shared between
+DiscreteActor(preprocess_net=net, action_shape) and DiscreteCritic(preprocess_net=net)
+(tianshou/utils/net/common.py:286-369, discrete.py:27-124, test/discrete/test_ppo_discrete.py:91-105),
+or the separate DecentralizedActor / CentralizedCritic 3-layer MLPs of ctde.py:346-414.
+
+Flat layout (torch.nn.Linear convention weight[out][in]):
+    W1[H][in] b1[H] W2[H][H] b2[H] W3[out][H] b3[out],  out = n_act (+ 1 value row when shared).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Any
+
+import numpy as np
+import torch
+from torch import nn
+
+from .. import _lib
+
+MODES = {"raw": 0, "sample": 1, "mode": 2, "eval": 3}
+
+
+class ActorCriticNet(nn.Module):
+    def __init__(self, in_dim: int, hidden: int = 64, n_act: int = 5, with_value: bool = True, n_value_only: int = 0,
+                 device: str | torch.device = "cuda", seed: int | None = None, orthogonal: bool = True) -> None:
+        super().__init__()
+        self.in_dim, self.hidden, self.n_act = int(in_dim), int(hidden), int(n_act)
+        if n_value_only:  # critic-only net: out_dim value heads, no logits
+            self.n_act, self.out_dim, self.value_index = 0, int(n_value_only), 0
+        else:
+            self.out_dim = self.n_act + (1 if with_value else 0)
+            self.value_index = self.n_act if with_value else -1
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise _lib.TsmError("ActorCriticNet needs a CUDA device (no CPU fallback)")
+        L = _lib.lib()
+        n = int(L.tsm_net_param_count(self.in_dim, self.hidden, self.out_dim))
+        self.n_params = n
+        self.flat = nn.Parameter(torch.zeros(n, dtype=torch.float32, device=self.device))
+        self.grads = torch.zeros(n, dtype=torch.float32, device=self.device)
+        self.adam_m = torch.zeros(n, dtype=torch.float32, device=self.device)
+        self.adam_v = torch.zeros(n, dtype=torch.float32, device=self.device)
+        self.adam_step = torch.zeros(1, dtype=torch.int64, device=self.device)
+        H, I, O = self.hidden, self.in_dim, self.out_dim
+        sizes = [("W1", (H, I)), ("b1", (H,)), ("W2", (H, H)), ("b2", (H,)), ("W3", (O, H)), ("b3", (O,))]
+        self._views: dict[str, tuple[int, tuple[int, ...]]] = {}
+        off = 0
+        for k, shp in sizes:
+            self._views[k] = (off, shp)
+            off += int(np.prod(shp))
+        assert off == n
+        self._desc = _lib.TsmNet()
+        self._fill_desc()
+        if orthogonal:
+            g = torch.Generator().manual_seed(0 if seed is None else seed)
+            with torch.no_grad():
+                for k in ("W1", "W2", "W3"):
+                    w = torch.empty(self._views[k][1])
+                    nn.init.orthogonal_(w, generator=g)  # test_ppo_discrete.py:101-105
+                    self.view(k).copy_(w)
+
+    # -- plumbing ---------------------------------------------------------------------------
+    def _fill_desc(self) -> None:
+        d = self._desc
+        d.in_dim, d.hidden, d.out_dim, d.n_act, d.value_index, d.n_params = (self.in_dim, self.hidden, self.out_dim, self.n_act,
+                                                                           self.value_index, self.n_params)
+        d.params, d.grads = self.flat.data_ptr(), self.grads.data_ptr()
+        d.adam_m, d.adam_v, d.adam_step = self.adam_m.data_ptr(), self.adam_v.data_ptr(), self.adam_step.data_ptr()
+
+    @property
+    def desc(self) -> Any:
+        if self._desc.params != self.flat.data_ptr():
+            self._fill_desc()
+        return C.byref(self._desc)
+
+    def view(self, name: str) -> torch.Tensor:
+        off, shp = self._views[name]
+        return self.flat.data[off: off + int(np.prod(shp))].view(shp)
+
+    def named_views(self) -> dict[str, torch.Tensor]:
+        return {k: self.view(k) for k in self._views}
+
+    def load_arrays(self, W1: Any, b1: Any, W2: Any, b2: Any, W3: Any, b3: Any) -> "ActorCriticNet":
+        with torch.no_grad():
+            for k, a in zip(("W1", "b1", "W2", "b2", "W3", "b3"), (W1, b1, W2, b2, W3, b3)):
+                self.view(k).copy_(torch.as_tensor(np.asarray(a), dtype=torch.float32).reshape(self._views[k][1]))
+        return self
+
+    def load_reference_state_dict(self, sd: dict[str, Any]) -> "ActorCriticNet":
+        """Copy weights from a reference ActorCritic(actor, critic).state_dict() (shared Net trunk)."""
+        pick = lambda suf, root: next(v for k, v in sd.items() if k.startswith(root) and k.endswith(suf))  # noqa: E731
+        W3 = [pick("last.model.0.weight", "actor")] + ([pick("last.model.0.weight", "critic")] if self.value_index >= 0 else [])
+        b3 = [pick("last.model.0.bias", "actor")] + ([pick("last.model.0.bias", "critic")] if self.value_index >= 0 else [])
+        return self.load_arrays(pick("model.model.0.weight", "actor.preprocess"), pick("model.model.0.bias", "actor.preprocess"),
+                                pick("model.model.2.weight", "actor.preprocess"), pick("model.model.2.bias", "actor.preprocess"),
+                                np.concatenate([np.asarray(w) for w in W3], 0), np.concatenate([np.asarray(b) for b in b3], 0))
+
+    def reset_optimizer(self) -> None:
+        self.grads.zero_(); self.adam_m.zero_(); self.adam_v.zero_(); self.adam_step.zero_()
+
+    # -- forward ----------------------------------------------------------------------------
+    def forward(self, obs: torch.Tensor, mode: str = "raw", act: torch.Tensor | None = None, seed: int = 0, counter: int = 0,
+                rows: torch.Tensor | None = None, scatter: bool = False, out: dict[str, torch.Tensor] | None = None,
+                want_logits: bool = False, want_entropy: bool = False) -> dict[str, torch.Tensor]:
+        """One kernel launch (tsm_net_forward).  obs: [n_total, in_dim] float32 on the device.
+        Returns a dict with `out` (mode raw) or `act`, `logp`, `value` (+ `logits`, `entropy`)."""
+        assert obs.is_cuda and obs.dtype == torch.float32 and obs.is_contiguous()
+        x = obs.view(-1, self.in_dim)
+        n = int(rows.numel()) if rows is not None else x.shape[0]
+        n_out = x.shape[0] if (scatter and rows is not None) else n
+        m = MODES[mode]
+        o = dict(out or {})
+        dev = self.device
+        if m == 0:
+            if "out" not in o and not (self.value_index >= 0 and "value" in o):
+                o["out"] = torch.empty(n_out, self.out_dim, dtype=torch.float32, device=dev)
+        else:
+            if m == 3:
+                assert act is not None
+                o["act"] = act.to(torch.int32).contiguous().view(-1)
+            elif "act" not in o:
+                o["act"] = torch.empty(n_out, dtype=torch.int32, device=dev)
+            if "logp" not in o:
+                o["logp"] = torch.empty(n_out, dtype=torch.float32, device=dev)
+            if self.value_index >= 0 and "value" not in o:
+                o["value"] = torch.empty(n_out, dtype=torch.float32, device=dev)
+            if want_logits and "out" not in o:
+                o["out"] = torch.empty(n_out, self.n_act, dtype=torch.float32, device=dev)
+            if want_entropy and "entropy" not in o:
+                o["entropy"] = torch.empty(n_out, dtype=torch.float32, device=dev)
+        P = _lib.ptr
+        _lib.check(_lib.lib().tsm_net_forward(self.desc, P(x), P(rows), n, m, int(scatter), int(seed), int(counter),
+                                              P(o.get("out")), P(o.get("act")), P(o.get("logp")), P(o.get("value")),
+                                              P(o.get("entropy")), _lib.stream_ptr()))
+        if m != 0 and "out" in o:
+            o["logits"] = o["out"]
+        return o
