@@ -160,6 +160,14 @@ int tsm_buf_gather(const tsm_buf* buf, const int64_t* idx, int64_t n,
                    const float* const* h_extra_in, float* const* h_extra_out, int n_extra,
                    tsm_stream_t stream);
 
+/* Episode statistics of one vector step (collector.py:983-1024, CollectStats :116-254): rows with
+ * ep_len > 0 (the outputs of tsm_buf_add) finished an episode.  acc (device double[9], caller
+ * initialises to {0,0,0,+inf,-inf,0,0,+inf,-inf}) accumulates {count, sum ret, sum ret^2, min ret,
+ * max ret, sum len, sum len^2, min len, max len}.  Optionally appends (ret, len) of each episode
+ * to list_ret / list_len through the device counter list_count (order within a step is not
+ * defined; entries beyond list_capacity are counted but dropped). */
+int tsm_episode_stats(const double* ep_ret, const int64_t* ep_len, int64_t n, double* acc, double* list_ret,
+                      int64_t* list_len, int64_t* list_count, int64_t list_capacity, tsm_stream_t stream);
 
 /* =========================================================================================
  * K1  Batched MPE (simple_spread / simple_tag) step, reset, observe, reward

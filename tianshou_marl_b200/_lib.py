@@ -96,6 +96,7 @@ _SIGS = {
     "tsm_ppo_minibatch": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i64, c_vp, c_vp, c_vp]),
     "tsm_adam_step": (c_i32, [c_vp, c_f32, c_f32, c_f32, c_f32, c_f32, c_f32, c_vp, c_vp]),
     "tsm_ppo_epoch": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_f32, c_f32, c_f32, c_f32, c_f32, c_vp, c_vp]),
+    "tsm_episode_stats": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_i64, c_vp]),
     "tsm_buf_gather": (c_i32, [c_vp, c_vp, c_i64] + [c_vp] * 9 + [c_vp, c_vp, c_i32, c_vp]),
 }
 
@@ -158,3 +159,38 @@ def stream_ptr() -> int:
     import torch
 
     return torch.cuda.current_stream().cuda_stream
+
+
+# -- optional stage timer (bench.py installs one; None costs one attribute check per stage) ------
+class StageTimer:
+    """CUDA-event pairs around stages, recorded on the launching (current) stream."""
+
+    def __init__(self) -> None:
+        self.pairs: list = []
+
+    def start(self, name: str):
+        import torch
+
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        self.pairs.append((name, a, b))
+        return b
+
+    def totals(self) -> dict:
+        out: dict = {}
+        for name, a, b in self.pairs:
+            ms, n = out.get(name, (0.0, 0))
+            out[name] = (ms + a.elapsed_time(b), n + 1)
+        return out
+
+
+timer: StageTimer | None = None
+
+
+def t_start(name: str):
+    return timer.start(name) if timer is not None else None
+
+
+def t_stop(tok) -> None:
+    if tok is not None:
+        tok.record()

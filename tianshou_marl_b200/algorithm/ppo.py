@@ -196,8 +196,13 @@ class PPO:
         # ---- _add_returns_and_advantages (a2c.py:113-151): critic(obs), critic(obs_next) ----
         if self.reuse_rollout and "value" in st and "logp" in st:
             raise NotImplementedError("reuse_rollout_policy_outputs is wired by the fused collector")
+        tk = _lib.t_start("critic_forward")
         net.forward(obs_all, mode="raw", out={"value": v_s.view(-1)})
+        _lib.t_stop(tk)
+        tk = _lib.t_start("critic_forward")
         net.forward(st["obs_next"].view(size * R, O), mode="raw", out={"value": v_n.view(-1)})
+        _lib.t_stop(tk)
+        tk = _lib.t_start("gae")
         if lockstep:
             start = buffer._lockstep_ins if lock_len == size else 0
             B = lock_len * R
@@ -218,8 +223,11 @@ class PPO:
             adv.view(-1)[slot] = a_f
             ret.view(-1)[slot] = r_f
             start, lock_len = 0, size
+        _lib.t_stop(tk)
         # ---- logp_old (ppo.py:157-161) ----
+        tk = _lib.t_start("logp_old_forward")
         net.forward(obs_all, mode="eval", act=st["act"].view(-1), out={"logp": logp.view(-1), "value": self._buf("scratch_v", (size * R,))})
+        _lib.t_stop(tk)
         # ---- minibatch loop (ppo.py:173-216) ----
         bounds = self.split_bounds(B, batch_size)
         n_mb = len(bounds) - 1
@@ -255,7 +263,10 @@ class PPO:
             self._epoch_counter += 1
             st_ep, sums_ep = stats[ep * n_mb:], sums[ep * n_mb:]
             if self.advantage_normalization:
+                tk = _lib.t_start("adv_stats")
                 _lib.check(L.tsm_ppo_adv_stats(C.byref(pb), P(bounds_dev), n_mb, self._eps, P(st_ep), S))
+                _lib.t_stop(tk)
+            tk = _lib.t_start("ppo_epoch")
             if world == 1:
                 _lib.check(L.tsm_ppo_epoch(net.desc, C.byref(pb), C.byref(self._cfg), h_bounds, n_mb,
                                            P(st_ep) if self.advantage_normalization else None, o.lr, o.betas[0], o.betas[1], o.eps,
@@ -266,6 +277,7 @@ class PPO:
                                                    P(st_ep[m:]) if self.advantage_normalization else None, P(sums_ep[m:]), S))
                     torch.distributed.all_reduce(net.grads)  # NCCL sum over ranks
                     _lib.check(L.tsm_adam_step(net.desc, o.lr, o.betas[0], o.betas[1], o.eps, mgn, 1.0 / world, None, S))
+            _lib.t_stop(tk)
         # ---- stats: one device -> host copy for the whole update (the reference does 4 .item() per minibatch) ----
         h = sums.cpu().numpy()
         n_per = np.tile(np.diff(np.asarray(bounds)), repeat).astype(np.float64)

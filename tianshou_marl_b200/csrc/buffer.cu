@@ -281,6 +281,59 @@ __global__ void gather_scalar_kernel(tsm_buf b, const int64_t* __restrict__ idx,
         if (q < ex.n) ex.out[q][k] = ex.in[q][s];
 }
 
+// ---------------------------------------------------------------------------------------------
+// episode statistics of one vector step: rows whose ep_len > 0 finished an episode
+// (collector.py:983-1024 loops over done envs on the host; CollectStats :116-254).
+// acc[0..8] = {count, sum_ret, sum_ret^2, min_ret, max_ret, sum_len, sum_len^2, min_len, max_len}
+__device__ __forceinline__ void atomic_min_d(double* a, double v) {
+    unsigned long long* p = reinterpret_cast<unsigned long long*>(a);
+    unsigned long long old = *p;
+    while (__longlong_as_double((long long)old) > v) {
+        const unsigned long long prev = atomicCAS(p, old, (unsigned long long)__double_as_longlong(v));
+        if (prev == old) break;
+        old = prev;
+    }
+}
+__device__ __forceinline__ void atomic_max_d(double* a, double v) {
+    unsigned long long* p = reinterpret_cast<unsigned long long*>(a);
+    unsigned long long old = *p;
+    while (__longlong_as_double((long long)old) < v) {
+        const unsigned long long prev = atomicCAS(p, old, (unsigned long long)__double_as_longlong(v));
+        if (prev == old) break;
+        old = prev;
+    }
+}
+
+__global__ void __launch_bounds__(THREADS) episode_stats_kernel(const double* __restrict__ ep_ret, const int64_t* __restrict__ ep_len,
+                                                               int64_t n, double* __restrict__ acc, double* __restrict__ list_ret,
+                                                               int64_t* __restrict__ list_len, int64_t* __restrict__ list_count,
+                                                               int64_t cap) {
+    double c = 0, s = 0, s2 = 0, mn = INFINITY, mx = -INFINITY, l = 0, l2 = 0, lmn = INFINITY, lmx = -INFINITY;
+    for (int64_t i = (int64_t)blockIdx.x * THREADS + threadIdx.x; i < n; i += (int64_t)gridDim.x * THREADS) {
+        const int64_t len = ep_len[i];
+        if (len > 0) {
+            const double r = ep_ret[i], dl = (double)len;
+            c += 1; s += r; s2 += r * r; mn = fmin(mn, r); mx = fmax(mx, r);
+            l += dl; l2 += dl * dl; lmn = fmin(lmn, dl); lmx = fmax(lmx, dl);
+            if (list_count) {
+                const int64_t at = (int64_t)atomicAdd(reinterpret_cast<unsigned long long*>(list_count), 1ull);
+                if (at < cap) { list_ret[at] = r; list_len[at] = len; }
+            }
+        }
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        c += __shfl_down_sync(0xffffffffu, c, d); s += __shfl_down_sync(0xffffffffu, s, d); s2 += __shfl_down_sync(0xffffffffu, s2, d);
+        l += __shfl_down_sync(0xffffffffu, l, d); l2 += __shfl_down_sync(0xffffffffu, l2, d);
+        mn = fmin(mn, __shfl_down_sync(0xffffffffu, mn, d)); mx = fmax(mx, __shfl_down_sync(0xffffffffu, mx, d));
+        lmn = fmin(lmn, __shfl_down_sync(0xffffffffu, lmn, d)); lmx = fmax(lmx, __shfl_down_sync(0xffffffffu, lmx, d));
+    }
+    if ((threadIdx.x & 31) == 0 && c > 0) {
+        atomicAdd(acc + 0, c); atomicAdd(acc + 1, s); atomicAdd(acc + 2, s2); atomic_min_d(acc + 3, mn); atomic_max_d(acc + 4, mx);
+        atomicAdd(acc + 5, l); atomicAdd(acc + 6, l2); atomic_min_d(acc + 7, lmn); atomic_max_d(acc + 8, lmx);
+    }
+}
+
 }  // namespace buf
 }  // namespace tsm
 
@@ -438,5 +491,17 @@ extern "C" int tsm_buf_gather(const tsm_buf* b, const int64_t* idx, int64_t n, f
                                                                               trunc_out, done_out, logp_out, value_out, ex);
         TSM_LAUNCH_CHECK();
     }
+    return TSM_OK;
+}
+
+extern "C" int tsm_episode_stats(const double* ep_ret, const int64_t* ep_len, int64_t n, double* acc, double* list_ret,
+                                 int64_t* list_len, int64_t* list_count, int64_t list_capacity, tsm_stream_t stream) {
+    TSM_REQUIRE(n >= 0, "n >= 0");
+    if (n == 0) return TSM_OK;
+    TSM_REQUIRE(ep_ret && ep_len && acc, "ep_ret / ep_len / acc != NULL");
+    TSM_REQUIRE(!list_count || (list_ret && list_len && list_capacity >= 0), "episode list arrays");
+    episode_stats_kernel<<<grid_for(n, THREADS), THREADS, 0, as_stream(stream)>>>(ep_ret, ep_len, n, acc, list_ret, list_len,
+                                                                                 list_count, list_capacity);
+    TSM_LAUNCH_CHECK();
     return TSM_OK;
 }

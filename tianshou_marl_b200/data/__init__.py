@@ -1,4 +1,5 @@
 from .batch import Batch, split_indices
 from .buffer import ReplayBuffer, VectorReplayBuffer
+from .collector import Collector
 
-__all__ = ["Batch", "split_indices", "ReplayBuffer", "VectorReplayBuffer"]
+__all__ = ["Batch", "split_indices", "ReplayBuffer", "VectorReplayBuffer", "Collector"]

@@ -1,0 +1,265 @@
+"""Device-resident Collector: drop-in for tianshou/data/collector.py:548-1098 (`Collector`) on the
+on-policy path.
+
+    reset / reset_env / reset_buffer / reset_stat   collector.py:404-442
+    collect(n_step | n_episode, random, ...)        collector.py:461-535
+    _collect loop                                   collector.py:770-1098
+    _compute_action_policy_hidden                   collector.py:704-767
+
+Two code paths, both through libtsm_b200 only:
+ * fused (MPEVectorEnv + DiscreteActorPolicy + lock-step VectorReplayBuffer): per vector step the
+   policy kernel writes act / logp / value straight into the buffer's time-major slot, the MPE
+   step kernel writes obs_next / rew / flags into the slot and the next observation into the
+   NEXT slot's obs (so obs is written once, by the kernel that produces it), and one counter
+   kernel updates the ring state.  No host round trip inside the loop; episode statistics are
+   reduced on the device and read once per collect() call.
+ * generic: any vector env with the reference protocol (reset(env_id) / step(action, id)), one
+   policy call + env.step + buffer.add(Batch) per step, like the reference loop.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import time
+from typing import Any
+
+import numpy as np
+import torch
+
+from .. import _lib
+from ..env.mpe import MPEVectorEnv
+from ..utils.stats import CollectStats
+from .batch import Batch
+from .buffer import VectorReplayBuffer
+
+
+class Collector:
+    def __init__(self, policy: Any, env: Any, buffer: VectorReplayBuffer | None = None, exploration_noise: bool = False,
+                 on_episode_done_hook: Any = None, on_step_hook: Any = None, raise_on_nan_in_buffer: bool = False,
+                 collect_stats_class: type = CollectStats, episode_list: bool = True, random_seed: int = 0) -> None:
+        self.algorithm = policy if hasattr(policy, "policy") else None  # accepts Policy or Algorithm (collector.py:358)
+        self.policy = policy.policy if hasattr(policy, "policy") else policy
+        self.env = env
+        self.env_num = len(env)
+        if buffer is None:
+            buffer = VectorReplayBuffer(self.env_num, self.env_num, index_type="torch")
+        if buffer.buffer_num < self.env_num:  # collector.py:373-376
+            raise ValueError(
+                f"Buffer has only {buffer.buffer_num} buffers, but at least {self.env_num=} are needed.")
+        self.buffer = buffer
+        self.exploration_noise = exploration_noise
+        self.on_episode_done_hook, self.on_step_hook = on_episode_done_hook, on_step_hook
+        if on_episode_done_hook is not None or on_step_hook is not None:
+            raise NotImplementedError("per-step / per-episode Python hooks are not on the device path")
+        self.raise_on_nan_in_buffer = raise_on_nan_in_buffer
+        self.collect_stats_class = collect_stats_class
+        self.episode_list = episode_list
+        self.collect_step, self.collect_episode, self.collect_time = 0, 0, 0.0
+        self._pre_collect_obs: Any = None
+        self._random_seed, self._random_counter = int(random_seed), 0
+        self._is_closed = False
+        dev = getattr(env, "device", getattr(buffer, "device", torch.device("cuda")))
+        self.device = dev
+        R = self.env_num
+        self._ep_ret = torch.zeros(R, dtype=torch.float64, device=dev)
+        self._ep_len = torch.zeros(R, dtype=torch.int64, device=dev)
+        self._acc = torch.zeros(9, dtype=torch.float64, device=dev)
+        self._list_cap = 0
+        self._list_ret = self._list_len = None
+        self._list_count = torch.zeros(1, dtype=torch.int64, device=dev)
+        self._carry: torch.Tensor | None = None
+
+    # -- reference surface ------------------------------------------------------------------
+    def close(self) -> None:
+        self.env.close()
+        self._pre_collect_obs = None
+        self._is_closed = True
+
+    def reset(self, reset_buffer: bool = True, reset_stats: bool = True, gym_reset_kwargs: dict | None = None) -> tuple[Any, Any]:
+        obs, info = self.reset_env(gym_reset_kwargs)
+        if reset_buffer:
+            self.reset_buffer()
+        if reset_stats:
+            self.reset_stat()
+        self._is_closed = False
+        return obs, info
+
+    def reset_stat(self) -> None:
+        self.collect_step, self.collect_episode, self.collect_time = 0, 0, 0.0
+
+    def reset_buffer(self, keep_statistics: bool = False) -> None:
+        self.buffer.reset(keep_statistics=keep_statistics)
+
+    def reset_env(self, gym_reset_kwargs: dict | None = None) -> tuple[Any, Any]:
+        obs, info = self.env.reset(**(gym_reset_kwargs or {}))
+        self._pre_collect_obs = obs
+        self._carry = None
+        return obs, info
+
+    # -- collect ------------------------------------------------------------------------------
+    def collect(self, n_step: int | None = None, n_episode: int | None = None, random: bool = False, render: float | None = None,
+                reset_before_collect: bool = False, gym_reset_kwargs: dict | None = None) -> CollectStats:
+        # collector.py:526-535
+        if n_step is not None and n_episode is not None or (n_step is None and n_episode is None):
+            raise ValueError(f"Only one of n_step and n_episode should be set, but got {n_step=} and {n_episode=}.")
+        if n_step is not None and n_step < 1 or n_episode is not None and n_episode < 1:
+            raise ValueError("n_step / n_episode must be positive")
+        if reset_before_collect:
+            self.reset(reset_buffer=False, gym_reset_kwargs=gym_reset_kwargs)
+        if self._pre_collect_obs is None:  # collector.py:827-831
+            raise ValueError("Initial obs and info should not be None. Either reset the collector (using reset or reset_env) "
+                             "or pass reset_before_collect=True to collect.")
+        t0 = time.time()
+        was_training = getattr(self.policy, "training", False)
+        if hasattr(self.policy, "train"):
+            self.policy.train(False)  # torch_train_mode(policy, False), collector.py:506
+        try:
+            stats = self._collect(n_step, n_episode, random)
+        finally:
+            if hasattr(self.policy, "train"):
+                self.policy.train(was_training)
+        stats.set_collect_time(max(time.time() - t0, 1e-9))
+        stats.refresh_all_sequence_stats()
+        self.collect_step += stats.n_collected_steps
+        self.collect_episode += stats.n_collected_episodes
+        self.collect_time += stats.collect_time
+        return stats
+
+    def _fused_ok(self, random: bool) -> bool:
+        from ..algorithm.ppo import DiscreteActorPolicy
+
+        b = self.buffer
+        return (isinstance(self.env, MPEVectorEnv) and (random or isinstance(self.policy, DiscreteActorPolicy))
+                and b._lockstep_len is not None and b.buffer_num == self.env_num and b._save_obs_next)
+
+    def _collect(self, n_step: int | None, n_episode: int | None, random: bool) -> CollectStats:
+        R = self.env_num
+        dev = self.device
+        self._acc.copy_(torch.tensor([0, 0, 0, np.inf, -np.inf, 0, 0, np.inf, -np.inf], dtype=torch.float64))
+        self._list_count.zero_()
+        n_vec = None if n_step is None else -(-n_step // R)  # ceil(n_step / R) vector steps (collector.py:917,1066)
+        if self.episode_list:
+            horizon = n_vec if n_vec is not None else 4 * getattr(self.env, "max_cycles", 25)
+            cap = R * max(1, horizon // max(1, getattr(self.env, "max_cycles", 25)) + 1)
+            if cap > self._list_cap:
+                self._list_ret = torch.zeros(cap, dtype=torch.float64, device=dev)
+                self._list_len = torch.zeros(cap, dtype=torch.int64, device=dev)
+                self._list_cap = cap
+        fused = self._fused_ok(random)
+        steps = 0
+        while True:
+            if fused:
+                self._fused_step(random, last=(n_vec is not None and steps == n_vec - 1) or n_vec is None)
+            else:
+                self._generic_step(random)
+            steps += 1
+            if n_vec is not None:
+                if steps >= n_vec:
+                    break
+            elif int(self._acc[0].item()) >= n_episode:  # one small D2H per step only in n_episode mode
+                break
+        acc = self._acc.cpu().numpy()
+        n_ep = int(acc[0])
+        st = self.collect_stats_class(n_collected_episodes=n_ep, n_collected_steps=steps * R)
+        if self.episode_list and n_ep > 0:
+            k = min(n_ep, self._list_cap)
+            st.returns = self._list_ret[:k].cpu().numpy()
+            st.lens = self._list_len[:k].cpu().numpy()
+        self.last_episode_summary = {"count": n_ep, "ret_sum": acc[1], "ret_sqsum": acc[2], "ret_min": acc[3], "ret_max": acc[4],
+                                     "len_sum": acc[5], "len_sqsum": acc[6], "len_min": acc[7], "len_max": acc[8]}
+        return st
+
+    # -- one vector step, fused ---------------------------------------------------------------
+    def _fused_step(self, random: bool, last: bool) -> None:
+        env, buf, L, P, S = self.env, self.buffer, _lib.lib(), _lib.ptr, _lib.stream_ptr()
+        R, O = self.env_num, env.obs_dim
+        if "obs" not in buf._store:
+            buf._alloc((O,), want_policy=True)
+        st = buf._store
+        size = buf._size
+        slot = buf._lockstep_ins
+        nxt = (slot + 1) % size
+        obs_slot = st["obs"][slot]
+        # the observation to act on: already in the slot if the previous fused step put it there
+        src = self._pre_collect_obs
+        if not (isinstance(src, torch.Tensor) and src.data_ptr() == obs_slot.data_ptr()):
+            obs_slot.copy_(torch.as_tensor(src, device=self.device).reshape(R, O))
+        act_slot = st["act"][slot]
+        if random:
+            _lib.check(L.tsm_random_actions(P(act_slot), R, env.single_action_space.n, self._random_seed, self._random_counter, S))
+            self._random_counter += 1
+            if "logp" in st:
+                st["logp"][slot].zero_()
+                st["value"][slot].zero_()
+        else:
+            pol = self.policy
+            mode = "mode" if (pol.deterministic_eval and not pol.is_within_training_step) else "sample"
+            out = {"act": act_slot, "logp": st["logp"][slot]} if "logp" in st else {"act": act_slot}
+            if "value" in st and pol.actor.value_index >= 0:
+                out["value"] = st["value"][slot]
+            tk = _lib.t_start("policy_forward")
+            pol.actor.forward(obs_slot, mode=mode, seed=pol.seed, counter=pol._counter, out=out)
+            _lib.t_stop(tk)
+            pol._counter += 1
+        # world step: obs_next / rew / flags into this slot; the observation to act on next goes to the
+        # next slot's obs unless this is the last step of the call or the ring would wrap onto live data
+        if last or buf._lockstep_len + 1 >= size:
+            if self._carry is None:
+                self._carry = torch.empty(R, O, dtype=torch.float32, device=self.device)
+            carry = self._carry
+        else:
+            carry = st["obs"][nxt]
+        tk = _lib.t_start("mpe_step")
+        _lib.check(L.tsm_mpe_step(C.byref(env._desc), P(act_slot), P(st["obs_next"][slot]), P(st["rew"][slot]),
+                                  P(st["terminated"][slot]), P(st["truncated"][slot]), 1, P(carry), S))
+        _lib.t_stop(tk)
+        tk = _lib.t_start("buf_counters")
+        # ring counters + done flag + episode return/length (payload pointers alias the slot: self-copy)
+        _lib.check(L.tsm_buf_add(C.byref(buf._desc), None, P(act_slot), P(st["rew"][slot]), P(st["terminated"][slot]),
+                                 P(st["truncated"][slot]), None, None, None, None, R, None, P(self._ep_ret), P(self._ep_len), None, S))
+        buf._lockstep_len = min(buf._lockstep_len + 1, size)
+        buf._lockstep_ins = nxt
+        _lib.check(L.tsm_episode_stats(P(self._ep_ret), P(self._ep_len), R, P(self._acc),
+                                       P(self._list_ret) if self.episode_list else None, P(self._list_len) if self.episode_list else None,
+                                       P(self._list_count) if self.episode_list else None, self._list_cap, S))
+        _lib.t_stop(tk)
+        self._pre_collect_obs = carry
+
+    # -- one vector step, generic (reference loop) ---------------------------------------------
+    def _generic_step(self, random: bool) -> None:
+        env, buf = self.env, self.buffer
+        obs = self._pre_collect_obs
+        R = self.env_num
+        if random:
+            act = np.array([env.action_space[i].sample() for i in range(R)])
+            pol_out = None
+        else:
+            pol_out = self.policy(Batch(obs=obs, info=Batch()), None)
+            act = pol_out.act
+        act_env = self.policy.map_action(act) if hasattr(self.policy, "map_action") else act
+        if isinstance(env, MPEVectorEnv):
+            obs_next, rew, term, trunc, info = env.step(act_env)
+        else:
+            a = act_env.cpu().numpy() if isinstance(act_env, torch.Tensor) else act_env
+            obs_next, rew, term, trunc, info = env.step(a, np.arange(R))
+        b = Batch(obs=obs, act=act, rew=rew, terminated=term, truncated=trunc, obs_next=obs_next)
+        if pol_out is not None and "logp" in pol_out and "value" in pol_out:
+            b.__dict__["policy"] = Batch(logp=pol_out.logp, value=pol_out.value)
+        _, ep_ret, ep_len, _ = buf.add(b, buffer_ids=None if buf.buffer_num == R else np.arange(R))
+        er = torch.as_tensor(ep_ret, device=self.device).to(torch.float64).contiguous()
+        el = torch.as_tensor(ep_len, device=self.device).to(torch.int64).contiguous()
+        P = _lib.ptr
+        _lib.check(_lib.lib().tsm_episode_stats(P(er), P(el), R, P(self._acc), P(self._list_ret) if self.episode_list else None,
+                                                P(self._list_len) if self.episode_list else None,
+                                                P(self._list_count) if self.episode_list else None, self._list_cap, _lib.stream_ptr()))
+        done = torch.as_tensor(np.asarray(term) | np.asarray(trunc)) if not isinstance(term, torch.Tensor) else (term | trunc)
+        if bool(done.any()):
+            ids = torch.nonzero(done).reshape(-1)
+            ids_h = ids.cpu().numpy()
+            obs_reset, _ = env.reset(ids if isinstance(env, MPEVectorEnv) else ids_h)
+            if isinstance(obs_next, torch.Tensor):
+                obs_next = obs_next.clone()
+                obs_next[ids.to(obs_next.device)] = torch.as_tensor(obs_reset, device=obs_next.device)
+            else:
+                obs_next = np.array(obs_next, copy=True)
+                obs_next[ids_h] = obs_reset
+        self._pre_collect_obs = obs_next
