@@ -47,6 +47,7 @@ def parse() -> argparse.Namespace:
     p.add_argument("--batch-size", type=int, default=65536)
     p.add_argument("--repeat", type=int, default=4)
     p.add_argument("--hidden", type=int, default=64)
+    p.add_argument("--engine", default="tc", choices=["tc", "fp32"], help="MLP kernels: tcgen05 (fp16 operands, fp32 accumulate) or exact fp32")
     p.add_argument("--no-update", action="store_true", help="collect + GAE only")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--cpu-envs", type=int, default=2048, help="reference arm: environments in the bounded sample")

@@ -244,7 +244,9 @@ int tsm_random_actions(int32_t* act, int64_t n, int n_act, uint64_t seed, uint64
  * setup (one Net trunk, DiscreteActor.last + DiscreteCritic.last) is out_dim = n_act + 1.
  * ========================================================================================= */
 typedef struct tsm_net {
-    int32_t in_dim, hidden, out_dim, n_act, value_index, _pad;
+    int32_t in_dim, hidden, out_dim, n_act, value_index;
+    int32_t engine;     /* 0: fp32 CUDA-core kernels (exact parity path); 1: tcgen05 kernels (fp16 operands, fp32 accumulate in
+                           TMEM; needs hidden == 64, in_dim <= 31, out_dim <= 8) */
     int64_t n_params;   /* == tsm_net_param_count(in_dim, hidden, out_dim) */
     float* params;      /* [n_params] */
     float* grads;       /* [n_params] accumulated by tsm_ppo_minibatch, zeroed by tsm_adam_step */
@@ -319,6 +321,14 @@ int tsm_adam_step(const tsm_net* net, float lr, float beta1, float beta2, float 
 int tsm_ppo_epoch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, const int64_t* h_mb_bounds,
                   int64_t n_minibatches, const float* mb_stats, float lr, float beta1, float beta2, float eps,
                   float max_grad_norm, double* loss_sums, tsm_stream_t stream);
+
+/* tcgen05 self test (tests only): D[128][n] = A * B with A / B given as shared-memory images
+ * (float32 words, copied verbatim to smem) and explicit descriptor fields
+ * h_desc = {a_lbo, a_sbo, a_kstep_bytes, b_lbo, b_sbo, b_kstep_bytes}; kind::tf32, M = 128,
+ * `ksteps` MMAs of K = 8 (tf32) or 16 (f16/bf16).  Pins the operand-layout semantics csrc/mlp_tc.cu relies on. */
+int tsm_tc_selftest(const float* a_img, int a_floats, const float* b_img, int b_floats, const uint32_t* h_desc,
+                    int a_mn_major, int b_mn_major, int n, int ksteps, int kind /*0 tf32 (K=8), 1 f16 (K=16)*/, int a_bf16,
+                    int b_bf16, float* d_out, tsm_stream_t stream);
 
 #ifdef __cplusplus
 }

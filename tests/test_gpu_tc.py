@@ -1,0 +1,145 @@
+"""tcgen05 engine (csrc/mlp_tc.cu) vs the exact fp32 engine (csrc/mlp.cu, itself pinned to the
+reference fixtures in test_gpu_ppo.py).  Operands are rounded to fp16 (11-bit significand), sums are
+fp32: forward outputs agree to ~2e-3 absolute on O(1) values; gradients to ~1% of their scale."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _h(a, dt=torch.float16):  # [rows][F] -> 16-bit image [F/8][rows][8] as float32 words, and the rounded values
+    r, f = a.shape
+    t = torch.as_tensor(a).to(dt).reshape(r, f // 8, 8).permute(1, 0, 2).contiguous()
+    return t.view(torch.float32).reshape(-1).numpy(), t.permute(1, 0, 2).reshape(r, f).double().numpy()
+
+
+def _gemm(a_img, b_img, desc, a_mn, b_mn, n, ksteps):
+    from tianshou_marl_b200 import _lib
+
+    d = torch.full((128, n), float("nan"), device="cuda")
+    A, B = torch.as_tensor(a_img, device="cuda"), torch.as_tensor(b_img, device="cuda")
+    h = (C.c_uint32 * 6)(*desc)
+    _lib.check(_lib.lib().tsm_tc_selftest(A.data_ptr(), A.numel(), B.data_ptr(), B.numel(), C.cast(h, C.c_void_p), a_mn, b_mn, n, ksteps,
+                                          1, 0, 0, d.data_ptr(), _lib.stream_ptr()))
+    torch.cuda.synchronize()
+    return d.cpu().numpy()
+
+
+def test_descriptor_semantics():
+    """The three operand views mlp_tc_kernels.cuh relies on, one tcgen05.mma group each."""
+    rng = np.random.default_rng(0)
+    N, K, O = 64, 32, 16
+    ai, a = _h(rng.normal(size=(128, K)).astype(np.float32))
+    bi, w = _h(rng.normal(size=(N, K)).astype(np.float32))
+    d = _gemm(ai, bi, [2048, 128, 4096, N * 16, 128, 2 * N * 16], 0, 0, N, K // 16)  # rows x feats times weights[out][in]
+    assert np.abs(d - a @ w.T).max() < 1e-4
+    ai, a = _h(rng.normal(size=(128, O)).astype(np.float32))
+    bi, w = _h(rng.normal(size=(O, N)).astype(np.float32))  # W[out][in] image read as N = in, K = out
+    d = _gemm(ai, bi, [2048, 128, 4096, 128, O * 16, 256], 0, 1, N, O // 16)
+    assert np.abs(d - a @ w).max() < 1e-4
+    pi, p = _h(rng.normal(size=(128, 128)).astype(np.float32))
+    qi, q = _h(rng.normal(size=(128, N)).astype(np.float32))
+    d = _gemm(pi, qi, [128, 2048, 256, 128, 2048, 256], 1, 1, N, 128 // 16)  # K = rows for both
+    assert np.abs(d - p.T @ q).max() < 1e-3
+
+
+@pytest.mark.parametrize("O,n", [(18, 128), (18, 5000), (16, 777), (7, 130), (31, 1000)])
+def test_forward_tc_vs_fp32(O, n):
+    from tianshou_marl_b200.utils import ActorCriticNet
+
+    net = ActorCriticNet(O, 64, 5, seed=O)
+    with torch.no_grad():
+        net.view("b1").normal_(0, 0.1); net.view("b2").normal_(0, 0.1); net.view("b3").normal_(0, 0.1)
+    obs = torch.randn(n, O, device="cuda")
+    net.engine = "fp32"
+    ref = net.forward(obs, mode="mode", want_logits=True, want_entropy=True)
+    net.engine = "tc"
+    got = net.forward(obs, mode="mode", want_logits=True, want_entropy=True)
+    assert (got["logits"] - ref["logits"]).abs().max().item() < 4e-3
+    assert (got["value"] - ref["value"]).abs().max().item() < 4e-3
+    assert (got["logp"] - ref["logp"]).abs().max().item() < 4e-3
+    assert (got["act"] == ref["act"]).float().mean().item() > 0.99  # arg-max flips only on near ties
+    # sampling: same Philox stream, so actions agree except where a CDF edge moved by the rounding
+    a1 = net.forward(obs, mode="sample", seed=3, counter=9)["act"]
+    net.engine = "fp32"
+    a0 = net.forward(obs, mode="sample", seed=3, counter=9)["act"]
+    assert (a0 == a1).float().mean().item() > 0.99
+    # gather / scatter rows
+    rows = torch.randperm(n, device="cuda")[: n // 2].contiguous()
+    net.engine = "tc"
+    sub = net.forward(obs, mode="raw", rows=rows)
+    full = net.forward(obs, mode="raw")
+    assert torch.allclose(sub["out"], full["out"][rows], atol=1e-6)
+
+
+@pytest.mark.parametrize("O,n", [(18, 128), (18, 3000), (16, 65536), (9, 200)])
+def test_ppo_minibatch_tc_vs_fp32(O, n):
+    from tianshou_marl_b200 import _lib
+    from tianshou_marl_b200.utils import ActorCriticNet
+
+    rng = np.random.default_rng(n)
+    net = ActorCriticNet(O, 64, 5, seed=1)
+    with torch.no_grad():
+        net.view("b1").normal_(0, 0.1); net.view("b2").normal_(0, 0.1); net.view("b3").normal_(0, 0.1)
+    d = lambda a, dt=torch.float32: torch.as_tensor(a, device="cuda").to(dt).contiguous()  # noqa: E731
+    t = dict(obs=d(rng.normal(size=(n, O))), act=d(rng.integers(0, 5, n), torch.int32), adv=d(rng.normal(size=n)), ret=d(rng.normal(size=n)),
+             lp=d(np.log(0.2) + 0.3 * rng.normal(size=n)), vo=d(rng.normal(size=n)))
+    P = _lib.ptr
+    key = 0xABCDEF1234567
+    for cfgk in (dict(adv_norm=1), dict(adv_norm=0, value_clip=1, dual_clip=2.0, eps_clip=0.1)):
+        pb = _lib.TsmPpoBatch(obs=P(t["obs"]), act=P(t["act"]), adv=P(t["adv"]), ret=P(t["ret"]), logp_old=P(t["lp"]), v_old=P(t["vo"]),
+                              indices=None, size=1, n_rows=n, start=0, len=1, perm_key=key, perm_n=n)
+        pc = _lib.TsmPpoCfg(eps_clip=cfgk.get("eps_clip", 0.2), dual_clip=cfgk.get("dual_clip", 0.0), vf_coef=0.5, ent_coef=0.01,
+                            value_clip=cfgk.get("value_clip", 0), adv_norm=cfgk["adv_norm"])
+        stats = d(np.array([float(t["adv"].mean()), 1.0 / (float(t["adv"].std()) + 1e-8)]))
+        res = {}
+        for eng in ("fp32", "tc"):
+            net.engine = eng
+            net.grads.zero_()
+            sums = torch.zeros(4, dtype=torch.float64, device="cuda")
+            _lib.check(_lib.lib().tsm_ppo_minibatch(net.desc, C.byref(pb), C.byref(pc), 0, n, P(stats), P(sums), _lib.stream_ptr()))
+            res[eng] = (net.grads.clone(), sums.cpu().numpy())
+        g0, g1 = res["fp32"][0], res["tc"][0]
+        off = 0
+        for name, (o_, shp) in net._views.items():
+            k = int(np.prod(shp))
+            a, b = g0[o_: o_ + k], g1[o_: o_ + k]
+            scale = a.abs().max().item() + 1e-12
+            err = (a - b).abs().max().item()
+            # forward outputs carry ~2e-3 absolute rounding (11-bit operands), which moves the PPO ratio / clip decisions of
+            # individual rows; the effect on a gradient entry averages out with the minibatch size
+            assert err < (0.03 if n >= 3000 else 0.12) * scale + 1e-7, (name, err, scale, cfgk)
+        assert np.allclose(res["tc"][1][:3] / n, res["fp32"][1][:3] / n, rtol=5e-3, atol=2e-3)
+    net.engine = "fp32"
+
+
+def test_update_tc_tracks_fp32():
+    """Whole PPO.update on both engines from the same start: losses track each other and fall."""
+    from tianshou_marl_b200.algorithm import PPO, AdamOptimizerFactory, DiscreteActorPolicy
+    from tianshou_marl_b200.data import Batch, VectorReplayBuffer
+    from tianshou_marl_b200.utils import ActorCriticNet
+
+    R, T, O = 1024, 32, 18
+    out = {}
+    for eng in ("fp32", "tc"):
+        net = ActorCriticNet(O, 64, 5, seed=4, engine=eng)
+        pol = DiscreteActorPolicy(actor=net, seed=5)
+        alg = PPO(policy=pol, critic=net, optim=AdamOptimizerFactory(lr=1e-3), minibatch_order="device", max_grad_norm=0.5, seed=1)
+        buf = VectorReplayBuffer(R * T, R, index_type="torch")
+        g = torch.Generator(device="cuda").manual_seed(0)
+        obs = torch.randn(R, O, device="cuda", generator=g)
+        for t in range(T):
+            act = torch.randint(0, 5, (R,), device="cuda", generator=g)
+            nxt = obs + 0.1 * torch.randn(R, O, device="cuda", generator=g)
+            buf.add(Batch(obs=obs, act=act, rew=(obs[:, 0] * (act == 2).float()).contiguous(), terminated=torch.zeros(R, dtype=torch.bool, device="cuda"),
+                          truncated=torch.full((R,), (t + 1) % 8 == 0, device="cuda"), obs_next=nxt))
+            obs = nxt
+        pol.is_within_training_step = True
+        alg.update(buf, 4096, 4)
+        out[eng] = alg.last_sequences
+    for k in ("loss", "vf", "ent", "clip"):
+        assert np.allclose(out["tc"][k], out["fp32"][k], rtol=3e-2, atol=3e-3), (k, np.abs(out["tc"][k] - out["fp32"][k]).max())
+    assert out["tc"]["vf"][-1] < out["tc"]["vf"][0]

@@ -27,7 +27,7 @@ class Workload:
         self.env = MPEVectorEnv("simple_spread_v3", n_envs=self.E, n_agents=self.A, seed=1000 + rank)
         self.O = self.env.obs_dim
         self.buf = VectorReplayBuffer(self.T * self.R, self.R, index_type="torch")
-        self.net = ActorCriticNet(self.O, args.hidden, 5, seed=0)  # same init on every rank
+        self.net = ActorCriticNet(self.O, args.hidden, 5, seed=0, engine=args.engine)  # same init on every rank
         self.policy = DiscreteActorPolicy(actor=self.net, seed=77 + rank)
         self.alg = PPO(policy=self.policy, critic=self.net, optim=AdamOptimizerFactory(lr=3e-4), max_grad_norm=0.5,
                        minibatch_order="device", seed=rank)
@@ -36,7 +36,7 @@ class Workload:
         self.policy.is_within_training_step = True
         self.update = not args.no_update
         self.agent_steps_per_step = self.R * self.T
-        self.dtype = "f32"
+        self.dtype = "f16 operands / f32 accumulate (tcgen05)" if args.engine == "tc" else "f32"
         B = self.R * self.T
         self.n_mb = len(PPO.split_bounds(B, args.batch_size)) - 1
         self.launches_per_step = self.T * (K_POLICY + K_MPE + K_ADD + K_STATS) + 1
@@ -99,7 +99,7 @@ class Workload:
             t = stages[dom]["launch_ms"] * 1e-3
             ach = flop / t / 1e12
             out.update({"bound": "tensor", "achieved": ach, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach / tf_peak, "traffic": None,
-                        "flop_per_unit": 3.0 * fwd_flop, "units_per_launch": B, "note": "fp32 CUDA-core path measured against the bf16 tensor peak"})
+                        "flop_per_unit": 3.0 * fwd_flop, "units_per_launch": B, "note": "engine=%s; achieved counts the algorithmic FLOPs of fwd+bwd (33.8 kFLOP/row), stage = n_mb x (minibatch kernel + adam kernel)" % self.args.engine})
         elif dom in ("policy_forward", "critic_forward", "logp_old_forward"):
             flop = fwd_flop * units[dom]
             t = stages[dom]["launch_ms"] * 1e-3
@@ -121,6 +121,6 @@ class Workload:
         what = "collect+GAE+PPO update" if self.update else "collect+buffer write (no update)"
         return {"workload": f"C2 simple_spread_v3 A={self.A} E={self.E}/GPU T={self.T}: {what}; shared actor-critic MLP "
                             f"{self.O}->{a.hidden}->{a.hidden}->(5 logits, 1 value)", "envs_per_gpu": self.E, "agents": self.A,
-                "horizon": self.T, "rows_per_gpu": self.R, "batch_size": a.batch_size, "repeat": a.repeat, "hidden": a.hidden,
+                "horizon": self.T, "rows_per_gpu": self.R, "batch_size": a.batch_size, "repeat": a.repeat, "hidden": a.hidden, "engine": a.engine,
                 "minibatches_per_epoch": self.n_mb,
                 "l2": "inputs larger than L2: per-step working set %.0f MB > 126 MB" % (self.R * self.T * (8 * self.O + 30) / 1e6)}

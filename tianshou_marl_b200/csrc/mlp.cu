@@ -24,12 +24,14 @@
 #include "common.cuh"
 #include "philox.cuh"
 #include "feistel.cuh"
+#include "ppo_math.cuh"
 
 namespace tsm {
 namespace mlp {
 
+using namespace tsm::ppo;
+
 constexpr int THREADS = 256;
-constexpr int OUTP = 8;  // head width padded to 8 (OUT <= 8)
 
 template <int H>
 struct Cfg {
@@ -39,21 +41,6 @@ struct Cfg {
     static constexpr int RC = TM / 64;               // row chunks of 4 per thread in the layer GEMMs
     static constexpr int CC = H / 64;                // col chunks of 4 per thread
 };
-
-struct Offsets {
-    int64_t w1, b1, w2, b2, w3, b3, total;
-};
-__host__ __device__ inline Offsets offsets(int in_dim, int H, int out_dim) {
-    Offsets o;
-    o.w1 = 0;
-    o.b1 = (int64_t)H * in_dim;
-    o.w2 = o.b1 + H;
-    o.b2 = o.w2 + (int64_t)H * H;
-    o.w3 = o.b2 + H;
-    o.b3 = o.w3 + (int64_t)out_dim * H;
-    o.total = o.b3 + out_dim;
-    return o;
-}
 
 template <int H>
 struct Smem {
@@ -79,28 +66,6 @@ struct Smem {
         total = p;
     }
 };
-
-// ---------------------------------------------------------------------------------------------
-// where batch position p lives in the time-major device buffer
-struct BatchView {
-    const int64_t* indices;  // explicit env-major buffer indices per position (may be NULL)
-    int64_t size, n_rows;    // ring: slots per row, rows
-    int64_t start, len;      // lock-step view: row r holds `len` valid slots from ring slot `start`
-    uint64_t perm_key;       // Feistel key of the minibatch permutation
-    int64_t perm_n;          // domain of the permutation (0 = identity)
-};
-__device__ __forceinline__ int64_t slot_of(const BatchView& b, int64_t p) {
-    if (b.indices) {
-        const int64_t i = b.indices[p];
-        const int64_t row = i / b.size, t = i - row * b.size;
-        return t * b.n_rows + row;
-    }
-    const int64_t q = b.perm_n > 0 ? (int64_t)feistel_permute((uint64_t)p, (uint64_t)b.perm_n, b.perm_key) : p;
-    const int64_t row = q / b.len, j = q - row * b.len;
-    int64_t t = b.start + j;
-    if (t >= b.size) t -= b.size;
-    return t * b.n_rows + row;
-}
 
 // ---------------------------------------------------------------------------------------------
 template <int H>
@@ -276,35 +241,6 @@ __device__ __forceinline__ void forward_tile(float* smem, const Smem<H>& L, int 
     __syncthreads();
 }
 
-// softmax pieces of one row
-struct Soft {
-    float logp[OUTP];
-    float p[OUTP];
-    float ent;
-};
-__device__ __forceinline__ Soft softmax_row(const float* z, int n_act) {
-    Soft s;
-    float m = -INFINITY;
-#pragma unroll
-    for (int j = 0; j < OUTP; ++j)
-        if (j < n_act) m = fmaxf(m, z[j]);
-    float sum = 0.f;
-#pragma unroll
-    for (int j = 0; j < OUTP; ++j) {
-        s.p[j] = j < n_act ? expf(z[j] - m) : 0.f;
-        sum += s.p[j];
-    }
-    const float lse = logf(sum);
-    s.ent = 0.f;
-#pragma unroll
-    for (int j = 0; j < OUTP; ++j) {
-        s.logp[j] = j < n_act ? (z[j] - m) - lse : 0.f;
-        s.p[j] = j < n_act ? s.p[j] / sum : 0.f;
-        if (j < n_act) s.ent -= s.p[j] * s.logp[j];
-    }
-    return s;
-}
-
 // ---------------------------------------------------------------------------------------------
 // forward kernel.  mode: 0 raw outputs [n][out_dim]; 1 sample action (Philox inverse-CDF);
 // 2 arg-max action (dist.mode, deterministic_eval); 3 evaluate given actions (log_prob).
@@ -427,11 +363,6 @@ __device__ __forceinline__ void wgrad(const float* __restrict__ sPT, const float
             }
     }
 }
-
-struct PpoCfg {
-    float eps_clip, dual_clip, vf_coef, ent_coef;
-    int value_clip, adv_norm;
-};
 
 struct PpoArgs {
     const float* params;
@@ -737,11 +668,19 @@ __global__ void __launch_bounds__(ADAM_THREADS) adam_kernel(float* __restrict__ 
 }  // namespace mlp
 }  // namespace tsm
 
+namespace tsm {
+int tc_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int64_t n, int mode, int scatter, uint64_t seed,
+                   uint64_t counter, float* out, int32_t* act, float* logp, float* value, float* entropy, cudaStream_t s);
+int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, int64_t mb_start, int64_t mb_len,
+                     const float* mb_stats, double* loss_sums, cudaStream_t s);
+}  // namespace tsm
+
 using namespace tsm;
 using namespace tsm::mlp;
 
 static int check_net(const tsm_net* n, const char* fn) {
     if (!n) return fail(TSM_ERR_INVALID, "%s: net is NULL", fn);
+    if (n->engine != 0 && n->engine != 1) return fail(TSM_ERR_INVALID, "%s: engine must be 0 (fp32) or 1 (tcgen05)", fn);
     if (n->hidden != 64 && n->hidden != 128) return fail(TSM_ERR_UNSUPPORTED, "%s: hidden must be 64 or 128", fn);
     if (n->in_dim < 1 || n->in_dim > 64) return fail(TSM_ERR_UNSUPPORTED, "%s: in_dim must be in 1..64 on the fp32 path", fn);
     if (n->out_dim < 1 || n->out_dim > OUTP) return fail(TSM_ERR_UNSUPPORTED, "%s: out_dim must be in 1..8", fn);
@@ -782,6 +721,8 @@ extern "C" int tsm_net_forward(const tsm_net* net, const float* x, const int64_t
     TSM_REQUIRE(x != nullptr, "x != NULL");
     TSM_REQUIRE(mode == 0 || net->n_act > 0, "sampling / evaluation needs n_act > 0");
     TSM_REQUIRE(mode != 3 || act != nullptr, "mode 3 (evaluate) needs act");
+    if (net->engine == 1)
+        return tc_net_forward(net, x, rows, n, mode, scatter, seed, counter, out, act, logp, value, entropy, as_stream(stream));
     FwdArgs a{};
     a.params = net->params; a.x = x; a.rows = rows; a.n = n;
     a.in_dim = net->in_dim; a.out_dim = net->out_dim; a.n_act = net->n_act; a.value_index = net->value_index;
@@ -879,6 +820,7 @@ extern "C" int tsm_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch,
     TSM_REQUIRE(net->value_index < 0 || batch->ret, "value loss needs ret");
     TSM_REQUIRE(!cfg->value_clip || batch->v_old, "value_clip needs v_old");
     TSM_REQUIRE(!cfg->adv_norm || mb_stats, "advantage normalisation needs mb_stats");
+    if (net->engine == 1) return tc_ppo_minibatch(net, batch, cfg, mb_start, mb_len, mb_stats, loss_sums, as_stream(stream));
     PpoArgs a{};
     a.params = net->params; a.grads = net->grads;
     a.obs = batch->obs; a.act = batch->act; a.adv = batch->adv; a.ret = batch->ret; a.logp_old = batch->logp_old; a.v_old = batch->v_old;

@@ -1,0 +1,156 @@
+// mlp_tc.cu -- K4/K5 on the 5th-generation tensor cores (tcgen05 + TMEM), sm_100a.
+//
+// Same contract as mlp.cu (forward / sample / evaluate, fused PPO minibatch fwd+loss+bwd) for the
+// net shape in(<=31) -> 64 -> 64 -> out(<=8), with every GEMM issued as tcgen05.mma kind::f16
+// (fp16 operands in shared memory, fp32 accumulators in TMEM).  See tc.cuh / mlp_tc_kernels.cuh.
+#include <algorithm>
+#include "common.cuh"
+#include "philox.cuh"
+#include <cuda_fp16.h>
+#include "feistel.cuh"
+#include "ppo_math.cuh"
+#include "tc.cuh"
+
+namespace tsm {
+namespace mlptc {
+
+using namespace tsm::ppo;
+
+#include "mlp_tc_kernels.cuh"
+
+// ---------------------------------------------------------------------------------------------
+// self test: one GEMM D[128][N] = A * B from caller-prepared shared-memory images and caller-chosen
+// descriptor fields; used by tests/test_gpu_tc.py to pin the descriptor semantics this file relies on
+struct SelfArgs {
+    const float* a_img; const float* b_img; int a_floats, b_floats;
+    uint32_t a_lbo, a_sbo, a_step, b_lbo, b_sbo, b_step;
+    int a_mn, b_mn, N, ksteps, kind, a_bf16, b_bf16;
+    float* d_out;
+};
+
+__global__ void __launch_bounds__(128) selftest_kernel(SelfArgs a) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    __shared__ uint64_t bar;
+    __shared__ uint32_t tmem_base_s;
+    float* sA = reinterpret_cast<float*>(smem);
+    float* sB = sA + ((a.a_floats + 255) / 256) * 256;
+    for (int i = threadIdx.x; i < a.a_floats; i += 128) sA[i] = a.a_img[i];
+    for (int i = threadIdx.x; i < a.b_floats; i += 128) sB[i] = a.b_img[i];
+    const int warp = threadIdx.x >> 5;
+    if (warp == 0) tc::tmem_alloc(&tmem_base_s, 256);
+    if (threadIdx.x == 0) { tc::mbar_init(&bar, 1); tc::fence_barrier_init(); }
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tmem_base = tmem_base_s;
+    if (threadIdx.x == 0) {
+        const uint32_t idesc = a.kind == 0 ? tc::make_idesc_tf32(128, a.N, a.a_mn, a.b_mn)
+                                           : tc::make_idesc_f16(128, a.N, a.a_bf16, a.b_bf16, a.a_mn, a.b_mn);
+        for (int ks = 0; ks < a.ksteps; ++ks) {
+            const uint64_t da = tc::make_desc(tc::smem_u32(sA) + ks * a.a_step, a.a_lbo, a.a_sbo);
+            const uint64_t db = tc::make_desc(tc::smem_u32(sB) + ks * a.b_step, a.b_lbo, a.b_sbo);
+            if (a.kind == 0) tc::mma_tf32(tmem_base, da, db, idesc, ks > 0);
+            else tc::mma_f16(tmem_base, da, db, idesc, ks > 0);
+        }
+        tc::commit(&bar);
+    }
+    tc::mbar_wait(&bar, 0);
+    tc::fence_after_sync();
+    for (int c = 0; c < a.N; c += 16) {
+        float v[16];
+        tc::tmem_ld16(tmem_base + ((uint32_t)(warp * 32) << 16) + c, v);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) a.d_out[(size_t)threadIdx.x * a.N + c + i] = v[i];
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc(tmem_base, 256);
+}
+
+}  // namespace mlptc
+}  // namespace tsm
+
+using namespace tsm;
+
+extern "C" int tsm_tc_selftest(const float* a_img, int a_floats, const float* b_img, int b_floats, const uint32_t* h_desc /*[6]*/,
+                               int a_mn_major, int b_mn_major, int n, int ksteps, int kind, int a_bf16, int b_bf16, float* d_out,
+                               tsm_stream_t stream) {
+    TSM_REQUIRE(a_img && b_img && h_desc && d_out, "pointers != NULL");
+    TSM_REQUIRE(n >= 16 && n <= 256 && n % 16 == 0 && ksteps >= 1, "16 <= n <= 256, n % 16 == 0, ksteps >= 1");
+    mlptc::SelfArgs a{};
+    a.a_img = a_img; a.b_img = b_img; a.a_floats = a_floats; a.b_floats = b_floats;
+    a.a_lbo = h_desc[0]; a.a_sbo = h_desc[1]; a.a_step = h_desc[2]; a.b_lbo = h_desc[3]; a.b_sbo = h_desc[4]; a.b_step = h_desc[5];
+    a.a_mn = a_mn_major; a.b_mn = b_mn_major; a.N = n; a.ksteps = ksteps; a.d_out = d_out; a.kind = kind; a.a_bf16 = a_bf16; a.b_bf16 = b_bf16;
+    const size_t smem = (size_t)(((a_floats + 255) / 256) * 256 + b_floats) * 4 + 1024;
+    TSM_REQUIRE(smem <= 200 * 1024, "images too large");
+    TSM_CUDA(cudaFuncSetAttribute(mlptc::selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    mlptc::selftest_kernel<<<1, 128, smem, as_stream(stream)>>>(a);
+    TSM_LAUNCH_CHECK();
+    return TSM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// engine 1 entry points (called from the dispatchers in mlp.cu)
+namespace tsm {
+
+static int tc_check_net(const tsm_net* n, const char* fn) {
+    if (n->hidden != 64 || n->in_dim < 1 || n->in_dim > 31 || n->out_dim < 1 || n->out_dim > 8)
+        return fail(TSM_ERR_UNSUPPORTED, "%s: the tcgen05 engine needs hidden == 64, in_dim <= 31, out_dim <= 8", fn);
+    return TSM_OK;
+}
+
+int tc_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int64_t n, int mode, int scatter, uint64_t seed,
+                   uint64_t counter, float* out, int32_t* act, float* logp, float* value, float* entropy, cudaStream_t s) {
+    int rc = tc_check_net(net, __func__);
+    if (rc) return rc;
+    mlptc::TcFwdArgs a{};
+    a.params = net->params; a.x = x; a.rows = rows; a.n = n;
+    a.in_dim = net->in_dim; a.out_dim = net->out_dim; a.n_act = net->n_act; a.value_index = net->value_index;
+    a.mode = mode; a.scatter = scatter; a.seed = seed; a.counter = counter;
+    a.out = out; a.act = act; a.logp = logp; a.value = value; a.entropy = entropy;
+    const size_t smem = mlptc::SM_FWD_TOTAL + 1024;
+    static bool attr = false;
+    if (!attr) {
+        TSM_CUDA(cudaFuncSetAttribute(mlptc::tc_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr = true;
+    }
+    const int64_t tiles = ceil_div(n, mlptc::TC_ROWS);
+    const unsigned grid = (unsigned)std::min<int64_t>(tiles, (int64_t)sm_count() * 2);
+    mlptc::tc_forward_kernel<<<grid, mlptc::TC_THREADS, smem, s>>>(a);
+    TSM_LAUNCH_CHECK();
+    return TSM_OK;
+}
+
+int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, int64_t mb_start, int64_t mb_len,
+                     const float* mb_stats, double* loss_sums, cudaStream_t s) {
+    int rc = tc_check_net(net, __func__);
+    if (rc) return rc;
+    mlptc::TcPpoArgs a{};
+    a.params = net->params; a.grads = net->grads;
+    a.obs = batch->obs; a.act = batch->act; a.adv = batch->adv; a.ret = batch->ret; a.logp_old = batch->logp_old; a.v_old = batch->v_old;
+    a.view.indices = batch->indices; a.view.size = batch->size; a.view.n_rows = batch->n_rows; a.view.start = batch->start;
+    a.view.len = batch->len; a.view.perm_key = batch->perm_key; a.view.perm_n = batch->perm_n;
+    a.mb_start = mb_start; a.mb_len = mb_len; a.mb_stats = mb_stats;
+    a.cfg.eps_clip = cfg->eps_clip; a.cfg.dual_clip = cfg->dual_clip; a.cfg.vf_coef = cfg->vf_coef; a.cfg.ent_coef = cfg->ent_coef;
+    a.cfg.value_clip = cfg->value_clip; a.cfg.adv_norm = cfg->adv_norm;
+    a.in_dim = net->in_dim; a.out_dim = net->out_dim; a.n_act = net->n_act; a.value_index = net->value_index;
+    float sc = 1.0f;  // S = 2^ceil(log2(mb_len)), capped, so that S / mb_len is in (0.5, 1]
+    while (sc < (float)mb_len && sc < 1048576.0f) sc *= 2.0f;
+    a.gscale = sc; a.inv_gscale = 1.0f / sc;
+    a.loss_sums = loss_sums;
+    const size_t smem = 100 * 1024;  // > 227/3 KB: at most two CTAs per SM (2 x 256 TMEM columns)
+    static_assert(mlptc::SM_TOTAL + 1024 <= 100 * 1024, "smem map too large");
+    static bool attr = false;
+    if (!attr) {
+        TSM_CUDA(cudaFuncSetAttribute(mlptc::tc_ppo_minibatch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr = true;
+    }
+    const int64_t tiles = ceil_div(mb_len, mlptc::TC_ROWS);
+    const unsigned grid = (unsigned)std::min<int64_t>(tiles, (int64_t)sm_count() * 2);
+    mlptc::tc_ppo_minibatch_kernel<<<grid, mlptc::TC_THREADS, smem, s>>>(a);
+    TSM_LAUNCH_CHECK();
+    return TSM_OK;
+}
+
+}  // namespace tsm

@@ -1,0 +1,146 @@
+// ppo_math.cuh -- pieces shared by the fp32 (mlp.cu) and tcgen05 (mlp_tc.cu) actor-critic kernels:
+// flat parameter layout, batch-position -> buffer-slot mapping, softmax pieces and the per-row PPO
+// loss with its gradient w.r.t. the head outputs (tianshou/algorithm/modelfree/ppo.py:181-211).
+#pragma once
+#include <stdint.h>
+#include "feistel.cuh"
+
+namespace tsm {
+namespace ppo {
+
+constexpr int OUTP = 8;  // head width padded to 8 (out_dim <= 8)
+
+struct Offsets {
+    int64_t w1, b1, w2, b2, w3, b3, total;
+};
+__host__ __device__ inline Offsets offsets(int in_dim, int H, int out_dim) {
+    Offsets o;
+    o.w1 = 0;
+    o.b1 = (int64_t)H * in_dim;
+    o.w2 = o.b1 + H;
+    o.b2 = o.w2 + (int64_t)H * H;
+    o.w3 = o.b2 + H;
+    o.b3 = o.w3 + (int64_t)out_dim * H;
+    o.total = o.b3 + out_dim;
+    return o;
+}
+
+// where batch position p lives in the time-major device buffer
+struct BatchView {
+    const int64_t* indices;  // explicit env-major buffer indices per position (may be NULL)
+    int64_t size, n_rows;    // ring: slots per row, rows
+    int64_t start, len;      // lock-step view: row r holds `len` valid slots from ring slot `start`
+    uint64_t perm_key;       // Feistel key of the minibatch permutation
+    int64_t perm_n;          // domain of the permutation (0 = identity)
+};
+__device__ __forceinline__ int64_t slot_of(const BatchView& b, int64_t p) {
+    if (b.indices) {
+        const int64_t i = b.indices[p];
+        const int64_t row = i / b.size, t = i - row * b.size;
+        return t * b.n_rows + row;
+    }
+    const int64_t q = b.perm_n > 0 ? (int64_t)feistel_permute((uint64_t)p, (uint64_t)b.perm_n, b.perm_key) : p;
+    const int64_t row = q / b.len, j = q - row * b.len;
+    int64_t t = b.start + j;
+    if (t >= b.size) t -= b.size;
+    return t * b.n_rows + row;
+}
+
+// softmax pieces of one row
+struct Soft {
+    float logp[OUTP];
+    float p[OUTP];
+    float ent;
+};
+__device__ __forceinline__ Soft softmax_row(const float* z, int n_act) {
+    Soft s;
+    float m = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < OUTP; ++j)
+        if (j < n_act) m = fmaxf(m, z[j]);
+    float sum = 0.f;
+#pragma unroll
+    for (int j = 0; j < OUTP; ++j) {
+        s.p[j] = j < n_act ? expf(z[j] - m) : 0.f;
+        sum += s.p[j];
+    }
+    const float lse = logf(sum);
+    s.ent = 0.f;
+#pragma unroll
+    for (int j = 0; j < OUTP; ++j) {
+        s.logp[j] = j < n_act ? (z[j] - m) - lse : 0.f;
+        s.p[j] = j < n_act ? s.p[j] / sum : 0.f;
+        if (j < n_act) s.ent -= s.p[j] * s.logp[j];
+    }
+    return s;
+}
+
+struct PpoCfg {
+    float eps_clip, dual_clip, vf_coef, ent_coef;
+    int value_clip, adv_norm;
+};
+
+
+// loss terms of one row and d(mean loss)/d(head outputs) (dz), ppo.py:181-211
+struct RowLoss {
+    float clip, vf, ent;
+};
+__device__ __forceinline__ RowLoss row_loss(const float (&z)[OUTP], int n_act, int value_index, int act, float adv, float ret,
+                                            float logp_old, float v_old, float mean, float rstd, const PpoCfg& cfg, float inv_n,
+                                            float (&dz)[OUTP]) {
+    RowLoss out{0.f, 0.f, 0.f};
+#pragma unroll
+    for (int j = 0; j < OUTP; ++j) dz[j] = 0.f;
+    if (n_act > 0) {
+        const Soft sm = softmax_row(z, n_act);
+        float lp = 0.f;
+#pragma unroll
+        for (int j = 0; j < OUTP; ++j)
+            if (j == act) lp = sm.logp[j];
+        float advn = adv;
+        if (cfg.adv_norm) advn = (advn - mean) * rstd;
+        const float ratio = expf(lp - logp_old);
+        const float lo = 1.f - cfg.eps_clip, hi = 1.f + cfg.eps_clip;
+        const float s1 = ratio * advn, s2 = fminf(fmaxf(ratio, lo), hi) * advn;
+        const bool inside = ratio >= lo && ratio <= hi;
+        const float clip1 = fminf(s1, s2);
+        float g_ratio = (inside || s1 < s2) ? advn : 0.f;  // d min(s1,s2) / d ratio
+        float li = -clip1;
+        if (cfg.dual_clip > 0.f && advn < 0.f) {
+            const float c2 = cfg.dual_clip * advn;
+            if (c2 > clip1) { li = -c2; g_ratio = 0.f; }
+        }
+        out.clip = li;
+        out.ent = sm.ent;
+        const float dlp = -g_ratio * ratio * inv_n;  // d loss / d logp(act)
+        const float ec = cfg.ent_coef * inv_n;
+#pragma unroll
+        for (int j = 0; j < OUTP; ++j)
+            if (j < n_act) dz[j] = dlp * ((j == act ? 1.f : 0.f) - sm.p[j]) + ec * sm.p[j] * (sm.logp[j] + sm.ent);
+    }
+    if (value_index >= 0) {
+        float v = 0.f;
+#pragma unroll
+        for (int j = 0; j < OUTP; ++j)
+            if (j == value_index) v = z[j];
+        float vf = (ret - v) * (ret - v), dv = 2.f * (v - ret);
+        if (cfg.value_clip) {
+            const float d = v - v_old;
+            const float vc = v_old + fminf(fmaxf(d, -cfg.eps_clip), cfg.eps_clip);
+            const float vf2 = (ret - vc) * (ret - vc);
+            if (vf2 > vf) {
+                vf = vf2;
+                dv = (d >= -cfg.eps_clip && d <= cfg.eps_clip) ? 2.f * (vc - ret) : 0.f;
+            }
+        }
+        out.vf = vf;
+        const float dvs = cfg.vf_coef * inv_n * dv;
+#pragma unroll
+        for (int j = 0; j < OUTP; ++j)
+            if (j == value_index) dz[j] = dvs;
+    }
+    return out;
+}
+
+}  // namespace ppo
+}  // namespace tsm

@@ -25,8 +25,14 @@ MODES = {"raw": 0, "sample": 1, "mode": 2, "eval": 3}
 
 class ActorCriticNet(nn.Module):
     def __init__(self, in_dim: int, hidden: int = 64, n_act: int = 5, with_value: bool = True, n_value_only: int = 0,
-                 device: str | torch.device = "cuda", seed: int | None = None, orthogonal: bool = True) -> None:
+                 device: str | torch.device = "cuda", seed: int | None = None, orthogonal: bool = True,
+                 engine: str = "fp32") -> None:
+        """engine: "fp32" = exact CUDA-core kernels (csrc/mlp.cu); "tc" = tcgen05 tensor-core kernels with fp16 operands and
+        fp32 accumulation (csrc/mlp_tc.cu; hidden 64, in_dim <= 31, out_dim <= 8)."""
         super().__init__()
+        if engine not in ("fp32", "tc"):
+            raise ValueError("engine must be 'fp32' or 'tc'")
+        self.engine = engine
         self.in_dim, self.hidden, self.n_act = int(in_dim), int(hidden), int(n_act)
         if n_value_only:  # critic-only net: out_dim value heads, no logits
             self.n_act, self.out_dim, self.value_index = 0, int(n_value_only), 0
@@ -67,12 +73,13 @@ class ActorCriticNet(nn.Module):
         d = self._desc
         d.in_dim, d.hidden, d.out_dim, d.n_act, d.value_index, d.n_params = (self.in_dim, self.hidden, self.out_dim, self.n_act,
                                                                            self.value_index, self.n_params)
+        d.engine = 1 if self.engine == "tc" else 0
         d.params, d.grads = self.flat.data_ptr(), self.grads.data_ptr()
         d.adam_m, d.adam_v, d.adam_step = self.adam_m.data_ptr(), self.adam_v.data_ptr(), self.adam_step.data_ptr()
 
     @property
     def desc(self) -> Any:
-        if self._desc.params != self.flat.data_ptr():
+        if self._desc.params != self.flat.data_ptr() or self._desc.engine != (1 if self.engine == "tc" else 0):
             self._fill_desc()
         return C.byref(self._desc)
 
