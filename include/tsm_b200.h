@@ -253,9 +253,16 @@ typedef struct tsm_net {
     float* adam_m;      /* [n_params] exp_avg */
     float* adam_v;      /* [n_params] exp_avg_sq */
     int64_t* adam_step; /* [1] device step counter */
+    void* tc_image;     /* engine 1 only: TSM_TC_IMAGE_BYTES device bytes, zero-initialised by the caller: the fp16 operand
+                           image of params (+ a CTA ticket).  Refreshed by tsm_adam_step / tsm_ppo_epoch; call tsm_net_pack
+                           after writing params any other way. */
 } tsm_net;
+#define TSM_TC_IMAGE_BYTES 17024
 
 int64_t tsm_net_param_count(int in_dim, int hidden, int out_dim);
+
+/* engine 1: rebuild net->tc_image from net->params (no-op for engine 0) */
+int tsm_net_pack(const tsm_net* net, tsm_stream_t stream);
 
 /* Forward over n rows of x ([.][in_dim] float32; `rows` optionally gathers x rows, and with
  * scatter != 0 results are written at those row ids instead of 0..n-1).
@@ -315,7 +322,8 @@ int tsm_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_
 int tsm_adam_step(const tsm_net* net, float lr, float beta1, float beta2, float eps, float max_grad_norm,
                   float grad_scale, float* grad_norm_out, tsm_stream_t stream);
 
-/* one epoch on one GPU: for each minibatch m: tsm_ppo_minibatch then tsm_adam_step.
+/* one epoch on one GPU: for each minibatch m: tsm_ppo_minibatch then tsm_adam_step (engine 1 runs the
+ * optimizer step in the tail of the minibatch kernel, in the last CTA to finish: one launch per minibatch).
  * h_mb_bounds is a HOST array [n_minibatches+1]; mb_stats [n_minibatches][2] and loss_sums
  * [n_minibatches][4] are device arrays (either may be NULL). */
 int tsm_ppo_epoch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, const int64_t* h_mb_bounds,

@@ -42,6 +42,9 @@ class TsmMpe(C.Structure):
     ]
 
 
+TC_IMAGE_BYTES = 17024  # TSM_TC_IMAGE_BYTES
+
+
 class TsmNet(C.Structure):
     """struct tsm_net (include/tsm_b200.h)."""
 
@@ -49,6 +52,7 @@ class TsmNet(C.Structure):
         ("in_dim", C.c_int32), ("hidden", C.c_int32), ("out_dim", C.c_int32), ("n_act", C.c_int32),
         ("value_index", C.c_int32), ("engine", C.c_int32), ("n_params", c_i64),
         ("params", c_vp), ("grads", c_vp), ("adam_m", c_vp), ("adam_v", c_vp), ("adam_step", c_vp),
+        ("tc_image", c_vp),
     ]
 
 
@@ -91,6 +95,7 @@ _SIGS = {
     "tsm_mpe_step": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
     "tsm_random_actions": (c_i32, [c_vp, c_i64, c_i32, C.c_uint64, C.c_uint64, c_vp]),
     "tsm_net_param_count": (c_i64, [c_i32, c_i32, c_i32]),
+    "tsm_net_pack": (c_i32, [c_vp, c_vp]),
     "tsm_net_forward": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_u64, c_u64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "tsm_ppo_adv_stats": (c_i32, [c_vp, c_vp, c_i64, c_f32, c_vp, c_vp]),
     "tsm_ppo_minibatch": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i64, c_vp, c_vp, c_vp]),

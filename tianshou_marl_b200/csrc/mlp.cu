@@ -25,6 +25,7 @@
 #include "philox.cuh"
 #include "feistel.cuh"
 #include "ppo_math.cuh"
+#include "adam.cuh"
 
 namespace tsm {
 namespace mlp {
@@ -616,53 +617,22 @@ __global__ void __launch_bounds__(THREADS) adv_stats_kernel(const float* __restr
 }
 
 // ---------------------------------------------------------------------------------------------
-// one CTA: global grad-norm clip (torch.nn.utils.clip_grad_norm_) + torch.optim.Adam step; zeroes grads
-constexpr int ADAM_THREADS = 1024;
-__global__ void __launch_bounds__(ADAM_THREADS) adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
-                                                           float* __restrict__ v, int64_t* __restrict__ step, int64_t n, float lr,
-                                                           float beta1, float beta2, float eps, float max_norm, float grad_scale,
-                                                           float* __restrict__ gnorm_out) {
-    __shared__ float sh[ADAM_THREADS / 32];
-    __shared__ float s_coef;
-    float coef = grad_scale;
-    if (max_norm > 0.f || gnorm_out) {
-        float sq = 0.f;
-        for (int64_t i = threadIdx.x; i < n; i += ADAM_THREADS) {
-            const float x = g[i] * grad_scale;
-            sq = fmaf(x, x, sq);
-        }
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) sq += __shfl_down_sync(0xffffffffu, sq, d);
-        if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = sq;
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            float t = 0.f;
-            for (int w = 0; w < ADAM_THREADS / 32; ++w) t += sh[w];
-            const float norm = sqrtf(t);
-            if (gnorm_out) *gnorm_out = norm;
-            float c = 1.f;
-            if (max_norm > 0.f) c = fminf(max_norm / (norm + 1e-6f), 1.f);
-            s_coef = c * grad_scale;
-        }
-        __syncthreads();
-        coef = s_coef;
-    }
-    const int64_t t = *step + 1;
-    const float bc1 = (float)(1.0 - pow((double)beta1, (double)t));
-    const float bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, (double)t));
-    const float step_size = lr / bc1;
-    for (int64_t i = threadIdx.x; i < n; i += ADAM_THREADS) {
-        const float gi = g[i] * coef;
-        const float mi = m[i] + (gi - m[i]) * (1.f - beta1);         // exp_avg.lerp_(grad, 1 - beta1)
-        const float vi = fmaf(gi * gi, 1.f - beta2, v[i] * beta2);   // mul_(beta2).addcmul_(g, g, 1 - beta2)
-        const float denom = sqrtf(vi) / bc2_sqrt + eps;
-        p[i] = p[i] - step_size * (mi / denom);
-        m[i] = mi;
-        v[i] = vi;
-        g[i] = 0.f;
-    }
+// one CTA: global grad-norm clip (torch.nn.utils.clip_grad_norm_) + torch.optim.Adam step; zeroes grads (adam.cuh)
+// (one 8-CTA cluster, see adam.cuh).  PDL: lets the next minibatch kernel start its parameter-independent prologue.
+__global__ void __cluster_dims__(opt::ADAM_CTAS, 1, 1) __launch_bounds__(opt::ADAM_THREADS) adam_kernel(opt::AdamArgs a) {
+    pdl_launch_dependents();
+    pdl_wait();
+    opt::adam_cluster(a);
+}
+constexpr int ADAM_THREADS = 512;  // pack_image_kernel
+
+// fp32 parameters -> fp16 operand image of the tcgen05 engine (one CTA)
+__global__ void __launch_bounds__(ADAM_THREADS) pack_image_kernel(const float* __restrict__ p, int64_t n, int in_dim, int out_dim,
+                                                                 __half* __restrict__ image) {
+    for (int i = threadIdx.x; i < opt::IMG_HALVES; i += ADAM_THREADS) image[i] = __float2half_rn(0.f);
     __syncthreads();
-    if (threadIdx.x == 0) *step = t;
+    const Offsets o = offsets(in_dim, 64, out_dim);
+    for (int64_t i = threadIdx.x; i < n; i += ADAM_THREADS) image[opt::image_index(i, o, in_dim)] = __float2half_rn(p[i]);
 }
 
 }  // namespace mlp
@@ -672,7 +642,7 @@ namespace tsm {
 int tc_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int64_t n, int mode, int scatter, uint64_t seed,
                    uint64_t counter, float* out, int32_t* act, float* logp, float* value, float* entropy, cudaStream_t s);
 int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, int64_t mb_start, int64_t mb_len,
-                     const float* mb_stats, double* loss_sums, cudaStream_t s);
+                     const float* mb_stats, double* loss_sums, int pdl, cudaStream_t s);
 }  // namespace tsm
 
 using namespace tsm;
@@ -688,6 +658,7 @@ static int check_net(const tsm_net* n, const char* fn) {
     if (n->value_index >= n->out_dim) return fail(TSM_ERR_INVALID, "%s: value_index < out_dim", fn);
     if (n->value_index >= 0 && n->value_index < n->n_act) return fail(TSM_ERR_INVALID, "%s: value_index must not alias a logit", fn);
     if (!n->params) return fail(TSM_ERR_INVALID, "%s: params is NULL", fn);
+    if (n->engine == 1 && !n->tc_image) return fail(TSM_ERR_INVALID, "%s: engine 1 needs tc_image", fn);
     if (n->n_params != offsets(n->in_dim, n->hidden, n->out_dim).total)
         return fail(TSM_ERR_INVALID, "%s: n_params does not match the layout (want %lld)", fn,
                     (long long)offsets(n->in_dim, n->hidden, n->out_dim).total);
@@ -820,7 +791,7 @@ extern "C" int tsm_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch,
     TSM_REQUIRE(net->value_index < 0 || batch->ret, "value loss needs ret");
     TSM_REQUIRE(!cfg->value_clip || batch->v_old, "value_clip needs v_old");
     TSM_REQUIRE(!cfg->adv_norm || mb_stats, "advantage normalisation needs mb_stats");
-    if (net->engine == 1) return tc_ppo_minibatch(net, batch, cfg, mb_start, mb_len, mb_stats, loss_sums, as_stream(stream));
+    if (net->engine == 1) return tc_ppo_minibatch(net, batch, cfg, mb_start, mb_len, mb_stats, loss_sums, 0, as_stream(stream));
     PpoArgs a{};
     a.params = net->params; a.grads = net->grads;
     a.obs = batch->obs; a.act = batch->act; a.adv = batch->adv; a.ret = batch->ret; a.logp_old = batch->logp_old; a.v_old = batch->v_old;
@@ -833,14 +804,43 @@ extern "C" int tsm_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch,
     return net->hidden == 64 ? launch_ppo<64>(a, as_stream(stream)) : launch_ppo<128>(a, as_stream(stream));
 }
 
+static opt::AdamArgs adam_args(const tsm_net* net, float lr, float beta1, float beta2, float eps, float max_grad_norm,
+                               float grad_scale, float* grad_norm_out) {
+    opt::AdamArgs a{};
+    a.p = net->params; a.g = net->grads; a.m = net->adam_m; a.v = net->adam_v; a.step = net->adam_step; a.n = net->n_params;
+    a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.max_norm = max_grad_norm; a.grad_scale = grad_scale;
+    a.gnorm_out = grad_norm_out;
+    a.image = net->engine == 1 ? reinterpret_cast<__half*>(net->tc_image) : nullptr;
+    a.in_dim = net->in_dim; a.out_dim = net->out_dim;
+    return a;
+}
+
+static int launch_adam(const opt::AdamArgs& a, int pdl, cudaStream_t s) {
+    cudaLaunchConfig_t lc{};
+    lc.gridDim = dim3(opt::ADAM_CTAS); lc.blockDim = dim3(opt::ADAM_THREADS); lc.dynamicSmemBytes = 0; lc.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = at; lc.numAttrs = pdl ? 1 : 0;
+    TSM_CUDA(cudaLaunchKernelEx(&lc, adam_kernel, a));
+    return TSM_OK;
+}
+
 extern "C" int tsm_adam_step(const tsm_net* net, float lr, float beta1, float beta2, float eps, float max_grad_norm,
                              float grad_scale, float* grad_norm_out, tsm_stream_t stream) {
     TSM_REQUIRE(net != nullptr, "net != NULL");
     TSM_REQUIRE(net->params && net->grads && net->adam_m && net->adam_v && net->adam_step, "params/grads/adam state != NULL");
     TSM_REQUIRE(net->n_params > 0, "n_params > 0");
-    adam_kernel<<<1, ADAM_THREADS, 0, as_stream(stream)>>>(net->params, net->grads, net->adam_m, net->adam_v, net->adam_step,
-                                                          net->n_params, lr, beta1, beta2, eps, max_grad_norm, grad_scale,
-                                                          grad_norm_out);
+    TSM_REQUIRE(net->engine != 1 || net->tc_image, "engine 1 needs tc_image");
+    return launch_adam(adam_args(net, lr, beta1, beta2, eps, max_grad_norm, grad_scale, grad_norm_out), 0, as_stream(stream));
+}
+
+extern "C" int tsm_net_pack(const tsm_net* net, tsm_stream_t stream) {
+    int rc = check_net(net, __func__);
+    if (rc) return rc;
+    if (net->engine != 1) return TSM_OK;
+    pack_image_kernel<<<1, ADAM_THREADS, 0, as_stream(stream)>>>(net->params, net->n_params, net->in_dim, net->out_dim,
+                                                                 reinterpret_cast<__half*>(net->tc_image));
     TSM_LAUNCH_CHECK();
     return TSM_OK;
 }
@@ -850,8 +850,28 @@ extern "C" int tsm_ppo_epoch(const tsm_net* net, const tsm_ppo_batch* batch, con
                              float max_grad_norm, double* loss_sums, tsm_stream_t stream) {
     TSM_REQUIRE(h_mb_bounds != nullptr && n_minibatches >= 0, "h_mb_bounds != NULL");
     for (int64_t m = 0; m < n_minibatches; ++m) {
-        int rc = tsm_ppo_minibatch(net, batch, cfg, h_mb_bounds[m], h_mb_bounds[m + 1] - h_mb_bounds[m],
-                                   mb_stats ? mb_stats + 2 * m : nullptr, loss_sums ? loss_sums + 4 * m : nullptr, stream);
+        const int64_t s0 = h_mb_bounds[m], len = h_mb_bounds[m + 1] - h_mb_bounds[m];
+        const float* st = mb_stats ? mb_stats + 2 * m : nullptr;
+        double* ls = loss_sums ? loss_sums + 4 * m : nullptr;
+        if (net && net->engine == 1 && len > 0) {
+            // programmatic dependent launches: minibatch(m) -> adam(m) -> minibatch(m+1); each dependent starts its prologue
+            // (TMEM allocation, first batch gather) while its predecessor drains.  The first minibatch launches normally.
+            int rc = check_net(net, __func__);
+            if (rc) return rc;
+            rc = check_batch(batch, __func__);
+            if (rc) return rc;
+            TSM_REQUIRE(cfg && net->grads && net->adam_m && net->adam_v && net->adam_step && batch->obs, "cfg / grads / adam state / obs != NULL");
+            TSM_REQUIRE(net->n_act == 0 || (batch->act && batch->adv && batch->logp_old), "policy loss needs act / adv / logp_old");
+            TSM_REQUIRE(net->value_index < 0 || batch->ret, "value loss needs ret");
+            TSM_REQUIRE(!cfg->value_clip || batch->v_old, "value_clip needs v_old");
+            TSM_REQUIRE(!cfg->adv_norm || st, "advantage normalisation needs mb_stats");
+            rc = tc_ppo_minibatch(net, batch, cfg, s0, len, st, ls, m > 0, as_stream(stream));
+            if (rc) return rc;
+            rc = launch_adam(adam_args(net, lr, beta1, beta2, eps, max_grad_norm, 1.0f, nullptr), 1, as_stream(stream));
+            if (rc) return rc;
+            continue;
+        }
+        int rc = tsm_ppo_minibatch(net, batch, cfg, s0, len, st, ls, stream);
         if (rc) return rc;
         rc = tsm_adam_step(net, lr, beta1, beta2, eps, max_grad_norm, 1.0f, nullptr, stream);
         if (rc) return rc;

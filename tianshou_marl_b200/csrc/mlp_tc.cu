@@ -4,11 +4,13 @@
 // net shape in(<=31) -> 64 -> 64 -> out(<=8), with every GEMM issued as tcgen05.mma kind::f16
 // (fp16 operands in shared memory, fp32 accumulators in TMEM).  See tc.cuh / mlp_tc_kernels.cuh.
 #include <algorithm>
+#include <cstdlib>
 #include "common.cuh"
 #include "philox.cuh"
 #include <cuda_fp16.h>
 #include "feistel.cuh"
 #include "ppo_math.cuh"
+#include "adam.cuh"
 #include "tc.cuh"
 
 namespace tsm {
@@ -105,29 +107,29 @@ int tc_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int6
     int rc = tc_check_net(net, __func__);
     if (rc) return rc;
     mlptc::TcFwdArgs a{};
-    a.params = net->params; a.x = x; a.rows = rows; a.n = n;
+    a.image = reinterpret_cast<const unsigned char*>(net->tc_image); a.x = x; a.rows = rows; a.n = n;
     a.in_dim = net->in_dim; a.out_dim = net->out_dim; a.n_act = net->n_act; a.value_index = net->value_index;
     a.mode = mode; a.scatter = scatter; a.seed = seed; a.counter = counter;
     a.out = out; a.act = act; a.logp = logp; a.value = value; a.entropy = entropy;
-    const size_t smem = mlptc::SM_FWD_TOTAL + 1024;
+    const size_t smem = mlptc::SM_TOTAL + 128;  // ~69 KB: three CTAs per SM (3 x 128 TMEM columns)
     static bool attr = false;
     if (!attr) {
         TSM_CUDA(cudaFuncSetAttribute(mlptc::tc_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr = true;
     }
     const int64_t tiles = ceil_div(n, mlptc::TC_ROWS);
-    const unsigned grid = (unsigned)std::min<int64_t>(tiles, (int64_t)sm_count() * 2);
+    const unsigned grid = (unsigned)std::min<int64_t>(tiles, (int64_t)sm_count() * 3);
     mlptc::tc_forward_kernel<<<grid, mlptc::TC_THREADS, smem, s>>>(a);
     TSM_LAUNCH_CHECK();
     return TSM_OK;
 }
 
 int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, int64_t mb_start, int64_t mb_len,
-                     const float* mb_stats, double* loss_sums, cudaStream_t s) {
+                     const float* mb_stats, double* loss_sums, int pdl, cudaStream_t s) {
     int rc = tc_check_net(net, __func__);
     if (rc) return rc;
     mlptc::TcPpoArgs a{};
-    a.params = net->params; a.grads = net->grads;
+    a.image = reinterpret_cast<const unsigned char*>(net->tc_image); a.grads = net->grads;
     a.obs = batch->obs; a.act = batch->act; a.adv = batch->adv; a.ret = batch->ret; a.logp_old = batch->logp_old; a.v_old = batch->v_old;
     a.view.indices = batch->indices; a.view.size = batch->size; a.view.n_rows = batch->n_rows; a.view.start = batch->start;
     a.view.len = batch->len; a.view.perm_key = batch->perm_key; a.view.perm_n = batch->perm_n;
@@ -139,8 +141,10 @@ int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_p
     while (sc < (float)mb_len && sc < 1048576.0f) sc *= 2.0f;
     a.gscale = sc; a.inv_gscale = 1.0f / sc;
     a.loss_sums = loss_sums;
+    static const int dbg = getenv("TSM_TC_DEBUG") ? atoi(getenv("TSM_TC_DEBUG")) : 0;
+    a.debug = dbg;
     const size_t smem = 100 * 1024;  // > 227/3 KB: at most two CTAs per SM (2 x 256 TMEM columns)
-    static_assert(mlptc::SM_TOTAL + 1024 <= 100 * 1024, "smem map too large");
+    static_assert(mlptc::SM_TOTAL + 128 <= 100 * 1024, "smem map too large");
     static bool attr = false;
     if (!attr) {
         TSM_CUDA(cudaFuncSetAttribute(mlptc::tc_ppo_minibatch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -148,8 +152,13 @@ int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_p
     }
     const int64_t tiles = ceil_div(mb_len, mlptc::TC_ROWS);
     const unsigned grid = (unsigned)std::min<int64_t>(tiles, (int64_t)sm_count() * 2);
-    mlptc::tc_ppo_minibatch_kernel<<<grid, mlptc::TC_THREADS, smem, s>>>(a);
-    TSM_LAUNCH_CHECK();
+    cudaLaunchConfig_t lc{};
+    lc.gridDim = dim3(grid); lc.blockDim = dim3(mlptc::TC_THREADS); lc.dynamicSmemBytes = smem; lc.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = at; lc.numAttrs = pdl ? 1 : 0;
+    TSM_CUDA(cudaLaunchKernelEx(&lc, mlptc::tc_ppo_minibatch_kernel, a));
     return TSM_OK;
 }
 

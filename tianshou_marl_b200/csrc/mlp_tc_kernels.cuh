@@ -2,45 +2,47 @@
 //
 // Net: in(<=31) -> 64 -> 64 -> out(<=8).  One CTA = 128 threads = one tile of 128 rows; thread t
 // owns row t (TMEM lane t).  All GEMM operands are fp16 in the chunked layout of tc.cuh with 8
-// features per 16-byte chunk:  act[f/8][row 0..127][f%8],  weight[in/8][out][in%8].
+// features per 16-byte chunk:  act[f/8][row 0..127][f%8],  weight[in/8][out][in%8].  Input feature
+// 31 is a column of ones; the biases ride on it (adam.cuh: b1 inside the W1 image, b2 / b3 as one
+// extra K = 16 block against X features 16..31), so no epilogue adds a bias.
 //
-//   forward      H1 = relu(X W1^T + b1)        A = X   (K-major, K = 32)   B = W1 (K-major)  N = 64
-//                H2 = relu(H1 W2^T + b2)       A = H1  (K-major, K = 64)   B = W2 (K-major)  N = 64
-//                OUT = H2 W3^T + b3            A = H2  (K-major, K = 64)   B = W3 (K-major)  N = 16
-//   data grads   DH2 = G W3                    A = G   (K-major, K = 16)   B = W3 (MN-major) N = 64
-//                DH1 = D2 W2                   A = D2  (K-major, K = 64)   B = W2 (MN-major) N = 64
+//   forward      H1 = relu([X|1] W1b^T)                 A = X   (K-major, K = 32)   B = W1b      N = 64
+//                H2 = relu(H1 W2^T + [X|1]_hi B2^T)     A = H1  (K = 64) + X hi (K = 16)         N = 64
+//                OUT = H2 W3^T + [X|1]_hi B3^T          A = H2  (K = 64) + X hi (K = 16)         N = 16
+//   data grads   DH2 = G W3                             A = G   (K-major, K = 16)   B = W3 (MN-major) N = 64
+//                DH1 = D2 W2                            A = D2  (K-major, K = 64)   B = W2 (MN-major) N = 64
 //   weight grads (K = the 128 rows, both operands MN-major views of the activation images,
-//                 M = 128 made of two adjacent 64-feature images):
-//                [dW3^T; .] += [H2; H1]^T G          N = 16   (rows 0..63 used)
-//                [dW2 ; .] += [D2; H1]^T H1          N = 64   (rows 0..63 used)
-//                [dW1|db1 ; .|db2] += [D1; D2]^T X   N = 32   (X feature 31 is a column of ones)
-// G = S * d(loss)/d(OUT) with S a power of two (fp16 range), D2 / D1 = ReLU-masked DH2 / DH1.
-// Weight-gradient accumulators stay in TMEM across all tiles of the CTA and are flushed once.
+//                 M = 128 made of the two adjacent 64-feature images [H2 slot][H1 slot]):
+//                [dW3^T; .]        += [H2; H1]^T G        N = 16   (lanes 0..63 used)
+//                [dW2 ; .]         += [D2; H1]^T H1       N = 64   (lanes 0..63 used)
+//                [.|db2; dW1|db1]  += [D2; D1]^T [X|1]    N = 32   (column 31 = bias gradients)
+// G = S * d(loss)/d(OUT) with S a power of two (fp16 range); D2 / D1 = ReLU-masked DH2 / DH1 written
+// in place over H2 / H1.  Weight-gradient accumulators stay in TMEM across all tiles of the CTA and
+// are flushed once, through a shared-memory staging copy so that the global atomics are coalesced.
 #pragma once
 
 constexpr int TC_THREADS = 128;
 constexpr int TC_ROWS = 128;
 constexpr int TC_H = 64;
-constexpr int TC_XF = 32;    // padded input features
+constexpr int TC_XF = 32;    // padded input features (31 = ones)
 constexpr int TC_OF = 16;    // padded head outputs (UMMA N >= 16 at M = 128)
 constexpr int CHUNK_B = TC_ROWS * 16;  // bytes of one 8-feature chunk of an activation image (2048)
 
-// shared-memory map (bytes).  [D1][H2/D2][H1][X] must stay adjacent and in this order.
-constexpr int SM_D1 = 0;
-constexpr int SM_H2 = SM_D1 + 8 * CHUNK_B;   // 16 KB each
-constexpr int SM_H1 = SM_H2 + 8 * CHUNK_B;
-constexpr int SM_X = SM_H1 + 8 * CHUNK_B;    // 4 chunks = 8 KB
-constexpr int SM_G = SM_X + 4 * CHUNK_B;     // 2 chunks = 4 KB (chunk 1 stays zero)
-constexpr int SM_W1 = SM_G + 2 * CHUNK_B;    // [32/8][64][8] fp16 = 4 KB
-constexpr int SM_W2 = SM_W1 + 4 * 64 * 16;   // [64/8][64][8] = 8 KB
-constexpr int SM_W3 = SM_W2 + 8 * 64 * 16;   // [64/8][16][8] = 2 KB
-constexpr int SM_B1 = SM_W3 + 8 * 16 * 16;   // fp32 biases
-constexpr int SM_B2 = SM_B1 + 64 * 4;
-constexpr int SM_B3 = SM_B2 + 64 * 4;
-constexpr int SM_RED = SM_B3 + 16 * 4;       // 8 warps x 4 doubles scratch
-constexpr int SM_BAR = SM_RED + 256;         // mbarrier + tmem base
+// shared-memory map (bytes).  [H2][H1] must stay adjacent and in this order.
+constexpr int SM_H2 = 0;                       // 16 KB (D2 in place)
+constexpr int SM_H1 = SM_H2 + 8 * CHUNK_B;     // 16 KB (D1 in place)
+constexpr int SM_X = SM_H1 + 8 * CHUNK_B;      // 2 x 8 KB, double buffered
+constexpr int SM_G = SM_X + 2 * 4 * CHUNK_B;   // 2 chunks = 4 KB (chunk 1 stays zero)
+constexpr int SM_IMG = SM_G + 2 * CHUNK_B;     // weight image (adam.cuh)
+constexpr int SM_W1 = SM_IMG + opt::IMG_W1 * 2;
+constexpr int SM_W2 = SM_IMG + opt::IMG_W2 * 2;
+constexpr int SM_W3 = SM_IMG + opt::IMG_W3 * 2;
+constexpr int SM_B2I = SM_IMG + opt::IMG_B2 * 2;
+constexpr int SM_B3I = SM_IMG + opt::IMG_B3 * 2;
+constexpr int SM_RED = SM_IMG + opt::IMG_BYTES;  // 4 warps x 12 floats + 4 x 3 doubles
+constexpr int SM_BAR = SM_RED + 384;             // 2 mbarriers + tmem base + flag
 constexpr int SM_TOTAL = SM_BAR + 64;
-constexpr int SM_FWD_TOTAL = SM_TOTAL;       // forward kernel uses the same map (D1 / G unused)
+constexpr int SM_STAGE = SM_H2;                  // flush staging: fp32 copy of the flat gradient (<= 32 KB)
 
 // TMEM columns (fp32 accumulators, 128 lanes)
 constexpr uint32_t TM_SCR = 0;     // 64: H1pre / H2pre / DH2 / DH1 in turn
@@ -51,43 +53,14 @@ constexpr uint32_t TM_GW3 = 192;   // 16
 constexpr uint32_t TM_COLS_BWD = 256;
 constexpr uint32_t TM_COLS_FWD = 128;
 
-__device__ __forceinline__ uint32_t pack_h2(float a, float b) {
-    const __half2 h = __floats2half2_rn(a, b);
-    return *reinterpret_cast<const uint32_t*>(&h);
+__device__ __forceinline__ uint32_t h2_bits(__half2 h) { return *reinterpret_cast<const uint32_t*>(&h); }
+__device__ __forceinline__ uint32_t pack_h2(float a, float b) { return h2_bits(__floats2half2_rn(a, b)); }
+__device__ __forceinline__ uint32_t pack_relu_h2(float a, float b) {
+    return h2_bits(__hmax2(__floats2half2_rn(a, b), __float2half2_rn(0.f)));
 }
 
-// weights: flat fp32 torch layout -> fp16 images [in/8][out][in%8] (zero padded)
-__device__ __forceinline__ void tc_load_weights(unsigned char* smem, const float* __restrict__ params, int in_dim, int out_dim) {
-    const Offsets o = offsets(in_dim, TC_H, out_dim);
-    __half* w1 = reinterpret_cast<__half*>(smem + SM_W1);
-    __half* w2 = reinterpret_cast<__half*>(smem + SM_W2);
-    __half* w3 = reinterpret_cast<__half*>(smem + SM_W3);
-    for (int i = threadIdx.x; i < TC_XF * TC_H; i += TC_THREADS) {  // i = out * 32 + in
-        const int out = i / TC_XF, in = i - out * TC_XF;
-        const float v = in < in_dim ? params[o.w1 + (int64_t)out * in_dim + in] : 0.f;
-        w1[((in >> 3) * TC_H + out) * 8 + (in & 7)] = __float2half_rn(v);
-    }
-    for (int i = threadIdx.x; i < TC_H * TC_H; i += TC_THREADS) {
-        const int out = i / TC_H, in = i - out * TC_H;
-        w2[((in >> 3) * TC_H + out) * 8 + (in & 7)] = __float2half_rn(params[o.w2 + i]);
-    }
-    for (int i = threadIdx.x; i < TC_OF * TC_H; i += TC_THREADS) {
-        const int out = i / TC_H, in = i - out * TC_H;
-        const float v = out < out_dim ? params[o.w3 + (int64_t)out * TC_H + in] : 0.f;
-        w3[((in >> 3) * TC_OF + out) * 8 + (in & 7)] = __float2half_rn(v);
-    }
-    float* b1 = reinterpret_cast<float*>(smem + SM_B1);
-    float* b2 = reinterpret_cast<float*>(smem + SM_B2);
-    float* b3 = reinterpret_cast<float*>(smem + SM_B3);
-    if (threadIdx.x < TC_H) {
-        b1[threadIdx.x] = params[o.b1 + threadIdx.x];
-        b2[threadIdx.x] = params[o.b2 + threadIdx.x];
-    }
-    if (threadIdx.x < TC_OF) b3[threadIdx.x] = threadIdx.x < out_dim ? params[o.b3 + threadIdx.x] : 0.f;
-}
-
-// this thread's input row (fp32 registers, feature 31 = `one`) -> X image
-__device__ __forceinline__ void tc_store_x(unsigned char* smem, const float (&x)[TC_XF]) {
+// this thread's input row (fp32 registers, feature 31 = 1) -> X image at smem + xoff
+__device__ __forceinline__ void tc_store_x(unsigned char* smem, int xoff, const float (&x)[TC_XF]) {
 #pragma unroll
     for (int c = 0; c < TC_XF / 8; ++c) {
         uint4 v;
@@ -95,12 +68,12 @@ __device__ __forceinline__ void tc_store_x(unsigned char* smem, const float (&x)
         v.y = pack_h2(x[8 * c + 2], x[8 * c + 3]);
         v.z = pack_h2(x[8 * c + 4], x[8 * c + 5]);
         v.w = pack_h2(x[8 * c + 6], x[8 * c + 7]);
-        *reinterpret_cast<uint4*>(smem + SM_X + c * CHUNK_B + threadIdx.x * 16) = v;
+        *reinterpret_cast<uint4*>(smem + xoff + c * CHUNK_B + threadIdx.x * 16) = v;
     }
 }
 
 // gather this thread's row of x (row-major [.][in_dim] fp32) into registers; zero when !valid
-__device__ __forceinline__ void tc_load_row(const float* __restrict__ x, int64_t row, int in_dim, bool valid, float one, float (&r)[TC_XF]) {
+__device__ __forceinline__ void tc_load_row(const float* __restrict__ x, int64_t row, int in_dim, bool valid, float (&r)[TC_XF]) {
 #pragma unroll
     for (int k = 0; k < TC_XF; ++k) r[k] = 0.f;
     if (valid) {
@@ -109,58 +82,55 @@ __device__ __forceinline__ void tc_load_row(const float* __restrict__ x, int64_t
 #pragma unroll
             for (int k = 0; k < TC_XF / 2; ++k)
                 if (2 * k < in_dim) {
-                    const float2 v = *reinterpret_cast<const float2*>(p + 2 * k);
+                    const float2 v = __ldg(reinterpret_cast<const float2*>(p + 2 * k));
                     r[2 * k] = v.x;
                     r[2 * k + 1] = v.y;
                 }
         } else {
 #pragma unroll
             for (int k = 0; k < TC_XF; ++k)
-                if (k < in_dim) r[k] = p[k];
+                if (k < in_dim) r[k] = __ldg(p + k);
         }
-        r[TC_XF - 1] = one;
+        r[TC_XF - 1] = 1.0f;
     }
 }
 
-// SCR accumulator (64 cols of this thread's lane) + bias, ReLU -> fp16 image at smem + dst
-__device__ __forceinline__ void tc_epilogue_relu(unsigned char* smem, uint32_t tmem_lane_base, int bias_off, int dst) {
-    const float* bias = reinterpret_cast<const float*>(smem + bias_off);
+// relu(SCR accumulator, 64 cols of this thread's lane) -> fp16 image at smem + dst
+__device__ __forceinline__ void tc_epilogue_relu(unsigned char* smem, uint32_t tmem_lane_base, int dst) {
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        float v[16];
-        tc::tmem_ld16(tmem_lane_base + TM_SCR + 16 * q, v);
+    for (int q = 0; q < 2; ++q) {
+        float v[32];
+        tc::tmem_ld32(tmem_lane_base + TM_SCR + 32 * q, v);
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            float f[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) f[i] = fmaxf(v[8 * h + i] + bias[16 * q + 8 * h + i], 0.f);
+        for (int h = 0; h < 4; ++h) {
             uint4 w;
-            w.x = pack_h2(f[0], f[1]); w.y = pack_h2(f[2], f[3]); w.z = pack_h2(f[4], f[5]); w.w = pack_h2(f[6], f[7]);
-            *reinterpret_cast<uint4*>(smem + dst + (2 * q + h) * CHUNK_B + threadIdx.x * 16) = w;
+            w.x = pack_relu_h2(v[8 * h + 0], v[8 * h + 1]);
+            w.y = pack_relu_h2(v[8 * h + 2], v[8 * h + 3]);
+            w.z = pack_relu_h2(v[8 * h + 4], v[8 * h + 5]);
+            w.w = pack_relu_h2(v[8 * h + 6], v[8 * h + 7]);
+            *reinterpret_cast<uint4*>(smem + dst + (4 * q + h) * CHUNK_B + threadIdx.x * 16) = w;
         }
     }
 }
 
-// SCR accumulator masked by (act image at `mask_src` > 0) -> fp16 image at `dst` (may equal mask_src)
-__device__ __forceinline__ void tc_epilogue_mask(unsigned char* smem, uint32_t tmem_lane_base, int mask_src, int dst) {
+// SCR accumulator masked by (activation image at `img` > 0), written back over the same image
+__device__ __forceinline__ void tc_epilogue_mask(unsigned char* smem, uint32_t tmem_lane_base, int img) {
+    const __half2 zero = __float2half2_rn(0.f);
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        float v[16];
-        tc::tmem_ld16(tmem_lane_base + TM_SCR + 16 * q, v);
+    for (int q = 0; q < 2; ++q) {
+        float v[32];
+        tc::tmem_ld32(tmem_lane_base + TM_SCR + 32 * q, v);
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            const uint4 m = *reinterpret_cast<const uint4*>(smem + mask_src + (2 * q + h) * CHUNK_B + threadIdx.x * 16);
+        for (int h = 0; h < 4; ++h) {
+            uint4* cell = reinterpret_cast<uint4*>(smem + img + (4 * q + h) * CHUNK_B + threadIdx.x * 16);
+            const uint4 m = *cell;
             const __half2* mh = reinterpret_cast<const __half2*>(&m);
-            float f[8];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const float2 a = __half22float2(mh[i]);
-                f[2 * i] = a.x > 0.f ? v[8 * h + 2 * i] : 0.f;
-                f[2 * i + 1] = a.y > 0.f ? v[8 * h + 2 * i + 1] : 0.f;
-            }
             uint4 w;
-            w.x = pack_h2(f[0], f[1]); w.y = pack_h2(f[2], f[3]); w.z = pack_h2(f[4], f[5]); w.w = pack_h2(f[6], f[7]);
-            *reinterpret_cast<uint4*>(smem + dst + (2 * q + h) * CHUNK_B + threadIdx.x * 16) = w;
+            w.x = pack_h2(v[8 * h + 0], v[8 * h + 1]) & __hgt2_mask(mh[0], zero);
+            w.y = pack_h2(v[8 * h + 2], v[8 * h + 3]) & __hgt2_mask(mh[1], zero);
+            w.z = pack_h2(v[8 * h + 4], v[8 * h + 5]) & __hgt2_mask(mh[2], zero);
+            w.w = pack_h2(v[8 * h + 6], v[8 * h + 7]) & __hgt2_mask(mh[3], zero);
+            *cell = w;
         }
     }
 }
@@ -189,7 +159,7 @@ __device__ __forceinline__ void tc_sync_for_mma() {
 
 // ---------------------------------------------------------------------------------------------
 struct TcFwdArgs {
-    const float* params;
+    const unsigned char* image;
     const float* x;
     const int64_t* rows;
     int64_t n;
@@ -203,22 +173,35 @@ struct TcFwdArgs {
 };
 
 struct TcSetup {
-    uint64_t* bar;
+    uint64_t* bar;   // bar[0]: waited phases; bar[1]: the unwaited weight-gradient commits of the backward
     uint32_t tmem, lane_base, sbase, phase;
 };
 
-__device__ __forceinline__ TcSetup tc_setup(unsigned char* smem, const float* params, int in_dim, int out_dim, uint32_t tmem_cols) {
-    TcSetup s;
-    s.bar = reinterpret_cast<uint64_t*>(smem + SM_BAR);
-    uint32_t* tmem_s = reinterpret_cast<uint32_t*>(smem + SM_BAR + 8);
+// part A: nothing here depends on the parameters (runs ahead of pdl_wait())
+__device__ __forceinline__ void tc_setup_begin(unsigned char* smem, uint32_t tmem_cols) {
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem + SM_BAR);
+    uint32_t* tmem_s = reinterpret_cast<uint32_t*>(smem + SM_BAR + 16);
     const int warp = threadIdx.x >> 5;
-    tc_load_weights(smem, params, in_dim, out_dim);
     for (int i = threadIdx.x; i < 2 * CHUNK_B / 16; i += TC_THREADS)  // G image (chunk 1 stays zero forever)
         *reinterpret_cast<uint4*>(smem + SM_G + i * 16) = make_uint4(0, 0, 0, 0);
     if (warp == 0) tc::tmem_alloc(tmem_s, tmem_cols);
     if (threadIdx.x == 0) {
-        tc::mbar_init(s.bar, 1);
+        tc::mbar_init(bar, 1);
+        tc::mbar_init(bar + 1, 1);
         tc::fence_barrier_init();
+    }
+}
+
+// part B: weight image (straight 16-byte copies; the image is rebuilt by the optimizer step, not here), then publish
+__device__ __forceinline__ TcSetup tc_setup_finish(unsigned char* smem, const unsigned char* image) {
+    TcSetup s;
+    s.bar = reinterpret_cast<uint64_t*>(smem + SM_BAR);
+    uint32_t* tmem_s = reinterpret_cast<uint32_t*>(smem + SM_BAR + 16);
+    const int warp = threadIdx.x >> 5;
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(image);
+        uint4* dst = reinterpret_cast<uint4*>(smem + SM_IMG);
+        for (int i = threadIdx.x; i < opt::IMG_BYTES / 16; i += TC_THREADS) dst[i] = __ldcg(src + i);
     }
     tc_sync_for_mma();
     s.tmem = *tmem_s;
@@ -234,49 +217,51 @@ __device__ __forceinline__ void tc_wait(TcSetup& s) {
     tc::fence_after_sync();
 }
 
-// X -> H1 -> H2 -> OUT for the tile currently in the X image; leaves OUT in TMEM (waited)
-__device__ __forceinline__ void tc_forward_tile(unsigned char* smem, TcSetup& s) {
+// [X|1] -> H1 -> H2 -> OUT for the tile in the X image at xoff; leaves OUT in TMEM (waited)
+__device__ __forceinline__ void tc_forward_tile(unsigned char* smem, TcSetup& s, int xoff) {
     constexpr uint32_t ID64 = tc::make_idesc_f16(128, 64, 0, 0, 0, 0);
     constexpr uint32_t ID16 = tc::make_idesc_f16(128, 16, 0, 0, 0, 0);
     tc_sync_for_mma();
     if (threadIdx.x == 0) {
 #pragma unroll
         for (int ks = 0; ks < TC_XF / 16; ++ks)
-            tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase + SM_X, ks), desc_w_k(s.sbase + SM_W1, TC_H, ks), ID64, ks > 0);
+            tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase + xoff, ks), desc_w_k(s.sbase + SM_W1, TC_H, ks), ID64, ks > 0);
         tc::commit(s.bar);
     }
     tc_wait(s);
-    tc_epilogue_relu(smem, s.lane_base, SM_B1, SM_H1);
+    tc_epilogue_relu(smem, s.lane_base, SM_H1);
     tc_sync_for_mma();
     if (threadIdx.x == 0) {
 #pragma unroll
         for (int ks = 0; ks < TC_H / 16; ++ks)
             tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase + SM_H1, ks), desc_w_k(s.sbase + SM_W2, TC_H, ks), ID64, ks > 0);
+        tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase + xoff, 1), desc_w_k(s.sbase + SM_B2I, TC_H, 0), ID64, 1);  // + b2
         tc::commit(s.bar);
     }
     tc_wait(s);
-    tc_epilogue_relu(smem, s.lane_base, SM_B2, SM_H2);
+    tc_epilogue_relu(smem, s.lane_base, SM_H2);
     tc_sync_for_mma();
     if (threadIdx.x == 0) {
 #pragma unroll
         for (int ks = 0; ks < TC_H / 16; ++ks)
             tc::mma_f16(s.tmem + TM_OUT, desc_act_k(s.sbase + SM_H2, ks), desc_w_k(s.sbase + SM_W3, TC_OF, ks), ID16, ks > 0);
+        tc::mma_f16(s.tmem + TM_OUT, desc_act_k(s.sbase + xoff, 1), desc_w_k(s.sbase + SM_B3I, TC_OF, 0), ID16, 1);  // + b3
         tc::commit(s.bar);
     }
     tc_wait(s);
 }
 
-__device__ __forceinline__ void tc_read_out(unsigned char* smem, const TcSetup& s, float (&z)[OUTP]) {
+__device__ __forceinline__ void tc_read_out(const TcSetup& s, float (&z)[OUTP]) {
     float o[16];
     tc::tmem_ld16(s.lane_base + TM_OUT, o);
-    const float* b3 = reinterpret_cast<const float*>(smem + SM_B3);
 #pragma unroll
-    for (int j = 0; j < OUTP; ++j) z[j] = o[j] + b3[j];
+    for (int j = 0; j < OUTP; ++j) z[j] = o[j];
 }
 
 __global__ void __launch_bounds__(TC_THREADS) tc_forward_kernel(TcFwdArgs a) {
     extern __shared__ __align__(1024) unsigned char smem[];
-    TcSetup s = tc_setup(smem, a.params, a.in_dim, a.out_dim, TM_COLS_FWD);
+    tc_setup_begin(smem, TM_COLS_FWD);
+    TcSetup s = tc_setup_finish(smem, a.image);
     const int64_t n_tiles = (a.n + TC_ROWS - 1) / TC_ROWS;
     const int r = threadIdx.x;
     float xr[TC_XF];
@@ -286,22 +271,23 @@ __global__ void __launch_bounds__(TC_THREADS) tc_forward_kernel(TcFwdArgs a) {
     if (tile < n_tiles) {
         nvalid = tile * TC_ROWS + r < a.n;
         nsrc = nvalid ? (a.rows ? a.rows[tile * TC_ROWS + r] : tile * TC_ROWS + r) : 0;
-        tc_load_row(a.x, nsrc, a.in_dim, nvalid, 0.f, xr);
+        tc_load_row(a.x, nsrc, a.in_dim, nvalid, xr);
     }
-    for (; tile < n_tiles; tile += gridDim.x) {
+    for (uint32_t it = 0; tile < n_tiles; tile += gridDim.x, ++it) {
         const bool valid = nvalid;
         const int64_t src = nsrc;
         const int64_t dst = (a.scatter && a.rows) ? src : tile * TC_ROWS + r;
-        tc_store_x(smem, xr);
+        const int xoff = SM_X + (int)(it & 1) * 4 * CHUNK_B;
+        tc_store_x(smem, xoff, xr);
         const int64_t nt = tile + gridDim.x;
         if (nt < n_tiles) {  // prefetch the next tile's row while this one computes
             nvalid = nt * TC_ROWS + r < a.n;
             nsrc = nvalid ? (a.rows ? a.rows[nt * TC_ROWS + r] : nt * TC_ROWS + r) : 0;
-            tc_load_row(a.x, nsrc, a.in_dim, nvalid, 0.f, xr);
+            tc_load_row(a.x, nsrc, a.in_dim, nvalid, xr);
         }
-        tc_forward_tile(smem, s);
+        tc_forward_tile(smem, s, xoff);
         float z[OUTP];
-        tc_read_out(smem, s, z);
+        tc_read_out(s, z);
         if (valid) {
             if (a.value && a.value_index >= 0) {
                 float v = 0.f;
@@ -363,7 +349,7 @@ __global__ void __launch_bounds__(TC_THREADS) tc_forward_kernel(TcFwdArgs a) {
 
 // ---------------------------------------------------------------------------------------------
 struct TcPpoArgs {
-    const float* params;
+    const unsigned char* image;
     float* grads;
     const float* obs;
     const int32_t* act;
@@ -378,6 +364,7 @@ struct TcPpoArgs {
     int in_dim, out_dim, n_act, value_index;
     float gscale, inv_gscale;  // S and 1/S (power of two)
     double* loss_sums;
+    int debug;  // experiments only (TSM_TC_DEBUG): 1 skip flush, 2 skip backward GEMM phases, 4 skip the loss math
 };
 
 struct RowData {
@@ -391,21 +378,32 @@ __device__ __forceinline__ void tc_prefetch_row(const TcPpoArgs& a, int64_t tile
     d = RowData{0, 0.f, 0.f, 0.f, 0.f};
     int64_t slot = 0;
     if (valid) {
-        slot = slot_of(a.view, p);
+        slot = (a.debug & 8) ? p : slot_of(a.view, p);
         if (a.n_act > 0) {
-            d.act = a.act[slot];
-            d.adv = a.adv[slot];
-            d.logp_old = a.logp_old[slot];
+            d.act = __ldg(a.act + slot);
+            d.adv = __ldg(a.adv + slot);
+            d.logp_old = __ldg(a.logp_old + slot);
         }
-        if (a.value_index >= 0) d.ret = a.ret[slot];
-        if (a.cfg.value_clip) d.v_old = a.v_old[slot];
+        if (a.value_index >= 0) d.ret = __ldg(a.ret + slot);
+        if (a.cfg.value_clip) d.v_old = __ldg(a.v_old + slot);
     }
-    tc_load_row(a.obs, slot, a.in_dim, valid, 1.0f, xr);
+    tc_load_row(a.obs, slot, a.in_dim, valid, xr);
+}
+
+// physical position of flat gradient element i inside the staging copy: the W2 block is XOR-swizzled
+// so that both the per-lane row writes (stride 64 floats) and the linear read-out are bank-conflict free
+__device__ __forceinline__ int stage_pos(int i, int w2_lo, int w2_hi) {
+    if (i >= w2_lo && i < w2_hi) {
+        const int rel = i - w2_lo, rr = rel >> 6, cc = rel & 63;
+        return w2_lo + (rr << 6) + (cc ^ (rr & 31));
+    }
+    return i;
 }
 
 __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs a) {
     extern __shared__ __align__(1024) unsigned char smem[];
-    TcSetup s = tc_setup(smem, a.params, a.in_dim, a.out_dim, TM_COLS_BWD);
+    pdl_launch_dependents();
+    tc_setup_begin(smem, TM_COLS_BWD);
     constexpr uint32_t ID_DH = tc::make_idesc_f16(128, 64, 0, 0, 0, 1);    // K-major A, MN-major B
     constexpr uint32_t ID_G64 = tc::make_idesc_f16(128, 64, 0, 0, 1, 1);   // both MN-major (K = rows)
     constexpr uint32_t ID_G32 = tc::make_idesc_f16(128, 32, 0, 0, 1, 1);
@@ -413,8 +411,6 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
     const int r = threadIdx.x;
     const int64_t n_tiles = (a.mb_len + TC_ROWS - 1) / TC_ROWS;
     const float inv_n = 1.0f / (float)a.mb_len;
-    float mean = 0.f, rstd = 1.f;
-    if (a.cfg.adv_norm && a.mb_stats) { mean = a.mb_stats[0]; rstd = a.mb_stats[1]; }
     float gb3[OUTP];
 #pragma unroll
     for (int j = 0; j < OUTP; ++j) gb3[j] = 0.f;
@@ -424,18 +420,29 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
     RowData nd;
     bool nvalid = false;
     int64_t tile = blockIdx.x;
-    if (tile < n_tiles) tc_prefetch_row(a, tile, r, nvalid, xr, nd);
+    if (tile < n_tiles) tc_prefetch_row(a, tile, r, nvalid, xr, nd);  // batch arrays only: safe ahead of the dependency wait
+    pdl_wait();  // parameters (image), gradients and mb_stats of the preceding launches are now visible
+    TcSetup s = tc_setup_finish(smem, a.image);
+    float mean = 0.f, rstd = 1.f;
+    if (a.cfg.adv_norm && a.mb_stats) { mean = __ldcg(a.mb_stats); rstd = __ldcg(a.mb_stats + 1); }
     uint32_t it = 0;
     for (; tile < n_tiles; tile += gridDim.x, ++it) {
         const bool valid = nvalid;
         const RowData d = nd;
-        tc_store_x(smem, xr);
+        const int xoff = SM_X + (int)(it & 1) * 4 * CHUNK_B;
+        tc_store_x(smem, xoff, xr);
         if (tile + gridDim.x < n_tiles) tc_prefetch_row(a, tile + gridDim.x, r, nvalid, xr, nd);
-        tc_forward_tile(smem, s);
+        tc_forward_tile(smem, s, xoff);  // its first wait also covers the previous tile's weight-gradient GEMMs
         // ---- loss and G = S * d(loss)/d(OUT) for this thread's row ----
         float z[OUTP], dz[OUTP];
-        tc_read_out(smem, s, z);
-        const RowLoss rl = row_loss(z, a.n_act, a.value_index, d.act, d.adv, d.ret, d.logp_old, d.v_old, mean, rstd, a.cfg, inv_n, dz);
+        tc_read_out(s, z);
+        RowLoss rl{0.f, 0.f, 0.f};
+        if (a.debug & 4) {
+#pragma unroll
+            for (int j = 0; j < OUTP; ++j) dz[j] = z[j] * inv_n;
+        } else {
+            rl = row_loss(z, a.n_act, a.value_index, d.act, d.adv, d.ret, d.logp_old, d.v_old, mean, rstd, a.cfg, inv_n, dz);
+        }
         if (valid) {
             l_clip += (double)rl.clip;
             l_vf += (double)rl.vf;
@@ -453,6 +460,11 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
             w.x = pack_h2(g[0], g[1]); w.y = pack_h2(g[2], g[3]); w.z = pack_h2(g[4], g[5]); w.w = pack_h2(g[6], g[7]);
             *reinterpret_cast<uint4*>(smem + SM_G + r * 16) = w;
         }
+        if (a.debug & 2) {
+            tc_sync_for_mma();
+            if (threadIdx.x == 0) tc::commit(s.bar + 1);
+            continue;
+        }
         tc_sync_for_mma();
         if (threadIdx.x == 0) {
 #pragma unroll
@@ -462,65 +474,63 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
             tc::commit(s.bar);
         }
         tc_wait(s);
-        tc_epilogue_mask(smem, s.lane_base, SM_H2, SM_H2);  // D2 over H2 (the dW3 GEMM has completed)
-        tc_sync_for_mma();
-        if (threadIdx.x == 0) {
-#pragma unroll
-            for (int ks = 0; ks < TC_H / 16; ++ks)  // DH1 = D2 W2
-                tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase + SM_H2, ks), desc_w_mn(s.sbase + SM_W2, TC_H, ks), ID_DH, ks > 0);
-            tc::commit(s.bar);
-        }
-        tc_wait(s);
-        tc_epilogue_mask(smem, s.lane_base, SM_H1, SM_D1);
+        tc_epilogue_mask(smem, s.lane_base, SM_H2);  // D2 over H2 (the dW3 GEMM has completed)
         tc_sync_for_mma();
         if (threadIdx.x == 0) {
 #pragma unroll
             for (int ks = 0; ks < TC_ROWS / 16; ++ks)  // [dW2; .] += [D2; H1]^T H1
                 tc::mma_f16(s.tmem + TM_GW2, desc_act_mn(s.sbase + SM_H2, ks), desc_act_mn(s.sbase + SM_H1, ks), ID_G64, (it | ks) > 0);
 #pragma unroll
-            for (int ks = 0; ks < TC_ROWS / 16; ++ks)  // [dW1 | db1; . | db2] += [D1; D2]^T X
-                tc::mma_f16(s.tmem + TM_GW1, desc_act_mn(s.sbase + SM_D1, ks), desc_act_mn(s.sbase + SM_X, ks), ID_G32, (it | ks) > 0);
+            for (int ks = 0; ks < TC_H / 16; ++ks)  // DH1 = D2 W2
+                tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase + SM_H2, ks), desc_w_mn(s.sbase + SM_W2, TC_H, ks), ID_DH, ks > 0);
             tc::commit(s.bar);
         }
-        tc_wait(s);  // X / H1 / H2 / D1 are free again
-    }
-    // ---- flush: TMEM gradient accumulators -> flat gradient buffer (scaled back by 1/S) ----
-    const Offsets o = offsets(a.in_dim, TC_H, a.out_dim);
-    const float inv_s = a.inv_gscale;
-    if (it > 0) {
-        if (r < TC_H) {
+        tc_wait(s);
+        tc_epilogue_mask(smem, s.lane_base, SM_H1);  // D1 over H1 (the dW2 GEMM has completed)
+        tc_sync_for_mma();
+        if (threadIdx.x == 0) {
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {  // dW2[r][16q..]
-                float v[16];
-                tc::tmem_ld16(s.lane_base + TM_GW2 + 16 * q, v);
-#pragma unroll
-                for (int e = 0; e < 16; ++e) atomicAdd(a.grads + o.w2 + (int64_t)r * TC_H + 16 * q + e, v[e] * inv_s);
-            }
-#pragma unroll
-            for (int q = 0; q < 2; ++q) {  // dW1[r][k], db1[r] (column 31)
-                float v[16];
-                tc::tmem_ld16(s.lane_base + TM_GW1 + 16 * q, v);
-#pragma unroll
-                for (int e = 0; e < 16; ++e) {
-                    const int k = 16 * q + e;
-                    if (k < a.in_dim) atomicAdd(a.grads + o.w1 + (int64_t)r * a.in_dim + k, v[e] * inv_s);
-                    if (k == TC_XF - 1) atomicAdd(a.grads + o.b1 + r, v[e] * inv_s);
-                }
-            }
-            {  // dW3^T[r][o]
-                float v[16];
-                tc::tmem_ld16(s.lane_base + TM_GW3, v);
-#pragma unroll
-                for (int e = 0; e < OUTP; ++e)
-                    if (e < a.out_dim) atomicAdd(a.grads + o.w3 + (int64_t)e * TC_H + r, v[e] * inv_s);
-            }
-        } else {  // lanes 64..127 of the [D1; D2]^T X accumulator: column 31 = db2
-            float v[16];
-            tc::tmem_ld16(s.lane_base + TM_GW1 + 16, v);
-            atomicAdd(a.grads + o.b2 + (r - TC_H), v[15] * inv_s);
+            for (int ks = 0; ks < TC_ROWS / 16; ++ks)  // [. | db2; dW1 | db1] += [D2; D1]^T [X | 1]
+                tc::mma_f16(s.tmem + TM_GW1, desc_act_mn(s.sbase + SM_H2, ks), desc_act_mn(s.sbase + xoff, ks), ID_G32, (it | ks) > 0);
+            tc::commit(s.bar + 1);  // not waited here: X is double buffered and H1 / H2 are next written after a wait
         }
     }
-    // db3 and the loss sums: warp shuffle, then one atomic per warp
+    const Offsets o = offsets(a.in_dim, TC_H, a.out_dim);
+    const float inv_s = a.inv_gscale;
+    if (it > 0 && !(a.debug & 1)) {
+        // ---- flush: TMEM gradient accumulators -> smem staging (flat gradient layout) -> coalesced atomics ----
+        tc::mbar_wait(s.bar + 1, (it - 1) & 1);
+        tc::fence_after_sync();
+        float* stage = reinterpret_cast<float*>(smem + SM_STAGE);
+        const int w2_lo = (int)o.w2;
+        if (r < TC_H) {
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {  // dW2[r][32q..]
+                float v[32];
+                tc::tmem_ld32(s.lane_base + TM_GW2 + 32 * q, v);
+#pragma unroll
+                for (int e = 0; e < 32; ++e) stage[w2_lo + (r << 6) + ((32 * q + e) ^ (r & 31))] = v[e];
+            }
+            float v[16];
+            tc::tmem_ld16(s.lane_base + TM_GW3, v);  // dW3^T[r][o]
+#pragma unroll
+            for (int e = 0; e < OUTP; ++e)
+                if (e < a.out_dim) stage[o.w3 + e * TC_H + r] = v[e];
+            tc::tmem_ld16(s.lane_base + TM_GW1 + 16, v);  // D2^T [X|1], column 31 = db2[r]
+            stage[o.b2 + r] = v[15];
+        } else {
+            float v[32];
+            tc::tmem_ld32(s.lane_base + TM_GW1, v);  // dW1[r-64][k], db1[r-64] (column 31)
+            const int rr = r - TC_H;
+#pragma unroll
+            for (int k = 0; k < 32; ++k)
+                if (k < a.in_dim) stage[o.w1 + rr * a.in_dim + k] = v[k];
+            stage[o.b1 + rr] = v[31];
+        }
+    }
+    // db3 and the loss sums: warp shuffle, then shared memory
+    float* red_f = reinterpret_cast<float*>(smem + SM_RED);
+    double* red_d = reinterpret_cast<double*>(smem + SM_RED + 192);
 #pragma unroll
     for (int dlt = 16; dlt > 0; dlt >>= 1) {
 #pragma unroll
@@ -529,17 +539,20 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
         l_vf += __shfl_down_sync(0xffffffffu, l_vf, dlt);
         l_ent += __shfl_down_sync(0xffffffffu, l_ent, dlt);
     }
-    if ((threadIdx.x & 31) == 0 && it > 0) {
+    if ((r & 31) == 0) {
+        const int w = r >> 5;
 #pragma unroll
-        for (int j = 0; j < OUTP; ++j)
-            if (j < a.out_dim) atomicAdd(a.grads + o.b3 + j, gb3[j]);
-        if (a.loss_sums) {
-            atomicAdd(a.loss_sums + 0, l_clip);
-            atomicAdd(a.loss_sums + 1, l_vf);
-            atomicAdd(a.loss_sums + 2, l_ent);
-        }
+        for (int j = 0; j < OUTP; ++j) red_f[w * OUTP + j] = gb3[j];
+        red_d[w * 3 + 0] = l_clip; red_d[w * 3 + 1] = l_vf; red_d[w * 3 + 2] = l_ent;
     }
     tc::fence_before_sync();
     __syncthreads();
-    if ((threadIdx.x >> 5) == 0) tc::tmem_dealloc(s.tmem, TM_COLS_BWD);
+    if ((r >> 5) == 0) tc::tmem_dealloc(s.tmem, TM_COLS_BWD);
+    if (it > 0 && !(a.debug & 1)) {
+        const float* stage = reinterpret_cast<const float*>(smem + SM_STAGE);
+        const int w2_lo = (int)o.w2, w2_hi = (int)o.b2, n_stage = (int)o.b3;
+        for (int i = r; i < n_stage; i += TC_THREADS) atomicAdd(a.grads + i, stage[stage_pos(i, w2_lo, w2_hi)] * inv_s);
+        if (r < a.out_dim) atomicAdd(a.grads + o.b3 + r, red_f[r] + red_f[OUTP + r] + red_f[2 * OUTP + r] + red_f[3 * OUTP + r]);
+        if (a.loss_sums && r < 3) atomicAdd(a.loss_sums + r, red_d[r] + red_d[3 + r] + red_d[6 + r] + red_d[9 + r]);
+    }
 }

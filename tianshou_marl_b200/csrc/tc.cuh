@@ -3,15 +3,16 @@
 // layouts below follow the PTX ISA "tcgen05 shared-memory descriptor" / "instruction descriptor".
 //
 // Operand layout used throughout (no swizzle, "interleaved" canonical layout): a matrix with a
-// row index r (128 rows) and a feature index f is stored as  [f/4][r][f%4]  fp32 words, i.e. 16-byte
-// chunks of 4 consecutive features, chunk-major.  The SAME bytes are a valid
+// row index r (128 rows) and a feature index f is stored as  [f/8][r][f%8]  fp16 halves, i.e. 16-byte
+// chunks of 8 consecutive features, chunk-major.  The SAME bytes are a valid
 //   * K-major operand with (M or N) = r, K = f:  8-row core matrices are 128 contiguous bytes,
 //     SBO (next 8 rows) = 128 B, LBO (next 16 bytes of K) = rows*16 B; and a valid
 //   * MN-major operand with (M or N) = f, K = r: a core matrix is 8 k-rows x 16 bytes of MN,
-//     LBO (next 8 k) = 128 B, SBO (next 4 features) = rows*16 B.
+//     LBO (next 8 k) = 128 B, SBO (next 8 features) = rows*16 B.
 // So activations are written once by the epilogue and read both by the next layer's GEMM
 // (K = features) and by the weight-gradient GEMMs (K = rows) without any transpose; weights are
-// stored once as [in/4][out][in%4] and serve forward (K-major B) and backward (MN-major B).
+// stored once as [in/8][out][in%8] and serve forward (K-major B) and backward (MN-major B).
+// (tf32 operands cannot be MN-major without a 128-byte swizzle, hence fp16: tests/test_gpu_tc.py.)
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -106,17 +107,29 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
 }
 
-// TMEM -> registers: this warp's 32 lanes x 16 consecutive 32-bit columns starting at taddr
+// TMEM -> registers: this warp's 32 lanes x 16 / 32 consecutive 32-bit columns starting at taddr.
+// The load and its wait are ONE asm statement so no use of the registers can be scheduled in between.
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
     uint32_t r[16];
     asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
-          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-        : "r"(taddr));
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n\t"
+        "tcgen05.wait::ld.sync.aligned;"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
 #pragma unroll
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+    uint32_t r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n\t"
+        "tcgen05.wait::ld.sync.aligned;"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
 
 }  // namespace tc

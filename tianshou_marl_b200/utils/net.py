@@ -50,6 +50,10 @@ class ActorCriticNet(nn.Module):
         self.adam_m = torch.zeros(n, dtype=torch.float32, device=self.device)
         self.adam_v = torch.zeros(n, dtype=torch.float32, device=self.device)
         self.adam_step = torch.zeros(1, dtype=torch.int64, device=self.device)
+        # engine "tc": fp16 operand image of the parameters, kept current by the optimizer kernels; any host-side
+        # write to `flat` (tracked through its version counter) triggers tsm_net_pack before the next kernel call
+        self.tc_image = torch.zeros(_lib.TC_IMAGE_BYTES, dtype=torch.uint8, device=self.device) if engine == "tc" else None
+        self._packed_version = -1
         H, I, O = self.hidden, self.in_dim, self.out_dim
         sizes = [("W1", (H, I)), ("b1", (H,)), ("W2", (H, H)), ("b2", (H,)), ("W3", (O, H)), ("b3", (O,))]
         self._views: dict[str, tuple[int, tuple[int, ...]]] = {}
@@ -76,16 +80,23 @@ class ActorCriticNet(nn.Module):
         d.engine = 1 if self.engine == "tc" else 0
         d.params, d.grads = self.flat.data_ptr(), self.grads.data_ptr()
         d.adam_m, d.adam_v, d.adam_step = self.adam_m.data_ptr(), self.adam_v.data_ptr(), self.adam_step.data_ptr()
+        d.tc_image = self.tc_image.data_ptr() if self.tc_image is not None else None
 
     @property
     def desc(self) -> Any:
         if self._desc.params != self.flat.data_ptr() or self._desc.engine != (1 if self.engine == "tc" else 0):
             self._fill_desc()
+        if self.engine == "tc" and self.flat._version != self._packed_version:
+            if self.tc_image is None:
+                self.tc_image = torch.zeros(_lib.TC_IMAGE_BYTES, dtype=torch.uint8, device=self.device)
+                self._fill_desc()
+            _lib.check(_lib.lib().tsm_net_pack(C.byref(self._desc), _lib.stream_ptr()))
+            self._packed_version = self.flat._version
         return C.byref(self._desc)
 
     def view(self, name: str) -> torch.Tensor:
         off, shp = self._views[name]
-        return self.flat.data[off: off + int(np.prod(shp))].view(shp)
+        return self.flat.detach()[off: off + int(np.prod(shp))].view(shp)  # shares flat's version counter
 
     def named_views(self) -> dict[str, torch.Tensor]:
         return {k: self.view(k) for k in self._views}
