@@ -5,6 +5,7 @@
 // (fp16 operands in shared memory, fp32 accumulators in TMEM).  See tc.cuh / mlp_tc_kernels.cuh.
 #include <algorithm>
 #include <cstdlib>
+#include <cstdio>
 #include "common.cuh"
 #include "philox.cuh"
 #include <cuda_fp16.h>
@@ -111,7 +112,7 @@ int tc_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int6
     a.in_dim = net->in_dim; a.out_dim = net->out_dim; a.n_act = net->n_act; a.value_index = net->value_index;
     a.mode = mode; a.scatter = scatter; a.seed = seed; a.counter = counter;
     a.out = out; a.act = act; a.logp = logp; a.value = value; a.entropy = entropy;
-    const size_t smem = mlptc::SM_TOTAL + 128;  // ~69 KB: three CTAs per SM (3 x 128 TMEM columns)
+    const size_t smem = mlptc::SM_FWD_TOTAL + 128;  // ~69 KB: three CTAs per SM (3 x 128 TMEM columns)
     static bool attr = false;
     if (!attr) {
         TSM_CUDA(cudaFuncSetAttribute(mlptc::tc_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -143,8 +144,8 @@ int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_p
     a.loss_sums = loss_sums;
     static const int dbg = getenv("TSM_TC_DEBUG") ? atoi(getenv("TSM_TC_DEBUG")) : 0;
     a.debug = dbg;
-    const size_t smem = 100 * 1024;  // > 227/3 KB: at most two CTAs per SM (2 x 256 TMEM columns)
-    static_assert(mlptc::SM_TOTAL + 128 <= 100 * 1024, "smem map too large");
+    const size_t smem = mlptc::SM_TOTAL + 128;  // ~101 KB: two CTAs per SM (2 x 256 TMEM columns)
+    static_assert(mlptc::SM_TOTAL + 128 <= 112 * 1024 && mlptc::SM_TOTAL > 76 * 1024, "smem map must give exactly two CTAs per SM");
     static bool attr = false;
     if (!attr) {
         TSM_CUDA(cudaFuncSetAttribute(mlptc::tc_ppo_minibatch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -159,6 +160,18 @@ int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_p
     at[0].val.programmaticStreamSerializationAllowed = 1;
     lc.attrs = at; lc.numAttrs = pdl ? 1 : 0;
     TSM_CUDA(cudaLaunchKernelEx(&lc, mlptc::tc_ppo_minibatch_kernel, a));
+#ifdef TSM_TC_TRACE
+    if (getenv("TSM_TC_TRACE_DUMP")) {
+        long long h[4][64];
+        cudaDeviceSynchronize();
+        cudaMemcpyFromSymbol(h, mlptc::g_trace, sizeof(h));
+        for (int row = 0; row < 4; ++row) {
+            printf("trace row %d:", row);
+            for (int k = 1; k < 24; ++k) printf(" %lld", h[row][k] - h[row][k - 1]);
+            printf("  total %lld\n", h[row][23] - h[row][0]);
+        }
+    }
+#endif
     return TSM_OK;
 }
 

@@ -12,13 +12,16 @@
 //   data grads   DH2 = G W3                             A = G   (K-major, K = 16)   B = W3 (MN-major) N = 64
 //                DH1 = D2 W2                            A = D2  (K-major, K = 64)   B = W2 (MN-major) N = 64
 //   weight grads (K = the 128 rows, both operands MN-major views of the activation images,
-//                 M = 128 made of the two adjacent 64-feature images [H2 slot][H1 slot]):
+//                 M = 128 made of two adjacent 64-feature images, [H2][H1] or [D2][D1]):
 //                [dW3^T; .]        += [H2; H1]^T G        N = 16   (lanes 0..63 used)
-//                [dW2 ; .]         += [D2; H1]^T H1       N = 64   (lanes 0..63 used)
+//                [dW2 ; .]         += [D2; D1]^T H1       N = 64   (lanes 0..63 used)
 //                [.|db2; dW1|db1]  += [D2; D1]^T [X|1]    N = 32   (column 31 = bias gradients)
-// G = S * d(loss)/d(OUT) with S a power of two (fp16 range); D2 / D1 = ReLU-masked DH2 / DH1 written
-// in place over H2 / H1.  Weight-gradient accumulators stay in TMEM across all tiles of the CTA and
-// are flushed once, through a shared-memory staging copy so that the global atomics are coalesced.
+// G = S * d(loss)/d(OUT) with S a power of two (fp16 range); D2 / D1 = ReLU-masked DH2 / DH1.
+// Only the five dependent GEMM stages (3 forward, 2 data-gradient) sit on a tile's critical path: the
+// 24 weight-gradient MMAs are issued last and never waited for inside the tile (the next tile's first
+// wait covers them; X is double buffered).  Weight-gradient accumulators stay in TMEM across all tiles
+// of the CTA and are flushed once, through a shared-memory staging copy so that the global atomics
+// are coalesced.
 #pragma once
 
 constexpr int TC_THREADS = 128;
@@ -28,9 +31,9 @@ constexpr int TC_XF = 32;    // padded input features (31 = ones)
 constexpr int TC_OF = 16;    // padded head outputs (UMMA N >= 16 at M = 128)
 constexpr int CHUNK_B = TC_ROWS * 16;  // bytes of one 8-feature chunk of an activation image (2048)
 
-// shared-memory map (bytes).  [H2][H1] must stay adjacent and in this order.
-constexpr int SM_H2 = 0;                       // 16 KB (D2 in place)
-constexpr int SM_H1 = SM_H2 + 8 * CHUNK_B;     // 16 KB (D1 in place)
+// shared-memory map (bytes).  [H2][H1] and [D2][D1] must each stay adjacent and in this order.
+constexpr int SM_H2 = 0;                       // 16 KB
+constexpr int SM_H1 = SM_H2 + 8 * CHUNK_B;     // 16 KB
 constexpr int SM_X = SM_H1 + 8 * CHUNK_B;      // 2 x 8 KB, double buffered
 constexpr int SM_G = SM_X + 2 * 4 * CHUNK_B;   // 2 chunks = 4 KB (chunk 1 stays zero)
 constexpr int SM_IMG = SM_G + 2 * CHUNK_B;     // weight image (adam.cuh)
@@ -39,9 +42,12 @@ constexpr int SM_W2 = SM_IMG + opt::IMG_W2 * 2;
 constexpr int SM_W3 = SM_IMG + opt::IMG_W3 * 2;
 constexpr int SM_B2I = SM_IMG + opt::IMG_B2 * 2;
 constexpr int SM_B3I = SM_IMG + opt::IMG_B3 * 2;
-constexpr int SM_RED = SM_IMG + opt::IMG_BYTES;  // 4 warps x 12 floats + 4 x 3 doubles
-constexpr int SM_BAR = SM_RED + 384;             // 2 mbarriers + tmem base + flag
-constexpr int SM_TOTAL = SM_BAR + 64;
+constexpr int SM_RED = SM_IMG + opt::IMG_BYTES;  // 4 warps x 8 floats + 4 x 3 doubles
+constexpr int SM_BAR = SM_RED + 384;             // 2 mbarriers + tmem base
+constexpr int SM_FWD_TOTAL = SM_BAR + 64;        // the forward kernel stops here (~69 KB: three CTAs per SM)
+constexpr int SM_D2 = SM_FWD_TOTAL;              // 16 KB  (backward only)
+constexpr int SM_D1 = SM_D2 + 8 * CHUNK_B;       // 16 KB
+constexpr int SM_TOTAL = SM_D1 + 8 * CHUNK_B;    // ~101 KB: two CTAs per SM
 constexpr int SM_STAGE = SM_H2;                  // flush staging: fp32 copy of the flat gradient (<= 32 KB)
 
 // TMEM columns (fp32 accumulators, 128 lanes)
@@ -113,8 +119,8 @@ __device__ __forceinline__ void tc_epilogue_relu(unsigned char* smem, uint32_t t
     }
 }
 
-// SCR accumulator masked by (activation image at `img` > 0), written back over the same image
-__device__ __forceinline__ void tc_epilogue_mask(unsigned char* smem, uint32_t tmem_lane_base, int img) {
+// SCR accumulator masked by (activation image at `img` > 0) -> fp16 image at `dst`
+__device__ __forceinline__ void tc_epilogue_mask(unsigned char* smem, uint32_t tmem_lane_base, int img, int dst) {
     const __half2 zero = __float2half2_rn(0.f);
 #pragma unroll
     for (int q = 0; q < 2; ++q) {
@@ -122,31 +128,37 @@ __device__ __forceinline__ void tc_epilogue_mask(unsigned char* smem, uint32_t t
         tc::tmem_ld32(tmem_lane_base + TM_SCR + 32 * q, v);
 #pragma unroll
         for (int h = 0; h < 4; ++h) {
-            uint4* cell = reinterpret_cast<uint4*>(smem + img + (4 * q + h) * CHUNK_B + threadIdx.x * 16);
-            const uint4 m = *cell;
+            const int cell = (4 * q + h) * CHUNK_B + threadIdx.x * 16;
+            const uint4 m = *reinterpret_cast<const uint4*>(smem + img + cell);
             const __half2* mh = reinterpret_cast<const __half2*>(&m);
             uint4 w;
             w.x = pack_h2(v[8 * h + 0], v[8 * h + 1]) & __hgt2_mask(mh[0], zero);
             w.y = pack_h2(v[8 * h + 2], v[8 * h + 3]) & __hgt2_mask(mh[1], zero);
             w.z = pack_h2(v[8 * h + 4], v[8 * h + 5]) & __hgt2_mask(mh[2], zero);
             w.w = pack_h2(v[8 * h + 6], v[8 * h + 7]) & __hgt2_mask(mh[3], zero);
-            *cell = w;
+            *reinterpret_cast<uint4*>(smem + dst + cell) = w;
         }
     }
 }
 
-// descriptor helpers for the four operand views (fp16, 8 features per chunk)
-__device__ __forceinline__ uint64_t desc_act_k(uint32_t base, int kstep) {  // rows x features, K = features
-    return tc::make_desc(base + kstep * 2 * CHUNK_B, CHUNK_B, 128);
+// descriptor helpers for the four operand views (fp16, 8 features per chunk).  sb4 = (CTA smem base) >> 4; every
+// offset is a compile-time constant, so each descriptor costs one integer add at run time.
+__device__ __forceinline__ uint64_t desc_at(uint32_t sb4, uint32_t off_bytes, uint32_t lbo, uint32_t sbo) {
+    const uint32_t lo = sb4 + ((off_bytes >> 4) + ((lbo >> 4) << 16));  // start address field cannot carry: smem < 256 KB
+    const uint32_t hi = (sbo >> 4) | (1u << 14);                        // descriptor version bit 46
+    return ((uint64_t)hi << 32) | lo;
 }
-__device__ __forceinline__ uint64_t desc_act_mn(uint32_t base, int kstep) {  // features x rows, K = rows
-    return tc::make_desc(base + kstep * 256, 128, CHUNK_B);
+__device__ __forceinline__ uint64_t desc_act_k(uint32_t sb4, int off, int kstep) {  // rows x features, K = features
+    return desc_at(sb4, off + kstep * 2 * CHUNK_B, CHUNK_B, 128);
 }
-__device__ __forceinline__ uint64_t desc_w_k(uint32_t base, int n_out, int kstep) {  // N = out, K = in
-    return tc::make_desc(base + kstep * 2 * n_out * 16, n_out * 16, 128);
+__device__ __forceinline__ uint64_t desc_act_mn(uint32_t sb4, int off, int kstep) {  // features x rows, K = rows
+    return desc_at(sb4, off + kstep * 256, 128, CHUNK_B);
 }
-__device__ __forceinline__ uint64_t desc_w_mn(uint32_t base, int n_out, int kstep) {  // N = in, K = out
-    return tc::make_desc(base + kstep * 256, 128, n_out * 16);
+__device__ __forceinline__ uint64_t desc_w_k(uint32_t sb4, int off, int n_out, int kstep) {  // N = out, K = in
+    return desc_at(sb4, off + kstep * 2 * n_out * 16, n_out * 16, 128);
+}
+__device__ __forceinline__ uint64_t desc_w_mn(uint32_t sb4, int off, int n_out, int kstep) {  // N = in, K = out
+    return desc_at(sb4, off + kstep * 256, 128, n_out * 16);
 }
 
 // publish generic-proxy smem writes + TMEM reads to the MMA-issuing thread
@@ -172,9 +184,16 @@ struct TcFwdArgs {
     float* entropy;
 };
 
+#ifdef TSM_TC_TRACE
+__device__ long long g_trace[4][64];
+#define TRACE(row, slot) do { if (threadIdx.x == 0 && (row) >= 0) g_trace[row][slot] = clock64(); } while (0)
+#else
+#define TRACE(row, slot) do { } while (0)
+#endif
+
 struct TcSetup {
     uint64_t* bar;   // bar[0]: waited phases; bar[1]: the unwaited weight-gradient commits of the backward
-    uint32_t tmem, lane_base, sbase, phase;
+    uint32_t tmem, lane_base, sbase, phase;  // sbase: CTA smem base >> 4
 };
 
 // part A: nothing here depends on the parameters (runs ahead of pdl_wait())
@@ -206,7 +225,7 @@ __device__ __forceinline__ TcSetup tc_setup_finish(unsigned char* smem, const un
     tc_sync_for_mma();
     s.tmem = *tmem_s;
     s.lane_base = s.tmem + ((uint32_t)(warp * 32) << 16);
-    s.sbase = tc::smem_u32(smem);
+    s.sbase = tc::smem_u32(smem) >> 4;  // descriptor units
     s.phase = 0;
     return s;
 }
@@ -218,37 +237,49 @@ __device__ __forceinline__ void tc_wait(TcSetup& s) {
 }
 
 // [X|1] -> H1 -> H2 -> OUT for the tile in the X image at xoff; leaves OUT in TMEM (waited)
-__device__ __forceinline__ void tc_forward_tile(unsigned char* smem, TcSetup& s, int xoff) {
+__device__ __forceinline__ void tc_forward_tile(unsigned char* smem, TcSetup& s, int xoff, int trow = -1) {
     constexpr uint32_t ID64 = tc::make_idesc_f16(128, 64, 0, 0, 0, 0);
     constexpr uint32_t ID16 = tc::make_idesc_f16(128, 16, 0, 0, 0, 0);
+    TRACE(trow, 1);
     tc_sync_for_mma();
+    TRACE(trow, 2);
     if (threadIdx.x == 0) {
 #pragma unroll
         for (int ks = 0; ks < TC_XF / 16; ++ks)
-            tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase + xoff, ks), desc_w_k(s.sbase + SM_W1, TC_H, ks), ID64, ks > 0);
+            tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase, xoff, ks), desc_w_k(s.sbase, SM_W1, TC_H, ks), ID64, ks > 0);
         tc::commit(s.bar);
     }
+    TRACE(trow, 3);
     tc_wait(s);
+    TRACE(trow, 4);
     tc_epilogue_relu(smem, s.lane_base, SM_H1);
+    TRACE(trow, 5);
     tc_sync_for_mma();
+    TRACE(trow, 6);
     if (threadIdx.x == 0) {
 #pragma unroll
         for (int ks = 0; ks < TC_H / 16; ++ks)
-            tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase + SM_H1, ks), desc_w_k(s.sbase + SM_W2, TC_H, ks), ID64, ks > 0);
-        tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase + xoff, 1), desc_w_k(s.sbase + SM_B2I, TC_H, 0), ID64, 1);  // + b2
+            tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase, SM_H1, ks), desc_w_k(s.sbase, SM_W2, TC_H, ks), ID64, ks > 0);
+        tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase, xoff, 1), desc_w_k(s.sbase, SM_B2I, TC_H, 0), ID64, 1);  // + b2
         tc::commit(s.bar);
     }
+    TRACE(trow, 7);
     tc_wait(s);
+    TRACE(trow, 8);
     tc_epilogue_relu(smem, s.lane_base, SM_H2);
+    TRACE(trow, 9);
     tc_sync_for_mma();
+    TRACE(trow, 10);
     if (threadIdx.x == 0) {
 #pragma unroll
         for (int ks = 0; ks < TC_H / 16; ++ks)
-            tc::mma_f16(s.tmem + TM_OUT, desc_act_k(s.sbase + SM_H2, ks), desc_w_k(s.sbase + SM_W3, TC_OF, ks), ID16, ks > 0);
-        tc::mma_f16(s.tmem + TM_OUT, desc_act_k(s.sbase + xoff, 1), desc_w_k(s.sbase + SM_B3I, TC_OF, 0), ID16, 1);  // + b3
+            tc::mma_f16(s.tmem + TM_OUT, desc_act_k(s.sbase, SM_H2, ks), desc_w_k(s.sbase, SM_W3, TC_OF, ks), ID16, ks > 0);
+        tc::mma_f16(s.tmem + TM_OUT, desc_act_k(s.sbase, xoff, 1), desc_w_k(s.sbase, SM_B3I, TC_OF, 0), ID16, 1);  // + b3
         tc::commit(s.bar);
     }
+    TRACE(trow, 11);
     tc_wait(s);
+    TRACE(trow, 12);
 }
 
 __device__ __forceinline__ void tc_read_out(const TcSetup& s, float (&z)[OUTP]) {
@@ -303,7 +334,7 @@ __global__ void __launch_bounds__(TC_THREADS) tc_forward_kernel(TcFwdArgs a) {
                         if (j < a.out_dim) a.out[dst * a.out_dim + j] = z[j];
                 }
             } else {
-                const Soft sm = softmax_row(z, a.n_act);
+                const Soft sm = softmax_row<true>(z, a.n_act);
                 int act = 0;
                 if (a.mode == 1) {
                     const Philox4 rnd = philox4x32((uint32_t)dst, (uint32_t)((uint64_t)dst >> 32), (uint32_t)a.counter,
@@ -414,6 +445,7 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
     float gb3[OUTP];
 #pragma unroll
     for (int j = 0; j < OUTP; ++j) gb3[j] = 0.f;
+    float f_clip = 0.f, f_vf = 0.f, f_ent = 0.f;  // per-thread partial sums of up to 16 tiles, then folded into doubles
     double l_clip = 0.0, l_vf = 0.0, l_ent = 0.0;
 
     float xr[TC_XF];
@@ -430,9 +462,11 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
         const bool valid = nvalid;
         const RowData d = nd;
         const int xoff = SM_X + (int)(it & 1) * 4 * CHUNK_B;
+        const int trow = (it < 2 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) ? (blockIdx.x != 0) * 2 + (int)it : -1;
+        TRACE(trow, 0);
         tc_store_x(smem, xoff, xr);
         if (tile + gridDim.x < n_tiles) tc_prefetch_row(a, tile + gridDim.x, r, nvalid, xr, nd);
-        tc_forward_tile(smem, s, xoff);  // its first wait also covers the previous tile's weight-gradient GEMMs
+        tc_forward_tile(smem, s, xoff, trow);  // its first wait also covers the previous tile's weight-gradient GEMMs
         // ---- loss and G = S * d(loss)/d(OUT) for this thread's row ----
         float z[OUTP], dz[OUTP];
         tc_read_out(s, z);
@@ -441,12 +475,16 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
 #pragma unroll
             for (int j = 0; j < OUTP; ++j) dz[j] = z[j] * inv_n;
         } else {
-            rl = row_loss(z, a.n_act, a.value_index, d.act, d.adv, d.ret, d.logp_old, d.v_old, mean, rstd, a.cfg, inv_n, dz);
+            rl = row_loss<true>(z, a.n_act, a.value_index, d.act, d.adv, d.ret, d.logp_old, d.v_old, mean, rstd, a.cfg, inv_n, dz);
         }
         if (valid) {
-            l_clip += (double)rl.clip;
-            l_vf += (double)rl.vf;
-            l_ent += (double)rl.ent;
+            f_clip += rl.clip;
+            f_vf += rl.vf;
+            f_ent += rl.ent;
+        }
+        if ((it & 15) == 15) {
+            l_clip += (double)f_clip; l_vf += (double)f_vf; l_ent += (double)f_ent;
+            f_clip = f_vf = f_ent = 0.f;
         }
         {
             float g[OUTP];
@@ -465,35 +503,48 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
             if (threadIdx.x == 0) tc::commit(s.bar + 1);
             continue;
         }
+        TRACE(trow, 13);
         tc_sync_for_mma();
+        TRACE(trow, 14);
         if (threadIdx.x == 0) {
-#pragma unroll
-            for (int ks = 0; ks < TC_ROWS / 16; ++ks)  // [dW3^T; .] += [H2; H1]^T G
-                tc::mma_f16(s.tmem + TM_GW3, desc_act_mn(s.sbase + SM_H2, ks), desc_act_mn(s.sbase + SM_G, ks), ID_G16, (it | ks) > 0);
-            tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase + SM_G, 0), desc_w_mn(s.sbase + SM_W3, TC_OF, 0), ID_DH, 0);  // DH2 = G W3
+            tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase, SM_G, 0), desc_w_mn(s.sbase, SM_W3, TC_OF, 0), ID_DH, 0);  // DH2 = G W3
             tc::commit(s.bar);
         }
+        TRACE(trow, 15);
         tc_wait(s);
-        tc_epilogue_mask(smem, s.lane_base, SM_H2);  // D2 over H2 (the dW3 GEMM has completed)
+        TRACE(trow, 16);
+        tc_epilogue_mask(smem, s.lane_base, SM_H2, SM_D2);
+        TRACE(trow, 17);
         tc_sync_for_mma();
+        TRACE(trow, 18);
         if (threadIdx.x == 0) {
-#pragma unroll
-            for (int ks = 0; ks < TC_ROWS / 16; ++ks)  // [dW2; .] += [D2; H1]^T H1
-                tc::mma_f16(s.tmem + TM_GW2, desc_act_mn(s.sbase + SM_H2, ks), desc_act_mn(s.sbase + SM_H1, ks), ID_G64, (it | ks) > 0);
 #pragma unroll
             for (int ks = 0; ks < TC_H / 16; ++ks)  // DH1 = D2 W2
-                tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase + SM_H2, ks), desc_w_mn(s.sbase + SM_W2, TC_H, ks), ID_DH, ks > 0);
+                tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase, SM_D2, ks), desc_w_mn(s.sbase, SM_W2, TC_H, ks), ID_DH, ks > 0);
             tc::commit(s.bar);
         }
+        TRACE(trow, 19);
         tc_wait(s);
-        tc_epilogue_mask(smem, s.lane_base, SM_H1);  // D1 over H1 (the dW2 GEMM has completed)
+        TRACE(trow, 20);
+        tc_epilogue_mask(smem, s.lane_base, SM_H1, SM_D1);
+        TRACE(trow, 21);
         tc_sync_for_mma();
+        TRACE(trow, 22);
         if (threadIdx.x == 0) {
+            // the weight-gradient GEMMs: off the critical path, completion tracked by bar[1] only
+            const uint32_t acc0 = it > 0;
+#pragma unroll
+            for (int ks = 0; ks < TC_ROWS / 16; ++ks)  // [dW3^T; .] += [H2; H1]^T G
+                tc::mma_f16(s.tmem + TM_GW3, desc_act_mn(s.sbase, SM_H2, ks), desc_act_mn(s.sbase, SM_G, ks), ID_G16, ks > 0 ? 1u : acc0);
+#pragma unroll
+            for (int ks = 0; ks < TC_ROWS / 16; ++ks)  // [dW2; .] += [D2; D1]^T H1
+                tc::mma_f16(s.tmem + TM_GW2, desc_act_mn(s.sbase, SM_D2, ks), desc_act_mn(s.sbase, SM_H1, ks), ID_G64, ks > 0 ? 1u : acc0);
 #pragma unroll
             for (int ks = 0; ks < TC_ROWS / 16; ++ks)  // [. | db2; dW1 | db1] += [D2; D1]^T [X | 1]
-                tc::mma_f16(s.tmem + TM_GW1, desc_act_mn(s.sbase + SM_H2, ks), desc_act_mn(s.sbase + xoff, ks), ID_G32, (it | ks) > 0);
-            tc::commit(s.bar + 1);  // not waited here: X is double buffered and H1 / H2 are next written after a wait
+                tc::mma_f16(s.tmem + TM_GW1, desc_act_mn(s.sbase, SM_D2, ks), desc_act_mn(s.sbase, xoff, ks), ID_G32, ks > 0 ? 1u : acc0);
+            tc::commit(s.bar + 1);  // not waited here: the next tile's first wait covers it (in-order completion); X is double buffered
         }
+        TRACE(trow, 23);
     }
     const Offsets o = offsets(a.in_dim, TC_H, a.out_dim);
     const float inv_s = a.inv_gscale;
@@ -529,6 +580,7 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
         }
     }
     // db3 and the loss sums: warp shuffle, then shared memory
+    l_clip += (double)f_clip; l_vf += (double)f_vf; l_ent += (double)f_ent;
     float* red_f = reinterpret_cast<float*>(smem + SM_RED);
     double* red_d = reinterpret_cast<double*>(smem + SM_RED + 192);
 #pragma unroll

@@ -52,6 +52,13 @@ struct Soft {
     float p[OUTP];
     float ent;
 };
+// FAST: hardware exp2 / log2 / reciprocal approximations (about 2 ulp), used by the tcgen05 engine whose
+// GEMM operands are already rounded to fp16; the fp32 engine keeps the IEEE library versions.
+template <bool FAST> __device__ __forceinline__ float exp_t(float x) { return FAST ? __expf(x) : expf(x); }
+template <bool FAST> __device__ __forceinline__ float log_t(float x) { return FAST ? __logf(x) : logf(x); }
+template <bool FAST> __device__ __forceinline__ float div_t(float a, float b) { return FAST ? __fdividef(a, b) : a / b; }
+
+template <bool FAST = false>
 __device__ __forceinline__ Soft softmax_row(const float* z, int n_act) {
     Soft s;
     float m = -INFINITY;
@@ -61,15 +68,16 @@ __device__ __forceinline__ Soft softmax_row(const float* z, int n_act) {
     float sum = 0.f;
 #pragma unroll
     for (int j = 0; j < OUTP; ++j) {
-        s.p[j] = j < n_act ? expf(z[j] - m) : 0.f;
+        s.p[j] = j < n_act ? exp_t<FAST>(z[j] - m) : 0.f;
         sum += s.p[j];
     }
-    const float lse = logf(sum);
+    const float lse = log_t<FAST>(sum);
+    const float inv_sum = div_t<FAST>(1.f, sum);
     s.ent = 0.f;
 #pragma unroll
     for (int j = 0; j < OUTP; ++j) {
         s.logp[j] = j < n_act ? (z[j] - m) - lse : 0.f;
-        s.p[j] = j < n_act ? s.p[j] / sum : 0.f;
+        s.p[j] = j < n_act ? (FAST ? s.p[j] * inv_sum : s.p[j] / sum) : 0.f;
         if (j < n_act) s.ent -= s.p[j] * s.logp[j];
     }
     return s;
@@ -85,6 +93,7 @@ struct PpoCfg {
 struct RowLoss {
     float clip, vf, ent;
 };
+template <bool FAST = false>
 __device__ __forceinline__ RowLoss row_loss(const float (&z)[OUTP], int n_act, int value_index, int act, float adv, float ret,
                                             float logp_old, float v_old, float mean, float rstd, const PpoCfg& cfg, float inv_n,
                                             float (&dz)[OUTP]) {
@@ -92,14 +101,14 @@ __device__ __forceinline__ RowLoss row_loss(const float (&z)[OUTP], int n_act, i
 #pragma unroll
     for (int j = 0; j < OUTP; ++j) dz[j] = 0.f;
     if (n_act > 0) {
-        const Soft sm = softmax_row(z, n_act);
+        const Soft sm = softmax_row<FAST>(z, n_act);
         float lp = 0.f;
 #pragma unroll
         for (int j = 0; j < OUTP; ++j)
             if (j == act) lp = sm.logp[j];
         float advn = adv;
         if (cfg.adv_norm) advn = (advn - mean) * rstd;
-        const float ratio = expf(lp - logp_old);
+        const float ratio = exp_t<FAST>(lp - logp_old);
         const float lo = 1.f - cfg.eps_clip, hi = 1.f + cfg.eps_clip;
         const float s1 = ratio * advn, s2 = fminf(fmaxf(ratio, lo), hi) * advn;
         const bool inside = ratio >= lo && ratio <= hi;
