@@ -294,7 +294,15 @@ typedef struct tsm_ppo_batch {
     int64_t size, n_rows, start, len;
     uint64_t perm_key;
     int64_t perm_n;
+    const void* records;     /* engine 1: [size][n_rows] packed rows built by tsm_ppo_pack_records (required by engine 1's
+                                tsm_ppo_minibatch / tsm_ppo_epoch; ignored by engine 0) */
 } tsm_ppo_batch;
+
+/* Engine 1 gathers each minibatch row as ONE 96-byte record (3 sectors, one page) instead of 7-8 sectors spread over
+ * five arrays: halves x[32] (obs as fp16, zero padded, x[31] = 1) | float adv, ret, logp_old | int32 act | float v_old |
+ * 12 bytes pad.  Packs every slot of the buffer ([size][n_rows], storage order); NULL source arrays pack as zeros. */
+#define TSM_PPO_RECORD_BYTES 96
+int tsm_ppo_pack_records(const tsm_net* net, const tsm_ppo_batch* batch, void* records, tsm_stream_t stream);
 
 typedef struct tsm_ppo_cfg {
     float eps_clip;   /* ppo.py:25 (0.2) */

@@ -91,7 +91,10 @@ def test_ppo_minibatch_tc_vs_fp32(O, n):
     key = 0xABCDEF1234567
     for cfgk in (dict(adv_norm=1), dict(adv_norm=0, value_clip=1, dual_clip=2.0, eps_clip=0.1)):
         pb = _lib.TsmPpoBatch(obs=P(t["obs"]), act=P(t["act"]), adv=P(t["adv"]), ret=P(t["ret"]), logp_old=P(t["lp"]), v_old=P(t["vo"]),
-                              indices=None, size=1, n_rows=n, start=0, len=1, perm_key=key, perm_n=n)
+                              indices=None, size=1, n_rows=n, start=0, len=1, perm_key=key, perm_n=n, records=None)
+        rec = torch.empty(n, _lib.PPO_RECORD_BYTES, dtype=torch.uint8, device="cuda")
+        _lib.check(_lib.lib().tsm_ppo_pack_records(net.desc, C.byref(pb), P(rec), _lib.stream_ptr()))
+        pb.records = P(rec)
         pc = _lib.TsmPpoCfg(eps_clip=cfgk.get("eps_clip", 0.2), dual_clip=cfgk.get("dual_clip", 0.0), vf_coef=0.5, ent_coef=0.01,
                             value_clip=cfgk.get("value_clip", 0), adv_norm=cfgk["adv_norm"])
         stats = d(np.array([float(t["adv"].mean()), 1.0 / (float(t["adv"].std()) + 1e-8)]))
@@ -114,6 +117,55 @@ def test_ppo_minibatch_tc_vs_fp32(O, n):
             assert err < (0.03 if n >= 3000 else 0.12) * scale + 1e-7, (name, err, scale, cfgk)
         assert np.allclose(res["tc"][1][:3] / n, res["fp32"][1][:3] / n, rtol=5e-3, atol=2e-3)
     net.engine = "fp32"
+
+
+def test_pack_records_bit_exact():
+    """tsm_ppo_pack_records: 96-byte rows = fp16(obs) zero padded with x[31] = 1 | adv ret logp_old | act | v_old | pad."""
+    from tianshou_marl_b200 import _lib
+    from tianshou_marl_b200.utils import ActorCriticNet
+
+    rng = np.random.default_rng(5)
+    for O, size, R in ((18, 3, 37), (7, 2, 5), (31, 1, 130)):
+        n = size * R
+        net = ActorCriticNet(O, 64, 5, seed=1)
+        obs = rng.normal(size=(n, O)).astype(np.float32) * 3
+        act = rng.integers(0, 5, n).astype(np.int32)
+        adv, ret, lp, vo = (rng.normal(size=n).astype(np.float32) for _ in range(4))
+        d = lambda a: torch.as_tensor(a, device="cuda").contiguous()  # noqa: E731
+        t = [d(x) for x in (obs, act, adv, ret, lp, vo)]
+        P = _lib.ptr
+        for with_vo in (True, False):
+            pb = _lib.TsmPpoBatch(obs=P(t[0]), act=P(t[1]), adv=P(t[2]), ret=P(t[3]), logp_old=P(t[4]), v_old=P(t[5]) if with_vo else None,
+                                  indices=None, size=size, n_rows=R, start=0, len=size, perm_key=0, perm_n=0, records=None)
+            rec = torch.full((n, _lib.PPO_RECORD_BYTES), 0xAB, dtype=torch.uint8, device="cuda")
+            _lib.check(_lib.lib().tsm_ppo_pack_records(net.desc, C.byref(pb), P(rec), _lib.stream_ptr()))
+            h = rec.cpu().numpy()
+            x = h[:, :64].copy().view(np.float16)
+            want = np.zeros((n, 32), np.float16)
+            want[:, :O] = obs.astype(np.float16)
+            want[:, 31] = 1.0
+            assert np.array_equal(x.view(np.uint16), want.view(np.uint16))
+            sc = h[:, 64:80].copy().view(np.float32)
+            assert np.array_equal(sc[:, 0], adv) and np.array_equal(sc[:, 1], ret) and np.array_equal(sc[:, 2], lp)
+            assert np.array_equal(h[:, 76:80].copy().view(np.int32)[:, 0], act)
+            assert np.array_equal(h[:, 80:84].copy().view(np.float32)[:, 0], vo if with_vo else np.zeros(n, np.float32))
+            assert not h[:, 84:].any()
+
+
+def test_minibatch_tc_needs_records():
+    from tianshou_marl_b200 import _lib
+    from tianshou_marl_b200.utils import ActorCriticNet
+
+    net = ActorCriticNet(18, 64, 5, seed=1, engine="tc")
+    x = torch.zeros(128, 18, device="cuda")
+    z = torch.zeros(128, device="cuda")
+    a = torch.zeros(128, dtype=torch.int32, device="cuda")
+    P = _lib.ptr
+    pb = _lib.TsmPpoBatch(obs=P(x), act=P(a), adv=P(z), ret=P(z), logp_old=P(z), v_old=None, indices=None, size=1, n_rows=128, start=0,
+                          len=1, perm_key=0, perm_n=0, records=None)
+    pc = _lib.TsmPpoCfg(eps_clip=0.2, dual_clip=0.0, vf_coef=0.5, ent_coef=0.01, value_clip=0, adv_norm=0)
+    with pytest.raises(ValueError):
+        _lib.check(_lib.lib().tsm_ppo_minibatch(net.desc, C.byref(pb), C.byref(pc), 0, 128, None, None, _lib.stream_ptr()))
 
 
 def test_update_tc_tracks_fp32():

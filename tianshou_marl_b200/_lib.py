@@ -43,6 +43,7 @@ class TsmMpe(C.Structure):
 
 
 TC_IMAGE_BYTES = 17024  # TSM_TC_IMAGE_BYTES
+PPO_RECORD_BYTES = 96  # TSM_PPO_RECORD_BYTES
 
 
 class TsmNet(C.Structure):
@@ -62,6 +63,7 @@ class TsmPpoBatch(C.Structure):
     _fields_ = [
         ("obs", c_vp), ("act", c_vp), ("adv", c_vp), ("ret", c_vp), ("logp_old", c_vp), ("v_old", c_vp), ("indices", c_vp),
         ("size", c_i64), ("n_rows", c_i64), ("start", c_i64), ("len", c_i64), ("perm_key", C.c_uint64), ("perm_n", c_i64),
+        ("records", c_vp),
     ]
 
 
@@ -96,6 +98,7 @@ _SIGS = {
     "tsm_random_actions": (c_i32, [c_vp, c_i64, c_i32, C.c_uint64, C.c_uint64, c_vp]),
     "tsm_net_param_count": (c_i64, [c_i32, c_i32, c_i32]),
     "tsm_net_pack": (c_i32, [c_vp, c_vp]),
+    "tsm_ppo_pack_records": (c_i32, [c_vp, c_vp, c_vp, c_vp]),
     "tsm_net_forward": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_u64, c_u64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "tsm_ppo_adv_stats": (c_i32, [c_vp, c_vp, c_i64, c_f32, c_vp, c_vp]),
     "tsm_ppo_minibatch": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i64, c_vp, c_vp, c_vp]),

@@ -237,7 +237,13 @@ class PPO:
         sums = self._buf("loss_sums", (repeat * n_mb, 4), torch.float64)
         sums.zero_()
         pb = _lib.TsmPpoBatch(obs=P(st["obs"]), act=P(st["act"]), adv=P(adv), ret=P(ret), logp_old=P(logp), v_old=P(v_s),
-                              indices=None, size=size, n_rows=R, start=start, len=lock_len, perm_key=0, perm_n=0)
+                              indices=None, size=size, n_rows=R, start=start, len=lock_len, perm_key=0, perm_n=0, records=None)
+        if net.engine == "tc":  # one 96-byte record per stored row: the minibatch kernels gather 3 sectors / 1 page per row
+            tk = _lib.t_start("pack_records")
+            rec = self._buf("records", (size * R, _lib.PPO_RECORD_BYTES), torch.uint8)
+            _lib.check(L.tsm_ppo_pack_records(net.desc, C.byref(pb), P(rec), S))
+            pb.records = P(rec)
+            _lib.t_stop(tk)
         world = torch.distributed.get_world_size() if torch.distributed.is_available() and torch.distributed.is_initialized() else 1
         o = self.optim
         mgn = float(self.max_grad_norm) if self.max_grad_norm else 0.0

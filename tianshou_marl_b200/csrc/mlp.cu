@@ -786,12 +786,12 @@ extern "C" int tsm_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch,
     TSM_REQUIRE(net->grads != nullptr, "net.grads != NULL");
     TSM_REQUIRE(mb_start >= 0 && mb_len >= 0, "mb_start, mb_len >= 0");
     if (mb_len == 0) return TSM_OK;
+    TSM_REQUIRE(!cfg->adv_norm || mb_stats, "advantage normalisation needs mb_stats");
+    if (net->engine == 1) return tc_ppo_minibatch(net, batch, cfg, mb_start, mb_len, mb_stats, loss_sums, 0, as_stream(stream));
     TSM_REQUIRE(batch->obs != nullptr, "batch.obs != NULL");
     TSM_REQUIRE(net->n_act == 0 || (batch->act && batch->adv && batch->logp_old), "policy loss needs act / adv / logp_old");
     TSM_REQUIRE(net->value_index < 0 || batch->ret, "value loss needs ret");
     TSM_REQUIRE(!cfg->value_clip || batch->v_old, "value_clip needs v_old");
-    TSM_REQUIRE(!cfg->adv_norm || mb_stats, "advantage normalisation needs mb_stats");
-    if (net->engine == 1) return tc_ppo_minibatch(net, batch, cfg, mb_start, mb_len, mb_stats, loss_sums, 0, as_stream(stream));
     PpoArgs a{};
     a.params = net->params; a.grads = net->grads;
     a.obs = batch->obs; a.act = batch->act; a.adv = batch->adv; a.ret = batch->ret; a.logp_old = batch->logp_old; a.v_old = batch->v_old;
@@ -860,10 +860,7 @@ extern "C" int tsm_ppo_epoch(const tsm_net* net, const tsm_ppo_batch* batch, con
             if (rc) return rc;
             rc = check_batch(batch, __func__);
             if (rc) return rc;
-            TSM_REQUIRE(cfg && net->grads && net->adam_m && net->adam_v && net->adam_step && batch->obs, "cfg / grads / adam state / obs != NULL");
-            TSM_REQUIRE(net->n_act == 0 || (batch->act && batch->adv && batch->logp_old), "policy loss needs act / adv / logp_old");
-            TSM_REQUIRE(net->value_index < 0 || batch->ret, "value loss needs ret");
-            TSM_REQUIRE(!cfg->value_clip || batch->v_old, "value_clip needs v_old");
+            TSM_REQUIRE(cfg && net->grads && net->adam_m && net->adam_v && net->adam_step, "cfg / grads / adam state != NULL");
             TSM_REQUIRE(!cfg->adv_norm || st, "advantage normalisation needs mb_stats");
             rc = tc_ppo_minibatch(net, batch, cfg, s0, len, st, ls, m > 0, as_stream(stream));
             if (rc) return rc;

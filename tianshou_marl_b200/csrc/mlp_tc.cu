@@ -94,6 +94,65 @@ extern "C" int tsm_tc_selftest(const float* a_img, int a_floats, const float* b_
 }
 
 // ---------------------------------------------------------------------------------------------
+// batch records (include/tsm_b200.h: TSM_PPO_RECORD_BYTES): one thread per storage slot, streaming
+namespace tsm {
+namespace mlptc {
+__global__ void __launch_bounds__(256) pack_records_kernel(const float* __restrict__ obs, const int32_t* __restrict__ act,
+                                                          const float* __restrict__ adv, const float* __restrict__ ret,
+                                                          const float* __restrict__ logp_old, const float* __restrict__ v_old,
+                                                          int64_t n_slots, int in_dim, uint4* __restrict__ records) {
+    const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_slots) return;
+    float x[TC_XF];
+#pragma unroll
+    for (int k = 0; k < TC_XF; ++k) x[k] = 0.f;
+    const float* p = obs + s * in_dim;
+    if ((in_dim & 1) == 0 && (reinterpret_cast<uintptr_t>(p) & 7) == 0) {
+#pragma unroll
+        for (int k = 0; k < TC_XF / 2; ++k)
+            if (2 * k < in_dim) {
+                const float2 v = __ldcs(reinterpret_cast<const float2*>(p + 2 * k));
+                x[2 * k] = v.x;
+                x[2 * k + 1] = v.y;
+            }
+    } else {
+#pragma unroll
+        for (int k = 0; k < TC_XF; ++k)
+            if (k < in_dim) x[k] = __ldcs(p + k);
+    }
+    x[TC_XF - 1] = 1.0f;
+    uint4* out = records + s * (REC_BYTES / 16);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        uint4 v;
+        v.x = pack_h2(x[8 * c + 0], x[8 * c + 1]); v.y = pack_h2(x[8 * c + 2], x[8 * c + 3]);
+        v.z = pack_h2(x[8 * c + 4], x[8 * c + 5]); v.w = pack_h2(x[8 * c + 6], x[8 * c + 7]);
+        out[c] = v;
+    }
+    uint4 sc;
+    sc.x = __float_as_uint(adv ? adv[s] : 0.f);
+    sc.y = __float_as_uint(ret ? ret[s] : 0.f);
+    sc.z = __float_as_uint(logp_old ? logp_old[s] : 0.f);
+    sc.w = (uint32_t)(act ? act[s] : 0);
+    out[4] = sc;
+    out[5] = make_uint4(__float_as_uint(v_old ? v_old[s] : 0.f), 0, 0, 0);
+}
+}  // namespace mlptc
+}  // namespace tsm
+
+extern "C" int tsm_ppo_pack_records(const tsm_net* net, const tsm_ppo_batch* batch, void* records, tsm_stream_t stream) {
+    TSM_REQUIRE(net && batch && records, "net / batch / records != NULL");
+    TSM_REQUIRE(net->in_dim >= 1 && net->in_dim <= 31, "1 <= in_dim <= 31");
+    TSM_REQUIRE(batch->obs != nullptr && batch->size > 0 && batch->n_rows > 0, "batch.obs / size / n_rows");
+    TSM_REQUIRE((reinterpret_cast<uintptr_t>(records) & 15) == 0, "records must be 16-byte aligned");
+    const int64_t n = batch->size * batch->n_rows;
+    mlptc::pack_records_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, as_stream(stream)>>>(
+        batch->obs, batch->act, batch->adv, batch->ret, batch->logp_old, batch->v_old, n, net->in_dim, reinterpret_cast<uint4*>(records));
+    TSM_LAUNCH_CHECK();
+    return TSM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // engine 1 entry points (called from the dispatchers in mlp.cu)
 namespace tsm {
 
@@ -131,7 +190,8 @@ int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_p
     if (rc) return rc;
     mlptc::TcPpoArgs a{};
     a.image = reinterpret_cast<const unsigned char*>(net->tc_image); a.grads = net->grads;
-    a.obs = batch->obs; a.act = batch->act; a.adv = batch->adv; a.ret = batch->ret; a.logp_old = batch->logp_old; a.v_old = batch->v_old;
+    if (!batch->records) return fail(TSM_ERR_INVALID, "%s: engine 1 needs batch.records (tsm_ppo_pack_records)", __func__);
+    a.records = reinterpret_cast<const unsigned char*>(batch->records);
     a.view.indices = batch->indices; a.view.size = batch->size; a.view.n_rows = batch->n_rows; a.view.start = batch->start;
     a.view.len = batch->len; a.view.perm_key = batch->perm_key; a.view.perm_n = batch->perm_n;
     a.mb_start = mb_start; a.mb_len = mb_len; a.mb_stats = mb_stats;

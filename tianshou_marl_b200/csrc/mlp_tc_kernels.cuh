@@ -382,12 +382,7 @@ __global__ void __launch_bounds__(TC_THREADS) tc_forward_kernel(TcFwdArgs a) {
 struct TcPpoArgs {
     const unsigned char* image;
     float* grads;
-    const float* obs;
-    const int32_t* act;
-    const float* adv;
-    const float* ret;
-    const float* logp_old;
-    const float* v_old;
+    const unsigned char* records;  // [slot] 96-byte packed rows (tsm_ppo_pack_records)
     BatchView view;
     int64_t mb_start, mb_len;
     const float* mb_stats;
@@ -398,27 +393,36 @@ struct TcPpoArgs {
     int debug;  // experiments only (TSM_TC_DEBUG): 1 skip flush, 2 skip backward GEMM phases, 4 skip the loss math
 };
 
-struct RowData {
-    int act;
-    float adv, ret, logp_old, v_old;
+constexpr int REC_BYTES = 96;  // halves x[32] | float adv, ret, logp_old | int32 act | float v_old | 12 bytes pad
+
+// one minibatch row: six 16-byte loads from one record (prefetched a tile ahead, kept in registers)
+struct RowRec {
+    uint4 x[4];   // fp16 input features, already in X-image chunk form
+    uint4 sc;     // adv, ret, logp_old, act
+    float v_old;
 };
 
-__device__ __forceinline__ void tc_prefetch_row(const TcPpoArgs& a, int64_t tile, int r, bool& valid, float (&xr)[TC_XF], RowData& d) {
+__device__ __forceinline__ void tc_prefetch_row(const TcPpoArgs& a, int64_t tile, int r, bool& valid, RowRec& d) {
     const int64_t p = a.mb_start + tile * TC_ROWS + r;
     valid = tile * TC_ROWS + r < a.mb_len;
-    d = RowData{0, 0.f, 0.f, 0.f, 0.f};
-    int64_t slot = 0;
     if (valid) {
-        slot = (a.debug & 8) ? p : slot_of(a.view, p);
-        if (a.n_act > 0) {
-            d.act = __ldg(a.act + slot);
-            d.adv = __ldg(a.adv + slot);
-            d.logp_old = __ldg(a.logp_old + slot);
-        }
-        if (a.value_index >= 0) d.ret = __ldg(a.ret + slot);
-        if (a.cfg.value_clip) d.v_old = __ldg(a.v_old + slot);
+        const int64_t slot = (a.debug & 8) ? p : slot_of(a.view, p);
+        const uint4* rec = reinterpret_cast<const uint4*>(a.records + slot * REC_BYTES);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) d.x[c] = __ldg(rec + c);
+        d.sc = __ldg(rec + 4);
+        d.v_old = __ldg(reinterpret_cast<const float*>(rec + 5));
+    } else {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) d.x[c] = make_uint4(0, 0, 0, 0);
+        d.sc = make_uint4(0, 0, 0, 0);
+        d.v_old = 0.f;
     }
-    tc_load_row(a.obs, slot, a.in_dim, valid, xr);
+}
+
+__device__ __forceinline__ void tc_store_rec(unsigned char* smem, int xoff, const RowRec& d) {
+#pragma unroll
+    for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4*>(smem + xoff + c * CHUNK_B + threadIdx.x * 16) = d.x[c];
 }
 
 // physical position of flat gradient element i inside the staging copy: the W2 block is XOR-swizzled
@@ -448,11 +452,10 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
     float f_clip = 0.f, f_vf = 0.f, f_ent = 0.f;  // per-thread partial sums of up to 16 tiles, then folded into doubles
     double l_clip = 0.0, l_vf = 0.0, l_ent = 0.0;
 
-    float xr[TC_XF];
-    RowData nd;
+    RowRec nd;
     bool nvalid = false;
     int64_t tile = blockIdx.x;
-    if (tile < n_tiles) tc_prefetch_row(a, tile, r, nvalid, xr, nd);  // batch arrays only: safe ahead of the dependency wait
+    if (tile < n_tiles) tc_prefetch_row(a, tile, r, nvalid, nd);  // batch records only: safe ahead of the dependency wait
     pdl_wait();  // parameters (image), gradients and mb_stats of the preceding launches are now visible
     TcSetup s = tc_setup_finish(smem, a.image);
     float mean = 0.f, rstd = 1.f;
@@ -460,12 +463,14 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
     uint32_t it = 0;
     for (; tile < n_tiles; tile += gridDim.x, ++it) {
         const bool valid = nvalid;
-        const RowData d = nd;
         const int xoff = SM_X + (int)(it & 1) * 4 * CHUNK_B;
         const int trow = (it < 2 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) ? (blockIdx.x != 0) * 2 + (int)it : -1;
         TRACE(trow, 0);
-        tc_store_x(smem, xoff, xr);
-        if (tile + gridDim.x < n_tiles) tc_prefetch_row(a, tile + gridDim.x, r, nvalid, xr, nd);
+        tc_store_rec(smem, xoff, nd);
+        const float d_adv = __uint_as_float(nd.sc.x), d_ret = __uint_as_float(nd.sc.y), d_logp_old = __uint_as_float(nd.sc.z);
+        const int d_act = (int)nd.sc.w;
+        const float d_v_old = nd.v_old;
+        if (tile + gridDim.x < n_tiles) tc_prefetch_row(a, tile + gridDim.x, r, nvalid, nd);
         tc_forward_tile(smem, s, xoff, trow);  // its first wait also covers the previous tile's weight-gradient GEMMs
         // ---- loss and G = S * d(loss)/d(OUT) for this thread's row ----
         float z[OUTP], dz[OUTP];
@@ -475,7 +480,7 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
 #pragma unroll
             for (int j = 0; j < OUTP; ++j) dz[j] = z[j] * inv_n;
         } else {
-            rl = row_loss<true>(z, a.n_act, a.value_index, d.act, d.adv, d.ret, d.logp_old, d.v_old, mean, rstd, a.cfg, inv_n, dz);
+            rl = row_loss<true>(z, a.n_act, a.value_index, d_act, d_adv, d_ret, d_logp_old, d_v_old, mean, rstd, a.cfg, inv_n, dz);
         }
         if (valid) {
             f_clip += rl.clip;

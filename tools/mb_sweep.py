@@ -25,6 +25,9 @@ cfg = _lib.TsmPpoCfg()
 cfg.eps_clip, cfg.dual_clip, cfg.vf_coef, cfg.ent_coef, cfg.value_clip, cfg.adv_norm = 0.2, 0.0, 0.5, 0.01, 0, 0
 st = _lib.stream_ptr()
 desc = net.desc
+rec = torch.empty(T * R, _lib.PPO_RECORD_BYTES, dtype=torch.uint8, device=dev)
+_lib.check(L.tsm_ppo_pack_records(desc, C.byref(b), P(rec), st))
+b.records = P(rec)
 
 
 def timeit(fn, n=200):
@@ -65,7 +68,7 @@ print(f"minibatch only mb=65536: {t:.1f} us")
 t = timeit(lambda: _lib.check(L.tsm_adam_step(desc, 3e-4, 0.9, 0.999, 1e-8, 0.5, 1.0, None, st)))
 print(f"adam only: {t:.1f} us")
 import numpy as np
-bounds = np.arange(0, 65536 * 33, 65536, dtype=np.int64)
+bounds = np.arange(0, 65536 * 33, 65536, dtype=np.int64) + 65536 * 100
 t = timeit(lambda: _lib.check(L.tsm_ppo_epoch(desc, C.byref(b), C.byref(cfg), bounds.ctypes.data_as(C.c_void_p), 32, None, 3e-4, 0.9, 0.999, 1e-8, 0.5, None, st)), n=20)
 print(f"epoch of 32 minibatches: {t/32:.1f} us per minibatch")
 x = obs.view(-1, O)

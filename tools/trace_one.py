@@ -17,6 +17,9 @@ b.size, b.n_rows, b.start, b.len, b.perm_key, b.perm_n = T, R, 0, T, 12345, B
 cfg = _lib.TsmPpoCfg()
 cfg.eps_clip, cfg.dual_clip, cfg.vf_coef, cfg.ent_coef, cfg.value_clip, cfg.adv_norm = 0.2, 0.0, 0.5, 0.01, 0, 0
 st = _lib.stream_ptr(); desc = net.desc
+rec = torch.empty(T * R, _lib.PPO_RECORD_BYTES, dtype=torch.uint8, device=dev)
+_lib.check(L.tsm_ppo_pack_records(desc, C.byref(b), P(rec), st))
+b.records = P(rec)
 mb = int(sys.argv[1]) if len(sys.argv) > 1 else 75776
 for i in range(5):
     if i == 4: os.environ["TSM_TC_TRACE_DUMP"] = "1"
