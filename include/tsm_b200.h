@@ -338,6 +338,40 @@ int tsm_ppo_epoch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_
                   int64_t n_minibatches, const float* mb_stats, float lr, float beta1, float beta2, float eps,
                   float max_grad_norm, double* loss_sums, tsm_stream_t stream);
 
+/* =========================================================================================
+ * The lock-step rollout loop (launches only)
+ * replaces  Collector._collect                   tianshou/data/collector.py:770-1098
+ * for the case where every environment advances every step: n_steps x { tsm_net_forward (mode 1 sample /
+ * 2 argmax; net == NULL: tsm_random_actions over n_random_act actions), tsm_mpe_step with auto-reset,
+ * tsm_buf_add (ring counters, episode return / length), tsm_episode_stats }, each writing straight into the
+ * time-major payload of the device buffer.  obs[slot] must hold the observation to act on.  On return
+ * *slot_out is the next slot, *lockstep_len_out the new number of valid slots and *obs_in_carry_out says
+ * whether the next observation is in `carry` (last step / ring wrap) or already in obs[*slot_out].
+ * ========================================================================================= */
+typedef struct tsm_rollout {
+    float* obs;           /* [size][n_rows][obs_dim] */
+    int32_t* act;         /* [size][n_rows] */
+    float* rew;
+    uint8_t* terminated;
+    uint8_t* truncated;
+    float* obs_next;      /* [size][n_rows][obs_dim] */
+    float* logp;          /* optional [size][n_rows] */
+    float* value;         /* optional */
+    float* carry;         /* [n_rows][obs_dim] */
+    int64_t size, n_rows, obs_dim, slot;
+    double* ep_ret;       /* [n_rows] scratch */
+    int64_t* ep_len;      /* [n_rows] scratch */
+    double* acc;          /* [9] episode statistics accumulator of tsm_episode_stats */
+    double* list_ret;     /* optional per-episode lists */
+    int64_t* list_len;
+    int64_t* list_count;
+    int64_t list_cap;
+} tsm_rollout;
+
+int tsm_collect_lockstep(const tsm_net* net, const tsm_mpe* env, const tsm_buf* buf, const tsm_rollout* ro, int64_t n_steps,
+                         int mode, uint64_t seed, uint64_t counter0, int64_t lockstep_len, int n_random_act,
+                         int64_t* slot_out, int64_t* lockstep_len_out, int* obs_in_carry_out, tsm_stream_t stream);
+
 /* tcgen05 self test (tests only): D[128][n] = A * B with A / B given as shared-memory images
  * (float32 words, copied verbatim to smem) and explicit descriptor fields
  * h_desc = {a_lbo, a_sbo, a_kstep_bytes, b_lbo, b_sbo, b_kstep_bytes}; kind::tf32, M = 128,

@@ -57,6 +57,17 @@ class TsmNet(C.Structure):
     ]
 
 
+class TsmRollout(C.Structure):
+    """struct tsm_rollout (include/tsm_b200.h)."""
+
+    _fields_ = [
+        ("obs", c_vp), ("act", c_vp), ("rew", c_vp), ("terminated", c_vp), ("truncated", c_vp), ("obs_next", c_vp), ("logp", c_vp),
+        ("value", c_vp), ("carry", c_vp), ("size", c_i64), ("n_rows", c_i64), ("obs_dim", c_i64), ("slot", c_i64),
+        ("ep_ret", c_vp), ("ep_len", c_vp), ("acc", c_vp), ("list_ret", c_vp), ("list_len", c_vp), ("list_count", c_vp),
+        ("list_cap", c_i64),
+    ]
+
+
 class TsmPpoBatch(C.Structure):
     """struct tsm_ppo_batch (include/tsm_b200.h)."""
 
@@ -96,6 +107,7 @@ _SIGS = {
     "tsm_mpe_reset": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_vp, c_vp]),
     "tsm_mpe_step": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
     "tsm_random_actions": (c_i32, [c_vp, c_i64, c_i32, C.c_uint64, C.c_uint64, c_vp]),
+    "tsm_collect_lockstep": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, C.c_uint64, C.c_uint64, c_i64, c_i32, c_vp, c_vp, c_vp, c_vp]),
     "tsm_net_param_count": (c_i64, [c_i32, c_i32, c_i32]),
     "tsm_net_pack": (c_i32, [c_vp, c_vp]),
     "tsm_ppo_pack_records": (c_i32, [c_vp, c_vp, c_vp, c_vp]),

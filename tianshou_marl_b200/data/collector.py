@@ -19,6 +19,7 @@ Two code paths, both through libtsm_b200 only:
 from __future__ import annotations
 
 import ctypes as C
+import os
 import time
 from typing import Any
 
@@ -146,16 +147,16 @@ class Collector:
                 self._list_cap = cap
         fused = self._fused_ok(random)
         steps = 0
-        while True:
+        if fused and n_vec is not None and not os.environ.get("TSM_COLLECT_PY"):
+            self._fused_run(n_vec, random)  # the whole loop in one C call (csrc/collect.cu)
+            steps = n_vec
+        while steps == 0 or n_vec is None or steps < n_vec:
             if fused:
                 self._fused_step(random, last=(n_vec is not None and steps == n_vec - 1) or n_vec is None)
             else:
                 self._generic_step(random)
             steps += 1
-            if n_vec is not None:
-                if steps >= n_vec:
-                    break
-            elif int(self._acc[0].item()) >= n_episode:  # one small D2H per step only in n_episode mode
+            if n_vec is None and int(self._acc[0].item()) >= n_episode:  # one small D2H per step only in n_episode mode
                 break
         acc = self._acc.cpu().numpy()
         n_ep = int(acc[0])
@@ -167,6 +168,44 @@ class Collector:
         self.last_episode_summary = {"count": n_ep, "ret_sum": acc[1], "ret_sqsum": acc[2], "ret_min": acc[3], "ret_max": acc[4],
                                      "len_sum": acc[5], "len_sqsum": acc[6], "len_min": acc[7], "len_max": acc[8]}
         return st
+
+    # -- n vector steps, fused, one C call ------------------------------------------------------
+    def _fused_run(self, n_vec: int, random: bool) -> None:
+        env, buf, L, P, S = self.env, self.buffer, _lib.lib(), _lib.ptr, _lib.stream_ptr()
+        R, O = self.env_num, env.obs_dim
+        if "obs" not in buf._store:
+            buf._alloc((O,), want_policy=True)
+        st = buf._store
+        size = buf._size
+        slot = buf._lockstep_ins
+        obs_slot = st["obs"][slot]
+        src = self._pre_collect_obs
+        if not (isinstance(src, torch.Tensor) and src.data_ptr() == obs_slot.data_ptr()):
+            obs_slot.copy_(torch.as_tensor(src, device=self.device).reshape(R, O))
+        if self._carry is None:
+            self._carry = torch.empty(R, O, dtype=torch.float32, device=self.device)
+        ro = _lib.TsmRollout(obs=P(st["obs"]), act=P(st["act"]), rew=P(st["rew"]), terminated=P(st["terminated"]),
+                             truncated=P(st["truncated"]), obs_next=P(st["obs_next"]), logp=P(st.get("logp")), value=P(st.get("value")),
+                             carry=P(self._carry), size=size, n_rows=R, obs_dim=O, slot=slot, ep_ret=P(self._ep_ret), ep_len=P(self._ep_len),
+                             acc=P(self._acc), list_ret=P(self._list_ret) if self.episode_list else None,
+                             list_len=P(self._list_len) if self.episode_list else None,
+                             list_count=P(self._list_count) if self.episode_list else None, list_cap=self._list_cap)
+        slot_o, len_o, carry_o = C.c_int64(0), C.c_int64(0), C.c_int(0)
+        tk = _lib.t_start("collect")
+        if random:
+            _lib.check(L.tsm_collect_lockstep(None, C.byref(env._desc), C.byref(buf._desc), C.byref(ro), n_vec, 0, self._random_seed,
+                                              self._random_counter, buf._lockstep_len, int(env.single_action_space.n),
+                                              C.byref(slot_o), C.byref(len_o), C.byref(carry_o), S))
+            self._random_counter += n_vec
+        else:
+            pol = self.policy
+            mode = 2 if (pol.deterministic_eval and not pol.is_within_training_step) else 1
+            _lib.check(L.tsm_collect_lockstep(pol.actor.desc, C.byref(env._desc), C.byref(buf._desc), C.byref(ro), n_vec, mode, pol.seed,
+                                              pol._counter, buf._lockstep_len, 0, C.byref(slot_o), C.byref(len_o), C.byref(carry_o), S))
+            pol._counter += n_vec
+        _lib.t_stop(tk)
+        buf._lockstep_ins, buf._lockstep_len = int(slot_o.value), int(len_o.value)
+        self._pre_collect_obs = self._carry if carry_o.value else st["obs"][buf._lockstep_ins]
 
     # -- one vector step, fused ---------------------------------------------------------------
     def _fused_step(self, random: bool, last: bool) -> None:
