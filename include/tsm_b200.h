@@ -254,10 +254,10 @@ typedef struct tsm_net {
     float* adam_v;      /* [n_params] exp_avg_sq */
     int64_t* adam_step; /* [1] device step counter */
     void* tc_image;     /* engine 1 only: TSM_TC_IMAGE_BYTES device bytes, zero-initialised by the caller: the fp16 operand
-                           image of params (+ a CTA ticket).  Refreshed by tsm_adam_step / tsm_ppo_epoch; call tsm_net_pack
+                           image of params.  Refreshed by tsm_adam_step / tsm_ppo_epoch; call tsm_net_pack
                            after writing params any other way. */
 } tsm_net;
-#define TSM_TC_IMAGE_BYTES 17024
+#define TSM_TC_IMAGE_BYTES 16896
 
 int64_t tsm_net_param_count(int in_dim, int hidden, int out_dim);
 

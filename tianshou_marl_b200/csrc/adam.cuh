@@ -21,8 +21,10 @@ constexpr int IMG_B2 = IMG_W3 + 8 * 16 * 8;    // [2][64][8], only k = 15 used
 constexpr int IMG_B3 = IMG_B2 + 2 * 64 * 8;    // [2][16][8]
 constexpr int IMG_HALVES = IMG_B3 + 2 * 16 * 8;
 constexpr int IMG_BYTES = IMG_HALVES * 2;      // 16 896
-constexpr int IMG_TICKET = IMG_BYTES;          // uint32 CTA ticket of the fused tail lives behind the image
-constexpr int IMG_ALLOC = IMG_BYTES + 128;
+// IMG_COPIES identical copies (CTA b reads copy b % IMG_COPIES) would spread the start-up reads of a launch over L2;
+// measured on B200: no gain for the readers and 2x the optimizer kernel's time at 16 copies, so one copy.
+constexpr int IMG_COPIES = 1;
+constexpr int IMG_ALLOC = IMG_BYTES * IMG_COPIES;
 
 __host__ __device__ inline int image_index(int64_t i, const ppo::Offsets& o, int in_dim) {
     if (i < o.b1) {
@@ -84,7 +86,10 @@ constexpr int ADAM_THREADS = 192;
 constexpr int ADAM_SLOTS = 4;  // float4 per thread held in registers: covers n <= 8 * 192 * 4 * 4 = 24 576 parameters
 
 __device__ __forceinline__ void adam_store_image(const AdamArgs& a, const ppo::Offsets& o, int64_t i, float pn) {
-    a.image[image_index(i, o, a.in_dim)] = __float2half_rn(pn);
+    const int idx = image_index(i, o, a.in_dim);
+    const __half h = __float2half_rn(pn);
+#pragma unroll
+    for (int c = 0; c < IMG_COPIES; ++c) a.image[c * IMG_HALVES + idx] = h;
 }
 
 __device__ __forceinline__ void adam_cluster(const AdamArgs& a) {

@@ -44,4 +44,34 @@ __host__ __device__ __forceinline__ uint64_t feistel_permute(uint64_t x, uint64_
     return x;
 }
 
+// The same permutation with everything that depends only on (n, key) prepared once on the host.
+struct FeistelPre {
+    uint32_t rk[FEISTEL_ROUNDS];
+    uint32_t mask_a, mask_b;
+    int a;
+};
+__host__ __device__ inline FeistelPre feistel_prepare(uint64_t n, uint64_t key) {
+    FeistelPre p;
+    const int bits = feistel_bits(n);
+    p.a = bits >> 1;
+    const int b = bits - p.a;
+    p.mask_a = (uint32_t)((1ull << p.a) - 1);
+    p.mask_b = (uint32_t)((1ull << b) - 1);
+    const uint32_t k0 = (uint32_t)key, k1 = (uint32_t)(key >> 32);
+    for (int r = 0; r < FEISTEL_ROUNDS; ++r) p.rk[r] = mix32(k0 + 0x9E3779B9u * (uint32_t)(r + 1)) ^ k1;
+    return p;
+}
+__device__ __forceinline__ uint64_t feistel_permute(uint64_t x, uint64_t n, const FeistelPre& p) {
+    do {
+        uint32_t lo = (uint32_t)x & p.mask_a, hi = (uint32_t)(x >> p.a) & p.mask_b;
+#pragma unroll
+        for (int r = 0; r < FEISTEL_ROUNDS; ++r) {
+            if (r & 1) lo ^= mix32(hi ^ p.rk[r]) & p.mask_a;
+            else hi ^= mix32(lo ^ p.rk[r]) & p.mask_b;
+        }
+        x = ((uint64_t)hi << p.a) | lo;
+    } while (x >= n);
+    return x;
+}
+
 }  // namespace tsm

@@ -585,18 +585,30 @@ __global__ void __launch_bounds__(THREADS) ppo_minibatch_kernel(PpoArgs a) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// mean and 1/(std_unbiased + eps) of adv over each minibatch (ppo.py:184-186), one CTA each
-__global__ void __launch_bounds__(THREADS) adv_stats_kernel(const float* __restrict__ adv, BatchView view,
-                                                           const int64_t* __restrict__ mb_bounds, float eps,
-                                                           float* __restrict__ stats) {
+// mean and 1/(std_unbiased + eps) of adv over each minibatch (ppo.py:184-186), one CTA each.  The reads are a random
+// gather (DRAM + page-walk latency of microseconds): 1024 threads x 8 independent loads in flight per thread.
+constexpr int STATS_THREADS = 1024;
+constexpr int STATS_UNROLL = 8;
+__global__ void __launch_bounds__(STATS_THREADS) adv_stats_kernel(const float* __restrict__ adv, BatchView view,
+                                                                 const int64_t* __restrict__ mb_bounds, float eps,
+                                                                 float* __restrict__ stats) {
     const int64_t s0 = mb_bounds[blockIdx.x], s1 = mb_bounds[blockIdx.x + 1];
     double sum = 0.0, sq = 0.0;
-    for (int64_t p = s0 + threadIdx.x; p < s1; p += THREADS) {
-        const double v = (double)adv[slot_of(view, p)];
-        sum += v;
-        sq += v * v;
+    for (int64_t p0 = s0 + threadIdx.x; p0 < s1; p0 += (int64_t)STATS_THREADS * STATS_UNROLL) {
+        float v[STATS_UNROLL];
+#pragma unroll
+        for (int u = 0; u < STATS_UNROLL; ++u) {
+            const int64_t p = p0 + (int64_t)u * STATS_THREADS;
+            v[u] = p < s1 ? __ldg(adv + slot_of(view, p)) : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < STATS_UNROLL; ++u) {
+            const double x = (double)v[u];
+            sum += x;
+            sq += x * x;
+        }
     }
-    __shared__ double sh[2][THREADS / 32];
+    __shared__ double sh[2][STATS_THREADS / 32];
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) {
         sum += __shfl_down_sync(0xffffffffu, sum, d);
@@ -606,7 +618,7 @@ __global__ void __launch_bounds__(THREADS) adv_stats_kernel(const float* __restr
     __syncthreads();
     if (threadIdx.x == 0) {
         double a = 0.0, b = 0.0;
-        for (int w = 0; w < THREADS / 32; ++w) { a += sh[0][w]; b += sh[1][w]; }
+        for (int w = 0; w < STATS_THREADS / 32; ++w) { a += sh[0][w]; b += sh[1][w]; }
         const double n = (double)(s1 - s0);
         const double mean = n > 0 ? a / n : 0.0;
         double var = n > 1 ? (b - n * mean * mean) / (n - 1.0) : NAN;  // torch.std of one element is nan
@@ -629,10 +641,14 @@ constexpr int ADAM_THREADS = 512;  // pack_image_kernel
 // fp32 parameters -> fp16 operand image of the tcgen05 engine (one CTA)
 __global__ void __launch_bounds__(ADAM_THREADS) pack_image_kernel(const float* __restrict__ p, int64_t n, int in_dim, int out_dim,
                                                                  __half* __restrict__ image) {
-    for (int i = threadIdx.x; i < opt::IMG_HALVES; i += ADAM_THREADS) image[i] = __float2half_rn(0.f);
+    for (int i = threadIdx.x; i < opt::IMG_HALVES * opt::IMG_COPIES; i += ADAM_THREADS) image[i] = __float2half_rn(0.f);
     __syncthreads();
     const Offsets o = offsets(in_dim, 64, out_dim);
-    for (int64_t i = threadIdx.x; i < n; i += ADAM_THREADS) image[opt::image_index(i, o, in_dim)] = __float2half_rn(p[i]);
+    for (int64_t i = threadIdx.x; i < n; i += ADAM_THREADS) {
+        const int idx = opt::image_index(i, o, in_dim);
+        const __half h = __float2half_rn(p[i]);
+        for (int c = 0; c < opt::IMG_COPIES; ++c) image[c * opt::IMG_HALVES + idx] = h;
+    }
 }
 
 }  // namespace mlp
@@ -721,10 +737,7 @@ extern "C" int tsm_net_forward(const tsm_net* net, const float* x, const int64_t
 }
 
 static BatchView make_view(const tsm_ppo_batch* b) {
-    BatchView v{};
-    v.indices = b->indices; v.size = b->size; v.n_rows = b->n_rows; v.start = b->start; v.len = b->len;
-    v.perm_key = b->perm_key; v.perm_n = b->perm_n;
-    return v;
+    return make_batch_view(b->indices, b->size, b->n_rows, b->start, b->len, b->perm_key, b->perm_n);
 }
 
 static int check_batch(const tsm_ppo_batch* b, const char* fn) {
@@ -744,7 +757,7 @@ extern "C" int tsm_ppo_adv_stats(const tsm_ppo_batch* batch, const int64_t* mb_b
     TSM_REQUIRE(n_minibatches >= 0, "n_minibatches >= 0");
     if (n_minibatches == 0) return TSM_OK;
     TSM_REQUIRE(batch->adv && mb_bounds && stats_out, "adv / mb_bounds / stats_out != NULL");
-    adv_stats_kernel<<<(unsigned)n_minibatches, THREADS, 0, as_stream(stream)>>>(batch->adv, make_view(batch), mb_bounds, eps,
+    adv_stats_kernel<<<(unsigned)n_minibatches, STATS_THREADS, 0, as_stream(stream)>>>(batch->adv, make_view(batch), mb_bounds, eps,
                                                                                 stats_out);
     TSM_LAUNCH_CHECK();
     return TSM_OK;

@@ -192,8 +192,7 @@ int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_p
     a.image = reinterpret_cast<const unsigned char*>(net->tc_image); a.grads = net->grads;
     if (!batch->records) return fail(TSM_ERR_INVALID, "%s: engine 1 needs batch.records (tsm_ppo_pack_records)", __func__);
     a.records = reinterpret_cast<const unsigned char*>(batch->records);
-    a.view.indices = batch->indices; a.view.size = batch->size; a.view.n_rows = batch->n_rows; a.view.start = batch->start;
-    a.view.len = batch->len; a.view.perm_key = batch->perm_key; a.view.perm_n = batch->perm_n;
+    a.view = ppo::make_batch_view(batch->indices, batch->size, batch->n_rows, batch->start, batch->len, batch->perm_key, batch->perm_n);
     a.mb_start = mb_start; a.mb_len = mb_len; a.mb_stats = mb_stats;
     a.cfg.eps_clip = cfg->eps_clip; a.cfg.dual_clip = cfg->dual_clip; a.cfg.vf_coef = cfg->vf_coef; a.cfg.ent_coef = cfg->ent_coef;
     a.cfg.value_clip = cfg->value_clip; a.cfg.adv_norm = cfg->adv_norm;
@@ -230,6 +229,10 @@ int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_p
             for (int k = 1; k < 24; ++k) printf(" %lld", h[row][k] - h[row][k - 1]);
             printf("  total %lld\n", h[row][23] - h[row][0]);
         }
+        for (int row = 0; row < 4; row += 2)
+            printf("kernel row %d: begin->setupA %lld ->prefetch issued %lld ->setup done %lld | tiles %lld | staging %lld reduce+sync %lld dealloc %lld atomics %lld | total %lld\n",
+                   row, h[row][31] - h[row][30], h[row][32] - h[row][31], h[row][33] - h[row][32], h[row][34] - h[row][33], h[row][35] - h[row][34],
+                   h[row][36] - h[row][35], h[row][37] - h[row][36], h[row][38] - h[row][37], h[row][38] - h[row][30]);
     }
 #endif
     return TSM_OK;

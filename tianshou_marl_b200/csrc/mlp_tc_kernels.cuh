@@ -218,9 +218,20 @@ __device__ __forceinline__ TcSetup tc_setup_finish(unsigned char* smem, const un
     uint32_t* tmem_s = reinterpret_cast<uint32_t*>(smem + SM_BAR + 16);
     const int warp = threadIdx.x >> 5;
     {
-        const uint4* src = reinterpret_cast<const uint4*>(image);
+        const uint4* src = reinterpret_cast<const uint4*>(image + (blockIdx.x % opt::IMG_COPIES) * opt::IMG_BYTES);
         uint4* dst = reinterpret_cast<uint4*>(smem + SM_IMG);
-        for (int i = threadIdx.x; i < opt::IMG_BYTES / 16; i += TC_THREADS) dst[i] = __ldcg(src + i);
+        constexpr int N16 = opt::IMG_BYTES / 16, PER = (N16 + TC_THREADS - 1) / TC_THREADS;
+        uint4 v[PER];  // all loads first (one L2 round trip), then the stores
+#pragma unroll
+        for (int u = 0; u < PER; ++u) {
+            const int i = threadIdx.x + u * TC_THREADS;
+            if (i < N16) v[u] = __ldcg(src + i);
+        }
+#pragma unroll
+        for (int u = 0; u < PER; ++u) {
+            const int i = threadIdx.x + u * TC_THREADS;
+            if (i < N16) dst[i] = v[u];
+        }
     }
     tc_sync_for_mma();
     s.tmem = *tmem_s;
@@ -437,8 +448,11 @@ __device__ __forceinline__ int stage_pos(int i, int w2_lo, int w2_hi) {
 
 __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs a) {
     extern __shared__ __align__(1024) unsigned char smem[];
+    [[maybe_unused]] const int krow = blockIdx.x == 0 ? 0 : (blockIdx.x == gridDim.x - 1 ? 2 : -1);
+    TRACE(krow, 30);
     pdl_launch_dependents();
     tc_setup_begin(smem, TM_COLS_BWD);
+    TRACE(krow, 31);
     constexpr uint32_t ID_DH = tc::make_idesc_f16(128, 64, 0, 0, 0, 1);    // K-major A, MN-major B
     constexpr uint32_t ID_G64 = tc::make_idesc_f16(128, 64, 0, 0, 1, 1);   // both MN-major (K = rows)
     constexpr uint32_t ID_G32 = tc::make_idesc_f16(128, 32, 0, 0, 1, 1);
@@ -456,8 +470,10 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
     bool nvalid = false;
     int64_t tile = blockIdx.x;
     if (tile < n_tiles) tc_prefetch_row(a, tile, r, nvalid, nd);  // batch records only: safe ahead of the dependency wait
+    TRACE(krow, 32);
     pdl_wait();  // parameters (image), gradients and mb_stats of the preceding launches are now visible
     TcSetup s = tc_setup_finish(smem, a.image);
+    TRACE(krow, 33);
     float mean = 0.f, rstd = 1.f;
     if (a.cfg.adv_norm && a.mb_stats) { mean = __ldcg(a.mb_stats); rstd = __ldcg(a.mb_stats + 1); }
     uint32_t it = 0;
@@ -551,6 +567,7 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
         }
         TRACE(trow, 23);
     }
+    TRACE(krow, 34);
     const Offsets o = offsets(a.in_dim, TC_H, a.out_dim);
     const float inv_s = a.inv_gscale;
     if (it > 0 && !(a.debug & 1)) {
@@ -584,6 +601,7 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
             stage[o.b1 + rr] = v[31];
         }
     }
+    TRACE(krow, 35);
     // db3 and the loss sums: warp shuffle, then shared memory
     l_clip += (double)f_clip; l_vf += (double)f_vf; l_ent += (double)f_ent;
     float* red_f = reinterpret_cast<float*>(smem + SM_RED);
@@ -612,4 +630,5 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
         if (r < a.out_dim) atomicAdd(a.grads + o.b3 + r, red_f[r] + red_f[OUTP + r] + red_f[2 * OUTP + r] + red_f[3 * OUTP + r]);
         if (a.loss_sums && r < 3) atomicAdd(a.loss_sums + r, red_d[r] + red_d[3 + r] + red_d[6 + r] + red_d[9 + r]);
     }
+    TRACE(krow, 38);
 }

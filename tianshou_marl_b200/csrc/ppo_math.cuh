@@ -32,15 +32,29 @@ struct BatchView {
     int64_t start, len;      // lock-step view: row r holds `len` valid slots from ring slot `start`
     uint64_t perm_key;       // Feistel key of the minibatch permutation
     int64_t perm_n;          // domain of the permutation (0 = identity)
+    FeistelPre pre;          // round keys / masks of (perm_n, perm_key), prepared by make_batch_view()
 };
+inline BatchView make_batch_view(const int64_t* indices, int64_t size, int64_t n_rows, int64_t start, int64_t len, uint64_t perm_key,
+                                 int64_t perm_n) {
+    BatchView v{};
+    v.indices = indices; v.size = size; v.n_rows = n_rows; v.start = start; v.len = len; v.perm_key = perm_key; v.perm_n = perm_n;
+    if (perm_n > 0) v.pre = feistel_prepare((uint64_t)perm_n, perm_key);
+    return v;
+}
 __device__ __forceinline__ int64_t slot_of(const BatchView& b, int64_t p) {
     if (b.indices) {
         const int64_t i = b.indices[p];
         const int64_t row = i / b.size, t = i - row * b.size;
         return t * b.n_rows + row;
     }
-    const int64_t q = b.perm_n > 0 ? (int64_t)feistel_permute((uint64_t)p, (uint64_t)b.perm_n, b.perm_key) : p;
-    const int64_t row = q / b.len, j = q - row * b.len;
+    const int64_t q = b.perm_n > 0 ? (int64_t)feistel_permute((uint64_t)p, (uint64_t)b.perm_n, b.pre) : p;
+    int64_t row, j;
+    if (((uint64_t)q | (uint64_t)b.len) >> 32) {
+        row = q / b.len; j = q - row * b.len;
+    } else {  // 32-bit division: the 64-bit one is emulated in about 70 instructions
+        const uint32_t r32 = (uint32_t)q / (uint32_t)b.len;
+        row = r32; j = (uint32_t)q - r32 * (uint32_t)b.len;
+    }
     int64_t t = b.start + j;
     if (t >= b.size) t -= b.size;
     return t * b.n_rows + row;

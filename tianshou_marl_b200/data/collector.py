@@ -28,7 +28,7 @@ import torch
 
 from .. import _lib
 from ..env.mpe import MPEVectorEnv
-from ..utils.stats import CollectStats
+from ..utils.stats import CollectStats, SequenceSummaryStats
 from .batch import Batch
 from .buffer import VectorReplayBuffer
 
@@ -68,6 +68,7 @@ class Collector:
         self._list_ret = self._list_len = None
         self._list_count = torch.zeros(1, dtype=torch.int64, device=dev)
         self._carry: torch.Tensor | None = None
+        self._pinned: dict[str, torch.Tensor] = {}
 
     # -- reference surface ------------------------------------------------------------------
     def close(self) -> None:
@@ -119,7 +120,16 @@ class Collector:
             if hasattr(self.policy, "train"):
                 self.policy.train(was_training)
         stats.set_collect_time(max(time.time() - t0, 1e-9))
-        stats.refresh_all_sequence_stats()
+        # returns_stat / lens_stat come from the device accumulators of tsm_episode_stats (count, sum, sum of squares, min,
+        # max in float64) rather than from a numpy pass over up to millions of episodes
+        summ = self.last_episode_summary
+        if summ["count"] > 0:
+            n = float(summ["count"])
+            for key, pre in (("returns_stat", "ret"), ("lens_stat", "len")):
+                mean = summ[pre + "_sum"] / n
+                var = max(summ[pre + "_sqsum"] / n - mean * mean, 0.0)
+                setattr(stats, key, SequenceSummaryStats(mean=float(mean), std=float(var ** 0.5), max=float(summ[pre + "_max"]),
+                                                         min=float(summ[pre + "_min"])))
         self.collect_step += stats.n_collected_steps
         self.collect_episode += stats.n_collected_episodes
         self.collect_time += stats.collect_time
@@ -163,11 +173,23 @@ class Collector:
         st = self.collect_stats_class(n_collected_episodes=n_ep, n_collected_steps=steps * R)
         if self.episode_list and n_ep > 0:
             k = min(n_ep, self._list_cap)
-            st.returns = self._list_ret[:k].cpu().numpy()
-            st.lens = self._list_len[:k].cpu().numpy()
+            st.returns = self._to_host("ret", self._list_ret[:k])
+            st.lens = self._to_host("len", self._list_len[:k])
+            torch.cuda.current_stream().synchronize()
         self.last_episode_summary = {"count": n_ep, "ret_sum": acc[1], "ret_sqsum": acc[2], "ret_min": acc[3], "ret_max": acc[4],
                                      "len_sum": acc[5], "len_sqsum": acc[6], "len_min": acc[7], "len_max": acc[8]}
         return st
+
+    def _to_host(self, name: str, t: torch.Tensor) -> np.ndarray:
+        """Asynchronous device -> pinned host copy (caller synchronises); the array aliases a pinned buffer that the next
+        collect() call with episode_list=True overwrites."""
+        n = t.numel()
+        h = self._pinned.get(name)
+        if h is None or h.numel() < n or h.dtype != t.dtype:
+            h = torch.empty(max(n, 1), dtype=t.dtype, pin_memory=True)
+            self._pinned[name] = h
+        h[:n].copy_(t, non_blocking=True)
+        return h[:n].numpy()
 
     # -- n vector steps, fused, one C call ------------------------------------------------------
     def _fused_run(self, n_vec: int, random: bool) -> None:
