@@ -339,6 +339,35 @@ int tsm_ppo_epoch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_
                   float max_grad_norm, double* loss_sums, tsm_stream_t stream);
 
 /* =========================================================================================
+ * Data-parallel update on one node: gradient all-reduce fused into the optimizer kernel
+ * replaces  torch DistributedDataParallel-style gradient averaging around Algorithm.Optimizer.step
+ *           (tianshou/algorithm/algorithm_base.py:485-498); SURVEY 8(e)
+ * Every rank maps every rank's receive area and flag pad into its address space (NVLink peer memory; torch
+ * symmetric memory provides the pointers).  Step `seq` (1, 2, ...): tsm_ppo_minibatch accumulates into the local
+ * net->grads as on one GPU; the optimizer kernel then PUSHES that gradient into slot [seq & 1][rank] of every
+ * rank's receive area (plain stores over NVLink, no round trip), signals and waits for all ranks (bounded spin:
+ * *status = 1 on time-out instead of a hang), sums the `world` slots of its own receive area in rank order --
+ * the same order on every rank, so parameters stay bit-identical -- applies grad_scale = 1 / world, clip and
+ * Adam, and clears net->grads.  One launch per minibatch does gradient exchange and optimizer step; there is no
+ * separate collective.
+ * ========================================================================================= */
+#define TSM_MAX_RANKS 8
+typedef struct tsm_peers {
+    int32_t world, rank;
+    float* recv[TSM_MAX_RANKS];     /* per rank: [2][world][n_stride] floats, n_stride = n_params rounded up to 4 */
+    uint32_t* flags[TSM_MAX_RANKS]; /* per rank: >= TSM_MAX_RANKS uint32, zero-initialised */
+    int32_t* status;                /* local device int, zero-initialised */
+} tsm_peers;
+
+int tsm_adam_step_dist(const tsm_net* net, const tsm_peers* peers, uint32_t seq, float lr, float beta1, float beta2, float eps,
+                       float max_grad_norm, float* grad_norm_out, tsm_stream_t stream);
+
+/* tsm_ppo_epoch across ranks: minibatch m is step seq0 + m (seq0 >= 1). */
+int tsm_ppo_epoch_dist(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, const int64_t* h_mb_bounds,
+                       int64_t n_minibatches, const float* mb_stats, float lr, float beta1, float beta2, float eps,
+                       float max_grad_norm, double* loss_sums, const tsm_peers* peers, uint32_t seq0, tsm_stream_t stream);
+
+/* =========================================================================================
  * The lock-step rollout loop (launches only)
  * replaces  Collector._collect                   tianshou/data/collector.py:770-1098
  * for the case where every environment advances every step: n_steps x { tsm_net_forward (mode 1 sample /

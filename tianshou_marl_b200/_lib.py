@@ -57,6 +57,12 @@ class TsmNet(C.Structure):
     ]
 
 
+class TsmPeers(C.Structure):
+    """struct tsm_peers (include/tsm_b200.h)."""
+
+    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("recv", c_vp * 8), ("flags", c_vp * 8), ("status", c_vp)]
+
+
 class TsmRollout(C.Structure):
     """struct tsm_rollout (include/tsm_b200.h)."""
 
@@ -108,6 +114,8 @@ _SIGS = {
     "tsm_mpe_step": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
     "tsm_random_actions": (c_i32, [c_vp, c_i64, c_i32, C.c_uint64, C.c_uint64, c_vp]),
     "tsm_collect_lockstep": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, C.c_uint64, C.c_uint64, c_i64, c_i32, c_vp, c_vp, c_vp, c_vp]),
+    "tsm_adam_step_dist": (c_i32, [c_vp, c_vp, C.c_uint32, c_f32, c_f32, c_f32, c_f32, c_f32, c_vp, c_vp]),
+    "tsm_ppo_epoch_dist": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_f32, c_f32, c_f32, c_f32, c_f32, c_vp, c_vp, C.c_uint32, c_vp]),
     "tsm_net_param_count": (c_i64, [c_i32, c_i32, c_i32]),
     "tsm_net_pack": (c_i32, [c_vp, c_vp]),
     "tsm_ppo_pack_records": (c_i32, [c_vp, c_vp, c_vp, c_vp]),

@@ -97,7 +97,8 @@ class PPO:
                  value_clip: bool = False, advantage_normalization: bool = True, recompute_advantage: bool = False,
                  vf_coef: float = 0.5, ent_coef: float = 0.01, max_grad_norm: float | None = None, gae_lambda: float = 0.95,
                  max_batchsize: int = 256, gamma: float = 0.99, return_scaling: bool = False,
-                 minibatch_order: str = "device", reuse_rollout_policy_outputs: bool = False, seed: int = 0) -> None:
+                 minibatch_order: str = "device", reuse_rollout_policy_outputs: bool = False, seed: int = 0,
+                 grad_sync: str = "auto") -> None:
         assert dual_clip is None or dual_clip > 1.0, f"Dual-clip PPO parameter should greater than 1.0 but got {dual_clip}"  # ppo.py
         assert 0.0 <= gamma <= 1.0 and 0.0 <= gae_lambda <= 1.0
         if return_scaling:
@@ -116,6 +117,10 @@ class PPO:
         self.vf_coef, self.ent_coef, self.max_grad_norm = vf_coef, ent_coef, max_grad_norm
         self.gae_lambda, self.gamma, self.max_batchsize = gae_lambda, gamma, max_batchsize
         self.minibatch_order = minibatch_order
+        if grad_sync not in ("auto", "peer", "nccl"):
+            raise ValueError("grad_sync must be 'auto', 'peer' or 'nccl'")
+        self.grad_sync = grad_sync  # world > 1: "peer" = exchange fused into the optimizer kernel, "nccl" = all_reduce per minibatch
+        self._peers = None
         self.reuse_rollout = reuse_rollout_policy_outputs
         self._eps = 1e-8
         self._epoch_counter = 0
@@ -273,7 +278,21 @@ class PPO:
                 _lib.check(L.tsm_ppo_adv_stats(C.byref(pb), P(bounds_dev), n_mb, self._eps, P(st_ep), S))
                 _lib.t_stop(tk)
             tk = _lib.t_start("ppo_epoch")
-            if world == 1:
+            if world > 1 and self.grad_sync != "nccl" and self._peers is None:
+                try:
+                    from .dist import PeerGradients
+                    self._peers = PeerGradients(net.n_params, net.device)
+                except Exception:  # no symmetric memory on this system: per-minibatch NCCL all-reduce
+                    if self.grad_sync == "peer":
+                        raise
+                    self.grad_sync = "nccl"
+            if world > 1 and self._peers is not None:
+                pg = self._peers
+                _lib.check(L.tsm_ppo_epoch_dist(net.desc, C.byref(pb), C.byref(self._cfg), h_bounds, n_mb,
+                                                P(st_ep) if self.advantage_normalization else None, o.lr, o.betas[0], o.betas[1],
+                                                o.eps, mgn, P(sums_ep), pg.byref(), pg.seq + 1, S))
+                pg.seq += n_mb
+            elif world == 1:
                 _lib.check(L.tsm_ppo_epoch(net.desc, C.byref(pb), C.byref(self._cfg), h_bounds, n_mb,
                                            P(st_ep) if self.advantage_normalization else None, o.lr, o.betas[0], o.betas[1], o.eps,
                                            mgn, P(sums_ep), S))
@@ -286,6 +305,8 @@ class PPO:
             _lib.t_stop(tk)
         # ---- stats: one device -> host copy for the whole update (the reference does 4 .item() per minibatch) ----
         h = sums.cpu().numpy()
+        if self._peers is not None:
+            self._peers.check()
         n_per = np.tile(np.diff(np.asarray(bounds)), repeat).astype(np.float64)
         clip_l, vf_l, ent_l = h[:, 0] / n_per, h[:, 1] / n_per, h[:, 2] / n_per
         loss = clip_l + self.vf_coef * vf_l - self.ent_coef * ent_l

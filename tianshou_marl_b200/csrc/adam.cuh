@@ -55,7 +55,19 @@ struct AdamArgs {
     float* gnorm_out;
     __half* image;  // NULL unless engine 1
     int in_dim, out_dim;
+    // data-parallel ranks on one node (world == 1: none of this is used).  Every rank PUSHES its local gradient g into
+    // slot [seq & 1][rank] of every rank's receive area (peer_recv[q]: device pointers mapped over NVLink; plain stores, no
+    // round trip), signals, waits for all ranks, and sums the world slots of its own receive area in rank order -- the
+    // same order everywhere, so parameters stay bit-identical across ranks.
+    int world, rank;
+    float* peer_recv[8];      // [2][world][n_stride] floats on rank q
+    uint32_t* peer_flag[8];   // peer_flag[q][r]: written by rank r into rank q's flag pad
+    int64_t n_stride;         // n rounded up to a multiple of 4
+    uint32_t seq;             // step number used as the flag value
+    int* status;              // set to 1 if the cross-rank wait times out
+    int debug;                // experiments only (TSM_DIST_DEBUG): 1 skip the barrier, 2 local gradients only
 };
+constexpr int ADAM_MAX_WORLD = 8;
 
 // beta^t for integer t by binary exponentiation (a serial double pow() costs microseconds on one thread)
 __device__ __forceinline__ double ipow(double b, int64_t t) {
@@ -92,6 +104,56 @@ __device__ __forceinline__ void adam_store_image(const AdamArgs& a, const ppo::O
     for (int c = 0; c < IMG_COPIES; ++c) a.image[c * IMG_HALVES + idx] = h;
 }
 
+// my gradient slice -> slot [seq & 1][rank] of every rank's receive area
+__device__ __forceinline__ int64_t adam_slot(const AdamArgs& a, int q) { return ((int64_t)(a.seq & 1u) * a.world + q) * a.n_stride; }
+__device__ __forceinline__ void adam_push4(const AdamArgs& a, int64_t j, float4 v) {
+    for (int q = 0; q < a.world; ++q)
+        if (q != a.rank) reinterpret_cast<float4*>(a.peer_recv[q] + adam_slot(a, a.rank))[j] = v;
+}
+__device__ __forceinline__ void adam_push1(const AdamArgs& a, int64_t i, float v) {
+    for (int q = 0; q < a.world; ++q)
+        if (q != a.rank) (a.peer_recv[q] + adam_slot(a, a.rank))[i] = v;
+}
+// sum over ranks in rank order; `mine` is this rank's own contribution (already in registers)
+__device__ __forceinline__ float4 adam_sum4(const AdamArgs& a, int64_t j, float4 mine) {
+    if (a.debug & 2) return mine;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int q = 0; q < a.world; ++q) {
+        const float4 x = q == a.rank ? mine : __ldcv(reinterpret_cast<const float4*>(a.peer_recv[a.rank] + adam_slot(a, q)) + j);
+        s.x += x.x; s.y += x.y; s.z += x.z; s.w += x.w;
+    }
+    return s;
+}
+__device__ __forceinline__ float adam_sum1(const AdamArgs& a, int64_t i, float mine) {
+    if (a.debug & 2) return mine;
+    float s = 0.f;
+    for (int q = 0; q < a.world; ++q) s += q == a.rank ? mine : __ldcv(a.peer_recv[a.rank] + adam_slot(a, q) + i);
+    return s;
+}
+
+// Cross-rank barrier of step `seq`, executed by one thread: publish "my gradient buffer of this step is complete" to
+// every peer's flag pad, then wait for every peer's flag.  The wait is bounded (about 2 s): a missing rank sets
+// *status instead of hanging the device.  Receive areas are double buffered by step parity, so one barrier per step
+// suffices: a rank overwrites parity b of a peer only after that peer has signalled the step after it last read b.
+__device__ __forceinline__ void adam_rank_barrier(const AdamArgs& a) {
+    __threadfence_system();
+    for (int q = 0; q < a.world; ++q)
+        if (q != a.rank) asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.peer_flag[q] + a.rank), "r"(a.seq) : "memory");
+    const long long t0 = clock64();
+    for (int q = 0; q < a.world; ++q) {
+        if (q == a.rank) continue;
+        uint32_t v;
+        do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(a.peer_flag[a.rank] + q) : "memory");
+            if ((int32_t)(v - a.seq) >= 0) break;
+            if (clock64() - t0 > 4000000000LL) {
+                if (a.status) *a.status = 1;
+                break;
+            }
+        } while (true);
+    }
+}
+
 __device__ __forceinline__ void adam_cluster(const AdamArgs& a) {
     namespace cg = cooperative_groups;
     cg::cluster_group cluster = cg::this_cluster();
@@ -105,39 +167,59 @@ __device__ __forceinline__ void adam_cluster(const AdamArgs& a) {
     float* __restrict__ G = a.g;
     float* __restrict__ M = a.m;
     float* __restrict__ V = a.v;
-    const bool vec = ((reinterpret_cast<uintptr_t>(P) | reinterpret_cast<uintptr_t>(G) | reinterpret_cast<uintptr_t>(M) |
-                       reinterpret_cast<uintptr_t>(V)) & 15) == 0;
+    uintptr_t al = reinterpret_cast<uintptr_t>(P) | reinterpret_cast<uintptr_t>(G) | reinterpret_cast<uintptr_t>(M) |
+                   reinterpret_cast<uintptr_t>(V);
+    for (int q = 0; q < a.world && a.world > 1; ++q) al |= reinterpret_cast<uintptr_t>(a.peer_recv[q]);
+    const bool vec = (al & 15) == 0;
     const int64_t n4 = vec ? a.n / 4 : 0;  // float4 body, scalar tail
     const bool in_regs = n4 <= GT * ADAM_SLOTS;
+    const bool dist = a.world > 1;
     float4 g[ADAM_SLOTS], p[ADAM_SLOTS], m[ADAM_SLOTS], v[ADAM_SLOTS];
     float sq = 0.f;
     const float gs = a.grad_scale;
+    // ---- local gradient (and, across ranks, its push to every peer) ----
     if (in_regs) {
 #pragma unroll
         for (int u = 0; u < ADAM_SLOTS; ++u) {
             const int64_t j = gtid + u * GT;
             if (j < n4) {
                 g[u] = __ldcg(reinterpret_cast<const float4*>(G) + j);
+                if (dist) adam_push4(a, j, g[u]);
                 p[u] = reinterpret_cast<const float4*>(P)[j];
                 m[u] = reinterpret_cast<const float4*>(M)[j];
                 v[u] = reinterpret_cast<const float4*>(V)[j];
             }
         }
+    } else if (dist) {
+        for (int64_t j = gtid; j < n4; j += GT) adam_push4(a, j, __ldcg(reinterpret_cast<const float4*>(G) + j));
+    }
+    if (dist) {
+        for (int64_t i = 4 * n4 + gtid; i < a.n; i += GT) adam_push1(a, i, __ldcg(G + i));
+        cluster.sync();  // all pushes of this cluster happen-before the system-scope fence + flag stores of thread 0 below
+        if (gtid == 0 && !(a.debug & 1)) adam_rank_barrier(a);
+        cluster.sync();
+    }
+    // ---- total gradient and its squared norm ----
+    if (in_regs) {
 #pragma unroll
         for (int u = 0; u < ADAM_SLOTS; ++u)
             if (gtid + u * GT < n4) {
+                if (dist) g[u] = adam_sum4(a, gtid + u * GT, g[u]);
                 sq = fmaf(g[u].x * gs, g[u].x * gs, sq); sq = fmaf(g[u].y * gs, g[u].y * gs, sq);
                 sq = fmaf(g[u].z * gs, g[u].z * gs, sq); sq = fmaf(g[u].w * gs, g[u].w * gs, sq);
             }
     } else {
         for (int64_t j = gtid; j < n4; j += GT) {
-            const float4 x = __ldcg(reinterpret_cast<const float4*>(G) + j);
+            float4 x = __ldcg(reinterpret_cast<const float4*>(G) + j);
+            if (dist) x = adam_sum4(a, j, x);
             sq = fmaf(x.x * gs, x.x * gs, sq); sq = fmaf(x.y * gs, x.y * gs, sq);
             sq = fmaf(x.z * gs, x.z * gs, sq); sq = fmaf(x.w * gs, x.w * gs, sq);
         }
     }
     for (int64_t i = 4 * n4 + gtid; i < a.n; i += GT) {
-        const float x = __ldcg(G + i) * gs;
+        float x = __ldcg(G + i);
+        if (dist) x = adam_sum1(a, i, x);
+        x *= gs;
         sq = fmaf(x, x, sq);
     }
 #pragma unroll
@@ -188,15 +270,17 @@ __device__ __forceinline__ void adam_cluster(const AdamArgs& a) {
         }
     } else {
         for (int64_t i = gtid; i < 4 * n4; i += GT) {
-            float mm = M[i], vv = V[i];
-            const float pn = adam_elem(P[i], __ldcg(G + i), mm, vv, coef, step_size, bc2_sqrt, a.beta1, a.beta2, a.eps);
+            float mm = M[i], vv = V[i], gi = __ldcg(G + i);
+            if (dist) gi = adam_sum1(a, i, gi);
+            const float pn = adam_elem(P[i], gi, mm, vv, coef, step_size, bc2_sqrt, a.beta1, a.beta2, a.eps);
             P[i] = pn; M[i] = mm; V[i] = vv; G[i] = 0.f;
             if (a.image) adam_store_image(a, o, i, pn);
         }
     }
     for (int64_t i = 4 * n4 + gtid; i < a.n; i += GT) {
-        float mm = M[i], vv = V[i];
-        const float pn = adam_elem(P[i], __ldcg(G + i), mm, vv, coef, step_size, bc2_sqrt, a.beta1, a.beta2, a.eps);
+        float mm = M[i], vv = V[i], gi = __ldcg(G + i);
+        if (dist) gi = adam_sum1(a, i, gi);
+        const float pn = adam_elem(P[i], gi, mm, vv, coef, step_size, bc2_sqrt, a.beta1, a.beta2, a.eps);
         P[i] = pn; M[i] = mm; V[i] = vv; G[i] = 0.f;
         if (a.image) adam_store_image(a, o, i, pn);
     }

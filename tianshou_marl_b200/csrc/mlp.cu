@@ -21,6 +21,7 @@
 // For the shared actor-critic OUT = n_act + 1: rows 0..n_act-1 of W3 are the
 // actor head (DiscreteActor.last), row n_act is the critic head (DiscreteCritic.last).
 #include <algorithm>
+#include <cstdlib>
 #include "common.cuh"
 #include "philox.cuh"
 #include "feistel.cuh"
@@ -825,6 +826,30 @@ static opt::AdamArgs adam_args(const tsm_net* net, float lr, float beta1, float 
     a.gnorm_out = grad_norm_out;
     a.image = net->engine == 1 ? reinterpret_cast<__half*>(net->tc_image) : nullptr;
     a.in_dim = net->in_dim; a.out_dim = net->out_dim;
+    a.world = 1; a.rank = 0; a.seq = 0; a.status = nullptr; a.n_stride = 0; a.debug = 0;
+    return a;
+}
+
+static int check_peers(const tsm_peers* p, const char* fn) {
+    if (!p) return fail(TSM_ERR_INVALID, "%s: peers is NULL", fn);
+    if (p->world < 1 || p->world > TSM_MAX_RANKS || p->rank < 0 || p->rank >= p->world)
+        return fail(TSM_ERR_INVALID, "%s: need 1 <= world <= %d and 0 <= rank < world", fn, TSM_MAX_RANKS);
+    for (int q = 0; q < p->world; ++q)
+        if (!p->recv[q] || !p->flags[q]) return fail(TSM_ERR_INVALID, "%s: peers.recv / flags of rank %d is NULL", fn, q);
+    return TSM_OK;
+}
+
+static opt::AdamArgs adam_args_dist(const tsm_net* net, const tsm_peers* peers, uint32_t seq, float lr, float beta1, float beta2,
+                                    float eps, float max_grad_norm, float* grad_norm_out) {
+    opt::AdamArgs a = adam_args(net, lr, beta1, beta2, eps, max_grad_norm, 1.0f / (float)peers->world, grad_norm_out);
+    a.world = peers->world; a.rank = peers->rank; a.seq = seq; a.status = peers->status;
+    a.n_stride = (net->n_params + 3) / 4 * 4;
+    static const int dbg = getenv("TSM_DIST_DEBUG") ? atoi(getenv("TSM_DIST_DEBUG")) : 0;
+    a.debug = dbg;
+    for (int q = 0; q < peers->world; ++q) {
+        a.peer_recv[q] = peers->recv[q];
+        a.peer_flag[q] = peers->flags[q];
+    }
     return a;
 }
 
@@ -875,15 +900,59 @@ extern "C" int tsm_ppo_epoch(const tsm_net* net, const tsm_ppo_batch* batch, con
             if (rc) return rc;
             TSM_REQUIRE(cfg && net->grads && net->adam_m && net->adam_v && net->adam_step, "cfg / grads / adam state != NULL");
             TSM_REQUIRE(!cfg->adv_norm || st, "advantage normalisation needs mb_stats");
-            rc = tc_ppo_minibatch(net, batch, cfg, s0, len, st, ls, m > 0, as_stream(stream));
+            static const int no_pdl = getenv("TSM_NO_PDL") != nullptr;
+            rc = tc_ppo_minibatch(net, batch, cfg, s0, len, st, ls, m > 0 && !no_pdl, as_stream(stream));
             if (rc) return rc;
-            rc = launch_adam(adam_args(net, lr, beta1, beta2, eps, max_grad_norm, 1.0f, nullptr), 1, as_stream(stream));
+            rc = launch_adam(adam_args(net, lr, beta1, beta2, eps, max_grad_norm, 1.0f, nullptr), !no_pdl, as_stream(stream));
             if (rc) return rc;
             continue;
         }
         int rc = tsm_ppo_minibatch(net, batch, cfg, s0, len, st, ls, stream);
         if (rc) return rc;
         rc = tsm_adam_step(net, lr, beta1, beta2, eps, max_grad_norm, 1.0f, nullptr, stream);
+        if (rc) return rc;
+    }
+    return TSM_OK;
+}
+
+extern "C" int tsm_adam_step_dist(const tsm_net* net, const tsm_peers* peers, uint32_t seq, float lr, float beta1, float beta2, float eps,
+                                  float max_grad_norm, float* grad_norm_out, tsm_stream_t stream) {
+    TSM_REQUIRE(net != nullptr, "net != NULL");
+    int rc = check_peers(peers, __func__);
+    if (rc) return rc;
+    TSM_REQUIRE(net->params && net->grads && net->adam_m && net->adam_v && net->adam_step && net->n_params > 0, "params / grads / adam state != NULL");
+    TSM_REQUIRE(net->engine != 1 || net->tc_image, "engine 1 needs tc_image");
+    TSM_REQUIRE(seq >= 1, "seq >= 1");
+    return launch_adam(adam_args_dist(net, peers, seq, lr, beta1, beta2, eps, max_grad_norm, grad_norm_out), 0, as_stream(stream));
+}
+
+extern "C" int tsm_ppo_epoch_dist(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, const int64_t* h_mb_bounds,
+                                  int64_t n_minibatches, const float* mb_stats, float lr, float beta1, float beta2, float eps,
+                                  float max_grad_norm, double* loss_sums, const tsm_peers* peers, uint32_t seq0, tsm_stream_t stream) {
+    TSM_REQUIRE(h_mb_bounds != nullptr && n_minibatches >= 0 && net != nullptr, "h_mb_bounds / net != NULL");
+    int rc = check_peers(peers, __func__);
+    if (rc) return rc;
+    TSM_REQUIRE(seq0 >= 1, "seq0 >= 1");
+    for (int64_t m = 0; m < n_minibatches; ++m) {
+        const uint32_t seq = seq0 + (uint32_t)m;
+        const int64_t s0 = h_mb_bounds[m], len = h_mb_bounds[m + 1] - h_mb_bounds[m];
+        const tsm_net& local = *net;
+        const float* st = mb_stats ? mb_stats + 2 * m : nullptr;
+        double* ls = loss_sums ? loss_sums + 4 * m : nullptr;
+        if (local.engine == 1 && len > 0) {
+            rc = check_net(&local, __func__);
+            if (rc) return rc;
+            rc = check_batch(batch, __func__);
+            if (rc) return rc;
+            TSM_REQUIRE(cfg && local.adam_m && local.adam_v && local.adam_step, "cfg / adam state != NULL");
+            TSM_REQUIRE(!cfg->adv_norm || st, "advantage normalisation needs mb_stats");
+            rc = tc_ppo_minibatch(&local, batch, cfg, s0, len, st, ls, m > 0, as_stream(stream));
+        } else {
+            rc = tsm_ppo_minibatch(&local, batch, cfg, s0, len, st, ls, stream);
+        }
+        if (rc) return rc;
+        rc = launch_adam(adam_args_dist(&local, peers, seq, lr, beta1, beta2, eps, max_grad_norm, nullptr), local.engine == 1,
+                         as_stream(stream));
         if (rc) return rc;
     }
     return TSM_OK;
