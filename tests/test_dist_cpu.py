@@ -1,0 +1,116 @@
+"""World-size-2 gloo tests (CPU) of the data-parallel update logic:
+  * shards: per-rank environment seeds differ, parameter seeds do not;
+  * exchange: allreduce_mean_ over ranks == gradient of the concatenated minibatch (oracle PPO, adv_norm off),
+    so the optimizer step leaves bit-identical parameters on every rank and matches the single-process step;
+  * rank-ordered summation (what the fused CUDA kernel does) is the same on every rank.
+The CUDA path itself is checked on two GPUs by tests/test_gpu_dist.py."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _make_case(n: int, seed: int):
+    rng = np.random.default_rng(seed)
+    O = 18
+    d = dict(obs=rng.normal(size=(n, O)).astype(np.float32), act=rng.integers(0, 5, n), adv=rng.normal(size=n).astype(np.float32),
+             ret=rng.normal(size=n).astype(np.float32), lp=(np.log(0.2) + 0.1 * rng.normal(size=n)).astype(np.float32),
+             vo=rng.normal(size=n).astype(np.float32))
+    return {k: torch.from_numpy(v) for k, v in d.items()}
+
+
+CFG = dict(eps_clip=0.2, dual_clip=None, value_clip=False, adv_norm=False, vf_coef=0.5, ent_coef=0.01, eps=1e-8)
+
+
+def _flat_grad(net) -> torch.Tensor:
+    return torch.cat([p.grad.reshape(-1) for p in net.p])
+
+
+def _set_flat_grad(net, flat: torch.Tensor) -> None:
+    off = 0
+    for p in net.p:
+        k = p.numel()
+        p.grad = flat[off: off + k].reshape(p.shape).clone()
+        off += k
+
+
+def _worker(rank: int, world: int, port: int, out_dir: str) -> None:
+    sys.path.insert(0, ROOT)
+    from oracle import ppo as oppo
+    from tianshou_marl_b200.algorithm import dist as tdist
+
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    assert tdist.world_info() == (rank, world)
+    assert tdist.shard_seed(1000, rank) != tdist.shard_seed(1000, 1 - rank) and tdist.grad_scale(world) == 0.5
+    n = 96
+    shard = _make_case(n, seed=10 + rank)  # this rank's half of the global minibatch
+    net = oppo.make_net(18, 64, 5, seed=0)  # identical init everywhere
+    for step in range(3):
+        for p in net.p:
+            p.grad = None
+        loss, *_ = oppo.minibatch_loss(net, shard["obs"], shard["act"], shard["adv"], shard["ret"], shard["lp"], shard["vo"], CFG)
+        loss.backward()
+        flat = _flat_grad(net)
+        # rank-ordered sum (the fused kernel's order) == all_reduce sum for two ranks, bit for bit
+        gathered = [torch.empty_like(flat) for _ in range(world)]
+        dist.all_gather(gathered, flat)
+        ordered = sum(gathered[1:], gathered[0].clone()) * tdist.grad_scale(world)
+        mean = tdist.allreduce_mean_(flat.clone())
+        assert torch.equal(ordered, mean)
+        _set_flat_grad(net, mean)
+        oppo.adam_step(net, lr=1e-3, max_grad_norm=0.5)
+    flat_p = torch.cat([p.detach().reshape(-1) for p in net.p])
+    both = [torch.empty_like(flat_p) for _ in range(world)]
+    dist.all_gather(both, flat_p)
+    assert torch.equal(both[0], both[1])  # parameters bit-identical across ranks
+    if rank == 0:
+        np.save(os.path.join(out_dir, "params.npy"), flat_p.numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_update_matches_single_process(tmp_path):
+    sys.path.insert(0, ROOT)
+    from oracle import ppo as oppo
+
+    port = _free_port()
+    mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    got = np.load(tmp_path / "params.npy")
+    # single process on the concatenated minibatch: mean over 2n rows == mean of the two per-rank means
+    a, b = _make_case(96, 10), _make_case(96, 11)
+    cat = {k: torch.cat([a[k], b[k]]) for k in a}
+    net = oppo.make_net(18, 64, 5, seed=0)
+    for step in range(3):
+        for p in net.p:
+            p.grad = None
+        loss, *_ = oppo.minibatch_loss(net, cat["obs"], cat["act"], cat["adv"], cat["ret"], cat["lp"], cat["vo"], CFG)
+        loss.backward()
+        oppo.adam_step(net, lr=1e-3, max_grad_norm=0.5)
+    want = torch.cat([p.detach().reshape(-1) for p in net.p]).numpy()
+    assert np.allclose(got, want, rtol=0, atol=2e-6), np.abs(got - want).max()
+
+
+def test_peer_struct_layout():
+    """tsm_peers as bound by ctypes: 8 receive pointers, 8 flag pointers, one status pointer."""
+    sys.path.insert(0, ROOT)
+    import ctypes as C
+
+    from tianshou_marl_b200 import _lib
+
+    p = _lib.TsmPeers()
+    assert C.sizeof(p) == 8 + 8 * 8 + 8 * 8 + 8
+    assert _lib.TsmPeers.recv.offset == 8 and _lib.TsmPeers.flags.offset == 72 and _lib.TsmPeers.status.offset == 136
