@@ -42,6 +42,7 @@ class Workload:
         self.launches_per_step = self.T * (K_POLICY + K_MPE + K_ADD + K_STATS) + 1
         if self.update:
             self.launches_per_step += 3 + 1 + args.repeat * (1 + 2 * self.n_mb)  # critic x2, logp, gae, per epoch: stats + (minibatch, adam)
+            self.launches_per_step += 1 if args.engine == "tc" else 0  # pack_records
         self.h2d_bytes = 0
         self.d2h_bytes = 0
         self.last_stats: Any = None
@@ -83,23 +84,33 @@ class Workload:
         """Dominant kernel by time in the step (DESIGN.md lists the per-unit figures)."""
         O, A, H = self.O, self.A, self.args.hidden
         fwd_flop = 2.0 * (O * H + H * H + H * 6)
-        per_unit_bytes = {"gae": 22.0, "mpe_step": (16 * A * 2 + 8 * A + 4 * A + 8 * A * O + 6 * A) / A, "buf_counters": 8.0,
+        per_unit_bytes = {"gae": 22.0, "collect": (16 * A * 2 + 8 * A + 4 * A + 8 * A * O + 6 * A) / A + 4.0 * O + 12.0 + 8.0, "mpe_step": (16 * A * 2 + 8 * A + 4 * A + 8 * A * O + 6 * A) / A, "buf_counters": 8.0,
                           "policy_forward": 4.0 * O + 12.0, "critic_forward": 4.0 * O + 4.0, "logp_old_forward": 4.0 * O + 8.0,
-                          "adv_stats": 4.0}
+                          "adv_stats": 4.0, "pack_records": 4.0 * O + 20.0 + 96.0}
         B = self.R * self.T
-        units = {"gae": B, "mpe_step": self.R, "buf_counters": self.R, "policy_forward": self.R, "critic_forward": B,
+        units = {"gae": B, "collect": B, "pack_records": B, "mpe_step": self.R, "buf_counters": self.R, "policy_forward": self.R, "critic_forward": B,
                  "logp_old_forward": B, "adv_stats": B}
         if not stages:
             return {}
         dom = max(stages, key=lambda k: stages[k]["ms_per_step"])
         out: dict[str, Any] = {"kernel": dom, "peak_source": peak_src}
         if dom == "ppo_epoch":
-            # one stage = n_mb x (ppo_minibatch_kernel + adam_kernel); FLOPs of the minibatch kernel: fwd + 2x bwd
-            flop = 3.0 * fwd_flop * B
-            t = stages[dom]["launch_ms"] * 1e-3
+            # one stage call = n_mb x (minibatch kernel + optimizer kernel); per-launch figures of the minibatch kernel:
+            # algorithmic FLOPs fwd + 2x bwd = 33.8 kFLOP/row, algorithmic bytes = one 96-byte record per row (tc engine) or
+            # 4*O + 20 gathered bytes (fp32 engine); duration = stage time / n_mb (so it also carries the optimizer kernel)
+            rows = min(self.args.batch_size, B)
+            t = stages[dom]["launch_ms"] * 1e-3 / self.n_mb
+            flop = 3.0 * fwd_flop * rows
             ach = flop / t / 1e12
-            out.update({"bound": "tensor", "achieved": ach, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach / tf_peak, "traffic": None,
-                        "flop_per_unit": 3.0 * fwd_flop, "units_per_launch": B, "note": "engine=%s; achieved counts the algorithmic FLOPs of fwd+bwd (33.8 kFLOP/row), stage = n_mb x (minibatch kernel + adam kernel)" % self.args.engine})
+            rec_bytes = 96.0 if self.args.engine == "tc" else 4.0 * O + 20.0
+            out.update({"bound": "tensor", "achieved": ach, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach / tf_peak,
+                        # dram__bytes_read.sum + dram__bytes_write.sum of tc_ppo_minibatch_kernel, one launch of 65 536 rows,
+                        # profiles/r01_ncu_full_tc_ppo_minibatch.csv (ncu --set full); null for other shapes / engines
+                        "traffic": 12.68e6 if (self.args.engine == "tc" and rows == 65536 and O == 18) else None,
+                        "flop_per_unit": 3.0 * fwd_flop, "bytes_per_unit": rec_bytes, "units_per_launch": rows,
+                        "launch_us": t * 1e6, "hbm_gbs": rec_bytes * rows / t / 1e9,
+                        "note": "engine=%s; latency bound (two 128-row tiles per CTA per launch): launch_us = stage time / %d "
+                                "minibatches and includes the 8-CTA optimizer kernel" % (self.args.engine, self.n_mb)})
         elif dom in ("policy_forward", "critic_forward", "logp_old_forward"):
             flop = fwd_flop * units[dom]
             t = stages[dom]["launch_ms"] * 1e-3
