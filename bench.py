@@ -50,8 +50,8 @@ def parse() -> argparse.Namespace:
     p.add_argument("--engine", default="tc", choices=["tc", "fp32"], help="MLP kernels: tcgen05 (fp16 operands, fp32 accumulate) or exact fp32")
     p.add_argument("--no-update", action="store_true", help="collect + GAE only")
     p.add_argument("--no-cpu-baseline", action="store_true")
-    p.add_argument("--cpu-envs", type=int, default=2048, help="reference arm: environments in the bounded sample")
-    p.add_argument("--cpu-horizon", type=int, default=32)
+    p.add_argument("--cpu-envs", type=int, default=4096, help="reference arm: environments in the bounded sample")
+    p.add_argument("--cpu-horizon", type=int, default=64)
     return p.parse_args()
 
 
@@ -284,7 +284,7 @@ def main() -> None:
                         "h2d_bytes_per_step": wl.h2d_bytes, "d2h_bytes_per_step": wl.d2h_bytes},
                 "stages_ms": stages, "roofline": roof}
         if not args.no_cpu_baseline and world == 1:
-            r = cpu_arm(args, 1, 1)
+            r = cpu_arm(args, 3, 1)
             line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]}
         print(json.dumps(line))
     if world > 1:
