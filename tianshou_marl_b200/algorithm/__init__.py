@@ -1,5 +1,6 @@
+from .multiagent import FlexibleMultiAgentPolicyManager
 from .ppo import PPO, AdamOptimizerFactory, DiscreteActorPolicy, ppo_smoke
 from .returns import compute_episodic_return, episode_mc_return_to_go, gae_flat, gae_time_major
 
 __all__ = ["compute_episodic_return", "episode_mc_return_to_go", "gae_flat", "gae_time_major", "PPO", "AdamOptimizerFactory",
-           "DiscreteActorPolicy", "ppo_smoke"]
+           "DiscreteActorPolicy", "ppo_smoke", "FlexibleMultiAgentPolicyManager"]

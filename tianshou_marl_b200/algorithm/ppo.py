@@ -179,7 +179,9 @@ class PPO:
         return b
 
     # -- the update ---------------------------------------------------------------------------
-    def update(self, buffer: Any, batch_size: int | None, repeat: int) -> A2CTrainingStats:
+    def update(self, buffer: Any, batch_size: int | None, repeat: int, rows: torch.Tensor | None = None) -> A2CTrainingStats:
+        """`rows` (device int64, optional) restricts the update to those sub-buffers (agent rows): the policy group of a
+        FlexibleMultiAgentPolicyManager.  GAE runs per row, so restricting rows only shrinks the batch."""
         if not self.policy.is_within_training_step:
             raise RuntimeError(
                 f"update() was called outside of a training step as signalled by {self.policy.is_within_training_step=} "
@@ -201,11 +203,15 @@ class PPO:
         # ---- _add_returns_and_advantages (a2c.py:113-151): critic(obs), critic(obs_next) ----
         if self.reuse_rollout and "value" in st and "logp" in st:
             raise NotImplementedError("reuse_rollout_policy_outputs is wired by the fused collector")
+        slots = None  # storage slots (t * R + row) this update touches; None = all
+        if rows is not None:
+            rows = rows.to(device=net.device, dtype=torch.int64).contiguous()
+            slots = (torch.arange(size, device=net.device, dtype=torch.int64)[:, None] * R + rows[None, :]).reshape(-1).contiguous()
         tk = _lib.t_start("critic_forward")
-        net.forward(obs_all, mode="raw", out={"value": v_s.view(-1)})
+        net.forward(obs_all, mode="raw", out={"value": v_s.view(-1)}, rows=slots, scatter=slots is not None)
         _lib.t_stop(tk)
         tk = _lib.t_start("critic_forward")
-        net.forward(st["obs_next"].view(size * R, O), mode="raw", out={"value": v_n.view(-1)})
+        net.forward(st["obs_next"].view(size * R, O), mode="raw", out={"value": v_n.view(-1)}, rows=slots, scatter=slots is not None)
         _lib.t_stop(tk)
         tk = _lib.t_start("gae")
         if lockstep:
@@ -213,8 +219,16 @@ class PPO:
             B = lock_len * R
             gae_time_major(v_s, v_n, st["rew"], st["terminated"], st["truncated"], start, lock_len, self.gamma, self.gae_lambda, adv, ret)
             idx_all = None
+            if rows is not None:  # env-major buffer indices of the group's rows, in buffer.sample(0) order
+                tt = (start + torch.arange(lock_len, device=net.device, dtype=torch.int64)) % size
+                idx_all = (rows[:, None] * size + tt[None, :]).reshape(-1).contiguous()
+                B = int(idx_all.numel())
         else:
             idx_all = buffer._all_indices_device()
+            if rows is not None:
+                member = torch.zeros(R, dtype=torch.bool, device=net.device)
+                member[rows] = True
+                idx_all = idx_all[member[idx_all // size]].contiguous()
             B = int(idx_all.numel())
             if B == 0:
                 return A2CTrainingStats(*(SequenceSummaryStats.from_sequence([]) for _ in range(4)))
@@ -231,7 +245,8 @@ class PPO:
         _lib.t_stop(tk)
         # ---- logp_old (ppo.py:157-161) ----
         tk = _lib.t_start("logp_old_forward")
-        net.forward(obs_all, mode="eval", act=st["act"].view(-1), out={"logp": logp.view(-1), "value": self._buf("scratch_v", (size * R,))})
+        net.forward(obs_all, mode="eval", act=st["act"].view(-1), out={"logp": logp.view(-1), "value": self._buf("scratch_v", (size * R,))},
+                    rows=slots, scatter=slots is not None)
         _lib.t_stop(tk)
         # ---- minibatch loop (ppo.py:173-216) ----
         bounds = self.split_bounds(B, batch_size)
