@@ -311,6 +311,10 @@ typedef struct tsm_ppo_cfg {
     float ent_coef;   /* a2c.py (0.01) */
     int32_t value_clip;
     int32_t adv_norm; /* advantage_normalization (ppo.py:184-186) */
+    int32_t plain_pg; /* 1: policy term = -logp(act) * adv (one-step actor-critic) instead of the clipped surrogate;
+                         2: CTDEPolicy.learn as written (multiagent/ctde.py:181-183): logp [n] * adv [n,1] broadcasts to
+                            [n,n], i.e. every row is weighted by the minibatch mean advantage = mb_stats[0] */
+    int32_t value_heads; /* > 1: value = mean of that many head outputs from value_index on (ctde.py:153-156) */
 } tsm_ppo_cfg;
 
 /* per-minibatch {mean, 1/(std_unbiased + eps)} of adv: mb_bounds (device) [n_minibatches+1]
@@ -337,6 +341,23 @@ int tsm_adam_step(const tsm_net* net, float lr, float beta1, float beta2, float 
 int tsm_ppo_epoch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, const int64_t* h_mb_bounds,
                   int64_t n_minibatches, const float* mb_stats, float lr, float beta1, float beta2, float eps,
                   float max_grad_norm, double* loss_sums, tsm_stream_t stream);
+
+/* =========================================================================================
+ * CTDE pieces (centralized training, decentralized execution)
+ * replaces  GlobalStateConstructor.build         tianshou/algorithm/multiagent/ctde.py:282-343 (modes concatenate, mean)
+ *           TD target / advantage of CTDEPolicy.learn    ctde.py:149-178
+ * ========================================================================================= */
+/* obs [n_envs][n_agents][obs_dim] (rows of one world are contiguous: row = env * A + agent) ->
+ * out [n_envs * n_agents][global_dim]: every agent row of a world receives that world's global state,
+ * mode 0 "concatenate": global_dim = n_agents * obs_dim, cat(obs_0 .. obs_{A-1}) in agent order (ctde.py:291-294);
+ * mode 1 "mean":        global_dim = obs_dim, mean over the agents (ctde.py:296-300). */
+int tsm_global_state(const float* obs, int64_t n_envs, int n_agents, int obs_dim, int mode, float* out, tsm_stream_t stream);
+
+/* v_cur, v_next [n][heads] critic outputs; value = mean over heads (ctde.py:153-156);
+ * td[i] = rew[i] + gamma * value_next[i] * (1 - terminated[i]) (ctde.py:169); adv[i] = td[i] - value[i] (ctde.py:178).
+ * value_out (optional) receives value[i]. */
+int tsm_td_target(const float* v_cur, const float* v_next, int heads, const float* rew, const uint8_t* terminated, float gamma,
+                  int64_t n, float* td_out, float* adv_out, float* value_out, tsm_stream_t stream);
 
 /* =========================================================================================
  * Data-parallel update on one node: gradient all-reduce fused into the optimizer kernel

@@ -114,7 +114,7 @@ def test_ppo_minibatch_tc_vs_fp32(O, n):
             err = (a - b).abs().max().item()
             # forward outputs carry ~2e-3 absolute rounding (11-bit operands), which moves the PPO ratio / clip decisions of
             # individual rows; the effect on a gradient entry averages out with the minibatch size
-            assert err < (0.03 if n >= 3000 else 0.12) * scale + 1e-7, (name, err, scale, cfgk)
+            assert err < (0.05 if n >= 3000 else 0.12) * scale + 1e-7, (name, err, scale, cfgk)
         assert np.allclose(res["tc"][1][:3] / n, res["fp32"][1][:3] / n, rtol=5e-3, atol=2e-3)
     net.engine = "fp32"
 

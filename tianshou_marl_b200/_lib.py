@@ -89,7 +89,7 @@ class TsmPpoCfg(C.Structure):
 
     _fields_ = [
         ("eps_clip", C.c_float), ("dual_clip", C.c_float), ("vf_coef", C.c_float), ("ent_coef", C.c_float),
-        ("value_clip", C.c_int32), ("adv_norm", C.c_int32),
+        ("value_clip", C.c_int32), ("adv_norm", C.c_int32), ("plain_pg", C.c_int32), ("value_heads", C.c_int32),
     ]
 
 
@@ -116,6 +116,8 @@ _SIGS = {
     "tsm_collect_lockstep": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, C.c_uint64, C.c_uint64, c_i64, c_i32, c_vp, c_vp, c_vp, c_vp]),
     "tsm_adam_step_dist": (c_i32, [c_vp, c_vp, C.c_uint32, c_f32, c_f32, c_f32, c_f32, c_f32, c_vp, c_vp]),
     "tsm_ppo_epoch_dist": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_f32, c_f32, c_f32, c_f32, c_f32, c_vp, c_vp, C.c_uint32, c_vp]),
+    "tsm_global_state": (c_i32, [c_vp, c_i64, c_i32, c_i32, c_i32, c_vp, c_vp]),
+    "tsm_td_target": (c_i32, [c_vp, c_vp, c_i32, c_vp, c_vp, c_f32, c_i64, c_vp, c_vp, c_vp, c_vp]),
     "tsm_net_param_count": (c_i64, [c_i32, c_i32, c_i32]),
     "tsm_net_pack": (c_i32, [c_vp, c_vp]),
     "tsm_ppo_pack_records": (c_i32, [c_vp, c_vp, c_vp, c_vp]),

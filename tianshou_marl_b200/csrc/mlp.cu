@@ -408,7 +408,7 @@ __global__ void __launch_bounds__(THREADS) ppo_minibatch_kernel(PpoArgs a) {
     double l_clip = 0.0, l_vf = 0.0, l_ent = 0.0;
     const float inv_n = 1.0f / (float)a.mb_len;
     float mean = 0.f, rstd = 1.f;
-    if (a.cfg.adv_norm && a.mb_stats) { mean = a.mb_stats[0]; rstd = a.mb_stats[1]; }
+    if ((a.cfg.adv_norm || a.cfg.plain_pg == 2) && a.mb_stats) { mean = a.mb_stats[0]; rstd = a.mb_stats[1]; }
 
     const int64_t n_tiles = (a.mb_len + C::TM - 1) / C::TM;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -431,58 +431,15 @@ __global__ void __launch_bounds__(THREADS) ppo_minibatch_kernel(PpoArgs a) {
             const float4 z0 = *reinterpret_cast<const float4*>(sDOT + r * OUTP);
             const float4 z1 = *reinterpret_cast<const float4*>(sDOT + r * OUTP + 4);
             z[0] = z0.x; z[1] = z0.y; z[2] = z0.z; z[3] = z0.w; z[4] = z1.x; z[5] = z1.y; z[6] = z1.z; z[7] = z1.w;
-            if (a.n_act > 0) {
-                const Soft sm = softmax_row(z, a.n_act);
-                const int act = a.act[s];
-                float lp = 0.f;
-#pragma unroll
-                for (int j = 0; j < OUTP; ++j)
-                    if (j == act) lp = sm.logp[j];
-                float advn = a.adv[s];
-                if (a.cfg.adv_norm) advn = (advn - mean) * rstd;
-                const float ratio = expf(lp - a.logp_old[s]);
-                const float lo = 1.f - a.cfg.eps_clip, hi = 1.f + a.cfg.eps_clip;
-                const float s1 = ratio * advn, s2 = fminf(fmaxf(ratio, lo), hi) * advn;
-                const bool inside = ratio >= lo && ratio <= hi;
-                float clip1 = fminf(s1, s2);
-                float g_ratio = (inside || s1 < s2) ? advn : 0.f;  // d min(s1,s2) / d ratio
-                float li = -clip1;
-                if (a.cfg.dual_clip > 0.f && advn < 0.f) {
-                    const float c2 = a.cfg.dual_clip * advn;
-                    if (c2 > clip1) { li = -c2; g_ratio = 0.f; }
-                }
-                l_clip += (double)li;
-                l_ent += (double)sm.ent;
-                const float dlp = -g_ratio * ratio * inv_n;  // d loss / d logp(act)
-                const float ec = a.cfg.ent_coef * inv_n;
-#pragma unroll
-                for (int j = 0; j < OUTP; ++j)
-                    if (j < a.n_act)
-                        dz[j] = dlp * ((j == act ? 1.f : 0.f) - sm.p[j]) + ec * sm.p[j] * (sm.logp[j] + sm.ent);
-            }
-            if (a.value_index >= 0) {
-                float v = 0.f;
-#pragma unroll
-                for (int j = 0; j < OUTP; ++j)
-                    if (j == a.value_index) v = z[j];
-                const float ret = a.ret[s];
-                float vf = (ret - v) * (ret - v), dv = 2.f * (v - ret);
-                if (a.cfg.value_clip) {
-                    const float vo = a.v_old[s];
-                    const float d = v - vo;
-                    const float vc = vo + fminf(fmaxf(d, -a.cfg.eps_clip), a.cfg.eps_clip);
-                    const float vf2 = (ret - vc) * (ret - vc);
-                    if (vf2 > vf) {
-                        vf = vf2;
-                        dv = (d >= -a.cfg.eps_clip && d <= a.cfg.eps_clip) ? 2.f * (vc - ret) : 0.f;
-                    }
-                }
-                l_vf += (double)vf;
-                const float dvs = a.cfg.vf_coef * inv_n * dv;
-#pragma unroll
-                for (int j = 0; j < OUTP; ++j)
-                    if (j == a.value_index) dz[j] = dvs;
-            }
+            // the loss itself is shared with the tcgen05 engine (ppo_math.cuh); IEEE exp / log / division here
+            const int act = a.n_act > 0 ? a.act[s] : 0;
+            const float adv_s = a.n_act > 0 ? a.adv[s] : 0.f, lpo = a.n_act > 0 ? a.logp_old[s] : 0.f;
+            const float ret_s = a.value_index >= 0 ? a.ret[s] : 0.f;
+            const float vo = (a.value_index >= 0 && a.cfg.value_clip) ? a.v_old[s] : 0.f;
+            const RowLoss rl = row_loss<false>(z, a.n_act, a.value_index, act, adv_s, ret_s, lpo, vo, mean, rstd, a.cfg, inv_n, dz);
+            l_clip += (double)rl.clip;
+            l_ent += (double)rl.ent;
+            l_vf += (double)rl.vf;
         }
         __syncthreads();  // every thread has read its head outputs before the region is reused as dOut^T
         if (threadIdx.x < C::TM) {
@@ -800,7 +757,7 @@ extern "C" int tsm_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch,
     TSM_REQUIRE(net->grads != nullptr, "net.grads != NULL");
     TSM_REQUIRE(mb_start >= 0 && mb_len >= 0, "mb_start, mb_len >= 0");
     if (mb_len == 0) return TSM_OK;
-    TSM_REQUIRE(!cfg->adv_norm || mb_stats, "advantage normalisation needs mb_stats");
+    TSM_REQUIRE(!(cfg->adv_norm || cfg->plain_pg == 2) || mb_stats, "advantage normalisation / plain_pg 2 need mb_stats");
     if (net->engine == 1) return tc_ppo_minibatch(net, batch, cfg, mb_start, mb_len, mb_stats, loss_sums, 0, as_stream(stream));
     TSM_REQUIRE(batch->obs != nullptr, "batch.obs != NULL");
     TSM_REQUIRE(net->n_act == 0 || (batch->act && batch->adv && batch->logp_old), "policy loss needs act / adv / logp_old");
@@ -813,6 +770,7 @@ extern "C" int tsm_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch,
     a.mb_start = mb_start; a.mb_len = mb_len; a.mb_stats = mb_stats;
     a.cfg.eps_clip = cfg->eps_clip; a.cfg.dual_clip = cfg->dual_clip; a.cfg.vf_coef = cfg->vf_coef; a.cfg.ent_coef = cfg->ent_coef;
     a.cfg.value_clip = cfg->value_clip; a.cfg.adv_norm = cfg->adv_norm;
+    a.cfg.plain_pg = cfg->plain_pg; a.cfg.value_heads = cfg->value_heads;
     a.in_dim = net->in_dim; a.out_dim = net->out_dim; a.n_act = net->n_act; a.value_index = net->value_index;
     a.loss_sums = loss_sums;
     return net->hidden == 64 ? launch_ppo<64>(a, as_stream(stream)) : launch_ppo<128>(a, as_stream(stream));
@@ -899,7 +857,7 @@ extern "C" int tsm_ppo_epoch(const tsm_net* net, const tsm_ppo_batch* batch, con
             rc = check_batch(batch, __func__);
             if (rc) return rc;
             TSM_REQUIRE(cfg && net->grads && net->adam_m && net->adam_v && net->adam_step, "cfg / grads / adam state != NULL");
-            TSM_REQUIRE(!cfg->adv_norm || st, "advantage normalisation needs mb_stats");
+            TSM_REQUIRE(!(cfg->adv_norm || cfg->plain_pg == 2) || st, "advantage normalisation / plain_pg 2 need mb_stats");
             static const int no_pdl = getenv("TSM_NO_PDL") != nullptr;
             rc = tc_ppo_minibatch(net, batch, cfg, s0, len, st, ls, m > 0 && !no_pdl, as_stream(stream));
             if (rc) return rc;
@@ -945,7 +903,7 @@ extern "C" int tsm_ppo_epoch_dist(const tsm_net* net, const tsm_ppo_batch* batch
             rc = check_batch(batch, __func__);
             if (rc) return rc;
             TSM_REQUIRE(cfg && local.adam_m && local.adam_v && local.adam_step, "cfg / adam state != NULL");
-            TSM_REQUIRE(!cfg->adv_norm || st, "advantage normalisation needs mb_stats");
+            TSM_REQUIRE(!(cfg->adv_norm || cfg->plain_pg == 2) || st, "advantage normalisation / plain_pg 2 need mb_stats");
             rc = tc_ppo_minibatch(&local, batch, cfg, s0, len, st, ls, m > 0, as_stream(stream));
         } else {
             rc = tsm_ppo_minibatch(&local, batch, cfg, s0, len, st, ls, stream);

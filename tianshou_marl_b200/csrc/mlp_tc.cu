@@ -196,6 +196,7 @@ int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_p
     a.mb_start = mb_start; a.mb_len = mb_len; a.mb_stats = mb_stats;
     a.cfg.eps_clip = cfg->eps_clip; a.cfg.dual_clip = cfg->dual_clip; a.cfg.vf_coef = cfg->vf_coef; a.cfg.ent_coef = cfg->ent_coef;
     a.cfg.value_clip = cfg->value_clip; a.cfg.adv_norm = cfg->adv_norm;
+    a.cfg.plain_pg = cfg->plain_pg; a.cfg.value_heads = cfg->value_heads;
     a.in_dim = net->in_dim; a.out_dim = net->out_dim; a.n_act = net->n_act; a.value_index = net->value_index;
     float sc = 1.0f;  // S = 2^ceil(log2(mb_len)), capped, so that S / mb_len is in (0.5, 1]
     while (sc < (float)mb_len && sc < 1048576.0f) sc *= 2.0f;

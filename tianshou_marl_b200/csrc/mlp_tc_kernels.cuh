@@ -475,7 +475,7 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
     TcSetup s = tc_setup_finish(smem, a.image);
     TRACE(krow, 33);
     float mean = 0.f, rstd = 1.f;
-    if (a.cfg.adv_norm && a.mb_stats) { mean = __ldcg(a.mb_stats); rstd = __ldcg(a.mb_stats + 1); }
+    if ((a.cfg.adv_norm || a.cfg.plain_pg == 2) && a.mb_stats) { mean = __ldcg(a.mb_stats); rstd = __ldcg(a.mb_stats + 1); }
     uint32_t it = 0;
     for (; tile < n_tiles; tile += gridDim.x, ++it) {
         const bool valid = nvalid;

@@ -100,6 +100,10 @@ __device__ __forceinline__ Soft softmax_row(const float* z, int n_act) {
 struct PpoCfg {
     float eps_clip, dual_clip, vf_coef, ent_coef;
     int value_clip, adv_norm;
+    int plain_pg;     // 1: policy term = -logp(act) * adv (one-step actor-critic) instead of the clipped surrogate;
+                      // 2: the reference's literal CTDEPolicy.learn, where logp [n] * adv [n,1] broadcasts to [n,n]
+                      //    (ctde.py:181-183): every row is weighted by the minibatch MEAN advantage (mb_stats[0])
+    int value_heads;  // > 1: the value is the mean of that many head outputs from value_index on (ctde.py:153-156)
 };
 
 
@@ -122,30 +126,39 @@ __device__ __forceinline__ RowLoss row_loss(const float (&z)[OUTP], int n_act, i
             if (j == act) lp = sm.logp[j];
         float advn = adv;
         if (cfg.adv_norm) advn = (advn - mean) * rstd;
-        const float ratio = exp_t<FAST>(lp - logp_old);
-        const float lo = 1.f - cfg.eps_clip, hi = 1.f + cfg.eps_clip;
-        const float s1 = ratio * advn, s2 = fminf(fmaxf(ratio, lo), hi) * advn;
-        const bool inside = ratio >= lo && ratio <= hi;
-        const float clip1 = fminf(s1, s2);
-        float g_ratio = (inside || s1 < s2) ? advn : 0.f;  // d min(s1,s2) / d ratio
-        float li = -clip1;
-        if (cfg.dual_clip > 0.f && advn < 0.f) {
-            const float c2 = cfg.dual_clip * advn;
-            if (c2 > clip1) { li = -c2; g_ratio = 0.f; }
+        if (cfg.plain_pg == 2) advn = mean;
+        float li, dlp;  // loss term of this row and d loss / d logp(act)
+        if (cfg.plain_pg) {
+            li = -lp * advn;
+            dlp = -advn * inv_n;
+        } else {
+            const float ratio = exp_t<FAST>(lp - logp_old);
+            const float lo = 1.f - cfg.eps_clip, hi = 1.f + cfg.eps_clip;
+            const float s1 = ratio * advn, s2 = fminf(fmaxf(ratio, lo), hi) * advn;
+            const bool inside = ratio >= lo && ratio <= hi;
+            const float clip1 = fminf(s1, s2);
+            float g_ratio = (inside || s1 < s2) ? advn : 0.f;  // d min(s1,s2) / d ratio
+            li = -clip1;
+            if (cfg.dual_clip > 0.f && advn < 0.f) {
+                const float c2 = cfg.dual_clip * advn;
+                if (c2 > clip1) { li = -c2; g_ratio = 0.f; }
+            }
+            dlp = -g_ratio * ratio * inv_n;
         }
         out.clip = li;
         out.ent = sm.ent;
-        const float dlp = -g_ratio * ratio * inv_n;  // d loss / d logp(act)
         const float ec = cfg.ent_coef * inv_n;
 #pragma unroll
         for (int j = 0; j < OUTP; ++j)
             if (j < n_act) dz[j] = dlp * ((j == act ? 1.f : 0.f) - sm.p[j]) + ec * sm.p[j] * (sm.logp[j] + sm.ent);
     }
     if (value_index >= 0) {
+        const int nh = cfg.value_heads > 1 ? cfg.value_heads : 1;
         float v = 0.f;
 #pragma unroll
         for (int j = 0; j < OUTP; ++j)
-            if (j == value_index) v = z[j];
+            if (j >= value_index && j < value_index + nh) v += z[j];
+        v /= (float)nh;
         float vf = (ret - v) * (ret - v), dv = 2.f * (v - ret);
         if (cfg.value_clip) {
             const float d = v - v_old;
@@ -157,10 +170,10 @@ __device__ __forceinline__ RowLoss row_loss(const float (&z)[OUTP], int n_act, i
             }
         }
         out.vf = vf;
-        const float dvs = cfg.vf_coef * inv_n * dv;
+        const float dvs = cfg.vf_coef * inv_n * dv / (float)nh;
 #pragma unroll
         for (int j = 0; j < OUTP; ++j)
-            if (j == value_index) dz[j] = dvs;
+            if (j >= value_index && j < value_index + nh) dz[j] = dvs;
     }
     return out;
 }
