@@ -257,7 +257,7 @@ typedef struct tsm_net {
                            image of params.  Refreshed by tsm_adam_step / tsm_ppo_epoch; call tsm_net_pack
                            after writing params any other way. */
 } tsm_net;
-#define TSM_TC_IMAGE_BYTES 16896
+#define TSM_TC_IMAGE_BYTES 45056 /* 16 896 image + room for a second gradient buffer (<= 6 792 floats) used by tsm_ppo_epoch */
 
 int64_t tsm_net_param_count(int in_dim, int hidden, int out_dim);
 
@@ -296,6 +296,12 @@ typedef struct tsm_ppo_batch {
     int64_t perm_n;
     const void* records;     /* engine 1: [size][n_rows] packed rows built by tsm_ppo_pack_records (required by engine 1's
                                 tsm_ppo_minibatch / tsm_ppo_epoch; ignored by engine 0) */
+    int32_t* slots;          /* optional device scratch [>= number of batch positions, len * n_rows or the length of indices]:
+                                the SLOT TABLE of this view, slots[p] = storage slot (t * n_rows + row) of batch position p.
+                                Filled by tsm_ppo_slot_table, or as a by-product by tsm_ppo_adv_stats for the positions it
+                                visits; engine 1's tsm_ppo_minibatch / tsm_ppo_epoch then read it instead of evaluating the
+                                permutation per row.  The caller refills it whenever perm_key / perm_n / start / len /
+                                indices change.  NULL: computed in the kernels.  Needs size * n_rows < 2^31. */
 } tsm_ppo_batch;
 
 /* Engine 1 gathers each minibatch row as ONE 96-byte record (3 sectors, one page) instead of 7-8 sectors spread over
@@ -317,6 +323,9 @@ typedef struct tsm_ppo_cfg {
     int32_t value_heads; /* > 1: value = mean of that many head outputs from value_index on (ctde.py:153-156) */
 } tsm_ppo_cfg;
 
+/* batch->slots[p] = storage slot of batch position p for p in [p0, p0 + n) (see tsm_ppo_batch.slots). */
+int tsm_ppo_slot_table(const tsm_ppo_batch* batch, int64_t p0, int64_t n, tsm_stream_t stream);
+
 /* per-minibatch {mean, 1/(std_unbiased + eps)} of adv: mb_bounds (device) [n_minibatches+1]
  * batch positions; stats_out [n_minibatches][2]. */
 int tsm_ppo_adv_stats(const tsm_ppo_batch* batch, const int64_t* mb_bounds, int64_t n_minibatches, float eps,
@@ -335,7 +344,8 @@ int tsm_adam_step(const tsm_net* net, float lr, float beta1, float beta2, float 
                   float grad_scale, float* grad_norm_out, tsm_stream_t stream);
 
 /* one epoch on one GPU: for each minibatch m: tsm_ppo_minibatch then tsm_adam_step (engine 1 runs the
- * optimizer step in the tail of the minibatch kernel, in the last CTA to finish: one launch per minibatch).
+ * whole epoch as ONE persistent cooperative launch when the minibatches are uniform -- optimizer steps spread over the
+ * grid between grid-wide barriers -- and otherwise as a chain of programmatic dependent launches).
  * h_mb_bounds is a HOST array [n_minibatches+1]; mb_stats [n_minibatches][2] and loss_sums
  * [n_minibatches][4] are device arrays (either may be NULL). */
 int tsm_ppo_epoch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, const int64_t* h_mb_bounds,

@@ -195,3 +195,88 @@ def test_update_tc_tracks_fp32():
     for k in ("loss", "vf", "ent", "clip"):
         assert np.allclose(out["tc"][k], out["fp32"][k], rtol=3e-2, atol=3e-3), (k, np.abs(out["tc"][k] - out["fp32"][k]).max())
     assert out["tc"]["vf"][-1] < out["tc"]["vf"][0]
+
+
+def test_slot_table_matches_oracle_permutation():
+    """tsm_ppo_slot_table / the adv_stats by-product: slots[p] = storage slot of batch position p (lock-step ring view,
+    Feistel permutation restated in oracle/philox.py; explicit indices)."""
+    from oracle.philox import feistel_permute
+    from tianshou_marl_b200 import _lib
+
+    P, L, S = _lib.ptr, _lib.lib(), _lib.stream_ptr()
+    size, R, start, ln = 7, 53, 5, 4
+    B = ln * R
+    key = 0x1234ABCD5678EF
+    adv = torch.randn(size * R, device="cuda")
+    slots = torch.full((B,), -1, dtype=torch.int32, device="cuda")
+    pb = _lib.TsmPpoBatch(obs=None, act=None, adv=P(adv), ret=None, logp_old=None, v_old=None, indices=None, size=size, n_rows=R, start=start,
+                          len=ln, perm_key=key, perm_n=B, records=None, slots=P(slots))
+    q = feistel_permute(np.arange(B, dtype=np.uint64), B, key).astype(np.int64)
+    row, j = q // ln, q % ln
+    want = ((start + j) % size) * R + row
+    _lib.check(L.tsm_ppo_slot_table(C.byref(pb), 0, B, S))
+    assert np.array_equal(slots.cpu().numpy(), want)
+    # by-product of adv_stats: only the visited positions are written
+    slots.fill_(-1)
+    bounds = torch.tensor([10, 100, B - 3], dtype=torch.int64, device="cuda")
+    stats = torch.zeros(2, 2, device="cuda")
+    _lib.check(L.tsm_ppo_adv_stats(C.byref(pb), P(bounds), 2, 1e-8, P(stats), S))
+    got = slots.cpu().numpy()
+    assert np.array_equal(got[10:B - 3], want[10:B - 3]) and (got[:10] == -1).all() and (got[B - 3:] == -1).all()
+    a = adv.cpu().numpy()[want[10:100]]
+    assert np.allclose(stats.cpu().numpy()[0], [a.mean(), 1.0 / (a.std(ddof=1) + 1e-8)], rtol=1e-5)
+    # explicit env-major indices (i = row * size + t)
+    idx = torch.randperm(size * R, device="cuda")[:B].contiguous()
+    pb.indices, pb.perm_n = P(idx), 0
+    _lib.check(L.tsm_ppo_slot_table(C.byref(pb), 0, B, S))
+    i = idx.cpu().numpy()
+    assert np.array_equal(slots.cpu().numpy(), (i % size) * R + i // size)
+
+
+@pytest.mark.parametrize("n_mb,mb", [(5, 1024), (3, 20000), (1, 700)])
+def test_epoch_slot_table_and_launch_chain_agree(n_mb, mb, monkeypatch):
+    """tsm_ppo_epoch, engine 1: the persistent launch (with and without a slot table) and the chain of dependent launches give
+    the same parameters after an epoch (the last minibatch is longer: Batch.split merge_last)."""
+    from tianshou_marl_b200 import _lib
+    from tianshou_marl_b200.utils import ActorCriticNet
+
+    P, L, S = _lib.ptr, _lib.lib(), _lib.stream_ptr()
+    O, size = 18, 4
+    total = n_mb * mb + (77 if n_mb > 1 else 0)
+    R = (total + size - 1) // size
+    B = size * R
+    g = torch.Generator(device="cuda").manual_seed(n_mb)
+    obs = torch.randn(B, O, device="cuda", generator=g)
+    act = torch.randint(0, 5, (B,), device="cuda", generator=g, dtype=torch.int32)
+    adv, ret = torch.randn(B, device="cuda", generator=g), torch.randn(B, device="cuda", generator=g)
+    lp = torch.full((B,), float(np.log(0.2)), device="cuda")
+    bounds = np.array([m * mb for m in range(n_mb)] + [total], dtype=np.int64)
+    hb = bounds.ctypes.data_as(C.c_void_p)
+    bounds_dev = torch.as_tensor(bounds, device="cuda")
+    pc = _lib.TsmPpoCfg(eps_clip=0.2, dual_clip=0.0, vf_coef=0.5, ent_coef=0.01, value_clip=0, adv_norm=1)
+    res = {}
+    for variant in ("chain", "persistent", "persistent+slots"):
+        if variant == "chain":
+            monkeypatch.setenv("TSM_NO_PERSISTENT", "1")
+        else:
+            monkeypatch.delenv("TSM_NO_PERSISTENT", raising=False)
+        net = ActorCriticNet(O, 64, 5, seed=9, engine="tc")
+        slots = torch.full((B,), -1, dtype=torch.int32, device="cuda")
+        pb = _lib.TsmPpoBatch(obs=P(obs), act=P(act), adv=P(adv), ret=P(ret), logp_old=P(lp), v_old=None, indices=None, size=size, n_rows=R,
+                              start=0, len=size, perm_key=99, perm_n=B, records=None, slots=P(slots) if variant.endswith("slots") else None)
+        rec = torch.empty(B, _lib.PPO_RECORD_BYTES, dtype=torch.uint8, device="cuda")
+        _lib.check(L.tsm_ppo_pack_records(net.desc, C.byref(pb), P(rec), S))
+        pb.records = P(rec)
+        stats = torch.zeros(n_mb, 2, device="cuda")
+        sums = torch.zeros(n_mb, 4, dtype=torch.float64, device="cuda")
+        _lib.check(L.tsm_ppo_adv_stats(C.byref(pb), P(bounds_dev), n_mb, 1e-8, P(stats), S))
+        _lib.check(L.tsm_ppo_epoch(net.desc, C.byref(pb), C.byref(pc), hb, n_mb, P(stats), 1e-3, 0.9, 0.999, 1e-8, 0.5, P(sums), S))
+        torch.cuda.synchronize()
+        res[variant] = (net.flat.detach().clone(), sums.cpu().numpy(), int(net.adam_step.item()), net.grads.abs().max().item())
+    for variant in ("persistent", "persistent+slots"):
+        assert res[variant][2] == n_mb and res[variant][3] == 0.0
+        # same arithmetic, different summation order of the gradient reductions / the norm.  Adam's first steps move a
+        # parameter by about lr * sign(g), so an entry whose gradient is rounding noise may differ by up to 2 * lr per step
+        diff = (res[variant][0] - res["chain"][0]).abs()
+        assert (diff < 2e-5).float().mean().item() > 0.995 and diff.max().item() < 2e-3 * n_mb + 1e-6, (variant, diff.max())
+        assert np.allclose(res[variant][1], res["chain"][1], rtol=1e-4, atol=1e-3)

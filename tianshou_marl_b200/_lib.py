@@ -42,7 +42,7 @@ class TsmMpe(C.Structure):
     ]
 
 
-TC_IMAGE_BYTES = 16896  # TSM_TC_IMAGE_BYTES
+TC_IMAGE_BYTES = 45056  # TSM_TC_IMAGE_BYTES
 PPO_RECORD_BYTES = 96  # TSM_PPO_RECORD_BYTES
 
 
@@ -80,7 +80,7 @@ class TsmPpoBatch(C.Structure):
     _fields_ = [
         ("obs", c_vp), ("act", c_vp), ("adv", c_vp), ("ret", c_vp), ("logp_old", c_vp), ("v_old", c_vp), ("indices", c_vp),
         ("size", c_i64), ("n_rows", c_i64), ("start", c_i64), ("len", c_i64), ("perm_key", C.c_uint64), ("perm_n", c_i64),
-        ("records", c_vp),
+        ("records", c_vp), ("slots", c_vp),
     ]
 
 
@@ -122,6 +122,7 @@ _SIGS = {
     "tsm_net_pack": (c_i32, [c_vp, c_vp]),
     "tsm_ppo_pack_records": (c_i32, [c_vp, c_vp, c_vp, c_vp]),
     "tsm_net_forward": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_u64, c_u64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "tsm_ppo_slot_table": (c_i32, [c_vp, c_i64, c_i64, c_vp]),
     "tsm_ppo_adv_stats": (c_i32, [c_vp, c_vp, c_i64, c_f32, c_vp, c_vp]),
     "tsm_ppo_minibatch": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i64, c_vp, c_vp, c_vp]),
     "tsm_adam_step": (c_i32, [c_vp, c_f32, c_f32, c_f32, c_f32, c_f32, c_f32, c_vp, c_vp]),

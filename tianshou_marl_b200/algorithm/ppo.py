@@ -264,6 +264,8 @@ class PPO:
             _lib.check(L.tsm_ppo_pack_records(net.desc, C.byref(pb), P(rec), S))
             pb.records = P(rec)
             _lib.t_stop(tk)
+            if size * R < 2**31:  # slot table of the epoch's permutation: filled by adv_stats as a by-product, read by the tiles
+                pb.slots = P(self._buf("slots", (B,), torch.int32))
         world = torch.distributed.get_world_size() if torch.distributed.is_available() and torch.distributed.is_initialized() else 1
         o = self.optim
         mgn = float(self.max_grad_norm) if self.max_grad_norm else 0.0
@@ -292,6 +294,8 @@ class PPO:
                 tk = _lib.t_start("adv_stats")
                 _lib.check(L.tsm_ppo_adv_stats(C.byref(pb), P(bounds_dev), n_mb, self._eps, P(st_ep), S))
                 _lib.t_stop(tk)
+            elif pb.slots:
+                _lib.check(L.tsm_ppo_slot_table(C.byref(pb), 0, B, S))
             tk = _lib.t_start("ppo_epoch")
             if world > 1 and self.grad_sync != "nccl" and self._peers is None:
                 try:

@@ -549,7 +549,7 @@ constexpr int STATS_THREADS = 1024;
 constexpr int STATS_UNROLL = 8;
 __global__ void __launch_bounds__(STATS_THREADS) adv_stats_kernel(const float* __restrict__ adv, BatchView view,
                                                                  const int64_t* __restrict__ mb_bounds, float eps,
-                                                                 float* __restrict__ stats) {
+                                                                 float* __restrict__ stats, int32_t* __restrict__ slots) {
     const int64_t s0 = mb_bounds[blockIdx.x], s1 = mb_bounds[blockIdx.x + 1];
     double sum = 0.0, sq = 0.0;
     for (int64_t p0 = s0 + threadIdx.x; p0 < s1; p0 += (int64_t)STATS_THREADS * STATS_UNROLL) {
@@ -557,7 +557,12 @@ __global__ void __launch_bounds__(STATS_THREADS) adv_stats_kernel(const float* _
 #pragma unroll
         for (int u = 0; u < STATS_UNROLL; ++u) {
             const int64_t p = p0 + (int64_t)u * STATS_THREADS;
-            v[u] = p < s1 ? __ldg(adv + slot_of(view, p)) : 0.f;
+            v[u] = 0.f;
+            if (p < s1) {
+                const int64_t slot = slot_of(view, p);
+                v[u] = __ldg(adv + slot);
+                if (slots) slots[p] = (int32_t)slot;  // the slot table as a by-product (tsm_ppo_batch.slots)
+            }
         }
 #pragma unroll
         for (int u = 0; u < STATS_UNROLL; ++u) {
@@ -584,6 +589,11 @@ __global__ void __launch_bounds__(STATS_THREADS) adv_stats_kernel(const float* _
         stats[2 * blockIdx.x] = (float)mean;
         stats[2 * blockIdx.x + 1] = (float)(1.0 / (sqrt(var) + (double)eps));
     }
+}
+
+__global__ void __launch_bounds__(256) slot_table_kernel(BatchView view, int64_t p0, int64_t n, int32_t* __restrict__ slots) {
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256)
+        slots[p0 + i] = (int32_t)slot_of(view, p0 + i);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -617,6 +627,9 @@ int tc_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int6
                    uint64_t counter, float* out, int32_t* act, float* logp, float* value, float* entropy, cudaStream_t s);
 int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, int64_t mb_start, int64_t mb_len,
                      const float* mb_stats, double* loss_sums, int pdl, cudaStream_t s);
+int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, int64_t start, int64_t mb_size,
+                            int64_t n_mb, int64_t total, const float* mb_stats, double* loss_sums, const opt::AdamArgs& adam,
+                            cudaStream_t s);
 }  // namespace tsm
 
 using namespace tsm;
@@ -716,7 +729,20 @@ extern "C" int tsm_ppo_adv_stats(const tsm_ppo_batch* batch, const int64_t* mb_b
     if (n_minibatches == 0) return TSM_OK;
     TSM_REQUIRE(batch->adv && mb_bounds && stats_out, "adv / mb_bounds / stats_out != NULL");
     adv_stats_kernel<<<(unsigned)n_minibatches, STATS_THREADS, 0, as_stream(stream)>>>(batch->adv, make_view(batch), mb_bounds, eps,
-                                                                                stats_out);
+                                                                                stats_out, slots_of(batch));
+    TSM_LAUNCH_CHECK();
+    return TSM_OK;
+}
+
+extern "C" int tsm_ppo_slot_table(const tsm_ppo_batch* batch, int64_t p0, int64_t n, tsm_stream_t stream) {
+    int rc = check_batch(batch, __func__);
+    if (rc) return rc;
+    TSM_REQUIRE(batch->slots != nullptr, "batch.slots != NULL");
+    TSM_REQUIRE(batch->size * batch->n_rows < (int64_t)1 << 31, "size * n_rows < 2^31");
+    TSM_REQUIRE(p0 >= 0 && n >= 0, "p0, n >= 0");
+    if (n == 0) return TSM_OK;
+    const unsigned grid = (unsigned)std::min<int64_t>(ceil_div(n, 256), (int64_t)sm_count() * 8);
+    slot_table_kernel<<<grid, 256, 0, as_stream(stream)>>>(make_view(batch), p0, n, batch->slots);
     TSM_LAUNCH_CHECK();
     return TSM_OK;
 }
@@ -845,6 +871,26 @@ extern "C" int tsm_ppo_epoch(const tsm_net* net, const tsm_ppo_batch* batch, con
                              int64_t n_minibatches, const float* mb_stats, float lr, float beta1, float beta2, float eps,
                              float max_grad_norm, double* loss_sums, tsm_stream_t stream) {
     TSM_REQUIRE(h_mb_bounds != nullptr && n_minibatches >= 0, "h_mb_bounds != NULL");
+    if (net && net->engine == 1 && n_minibatches >= 1 && !getenv("TSM_NO_PERSISTENT")) {
+        // uniform minibatches (Batch.split with merge_last: all of size bs, the last one possibly longer): one persistent
+        // cooperative launch runs the whole epoch, optimizer steps included (mlp_tc_kernels.cuh: tc_ppo_epoch_kernel)
+        const int64_t bs = h_mb_bounds[1] - h_mb_bounds[0];
+        bool uniform = bs > 0;
+        for (int64_t m = 1; m + 1 < n_minibatches && uniform; ++m) uniform = h_mb_bounds[m + 1] - h_mb_bounds[m] == bs;
+        if (uniform && n_minibatches > 1) uniform = h_mb_bounds[n_minibatches] - h_mb_bounds[n_minibatches - 1] >= bs;
+        if (uniform) {
+            int rc = check_net(net, __func__);
+            if (rc) return rc;
+            rc = check_batch(batch, __func__);
+            if (rc) return rc;
+            TSM_REQUIRE(cfg && net->grads && net->adam_m && net->adam_v && net->adam_step, "cfg / grads / adam state != NULL");
+            TSM_REQUIRE(!(cfg->adv_norm || cfg->plain_pg == 2) || mb_stats, "advantage normalisation / plain_pg 2 need mb_stats");
+            rc = tc_ppo_epoch_persistent(net, batch, cfg, h_mb_bounds[0], bs, n_minibatches, h_mb_bounds[n_minibatches] - h_mb_bounds[0],
+                                         mb_stats, loss_sums, adam_args(net, lr, beta1, beta2, eps, max_grad_norm, 1.0f, nullptr),
+                                         as_stream(stream));
+            if (rc <= 0) return rc;  // done, or a real error; rc == 1: not launchable here, fall through
+        }
+    }
     for (int64_t m = 0; m < n_minibatches; ++m) {
         const int64_t s0 = h_mb_bounds[m], len = h_mb_bounds[m + 1] - h_mb_bounds[m];
         const float* st = mb_stats ? mb_stats + 2 * m : nullptr;

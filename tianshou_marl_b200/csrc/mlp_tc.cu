@@ -191,7 +191,7 @@ int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_p
     mlptc::TcPpoArgs a{};
     a.image = reinterpret_cast<const unsigned char*>(net->tc_image); a.grads = net->grads;
     if (!batch->records) return fail(TSM_ERR_INVALID, "%s: engine 1 needs batch.records (tsm_ppo_pack_records)", __func__);
-    a.records = reinterpret_cast<const unsigned char*>(batch->records);
+    a.records = reinterpret_cast<const unsigned char*>(batch->records); a.slots = ppo::slots_of(batch);
     a.view = ppo::make_batch_view(batch->indices, batch->size, batch->n_rows, batch->start, batch->len, batch->perm_key, batch->perm_n);
     a.mb_start = mb_start; a.mb_len = mb_len; a.mb_stats = mb_stats;
     a.cfg.eps_clip = cfg->eps_clip; a.cfg.dual_clip = cfg->dual_clip; a.cfg.vf_coef = cfg->vf_coef; a.cfg.ent_coef = cfg->ent_coef;
@@ -204,8 +204,9 @@ int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_p
     a.loss_sums = loss_sums;
     static const int dbg = getenv("TSM_TC_DEBUG") ? atoi(getenv("TSM_TC_DEBUG")) : 0;
     a.debug = dbg;
-    const size_t smem = mlptc::SM_TOTAL + 128;  // ~101 KB: two CTAs per SM (2 x 256 TMEM columns)
-    static_assert(mlptc::SM_TOTAL + 128 <= 112 * 1024 && mlptc::SM_TOTAL > 76 * 1024, "smem map must give exactly two CTAs per SM");
+    const size_t smem = mlptc::SM_TOTAL;  // ~113 KB: two CTAs per SM (2 x 256 TMEM columns); 1 KB per CTA is reserved by the driver
+    static_assert(2 * (mlptc::SM_TOTAL + 1024) <= 228 * 1024 && 3 * (mlptc::SM_TOTAL + 1024) > 228 * 1024,
+                  "smem map must give exactly two CTAs per SM");
     static bool attr = false;
     if (!attr) {
         TSM_CUDA(cudaFuncSetAttribute(mlptc::tc_ppo_minibatch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -234,6 +235,81 @@ int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_p
             printf("kernel row %d: begin->setupA %lld ->prefetch issued %lld ->setup done %lld | tiles %lld | staging %lld reduce+sync %lld dealloc %lld atomics %lld | total %lld\n",
                    row, h[row][31] - h[row][30], h[row][32] - h[row][31], h[row][33] - h[row][32], h[row][34] - h[row][33], h[row][35] - h[row][34],
                    h[row][36] - h[row][35], h[row][37] - h[row][36], h[row][38] - h[row][37], h[row][38] - h[row][30]);
+    }
+#endif
+    return TSM_OK;
+}
+
+
+// One cooperative launch for a whole epoch of uniform minibatches; returns 1 (not an error) when the launch cannot be used
+// (no cooperative launch support, grid not co-resident) so that the caller falls back to one launch pair per minibatch.
+int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, int64_t start, int64_t mb_size,
+                            int64_t n_mb, int64_t total, const float* mb_stats, double* loss_sums, const opt::AdamArgs& adam,
+                            cudaStream_t s) {
+    int rc = tc_check_net(net, __func__);
+    if (rc) return rc;
+    if (!batch->records) return fail(TSM_ERR_INVALID, "%s: engine 1 needs batch.records (tsm_ppo_pack_records)", __func__);
+    if (reinterpret_cast<uintptr_t>(net->grads) & 15) return fail(TSM_ERR_INVALID, "%s: grads must be 16-byte aligned", __func__);
+    if (adam.n > (int64_t)mlptc::EP_NORM_LOADS * mlptc::EP_THREADS * 4) return 1;
+    static int coop = -1, occ = 0;
+    const size_t smem = mlptc::SM_EP_TOTAL;
+    if (coop < 0) {
+        int dev = 0;
+        TSM_CUDA(cudaGetDevice(&dev));
+        TSM_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+        TSM_CUDA(cudaFuncSetAttribute(mlptc::tc_ppo_epoch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        TSM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mlptc::tc_ppo_epoch_kernel, mlptc::EP_THREADS, smem));
+        if (occ > 1) occ = 1;  // one CTA owns the SM's 512 TMEM columns
+    }
+    if (!coop || occ < 1) return 1;
+    mlptc::TcEpochArgs e{};
+    mlptc::TcPpoArgs& a = e.p;
+    a.image = reinterpret_cast<const unsigned char*>(net->tc_image); a.grads = net->grads;
+    a.records = reinterpret_cast<const unsigned char*>(batch->records); a.slots = ppo::slots_of(batch);
+    a.view = ppo::make_batch_view(batch->indices, batch->size, batch->n_rows, batch->start, batch->len, batch->perm_key, batch->perm_n);
+    a.mb_start = start; a.mb_len = mb_size; a.mb_stats = nullptr;
+    a.cfg.eps_clip = cfg->eps_clip; a.cfg.dual_clip = cfg->dual_clip; a.cfg.vf_coef = cfg->vf_coef; a.cfg.ent_coef = cfg->ent_coef;
+    a.cfg.value_clip = cfg->value_clip; a.cfg.adv_norm = cfg->adv_norm;
+    a.cfg.plain_pg = cfg->plain_pg; a.cfg.value_heads = cfg->value_heads;
+    a.in_dim = net->in_dim; a.out_dim = net->out_dim; a.n_act = net->n_act; a.value_index = net->value_index;
+    a.gscale = 1.f; a.inv_gscale = 1.f; a.loss_sums = nullptr;
+    a.debug = getenv("TSM_TC_DEBUG") ? atoi(getenv("TSM_TC_DEBUG")) : 0;
+    e.grads1 = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(net->tc_image) + opt::IMG_BYTES);
+    e.n_mb = n_mb; e.mb_size = mb_size; e.total = total; e.mb_stats = mb_stats; e.loss_sums = loss_sums; e.adam = adam;
+    const int64_t tiles = ceil_div(n_mb > 1 ? mb_size : total, mlptc::TC_ROWS);
+    const unsigned grid = (unsigned)std::min<int64_t>(ceil_div(tiles, (int64_t)mlptc::TC_GROUPS), (int64_t)sm_count() * occ);
+    void* args[] = {&e};
+    const cudaError_t err = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(mlptc::tc_ppo_epoch_kernel), dim3(grid),
+                                                        dim3(mlptc::EP_THREADS), args, smem, s);
+    if (err == cudaErrorCooperativeLaunchTooLarge) {
+        cudaGetLastError();
+        return 1;
+    }
+    TSM_CUDA(err);
+#ifdef TSM_TC_TRACE
+    if (getenv("TSM_TC_TRACE_DUMP")) {
+        long long h[4][64];
+        cudaDeviceSynchronize();
+        cudaMemcpyFromSymbol(h, mlptc::g_trace, sizeof(h));
+        for (int row = 0; row < 4; ++row) {
+            printf("epoch tile row %d:", row);
+            for (int k = 1; k < 24; ++k) printf(" %lld", h[row][k] - h[row][k - 1]);
+            printf("  total %lld\n", h[row][23] - h[row][0]);
+        }
+        {
+            cudaFuncAttributes fa;
+            cudaFuncGetAttributes(&fa, mlptc::tc_ppo_epoch_kernel);
+            printf("grid %u x %d threads, occ %d, smem %zu, regs %d\n", grid, mlptc::EP_THREADS, occ, smem, fa.numRegs);
+        }
+        for (int row = 0; row < 3; ++row)
+            printf("tile row %d: store_rec %lld prefetch-issue %lld to-forward %lld\n", row, h[row][24] - h[row][0], h[row][25] - h[row][24],
+                   h[row][1] - h[row][25]);
+        printf("abs offsets from slot40 (CTA0): tile0 start %lld end %lld | tile1 start %lld end %lld | loop end %lld\n", h[0][0] - h[0][40],
+               h[0][23] - h[0][40], h[1][0] - h[0][40], h[1][23] - h[0][40], h[0][41] - h[0][40]);
+        for (int row = 0; row < 4; row += 2)
+            printf("epoch row %d (minibatch 2): tiles %lld flush-stage %lld atomics %lld sync1 %lld norm %lld adam %lld sync2 %lld zero+image %lld | total %lld\n",
+                   row, h[row][41] - h[row][40], 0LL, h[row][42] - h[row][41], h[row][43] - h[row][42], h[row][44] - h[row][43],
+                   h[row][45] - h[row][44], h[row][46] - h[row][45], h[row][47] - h[row][46], h[row][47] - h[row][40]);
     }
 #endif
     return TSM_OK;

@@ -43,11 +43,13 @@ constexpr int SM_W3 = SM_IMG + opt::IMG_W3 * 2;
 constexpr int SM_B2I = SM_IMG + opt::IMG_B2 * 2;
 constexpr int SM_B3I = SM_IMG + opt::IMG_B3 * 2;
 constexpr int SM_RED = SM_IMG + opt::IMG_BYTES;  // 4 warps x 8 floats + 4 x 3 doubles
-constexpr int SM_BAR = SM_RED + 384;             // 2 mbarriers + tmem base
+constexpr int SM_BAR = SM_RED + 384;             // mbarriers at +0 (MMA, waited), +8 (weight-gradient MMAs), +24 (records); TMEM base at +16
 constexpr int SM_FWD_TOTAL = SM_BAR + 64;        // the forward kernel stops here (~69 KB: three CTAs per SM)
 constexpr int SM_D2 = SM_FWD_TOTAL;              // 16 KB  (backward only)
 constexpr int SM_D1 = SM_D2 + 8 * CHUNK_B;       // 16 KB
-constexpr int SM_TOTAL = SM_D1 + 8 * CHUNK_B;    // ~101 KB: two CTAs per SM
+constexpr int REC_BYTES = 96;  // halves x[32] | float adv, ret, logp_old | int32 act | float v_old | 12 bytes pad
+constexpr int SM_REC = SM_D1 + 8 * CHUNK_B;      // 12 KB: the next tile's batch records, landed by TMA bulk copies
+constexpr int SM_TOTAL = SM_REC + TC_ROWS * REC_BYTES;  // 115,648 B: still two CTAs per SM (2 x (this + 1 KB) <= 228 KB)
 constexpr int SM_STAGE = SM_H2;                  // flush staging: fp32 copy of the flat gradient (<= 32 KB)
 
 // TMEM columns (fp32 accumulators, 128 lanes)
@@ -58,6 +60,16 @@ constexpr uint32_t TM_GW1 = 160;   // 32
 constexpr uint32_t TM_GW3 = 192;   // 16
 constexpr uint32_t TM_COLS_BWD = 256;
 constexpr uint32_t TM_COLS_FWD = 128;
+
+// A "group" is one 128-thread warpgroup working on one tile.  The forward and minibatch kernels run one group per CTA;
+// the persistent epoch kernel runs TC_GROUPS of them per CTA, each with its own shared-memory map, TMEM columns,
+// mbarriers and named barrier (id 1 + group), so every helper below addresses by group-local thread index.
+constexpr int TC_GROUPS = 2;
+__device__ __forceinline__ int tc_tid() { return (int)(threadIdx.x & (TC_THREADS - 1)); }
+__device__ __forceinline__ int tc_grp() { return (int)(threadIdx.x / TC_THREADS); }
+__device__ __forceinline__ void tc_group_sync() {
+    asm volatile("bar.sync %0, %1;" ::"r"(1 + tc_grp()), "n"(TC_THREADS) : "memory");
+}
 
 __device__ __forceinline__ uint32_t h2_bits(__half2 h) { return *reinterpret_cast<const uint32_t*>(&h); }
 __device__ __forceinline__ uint32_t pack_h2(float a, float b) { return h2_bits(__floats2half2_rn(a, b)); }
@@ -74,7 +86,7 @@ __device__ __forceinline__ void tc_store_x(unsigned char* smem, int xoff, const 
         v.y = pack_h2(x[8 * c + 2], x[8 * c + 3]);
         v.z = pack_h2(x[8 * c + 4], x[8 * c + 5]);
         v.w = pack_h2(x[8 * c + 6], x[8 * c + 7]);
-        *reinterpret_cast<uint4*>(smem + xoff + c * CHUNK_B + threadIdx.x * 16) = v;
+        *reinterpret_cast<uint4*>(smem + xoff + c * CHUNK_B + tc_tid() * 16) = v;
     }
 }
 
@@ -114,7 +126,7 @@ __device__ __forceinline__ void tc_epilogue_relu(unsigned char* smem, uint32_t t
             w.y = pack_relu_h2(v[8 * h + 2], v[8 * h + 3]);
             w.z = pack_relu_h2(v[8 * h + 4], v[8 * h + 5]);
             w.w = pack_relu_h2(v[8 * h + 6], v[8 * h + 7]);
-            *reinterpret_cast<uint4*>(smem + dst + (4 * q + h) * CHUNK_B + threadIdx.x * 16) = w;
+            *reinterpret_cast<uint4*>(smem + dst + (4 * q + h) * CHUNK_B + tc_tid() * 16) = w;
         }
     }
 }
@@ -128,7 +140,7 @@ __device__ __forceinline__ void tc_epilogue_mask(unsigned char* smem, uint32_t t
         tc::tmem_ld32(tmem_lane_base + TM_SCR + 32 * q, v);
 #pragma unroll
         for (int h = 0; h < 4; ++h) {
-            const int cell = (4 * q + h) * CHUNK_B + threadIdx.x * 16;
+            const int cell = (4 * q + h) * CHUNK_B + tc_tid() * 16;
             const uint4 m = *reinterpret_cast<const uint4*>(smem + img + cell);
             const __half2* mh = reinterpret_cast<const __half2*>(&m);
             uint4 w;
@@ -165,7 +177,7 @@ __device__ __forceinline__ uint64_t desc_w_mn(uint32_t sb4, int off, int n_out, 
 __device__ __forceinline__ void tc_sync_for_mma() {
     tc::fence_async_smem();
     tc::fence_before_sync();
-    __syncthreads();
+    tc_group_sync();
     tc::fence_after_sync();
 }
 
@@ -196,45 +208,52 @@ struct TcSetup {
     uint32_t tmem, lane_base, sbase, phase;  // sbase: CTA smem base >> 4
 };
 
-// part A: nothing here depends on the parameters (runs ahead of pdl_wait())
+// part A: nothing here depends on the parameters (runs ahead of pdl_wait()).  `smem` is the group's own map; TMEM is
+// allocated once per CTA by its first warp (tmem_cols covers every group) into group 0's slot.
 __device__ __forceinline__ void tc_setup_begin(unsigned char* smem, uint32_t tmem_cols) {
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem + SM_BAR);
     uint32_t* tmem_s = reinterpret_cast<uint32_t*>(smem + SM_BAR + 16);
-    const int warp = threadIdx.x >> 5;
-    for (int i = threadIdx.x; i < 2 * CHUNK_B / 16; i += TC_THREADS)  // G image (chunk 1 stays zero forever)
+    for (int i = tc_tid(); i < 2 * CHUNK_B / 16; i += TC_THREADS)  // G image (chunk 1 stays zero forever)
         *reinterpret_cast<uint4*>(smem + SM_G + i * 16) = make_uint4(0, 0, 0, 0);
-    if (warp == 0) tc::tmem_alloc(tmem_s, tmem_cols);
-    if (threadIdx.x == 0) {
+    if ((threadIdx.x >> 5) == 0) tc::tmem_alloc(tmem_s, tmem_cols);
+    if (tc_tid() == 0) {
         tc::mbar_init(bar, 1);
         tc::mbar_init(bar + 1, 1);
+        tc::mbar_init(bar + 3, 1);
         tc::fence_barrier_init();
     }
 }
 
-// part B: weight image (straight 16-byte copies; the image is rebuilt by the optimizer step, not here), then publish
-__device__ __forceinline__ TcSetup tc_setup_finish(unsigned char* smem, const unsigned char* image) {
+// the group's copy of the fp16 weight image: all loads first (one L2 round trip), then the stores
+__device__ __forceinline__ void tc_load_image(unsigned char* smem, const unsigned char* image) {
+    const uint4* src = reinterpret_cast<const uint4*>(image);
+    uint4* dst = reinterpret_cast<uint4*>(smem + SM_IMG);
+    constexpr int N16 = opt::IMG_BYTES / 16, PER = (N16 + TC_THREADS - 1) / TC_THREADS;
+    uint4 v[PER];
+#pragma unroll
+    for (int u = 0; u < PER; ++u) {
+        const int i = tc_tid() + u * TC_THREADS;
+        if (i < N16) v[u] = __ldcg(src + i);
+    }
+#pragma unroll
+    for (int u = 0; u < PER; ++u) {
+        const int i = tc_tid() + u * TC_THREADS;
+        if (i < N16) dst[i] = v[u];
+    }
+}
+
+// part B: weight image (straight 16-byte copies; the image is rebuilt by the optimizer step, not here), then publish.
+// tmem_slot: where the CTA's TMEM base was written (the group's own map for one-group kernels); this group owns
+// TM_COLS_BWD columns from base + tmem_col0.
+__device__ __forceinline__ TcSetup tc_setup_finish(unsigned char* smem, const unsigned char* image, const uint32_t* tmem_slot = nullptr,
+                                                   uint32_t tmem_col0 = 0) {
     TcSetup s;
     s.bar = reinterpret_cast<uint64_t*>(smem + SM_BAR);
-    uint32_t* tmem_s = reinterpret_cast<uint32_t*>(smem + SM_BAR + 16);
-    const int warp = threadIdx.x >> 5;
-    {
-        const uint4* src = reinterpret_cast<const uint4*>(image + (blockIdx.x % opt::IMG_COPIES) * opt::IMG_BYTES);
-        uint4* dst = reinterpret_cast<uint4*>(smem + SM_IMG);
-        constexpr int N16 = opt::IMG_BYTES / 16, PER = (N16 + TC_THREADS - 1) / TC_THREADS;
-        uint4 v[PER];  // all loads first (one L2 round trip), then the stores
-#pragma unroll
-        for (int u = 0; u < PER; ++u) {
-            const int i = threadIdx.x + u * TC_THREADS;
-            if (i < N16) v[u] = __ldcg(src + i);
-        }
-#pragma unroll
-        for (int u = 0; u < PER; ++u) {
-            const int i = threadIdx.x + u * TC_THREADS;
-            if (i < N16) dst[i] = v[u];
-        }
-    }
+    if (!tmem_slot) tmem_slot = reinterpret_cast<const uint32_t*>(smem + SM_BAR + 16);
+    const int warp = tc_tid() >> 5;
+    tc_load_image(smem, image);
     tc_sync_for_mma();
-    s.tmem = *tmem_s;
+    s.tmem = *tmem_slot + tmem_col0;
     s.lane_base = s.tmem + ((uint32_t)(warp * 32) << 16);
     s.sbase = tc::smem_u32(smem) >> 4;  // descriptor units
     s.phase = 0;
@@ -254,7 +273,7 @@ __device__ __forceinline__ void tc_forward_tile(unsigned char* smem, TcSetup& s,
     TRACE(trow, 1);
     tc_sync_for_mma();
     TRACE(trow, 2);
-    if (threadIdx.x == 0) {
+    if (tc_tid() == 0) {
 #pragma unroll
         for (int ks = 0; ks < TC_XF / 16; ++ks)
             tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase, xoff, ks), desc_w_k(s.sbase, SM_W1, TC_H, ks), ID64, ks > 0);
@@ -267,7 +286,7 @@ __device__ __forceinline__ void tc_forward_tile(unsigned char* smem, TcSetup& s,
     TRACE(trow, 5);
     tc_sync_for_mma();
     TRACE(trow, 6);
-    if (threadIdx.x == 0) {
+    if (tc_tid() == 0) {
 #pragma unroll
         for (int ks = 0; ks < TC_H / 16; ++ks)
             tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase, SM_H1, ks), desc_w_k(s.sbase, SM_W2, TC_H, ks), ID64, ks > 0);
@@ -281,7 +300,7 @@ __device__ __forceinline__ void tc_forward_tile(unsigned char* smem, TcSetup& s,
     TRACE(trow, 9);
     tc_sync_for_mma();
     TRACE(trow, 10);
-    if (threadIdx.x == 0) {
+    if (tc_tid() == 0) {
 #pragma unroll
         for (int ks = 0; ks < TC_H / 16; ++ks)
             tc::mma_f16(s.tmem + TM_OUT, desc_act_k(s.sbase, SM_H2, ks), desc_w_k(s.sbase, SM_W3, TC_OF, ks), ID16, ks > 0);
@@ -394,6 +413,7 @@ struct TcPpoArgs {
     const unsigned char* image;
     float* grads;
     const unsigned char* records;  // [slot] 96-byte packed rows (tsm_ppo_pack_records)
+    const int32_t* slots;          // optional slot table: slots[p] = record slot of batch position p (tsm_ppo_slot_table)
     BatchView view;
     int64_t mb_start, mb_len;
     const float* mb_stats;
@@ -404,46 +424,98 @@ struct TcPpoArgs {
     int debug;  // experiments only (TSM_TC_DEBUG): 1 skip flush, 2 skip backward GEMM phases, 4 skip the loss math
 };
 
-constexpr int REC_BYTES = 96;  // halves x[32] | float adv, ret, logp_old | int32 act | float v_old | 12 bytes pad
-
-// one minibatch row: six 16-byte loads from one record (prefetched a tile ahead, kept in registers)
-struct RowRec {
-    uint4 x[4];   // fp16 input features, already in X-image chunk form
-    uint4 sc;     // adv, ret, logp_old, act
-    float v_old;
+// The batch gather.  Every thread fetches the 96-byte record of its own row of the NEXT tile with one TMA bulk copy into the
+// group's record staging area (SM_REC), a whole tile ahead of its use.  Plain loads did not work as a prefetch here: the
+// records of a tile sit on ~128 different pages, and a warp stalls at ISSUE of a global load until its address is
+// translated (1.7k - 4.6k cycles per tile measured, against ~600 for contiguous records); the bulk-copy engine takes the
+// translation off the warp.  With a slot table (TcPpoArgs::slots) the table entry is fetched one more tile ahead, so
+// neither the permutation arithmetic nor a dependent load sits on the tile's critical path.
+struct RowScalars {
+    float adv, ret, logp_old, v_old;
+    int act;
 };
 
-__device__ __forceinline__ void tc_prefetch_row(const TcPpoArgs& a, int64_t tile, int r, bool& valid, RowRec& d) {
-    const int64_t p = a.mb_start + tile * TC_ROWS + r;
-    valid = tile * TC_ROWS + r < a.mb_len;
+// slot of batch position p: from the table when there is one, else computed here
+__device__ __forceinline__ int64_t tc_slot(const TcPpoArgs& a, int64_t p) {
+    if (a.slots) return (int64_t)__ldg(a.slots + p);
+    return (a.debug & 8) ? p : slot_of(a.view, p);
+}
+
+// issue: rows_valid = number of rows of that tile (the barrier expects rows_valid * 96 bytes); `valid` = this thread's row exists
+__device__ __forceinline__ void tc_gather_issue(unsigned char* smem, const TcPpoArgs& a, int64_t slot, bool valid, int64_t rows_valid) {
+    uint64_t* rbar = reinterpret_cast<uint64_t*>(smem + SM_BAR) + 3;
+    if (tc_tid() == 0) tc::mbar_expect_tx(rbar, (uint32_t)rows_valid * REC_BYTES);
+    if (valid) tc::bulk_g2s(smem + SM_REC + tc_tid() * REC_BYTES, a.records + slot * REC_BYTES, REC_BYTES, rbar);
+}
+
+// take: wait for the tile's records, move this thread's row into the X image at xoff (fp16 chunks, as packed) and its scalars
+// into registers.  Afterwards the thread's staging row is free for the next issue (it is only ever touched by this thread).
+__device__ __forceinline__ void tc_gather_take(unsigned char* smem, int xoff, bool valid, uint32_t& rphase, RowScalars& d) {
+    uint64_t* rbar = reinterpret_cast<uint64_t*>(smem + SM_BAR) + 3;
+    tc::mbar_wait(rbar, rphase);
+    rphase ^= 1;
+    const uint4* rec = reinterpret_cast<const uint4*>(smem + SM_REC + tc_tid() * REC_BYTES);
+    const uint4 zero = make_uint4(0, 0, 0, 0);
+    uint4 x[4], sc = zero;
+    uint32_t vo = 0;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) x[c] = valid ? rec[c] : zero;
     if (valid) {
-        const int64_t slot = (a.debug & 8) ? p : slot_of(a.view, p);
-        const uint4* rec = reinterpret_cast<const uint4*>(a.records + slot * REC_BYTES);
-#pragma unroll
-        for (int c = 0; c < 4; ++c) d.x[c] = __ldg(rec + c);
-        d.sc = __ldg(rec + 4);
-        d.v_old = __ldg(reinterpret_cast<const float*>(rec + 5));
-    } else {
-#pragma unroll
-        for (int c = 0; c < 4; ++c) d.x[c] = make_uint4(0, 0, 0, 0);
-        d.sc = make_uint4(0, 0, 0, 0);
-        d.v_old = 0.f;
+        sc = rec[4];
+        vo = *reinterpret_cast<const uint32_t*>(rec + 5);
     }
-}
-
-__device__ __forceinline__ void tc_store_rec(unsigned char* smem, int xoff, const RowRec& d) {
 #pragma unroll
-    for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4*>(smem + xoff + c * CHUNK_B + threadIdx.x * 16) = d.x[c];
+    for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4*>(smem + xoff + c * CHUNK_B + tc_tid() * 16) = x[c];
+    d.adv = __uint_as_float(sc.x); d.ret = __uint_as_float(sc.y); d.logp_old = __uint_as_float(sc.z);
+    d.act = (int)sc.w;
+    d.v_old = __uint_as_float(vo);
 }
 
-// physical position of flat gradient element i inside the staging copy: the W2 block is XOR-swizzled
-// so that both the per-lane row writes (stride 64 floats) and the linear read-out are bank-conflict free
-__device__ __forceinline__ int stage_pos(int i, int w2_lo, int w2_hi) {
+// Staging copy of the flat gradient (fp32, in the group's own smem at SM_STAGE).  The W2 block is XOR-swizzled at
+// float4 granularity so that both the per-lane row writes (stride 64 floats) and the linear 16-byte read-out are
+// bank-conflict free.  Every block of the flat layout up to b3 starts on a multiple of 4 floats.
+__device__ __forceinline__ int stage_pos4(int i, int w2_lo, int w2_hi) {  // i = 4 * j: float offset of logical float4 j
     if (i >= w2_lo && i < w2_hi) {
-        const int rel = i - w2_lo, rr = rel >> 6, cc = rel & 63;
-        return w2_lo + (rr << 6) + (cc ^ (rr & 31));
+        const int rel = i - w2_lo, rr = rel >> 6, c4 = (rel & 63) >> 2;
+        return w2_lo + (rr << 6) + ((c4 ^ (rr & 15)) << 2);
     }
     return i;
+}
+
+// TMEM weight-gradient accumulators of this group -> its staging copy
+__device__ __forceinline__ void tc_stage_grads(unsigned char* smem, const TcSetup& s, const Offsets& o, int in_dim, int out_dim) {
+    float* stage = reinterpret_cast<float*>(smem + SM_STAGE);
+    const int r = tc_tid();
+    if (r < TC_H) {
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {  // dW2[r][32q..]
+            float v[32];
+            tc::tmem_ld32(s.lane_base + TM_GW2 + 32 * q, v);
+#pragma unroll
+            for (int h = 0; h < 8; ++h)
+                *reinterpret_cast<float4*>(stage + o.w2 + (r << 6) + (((8 * q + h) ^ (r & 15)) << 2)) =
+                    make_float4(v[4 * h], v[4 * h + 1], v[4 * h + 2], v[4 * h + 3]);
+        }
+        float v[16];
+        tc::tmem_ld16(s.lane_base + TM_GW3, v);  // dW3^T[r][o]
+#pragma unroll
+        for (int k = 0; k < OUTP; ++k)
+            if (k < out_dim) stage[o.w3 + k * TC_H + r] = v[k];
+        tc::tmem_ld16(s.lane_base + TM_GW1 + 16, v);  // D2^T [X|1], column 31 = db2[r]
+        stage[o.b2 + r] = v[15];
+    } else {
+        float v[32];
+        tc::tmem_ld32(s.lane_base + TM_GW1, v);  // dW1[r-64][k], db1[r-64] (column 31)
+        const int rr = r - TC_H;
+#pragma unroll
+        for (int k = 0; k < 32; ++k)
+            if (k < in_dim) stage[o.w1 + rr * in_dim + k] = v[k];
+        stage[o.b1 + rr] = v[31];
+    }
+}
+
+__device__ __forceinline__ void red_add4(float* dst, float4 v) {  // one 16-byte reduction at L2, no return value
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
 __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs a) {
@@ -466,10 +538,21 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
     float f_clip = 0.f, f_vf = 0.f, f_ent = 0.f;  // per-thread partial sums of up to 16 tiles, then folded into doubles
     double l_clip = 0.0, l_vf = 0.0, l_ent = 0.0;
 
-    RowRec nd;
-    bool nvalid = false;
+    __syncthreads();  // barriers initialised before any thread's bulk copy names them
+    auto rows_of = [&](int64_t t_) { const int64_t left = a.mb_len - t_ * TC_ROWS; return left < TC_ROWS ? left : (int64_t)TC_ROWS; };
+    uint32_t rphase = 0;
     int64_t tile = blockIdx.x;
-    if (tile < n_tiles) tc_prefetch_row(a, tile, r, nvalid, nd);  // batch records only: safe ahead of the dependency wait
+    if (tile < n_tiles) {  // batch records only: safe ahead of the dependency wait
+        const int64_t q = tile * TC_ROWS + r;
+        tc_gather_issue(smem, a, q < a.mb_len ? tc_slot(a, a.mb_start + q) : 0, q < a.mb_len, rows_of(tile));
+    }
+    int64_t sl_next = 0;  // table path: slot of this thread's row in tile + gridDim.x, fetched a tile before its gather is issued
+    bool v_next = false;
+    if (a.slots) {
+        const int64_t q = (tile + gridDim.x) * TC_ROWS + r;
+        v_next = q < a.mb_len;
+        if (v_next) sl_next = (int64_t)__ldg(a.slots + a.mb_start + q);
+    }
     TRACE(krow, 32);
     pdl_wait();  // parameters (image), gradients and mb_stats of the preceding launches are now visible
     TcSetup s = tc_setup_finish(smem, a.image);
@@ -478,15 +561,24 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
     if ((a.cfg.adv_norm || a.cfg.plain_pg == 2) && a.mb_stats) { mean = __ldcg(a.mb_stats); rstd = __ldcg(a.mb_stats + 1); }
     uint32_t it = 0;
     for (; tile < n_tiles; tile += gridDim.x, ++it) {
-        const bool valid = nvalid;
+        const bool valid = tile * TC_ROWS + r < a.mb_len;
         const int xoff = SM_X + (int)(it & 1) * 4 * CHUNK_B;
         const int trow = (it < 2 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) ? (blockIdx.x != 0) * 2 + (int)it : -1;
         TRACE(trow, 0);
-        tc_store_rec(smem, xoff, nd);
-        const float d_adv = __uint_as_float(nd.sc.x), d_ret = __uint_as_float(nd.sc.y), d_logp_old = __uint_as_float(nd.sc.z);
-        const int d_act = (int)nd.sc.w;
-        const float d_v_old = nd.v_old;
-        if (tile + gridDim.x < n_tiles) tc_prefetch_row(a, tile + gridDim.x, r, nvalid, nd);
+        RowScalars d;
+        tc_gather_take(smem, xoff, valid, rphase, d);
+        const float d_adv = d.adv, d_ret = d.ret, d_logp_old = d.logp_old, d_v_old = d.v_old;
+        const int d_act = d.act;
+        if (tile + gridDim.x < n_tiles) {
+            const int64_t q = (tile + gridDim.x) * TC_ROWS + r;
+            const bool nv = q < a.mb_len;
+            tc_gather_issue(smem, a, a.slots ? sl_next : (nv ? tc_slot(a, a.mb_start + q) : 0), nv, rows_of(tile + gridDim.x));
+            if (a.slots) {
+                const int64_t q2 = (tile + 2 * (int64_t)gridDim.x) * TC_ROWS + r;
+                v_next = q2 < a.mb_len;
+                if (v_next) sl_next = (int64_t)__ldg(a.slots + a.mb_start + q2);
+            }
+        }
         tc_forward_tile(smem, s, xoff, trow);  // its first wait also covers the previous tile's weight-gradient GEMMs
         // ---- loss and G = S * d(loss)/d(OUT) for this thread's row ----
         float z[OUTP], dz[OUTP];
@@ -571,35 +663,10 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
     const Offsets o = offsets(a.in_dim, TC_H, a.out_dim);
     const float inv_s = a.inv_gscale;
     if (it > 0 && !(a.debug & 1)) {
-        // ---- flush: TMEM gradient accumulators -> smem staging (flat gradient layout) -> coalesced atomics ----
+        // ---- flush: TMEM gradient accumulators -> smem staging (flat gradient layout) -> coalesced 16-byte reductions ----
         tc::mbar_wait(s.bar + 1, (it - 1) & 1);
         tc::fence_after_sync();
-        float* stage = reinterpret_cast<float*>(smem + SM_STAGE);
-        const int w2_lo = (int)o.w2;
-        if (r < TC_H) {
-#pragma unroll
-            for (int q = 0; q < 2; ++q) {  // dW2[r][32q..]
-                float v[32];
-                tc::tmem_ld32(s.lane_base + TM_GW2 + 32 * q, v);
-#pragma unroll
-                for (int e = 0; e < 32; ++e) stage[w2_lo + (r << 6) + ((32 * q + e) ^ (r & 31))] = v[e];
-            }
-            float v[16];
-            tc::tmem_ld16(s.lane_base + TM_GW3, v);  // dW3^T[r][o]
-#pragma unroll
-            for (int e = 0; e < OUTP; ++e)
-                if (e < a.out_dim) stage[o.w3 + e * TC_H + r] = v[e];
-            tc::tmem_ld16(s.lane_base + TM_GW1 + 16, v);  // D2^T [X|1], column 31 = db2[r]
-            stage[o.b2 + r] = v[15];
-        } else {
-            float v[32];
-            tc::tmem_ld32(s.lane_base + TM_GW1, v);  // dW1[r-64][k], db1[r-64] (column 31)
-            const int rr = r - TC_H;
-#pragma unroll
-            for (int k = 0; k < 32; ++k)
-                if (k < a.in_dim) stage[o.w1 + rr * a.in_dim + k] = v[k];
-            stage[o.b1 + rr] = v[31];
-        }
+        tc_stage_grads(smem, s, o, a.in_dim, a.out_dim);
     }
     TRACE(krow, 35);
     // db3 and the loss sums: warp shuffle, then shared memory
@@ -626,9 +693,344 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
     if (it > 0 && !(a.debug & 1)) {
         const float* stage = reinterpret_cast<const float*>(smem + SM_STAGE);
         const int w2_lo = (int)o.w2, w2_hi = (int)o.b2, n_stage = (int)o.b3;
-        for (int i = r; i < n_stage; i += TC_THREADS) atomicAdd(a.grads + i, stage[stage_pos(i, w2_lo, w2_hi)] * inv_s);
+        for (int i = 4 * r; i < n_stage; i += 4 * TC_THREADS) {
+            float4 v = *reinterpret_cast<const float4*>(stage + stage_pos4(i, w2_lo, w2_hi));
+            v.x *= inv_s; v.y *= inv_s; v.z *= inv_s; v.w *= inv_s;
+            red_add4(a.grads + i, v);
+        }
         if (r < a.out_dim) atomicAdd(a.grads + o.b3 + r, red_f[r] + red_f[OUTP + r] + red_f[2 * OUTP + r] + red_f[3 * OUTP + r]);
         if (a.loss_sums && r < 3) atomicAdd(a.loss_sums + r, red_d[r] + red_d[3 + r] + red_d[6 + r] + red_d[9 + r]);
     }
     TRACE(krow, 38);
+}
+
+// ---------------------------------------------------------------------------------------------
+// One PERSISTENT cooperative launch per epoch (uniform minibatch size).  Same tile pipeline as tc_ppo_minibatch_kernel,
+// but one CTA per SM holding TC_GROUPS independent 128-thread groups (each with its own shared-memory map, TMEM columns
+// and mbarriers -- two groups per SM overlap one tile's CUDA-core phases with the other's tensor-core phases, the job
+// two co-resident CTAs do in the launch-per-minibatch path; the driver's occupancy calculator only ever admits ONE
+// cooperative CTA per SM for a kernel that allocates TMEM).  Every group keeps its TMEM / barriers / smem across all
+// minibatches and the optimizer step runs inside the kernel, spread over all CTAs, between two grid-wide barriers:
+//   tiles of minibatch m -> the groups' staged gradients are summed in shared memory -> 16-byte reductions into the
+//                           gradient buffer of parity m & 1
+//   grid.sync -> every CTA: squared norm of the whole gradient (same order everywhere -> same clip coefficient),
+//                Adam for its own slice of ~n/grid parameters, fp16 image entries of that slice
+//   grid.sync -> owners clear their slice of the gradient buffer; every group reloads the 16.9 KB image
+// No launch, TMEM allocation, barrier init or cold record gather per minibatch (the first tile of minibatch m + 1 is
+// prefetched before the flush of m).  cooperative_groups grid barriers; the launch is refused unless all CTAs are
+// co-resident (cudaLaunchCooperativeKernel).
+struct TcEpochArgs {
+    TcPpoArgs p;           // mb_start = first batch position of the epoch; grads = gradient buffer of parity 0
+    float* grads1;         // gradient buffer of parity 1 (zero on entry, zero on exit)
+    int64_t n_mb, mb_size, total;  // minibatch m = [m * mb_size, (m + 1) * mb_size), the last one runs to `total`
+    const float* mb_stats;         // [n_mb][2] or NULL
+    double* loss_sums;             // [n_mb][4] or NULL
+    opt::AdamArgs adam;
+};
+
+constexpr int EP_THREADS = TC_THREADS * TC_GROUPS;
+constexpr int SM_GROUP = (SM_TOTAL + 1023) & ~1023;   // stride between the groups' maps
+constexpr int SM_EP_SHARED = TC_GROUPS * SM_GROUP;    // CTA-wide scratch: 8 norm partials, 3 coefficients, TC_GROUPS flags
+constexpr int SM_EP_TOTAL = SM_EP_SHARED + 128;
+constexpr int EP_NORM_LOADS = 7;                      // float4 loads per thread covering the largest net (7168 floats)
+
+__global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs e) {
+    extern __shared__ __align__(1024) unsigned char smem_all[];
+    namespace cg = cooperative_groups;
+    cg::grid_group grid = cg::this_grid();
+    TcPpoArgs& a = e.p;
+    const int grp = tc_grp(), r = tc_tid(), rc = (int)threadIdx.x;
+    unsigned char* smem = smem_all + grp * SM_GROUP;
+    float* s_red = reinterpret_cast<float*>(smem_all + SM_EP_SHARED);
+    float* s_coef = s_red + 8;
+    int* s_has = reinterpret_cast<int*>(s_red + 12);
+    const int64_t vb = (int64_t)blockIdx.x * TC_GROUPS + grp, vg = (int64_t)gridDim.x * TC_GROUPS;  // virtual CTA = group
+    tc_setup_begin(smem, TM_COLS_BWD * TC_GROUPS);
+    constexpr uint32_t ID_DH = tc::make_idesc_f16(128, 64, 0, 0, 0, 1);
+    constexpr uint32_t ID_G64 = tc::make_idesc_f16(128, 64, 0, 0, 1, 1);
+    constexpr uint32_t ID_G32 = tc::make_idesc_f16(128, 32, 0, 0, 1, 1);
+    constexpr uint32_t ID_G16 = tc::make_idesc_f16(128, 16, 0, 0, 1, 1);
+    const Offsets o = offsets(a.in_dim, TC_H, a.out_dim);
+    const int64_t epoch_start = a.mb_start;
+
+    // this group's tile sequence over the whole epoch: (m, tile) -> next (m, tile); false at the end
+    auto len_of = [&](int64_t m_) { return m_ == e.n_mb - 1 ? e.total - m_ * e.mb_size : e.mb_size; };
+    auto advance = [&](int64_t& m_, int64_t& t_) -> bool {
+        if ((t_ + vg) * TC_ROWS < len_of(m_)) { t_ += vg; return true; }
+        for (int64_t mm = m_ + 1; mm < e.n_mb; ++mm)
+            if (vb * TC_ROWS < len_of(mm)) { m_ = mm; t_ = vb; return true; }
+        return false;
+    };
+    auto pos_of = [&](int64_t m_, int64_t t_, bool& valid) -> int64_t {  // batch position of this thread's row
+        const int64_t q = t_ * TC_ROWS + r;
+        valid = q < len_of(m_);
+        return epoch_start + m_ * e.mb_size + q;
+    };
+    auto rows_of = [&](int64_t m_, int64_t t_) { const int64_t left = len_of(m_) - t_ * TC_ROWS; return left < TC_ROWS ? left : (int64_t)TC_ROWS; };
+    uint32_t rphase = 0;
+    __syncthreads();  // barriers initialised before any thread's bulk copy names them
+    int64_t nm = 0, nt = vb;       // the tile whose records are in flight
+    bool n_ok = vb * TC_ROWS < len_of(0);
+    if (!n_ok) n_ok = advance(nm, nt);
+    if (n_ok) {
+        bool v;
+        const int64_t p = pos_of(nm, nt, v);
+        tc_gather_issue(smem, a, v ? tc_slot(a, p) : 0, v, rows_of(nm, nt));
+    }
+    int64_t am = nm, at = nt;      // table path: the tile after that, whose slots are in flight (sl_next / v_next)
+    bool a_ok = n_ok && advance(am, at);
+    int64_t sl_next = 0;
+    bool v_next = false;
+    if (a.slots && a_ok) {
+        const int64_t p = pos_of(am, at, v_next);
+        if (v_next) sl_next = (int64_t)__ldg(a.slots + p);
+    }
+    tc::fence_before_sync();
+    __syncthreads();  // the CTA's TMEM base (group 0's slot) is visible to every group
+    tc::fence_after_sync();
+    TcSetup s = tc_setup_finish(smem, a.image, reinterpret_cast<const uint32_t*>(smem_all + SM_BAR + 16), grp * TM_COLS_BWD);
+    uint32_t xb = 0, wg_commits = 0;  // X buffer toggle and number of commits to bar[1] so far (its phase parity)
+
+    for (int64_t m = 0; m < e.n_mb; ++m) {
+        a.mb_start = epoch_start + m * e.mb_size;
+        a.mb_len = (m == e.n_mb - 1) ? e.total - m * e.mb_size : e.mb_size;
+        float* g_cur = (m & 1) ? e.grads1 : a.grads;
+        [[maybe_unused]] const int erow = (m == 2 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) ? (blockIdx.x != 0) * 2 : -1;
+        TRACE(erow, 40);
+        const int64_t n_tiles = (a.mb_len + TC_ROWS - 1) / TC_ROWS;
+        const float inv_n = 1.0f / (float)a.mb_len;
+        float gscale = 1.0f;
+        while (gscale < (float)a.mb_len && gscale < 1048576.0f) gscale *= 2.0f;
+        const float inv_s = 1.0f / gscale;
+        float mean = 0.f, rstd = 1.f;
+        if ((a.cfg.adv_norm || a.cfg.plain_pg == 2) && e.mb_stats) { mean = __ldcg(e.mb_stats + 2 * m); rstd = __ldcg(e.mb_stats + 2 * m + 1); }
+        float gb3[OUTP];
+#pragma unroll
+        for (int j = 0; j < OUTP; ++j) gb3[j] = 0.f;
+        float f_clip = 0.f, f_vf = 0.f, f_ent = 0.f;
+        double l_clip = 0.0, l_vf = 0.0, l_ent = 0.0;
+        uint32_t it = 0;
+        for (int64_t tile = vb; tile < n_tiles; tile += vg, ++it) {
+            const bool valid = tile * TC_ROWS + r < a.mb_len;
+            const int xoff = SM_X + (int)(xb & 1) * 4 * CHUNK_B;
+            ++xb;
+            [[maybe_unused]] const int trow = (erow >= 0 && it < 2) ? erow + (int)it : -1;
+            TRACE(trow, 0);
+            RowScalars d;
+            tc_gather_take(smem, xoff, valid, rphase, d);
+            const float d_adv = d.adv, d_ret = d.ret, d_logp_old = d.logp_old, d_v_old = d.v_old;
+            const int d_act = d.act;
+            TRACE(trow, 24);
+            // gather of this group's next tile (possibly the first one of a later minibatch: it then overlaps the flush and
+            // the barriers); with a slot table its entries were fetched a tile ago and the ones after are fetched now
+            nm = am; nt = at; n_ok = a_ok;
+            if (n_ok) {
+                bool v;
+                const int64_t p = pos_of(nm, nt, v);
+                tc_gather_issue(smem, a, a.slots ? sl_next : (v ? tc_slot(a, p) : 0), v, rows_of(nm, nt));
+                a_ok = advance(am, at);
+                if (a.slots && a_ok) {
+                    const int64_t p2 = pos_of(am, at, v_next);
+                    if (v_next) sl_next = (int64_t)__ldg(a.slots + p2);
+                }
+            }
+            TRACE(trow, 25);
+            tc_forward_tile(smem, s, xoff, trow);
+            float z[OUTP], dz[OUTP];
+            tc_read_out(s, z);
+            const RowLoss rl = row_loss<true>(z, a.n_act, a.value_index, d_act, d_adv, d_ret, d_logp_old, d_v_old, mean, rstd, a.cfg, inv_n, dz);
+            if (valid) { f_clip += rl.clip; f_vf += rl.vf; f_ent += rl.ent; }
+            if ((it & 15) == 15) {
+                l_clip += (double)f_clip; l_vf += (double)f_vf; l_ent += (double)f_ent;
+                f_clip = f_vf = f_ent = 0.f;
+            }
+            {
+                float g[OUTP];
+#pragma unroll
+                for (int j = 0; j < OUTP; ++j) {
+                    if (!valid) dz[j] = 0.f;
+                    gb3[j] += dz[j];
+                    g[j] = fminf(fmaxf(dz[j] * gscale, -65000.f), 65000.f);
+                }
+                uint4 w;
+                w.x = pack_h2(g[0], g[1]); w.y = pack_h2(g[2], g[3]); w.z = pack_h2(g[4], g[5]); w.w = pack_h2(g[6], g[7]);
+                *reinterpret_cast<uint4*>(smem + SM_G + r * 16) = w;
+            }
+            TRACE(trow, 13);
+            tc_sync_for_mma();
+            TRACE(trow, 14);
+            if (r == 0) {
+                tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase, SM_G, 0), desc_w_mn(s.sbase, SM_W3, TC_OF, 0), ID_DH, 0);
+                tc::commit(s.bar);
+            }
+            TRACE(trow, 15);
+            tc_wait(s);
+            TRACE(trow, 16);
+            tc_epilogue_mask(smem, s.lane_base, SM_H2, SM_D2);
+            TRACE(trow, 17);
+            tc_sync_for_mma();
+            TRACE(trow, 18);
+            if (r == 0) {
+#pragma unroll
+                for (int ks = 0; ks < TC_H / 16; ++ks)
+                    tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase, SM_D2, ks), desc_w_mn(s.sbase, SM_W2, TC_H, ks), ID_DH, ks > 0);
+                tc::commit(s.bar);
+            }
+            TRACE(trow, 19);
+            tc_wait(s);
+            TRACE(trow, 20);
+            tc_epilogue_mask(smem, s.lane_base, SM_H1, SM_D1);
+            TRACE(trow, 21);
+            tc_sync_for_mma();
+            TRACE(trow, 22);
+            if (r == 0) {
+                const uint32_t acc0 = it > 0;
+#pragma unroll
+                for (int ks = 0; ks < TC_ROWS / 16; ++ks)
+                    tc::mma_f16(s.tmem + TM_GW3, desc_act_mn(s.sbase, SM_H2, ks), desc_act_mn(s.sbase, SM_G, ks), ID_G16, ks > 0 ? 1u : acc0);
+#pragma unroll
+                for (int ks = 0; ks < TC_ROWS / 16; ++ks)
+                    tc::mma_f16(s.tmem + TM_GW2, desc_act_mn(s.sbase, SM_D2, ks), desc_act_mn(s.sbase, SM_H1, ks), ID_G64, ks > 0 ? 1u : acc0);
+#pragma unroll
+                for (int ks = 0; ks < TC_ROWS / 16; ++ks)
+                    tc::mma_f16(s.tmem + TM_GW1, desc_act_mn(s.sbase, SM_D2, ks), desc_act_mn(s.sbase, xoff, ks), ID_G32, ks > 0 ? 1u : acc0);
+                tc::commit(s.bar + 1);
+            }
+            ++wg_commits;
+            TRACE(trow, 23);
+        }
+        TRACE(erow, 41);
+        // ---- flush: each group stages its accumulators, the CTA adds the stagings and issues one set of reductions ----
+        if (it > 0) {
+            tc::mbar_wait(s.bar + 1, (wg_commits - 1) & 1);
+            tc::fence_after_sync();
+            tc_stage_grads(smem, s, o, a.in_dim, a.out_dim);
+        }
+        l_clip += (double)f_clip; l_vf += (double)f_vf; l_ent += (double)f_ent;
+        {
+            float* red_f = reinterpret_cast<float*>(smem + SM_RED);
+            double* red_d = reinterpret_cast<double*>(smem + SM_RED + 192);
+#pragma unroll
+            for (int dlt = 16; dlt > 0; dlt >>= 1) {
+#pragma unroll
+                for (int j = 0; j < OUTP; ++j) gb3[j] += __shfl_down_sync(0xffffffffu, gb3[j], dlt);
+                l_clip += __shfl_down_sync(0xffffffffu, l_clip, dlt);
+                l_vf += __shfl_down_sync(0xffffffffu, l_vf, dlt);
+                l_ent += __shfl_down_sync(0xffffffffu, l_ent, dlt);
+            }
+            if ((r & 31) == 0) {
+                const int w = r >> 5;
+#pragma unroll
+                for (int j = 0; j < OUTP; ++j) red_f[w * OUTP + j] = gb3[j];
+                red_d[w * 3 + 0] = l_clip; red_d[w * 3 + 1] = l_vf; red_d[w * 3 + 2] = l_ent;
+            }
+            if (r == 0) s_has[grp] = it > 0;
+        }
+        tc::fence_before_sync();
+        __syncthreads();
+        tc::fence_after_sync();
+        {
+            const int w2_lo = (int)o.w2, w2_hi = (int)o.b2, n_stage = (int)o.b3;
+            bool has[TC_GROUPS];
+            bool any = false;
+#pragma unroll
+            for (int g = 0; g < TC_GROUPS; ++g) { has[g] = s_has[g] != 0; any |= has[g]; }
+            if (any) {
+                for (int i = 4 * rc; i < n_stage; i += 4 * EP_THREADS) {
+                    const int pos = stage_pos4(i, w2_lo, w2_hi);
+                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                    for (int g = 0; g < TC_GROUPS; ++g)
+                        if (has[g]) {
+                            const float4 u = *reinterpret_cast<const float4*>(smem_all + g * SM_GROUP + SM_STAGE + 4 * pos);
+                            v.x += u.x; v.y += u.y; v.z += u.z; v.w += u.w;
+                        }
+                    v.x *= inv_s; v.y *= inv_s; v.z *= inv_s; v.w *= inv_s;
+                    red_add4(g_cur + i, v);
+                }
+                if (rc < a.out_dim) {
+                    float t = 0.f;
+#pragma unroll
+                    for (int g = 0; g < TC_GROUPS; ++g) {
+                        const float* rf = reinterpret_cast<const float*>(smem_all + g * SM_GROUP + SM_RED);
+                        t += rf[rc] + rf[OUTP + rc] + rf[2 * OUTP + rc] + rf[3 * OUTP + rc];
+                    }
+                    atomicAdd(g_cur + o.b3 + rc, t);
+                }
+                if (e.loss_sums && rc < 3) {
+                    double t = 0.0;
+#pragma unroll
+                    for (int g = 0; g < TC_GROUPS; ++g) {
+                        const double* rd = reinterpret_cast<const double*>(smem_all + g * SM_GROUP + SM_RED + 192);
+                        t += rd[rc] + rd[3 + rc] + rd[6 + rc] + rd[9 + rc];
+                    }
+                    atomicAdd(e.loss_sums + 4 * m + rc, t);
+                }
+            }
+        }
+        TRACE(erow, 42);
+        __threadfence();
+        grid.sync();
+        TRACE(erow, 43);
+        // ---- optimizer step, spread over the grid ----
+        const opt::AdamArgs& ad = e.adam;
+        const int64_t n = ad.n, n4 = n / 4;
+        {
+            const float gs = ad.grad_scale;
+            float4 x[EP_NORM_LOADS];  // all loads first (one L2 round trip)
+#pragma unroll
+            for (int u = 0; u < EP_NORM_LOADS; ++u) {
+                const int64_t j = rc + u * EP_THREADS;
+                x[u] = j < n4 ? __ldcg(reinterpret_cast<const float4*>(g_cur) + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+            float sq = 0.f;
+#pragma unroll
+            for (int u = 0; u < EP_NORM_LOADS; ++u) {
+                sq = fmaf(x[u].x * gs, x[u].x * gs, sq); sq = fmaf(x[u].y * gs, x[u].y * gs, sq);
+                sq = fmaf(x[u].z * gs, x[u].z * gs, sq); sq = fmaf(x[u].w * gs, x[u].w * gs, sq);
+            }
+            for (int64_t i = 4 * n4 + rc; i < n; i += EP_THREADS) {
+                const float y = __ldcg(g_cur + i) * gs;
+                sq = fmaf(y, y, sq);
+            }
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) sq += __shfl_down_sync(0xffffffffu, sq, d);
+            if ((rc & 31) == 0) s_red[rc >> 5] = sq;
+            __syncthreads();
+            if (rc == 0) {
+                float t = 0.f;
+                for (int w = 0; w < EP_THREADS / 32; ++w) t += s_red[w];
+                const float norm = sqrtf(t);
+                float c = 1.f;
+                if (ad.max_norm > 0.f) c = fminf(ad.max_norm / (norm + 1e-6f), 1.f);
+                const int64_t step = *reinterpret_cast<volatile int64_t*>(ad.step) + 1;
+                s_coef[0] = c * gs;
+                s_coef[1] = ad.lr / (float)(1.0 - opt::ipow((double)ad.beta1, step));
+                s_coef[2] = (float)sqrt(1.0 - opt::ipow((double)ad.beta2, step));
+                if (ad.gnorm_out && blockIdx.x == 0) *ad.gnorm_out = norm;
+            }
+            __syncthreads();
+        }
+        TRACE(erow, 44);
+        const int64_t per = (n + gridDim.x - 1) / gridDim.x;
+        const int64_t lo = (int64_t)blockIdx.x * per, hi = lo + per < n ? lo + per : n;
+        for (int64_t i = lo + rc; i < hi; i += EP_THREADS) {
+            float mm = ad.m[i], vv = ad.v[i];
+            const float pn = opt::adam_elem(ad.p[i], __ldcg(g_cur + i), mm, vv, s_coef[0], s_coef[1], s_coef[2], ad.beta1, ad.beta2, ad.eps);
+            ad.p[i] = pn; ad.m[i] = mm; ad.v[i] = vv;
+            ad.image[opt::image_index(i, o, a.in_dim)] = __float2half_rn(pn);
+        }
+        TRACE(erow, 45);
+        __threadfence();
+        grid.sync();
+        TRACE(erow, 46);
+        for (int64_t i = lo + rc; i < hi; i += EP_THREADS) g_cur[i] = 0.f;  // next written by the flush of minibatch m + 2
+        if (blockIdx.x == 0 && rc == 0) *ad.step += 1;
+        tc_load_image(smem, a.image);  // refreshed weight image, one copy per group
+        TRACE(erow, 47);
+        // (the first tc_sync_for_mma of the next tile publishes the image and the overwritten staging area to the tensor core)
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if ((rc >> 5) == 0) tc::tmem_dealloc(*reinterpret_cast<const uint32_t*>(smem_all + SM_BAR + 16), TM_COLS_BWD * TC_GROUPS);
 }

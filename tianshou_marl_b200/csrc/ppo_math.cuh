@@ -41,6 +41,10 @@ inline BatchView make_batch_view(const int64_t* indices, int64_t size, int64_t n
     if (perm_n > 0) v.pre = feistel_prepare((uint64_t)perm_n, perm_key);
     return v;
 }
+// the batch's slot table if it can be used (32-bit slots), else NULL
+inline int32_t* slots_of(const tsm_ppo_batch* b) {
+    return (b->slots && b->size * b->n_rows < (int64_t)1 << 31) ? b->slots : nullptr;
+}
 __device__ __forceinline__ int64_t slot_of(const BatchView& b, int64_t p) {
     if (b.indices) {
         const int64_t i = b.indices[p];
