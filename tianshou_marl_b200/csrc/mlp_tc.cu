@@ -9,6 +9,7 @@
 #include "common.cuh"
 #include "philox.cuh"
 #include <cuda_fp16.h>
+#include <cuda.h>  // CUtensorMap (types only: the encoder is reached through cudaGetDriverEntryPoint)
 #include "feistel.cuh"
 #include "ppo_math.cuh"
 #include "adam.cuh"
@@ -184,6 +185,36 @@ int tc_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int6
     return TSM_OK;
 }
 
+// tensor map of the record array as a [n_slots][24 x u32] matrix with a {24, 1} box: the operand of the gather4 copies
+static int record_map(const void* records, int64_t n_slots, CUtensorMap* out, const char* fn) {
+    typedef CUresult (*Encode)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                               const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static Encode encode = nullptr;
+    if (!encode) {
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        TSM_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q));
+        if (!f || q != cudaDriverEntryPointSuccess) return fail(TSM_ERR_UNSUPPORTED, "%s: the driver has no cuTensorMapEncodeTiled", fn);
+        encode = reinterpret_cast<Encode>(f);
+    }
+    static const void* c_rec = nullptr;  // the map only depends on (records, n_slots): keep the last one
+    static int64_t c_n = 0;
+    static CUtensorMap c_map;
+    if (records != c_rec || n_slots != c_n) {
+        if (n_slots <= 0 || n_slots >= (int64_t)1 << 31) return fail(TSM_ERR_UNSUPPORTED, "%s: engine 1 needs size * n_rows < 2^31", fn);
+        if (reinterpret_cast<uintptr_t>(records) & 15) return fail(TSM_ERR_INVALID, "%s: records must be 16-byte aligned", fn);
+        const cuuint64_t dim[2] = {mlptc::REC_BYTES / 4, (cuuint64_t)n_slots}, stride[1] = {mlptc::REC_BYTES};
+        const cuuint32_t box[2] = {mlptc::REC_BYTES / 4, 1}, estr[2] = {1, 1};
+        const CUresult r = encode(&c_map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void*>(records), dim, stride, box, estr,
+                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return fail(TSM_ERR_CUDA, "%s: cuTensorMapEncodeTiled failed (%d)", fn, (int)r);
+        c_rec = records; c_n = n_slots;
+    }
+    *out = c_map;
+    return TSM_OK;
+}
+
 int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, int64_t mb_start, int64_t mb_len,
                      const float* mb_stats, double* loss_sums, int pdl, cudaStream_t s) {
     int rc = tc_check_net(net, __func__);
@@ -220,7 +251,10 @@ int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_p
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     lc.attrs = at; lc.numAttrs = pdl ? 1 : 0;
-    TSM_CUDA(cudaLaunchKernelEx(&lc, mlptc::tc_ppo_minibatch_kernel, a));
+    CUtensorMap rec_map;
+    rc = record_map(batch->records, batch->size * batch->n_rows, &rec_map, __func__);
+    if (rc) return rc;
+    TSM_CUDA(cudaLaunchKernelEx(&lc, mlptc::tc_ppo_minibatch_kernel, a, rec_map));
 #ifdef TSM_TC_TRACE
     if (getenv("TSM_TC_TRACE_DUMP")) {
         long long h[4][64];
@@ -278,7 +312,10 @@ int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, cons
     e.n_mb = n_mb; e.mb_size = mb_size; e.total = total; e.mb_stats = mb_stats; e.loss_sums = loss_sums; e.adam = adam;
     const int64_t tiles = ceil_div(n_mb > 1 ? mb_size : total, mlptc::TC_ROWS);
     const unsigned grid = (unsigned)std::min<int64_t>(ceil_div(tiles, (int64_t)mlptc::TC_GROUPS), (int64_t)sm_count() * occ);
-    void* args[] = {&e};
+    CUtensorMap rec_map;
+    rc = record_map(batch->records, batch->size * batch->n_rows, &rec_map, __func__);
+    if (rc) return rc;
+    void* args[] = {&e, &rec_map};
     const cudaError_t err = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(mlptc::tc_ppo_epoch_kernel), dim3(grid),
                                                         dim3(mlptc::EP_THREADS), args, smem, s);
     if (err == cudaErrorCooperativeLaunchTooLarge) {

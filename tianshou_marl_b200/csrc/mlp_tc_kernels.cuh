@@ -48,8 +48,8 @@ constexpr int SM_FWD_TOTAL = SM_BAR + 64;        // the forward kernel stops her
 constexpr int SM_D2 = SM_FWD_TOTAL;              // 16 KB  (backward only)
 constexpr int SM_D1 = SM_D2 + 8 * CHUNK_B;       // 16 KB
 constexpr int REC_BYTES = 96;  // halves x[32] | float adv, ret, logp_old | int32 act | float v_old | 12 bytes pad
-constexpr int SM_REC = SM_D1 + 8 * CHUNK_B;      // 12 KB: the next tile's batch records, landed by TMA bulk copies
-constexpr int SM_TOTAL = SM_REC + TC_ROWS * REC_BYTES;  // 115,648 B: still two CTAs per SM (2 x (this + 1 KB) <= 228 KB)
+constexpr int SM_REC = (SM_D1 + 8 * CHUNK_B + 127) & ~127;  // 12 KB: the next tile's batch records, landed by TMA gather4 (128-byte aligned)
+constexpr int SM_TOTAL = SM_REC + TC_ROWS * REC_BYTES;  // 115,712 B: still two CTAs per SM (2 x (this + 1 KB) = 228 KB exactly)
 constexpr int SM_STAGE = SM_H2;                  // flush staging: fp32 copy of the flat gradient (<= 32 KB)
 
 // TMEM columns (fp32 accumulators, 128 lanes)
@@ -424,28 +424,32 @@ struct TcPpoArgs {
     int debug;  // experiments only (TSM_TC_DEBUG): 1 skip flush, 2 skip backward GEMM phases, 4 skip the loss math
 };
 
-// The batch gather.  Every thread fetches the 96-byte record of its own row of the NEXT tile with one TMA bulk copy into the
-// group's record staging area (SM_REC), a whole tile ahead of its use.  Plain loads did not work as a prefetch here: the
-// records of a tile sit on ~128 different pages, and a warp stalls at ISSUE of a global load until its address is
-// translated (1.7k - 4.6k cycles per tile measured, against ~600 for contiguous records); the bulk-copy engine takes the
-// translation off the warp.  With a slot table (TcPpoArgs::slots) the table entry is fetched one more tile ahead, so
-// neither the permutation arithmetic nor a dependent load sits on the tile's critical path.
+// The batch gather.  The 96-byte records of the NEXT tile are fetched a whole tile ahead of their use by TMA gather4
+// copies (four rows per instruction, issued by every fourth lane with the slots of its three neighbours) into the group's
+// record staging area (SM_REC).  Plain loads did not work as a prefetch here: the records of a tile sit on ~128 different
+// pages, and a warp stalls at ISSUE of a global load until its address is translated (1.7k - 4.6k cycles per tile measured,
+// against ~600 for contiguous records); one bulk copy per row costs as much, because the instruction takes uniform
+// operands and the compiler serialises the 32 lanes of a warp.  With a slot table (TcPpoArgs::slots) the table entry is
+// fetched one more tile ahead, so neither the permutation arithmetic nor a dependent load sits on the tile's critical path.
 struct RowScalars {
     float adv, ret, logp_old, v_old;
     int act;
 };
 
 // slot of batch position p: from the table when there is one, else computed here
-__device__ __forceinline__ int64_t tc_slot(const TcPpoArgs& a, int64_t p) {
-    if (a.slots) return (int64_t)__ldg(a.slots + p);
-    return (a.debug & 8) ? p : slot_of(a.view, p);
+__device__ __forceinline__ int32_t tc_slot(const TcPpoArgs& a, int64_t p) {
+    if (a.slots) return __ldg(a.slots + p);
+    return (int32_t)((a.debug & 8) ? p : slot_of(a.view, p));
 }
 
-// issue: rows_valid = number of rows of that tile (the barrier expects rows_valid * 96 bytes); `valid` = this thread's row exists
-__device__ __forceinline__ void tc_gather_issue(unsigned char* smem, const TcPpoArgs& a, int64_t slot, bool valid, int64_t rows_valid) {
+// issue (all 128 threads of the group): slot = record of this thread's row, any valid slot (0) for a row past the end
+__device__ __forceinline__ void tc_gather_issue(unsigned char* smem, const CUtensorMap* tmap, int32_t slot) {
     uint64_t* rbar = reinterpret_cast<uint64_t*>(smem + SM_BAR) + 3;
-    if (tc_tid() == 0) tc::mbar_expect_tx(rbar, (uint32_t)rows_valid * REC_BYTES);
-    if (valid) tc::bulk_g2s(smem + SM_REC + tc_tid() * REC_BYTES, a.records + slot * REC_BYTES, REC_BYTES, rbar);
+    const int lane = tc_tid() & 31, base = lane & ~3;
+    const int s0 = __shfl_sync(0xffffffffu, slot, base), s1 = __shfl_sync(0xffffffffu, slot, base + 1);
+    const int s2 = __shfl_sync(0xffffffffu, slot, base + 2), s3 = __shfl_sync(0xffffffffu, slot, base + 3);
+    if (tc_tid() == 0) tc::mbar_expect_tx(rbar, TC_ROWS * REC_BYTES);
+    if ((lane & 3) == 0) tc::tma_gather4(smem + SM_REC + tc_tid() * REC_BYTES, tmap, 0, s0, s1, s2, s3, rbar);
 }
 
 // take: wait for the tile's records, move this thread's row into the X image at xoff (fp16 chunks, as packed) and its scalars
@@ -518,7 +522,7 @@ __device__ __forceinline__ void red_add4(float* dst, float4 v) {  // one 16-byte
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
-__global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs a) {
+__global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs a, const __grid_constant__ CUtensorMap rec_map) {
     extern __shared__ __align__(1024) unsigned char smem[];
     [[maybe_unused]] const int krow = blockIdx.x == 0 ? 0 : (blockIdx.x == gridDim.x - 1 ? 2 : -1);
     TRACE(krow, 30);
@@ -539,19 +543,18 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
     double l_clip = 0.0, l_vf = 0.0, l_ent = 0.0;
 
     __syncthreads();  // barriers initialised before any thread's bulk copy names them
-    auto rows_of = [&](int64_t t_) { const int64_t left = a.mb_len - t_ * TC_ROWS; return left < TC_ROWS ? left : (int64_t)TC_ROWS; };
     uint32_t rphase = 0;
     int64_t tile = blockIdx.x;
     if (tile < n_tiles) {  // batch records only: safe ahead of the dependency wait
         const int64_t q = tile * TC_ROWS + r;
-        tc_gather_issue(smem, a, q < a.mb_len ? tc_slot(a, a.mb_start + q) : 0, q < a.mb_len, rows_of(tile));
+        tc_gather_issue(smem, &rec_map, q < a.mb_len ? tc_slot(a, a.mb_start + q) : 0);
     }
-    int64_t sl_next = 0;  // table path: slot of this thread's row in tile + gridDim.x, fetched a tile before its gather is issued
+    int32_t sl_next = 0;  // table path: slot of this thread's row in tile + gridDim.x, fetched a tile before its gather is issued
     bool v_next = false;
     if (a.slots) {
         const int64_t q = (tile + gridDim.x) * TC_ROWS + r;
         v_next = q < a.mb_len;
-        if (v_next) sl_next = (int64_t)__ldg(a.slots + a.mb_start + q);
+        if (v_next) sl_next = __ldg(a.slots + a.mb_start + q);
     }
     TRACE(krow, 32);
     pdl_wait();  // parameters (image), gradients and mb_stats of the preceding launches are now visible
@@ -572,11 +575,11 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
         if (tile + gridDim.x < n_tiles) {
             const int64_t q = (tile + gridDim.x) * TC_ROWS + r;
             const bool nv = q < a.mb_len;
-            tc_gather_issue(smem, a, a.slots ? sl_next : (nv ? tc_slot(a, a.mb_start + q) : 0), nv, rows_of(tile + gridDim.x));
+            tc_gather_issue(smem, &rec_map, !nv ? 0 : (a.slots ? sl_next : tc_slot(a, a.mb_start + q)));
             if (a.slots) {
                 const int64_t q2 = (tile + 2 * (int64_t)gridDim.x) * TC_ROWS + r;
                 v_next = q2 < a.mb_len;
-                if (v_next) sl_next = (int64_t)__ldg(a.slots + a.mb_start + q2);
+                if (v_next) sl_next = __ldg(a.slots + a.mb_start + q2);
             }
         }
         tc_forward_tile(smem, s, xoff, trow);  // its first wait also covers the previous tile's weight-gradient GEMMs
@@ -734,7 +737,7 @@ constexpr int SM_EP_SHARED = TC_GROUPS * SM_GROUP;    // CTA-wide scratch: 8 nor
 constexpr int SM_EP_TOTAL = SM_EP_SHARED + 128;
 constexpr int EP_NORM_LOADS = 7;                      // float4 loads per thread covering the largest net (7168 floats)
 
-__global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs e) {
+__global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs e, const __grid_constant__ CUtensorMap rec_map) {
     extern __shared__ __align__(1024) unsigned char smem_all[];
     namespace cg = cooperative_groups;
     cg::grid_group grid = cg::this_grid();
@@ -766,7 +769,6 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
         valid = q < len_of(m_);
         return epoch_start + m_ * e.mb_size + q;
     };
-    auto rows_of = [&](int64_t m_, int64_t t_) { const int64_t left = len_of(m_) - t_ * TC_ROWS; return left < TC_ROWS ? left : (int64_t)TC_ROWS; };
     uint32_t rphase = 0;
     __syncthreads();  // barriers initialised before any thread's bulk copy names them
     int64_t nm = 0, nt = vb;       // the tile whose records are in flight
@@ -775,15 +777,15 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
     if (n_ok) {
         bool v;
         const int64_t p = pos_of(nm, nt, v);
-        tc_gather_issue(smem, a, v ? tc_slot(a, p) : 0, v, rows_of(nm, nt));
+        tc_gather_issue(smem, &rec_map, v ? tc_slot(a, p) : 0);
     }
     int64_t am = nm, at = nt;      // table path: the tile after that, whose slots are in flight (sl_next / v_next)
     bool a_ok = n_ok && advance(am, at);
-    int64_t sl_next = 0;
+    int32_t sl_next = 0;
     bool v_next = false;
     if (a.slots && a_ok) {
         const int64_t p = pos_of(am, at, v_next);
-        if (v_next) sl_next = (int64_t)__ldg(a.slots + p);
+        if (v_next) sl_next = __ldg(a.slots + p);
     }
     tc::fence_before_sync();
     __syncthreads();  // the CTA's TMEM base (group 0's slot) is visible to every group
@@ -827,11 +829,11 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
             if (n_ok) {
                 bool v;
                 const int64_t p = pos_of(nm, nt, v);
-                tc_gather_issue(smem, a, a.slots ? sl_next : (v ? tc_slot(a, p) : 0), v, rows_of(nm, nt));
+                tc_gather_issue(smem, &rec_map, !v ? 0 : (a.slots ? sl_next : tc_slot(a, p)));
                 a_ok = advance(am, at);
                 if (a.slots && a_ok) {
                     const int64_t p2 = pos_of(am, at, v_next);
-                    if (v_next) sl_next = (int64_t)__ldg(a.slots + p2);
+                    if (v_next) sl_next = __ldg(a.slots + p2);
                 }
             }
             TRACE(trow, 25);

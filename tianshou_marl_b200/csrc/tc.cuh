@@ -103,6 +103,15 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32
                  "l"(src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
+// TMA gather: four rows (r0..r3) of a 2-D tensor, `col` = first element of the box in the row, land back to back at dst
+// (128-byte aligned); completion on `bar` as 4 x box bytes.  The tensor map's box is {inner, 1} (cuTensorMapEncodeTiled).
+__device__ __forceinline__ void tma_gather4(void* dst_smem, const void* tmap, int col, int r0, int r1, int r2, int r3, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cta.global.tile::gather4.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5, %6}], [%7];" ::"r"(
+            smem_u32(dst_smem)),
+        "l"(tmap), "r"(col), "r"(r0), "r"(r1), "r"(r2), "r"(r3), "r"(smem_u32(bar))
+        : "memory");
+}
 __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 // generic-proxy smem writes -> visible to the async proxy (tensor core reads)
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
