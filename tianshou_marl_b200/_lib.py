@@ -11,7 +11,7 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libtsm_b200.so")
+LIB_PATH = os.environ.get("TSM_B200_LIB") or os.path.join(_HERE, "libtsm_b200.so")  # override: instrumented builds (tools/)
 
 c_i64, c_i32, c_f64, c_vp, c_sz = C.c_int64, C.c_int, C.c_double, C.c_void_p, C.c_size_t
 
@@ -42,7 +42,7 @@ class TsmMpe(C.Structure):
     ]
 
 
-TC_IMAGE_BYTES = 45056  # TSM_TC_IMAGE_BYTES
+TC_IMAGE_BYTES = 74240  # TSM_TC_IMAGE_BYTES
 PPO_RECORD_BYTES = 96  # TSM_PPO_RECORD_BYTES
 
 

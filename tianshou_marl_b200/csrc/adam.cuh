@@ -90,6 +90,19 @@ __device__ __forceinline__ float adam_elem(float p, float g, float& m, float& v,
     return p - step_size * (m / denom);
 }
 
+// Same update with hardware approximations (sqrt.approx, rcp.approx: ~1 ulp each, ~15 instructions instead of ~70):
+// used by the tcgen05 engine's persistent epoch kernel, where every CTA steps all parameters.
+__device__ __forceinline__ float adam_elem_fast(float p, float g, float& m, float& v, float coef, float step_size, float inv_bc2_sqrt,
+                                                float beta1, float beta2, float eps) {
+    const float gi = g * coef;
+    m = m + (gi - m) * (1.f - beta1);
+    v = fmaf(gi * gi, 1.f - beta2, v * beta2);
+    float sq, r;
+    asm("sqrt.approx.f32 %0, %1;" : "=f"(sq) : "f"(v));
+    asm("rcp.approx.f32 %0, %1;" : "=f"(r) : "f"(fmaf(sq, inv_bc2_sqrt, eps)));
+    return fmaf(-step_size * m, r, p);
+}
+
 // One cluster of ADAM_CTAS CTAs: thread-owned float4 slices, so the gradient is read once, kept in registers for
 // both the norm and the update, and zeroed by its owner; the squared-norm partials are exchanged through
 // distributed shared memory (every CTA sums the same partials in the same order: identical clip coefficient).

@@ -284,7 +284,7 @@ int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, cons
     if (rc) return rc;
     if (!batch->records) return fail(TSM_ERR_INVALID, "%s: engine 1 needs batch.records (tsm_ppo_pack_records)", __func__);
     if (reinterpret_cast<uintptr_t>(net->grads) & 15) return fail(TSM_ERR_INVALID, "%s: grads must be 16-byte aligned", __func__);
-    if (adam.n > (int64_t)mlptc::EP_NORM_LOADS * mlptc::EP_THREADS * 4) return 1;
+    if (adam.n > (int64_t)mlptc::EP_G_STRIDE) return 1;
     static int coop = -1, occ = 0;
     const size_t smem = mlptc::SM_EP_TOTAL;
     if (coop < 0) {
@@ -308,7 +308,10 @@ int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, cons
     a.in_dim = net->in_dim; a.out_dim = net->out_dim; a.n_act = net->n_act; a.value_index = net->value_index;
     a.gscale = 1.f; a.inv_gscale = 1.f; a.loss_sums = nullptr;
     a.debug = getenv("TSM_TC_DEBUG") ? atoi(getenv("TSM_TC_DEBUG")) : 0;
+    // workspace behind the image (TSM_TC_IMAGE_BYTES): two more gradient buffers
+    static_assert(TSM_TC_IMAGE_BYTES >= opt::IMG_BYTES + 2 * mlptc::EP_G_STRIDE * 4, "TSM_TC_IMAGE_BYTES too small for the epoch kernel's workspace");
     e.grads1 = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(net->tc_image) + opt::IMG_BYTES);
+    e.grads2 = e.grads1 + mlptc::EP_G_STRIDE;
     e.n_mb = n_mb; e.mb_size = mb_size; e.total = total; e.mb_stats = mb_stats; e.loss_sums = loss_sums; e.adam = adam;
     const int64_t tiles = ceil_div(n_mb > 1 ? mb_size : total, mlptc::TC_ROWS);
     const unsigned grid = (unsigned)std::min<int64_t>(ceil_div(tiles, (int64_t)mlptc::TC_GROUPS), (int64_t)sm_count() * occ);

@@ -714,17 +714,24 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
 // two co-resident CTAs do in the launch-per-minibatch path; the driver's occupancy calculator only ever admits ONE
 // cooperative CTA per SM for a kernel that allocates TMEM).  Every group keeps its TMEM / barriers / smem across all
 // minibatches and the optimizer step runs inside the kernel, spread over all CTAs, between two grid-wide barriers:
-//   tiles of minibatch m -> the groups' staged gradients are summed in shared memory -> 16-byte reductions into the
-//                           gradient buffer of parity m & 1
-//   grid.sync -> every CTA: squared norm of the whole gradient (same order everywhere -> same clip coefficient),
-//                Adam for its own slice of ~n/grid parameters, fp16 image entries of that slice
-//   grid.sync -> owners clear their slice of the gradient buffer; every group reloads the 16.9 KB image
+//   tiles of minibatch m -> the groups' staged gradients are summed in shared memory -> 16-byte reductions into
+//                           gradient buffer m % 3; the CTA's copy of params / exp_avg / exp_avg_sq is fetched into registers
+//   grid.sync -> EVERY CTA runs the WHOLE optimizer step on its own copy of the state: squared norm of the gradient,
+//                clip coefficient, Adam for all n parameters, fp16 image entries written straight into both groups'
+//                shared-memory images.  Same instructions on the same values in every CTA -> bit-identical copies, so
+//                there is no second grid barrier, no image round trip through L2 and no slice ownership.  The copy
+//                never touches memory: a thread owns 7 float4 of the flat parameter vector, keeps the fp32 masters in
+//                registers and exp_avg / exp_avg_sq in the 64 TMEM columns its group leaves unused (148 copies kept in
+//                L2 cost 20-30 MB of traffic per step: measured 2x slower than the two-barrier version).
+//                Buffer (m - 1) % 3, which nobody reads any more, is cleared by slice owners off the critical path;
+//                CTA 0 writes the net's flat arrays and global image after the last minibatch.
 // No launch, TMEM allocation, barrier init or cold record gather per minibatch (the first tile of minibatch m + 1 is
 // prefetched before the flush of m).  cooperative_groups grid barriers; the launch is refused unless all CTAs are
 // co-resident (cudaLaunchCooperativeKernel).
 struct TcEpochArgs {
-    TcPpoArgs p;           // mb_start = first batch position of the epoch; grads = gradient buffer of parity 0
-    float* grads1;         // gradient buffer of parity 1 (zero on entry, zero on exit)
+    TcPpoArgs p;           // mb_start = first batch position of the epoch; grads = gradient buffer 0
+    float* grads1;         // gradient buffers 1 and 2 (minibatch m reduces into buffer m % 3; all zero on entry and on exit)
+    float* grads2;
     int64_t n_mb, mb_size, total;  // minibatch m = [m * mb_size, (m + 1) * mb_size), the last one runs to `total`
     const float* mb_stats;         // [n_mb][2] or NULL
     double* loss_sums;             // [n_mb][4] or NULL
@@ -735,7 +742,43 @@ constexpr int EP_THREADS = TC_THREADS * TC_GROUPS;
 constexpr int SM_GROUP = (SM_TOTAL + 1023) & ~1023;   // stride between the groups' maps
 constexpr int SM_EP_SHARED = TC_GROUPS * SM_GROUP;    // CTA-wide scratch: 8 norm partials, 3 coefficients, TC_GROUPS flags
 constexpr int SM_EP_TOTAL = SM_EP_SHARED + 128;
-constexpr int EP_NORM_LOADS = 7;                      // float4 loads per thread covering the largest net (7168 floats)
+constexpr int EP_G_STRIDE = 7168;                     // floats per gradient buffer (largest net: 6 728 parameters)
+constexpr int EP_OPT = EP_G_STRIDE / 4 / EP_THREADS;  // 7 float4 of the flat parameter vector per thread: j = t + u * EP_THREADS
+constexpr uint32_t TM_OPT_M = 208;                    // exp_avg: 28 columns (of 32)
+constexpr uint32_t TM_OPT_V0 = 240, TM_OPT_V1 = 80;   // exp_avg_sq: 16 + 12 (of 16) columns
+static_assert(EP_OPT == 7, "column map below is for 7 float4 per thread");
+
+// 32-bit opt::image_index
+__device__ __forceinline__ int ep_image_index(int i, const Offsets& o, int in_dim) {
+    if (i < (int)o.b1) {
+        const int out = i / in_dim, in = i - out * in_dim;
+        return opt::IMG_W1 + ((in >> 3) * 64 + out) * 8 + (in & 7);
+    }
+    if (i < (int)o.w2) return opt::IMG_W1 + (3 * 64 + (i - (int)o.b1)) * 8 + 7;
+    if (i < (int)o.b2) {
+        const int rel = i - (int)o.w2;
+        return opt::IMG_W2 + (((rel & 63) >> 3) * 64 + (rel >> 6)) * 8 + (rel & 7);
+    }
+    if (i < (int)o.w3) return opt::IMG_B2 + (64 + (i - (int)o.b2)) * 8 + 7;
+    if (i < (int)o.b3) {
+        const int rel = i - (int)o.w3;
+        return opt::IMG_W3 + (((rel & 63) >> 3) * 16 + (rel >> 6)) * 8 + (rel & 7);
+    }
+    return opt::IMG_B3 + (16 + (i - (int)o.b3)) * 8 + 7;
+}
+// exp_avg / exp_avg_sq of float4 u: 4 TMEM columns each
+__device__ __forceinline__ void ep_ld4(uint32_t taddr, float4& v) {
+    uint32_t r0, r1, r2, r3;
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];\n\ttcgen05.wait::ld.sync.aligned;"
+                 : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(taddr) : "memory");
+    v = make_float4(__uint_as_float(r0), __uint_as_float(r1), __uint_as_float(r2), __uint_as_float(r3));
+}
+__device__ __forceinline__ void ep_st4(uint32_t taddr, const float4& v) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(taddr), "r"(__float_as_uint(v.x)),
+                 "r"(__float_as_uint(v.y)), "r"(__float_as_uint(v.z)), "r"(__float_as_uint(v.w)) : "memory");
+}
+__device__ __forceinline__ uint32_t ep_m_col(int u) { return TM_OPT_M + 4 * u; }
+__device__ __forceinline__ uint32_t ep_v_col(int u) { return u < 4 ? TM_OPT_V0 + 4 * u : TM_OPT_V1 + 4 * (u - 4); }
 
 __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs e, const __grid_constant__ CUtensorMap rec_map) {
     extern __shared__ __align__(1024) unsigned char smem_all[];
@@ -755,7 +798,9 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
     constexpr uint32_t ID_G16 = tc::make_idesc_f16(128, 16, 0, 0, 1, 1);
     const Offsets o = offsets(a.in_dim, TC_H, a.out_dim);
     const int64_t epoch_start = a.mb_start;
-
+    const opt::AdamArgs& ad = e.adam;
+    const int64_t n = ad.n;
+    const int64_t step0 = *ad.step;  // rewritten by CTA 0 only after the last grid barrier
     // this group's tile sequence over the whole epoch: (m, tile) -> next (m, tile); false at the end
     auto len_of = [&](int64_t m_) { return m_ == e.n_mb - 1 ? e.total - m_ * e.mb_size : e.mb_size; };
     auto advance = [&](int64_t& m_, int64_t& t_) -> bool {
@@ -792,11 +837,31 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
     tc::fence_after_sync();
     TcSetup s = tc_setup_finish(smem, a.image, reinterpret_cast<const uint32_t*>(smem_all + SM_BAR + 16), grp * TM_COLS_BWD);
     uint32_t xb = 0, wg_commits = 0;  // X buffer toggle and number of commits to bar[1] so far (its phase parity)
+    // ---- this CTA's copy of the optimizer state: fp32 masters in registers, moments in the group's spare TMEM columns ----
+    float4 Pr[EP_OPT];
+    uint2 Q[EP_OPT];        // image positions of the four parameters (0xffff: none), computed once
+    uint32_t q_contig = 0;  // bit u: they are four consecutive positions (W2 / W3 rows): one 8-byte store
+#pragma unroll
+    for (int u = 0; u < EP_OPT; ++u) {
+        const int i = 4 * (rc + u * EP_THREADS);
+        {
+            uint32_t q[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) q[k] = i + k < n ? (uint32_t)ep_image_index(i + k, o, a.in_dim) : 0xffffu;
+            Q[u] = make_uint2(q[0] | (q[1] << 16), q[2] | (q[3] << 16));
+            if (q[0] != 0xffffu && (q[0] & 3) == 0 && q[1] == q[0] + 1 && q[2] == q[0] + 2 && q[3] == q[0] + 3) q_contig |= 1u << u;
+        }
+        auto get = [&](const float* src, int k) { return i + k < n ? __ldcg(src + i + k) : 0.f; };
+        Pr[u] = make_float4(get(ad.p, 0), get(ad.p, 1), get(ad.p, 2), get(ad.p, 3));
+        ep_st4(s.lane_base + ep_m_col(u), make_float4(get(ad.m, 0), get(ad.m, 1), get(ad.m, 2), get(ad.m, 3)));
+        ep_st4(s.lane_base + ep_v_col(u), make_float4(get(ad.v, 0), get(ad.v, 1), get(ad.v, 2), get(ad.v, 3)));
+    }
+    tc::tmem_st_wait();
 
     for (int64_t m = 0; m < e.n_mb; ++m) {
         a.mb_start = epoch_start + m * e.mb_size;
         a.mb_len = (m == e.n_mb - 1) ? e.total - m * e.mb_size : e.mb_size;
-        float* g_cur = (m & 1) ? e.grads1 : a.grads;
+        float* g_cur = (m % 3 == 0) ? a.grads : (m % 3 == 1 ? e.grads1 : e.grads2);
         [[maybe_unused]] const int erow = (m == 2 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) ? (blockIdx.x != 0) * 2 : -1;
         TRACE(erow, 40);
         const int64_t n_tiles = (a.mb_len + TC_ROWS - 1) / TC_ROWS;
@@ -971,29 +1036,28 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
             }
         }
         TRACE(erow, 42);
+        // ---- optimizer step: the whole of it in every CTA, on the CTA's own copy of the state ----
         __threadfence();
         grid.sync();
         TRACE(erow, 43);
-        // ---- optimizer step, spread over the grid ----
-        const opt::AdamArgs& ad = e.adam;
-        const int64_t n = ad.n, n4 = n / 4;
+        float4 G[EP_OPT];  // all loads first (one L2 round trip)
         {
             const float gs = ad.grad_scale;
-            float4 x[EP_NORM_LOADS];  // all loads first (one L2 round trip)
 #pragma unroll
-            for (int u = 0; u < EP_NORM_LOADS; ++u) {
-                const int64_t j = rc + u * EP_THREADS;
-                x[u] = j < n4 ? __ldcg(reinterpret_cast<const float4*>(g_cur) + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int u = 0; u < EP_OPT; ++u) {
+                const int i = 4 * (rc + u * EP_THREADS);
+                if (i + 3 < n) {
+                    G[u] = __ldcg(reinterpret_cast<const float4*>(g_cur) + rc + u * EP_THREADS);
+                } else {  // (buffer 0 is the net's own gradient array: exactly n floats)
+                    auto get = [&](int k) { return i + k < n ? __ldcg(g_cur + i + k) : 0.f; };
+                    G[u] = make_float4(get(0), get(1), get(2), get(3));
+                }
             }
             float sq = 0.f;
 #pragma unroll
-            for (int u = 0; u < EP_NORM_LOADS; ++u) {
-                sq = fmaf(x[u].x * gs, x[u].x * gs, sq); sq = fmaf(x[u].y * gs, x[u].y * gs, sq);
-                sq = fmaf(x[u].z * gs, x[u].z * gs, sq); sq = fmaf(x[u].w * gs, x[u].w * gs, sq);
-            }
-            for (int64_t i = 4 * n4 + rc; i < n; i += EP_THREADS) {
-                const float y = __ldcg(g_cur + i) * gs;
-                sq = fmaf(y, y, sq);
+            for (int u = 0; u < EP_OPT; ++u) {
+                sq = fmaf(G[u].x * gs, G[u].x * gs, sq); sq = fmaf(G[u].y * gs, G[u].y * gs, sq);
+                sq = fmaf(G[u].z * gs, G[u].z * gs, sq); sq = fmaf(G[u].w * gs, G[u].w * gs, sq);
             }
 #pragma unroll
             for (int d = 16; d > 0; d >>= 1) sq += __shfl_down_sync(0xffffffffu, sq, d);
@@ -1005,32 +1069,96 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
                 const float norm = sqrtf(t);
                 float c = 1.f;
                 if (ad.max_norm > 0.f) c = fminf(ad.max_norm / (norm + 1e-6f), 1.f);
-                const int64_t step = *reinterpret_cast<volatile int64_t*>(ad.step) + 1;
+                const int64_t step = step0 + m + 1;
                 s_coef[0] = c * gs;
                 s_coef[1] = ad.lr / (float)(1.0 - opt::ipow((double)ad.beta1, step));
-                s_coef[2] = (float)sqrt(1.0 - opt::ipow((double)ad.beta2, step));
+                s_coef[2] = (float)(1.0 / sqrt(1.0 - opt::ipow((double)ad.beta2, step)));
                 if (ad.gnorm_out && blockIdx.x == 0) *ad.gnorm_out = norm;
             }
             __syncthreads();
         }
         TRACE(erow, 44);
-        const int64_t per = (n + gridDim.x - 1) / gridDim.x;
-        const int64_t lo = (int64_t)blockIdx.x * per, hi = lo + per < n ? lo + per : n;
-        for (int64_t i = lo + rc; i < hi; i += EP_THREADS) {
-            float mm = ad.m[i], vv = ad.v[i];
-            const float pn = opt::adam_elem(ad.p[i], __ldcg(g_cur + i), mm, vv, s_coef[0], s_coef[1], s_coef[2], ad.beta1, ad.beta2, ad.eps);
-            ad.p[i] = pn; ad.m[i] = mm; ad.v[i] = vv;
-            ad.image[opt::image_index(i, o, a.in_dim)] = __float2half_rn(pn);
+        {
+            const float c0 = s_coef[0], c1 = s_coef[1], c2 = s_coef[2];
+            const bool last = m == e.n_mb - 1 && blockIdx.x == 0;
+            float Mo[32], Vo[32];  // one TMEM round trip for all moments of this thread (entries 28..31 unused)
+            {
+                float v0[16], v1[16];
+                tc::tmem_ld32(s.lane_base + TM_OPT_M, Mo);
+                tc::tmem_ld16(s.lane_base + TM_OPT_V0, v0);
+                tc::tmem_ld16(s.lane_base + TM_OPT_V1, v1);
+#pragma unroll
+                for (int k = 0; k < 16; ++k) { Vo[k] = v0[k]; Vo[16 + k] = v1[k]; }
+            }
+#pragma unroll
+            for (int u = 0; u < EP_OPT; ++u) {
+                const int i = 4 * (rc + u * EP_THREADS);
+                const bool live = i < n;  // TMEM traffic stays warp-uniform: dead entries are all-zero and stay so
+                float4 mm = make_float4(Mo[4 * u], Mo[4 * u + 1], Mo[4 * u + 2], Mo[4 * u + 3]);
+                float4 vv = make_float4(Vo[4 * u], Vo[4 * u + 1], Vo[4 * u + 2], Vo[4 * u + 3]);
+                Pr[u].x = opt::adam_elem_fast(Pr[u].x, G[u].x, mm.x, vv.x, c0, c1, c2, ad.beta1, ad.beta2, ad.eps);
+                Pr[u].y = opt::adam_elem_fast(Pr[u].y, G[u].y, mm.y, vv.y, c0, c1, c2, ad.beta1, ad.beta2, ad.eps);
+                Pr[u].z = opt::adam_elem_fast(Pr[u].z, G[u].z, mm.z, vv.z, c0, c1, c2, ad.beta1, ad.beta2, ad.eps);
+                Pr[u].w = opt::adam_elem_fast(Pr[u].w, G[u].w, mm.w, vv.w, c0, c1, c2, ad.beta1, ad.beta2, ad.eps);
+                Mo[4 * u] = mm.x; Mo[4 * u + 1] = mm.y; Mo[4 * u + 2] = mm.z; Mo[4 * u + 3] = mm.w;
+                Vo[4 * u] = vv.x; Vo[4 * u + 1] = vv.y; Vo[4 * u + 2] = vv.z; Vo[4 * u + 3] = vv.w;
+                if ((q_contig >> u) & 1u) {  // four consecutive inputs of one output unit: 8 contiguous bytes of the image
+                    const uint32_t q = Q[u].x & 0xffffu;
+                    const uint2 h = make_uint2(pack_h2(Pr[u].x, Pr[u].y), pack_h2(Pr[u].z, Pr[u].w));
+#pragma unroll
+                    for (int g = 0; g < TC_GROUPS; ++g) *reinterpret_cast<uint2*>(smem_all + g * SM_GROUP + SM_IMG + 2 * q) = h;
+                    if (last) *reinterpret_cast<uint2*>(ad.image + q) = h;
+                } else if (live) {  // W1 rows (in_dim is not a multiple of 8) and the biases: one position at a time
+                    const float pp[4] = {Pr[u].x, Pr[u].y, Pr[u].z, Pr[u].w};
+                    const uint32_t qq[4] = {Q[u].x & 0xffffu, Q[u].x >> 16, Q[u].y & 0xffffu, Q[u].y >> 16};
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        if (qq[k] != 0xffffu) {
+                            const __half h = __float2half_rn(pp[k]);
+#pragma unroll
+                            for (int g = 0; g < TC_GROUPS; ++g) *reinterpret_cast<__half*>(smem_all + g * SM_GROUP + SM_IMG + 2 * qq[k]) = h;
+                            if (last) ad.image[qq[k]] = h;
+                        }
+                }
+                if (last) {  // the net's own arrays, once per launch
+                    const float pp[4] = {Pr[u].x, Pr[u].y, Pr[u].z, Pr[u].w}, m4[4] = {mm.x, mm.y, mm.z, mm.w}, v4[4] = {vv.x, vv.y, vv.z, vv.w};
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        if (i + k < n) { ad.p[i + k] = pp[k]; ad.m[i + k] = m4[k]; ad.v[i + k] = v4[k]; }
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                float t8[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) t8[k] = Mo[8 * c + k];
+                tc::tmem_st8(s.lane_base + TM_OPT_M + 8 * c, t8);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) t8[k] = Vo[8 * c + k];
+                tc::tmem_st8(s.lane_base + (c < 2 ? TM_OPT_V0 + 8 * c : TM_OPT_V1 + 8 * (c - 2)), t8);
+            }
+            tc::tmem_st_wait();
         }
         TRACE(erow, 45);
+        {   // buffer (m - 1) % 3 has been read by everybody (all CTAs are past barrier m); it is next reduced into after barrier m + 1
+            float* g_old = ((m + 2) % 3 == 0) ? a.grads : ((m + 2) % 3 == 1 ? e.grads1 : e.grads2);
+            const int64_t per = (n + gridDim.x - 1) / gridDim.x;
+            const int64_t lo = (int64_t)blockIdx.x * per, hi = lo + per < n ? lo + per : n;
+            for (int64_t i = lo + rc; i < hi; i += EP_THREADS) g_old[i] = 0.f;
+        }
+        TRACE(erow, 46);
+        tc::fence_async_smem();  // the image entries written above are read by both groups' MMAs
+        __syncthreads();
+        TRACE(erow, 47);
+    }
+    {   // the last buffer: clear it once nobody reads it any more; publish the step count
         __threadfence();
         grid.sync();
-        TRACE(erow, 46);
-        for (int64_t i = lo + rc; i < hi; i += EP_THREADS) g_cur[i] = 0.f;  // next written by the flush of minibatch m + 2
-        if (blockIdx.x == 0 && rc == 0) *ad.step += 1;
-        tc_load_image(smem, a.image);  // refreshed weight image, one copy per group
-        TRACE(erow, 47);
-        // (the first tc_sync_for_mma of the next tile publishes the image and the overwritten staging area to the tensor core)
+        float* g_last = ((e.n_mb - 1) % 3 == 0) ? a.grads : ((e.n_mb - 1) % 3 == 1 ? e.grads1 : e.grads2);
+        const int64_t per = (n + gridDim.x - 1) / gridDim.x;
+        const int64_t lo = (int64_t)blockIdx.x * per, hi = lo + per < n ? lo + per : n;
+        for (int64_t i = lo + rc; i < hi; i += EP_THREADS) g_last[i] = 0.f;
+        if (blockIdx.x == 0 && rc == 0) *ad.step = step0 + e.n_mb;
     }
     tc::fence_before_sync();
     __syncthreads();
