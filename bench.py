@@ -207,6 +207,15 @@ def reference_main(args: argparse.Namespace) -> None:
 # ------------------------------------------------------------------------------------------
 def main() -> None:
     args = parse()
+    # stdout carries exactly ONE JSON line: anything a library prints there (NCCL's version banner under torchrun) goes to stderr
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+    global print
+
+    def print(*a, **k):  # noqa: A001  (the result line only)
+        os.write(json_fd, (" ".join(str(x) for x in a) + "\n").encode())
+
     if args.impl == "reference":
         reference_main(args)
         return

@@ -45,3 +45,19 @@ def _oracle_clib():
         import subprocess
 
         subprocess.run(["make", "-C", os.path.join(ROOT, "oracle")], check=False, capture_output=True)
+
+
+@pytest.fixture(autouse=True)
+def _seed_everything(request):
+    """Tests draw parameters / inputs from torch's and numpy's global generators; torch's default CUDA seed differs from
+    process to process in this build, so pin both per test (seed derived from the test's node id)."""
+    import zlib
+
+    seed = zlib.crc32(request.node.nodeid.encode()) & 0x7FFFFFFF
+    np.random.seed(seed)
+    try:
+        import torch
+
+        torch.manual_seed(seed)
+    except Exception:
+        pass

@@ -937,6 +937,25 @@ extern "C" int tsm_ppo_epoch_dist(const tsm_net* net, const tsm_ppo_batch* batch
     int rc = check_peers(peers, __func__);
     if (rc) return rc;
     TSM_REQUIRE(seq0 >= 1, "seq0 >= 1");
+    if (net->engine == 1 && n_minibatches >= 1 && !getenv("TSM_NO_PERSISTENT")) {
+        // as tsm_ppo_epoch: one persistent cooperative launch per epoch; the gradient exchange runs inside it
+        const int64_t bs = h_mb_bounds[1] - h_mb_bounds[0];
+        bool uniform = bs > 0;
+        for (int64_t m = 1; m + 1 < n_minibatches && uniform; ++m) uniform = h_mb_bounds[m + 1] - h_mb_bounds[m] == bs;
+        if (uniform && n_minibatches > 1) uniform = h_mb_bounds[n_minibatches] - h_mb_bounds[n_minibatches - 1] >= bs;
+        if (uniform) {
+            rc = check_net(net, __func__);
+            if (rc) return rc;
+            rc = check_batch(batch, __func__);
+            if (rc) return rc;
+            TSM_REQUIRE(cfg && net->grads && net->adam_m && net->adam_v && net->adam_step, "cfg / grads / adam state != NULL");
+            TSM_REQUIRE(!(cfg->adv_norm || cfg->plain_pg == 2) || mb_stats, "advantage normalisation / plain_pg 2 need mb_stats");
+            rc = tc_ppo_epoch_persistent(net, batch, cfg, h_mb_bounds[0], bs, n_minibatches, h_mb_bounds[n_minibatches] - h_mb_bounds[0],
+                                         mb_stats, loss_sums, adam_args_dist(net, peers, seq0, lr, beta1, beta2, eps, max_grad_norm, nullptr),
+                                         as_stream(stream));
+            if (rc <= 0) return rc;
+        }
+    }
     for (int64_t m = 0; m < n_minibatches; ++m) {
         const uint32_t seq = seq0 + (uint32_t)m;
         const int64_t s0 = h_mb_bounds[m], len = h_mb_bounds[m + 1] - h_mb_bounds[m];

@@ -309,9 +309,10 @@ int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, cons
     a.gscale = 1.f; a.inv_gscale = 1.f; a.loss_sums = nullptr;
     a.debug = getenv("TSM_TC_DEBUG") ? atoi(getenv("TSM_TC_DEBUG")) : 0;
     // workspace behind the image (TSM_TC_IMAGE_BYTES): two more gradient buffers
-    static_assert(TSM_TC_IMAGE_BYTES >= opt::IMG_BYTES + 2 * mlptc::EP_G_STRIDE * 4, "TSM_TC_IMAGE_BYTES too small for the epoch kernel's workspace");
+    static_assert(TSM_TC_IMAGE_BYTES >= opt::IMG_BYTES + 2 * mlptc::EP_G_STRIDE * 4 + 256, "TSM_TC_IMAGE_BYTES too small for the epoch kernel's workspace");
     e.grads1 = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(net->tc_image) + opt::IMG_BYTES);
     e.grads2 = e.grads1 + mlptc::EP_G_STRIDE;
+    e.sync_words = reinterpret_cast<uint32_t*>(e.grads2 + mlptc::EP_G_STRIDE);
     e.n_mb = n_mb; e.mb_size = mb_size; e.total = total; e.mb_stats = mb_stats; e.loss_sums = loss_sums; e.adam = adam;
     const int64_t tiles = ceil_div(n_mb > 1 ? mb_size : total, mlptc::TC_ROWS);
     const unsigned grid = (unsigned)std::min<int64_t>(ceil_div(tiles, (int64_t)mlptc::TC_GROUPS), (int64_t)sm_count() * occ);
@@ -347,9 +348,9 @@ int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, cons
         printf("abs offsets from slot40 (CTA0): tile0 start %lld end %lld | tile1 start %lld end %lld | loop end %lld\n", h[0][0] - h[0][40],
                h[0][23] - h[0][40], h[1][0] - h[0][40], h[1][23] - h[0][40], h[0][41] - h[0][40]);
         for (int row = 0; row < 4; row += 2)
-            printf("epoch row %d (minibatch 2): tiles %lld flush-stage %lld atomics %lld sync1 %lld norm %lld adam %lld sync2 %lld zero+image %lld | total %lld\n",
-                   row, h[row][41] - h[row][40], 0LL, h[row][42] - h[row][41], h[row][43] - h[row][42], h[row][44] - h[row][43],
-                   h[row][45] - h[row][44], h[row][46] - h[row][45], h[row][47] - h[row][46], h[row][47] - h[row][40]);
+            printf("epoch row %d (minibatch 2): tiles %lld flush %lld grid-barrier %lld rank-exchange %lld norm %lld adam %lld clear+publish %lld | total %lld\n",
+                   row, h[row][41] - h[row][40], h[row][42] - h[row][41], h[row][43] - h[row][42], h[row][48] - h[row][43], h[row][44] - h[row][48],
+                   h[row][45] - h[row][44], h[row][47] - h[row][45], h[row][47] - h[row][40]);
     }
 #endif
     return TSM_OK;

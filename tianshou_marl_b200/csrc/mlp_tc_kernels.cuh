@@ -732,6 +732,7 @@ struct TcEpochArgs {
     TcPpoArgs p;           // mb_start = first batch position of the epoch; grads = gradient buffer 0
     float* grads1;         // gradient buffers 1 and 2 (minibatch m reduces into buffer m % 3; all zero on entry and on exit)
     float* grads2;
+    uint32_t* sync_words;  // [0] arrival counter of the in-kernel grid barrier (zero between launches)
     int64_t n_mb, mb_size, total;  // minibatch m = [m * mb_size, (m + 1) * mb_size), the last one runs to `total`
     const float* mb_stats;         // [n_mb][2] or NULL
     double* loss_sums;             // [n_mb][4] or NULL
@@ -784,7 +785,7 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
     extern __shared__ __align__(1024) unsigned char smem_all[];
     namespace cg = cooperative_groups;
     cg::grid_group grid = cg::this_grid();
-    TcPpoArgs& a = e.p;
+    const TcPpoArgs& a = e.p;  // (never written: the argument struct stays in the constant bank)
     const int grp = tc_grp(), r = tc_tid(), rc = (int)threadIdx.x;
     unsigned char* smem = smem_all + grp * SM_GROUP;
     float* s_red = reinterpret_cast<float*>(smem_all + SM_EP_SHARED);
@@ -859,15 +860,14 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
     tc::tmem_st_wait();
 
     for (int64_t m = 0; m < e.n_mb; ++m) {
-        a.mb_start = epoch_start + m * e.mb_size;
-        a.mb_len = (m == e.n_mb - 1) ? e.total - m * e.mb_size : e.mb_size;
+        const int64_t mb_len = (m == e.n_mb - 1) ? e.total - m * e.mb_size : e.mb_size;
         float* g_cur = (m % 3 == 0) ? a.grads : (m % 3 == 1 ? e.grads1 : e.grads2);
         [[maybe_unused]] const int erow = (m == 2 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) ? (blockIdx.x != 0) * 2 : -1;
         TRACE(erow, 40);
-        const int64_t n_tiles = (a.mb_len + TC_ROWS - 1) / TC_ROWS;
-        const float inv_n = 1.0f / (float)a.mb_len;
+        const int64_t n_tiles = (mb_len + TC_ROWS - 1) / TC_ROWS;
+        const float inv_n = 1.0f / (float)mb_len;
         float gscale = 1.0f;
-        while (gscale < (float)a.mb_len && gscale < 1048576.0f) gscale *= 2.0f;
+        while (gscale < (float)mb_len && gscale < 1048576.0f) gscale *= 2.0f;
         const float inv_s = 1.0f / gscale;
         float mean = 0.f, rstd = 1.f;
         if ((a.cfg.adv_norm || a.cfg.plain_pg == 2) && e.mb_stats) { mean = __ldcg(e.mb_stats + 2 * m); rstd = __ldcg(e.mb_stats + 2 * m + 1); }
@@ -878,7 +878,7 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
         double l_clip = 0.0, l_vf = 0.0, l_ent = 0.0;
         uint32_t it = 0;
         for (int64_t tile = vb; tile < n_tiles; tile += vg, ++it) {
-            const bool valid = tile * TC_ROWS + r < a.mb_len;
+            const bool valid = tile * TC_ROWS + r < mb_len;
             const int xoff = SM_X + (int)(xb & 1) * 4 * CHUNK_B;
             ++xb;
             [[maybe_unused]] const int trow = (erow >= 0 && it < 2) ? erow + (int)it : -1;
@@ -1037,9 +1037,66 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
         }
         TRACE(erow, 42);
         // ---- optimizer step: the whole of it in every CTA, on the CTA's own copy of the state ----
+        // ---- grid barrier with the cross-rank gradient exchange folded into it ----
+        // Arrive: one atomic per CTA on a device counter.  The LAST CTA to arrive knows the local gradient is complete; with
+        // data-parallel ranks (ad.world > 1) it PUSHES the whole gradient (<= 28 KB) into slot [seq & 1][rank] of every
+        // peer's receive area (plain NVLink peer stores), fences, and publishes step `seq` in every peer's flag pad
+        // (st.release.sys) -- one flag per peer and step, not one signal per CTA (148 remote atomics on one word cost
+        // ~10 us).  Every CTA waits until the counter shows all local arrivals and, with ranks, for every peer's flag of
+        // this step (both in local memory).  Receive areas are double buffered by step parity: a peer
+        // overwrites parity b only after its own wait of the step in between, which needs this rank's flag of that step,
+        // which its last CTA publishes only after every CTA here has finished reading parity b.
+        int* s_last = s_has + TC_GROUPS;
+        const uint32_t seq = ad.seq + (uint32_t)m;
         __threadfence();
-        grid.sync();
+        __syncthreads();
+        const uint32_t arrivals = (uint32_t)(m + 1) * gridDim.x;  // counter value once every CTA has arrived at this barrier
+        if (rc == 0) s_last[0] = ad.world > 1 ? (atomicAdd(e.sync_words, 1u) + 1u == arrivals) : (atomicAdd(e.sync_words, 1u), 0);
+        __syncthreads();
+        if (s_last[0]) {
+            __threadfence();
+            if (ad.world > 1) {
+                const int64_t off = ((int64_t)(seq & 1u) * ad.world + ad.rank) * ad.n_stride;
+#pragma unroll
+                for (int u = 0; u < EP_OPT; ++u) {
+                    const int i = 4 * (rc + u * EP_THREADS);
+                    if (i < ad.n_stride) {
+                        float4 v;
+                        if (i + 3 < n) {
+                            v = __ldcg(reinterpret_cast<const float4*>(g_cur + i));
+                        } else {
+                            auto get = [&](int k) { return i + k < n ? __ldcg(g_cur + i + k) : 0.f; };
+                            v = make_float4(get(0), get(1), get(2), get(3));
+                        }
+                        for (int q = 0; q < ad.world; ++q)
+                            if (q != ad.rank) *reinterpret_cast<float4*>(ad.peer_recv[q] + off + i) = v;
+                    }
+                }
+                __syncthreads();
+                // one cumulative fence by the publishing thread (covers the CTA's peer stores, ordered before it by the barrier)
+                if (rc < ad.world && rc != ad.rank)
+                    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(ad.peer_flag[rc] + ad.rank), "r"(seq) : "memory");
+            }
+        }
+        if (rc == 0 || (ad.world > 1 && rc >= 32 && rc < 32 + ad.world && rc - 32 != ad.rank)) {
+            const uint32_t* w = rc == 0 ? e.sync_words : ad.peer_flag[ad.rank] + (rc - 32);
+            const uint32_t want = rc == 0 ? arrivals : seq;
+            const long long t0 = clock64();
+            uint32_t v;
+            do {
+                if (rc == 0) asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(w) : "memory");
+                else asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(w) : "memory");
+                if ((int32_t)(v - want) >= 0) break;
+                if (clock64() - t0 > 4000000000LL) {  // ~2 s: a CTA or a peer rank is missing; report instead of hanging the device
+                    if (ad.status) *ad.status = 1;
+                    break;
+                }
+            } while (true);
+        }
+        __syncthreads();
         TRACE(erow, 43);
+        const float* r_base = ad.world > 1 ? ad.peer_recv[ad.rank] + (int64_t)(seq & 1u) * ad.world * ad.n_stride : nullptr;
+        TRACE(erow, 48);
         float4 G[EP_OPT];  // all loads first (one L2 round trip)
         {
             const float gs = ad.grad_scale;
@@ -1051,6 +1108,20 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
                 } else {  // (buffer 0 is the net's own gradient array: exactly n floats)
                     auto get = [&](int k) { return i + k < n ? __ldcg(g_cur + i + k) : 0.f; };
                     G[u] = make_float4(get(0), get(1), get(2), get(3));
+                }
+            }
+            if (r_base) {  // sum over ranks in rank order (own contribution from the local buffer): the same order on every rank
+#pragma unroll
+                for (int u = 0; u < EP_OPT; ++u) {
+                    const int i = 4 * (rc + u * EP_THREADS);
+                    if (i < ad.n_stride) {
+                        float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+                        for (int q = 0; q < ad.world; ++q) {
+                            const float4 y = q == ad.rank ? G[u] : __ldcg(reinterpret_cast<const float4*>(r_base + (int64_t)q * ad.n_stride) + rc + u * EP_THREADS);
+                            sum.x += y.x; sum.y += y.y; sum.z += y.z; sum.w += y.w;
+                        }
+                        G[u] = sum;
+                    }
                 }
             }
             float sq = 0.f;
@@ -1159,6 +1230,7 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
         const int64_t lo = (int64_t)blockIdx.x * per, hi = lo + per < n ? lo + per : n;
         for (int64_t i = lo + rc; i < hi; i += EP_THREADS) g_last[i] = 0.f;
         if (blockIdx.x == 0 && rc == 0) *ad.step = step0 + e.n_mb;
+        if (blockIdx.x == 0 && rc == 0) e.sync_words[0] = 0u;  // arrival counter: zero between launches
     }
     tc::fence_before_sync();
     __syncthreads();
