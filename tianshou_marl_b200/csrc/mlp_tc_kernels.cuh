@@ -67,6 +67,12 @@ constexpr uint32_t TM_COLS_FWD = 128;
 constexpr int TC_GROUPS = 2;
 __device__ __forceinline__ int tc_tid() { return (int)(threadIdx.x & (TC_THREADS - 1)); }
 __device__ __forceinline__ int tc_grp() { return (int)(threadIdx.x / TC_THREADS); }
+// The thread that issues a group's MMAs: one elected lane of the group's first warp.  The warp index is a shuffle
+// broadcast, so the branch is warp-uniform for the compiler, and TcSetup::tmem / sbase are broadcast values too: the
+// descriptors are then built in uniform registers.  (With `if (tid == 0)` every operand went through R2UR inside an
+// elect loop: ~15 dependent instructions = 85 cycles per MMA, 3.9k of a tile's 10.3k cycles.)
+__device__ __forceinline__ int tc_warp_u() { return __shfl_sync(0xffffffffu, (int)((threadIdx.x >> 5) & (TC_THREADS / 32 - 1)), 0); }
+__device__ __forceinline__ bool tc_issuer(bool w0) { return w0 && tc::elect_one(); }  // w0 = TcSetup::w0 (warp-uniform, computed once)
 __device__ __forceinline__ void tc_group_sync() {
     asm volatile("bar.sync %0, %1;" ::"r"(1 + tc_grp()), "n"(TC_THREADS) : "memory");
 }
@@ -206,6 +212,7 @@ __device__ long long g_trace[4][64];
 struct TcSetup {
     uint64_t* bar;   // bar[0]: waited phases; bar[1]: the unwaited weight-gradient commits of the backward
     uint32_t tmem, lane_base, sbase, phase;  // sbase: CTA smem base >> 4
+    bool w0;         // this thread is in the group's first warp (shuffle broadcast: warp-uniform for the compiler)
 };
 
 // part A: nothing here depends on the parameters (runs ahead of pdl_wait()).  `smem` is the group's own map; TMEM is
@@ -253,10 +260,11 @@ __device__ __forceinline__ TcSetup tc_setup_finish(unsigned char* smem, const un
     const int warp = tc_tid() >> 5;
     tc_load_image(smem, image);
     tc_sync_for_mma();
-    s.tmem = *tmem_slot + tmem_col0;
+    s.tmem = __shfl_sync(0xffffffffu, *tmem_slot + tmem_col0, 0);
     s.lane_base = s.tmem + ((uint32_t)(warp * 32) << 16);
-    s.sbase = tc::smem_u32(smem) >> 4;  // descriptor units
+    s.sbase = __shfl_sync(0xffffffffu, tc::smem_u32(smem) >> 4, 0);  // descriptor units
     s.phase = 0;
+    s.w0 = tc_warp_u() == 0;
     return s;
 }
 
@@ -273,7 +281,7 @@ __device__ __forceinline__ void tc_forward_tile(unsigned char* smem, TcSetup& s,
     TRACE(trow, 1);
     tc_sync_for_mma();
     TRACE(trow, 2);
-    if (tc_tid() == 0) {
+    if (tc_issuer(s.w0)) {
 #pragma unroll
         for (int ks = 0; ks < TC_XF / 16; ++ks)
             tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase, xoff, ks), desc_w_k(s.sbase, SM_W1, TC_H, ks), ID64, ks > 0);
@@ -286,7 +294,7 @@ __device__ __forceinline__ void tc_forward_tile(unsigned char* smem, TcSetup& s,
     TRACE(trow, 5);
     tc_sync_for_mma();
     TRACE(trow, 6);
-    if (tc_tid() == 0) {
+    if (tc_issuer(s.w0)) {
 #pragma unroll
         for (int ks = 0; ks < TC_H / 16; ++ks)
             tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase, SM_H1, ks), desc_w_k(s.sbase, SM_W2, TC_H, ks), ID64, ks > 0);
@@ -300,7 +308,7 @@ __device__ __forceinline__ void tc_forward_tile(unsigned char* smem, TcSetup& s,
     TRACE(trow, 9);
     tc_sync_for_mma();
     TRACE(trow, 10);
-    if (tc_tid() == 0) {
+    if (tc_issuer(s.w0)) {
 #pragma unroll
         for (int ks = 0; ks < TC_H / 16; ++ks)
             tc::mma_f16(s.tmem + TM_OUT, desc_act_k(s.sbase, SM_H2, ks), desc_w_k(s.sbase, SM_W3, TC_OF, ks), ID16, ks > 0);
@@ -616,13 +624,13 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
         }
         if (a.debug & 2) {
             tc_sync_for_mma();
-            if (threadIdx.x == 0) tc::commit(s.bar + 1);
+            if (tc_issuer(s.w0)) tc::commit(s.bar + 1);
             continue;
         }
         TRACE(trow, 13);
         tc_sync_for_mma();
         TRACE(trow, 14);
-        if (threadIdx.x == 0) {
+        if (tc_issuer(s.w0)) {
             tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase, SM_G, 0), desc_w_mn(s.sbase, SM_W3, TC_OF, 0), ID_DH, 0);  // DH2 = G W3
             tc::commit(s.bar);
         }
@@ -633,7 +641,7 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
         TRACE(trow, 17);
         tc_sync_for_mma();
         TRACE(trow, 18);
-        if (threadIdx.x == 0) {
+        if (tc_issuer(s.w0)) {
 #pragma unroll
             for (int ks = 0; ks < TC_H / 16; ++ks)  // DH1 = D2 W2
                 tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase, SM_D2, ks), desc_w_mn(s.sbase, SM_W2, TC_H, ks), ID_DH, ks > 0);
@@ -646,7 +654,7 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
         TRACE(trow, 21);
         tc_sync_for_mma();
         TRACE(trow, 22);
-        if (threadIdx.x == 0) {
+        if (tc_issuer(s.w0)) {
             // the weight-gradient GEMMs: off the critical path, completion tracked by bar[1] only
             const uint32_t acc0 = it > 0;
 #pragma unroll
@@ -732,6 +740,7 @@ struct TcEpochArgs {
     TcPpoArgs p;           // mb_start = first batch position of the epoch; grads = gradient buffer 0
     float* grads1;         // gradient buffers 1 and 2 (minibatch m reduces into buffer m % 3; all zero on entry and on exit)
     float* grads2;
+    uint2* q_table;        // [EP_THREADS][EP_OPT + 1] scratch (see the kernel)
     uint32_t* sync_words;  // [0] arrival counter of the in-kernel grid barrier (zero between launches)
     int64_t n_mb, mb_size, total;  // minibatch m = [m * mb_size, (m + 1) * mb_size), the last one runs to `total`
     const float* mb_stats;         // [n_mb][2] or NULL
@@ -840,8 +849,13 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
     uint32_t xb = 0, wg_commits = 0;  // X buffer toggle and number of commits to bar[1] so far (its phase parity)
     // ---- this CTA's copy of the optimizer state: fp32 masters in registers, moments in the group's spare TMEM columns ----
     float4 Pr[EP_OPT];
-    uint2 Q[EP_OPT];        // image positions of the four parameters (0xffff: none), computed once
-    uint32_t q_contig = 0;  // bit u: they are four consecutive positions (W2 / W3 rows): one 8-byte store
+    // image positions of each float4's four parameters (0xffff: none) and, in word EP_OPT, bit u = "four consecutive
+    // positions" (W2 / W3 rows: one 8-byte store).  Computed once and parked in global memory (the same values from
+    // every CTA; a thread only reads back what it wrote itself): 15 registers less across the tile loop.
+    uint2* q_tab = e.q_table + (size_t)rc * (EP_OPT + 1);
+    {
+    uint2 Q[EP_OPT];
+    uint32_t q_contig = 0;
 #pragma unroll
     for (int u = 0; u < EP_OPT; ++u) {
         const int i = 4 * (rc + u * EP_THREADS);
@@ -856,6 +870,10 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
         Pr[u] = make_float4(get(ad.p, 0), get(ad.p, 1), get(ad.p, 2), get(ad.p, 3));
         ep_st4(s.lane_base + ep_m_col(u), make_float4(get(ad.m, 0), get(ad.m, 1), get(ad.m, 2), get(ad.m, 3)));
         ep_st4(s.lane_base + ep_v_col(u), make_float4(get(ad.v, 0), get(ad.v, 1), get(ad.v, 2), get(ad.v, 3)));
+    }
+#pragma unroll
+    for (int u = 0; u < EP_OPT; ++u) q_tab[u] = Q[u];
+    q_tab[EP_OPT] = make_uint2(q_contig, 0u);
     }
     tc::tmem_st_wait();
 
@@ -926,7 +944,7 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
             TRACE(trow, 13);
             tc_sync_for_mma();
             TRACE(trow, 14);
-            if (r == 0) {
+            if (tc_issuer(s.w0)) {
                 tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase, SM_G, 0), desc_w_mn(s.sbase, SM_W3, TC_OF, 0), ID_DH, 0);
                 tc::commit(s.bar);
             }
@@ -937,7 +955,7 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
             TRACE(trow, 17);
             tc_sync_for_mma();
             TRACE(trow, 18);
-            if (r == 0) {
+            if (tc_issuer(s.w0)) {
 #pragma unroll
                 for (int ks = 0; ks < TC_H / 16; ++ks)
                     tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase, SM_D2, ks), desc_w_mn(s.sbase, SM_W2, TC_H, ks), ID_DH, ks > 0);
@@ -950,7 +968,7 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
             TRACE(trow, 21);
             tc_sync_for_mma();
             TRACE(trow, 22);
-            if (r == 0) {
+            if (tc_issuer(s.w0)) {
                 const uint32_t acc0 = it > 0;
 #pragma unroll
                 for (int ks = 0; ks < TC_ROWS / 16; ++ks)
@@ -1046,6 +1064,10 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
         // this step (both in local memory).  Receive areas are double buffered by step parity: a peer
         // overwrites parity b only after its own wait of the step in between, which needs this rank's flag of that step,
         // which its last CTA publishes only after every CTA here has finished reading parity b.
+        uint2 Q[EP_OPT];  // (in flight across the barrier)
+#pragma unroll
+        for (int u = 0; u < EP_OPT; ++u) Q[u] = q_tab[u];
+        const uint32_t q_contig = q_tab[EP_OPT].x;
         int* s_last = s_has + TC_GROUPS;
         const uint32_t seq = ad.seq + (uint32_t)m;
         __threadfence();
