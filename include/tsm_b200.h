@@ -428,6 +428,17 @@ typedef struct tsm_rollout {
     int64_t list_cap;
 } tsm_rollout;
 
+/* One vector step of a lock-step rollout in ONE launch: tsm_mpe_step with auto-reset, then for every row the ring
+ * counters of tsm_buf_add (buffer_ids = arange, act / rew / flags written to the row's current slot of buf's time-major
+ * payload, ep_ret_out / ep_len_out as tsm_buf_add's outputs) and tsm_episode_stats (acc, optional episode list).
+ * Needs one sub-buffer per row (buf->n_bufs == n_envs * n_agents).
+ * replaces  BaseVectorEnv.step + ReplayBufferManager.add + the done-env loop of Collector._collect
+ *           (venvs.py:237-322, manager.py:131-193, collector.py:983-1024) */
+int tsm_rollout_step(const tsm_mpe* env, const tsm_buf* buf, const int32_t* act, float* obs_next, float* rew,
+                     uint8_t* terminated, uint8_t* truncated, float* obs_carry, double* ep_ret_out, int64_t* ep_len_out,
+                     double* acc, double* list_ret, int64_t* list_len, int64_t* list_count, int64_t list_capacity,
+                     tsm_stream_t stream);
+
 int tsm_collect_lockstep(const tsm_net* net, const tsm_mpe* env, const tsm_buf* buf, const tsm_rollout* ro, int64_t n_steps,
                          int mode, uint64_t seed, uint64_t counter0, int64_t lockstep_len, int n_random_act,
                          int64_t* slot_out, int64_t* lockstep_len_out, int* obs_in_carry_out, tsm_stream_t stream);

@@ -16,7 +16,7 @@ from .env import MPEVectorEnv
 from .utils import ActorCriticNet
 
 # kernels launched per public call (for gpu_launches): see the C entry points
-K_POLICY, K_MPE, K_ADD, K_STATS = 1, 1, 1, 1
+K_POLICY, K_ROLLOUT_STEP = 1, 1  # tsm_net_forward; tsm_rollout_step (world step + ring counters + episode statistics)
 
 
 class Workload:
@@ -39,9 +39,12 @@ class Workload:
         self.dtype = "f16 operands / f32 accumulate (tcgen05)" if args.engine == "tc" else "f32"
         B = self.R * self.T
         self.n_mb = len(PPO.split_bounds(B, args.batch_size)) - 1
-        self.launches_per_step = self.T * (K_POLICY + K_MPE + K_ADD + K_STATS) + 1
+        self.launches_per_step = self.T * (K_POLICY + K_ROLLOUT_STEP) + 1  # + buffer reset
         if self.update:
-            self.launches_per_step += 3 + 1 + args.repeat * (1 + 2 * self.n_mb)  # critic x2, logp, gae, per epoch: stats + (minibatch, adam)
+            # critic x2, logp_old, gae; per epoch: adv stats + either ONE persistent epoch kernel (tc engine, uniform
+            # minibatches) or a (minibatch, optimizer) launch pair per minibatch (fp32 engine)
+            per_epoch = 2 if args.engine == "tc" else 1 + 2 * self.n_mb
+            self.launches_per_step += 3 + 1 + args.repeat * per_epoch
             self.launches_per_step += 1 if args.engine == "tc" else 0  # pack_records
         self.h2d_bytes = 0
         self.d2h_bytes = 0

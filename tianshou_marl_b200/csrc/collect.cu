@@ -4,10 +4,10 @@
 // for the case every environment advances every step: per vector step
 //   policy forward + sample -> act / logp / value written straight into buffer slot t   (collector.py:704-767)
 //   batched MPE step        -> obs_next / rew / flags into slot t, next obs into slot t+1 (venvs.py:237-322)
-//   ring counters + episode return / length                                             (manager.py:131-193)
-//   episode statistics                                                                  (collector.py:983-1024)
+//   + ring counters, episode return / length (manager.py:131-193) and episode statistics (collector.py:983-1024) in
+//     the same launch (tsm_rollout_step)
 // The host loop costs ~3 us per launch instead of ~20 us of interpreter time, which is what bounds a rollout of
-// 4 small kernels per step.
+// 2 small kernels per step.
 #include "common.cuh"
 
 using namespace tsm;
@@ -45,13 +45,10 @@ extern "C" int tsm_collect_lockstep(const tsm_net* net, const tsm_mpe* env, cons
         const int64_t nxt = (slot + 1) % size;
         const bool to_carry = (k == n_steps - 1) || (len + 1 >= size);
         float* carry = to_carry ? ro->carry : ro->obs + nxt * R * O;
-        rc = tsm_mpe_step(env, act_slot, ro->obs_next + slot * R * O, ro->rew + slot * R, ro->terminated + slot * R,
-                          ro->truncated + slot * R, 1, carry, stream);
-        if (rc) return rc;
-        rc = tsm_buf_add(buf, nullptr, act_slot, ro->rew + slot * R, ro->terminated + slot * R, ro->truncated + slot * R, nullptr, nullptr,
-                         nullptr, nullptr, R, nullptr, ro->ep_ret, ro->ep_len, nullptr, stream);
-        if (rc) return rc;
-        rc = tsm_episode_stats(ro->ep_ret, ro->ep_len, R, ro->acc, ro->list_ret, ro->list_len, ro->list_count, ro->list_cap, stream);
+        // world step + ring counters + episode statistics: one launch
+        rc = tsm_rollout_step(env, buf, act_slot, ro->obs_next + slot * R * O, ro->rew + slot * R, ro->terminated + slot * R,
+                              ro->truncated + slot * R, carry, ro->ep_ret, ro->ep_len, ro->acc, ro->list_ret, ro->list_len, ro->list_count,
+                              ro->list_cap, stream);
         if (rc) return rc;
         len = len + 1 < size ? len + 1 : size;
         slot = nxt;

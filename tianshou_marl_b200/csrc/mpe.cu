@@ -145,11 +145,44 @@ __global__ void __launch_bounds__(THREADS) reset_kernel(tsm_mpe e, const int64_t
     }
 }
 
-template <int G>
+// ---- what a lock-step rollout does after the world step, fused into the same launch (tsm_rollout_step) ----
+// per row: the ring-buffer state machine of ReplayBufferManager.add (manager.py:131-193, buffer_base.py:355-410; the
+// standalone version is buf::add_state_kernel) and the episode statistics of Collector._collect (collector.py:983-1024;
+// standalone: buf::episode_stats_kernel).
+struct RolloutTail {
+    tsm_buf b;
+    double* ep_ret_out;   // [R] episode return of rows that finished an episode, else 0 (tsm_buf_add's outputs)
+    int64_t* ep_len_out;  // [R]
+    double* acc;          // [9] {count, sum ret, sum ret^2, min ret, max ret, sum len, sum len^2, min len, max len}
+    double* list_ret;     // optional episode list
+    int64_t* list_len;
+    int64_t* list_count;
+    int64_t list_cap;
+};
+__device__ __forceinline__ void atomic_min_f64(double* a, double v) {
+    unsigned long long* p = reinterpret_cast<unsigned long long*>(a);
+    unsigned long long old = *p;
+    while (__longlong_as_double((long long)old) > v) {
+        const unsigned long long prev = atomicCAS(p, old, (unsigned long long)__double_as_longlong(v));
+        if (prev == old) break;
+        old = prev;
+    }
+}
+__device__ __forceinline__ void atomic_max_f64(double* a, double v) {
+    unsigned long long* p = reinterpret_cast<unsigned long long*>(a);
+    unsigned long long old = *p;
+    while (__longlong_as_double((long long)old) < v) {
+        const unsigned long long prev = atomicCAS(p, old, (unsigned long long)__double_as_longlong(v));
+        if (prev == old) break;
+        old = prev;
+    }
+}
+
+template <int G, bool TAIL>
 __global__ void __launch_bounds__(THREADS) step_kernel(tsm_mpe e, const int32_t* __restrict__ act,
                                                       float* __restrict__ obs_next, float* __restrict__ rew,
                                                       uint8_t* __restrict__ term, uint8_t* __restrict__ trunc, int autoreset,
-                                                      float* __restrict__ obs_carry) {
+                                                      float* __restrict__ obs_carry, RolloutTail t) {
     const int64_t env = ((int64_t)blockIdx.x * THREADS + threadIdx.x) / G;
     const int j = threadIdx.x % G;
     const int A = e.n_agents, L = e.n_landmarks;
@@ -282,6 +315,77 @@ __global__ void __launch_bounds__(THREADS) step_kernel(tsm_mpe e, const int32_t*
         e.steps[env] = do_reset ? 0 : st;
         if (do_reset) e.episode[env] += 1;
     }
+    if constexpr (TAIL) {
+        // ---- ring counters of sub-buffer `row` (one per row, buffer_ids = arange) ----
+        bool dn = false;
+        double ret_done = 0.0;
+        int64_t len_done = 0;
+        if (is_agent) {
+            const tsm_buf& b = t.b;
+            const int64_t off = row * b.size, cur = b.ins[row];
+            const int64_t nsz = min(b.sz[row] + 1, b.size), nins = (cur + 1) % b.size;
+            dn = tr;  // no termination in these scenarios
+            const double eret = b.ep_ret[row] + (double)r;
+            const int64_t elen = b.ep_len[row] + 1, estart = b.ep_start[row];
+            const int64_t slot = cur * b.n_bufs + row;  // time-major payload
+            b.act[slot] = a;
+            b.rew[slot] = r;
+            b.terminated[slot] = 0;
+            b.truncated[slot] = tr ? 1 : 0;
+            b.done[slot] = dn ? 1 : 0;
+            ret_done = dn ? eret : 0.0;
+            len_done = dn ? elen : 0;
+            if (t.ep_ret_out) t.ep_ret_out[row] = ret_done;
+            if (t.ep_len_out) t.ep_len_out[row] = len_done;
+            b.ins[row] = nins;
+            b.sz[row] = nsz;
+            b.last_index[row] = cur + off;
+            b.ep_ret[row] = dn ? 0.0 : eret;
+            b.ep_len[row] = dn ? 0 : elen;
+            b.ep_start[row] = dn ? nins : estart;  // buffer_base.py:408
+        }
+        // ---- episode statistics: only on steps where some episode of this block ended ----
+        if (__syncthreads_or(dn ? 1 : 0)) {
+            __shared__ double s_part[THREADS / 32][9];
+            const double dl = (double)len_done;
+            double v[9] = {dn ? 1.0 : 0.0, ret_done, ret_done * ret_done, dn ? ret_done : INFINITY, dn ? ret_done : -INFINITY,
+                           dl, dl * dl, dn ? dl : INFINITY, dn ? dl : -INFINITY};
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) {
+#pragma unroll
+                for (int k = 0; k < 9; ++k) {
+                    const double o = __shfl_down_sync(0xffffffffu, v[k], d);
+                    v[k] = (k == 3 || k == 7) ? fmin(v[k], o) : ((k == 4 || k == 8) ? fmax(v[k], o) : v[k] + o);
+                }
+            }
+            const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+            if (lane == 0)
+#pragma unroll
+                for (int k = 0; k < 9; ++k) s_part[w][k] = v[k];
+            if (t.list_count) {  // one counter bump per warp, then every finished row writes its own entry
+                const unsigned m = __ballot_sync(0xffffffffu, dn);
+                if (m) {
+                    int64_t base = 0;
+                    if (lane == __ffs(m) - 1) base = (int64_t)atomicAdd(reinterpret_cast<unsigned long long*>(t.list_count), (unsigned long long)__popc(m));
+                    base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+                    const int64_t at = base + __popc(m & ((1u << lane) - 1u));
+                    if (dn && at < t.list_cap) { t.list_ret[at] = ret_done; t.list_len[at] = len_done; }
+                }
+            }
+            __syncthreads();
+            if (threadIdx.x < 9) {
+                const int k = threadIdx.x;
+                double x = s_part[0][k];
+                for (int ww = 1; ww < THREADS / 32; ++ww) {
+                    const double o = s_part[ww][k];
+                    x = (k == 3 || k == 7) ? fmin(x, o) : ((k == 4 || k == 8) ? fmax(x, o) : x + o);
+                }
+                if (k == 3 || k == 7) atomic_min_f64(t.acc + k, x);
+                else if (k == 4 || k == 8) atomic_max_f64(t.acc + k, x);
+                else atomicAdd(t.acc + k, x);
+            }
+        }
+    }
 }
 
 }  // namespace mpe
@@ -332,20 +436,40 @@ extern "C" int tsm_mpe_reset(const tsm_mpe* e, const int64_t* env_ids, int64_t n
     return TSM_OK;
 }
 
+template <bool TAIL>
+static int launch_step(const tsm_mpe* e, const int32_t* act, float* obs_next, float* rew, uint8_t* terminated, uint8_t* truncated,
+                       int autoreset, float* obs_carry, const RolloutTail& t, cudaStream_t s) {
+    const int G = group_width(e);
+    const unsigned grid = (unsigned)ceil_div(e->n_envs * G, THREADS);
+    switch (G) {
+        case 4: step_kernel<4, TAIL><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t); break;
+        case 8: step_kernel<8, TAIL><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t); break;
+        case 16: step_kernel<16, TAIL><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t); break;
+        default: step_kernel<32, TAIL><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t); break;
+    }
+    TSM_LAUNCH_CHECK();
+    return TSM_OK;
+}
+
 extern "C" int tsm_mpe_step(const tsm_mpe* e, const int32_t* act, float* obs_next, float* rew, uint8_t* terminated,
                             uint8_t* truncated, int autoreset, float* obs_carry, tsm_stream_t stream) {
     int rc = check_env(e, __func__);
     if (rc) return rc;
     TSM_REQUIRE(act && rew && terminated && truncated, "act/rew/terminated/truncated != NULL");
-    const int G = group_width(e);
-    const unsigned grid = (unsigned)ceil_div(e->n_envs * G, THREADS);
-    cudaStream_t s = as_stream(stream);
-    switch (G) {
-        case 4: step_kernel<4><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry); break;
-        case 8: step_kernel<8><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry); break;
-        case 16: step_kernel<16><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry); break;
-        default: step_kernel<32><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry); break;
-    }
-    TSM_LAUNCH_CHECK();
-    return TSM_OK;
+    return launch_step<false>(e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, RolloutTail{}, as_stream(stream));
+}
+
+extern "C" int tsm_rollout_step(const tsm_mpe* e, const tsm_buf* buf, const int32_t* act, float* obs_next, float* rew,
+                                uint8_t* terminated, uint8_t* truncated, float* obs_carry, double* ep_ret_out, int64_t* ep_len_out,
+                                double* acc, double* list_ret, int64_t* list_len, int64_t* list_count, int64_t list_capacity,
+                                tsm_stream_t stream) {
+    int rc = check_env(e, __func__);
+    if (rc) return rc;
+    TSM_REQUIRE(buf && act && rew && terminated && truncated && acc, "buf / act / rew / terminated / truncated / acc != NULL");
+    TSM_REQUIRE(buf->n_bufs == e->n_envs * e->n_agents && buf->size > 0, "one sub-buffer per row (n_bufs == n_envs * n_agents)");
+    TSM_REQUIRE(buf->ins && buf->sz && buf->last_index && buf->ep_len && buf->ep_start && buf->ep_ret, "counter arrays != NULL");
+    TSM_REQUIRE(buf->act && buf->rew && buf->terminated && buf->truncated && buf->done, "payload arrays != NULL");
+    TSM_REQUIRE(!list_count || (list_ret && list_len && list_capacity >= 0), "episode list arrays");
+    RolloutTail t{*buf, ep_ret_out, ep_len_out, acc, list_ret, list_len, list_count, list_capacity};
+    return launch_step<true>(e, act, obs_next, rew, terminated, truncated, 1, obs_carry, t, as_stream(stream));
 }
