@@ -257,7 +257,7 @@ typedef struct tsm_net {
                            image of params.  Refreshed by tsm_adam_step / tsm_ppo_epoch; call tsm_net_pack
                            after writing params any other way. */
 } tsm_net;
-#define TSM_TC_IMAGE_BYTES 90880 /* 16 896 image + tsm_ppo_epoch's two extra gradient buffers of 7 168 floats + 256 bytes of barrier words + a 16 KB index table */
+#define TSM_TC_IMAGE_BYTES 119552 /* 16 896 image + tsm_ppo_epoch's three more gradient-sized buffers of 7 168 floats + 256 bytes of barrier words + a 16 KB index table */
 
 int64_t tsm_net_param_count(int in_dim, int hidden, int out_dim);
 

@@ -309,12 +309,13 @@ int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, cons
     a.gscale = 1.f; a.inv_gscale = 1.f; a.loss_sums = nullptr;
     a.debug = getenv("TSM_TC_DEBUG") ? atoi(getenv("TSM_TC_DEBUG")) : 0;
     // workspace behind the image (TSM_TC_IMAGE_BYTES): two more gradient buffers
-    static_assert(TSM_TC_IMAGE_BYTES >= opt::IMG_BYTES + 2 * mlptc::EP_G_STRIDE * 4 + 256 + mlptc::EP_THREADS * (mlptc::EP_OPT + 1) * 8,
+    static_assert(TSM_TC_IMAGE_BYTES >= opt::IMG_BYTES + 2 * mlptc::EP_G_STRIDE * 4 + 256 + mlptc::EP_THREADS * (mlptc::EP_OPT + 1) * 8 + mlptc::EP_G_STRIDE * 4,
                   "TSM_TC_IMAGE_BYTES too small for the epoch kernel's workspace");
     e.grads1 = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(net->tc_image) + opt::IMG_BYTES);
     e.grads2 = e.grads1 + mlptc::EP_G_STRIDE;
     e.sync_words = reinterpret_cast<uint32_t*>(e.grads2 + mlptc::EP_G_STRIDE);
     e.q_table = reinterpret_cast<uint2*>(e.sync_words + 64);
+    e.g_total = reinterpret_cast<float*>(e.q_table + mlptc::EP_THREADS * (mlptc::EP_OPT + 1));
     e.n_mb = n_mb; e.mb_size = mb_size; e.total = total; e.mb_stats = mb_stats; e.loss_sums = loss_sums; e.adam = adam;
     const int64_t tiles = ceil_div(n_mb > 1 ? mb_size : total, mlptc::TC_ROWS);
     const unsigned grid = (unsigned)std::min<int64_t>(ceil_div(tiles, (int64_t)mlptc::TC_GROUPS), (int64_t)sm_count() * occ);

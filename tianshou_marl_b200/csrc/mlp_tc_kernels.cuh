@@ -741,7 +741,8 @@ struct TcEpochArgs {
     float* grads1;         // gradient buffers 1 and 2 (minibatch m reduces into buffer m % 3; all zero on entry and on exit)
     float* grads2;
     uint2* q_table;        // [EP_THREADS][EP_OPT + 1] scratch (see the kernel)
-    uint32_t* sync_words;  // [0] arrival counter of the in-kernel grid barrier (zero between launches)
+    float* g_total;        // [EP_G_STRIDE] sum over ranks (world > 2 only)
+    uint32_t* sync_words;  // [0], [1] arrival counters of the in-kernel grid barriers (zero between launches)
     int64_t n_mb, mb_size, total;  // minibatch m = [m * mb_size, (m + 1) * mb_size), the last one runs to `total`
     const float* mb_stats;         // [n_mb][2] or NULL
     double* loss_sums;             // [n_mb][4] or NULL
@@ -1118,6 +1119,47 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
         __syncthreads();
         TRACE(erow, 43);
         const float* r_base = ad.world > 1 ? ad.peer_recv[ad.rank] + (int64_t)(seq & 1u) * ad.world * ad.n_stride : nullptr;
+        const float* g_src = g_cur;  // where the (summed) gradient is read from below
+        if (ad.world > 2) {
+            // More than two ranks: every CTA reading all `world` slots would move world x 28 KB x grid through L2 per step.
+            // Slice owners sum the slots of their slice (rank order) into g_total, one more grid barrier, and everybody
+            // reads the total once.
+            const int64_t n4s = ad.n_stride / 4, per4 = (n4s + gridDim.x - 1) / gridDim.x;
+            const int64_t lo4 = (int64_t)blockIdx.x * per4, hi4 = lo4 + per4 < n4s ? lo4 + per4 : n4s;
+            for (int64_t j = lo4 + rc; j < hi4; j += EP_THREADS) {
+                float4 own;
+                if (4 * j + 3 < n) {
+                    own = __ldcg(reinterpret_cast<const float4*>(g_cur) + j);
+                } else {
+                    auto get = [&](int k) { return 4 * j + k < n ? __ldcg(g_cur + 4 * j + k) : 0.f; };
+                    own = make_float4(get(0), get(1), get(2), get(3));
+                }
+                float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int q = 0; q < ad.world; ++q) {
+                    const float4 y = q == ad.rank ? own : __ldcg(reinterpret_cast<const float4*>(r_base + (int64_t)q * ad.n_stride) + j);
+                    sum.x += y.x; sum.y += y.y; sum.z += y.z; sum.w += y.w;
+                }
+                __stcg(reinterpret_cast<float4*>(e.g_total) + j, sum);
+            }
+            __threadfence();
+            __syncthreads();
+            if (rc == 0) {
+                atomicAdd(e.sync_words + 1, 1u);
+                const long long t0 = clock64();
+                uint32_t v;
+                do {
+                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(e.sync_words + 1) : "memory");
+                    if ((int32_t)(v - arrivals) >= 0) break;
+                    if (clock64() - t0 > 4000000000LL) {
+                        if (ad.status) *ad.status = 1;
+                        break;
+                    }
+                } while (true);
+            }
+            __syncthreads();
+            g_src = e.g_total;
+            r_base = nullptr;
+        }
         TRACE(erow, 48);
         float4 G[EP_OPT];  // all loads first (one L2 round trip)
         {
@@ -1126,9 +1168,9 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
             for (int u = 0; u < EP_OPT; ++u) {
                 const int i = 4 * (rc + u * EP_THREADS);
                 if (i + 3 < n) {
-                    G[u] = __ldcg(reinterpret_cast<const float4*>(g_cur) + rc + u * EP_THREADS);
+                    G[u] = __ldcg(reinterpret_cast<const float4*>(g_src) + rc + u * EP_THREADS);
                 } else {  // (buffer 0 is the net's own gradient array: exactly n floats)
-                    auto get = [&](int k) { return i + k < n ? __ldcg(g_cur + i + k) : 0.f; };
+                    auto get = [&](int k) { return i + k < n ? __ldcg(g_src + i + k) : 0.f; };
                     G[u] = make_float4(get(0), get(1), get(2), get(3));
                 }
             }
@@ -1252,7 +1294,7 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
         const int64_t lo = (int64_t)blockIdx.x * per, hi = lo + per < n ? lo + per : n;
         for (int64_t i = lo + rc; i < hi; i += EP_THREADS) g_last[i] = 0.f;
         if (blockIdx.x == 0 && rc == 0) *ad.step = step0 + e.n_mb;
-        if (blockIdx.x == 0 && rc == 0) e.sync_words[0] = 0u;  // arrival counter: zero between launches
+        if (blockIdx.x == 0 && rc < 2) e.sync_words[rc] = 0u;  // arrival counters: zero between launches
     }
     tc::fence_before_sync();
     __syncthreads();
