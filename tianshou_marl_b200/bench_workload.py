@@ -98,22 +98,26 @@ class Workload:
         dom = max(stages, key=lambda k: stages[k]["ms_per_step"])
         out: dict[str, Any] = {"kernel": dom, "peak_source": peak_src}
         if dom == "ppo_epoch":
-            # one stage call = n_mb x (minibatch kernel + optimizer kernel); per-launch figures of the minibatch kernel:
             # algorithmic FLOPs fwd + 2x bwd = 33.8 kFLOP/row, algorithmic bytes = one 96-byte record per row (tc engine) or
-            # 4*O + 20 gathered bytes (fp32 engine); duration = stage time / n_mb (so it also carries the optimizer kernel)
-            rows = min(self.args.batch_size, B)
-            t = stages[dom]["launch_ms"] * 1e-3 / self.n_mb
+            # 4*O + 20 gathered bytes (fp32 engine).  tc engine, uniform minibatches: ONE persistent launch (tc_ppo_epoch_kernel)
+            # per epoch = per stage call, optimizer steps and grid barriers inside; fp32 engine: a launch pair per minibatch.
+            persistent = self.args.engine == "tc" and B % self.args.batch_size == 0
+            rows = B if persistent else min(self.args.batch_size, B)
+            t = stages[dom]["launch_ms"] * 1e-3 / (1 if persistent else self.n_mb)
             flop = 3.0 * fwd_flop * rows
             ach = flop / t / 1e12
             rec_bytes = 96.0 if self.args.engine == "tc" else 4.0 * O + 20.0
-            out.update({"bound": "tensor", "achieved": ach, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach / tf_peak,
-                        # dram__bytes_read.sum + dram__bytes_write.sum of tc_ppo_minibatch_kernel, one launch of 65 536 rows,
-                        # profiles/r01_ncu_full_tc_ppo_minibatch.csv (ncu --set full); null for other shapes / engines
-                        "traffic": 12.68e6 if (self.args.engine == "tc" and rows == 65536 and O == 18) else None,
+            out.update({"kernel": "tc_ppo_epoch_kernel" if persistent else "ppo_minibatch_kernel",
+                        "bound": "tensor", "achieved": ach, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach / tf_peak,
+                        # dram__bytes_read.sum + dram__bytes_write.sum of one tc_ppo_epoch_kernel launch over 25 165 824 rows,
+                        # profiles/r01_ncu_full_v4.csv (ncu --set full); null for other shapes / engines
+                        "traffic": 4.848e9 if (persistent and rows == 25165824 and O == 18) else None,
                         "flop_per_unit": 3.0 * fwd_flop, "bytes_per_unit": rec_bytes, "units_per_launch": rows,
-                        "launch_us": t * 1e6, "hbm_gbs": rec_bytes * rows / t / 1e9,
-                        "note": "engine=%s; latency bound (two 128-row tiles per CTA per launch): launch_us = stage time / %d "
-                                "minibatches and includes the 8-CTA optimizer kernel" % (self.args.engine, self.n_mb)})
+                        "launch_us": t * 1e6, "minibatch_us": stages[dom]["launch_ms"] * 1e3 / self.n_mb,
+                        "hbm_gbs": rec_bytes * rows / t / 1e9,
+                        "note": "engine=%s; latency bound: per minibatch two rounds of 128-row tiles per SM tile group (5 dependent "
+                                "tcgen05 GEMM stages + loss each), gradient flush, one grid barrier, optimizer step in every CTA; "
+                                "%d minibatches per launch" % (self.args.engine, self.n_mb if persistent else 1)})
         elif dom in ("policy_forward", "critic_forward", "logp_old_forward"):
             flop = fwd_flop * units[dom]
             t = stages[dom]["launch_ms"] * 1e-3
