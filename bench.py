@@ -49,6 +49,10 @@ def parse() -> argparse.Namespace:
     p.add_argument("--hidden", type=int, default=64)
     p.add_argument("--engine", default="tc", choices=["tc", "fp32"], help="MLP kernels: tcgen05 (fp16 operands, fp32 accumulate) or exact fp32")
     p.add_argument("--no-update", action="store_true", help="collect + GAE only")
+    p.add_argument("--reuse-rollout", action="store_true",
+                   help="PPO(reuse_rollout_policy_outputs=True): critic(obs) / logp_old come from the collect-time forward (off in the headline run)")
+    p.add_argument("--workload", default="c2", choices=["c2", "c5"],
+                   help="c2: the headline collect+GAE+PPO step; c5: GAE + buffer add/sample microbench (T=128, 1M rows), one GPU")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--cpu-envs", type=int, default=4096, help="reference arm: environments in the bounded sample")
     p.add_argument("--cpu-horizon", type=int, default=64)
@@ -205,6 +209,78 @@ def reference_main(args: argparse.Namespace) -> None:
 
 
 # ------------------------------------------------------------------------------------------
+def c5_main(args: argparse.Namespace) -> None:
+    """BASELINE.json configs[4]: GAE + buffer add / sample at T = 128, envs x agents = 1 048 576, gamma 0.99, lambda 0.95.
+    One step = T vector adds of R rows (obs dim 18) through VectorReplayBuffer.add, GAE over the [T, R] block in place,
+    sample_indices(0) over the full buffer.  Inputs per SURVEY 8(d): done every 25th step with a per-row phase, 1 % terminated."""
+    import torch
+
+    from tianshou_marl_b200 import _lib
+    from tianshou_marl_b200.algorithm import gae_time_major
+    from tianshou_marl_b200.data import Batch, VectorReplayBuffer
+
+    torch.cuda.set_device(0)
+    _lib.lib()
+    try:
+        hbm_peak, src = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"], "measured"
+    except Exception:
+        hbm_peak, src = 6650.0, "fallback"
+    T, R, O = 128, 1 << 20, 18
+    g = torch.Generator(device="cuda").manual_seed(0)
+    obs = torch.randn(R, O, device="cuda", generator=g)
+    obs2 = torch.randn(R, O, device="cuda", generator=g)
+    act = torch.randint(0, 5, (R,), device="cuda", generator=g, dtype=torch.int32)
+    rew = torch.randn(R, device="cuda", generator=g)
+    phase = torch.randint(0, 25, (R,), device="cuda", generator=g)
+    trunc = [(((t + phase) % 25) == 24).to(torch.uint8) for t in range(25)]
+    term = (torch.rand(R, device="cuda", generator=g) < 0.01).to(torch.uint8)
+    buf = VectorReplayBuffer(T * R, R, index_type="torch")
+    v_s, v_n = torch.randn(T, R, device="cuda", generator=g), torch.randn(T, R, device="cuda", generator=g)
+    adv, ret = torch.empty_like(v_s), torch.empty_like(v_s)
+    ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+    tot = {"add": 0.0, "gae": 0.0, "sample_indices": 0.0}
+
+    def step(timed: bool) -> None:
+        buf.reset()
+        e = [ev() for _ in range(4)]
+        e[0].record()
+        for t in range(T):
+            buf.add(Batch(obs=obs, act=act, rew=rew, terminated=term, truncated=trunc[t % 25], obs_next=obs2))
+        e[1].record()
+        st = buf._store
+        gae_time_major(v_s, v_n, st["rew"], st["terminated"], st["truncated"], 0, T, 0.99, 0.95, adv, ret)
+        e[2].record()
+        idx = buf.sample_indices(0)
+        e[3].record()
+        torch.cuda.synchronize()
+        assert idx.numel() == T * R
+        if timed:
+            for k, (a, b) in zip(tot, ((0, 1), (1, 2), (2, 3))):
+                tot[k] += e[a].elapsed_time(e[b])
+
+    for _ in range(max(args.warmup, 3)):
+        step(False)
+    with Clocks(0) as clk:
+        for _ in range(args.steps):
+            step(True)
+    n = T * R
+    ms = {k: v / args.steps for k, v in tot.items()}
+    gbs = {"gae": GAE_BYTES_PER_ELT * n / ms["gae"] / 1e6, "add": (2 * 4 * O + 4 + 4 + 3) * n / ms["add"] / 1e6,
+           "sample_indices": 8 * n / ms["sample_indices"] / 1e6}
+    line = {"metric": "GAE GB/s vs HBM peak", "value": gbs["gae"], "unit": "GB/s", "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": sum(ms.values()), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 I/O, f64 carry",
+            "data": "synthetic", "config": {"workload": "C5 GAE + buffer add/sample microbench T=128 rows=1048576 gamma=0.99 lambda=0.95 obs_dim=18",
+                                            "l2": "inputs larger than L2: 2.95 GB per GAE call, 20.8 GB per 128 adds"},
+            "clocks": clk.summary(), "gpu_launches": args.steps * (1 + 2 * T + 1 + 1),
+            "stages_ms": ms,
+            "roofline": {"kernel": "gae_tm_kernel", "bound": "hbm", "achieved": gbs["gae"], "peak": hbm_peak, "peak_source": src, "unit": "GB/s",
+                         "frac": gbs["gae"] / hbm_peak, "traffic": None, "bytes_per_unit": GAE_BYTES_PER_ELT, "units_per_launch": n,
+                         "buffer_add": {"achieved": gbs["add"], "frac": gbs["add"] / hbm_peak, "bytes_per_unit": 2 * 4 * O + 11,
+                                        "note": "128 VectorReplayBuffer.add calls of 1M rows (payload copy + counters kernel each)"},
+                         "sample_indices": {"achieved": gbs["sample_indices"], "frac": gbs["sample_indices"] / hbm_peak, "bytes_per_unit": 8}}}
+    print(json.dumps(line))
+
+
 def main() -> None:
     args = parse()
     # stdout carries exactly ONE JSON line: anything a library prints there (NCCL's version banner under torchrun) goes to stderr
@@ -218,6 +294,10 @@ def main() -> None:
 
     if args.impl == "reference":
         reference_main(args)
+        return
+    if args.workload == "c5":
+        if int(os.environ.get("RANK", "0")) == 0:
+            c5_main(args)
         return
     import torch
     import torch.distributed as dist

@@ -84,6 +84,15 @@ int tsm_gae_tm(const float* v_s, const float* v_next, const float* rew,
                int64_t size, int64_t n_rows, int64_t start, int64_t len,
                double gamma, double lam, float* adv_out, float* ret_out, tsm_stream_t stream);
 
+/* critic(obs_next) from the values the policy forward stored at collect time (time-major [size][n_rows], valid slots
+ * (start + j) % size, j < len): v_next[slot][row] = value[next slot][row] where obs_next IS the next stored obs (row not
+ * done at that slot and not the last collected slot); the other (slot * n_rows + row) positions are appended to
+ * need_list (capacity len * n_rows, any order) and counted in *need_count (device int64) -- evaluate the critic on
+ * obs_next for exactly those rows (tsm_net_forward with rows = need_list, scatter = 1).
+ * replaces  the second critic pass of A2C._add_returns_and_advantages  tianshou/algorithm/modelfree/a2c.py:120-127 */
+int tsm_values_next_prepare(const float* value, const uint8_t* done, int64_t size, int64_t n_rows, int64_t start, int64_t len,
+                            float* v_next, int64_t* need_list, int64_t* need_count, tsm_stream_t stream);
+
 /* =========================================================================================
  * K2  Device ring buffer (VectorReplayBuffer)
  * replaces  ReplayBufferManager.add             tianshou/data/buffer/manager.py:131-193

@@ -193,3 +193,45 @@ def test_device_order_update_runs_and_learns_value():
     seq = alg.last_sequences
     assert np.isfinite(seq["loss"]).all()
     assert seq["vf"][-1] < 0.7 * seq["vf"][0]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("engine", ["fp32", "tc"])
+def test_reuse_rollout_policy_outputs(engine):
+    """PPO(reuse_rollout_policy_outputs=True) takes critic(obs) / logp_old from the collect-time forward and evaluates the
+    critic on obs_next only where an episode ended (a2c.py:120-127, ppo.py:157-161 recompute both).  Same parameters, same
+    kernels: everything the update is fed with (values, logp_old, advantages, returns) must agree BIT FOR BIT with the
+    recomputing path; the parameters after the update agree up to the order of the gradient atomics.  The stamp on the
+    buffer goes stale once the parameters move."""
+    from tianshou_marl_b200.algorithm import PPO, AdamOptimizerFactory, DiscreteActorPolicy
+    from tianshou_marl_b200.data import Collector, VectorReplayBuffer
+    from tianshou_marl_b200.env import MPEVectorEnv
+    from tianshou_marl_b200.utils import ActorCriticNet
+
+    E, A, T = 96, 3, 60  # 60 steps: two truncations (max_cycles 25) inside the rollout
+    res = []
+    for reuse in (False, True):
+        env = MPEVectorEnv("simple_spread_v3", n_envs=E, n_agents=A, seed=5)
+        buf = VectorReplayBuffer(T * E * A, E * A, index_type="torch")
+        net = ActorCriticNet(env.obs_dim, 64, 5, seed=3, engine=engine)
+        pol = DiscreteActorPolicy(actor=net, seed=11)
+        alg = PPO(policy=pol, critic=net, optim=AdamOptimizerFactory(lr=1e-3), max_grad_norm=0.5, minibatch_order="device", seed=2,
+                  reuse_rollout_policy_outputs=reuse)
+        col = Collector(alg, env, buf)
+        col.reset()
+        pol.is_within_training_step = True
+        col.collect(n_step=T * E * A)
+        assert buf._policy_version == net.param_version
+        alg.update(buf, 2048, 2)
+        assert buf._policy_version != net.param_version  # parameters moved on: the stored outputs are stale now
+        w = alg._work
+        v_s = buf._store["value"] if reuse else w["v_s"]
+        logp = buf._store["logp"] if reuse else w["logp_old"]
+        res.append({"v_s": v_s.clone(), "v_n": w["v_n"].clone(), "logp": logp.clone(), "adv": w["adv"].clone(), "ret": w["ret"].clone(),
+                    "p": net.flat.detach().clone(), "timed_passes": None})
+        # a second update from the same (now stale) buffer must take the recomputing path and still work
+        st2 = alg.update(buf, 2048, 1)
+        assert np.isfinite(st2.loss.mean)
+    for k in ("v_s", "v_n", "logp", "adv", "ret"):
+        assert torch.equal(res[0][k], res[1][k]), k
+    assert torch.allclose(res[0]["p"], res[1]["p"], atol=2e-5 if engine == "fp32" else 2e-3)

@@ -175,6 +175,7 @@ class CTDEPolicy:
             pb.records = P(rec)
         _lib.check(L.tsm_ppo_minibatch(net.desc, C.byref(pb), C.byref(cfg), 0, n, P(stats), P(sums), S))
         _lib.check(L.tsm_adam_step(net.desc, opt.lr, opt.betas[0], opt.betas[1], opt.eps, 0.0, 1.0, None, S))
+        net.kernel_updates += 1
 
     def soft_update_targets(self) -> None:
         """ctde.py:200-208: no target networks are attached on this path (the reference only updates them when present)."""

@@ -201,18 +201,35 @@ class PPO:
         adv = self._buf("adv", (size, R))
         ret = self._buf("ret", (size, R))
         # ---- _add_returns_and_advantages (a2c.py:113-151): critic(obs), critic(obs_next) ----
-        if self.reuse_rollout and "value" in st and "logp" in st:
-            raise NotImplementedError("reuse_rollout_policy_outputs is wired by the fused collector")
         slots = None  # storage slots (t * R + row) this update touches; None = all
         if rows is not None:
             rows = rows.to(device=net.device, dtype=torch.int64).contiguous()
             slots = (torch.arange(size, device=net.device, dtype=torch.int64)[:, None] * R + rows[None, :]).reshape(-1).contiguous()
-        tk = _lib.t_start("critic_forward")
-        net.forward(obs_all, mode="raw", out={"value": v_s.view(-1)}, rows=slots, scatter=slots is not None)
-        _lib.t_stop(tk)
-        tk = _lib.t_start("critic_forward")
-        net.forward(st["obs_next"].view(size * R, O), mode="raw", out={"value": v_n.view(-1)}, rows=slots, scatter=slots is not None)
-        _lib.t_stop(tk)
+        # reuse_rollout_policy_outputs: the fused collector stored value = critic(obs) and logp = log pi(act | obs) of EVERY valid
+        # slot, computed by the same forward kernel with the parameters this update starts from (buffer._policy_version), so
+        # critic(obs) and logp_old need no second pass, and critic(obs_next[t]) = value[t + 1] wherever obs_next[t] is the
+        # next stored obs; only rows whose episode ended at t and the last slot get a critic evaluation of obs_next.
+        reuse = (self.reuse_rollout and lockstep and rows is None and "value" in st and "logp" in st and net.value_index >= 0
+                 and getattr(self.policy, "actor", None) is net and buffer._policy_version is not None
+                 and buffer._policy_version == net.param_version)
+        if reuse:
+            tk = _lib.t_start("critic_forward")
+            v_s, logp = st["value"], st["logp"]
+            start0 = buffer._lockstep_ins if lock_len == size else 0
+            need = self._buf("need_list", (size * R,), torch.int64)
+            cnt = self._buf("need_count", (1,), torch.int64)
+            _lib.check(L.tsm_values_next_prepare(P(v_s), P(st["done"]), size, R, start0, lock_len, P(v_n), P(need), P(cnt), S))
+            n_need = int(cnt.item())
+            if n_need > 0:
+                net.forward(st["obs_next"].view(size * R, O), mode="raw", out={"value": v_n.view(-1)}, rows=need[:n_need], scatter=True)
+            _lib.t_stop(tk)
+        else:
+            tk = _lib.t_start("critic_forward")
+            net.forward(obs_all, mode="raw", out={"value": v_s.view(-1)}, rows=slots, scatter=slots is not None)
+            _lib.t_stop(tk)
+            tk = _lib.t_start("critic_forward")
+            net.forward(st["obs_next"].view(size * R, O), mode="raw", out={"value": v_n.view(-1)}, rows=slots, scatter=slots is not None)
+            _lib.t_stop(tk)
         tk = _lib.t_start("gae")
         if lockstep:
             start = buffer._lockstep_ins if lock_len == size else 0
@@ -244,10 +261,11 @@ class PPO:
             start, lock_len = 0, size
         _lib.t_stop(tk)
         # ---- logp_old (ppo.py:157-161) ----
-        tk = _lib.t_start("logp_old_forward")
-        net.forward(obs_all, mode="eval", act=st["act"].view(-1), out={"logp": logp.view(-1), "value": self._buf("scratch_v", (size * R,))},
-                    rows=slots, scatter=slots is not None)
-        _lib.t_stop(tk)
+        if not reuse:
+            tk = _lib.t_start("logp_old_forward")
+            net.forward(obs_all, mode="eval", act=st["act"].view(-1), out={"logp": logp.view(-1), "value": self._buf("scratch_v", (size * R,))},
+                        rows=slots, scatter=slots is not None)
+            _lib.t_stop(tk)
         # ---- minibatch loop (ppo.py:173-216) ----
         bounds = self.split_bounds(B, batch_size)
         n_mb = len(bounds) - 1
@@ -322,6 +340,7 @@ class PPO:
                     torch.distributed.all_reduce(net.grads)  # NCCL sum over ranks
                     _lib.check(L.tsm_adam_step(net.desc, o.lr, o.betas[0], o.betas[1], o.eps, mgn, 1.0 / world, None, S))
             _lib.t_stop(tk)
+        net.kernel_updates += repeat * n_mb
         # ---- stats: one device -> host copy for the whole update (the reference does 4 .item() per minibatch) ----
         h = sums.cpu().numpy()
         if self._peers is not None:

@@ -30,7 +30,7 @@ class Workload:
         self.net = ActorCriticNet(self.O, args.hidden, 5, seed=0, engine=args.engine)  # same init on every rank
         self.policy = DiscreteActorPolicy(actor=self.net, seed=77 + rank)
         self.alg = PPO(policy=self.policy, critic=self.net, optim=AdamOptimizerFactory(lr=3e-4), max_grad_norm=0.5,
-                       minibatch_order="device", seed=rank)
+                       minibatch_order="device", seed=rank, reuse_rollout_policy_outputs=bool(getattr(args, "reuse_rollout", False)))
         self.collector = Collector(self.alg, self.env, self.buf, episode_list=False)
         self.collector.reset()
         self.policy.is_within_training_step = True
@@ -139,6 +139,6 @@ class Workload:
         what = "collect+GAE+PPO update" if self.update else "collect+buffer write (no update)"
         return {"workload": f"C2 simple_spread_v3 A={self.A} E={self.E}/GPU T={self.T}: {what}; shared actor-critic MLP "
                             f"{self.O}->{a.hidden}->{a.hidden}->(5 logits, 1 value)", "envs_per_gpu": self.E, "agents": self.A,
-                "horizon": self.T, "rows_per_gpu": self.R, "batch_size": a.batch_size, "repeat": a.repeat, "hidden": a.hidden, "engine": a.engine,
+                "horizon": self.T, "rows_per_gpu": self.R, "batch_size": a.batch_size, "repeat": a.repeat, "hidden": a.hidden, "engine": a.engine, "reuse_rollout_policy_outputs": bool(getattr(a, "reuse_rollout", False)),
                 "minibatches_per_epoch": self.n_mb,
                 "l2": "inputs larger than L2: per-step working set %.0f MB > 126 MB" % (self.R * self.T * (8 * self.O + 30) / 1e6)}

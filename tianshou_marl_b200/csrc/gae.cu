@@ -262,6 +262,60 @@ __global__ void __launch_bounds__(TM_THREADS) gae_tm_kernel(
 using namespace tsm;
 using namespace tsm::gae;
 
+// ---------------------------------------------------------------------------------------------
+// critic(obs_next) without a second full forward pass (a2c.py:120-127 evaluates the critic on obs and on obs_next).
+// In a rollout obs_next[t] IS obs[t + 1] unless the row's episode ended at t (the env was reset) or t is the last
+// collected slot, so v(obs_next[t]) = value[t + 1] there -- the value the policy forward already produced at collect time.
+// This kernel writes those shifted values and appends the (slot, row) pairs that do need a critic evaluation of obs_next
+// to need_list (order irrelevant: the forward kernel scatters by index).
+namespace tsm {
+namespace gae {
+__global__ void __launch_bounds__(256) values_next_kernel(const float* __restrict__ value, const uint8_t* __restrict__ done, int64_t size,
+                                                         int64_t n_rows, int64_t start, int64_t len, float* __restrict__ v_next,
+                                                         int64_t* __restrict__ need_list, unsigned long long* __restrict__ need_count) {
+    const int64_t total = len * n_rows;
+    const int lane = threadIdx.x & 31;
+    for (int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) - lane; i0 < total; i0 += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = i0 + lane;
+        bool need = false;
+        int64_t at = 0;
+        if (i < total) {
+            const int64_t j = i / n_rows, r = i - j * n_rows;     // j-th slot in time order
+            const int64_t p = (start + j) % size;                 // its ring slot
+            at = p * n_rows + r;
+            need = done[at] != 0 || j == len - 1;
+            v_next[at] = need ? 0.f : value[((p + 1) % size) * n_rows + r];
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, need);
+        if (m) {
+            unsigned long long base = 0;
+            if (lane == __ffs(m) - 1) base = atomicAdd(need_count, (unsigned long long)__popc(m));
+            base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+            if (need) need_list[base + __popc(m & ((1u << lane) - 1u))] = at;
+        }
+    }
+}
+}  // namespace gae
+}  // namespace tsm
+
+extern "C" int tsm_values_next_prepare(const float* value, const uint8_t* done, int64_t size, int64_t n_rows, int64_t start, int64_t len,
+                                       float* v_next, int64_t* need_list, int64_t* need_count, tsm_stream_t stream) {
+    using namespace tsm;
+    TSM_REQUIRE(value && done && v_next && need_list && need_count, "value / done / v_next / need_list / need_count != NULL");
+    TSM_REQUIRE(size > 0 && n_rows > 0 && start >= 0 && start < size && len >= 0 && len <= size, "size, n_rows > 0; 0 <= start < size; 0 <= len <= size");
+    cudaStream_t s = as_stream(stream);
+    TSM_CUDA(cudaMemsetAsync(need_count, 0, sizeof(int64_t), s));
+    if (len == 0) return TSM_OK;
+    const int64_t total = len * n_rows;
+    int64_t grid = ceil_div(total, (int64_t)256);
+    const int64_t cap = (int64_t)sm_count() * 16;
+    if (grid > cap) grid = cap;
+    gae::values_next_kernel<<<(unsigned)grid, 256, 0, s>>>(value, done, size, n_rows, start, len, v_next, need_list,
+                                                          reinterpret_cast<unsigned long long*>(need_count));
+    TSM_LAUNCH_CHECK();
+    return TSM_OK;
+}
+
 extern "C" size_t tsm_gae_flat_workspace_bytes(int64_t n) {
     if (n < 0) n = 0;
     int64_t tiles = ceil_div(n, TILE);

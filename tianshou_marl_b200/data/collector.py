@@ -212,6 +212,9 @@ class Collector:
                              acc=P(self._acc), list_ret=P(self._list_ret) if self.episode_list else None,
                              list_len=P(self._list_len) if self.episode_list else None,
                              list_count=P(self._list_count) if self.episode_list else None, list_cap=self._list_cap)
+        # which parameters produced the stored logp / value (PPO's reuse_rollout_policy_outputs checks this)
+        ver = None if random or st.get("value") is None or self.policy.actor.value_index < 0 else self.policy.actor.param_version
+        buf._policy_version = ver if (buf._lockstep_len == 0 or buf._policy_version == ver) else None
         slot_o, len_o, carry_o = C.c_int64(0), C.c_int64(0), C.c_int(0)
         tk = _lib.t_start("collect")
         if random:
@@ -238,6 +241,7 @@ class Collector:
         st = buf._store
         size = buf._size
         slot = buf._lockstep_ins
+        buf._policy_version = None  # (only the fused multi-step loop vouches for the stored policy outputs)
         nxt = (slot + 1) % size
         obs_slot = st["obs"][slot]
         # the observation to act on: already in the slot if the previous fused step put it there

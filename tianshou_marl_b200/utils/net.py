@@ -54,6 +54,7 @@ class ActorCriticNet(nn.Module):
         # write to `flat` (tracked through its version counter) triggers tsm_net_pack before the next kernel call
         self.tc_image = torch.zeros(_lib.TC_IMAGE_BYTES, dtype=torch.uint8, device=self.device) if engine == "tc" else None
         self._packed_version = -1
+        self.kernel_updates = 0  # optimizer steps taken by kernels (they do not bump flat._version): see param_version
         H, I, O = self.hidden, self.in_dim, self.out_dim
         sizes = [("W1", (H, I)), ("b1", (H,)), ("W2", (H, H)), ("b2", (H,)), ("W3", (O, H)), ("b3", (O,))]
         self._views: dict[str, tuple[int, tuple[int, ...]]] = {}
@@ -93,6 +94,11 @@ class ActorCriticNet(nn.Module):
             _lib.check(_lib.lib().tsm_net_pack(C.byref(self._desc), _lib.stream_ptr()))
             self._packed_version = self.flat._version
         return C.byref(self._desc)
+
+    @property
+    def param_version(self) -> tuple[int, int]:
+        """Changes whenever the parameters do: host-side writes (torch's version counter) or kernel optimizer steps."""
+        return (int(self.flat._version), int(self.kernel_updates))
 
     def view(self, name: str) -> torch.Tensor:
         off, shp = self._views[name]
