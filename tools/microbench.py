@@ -38,6 +38,10 @@ def main():
     f = lambda x: x.view(-1)  # noqa: E731
     med, best = timeit(lambda: gae_flat(f(v_s), f(v_n), f(rew), f(term), f(trunc), None, T, 0.99, 0.95))
     out["gae_flat"] = {"ms": med, "best_ms": best, "GBps": 22 * n / med / 1e6}
+    fe = torch.zeros(n, dtype=torch.uint8, device="cuda")
+    fe[T - 1::T] = 1  # what compute_episodic_return passes: no seg_len, the unfinished slots as force_end
+    med, best = timeit(lambda: gae_flat(f(v_s), f(v_n), f(rew), f(term), f(trunc), fe, 0, 0.99, 0.95))
+    out["gae_flat_force_end"] = {"ms": med, "best_ms": best, "GBps": 23 * n / med / 1e6}
     a, b = torch.empty(1 << 29, device="cuda", dtype=torch.float32), torch.empty(1 << 29, device="cuda", dtype=torch.float32)
     med, best = timeit(lambda: b.copy_(a))
     out["copy_4GiB"] = {"ms": med, "GBps": 2 * a.numel() * 4 / med / 1e6}
