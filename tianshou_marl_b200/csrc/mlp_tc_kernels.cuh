@@ -741,7 +741,7 @@ struct TcEpochArgs {
     float* grads1;         // gradient buffers 1 and 2 (minibatch m reduces into buffer m % 3; all zero on entry and on exit)
     float* grads2;
     uint2* q_table;        // [EP_THREADS][EP_OPT + 1] scratch (see the kernel)
-    float* g_total;        // [EP_G_STRIDE] sum over ranks (world > 2 only)
+    float* g_total;        // [EP_G_STRIDE] sum over ranks (world > 1 only)
     uint32_t* sync_words;  // [0], [1] arrival counters of the in-kernel grid barriers (zero between launches)
     int64_t n_mb, mb_size, total;  // minibatch m = [m * mb_size, (m + 1) * mb_size), the last one runs to `total`
     const float* mb_stats;         // [n_mb][2] or NULL
@@ -1120,10 +1120,11 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
         TRACE(erow, 43);
         const float* r_base = ad.world > 1 ? ad.peer_recv[ad.rank] + (int64_t)(seq & 1u) * ad.world * ad.n_stride : nullptr;
         const float* g_src = g_cur;  // where the (summed) gradient is read from below
-        if (ad.world > 2) {
-            // More than two ranks: every CTA reading all `world` slots would move world x 28 KB x grid through L2 per step.
-            // Slice owners sum the slots of their slice (rank order) into g_total, one more grid barrier, and everybody
-            // reads the total once.
+        if (ad.world > 1) {
+            // Slice owners sum the `world` slots of their slice (rank order) into g_total, one more grid barrier, and
+            // everybody reads the total once.  Every CTA summing all slots itself would move world x 28 KB x grid per step,
+            // and reads of the peer-written receive area are slow (they miss L2: +3 us per step at two ranks when all 148
+            // CTAs read the whole slot, +1 us for one slice each); the extra barrier costs ~1.3 us.
             const int64_t n4s = ad.n_stride / 4, per4 = (n4s + gridDim.x - 1) / gridDim.x;
             const int64_t lo4 = (int64_t)blockIdx.x * per4, hi4 = lo4 + per4 < n4s ? lo4 + per4 : n4s;
             for (int64_t j = lo4 + rc; j < hi4; j += EP_THREADS) {
@@ -1158,7 +1159,6 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
             }
             __syncthreads();
             g_src = e.g_total;
-            r_base = nullptr;
         }
         TRACE(erow, 48);
         float4 G[EP_OPT];  // all loads first (one L2 round trip)
@@ -1172,20 +1172,6 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
                 } else {  // (buffer 0 is the net's own gradient array: exactly n floats)
                     auto get = [&](int k) { return i + k < n ? __ldcg(g_src + i + k) : 0.f; };
                     G[u] = make_float4(get(0), get(1), get(2), get(3));
-                }
-            }
-            if (r_base) {  // sum over ranks in rank order (own contribution from the local buffer): the same order on every rank
-#pragma unroll
-                for (int u = 0; u < EP_OPT; ++u) {
-                    const int i = 4 * (rc + u * EP_THREADS);
-                    if (i < ad.n_stride) {
-                        float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
-                        for (int q = 0; q < ad.world; ++q) {
-                            const float4 y = q == ad.rank ? G[u] : __ldcg(reinterpret_cast<const float4*>(r_base + (int64_t)q * ad.n_stride) + rc + u * EP_THREADS);
-                            sum.x += y.x; sum.y += y.y; sum.z += y.z; sum.w += y.w;
-                        }
-                        G[u] = sum;
-                    }
                 }
             }
             float sq = 0.f;
