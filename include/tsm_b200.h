@@ -286,6 +286,12 @@ int tsm_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int
                     uint64_t seed, uint64_t counter, float* out, int32_t* act, float* logp, float* value,
                     float* entropy, tsm_stream_t stream);
 
+/* tsm_net_forward (mode 1 sample / 2 argmax) over rows [row0, row0 + n) of a larger batch: x, act, logp, value are the
+ * FULL arrays; the sampling key uses the global row index, so splitting a batch into ranges (e.g. to run them on
+ * different streams) draws exactly the actions of one launch over the whole batch. */
+int tsm_net_forward_range(const tsm_net* net, const float* x, int64_t row0, int64_t n, int mode, uint64_t seed, uint64_t counter,
+                          int32_t* act, float* logp, float* value, tsm_stream_t stream);
+
 /* The update batch, addressed in place inside the time-major device buffer ([size][n_rows]
  * arrays, obs [size][n_rows][in_dim]).  Batch position p (0 <= p < B, the order of
  * buffer.sample(0), manager.py:212-229) maps to a storage slot either through an explicit list
@@ -440,13 +446,14 @@ typedef struct tsm_rollout {
 /* One vector step of a lock-step rollout in ONE launch: tsm_mpe_step with auto-reset, then for every row the ring
  * counters of tsm_buf_add (buffer_ids = arange, act / rew / flags written to the row's current slot of buf's time-major
  * payload, ep_ret_out / ep_len_out as tsm_buf_add's outputs) and tsm_episode_stats (acc, optional episode list).
- * Needs one sub-buffer per row (buf->n_bufs == n_envs * n_agents).
+ * Needs one sub-buffer per row (buf->n_bufs == n_envs * n_agents).  The launch covers environments [env_begin, env_begin +
+ * env_count); every array stays indexed by the global row, so disjoint ranges may run concurrently on different streams.
  * replaces  BaseVectorEnv.step + ReplayBufferManager.add + the done-env loop of Collector._collect
  *           (venvs.py:237-322, manager.py:131-193, collector.py:983-1024) */
 int tsm_rollout_step(const tsm_mpe* env, const tsm_buf* buf, const int32_t* act, float* obs_next, float* rew,
                      uint8_t* terminated, uint8_t* truncated, float* obs_carry, double* ep_ret_out, int64_t* ep_len_out,
                      double* acc, double* list_ret, int64_t* list_len, int64_t* list_count, int64_t list_capacity,
-                     tsm_stream_t stream);
+                     int64_t env_begin, int64_t env_count /* <= 0: all environments */, tsm_stream_t stream);
 
 int tsm_collect_lockstep(const tsm_net* net, const tsm_mpe* env, const tsm_buf* buf, const tsm_rollout* ro, int64_t n_steps,
                          int mode, uint64_t seed, uint64_t counter0, int64_t lockstep_len, int n_random_act,

@@ -102,3 +102,22 @@ def test_collect_then_update_learns():
         c.reset_buffer(keep_statistics=True)
     assert np.isfinite(rets).all()
     assert np.mean(rets[-3:]) > np.mean(rets[:3]), rets
+
+
+@pytest.mark.gpu
+def test_parallel_stream_rollout_equals_single_stream():
+    """tsm_collect_lockstep splits the environments into ranges that run on their own streams (TSM_COLLECT_STREAMS,
+    read once per process): the rollout -- actions included, the sampling key is the global row -- must not depend on it."""
+    import os
+    import subprocess
+    import sys
+
+    here = os.path.dirname(os.path.abspath(__file__))
+    lines = []
+    for parts in ("1", "2", "3"):
+        out = subprocess.run([sys.executable, os.path.join(here, "_split_rollout.py")], capture_output=True, text=True, timeout=300,
+                             env={**os.environ, "TSM_COLLECT_STREAMS": parts})
+        chk = [l for l in out.stdout.splitlines() if l.startswith("CHK")]
+        assert out.returncode == 0 and chk, out.stdout[-2000:] + out.stderr[-2000:]
+        lines.append(chk[0])
+    assert lines[0] == lines[1] == lines[2], lines

@@ -129,7 +129,8 @@ _SIGS = {
     "tsm_adam_step": (c_i32, [c_vp, c_f32, c_f32, c_f32, c_f32, c_f32, c_f32, c_vp, c_vp]),
     "tsm_ppo_epoch": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_f32, c_f32, c_f32, c_f32, c_f32, c_vp, c_vp]),
     "tsm_episode_stats": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_i64, c_vp]),
-    "tsm_rollout_step": (c_i32, [c_vp] * 14 + [c_i64, c_vp]),
+    "tsm_rollout_step": (c_i32, [c_vp] * 14 + [c_i64, c_i64, c_i64, c_vp]),
+    "tsm_net_forward_range": (c_i32, [c_vp, c_vp, c_i64, c_i64, c_i32, C.c_uint64, C.c_uint64, c_vp, c_vp, c_vp, c_vp]),
     "tsm_tc_selftest": (c_i32, [c_vp, c_i32, c_vp, c_i32, c_vp, c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp]),
     "tsm_buf_gather": (c_i32, [c_vp, c_vp, c_i64] + [c_vp] * 9 + [c_vp, c_vp, c_i32, c_vp]),
 }

@@ -39,7 +39,8 @@ class Workload:
         self.dtype = "f16 operands / f32 accumulate (tcgen05)" if args.engine == "tc" else "f32"
         B = self.R * self.T
         self.n_mb = len(PPO.split_bounds(B, args.batch_size)) - 1
-        self.launches_per_step = self.T * (K_POLICY + K_ROLLOUT_STEP) + 1  # + buffer reset
+        parts = 2 if self.E >= 8192 else 1  # tsm_collect_lockstep: environment ranges on their own streams (TSM_COLLECT_STREAMS)
+        self.launches_per_step = self.T * parts * (K_POLICY + K_ROLLOUT_STEP) + 1  # + buffer reset
         if self.update:
             # critic x2, logp_old, gae; per epoch: adv stats + either ONE persistent epoch kernel (tc engine, uniform
             # minibatches) or a (minibatch, optimizer) launch pair per minibatch (fp32 engine)

@@ -8,6 +8,8 @@
 //     the same launch (tsm_rollout_step)
 // The host loop costs ~3 us per launch instead of ~20 us of interpreter time, which is what bounds a rollout of
 // 2 small kernels per step.
+#include <algorithm>
+#include <cstdlib>
 #include "common.cuh"
 
 using namespace tsm;
@@ -26,33 +28,71 @@ extern "C" int tsm_collect_lockstep(const tsm_net* net, const tsm_mpe* env, cons
     int64_t slot = ro->slot, len = lockstep_len;
     bool in_carry = false;  // the observation to act on sits in ro->carry instead of obs[slot]
     cudaStream_t s = as_stream(stream);
+    // Environments never interact, so the rollout of one half of them is independent of the other half's for ALL steps:
+    // with a policy net the environments are split into `parts` ranges, each range runs its own forward -> step chain on
+    // its own stream (forked from / joined into the caller's stream), and the GPU overlaps one range's latency-bound
+    // tensor-core forward with the other's CUDA-core world step.  Sampling keys use the global row index
+    // (tsm_net_forward_range), so the actions are those of the unsplit loop.
+    static const int want_parts = getenv("TSM_COLLECT_STREAMS") ? atoi(getenv("TSM_COLLECT_STREAMS")) : 2;
+    constexpr int MAX_PARTS = 4;
+    const int64_t E = env->n_envs, A = env->n_agents;
+    int parts = (net && E >= 8192) ? std::min(std::max(want_parts, 1), MAX_PARTS) : 1;
+    static cudaStream_t part_stream[MAX_PARTS] = {};
+    static cudaEvent_t fork_ev = nullptr, join_ev[MAX_PARTS] = {};
+    static int ev_device = -1;
+    if (parts > 1) {
+        int dev = 0;
+        TSM_CUDA(cudaGetDevice(&dev));
+        if (ev_device != dev) {  // (one device per process)
+            for (int p = 0; p < MAX_PARTS; ++p) {
+                TSM_CUDA(cudaStreamCreateWithFlags(&part_stream[p], cudaStreamNonBlocking));
+                TSM_CUDA(cudaEventCreateWithFlags(&join_ev[p], cudaEventDisableTiming));
+            }
+            TSM_CUDA(cudaEventCreateWithFlags(&fork_ev, cudaEventDisableTiming));
+            ev_device = dev;
+        }
+        TSM_CUDA(cudaEventRecord(fork_ev, s));
+        for (int p = 0; p < parts; ++p) TSM_CUDA(cudaStreamWaitEvent(part_stream[p], fork_ev, 0));
+    }
     for (int64_t k = 0; k < n_steps; ++k) {
         float* obs_slot = ro->obs + slot * R * O;
         int32_t* act_slot = ro->act + slot * R;
-        if (in_carry) TSM_CUDA(cudaMemcpyAsync(obs_slot, ro->carry, sizeof(float) * R * O, cudaMemcpyDeviceToDevice, s));
-        int rc;
-        if (net) {
-            rc = tsm_net_forward(net, obs_slot, nullptr, R, mode, 0, seed, counter0 + (uint64_t)k, nullptr, act_slot,
-                                 ro->logp ? ro->logp + slot * R : nullptr,
-                                 (ro->value && net->value_index >= 0) ? ro->value + slot * R : nullptr, nullptr, stream);
-        } else {
-            rc = tsm_random_actions(act_slot, R, n_random_act, seed, counter0 + (uint64_t)k, stream);
-            if (!rc && ro->logp) TSM_CUDA(cudaMemsetAsync(ro->logp + slot * R, 0, sizeof(float) * R, s));
-            if (!rc && ro->value) TSM_CUDA(cudaMemsetAsync(ro->value + slot * R, 0, sizeof(float) * R, s));
-        }
-        if (rc) return rc;
         // the next observation goes straight into the next slot unless this is the last step or the ring would wrap onto live data
         const int64_t nxt = (slot + 1) % size;
         const bool to_carry = (k == n_steps - 1) || (len + 1 >= size);
         float* carry = to_carry ? ro->carry : ro->obs + nxt * R * O;
-        // world step + ring counters + episode statistics: one launch
-        rc = tsm_rollout_step(env, buf, act_slot, ro->obs_next + slot * R * O, ro->rew + slot * R, ro->terminated + slot * R,
-                              ro->truncated + slot * R, carry, ro->ep_ret, ro->ep_len, ro->acc, ro->list_ret, ro->list_len, ro->list_count,
-                              ro->list_cap, stream);
-        if (rc) return rc;
+        for (int p = 0; p < parts; ++p) {
+            const int64_t e0 = E * p / parts, e1 = E * (p + 1) / parts, r0 = e0 * A, nr = (e1 - e0) * A;
+            cudaStream_t ps = parts > 1 ? part_stream[p] : s;
+            tsm_stream_t pst = parts > 1 ? reinterpret_cast<tsm_stream_t>(ps) : stream;
+            if (in_carry)
+                TSM_CUDA(cudaMemcpyAsync(obs_slot + r0 * O, ro->carry + r0 * O, sizeof(float) * nr * O, cudaMemcpyDeviceToDevice, ps));
+            int rc;
+            if (net) {
+                rc = tsm_net_forward_range(net, obs_slot, r0, nr, mode, seed, counter0 + (uint64_t)k, act_slot,
+                                           ro->logp ? ro->logp + slot * R : nullptr,
+                                           (ro->value && net->value_index >= 0) ? ro->value + slot * R : nullptr, pst);
+            } else {
+                rc = tsm_random_actions(act_slot, R, n_random_act, seed, counter0 + (uint64_t)k, stream);
+                if (!rc && ro->logp) TSM_CUDA(cudaMemsetAsync(ro->logp + slot * R, 0, sizeof(float) * R, s));
+                if (!rc && ro->value) TSM_CUDA(cudaMemsetAsync(ro->value + slot * R, 0, sizeof(float) * R, s));
+            }
+            if (rc) return rc;
+            // world step + ring counters + episode statistics: one launch
+            rc = tsm_rollout_step(env, buf, act_slot, ro->obs_next + slot * R * O, ro->rew + slot * R, ro->terminated + slot * R,
+                                  ro->truncated + slot * R, carry, ro->ep_ret, ro->ep_len, ro->acc, ro->list_ret, ro->list_len,
+                                  ro->list_count, ro->list_cap, e0, e1 - e0, pst);
+            if (rc) return rc;
+        }
         len = len + 1 < size ? len + 1 : size;
         slot = nxt;
         in_carry = to_carry;
+    }
+    if (parts > 1) {
+        for (int p = 0; p < parts; ++p) {
+            TSM_CUDA(cudaEventRecord(join_ev[p], part_stream[p]));
+            TSM_CUDA(cudaStreamWaitEvent(s, join_ev[p], 0));
+        }
     }
     if (slot_out) *slot_out = slot;
     if (lockstep_len_out) *lockstep_len_out = len;

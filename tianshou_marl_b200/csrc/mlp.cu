@@ -253,6 +253,7 @@ struct FwdArgs {
     int64_t n;
     int in_dim, out_dim, n_act, value_index, mode, scatter;
     uint64_t seed, counter;
+    int64_t rng_row0;        // added to the row index in the sampling key
     float* out;              // mode 0: [n][out_dim]
     int32_t* act;            // modes 1,2: written; mode 3: read
     float* logp;             // [n]
@@ -301,7 +302,8 @@ __global__ void __launch_bounds__(THREADS) forward_kernel(FwdArgs a) {
                 const Soft s = softmax_row(z, a.n_act);
                 int act = 0;
                 if (a.mode == 1) {
-                    const Philox4 rnd = philox4x32((uint32_t)dst, (uint32_t)((uint64_t)dst >> 32), (uint32_t)a.counter,
+                    const int64_t key = dst + a.rng_row0;
+                    const Philox4 rnd = philox4x32((uint32_t)key, (uint32_t)((uint64_t)key >> 32), (uint32_t)a.counter,
                                                    (uint32_t)(a.counter >> 32), (uint32_t)a.seed, (uint32_t)(a.seed >> 32) ^ STREAM_ACT);
                     const float u = u01(rnd.x);
                     float c = 0.f;
@@ -624,7 +626,7 @@ __global__ void __launch_bounds__(ADAM_THREADS) pack_image_kernel(const float* _
 
 namespace tsm {
 int tc_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int64_t n, int mode, int scatter, uint64_t seed,
-                   uint64_t counter, float* out, int32_t* act, float* logp, float* value, float* entropy, cudaStream_t s);
+                   uint64_t counter, float* out, int32_t* act, float* logp, float* value, float* entropy, int64_t rng_row0, cudaStream_t s);
 int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, int64_t mb_start, int64_t mb_len,
                      const float* mb_stats, double* loss_sums, int pdl, cudaStream_t s);
 int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, int64_t start, int64_t mb_size,
@@ -669,9 +671,9 @@ static int prep_kernel(K kernel, size_t smem, int* ctas_per_sm) {
 
 extern "C" int64_t tsm_net_param_count(int in_dim, int hidden, int out_dim) { return offsets(in_dim, hidden, out_dim).total; }
 
-extern "C" int tsm_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int64_t n, int mode, int scatter,
-                               uint64_t seed, uint64_t counter, float* out, int32_t* act, float* logp, float* value,
-                               float* entropy, tsm_stream_t stream) {
+static int net_forward_impl(const tsm_net* net, const float* x, const int64_t* rows, int64_t n, int mode, int scatter,
+                            uint64_t seed, uint64_t counter, float* out, int32_t* act, float* logp, float* value,
+                            float* entropy, int64_t rng_row0, tsm_stream_t stream) {
     int rc = check_net(net, __func__);
     if (rc) return rc;
     TSM_REQUIRE(n >= 0 && mode >= 0 && mode <= 3, "n >= 0, 0 <= mode <= 3");
@@ -680,11 +682,11 @@ extern "C" int tsm_net_forward(const tsm_net* net, const float* x, const int64_t
     TSM_REQUIRE(mode == 0 || net->n_act > 0, "sampling / evaluation needs n_act > 0");
     TSM_REQUIRE(mode != 3 || act != nullptr, "mode 3 (evaluate) needs act");
     if (net->engine == 1)
-        return tc_net_forward(net, x, rows, n, mode, scatter, seed, counter, out, act, logp, value, entropy, as_stream(stream));
+        return tc_net_forward(net, x, rows, n, mode, scatter, seed, counter, out, act, logp, value, entropy, rng_row0, as_stream(stream));
     FwdArgs a{};
     a.params = net->params; a.x = x; a.rows = rows; a.n = n;
     a.in_dim = net->in_dim; a.out_dim = net->out_dim; a.n_act = net->n_act; a.value_index = net->value_index;
-    a.mode = mode; a.scatter = scatter; a.seed = seed; a.counter = counter;
+    a.mode = mode; a.scatter = scatter; a.seed = seed; a.counter = counter; a.rng_row0 = rng_row0;
     a.out = out; a.act = act; a.logp = logp; a.value = value; a.entropy = entropy;
     cudaStream_t s = as_stream(stream);
     int occ = 1;
@@ -705,6 +707,20 @@ extern "C" int tsm_net_forward(const tsm_net* net, const float* x, const int64_t
     }
     TSM_LAUNCH_CHECK();
     return TSM_OK;
+}
+
+extern "C" int tsm_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int64_t n, int mode, int scatter,
+                               uint64_t seed, uint64_t counter, float* out, int32_t* act, float* logp, float* value,
+                               float* entropy, tsm_stream_t stream) {
+    return net_forward_impl(net, x, rows, n, mode, scatter, seed, counter, out, act, logp, value, entropy, 0, stream);
+}
+
+extern "C" int tsm_net_forward_range(const tsm_net* net, const float* x, int64_t row0, int64_t n, int mode, uint64_t seed,
+                                     uint64_t counter, int32_t* act, float* logp, float* value, tsm_stream_t stream) {
+    TSM_REQUIRE(net != nullptr && row0 >= 0, "net != NULL, row0 >= 0");
+    TSM_REQUIRE(mode == 1 || mode == 2, "mode: 1 sample, 2 argmax");
+    return net_forward_impl(net, x ? x + row0 * net->in_dim : nullptr, nullptr, n, mode, 0, seed, counter, nullptr, act ? act + row0 : nullptr,
+                            logp ? logp + row0 : nullptr, value ? value + row0 : nullptr, nullptr, row0, stream);
 }
 
 static BatchView make_view(const tsm_ppo_batch* b) {

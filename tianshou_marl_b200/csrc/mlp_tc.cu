@@ -164,13 +164,13 @@ static int tc_check_net(const tsm_net* n, const char* fn) {
 }
 
 int tc_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int64_t n, int mode, int scatter, uint64_t seed,
-                   uint64_t counter, float* out, int32_t* act, float* logp, float* value, float* entropy, cudaStream_t s) {
+                   uint64_t counter, float* out, int32_t* act, float* logp, float* value, float* entropy, int64_t rng_row0, cudaStream_t s) {
     int rc = tc_check_net(net, __func__);
     if (rc) return rc;
     mlptc::TcFwdArgs a{};
     a.image = reinterpret_cast<const unsigned char*>(net->tc_image); a.x = x; a.rows = rows; a.n = n;
     a.in_dim = net->in_dim; a.out_dim = net->out_dim; a.n_act = net->n_act; a.value_index = net->value_index;
-    a.mode = mode; a.scatter = scatter; a.seed = seed; a.counter = counter;
+    a.mode = mode; a.scatter = scatter; a.seed = seed; a.counter = counter; a.rng_row0 = rng_row0;
     a.out = out; a.act = act; a.logp = logp; a.value = value; a.entropy = entropy;
     const size_t smem = mlptc::SM_FWD_TOTAL + 128;  // ~69 KB: three CTAs per SM (3 x 128 TMEM columns)
     static bool attr = false;

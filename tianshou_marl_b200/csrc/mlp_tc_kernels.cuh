@@ -195,6 +195,7 @@ struct TcFwdArgs {
     int64_t n;
     int in_dim, out_dim, n_act, value_index, mode, scatter;
     uint64_t seed, counter;
+    int64_t rng_row0;  // added to the row index in the sampling key (a launch over rows [row0, row0 + n) of a larger batch)
     float* out;
     int32_t* act;
     float* logp;
@@ -375,7 +376,8 @@ __global__ void __launch_bounds__(TC_THREADS) tc_forward_kernel(TcFwdArgs a) {
                 const Soft sm = softmax_row<true>(z, a.n_act);
                 int act = 0;
                 if (a.mode == 1) {
-                    const Philox4 rnd = philox4x32((uint32_t)dst, (uint32_t)((uint64_t)dst >> 32), (uint32_t)a.counter,
+                    const int64_t key = dst + a.rng_row0;
+                    const Philox4 rnd = philox4x32((uint32_t)key, (uint32_t)((uint64_t)key >> 32), (uint32_t)a.counter,
                                                    (uint32_t)(a.counter >> 32), (uint32_t)a.seed, (uint32_t)(a.seed >> 32) ^ STREAM_ACT);
                     const float u = u01(rnd.x);
                     float c = 0.f;

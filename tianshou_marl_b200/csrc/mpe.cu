@@ -182,11 +182,13 @@ template <int G, bool TAIL>
 __global__ void __launch_bounds__(THREADS) step_kernel(tsm_mpe e, const int32_t* __restrict__ act,
                                                       float* __restrict__ obs_next, float* __restrict__ rew,
                                                       uint8_t* __restrict__ term, uint8_t* __restrict__ trunc, int autoreset,
-                                                      float* __restrict__ obs_carry, RolloutTail t) {
-    const int64_t env = ((int64_t)blockIdx.x * THREADS + threadIdx.x) / G;
+                                                      float* __restrict__ obs_carry, RolloutTail t, int64_t env0, int64_t n_sub) {
+    // the launch covers environments [env0, env0 + n_sub) (all arrays stay indexed by the global env / row)
+    const int64_t local = ((int64_t)blockIdx.x * THREADS + threadIdx.x) / G;
+    const int64_t env = env0 + local;
     const int j = threadIdx.x % G;
     const int A = e.n_agents, L = e.n_landmarks;
-    const bool live = env < e.n_envs;
+    const bool live = local < n_sub;
     const bool is_agent = live && j < A;
     const int64_t row = env * A + j;
 
@@ -438,14 +440,14 @@ extern "C" int tsm_mpe_reset(const tsm_mpe* e, const int64_t* env_ids, int64_t n
 
 template <bool TAIL>
 static int launch_step(const tsm_mpe* e, const int32_t* act, float* obs_next, float* rew, uint8_t* terminated, uint8_t* truncated,
-                       int autoreset, float* obs_carry, const RolloutTail& t, cudaStream_t s) {
+                       int autoreset, float* obs_carry, const RolloutTail& t, int64_t env0, int64_t n_sub, cudaStream_t s) {
     const int G = group_width(e);
-    const unsigned grid = (unsigned)ceil_div(e->n_envs * G, THREADS);
+    const unsigned grid = (unsigned)ceil_div(n_sub * G, THREADS);
     switch (G) {
-        case 4: step_kernel<4, TAIL><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t); break;
-        case 8: step_kernel<8, TAIL><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t); break;
-        case 16: step_kernel<16, TAIL><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t); break;
-        default: step_kernel<32, TAIL><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t); break;
+        case 4: step_kernel<4, TAIL><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t, env0, n_sub); break;
+        case 8: step_kernel<8, TAIL><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t, env0, n_sub); break;
+        case 16: step_kernel<16, TAIL><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t, env0, n_sub); break;
+        default: step_kernel<32, TAIL><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t, env0, n_sub); break;
     }
     TSM_LAUNCH_CHECK();
     return TSM_OK;
@@ -456,13 +458,13 @@ extern "C" int tsm_mpe_step(const tsm_mpe* e, const int32_t* act, float* obs_nex
     int rc = check_env(e, __func__);
     if (rc) return rc;
     TSM_REQUIRE(act && rew && terminated && truncated, "act/rew/terminated/truncated != NULL");
-    return launch_step<false>(e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, RolloutTail{}, as_stream(stream));
+    return launch_step<false>(e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, RolloutTail{}, 0, e->n_envs, as_stream(stream));
 }
 
 extern "C" int tsm_rollout_step(const tsm_mpe* e, const tsm_buf* buf, const int32_t* act, float* obs_next, float* rew,
                                 uint8_t* terminated, uint8_t* truncated, float* obs_carry, double* ep_ret_out, int64_t* ep_len_out,
                                 double* acc, double* list_ret, int64_t* list_len, int64_t* list_count, int64_t list_capacity,
-                                tsm_stream_t stream) {
+                                int64_t env_begin, int64_t env_count, tsm_stream_t stream) {
     int rc = check_env(e, __func__);
     if (rc) return rc;
     TSM_REQUIRE(buf && act && rew && terminated && truncated && acc, "buf / act / rew / terminated / truncated / acc != NULL");
@@ -471,5 +473,7 @@ extern "C" int tsm_rollout_step(const tsm_mpe* e, const tsm_buf* buf, const int3
     TSM_REQUIRE(buf->act && buf->rew && buf->terminated && buf->truncated && buf->done, "payload arrays != NULL");
     TSM_REQUIRE(!list_count || (list_ret && list_len && list_capacity >= 0), "episode list arrays");
     RolloutTail t{*buf, ep_ret_out, ep_len_out, acc, list_ret, list_len, list_count, list_capacity};
-    return launch_step<true>(e, act, obs_next, rew, terminated, truncated, 1, obs_carry, t, as_stream(stream));
+    if (env_count <= 0) { env_begin = 0; env_count = e->n_envs; }  // the whole vector env
+    TSM_REQUIRE(env_begin >= 0 && env_begin + env_count <= e->n_envs, "0 <= env_begin, env_begin + env_count <= n_envs");
+    return launch_step<true>(e, act, obs_next, rew, terminated, truncated, 1, obs_carry, t, env_begin, env_count, as_stream(stream));
 }
