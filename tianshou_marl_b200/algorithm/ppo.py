@@ -224,8 +224,11 @@ class PPO:
                 net.forward(st["obs_next"].view(size * R, O), mode="raw", out={"value": v_n.view(-1)}, rows=need[:n_need], scatter=True)
             _lib.t_stop(tk)
         else:
-            tk = _lib.t_start("critic_forward")
-            net.forward(obs_all, mode="raw", out={"value": v_s.view(-1)}, rows=slots, scatter=slots is not None)
+            # critic(obs) (a2c.py:120-123) and logp_old = log pi(act | obs) (ppo.py:157-161) read the same rows through the
+            # same trunk: ONE evaluation pass yields both (the reference runs the network twice)
+            tk = _lib.t_start("logp_old_forward")
+            net.forward(obs_all, mode="eval", act=st["act"].view(-1), out={"logp": logp.view(-1), "value": v_s.view(-1)},
+                        rows=slots, scatter=slots is not None)
             _lib.t_stop(tk)
             tk = _lib.t_start("critic_forward")
             net.forward(st["obs_next"].view(size * R, O), mode="raw", out={"value": v_n.view(-1)}, rows=slots, scatter=slots is not None)
@@ -261,11 +264,6 @@ class PPO:
             start, lock_len = 0, size
         _lib.t_stop(tk)
         # ---- logp_old (ppo.py:157-161) ----
-        if not reuse:
-            tk = _lib.t_start("logp_old_forward")
-            net.forward(obs_all, mode="eval", act=st["act"].view(-1), out={"logp": logp.view(-1), "value": self._buf("scratch_v", (size * R,))},
-                        rows=slots, scatter=slots is not None)
-            _lib.t_stop(tk)
         # ---- minibatch loop (ppo.py:173-216) ----
         bounds = self.split_bounds(B, batch_size)
         n_mb = len(bounds) - 1
