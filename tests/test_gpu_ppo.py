@@ -235,3 +235,32 @@ def test_reuse_rollout_policy_outputs(engine):
     for k in ("v_s", "v_n", "logp", "adv", "ret"):
         assert torch.equal(res[0][k], res[1][k]), k
     assert torch.allclose(res[0]["p"], res[1]["p"], atol=2e-5 if engine == "fp32" else 2e-3)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("engine", ["fp32", "tc"])
+def test_dedup_next_values_is_bit_identical(engine):
+    """PPO(dedup_next_values=True, the default) evaluates critic(obs_next) only where an episode ended and takes v_s[t + 1]
+    elsewhere; the full second critic pass of a2c.py:120-127 must give the same bits (values, advantages, returns)."""
+    from tianshou_marl_b200.algorithm import PPO, AdamOptimizerFactory, DiscreteActorPolicy
+    from tianshou_marl_b200.data import Collector, VectorReplayBuffer
+    from tianshou_marl_b200.env import MPEVectorEnv
+    from tianshou_marl_b200.utils import ActorCriticNet
+
+    E, A, T = 96, 3, 60
+    res = []
+    for dedup in (False, True):
+        env = MPEVectorEnv("simple_spread_v3", n_envs=E, n_agents=A, seed=5)
+        buf = VectorReplayBuffer(T * E * A, E * A, index_type="torch")
+        net = ActorCriticNet(env.obs_dim, 64, 5, seed=3, engine=engine)
+        pol = DiscreteActorPolicy(actor=net, seed=11)
+        alg = PPO(policy=pol, critic=net, optim=AdamOptimizerFactory(lr=1e-3), minibatch_order="device", seed=2, dedup_next_values=dedup)
+        col = Collector(alg, env, buf)
+        col.reset()
+        pol.is_within_training_step = True
+        col.collect(n_step=T * E * A)
+        assert buf._obs_chain is True
+        alg.update(buf, 2048, 1)
+        res.append({k: alg._work[k].clone() for k in ("v_s", "v_n", "adv", "ret")})
+    for k in res[0]:
+        assert torch.equal(res[0][k], res[1][k]), k

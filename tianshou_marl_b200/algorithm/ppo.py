@@ -97,7 +97,7 @@ class PPO:
                  value_clip: bool = False, advantage_normalization: bool = True, recompute_advantage: bool = False,
                  vf_coef: float = 0.5, ent_coef: float = 0.01, max_grad_norm: float | None = None, gae_lambda: float = 0.95,
                  max_batchsize: int = 256, gamma: float = 0.99, return_scaling: bool = False,
-                 minibatch_order: str = "device", reuse_rollout_policy_outputs: bool = False, seed: int = 0,
+                 minibatch_order: str = "device", reuse_rollout_policy_outputs: bool = False, dedup_next_values: bool = True, seed: int = 0,
                  grad_sync: str = "auto") -> None:
         assert dual_clip is None or dual_clip > 1.0, f"Dual-clip PPO parameter should greater than 1.0 but got {dual_clip}"  # ppo.py
         assert 0.0 <= gamma <= 1.0 and 0.0 <= gae_lambda <= 1.0
@@ -122,6 +122,7 @@ class PPO:
         self.grad_sync = grad_sync  # world > 1: "peer" = exchange fused into the optimizer kernel, "nccl" = all_reduce per minibatch
         self._peers = None
         self.reuse_rollout = reuse_rollout_policy_outputs
+        self.dedup_next_values = dedup_next_values  # critic(obs_next[t]) = critic(obs[t + 1]) where the rollout kernel vouches for obs_next[t] == obs[t + 1]
         self._eps = 1e-8
         self._epoch_counter = 0
         self._seed = seed
@@ -231,7 +232,18 @@ class PPO:
                         rows=slots, scatter=slots is not None)
             _lib.t_stop(tk)
             tk = _lib.t_start("critic_forward")
-            net.forward(st["obs_next"].view(size * R, O), mode="raw", out={"value": v_n.view(-1)}, rows=slots, scatter=slots is not None)
+            if self.dedup_next_values and lockstep and rows is None and buffer._obs_chain is True:
+                # the rollout kernel wrote obs_next[t] and obs[t + 1] from the same registers wherever the episode went on:
+                # critic(obs_next[t]) IS v_s[t + 1] there; only rows that ended an episode at t, and the last slot, are evaluated
+                start0 = buffer._lockstep_ins if lock_len == size else 0
+                need = self._buf("need_list", (size * R,), torch.int64)
+                cnt = self._buf("need_count", (1,), torch.int64)
+                _lib.check(L.tsm_values_next_prepare(P(v_s), P(st["done"]), size, R, start0, lock_len, P(v_n), P(need), P(cnt), S))
+                n_need = int(cnt.item())
+                if n_need > 0:
+                    net.forward(st["obs_next"].view(size * R, O), mode="raw", out={"value": v_n.view(-1)}, rows=need[:n_need], scatter=True)
+            else:
+                net.forward(st["obs_next"].view(size * R, O), mode="raw", out={"value": v_n.view(-1)}, rows=slots, scatter=slots is not None)
             _lib.t_stop(tk)
         tk = _lib.t_start("gae")
         if lockstep:

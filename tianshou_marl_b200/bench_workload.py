@@ -45,7 +45,8 @@ class Workload:
             # critic x2, logp_old, gae; per epoch: adv stats + either ONE persistent epoch kernel (tc engine, uniform
             # minibatches) or a (minibatch, optimizer) launch pair per minibatch (fp32 engine)
             per_epoch = 2 if args.engine == "tc" else 1 + 2 * self.n_mb
-            self.launches_per_step += (2 if getattr(args, "reuse_rollout", False) else 2) + 1 + args.repeat * per_epoch  # (value + logp_old pass | values_next), critic(obs_next), gae
+            # reuse_rollout: values_next + critic over ended rows; else: value + logp_old pass, values_next, critic over ended rows; + gae
+            self.launches_per_step += (2 if getattr(args, "reuse_rollout", False) else 3) + 1 + args.repeat * per_epoch
             self.launches_per_step += 1 if args.engine == "tc" else 0  # pack_records
         self.h2d_bytes = 0
         self.d2h_bytes = 0

@@ -70,6 +70,7 @@ class VectorReplayBuffer:
         self._desc = _lib.TsmBuf()
         self._lockstep_len: int | None = 0  # host-known common length while every add was a full lock-step add
         self._lockstep_ins = 0  # host-known common insertion index in lock-step use
+        self._obs_chain = None  # True while EVERY valid slot was written by the fused rollout: obs[t + 1] is obs_next[t] bit for bit unless done[t]
         self._policy_version = None  # param_version of the net whose logp / value the fused collector stored for EVERY valid slot, else None
         self._refresh_desc()
 
@@ -130,6 +131,7 @@ class VectorReplayBuffer:
         self._lockstep_len = 0
         self._lockstep_ins = 0
         self._policy_version = None
+        self._obs_chain = None
 
     def update(self, buffer: Any) -> np.ndarray:
         """manager.py:127-129."""
@@ -180,6 +182,7 @@ class VectorReplayBuffer:
             C.byref(self._desc), P(obs_t), P(act_t), P(rew_t), P(te_t), P(tr_t), P(on_t), P(logp_t), P(value_t),
             P(ids_t), n, P(idx), P(ep_ret), P(ep_len), P(ep_start), _lib.stream_ptr()))
         self._policy_version = None  # generic adds: stored logp / value (if any) are not known to cover every slot
+        self._obs_chain = False  # nor is obs[t + 1] known to repeat obs_next[t]
         if buffer_ids is None and self._lockstep_len is not None:
             self._lockstep_len = min(self._lockstep_len + 1, self._size)
             self._lockstep_ins = (self._lockstep_ins + 1) % self._size

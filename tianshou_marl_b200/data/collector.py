@@ -215,6 +215,7 @@ class Collector:
         # which parameters produced the stored logp / value (PPO's reuse_rollout_policy_outputs checks this)
         ver = None if random or st.get("value") is None or self.policy.actor.value_index < 0 else self.policy.actor.param_version
         buf._policy_version = ver if (buf._lockstep_len == 0 or buf._policy_version == ver) else None
+        buf._obs_chain = bool(buf._lockstep_len == 0 or buf._obs_chain)  # the kernel writes obs_next[t] and obs[t + 1] from the same registers
         slot_o, len_o, carry_o = C.c_int64(0), C.c_int64(0), C.c_int(0)
         tk = _lib.t_start("collect")
         if random:
@@ -242,6 +243,7 @@ class Collector:
         size = buf._size
         slot = buf._lockstep_ins
         buf._policy_version = None  # (only the fused multi-step loop vouches for the stored policy outputs)
+        buf._obs_chain = bool(buf._lockstep_len == 0 or buf._obs_chain)
         nxt = (slot + 1) % size
         obs_slot = st["obs"][slot]
         # the observation to act on: already in the slot if the previous fused step put it there
