@@ -403,6 +403,10 @@ typedef struct tsm_peers {
     float* recv[TSM_MAX_RANKS];     /* per rank: [2][world][n_stride] floats, n_stride = n_params rounded up to 4 */
     uint32_t* flags[TSM_MAX_RANKS]; /* per rank: >= TSM_MAX_RANKS uint32, zero-initialised */
     int32_t* status;                /* local device int, zero-initialised */
+    void* ll[TSM_MAX_RANKS];        /* per rank: [2][world][n_stride] 8-byte (value, step) pairs, zero-initialised: the receive area
+                                       of the persistent epoch kernel (flag-in-data: an entry is valid once its step word equals
+                                       the step waited for, so no fence or separate flag follows the peer stores).  NULL: the
+                                       epoch runs as one launch pair per minibatch */
 } tsm_peers;
 
 int tsm_adam_step_dist(const tsm_net* net, const tsm_peers* peers, uint32_t seq, float lr, float beta1, float beta2, float eps,

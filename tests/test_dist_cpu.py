@@ -105,12 +105,12 @@ def test_two_rank_update_matches_single_process(tmp_path):
 
 
 def test_peer_struct_layout():
-    """tsm_peers as bound by ctypes: 8 receive pointers, 8 flag pointers, one status pointer."""
+    """tsm_peers as bound by ctypes: 8 receive pointers, 8 flag pointers, one status pointer, 8 flag-in-data receive areas."""
     sys.path.insert(0, ROOT)
     import ctypes as C
 
     from tianshou_marl_b200 import _lib
 
     p = _lib.TsmPeers()
-    assert C.sizeof(p) == 8 + 8 * 8 + 8 * 8 + 8
-    assert _lib.TsmPeers.recv.offset == 8 and _lib.TsmPeers.flags.offset == 72 and _lib.TsmPeers.status.offset == 136
+    assert C.sizeof(p) == 8 + 8 * 8 + 8 * 8 + 8 + 8 * 8
+    assert _lib.TsmPeers.recv.offset == 8 and _lib.TsmPeers.flags.offset == 72 and _lib.TsmPeers.status.offset == 136 and _lib.TsmPeers.ll.offset == 144

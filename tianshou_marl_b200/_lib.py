@@ -60,7 +60,7 @@ class TsmNet(C.Structure):
 class TsmPeers(C.Structure):
     """struct tsm_peers (include/tsm_b200.h)."""
 
-    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("recv", c_vp * 8), ("flags", c_vp * 8), ("status", c_vp)]
+    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("recv", c_vp * 8), ("flags", c_vp * 8), ("status", c_vp), ("ll", c_vp * 8)]
 
 
 class TsmRollout(C.Structure):

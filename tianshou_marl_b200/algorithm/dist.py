@@ -58,7 +58,8 @@ class PeerGradients:
         self.n_params = int(n_params)
         self.n_stride = (self.n_params + 3) // 4 * 4
         n_pad = 2 * self.world * self.n_stride
-        self.block = symm_mem.empty(n_pad + FLAG_WORDS, dtype=torch.float32, device=device)
+        n_ll = 2 * n_pad  # the persistent epoch kernel's receive area: one (value, step) pair per element
+        self.block = symm_mem.empty(n_pad + FLAG_WORDS + n_ll, dtype=torch.float32, device=device)
         self.block.zero_()
         self.handle = symm_mem.rendezvous(self.block, group=dist.group.WORLD.group_name)
         self.status = torch.zeros(1, dtype=torch.int32, device=device)
@@ -69,6 +70,7 @@ class PeerGradients:
             base = int(self.handle.buffer_ptrs[q])
             p.recv[q] = base
             p.flags[q] = base + 4 * n_pad
+            p.ll[q] = base + 4 * (n_pad + FLAG_WORDS)
         p.status = self.status.data_ptr()
         self.desc = p
         torch.cuda.synchronize(device)

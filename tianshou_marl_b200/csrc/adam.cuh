@@ -62,6 +62,7 @@ struct AdamArgs {
     int world, rank;
     float* peer_recv[8];      // [2][world][n_stride] floats on rank q
     uint32_t* peer_flag[8];   // peer_flag[q][r]: written by rank r into rank q's flag pad
+    uint4* peer_ll[8];        // [2][world][n_stride / 2] x {v0, step, v1, step}: flag-in-data receive area (persistent epoch kernel)
     int64_t n_stride;         // n rounded up to a multiple of 4
     uint32_t seq;             // step number used as the flag value
     int* status;              // set to 1 if the cross-rank wait times out

@@ -849,6 +849,7 @@ static opt::AdamArgs adam_args_dist(const tsm_net* net, const tsm_peers* peers, 
     for (int q = 0; q < peers->world; ++q) {
         a.peer_recv[q] = peers->recv[q];
         a.peer_flag[q] = peers->flags[q];
+        a.peer_ll[q] = reinterpret_cast<uint4*>(peers->ll[q]);
     }
     return a;
 }
@@ -953,7 +954,9 @@ extern "C" int tsm_ppo_epoch_dist(const tsm_net* net, const tsm_ppo_batch* batch
     int rc = check_peers(peers, __func__);
     if (rc) return rc;
     TSM_REQUIRE(seq0 >= 1, "seq0 >= 1");
-    if (net->engine == 1 && n_minibatches >= 1 && !getenv("TSM_NO_PERSISTENT")) {
+    bool have_ll = true;
+    for (int q = 0; q < peers->world; ++q) have_ll = have_ll && peers->ll[q] != nullptr;
+    if (net->engine == 1 && n_minibatches >= 1 && have_ll && !getenv("TSM_NO_PERSISTENT")) {
         // as tsm_ppo_epoch: one persistent cooperative launch per epoch; the gradient exchange runs inside it
         const int64_t bs = h_mb_bounds[1] - h_mb_bounds[0];
         bool uniform = bs > 0;

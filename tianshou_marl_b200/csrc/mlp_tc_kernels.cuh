@@ -1059,14 +1059,14 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
         TRACE(erow, 42);
         // ---- optimizer step: the whole of it in every CTA, on the CTA's own copy of the state ----
         // ---- grid barrier with the cross-rank gradient exchange folded into it ----
-        // Arrive: one atomic per CTA on a device counter.  The LAST CTA to arrive knows the local gradient is complete; with
-        // data-parallel ranks (ad.world > 1) it PUSHES the whole gradient (<= 28 KB) into slot [seq & 1][rank] of every
-        // peer's receive area (plain NVLink peer stores), fences, and publishes step `seq` in every peer's flag pad
-        // (st.release.sys) -- one flag per peer and step, not one signal per CTA (148 remote atomics on one word cost
-        // ~10 us).  Every CTA waits until the counter shows all local arrivals and, with ranks, for every peer's flag of
-        // this step (both in local memory).  Receive areas are double buffered by step parity: a peer
-        // overwrites parity b only after its own wait of the step in between, which needs this rank's flag of that step,
-        // which its last CTA publishes only after every CTA here has finished reading parity b.
+        // Arrive: one atomic per CTA on a device counter; every CTA waits until the counter shows all local arrivals.  The
+        // LAST CTA to arrive knows the local gradient is complete; with data-parallel ranks (ad.world > 1) it PUSHES the
+        // whole gradient (<= 28 KB) into slot [seq & 1][rank] of every peer's receive area over NVLink as 16-byte stores of
+        // {value, seq, value, seq}: every 8-byte (value, step) pair is self-validating, so no fence, release or flag
+        // follows the data (a release after the stores costs a full NVLink round trip, a flag one more hop; one remote
+        // atomic per CTA, 148 per peer and step, cost ~10 us).  Receivers poll the pairs they need.  Receive areas are
+        // double buffered by step parity: a peer overwrites parity b at step seq + 2, after it has finished step seq + 1,
+        // which needed this rank's data of step seq + 1, pushed only after every CTA here was done with step seq.
         uint2 Q[EP_OPT];  // (in flight across the barrier)
 #pragma unroll
         for (int u = 0; u < EP_OPT; ++u) Q[u] = q_tab[u];
@@ -1093,24 +1093,25 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
                             auto get = [&](int k) { return i + k < n ? __ldcg(g_cur + i + k) : 0.f; };
                             v = make_float4(get(0), get(1), get(2), get(3));
                         }
+                        const uint4 lo = make_uint4(__float_as_uint(v.x), seq, __float_as_uint(v.y), seq);
+                        const uint4 hi = make_uint4(__float_as_uint(v.z), seq, __float_as_uint(v.w), seq);
                         for (int q = 0; q < ad.world; ++q)
-                            if (q != ad.rank) *reinterpret_cast<float4*>(ad.peer_recv[q] + off + i) = v;
+                            if (q != ad.rank) {
+                                uint4* dst = ad.peer_ll[q] + (off + i) / 2;
+                                asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "r"(lo.x), "r"(lo.y), "r"(lo.z), "r"(lo.w) : "memory");
+                                asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(dst + 1), "r"(hi.x), "r"(hi.y), "r"(hi.z), "r"(hi.w) : "memory");
+                            }
                     }
                 }
-                __syncthreads();
-                // one cumulative fence by the publishing thread (covers the CTA's peer stores, ordered before it by the barrier)
-                if (rc < ad.world && rc != ad.rank)
-                    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(ad.peer_flag[rc] + ad.rank), "r"(seq) : "memory");
             }
         }
-        if (rc == 0 || (ad.world > 1 && rc >= 32 && rc < 32 + ad.world && rc - 32 != ad.rank)) {
-            const uint32_t* w = rc == 0 ? e.sync_words : ad.peer_flag[ad.rank] + (rc - 32);
-            const uint32_t want = rc == 0 ? arrivals : seq;
+        if (rc == 0) {
+            const uint32_t* w = e.sync_words;
+            const uint32_t want = arrivals;
             const long long t0 = clock64();
             uint32_t v;
             do {
-                if (rc == 0) asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(w) : "memory");
-                else asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(w) : "memory");
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(w) : "memory");
                 if ((int32_t)(v - want) >= 0) break;
                 if (clock64() - t0 > 4000000000LL) {  // ~2 s: a CTA or a peer rank is missing; report instead of hanging the device
                     if (ad.status) *ad.status = 1;
@@ -1120,11 +1121,11 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
         }
         __syncthreads();
         TRACE(erow, 43);
-        const float* r_base = ad.world > 1 ? ad.peer_recv[ad.rank] + (int64_t)(seq & 1u) * ad.world * ad.n_stride : nullptr;
+        const uint4* r_base = ad.world > 1 ? ad.peer_ll[ad.rank] + (int64_t)(seq & 1u) * ad.world * ad.n_stride / 2 : nullptr;
         const float* g_src = g_cur;  // where the (summed) gradient is read from below
         if (ad.world > 1) {
-            // Slice owners sum the `world` slots of their slice (rank order) into g_total, one more grid barrier, and
-            // everybody reads the total once.  Every CTA summing all slots itself would move world x 28 KB x grid per step,
+            // Slice owners wait for the (value, step) pairs of their slice from every peer, sum the `world` contributions
+            // (rank order) into g_total, one more grid barrier, and everybody reads the total once.  Every CTA summing all slots itself would move world x 28 KB x grid per step,
             // and reads of the peer-written receive area are slow (they miss L2: +3 us per step at two ranks when all 148
             // CTAs read the whole slot, +1 us for one slice each); the extra barrier costs ~1.3 us.
             const int64_t n4s = ad.n_stride / 4, per4 = (n4s + gridDim.x - 1) / gridDim.x;
@@ -1139,7 +1140,22 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
                 }
                 float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
                 for (int q = 0; q < ad.world; ++q) {
-                    const float4 y = q == ad.rank ? own : __ldcg(reinterpret_cast<const float4*>(r_base + (int64_t)q * ad.n_stride) + j);
+                    float4 y = own;
+                    if (q != ad.rank) {
+                        const uint4* src = r_base + ((int64_t)q * ad.n_stride + 4 * j) / 2;
+                        uint4 lo, hi;
+                        const long long t0 = clock64();
+                        while (true) {
+                            asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(lo.x), "=r"(lo.y), "=r"(lo.z), "=r"(lo.w) : "l"(src) : "memory");
+                            asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(hi.x), "=r"(hi.y), "=r"(hi.z), "=r"(hi.w) : "l"(src + 1) : "memory");
+                            if (lo.y == seq && lo.w == seq && hi.y == seq && hi.w == seq) break;
+                            if (clock64() - t0 > 4000000000LL) {  // ~2 s: a peer rank is missing; report instead of hanging the device
+                                if (ad.status) *ad.status = 1;
+                                break;
+                            }
+                        }
+                        y = make_float4(__uint_as_float(lo.x), __uint_as_float(lo.z), __uint_as_float(hi.x), __uint_as_float(hi.z));
+                    }
                     sum.x += y.x; sum.y += y.y; sum.z += y.z; sum.w += y.w;
                 }
                 __stcg(reinterpret_cast<float4*>(e.g_total) + j, sum);
