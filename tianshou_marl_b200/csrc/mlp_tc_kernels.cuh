@@ -1059,52 +1059,24 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
         TRACE(erow, 42);
         // ---- optimizer step: the whole of it in every CTA, on the CTA's own copy of the state ----
         // ---- grid barrier with the cross-rank gradient exchange folded into it ----
-        // Arrive: one atomic per CTA on a device counter; every CTA waits until the counter shows all local arrivals.  The
-        // LAST CTA to arrive knows the local gradient is complete; with data-parallel ranks (ad.world > 1) it PUSHES the
-        // whole gradient (<= 28 KB) into slot [seq & 1][rank] of every peer's receive area over NVLink as 16-byte stores of
-        // {value, seq, value, seq}: every 8-byte (value, step) pair is self-validating, so no fence, release or flag
-        // follows the data (a release after the stores costs a full NVLink round trip, a flag one more hop; one remote
-        // atomic per CTA, 148 per peer and step, cost ~10 us).  Receivers poll the pairs they need.  Receive areas are
-        // double buffered by step parity: a peer overwrites parity b at step seq + 2, after it has finished step seq + 1,
-        // which needed this rank's data of step seq + 1, pushed only after every CTA here was done with step seq.
+        // Arrive: one atomic per CTA on a device counter; every CTA waits until the counter shows all local arrivals: the
+        // local gradient is complete.  With data-parallel ranks (ad.world > 1) every CTA then PUSHES its slice of it into
+        // slot [seq & 1][rank] of every peer's receive area over NVLink as 16-byte stores of {value, seq, value, seq}:
+        // every 8-byte (value, step) pair is self-validating, so no fence, release or flag follows the data (a release
+        // after the stores costs a full NVLink round trip, a flag one more hop; one remote atomic per CTA cost ~10 us;
+        // one CTA pushing everything is fine at 2 ranks but store-issue bound at 8: 322 KB from one SM).  The same CTA
+        // polls the pairs of its slice from every peer.  Receive areas are double buffered by step parity: a peer
+        // overwrites parity b at step seq + 2, after it has finished step seq + 1, which needed this rank's data of step
+        // seq + 1, pushed only after every CTA here was done with step seq.
         uint2 Q[EP_OPT];  // (in flight across the barrier)
 #pragma unroll
         for (int u = 0; u < EP_OPT; ++u) Q[u] = q_tab[u];
         const uint32_t q_contig = q_tab[EP_OPT].x;
-        int* s_last = s_has + TC_GROUPS;
         const uint32_t seq = ad.seq + (uint32_t)m;
         __threadfence();
         __syncthreads();
         const uint32_t arrivals = (uint32_t)(m + 1) * gridDim.x;  // counter value once every CTA has arrived at this barrier
-        if (rc == 0) s_last[0] = ad.world > 1 ? (atomicAdd(e.sync_words, 1u) + 1u == arrivals) : (atomicAdd(e.sync_words, 1u), 0);
-        __syncthreads();
-        if (s_last[0]) {
-            __threadfence();
-            if (ad.world > 1) {
-                const int64_t off = ((int64_t)(seq & 1u) * ad.world + ad.rank) * ad.n_stride;
-#pragma unroll
-                for (int u = 0; u < EP_OPT; ++u) {
-                    const int i = 4 * (rc + u * EP_THREADS);
-                    if (i < ad.n_stride) {
-                        float4 v;
-                        if (i + 3 < n) {
-                            v = __ldcg(reinterpret_cast<const float4*>(g_cur + i));
-                        } else {
-                            auto get = [&](int k) { return i + k < n ? __ldcg(g_cur + i + k) : 0.f; };
-                            v = make_float4(get(0), get(1), get(2), get(3));
-                        }
-                        const uint4 lo = make_uint4(__float_as_uint(v.x), seq, __float_as_uint(v.y), seq);
-                        const uint4 hi = make_uint4(__float_as_uint(v.z), seq, __float_as_uint(v.w), seq);
-                        for (int q = 0; q < ad.world; ++q)
-                            if (q != ad.rank) {
-                                uint4* dst = ad.peer_ll[q] + (off + i) / 2;
-                                asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "r"(lo.x), "r"(lo.y), "r"(lo.z), "r"(lo.w) : "memory");
-                                asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(dst + 1), "r"(hi.x), "r"(hi.y), "r"(hi.z), "r"(hi.w) : "memory");
-                            }
-                    }
-                }
-            }
-        }
+        if (rc == 0) atomicAdd(e.sync_words, 1u);
         if (rc == 0) {
             const uint32_t* w = e.sync_words;
             const uint32_t want = arrivals;
@@ -1137,6 +1109,17 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
                 } else {
                     auto get = [&](int k) { return 4 * j + k < n ? __ldcg(g_cur + 4 * j + k) : 0.f; };
                     own = make_float4(get(0), get(1), get(2), get(3));
+                }
+                {   // this CTA's slice of the local gradient -> slot [seq & 1][rank] of every peer
+                    const uint4 plo = make_uint4(__float_as_uint(own.x), seq, __float_as_uint(own.y), seq);
+                    const uint4 phi = make_uint4(__float_as_uint(own.z), seq, __float_as_uint(own.w), seq);
+                    const int64_t off = ((int64_t)(seq & 1u) * ad.world + ad.rank) * ad.n_stride + 4 * j;
+                    for (int q = 0; q < ad.world; ++q)
+                        if (q != ad.rank) {
+                            uint4* dst = ad.peer_ll[q] + off / 2;
+                            asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "r"(plo.x), "r"(plo.y), "r"(plo.z), "r"(plo.w) : "memory");
+                            asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(dst + 1), "r"(phi.x), "r"(phi.y), "r"(phi.z), "r"(phi.w) : "memory");
+                        }
                 }
                 float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
                 for (int q = 0; q < ad.world; ++q) {
