@@ -9,7 +9,8 @@ of `simple_spread_v3` over E environments per GPU (policy forward -> MPE world s
 buffer add), GAE over the collected [T, E*A] block, and the PPO minibatch update (`repeat`
 epochs).  Metric (BASELINE.json): agent-steps/s, whole job.  One process per GPU; environments
 shard across ranks with no data-path collective during collect/GAE (scaling: weak); the PPO
-update all-reduces the flat gradient over NCCL.
+update exchanges the flat gradient between ranks inside its persistent kernel over NVLink peer
+memory (torch.distributed / NCCL only for the rendezvous and the timing all-reduce).
 
 Nothing here reads /root/reference.  oracle/ is executed only by the `cpu_baseline` leg and
 by `--impl reference`.

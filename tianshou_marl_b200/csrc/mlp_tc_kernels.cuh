@@ -989,11 +989,7 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
         }
         TRACE(erow, 41);
         // ---- flush: each group stages its accumulators, the CTA adds the stagings and issues one set of reductions ----
-        if (it > 0) {
-            tc::mbar_wait(s.bar + 1, (wg_commits - 1) & 1);
-            tc::fence_after_sync();
-            tc_stage_grads(smem, s, o, a.in_dim, a.out_dim);
-        }
+        // (the register reductions first: they overlap the last tile's weight-gradient MMAs, which the staging has to wait for)
         l_clip += (double)f_clip; l_vf += (double)f_vf; l_ent += (double)f_ent;
         {
             float* red_f = reinterpret_cast<float*>(smem + SM_RED);
@@ -1013,6 +1009,11 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
                 red_d[w * 3 + 0] = l_clip; red_d[w * 3 + 1] = l_vf; red_d[w * 3 + 2] = l_ent;
             }
             if (r == 0) s_has[grp] = it > 0;
+        }
+        if (it > 0) {
+            tc::mbar_wait(s.bar + 1, (wg_commits - 1) & 1);
+            tc::fence_after_sync();
+            tc_stage_grads(smem, s, o, a.in_dim, a.out_dim);
         }
         tc::fence_before_sync();
         __syncthreads();
@@ -1206,6 +1207,7 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
             float Mo[32], Vo[32];  // one TMEM round trip for all moments of this thread (entries 28..31 unused)
             {
                 float v0[16], v1[16];
+                tc::tmem_st_wait();  // the previous step's stores of these columns (waited here, not there)
                 tc::tmem_ld32(s.lane_base + TM_OPT_M, Mo);
                 tc::tmem_ld16(s.lane_base + TM_OPT_V0, v0);
                 tc::tmem_ld16(s.lane_base + TM_OPT_V1, v1);
@@ -1259,7 +1261,6 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
                 for (int k = 0; k < 8; ++k) t8[k] = Vo[8 * c + k];
                 tc::tmem_st8(s.lane_base + (c < 2 ? TM_OPT_V0 + 8 * c : TM_OPT_V1 + 8 * (c - 2)), t8);
             }
-            tc::tmem_st_wait();
         }
         TRACE(erow, 45);
         {   // buffer (m - 1) % 3 has been read by everybody (all CTAs are past barrier m); it is next reduced into after barrier m + 1
@@ -1283,6 +1284,7 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
         if (blockIdx.x == 0 && rc == 0) *ad.step = step0 + e.n_mb;
         if (blockIdx.x == 0 && rc < 2) e.sync_words[rc] = 0u;  // arrival counters: zero between launches
     }
+    tc::tmem_st_wait();
     tc::fence_before_sync();
     __syncthreads();
     if ((rc >> 5) == 0) tc::tmem_dealloc(*reinterpret_cast<const uint32_t*>(smem_all + SM_BAR + 16), TM_COLS_BWD * TC_GROUPS);
