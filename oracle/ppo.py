@@ -144,13 +144,21 @@ def minibatch_loss(net: Net, obs, act_, adv, ret, logp_old, v_old, cfg: dict, pr
 
 
 def update_with_orders(net: Net, obs, act_, adv, ret, logp_old, v_old, cfg: dict, orders: list[np.ndarray], batch_size: int,
-                       lr: float, max_grad_norm: float, probs_param=False) -> dict[str, list[float]]:
-    """ppo.py:164-224 with the per-epoch permutations given (np.random.permutation(B) in the reference)."""
+                       lr: float, max_grad_norm: float, probs_param=False, recompute: dict | None = None) -> dict[str, list[float]]:
+    """ppo.py:164-224 with the per-epoch permutations given (np.random.permutation(B) in the reference).
+    recompute (recompute_advantage=True, ppo.py:174-178): dict(obs_next, rew, term, trunc, indices, unfinished, gamma, lam);
+    before every epoch after the first, v_s / returns / advantages are re-evaluated with the current parameters."""
+    obs_np = np.ascontiguousarray(obs, np.float32)
     T = lambda a, dt=torch.float32: torch.from_numpy(np.ascontiguousarray(a)).to(dt)  # noqa: E731
     obs, adv, ret, logp_old, v_old, act_t = T(obs), T(adv), T(ret), T(logp_old), T(v_old), T(act_)
     log = {"loss": [], "clip": [], "vf": [], "ent": [], "gnorm": []}
     B = len(adv)
-    for order in orders:
+    for ep, order in enumerate(orders):
+        if recompute is not None and ep > 0:
+            r = recompute
+            v_new, v_nn = values(net, obs_np), values(net, r["obs_next"])
+            ret_n, adv_n = _gae(r["rew"], r["term"], r["trunc"], r["indices"], r["unfinished"], v_nn, v_new, r["gamma"], r["lam"])
+            adv, ret, v_old = T(adv_n.astype(np.float32)), T(ret_n.astype(np.float32)), T(v_new)
         for s, e in split_bounds(B, batch_size, True):
             ix = torch.from_numpy(np.asarray(order[s:e], np.int64))
             loss, c, v, en = minibatch_loss(net, obs[ix], act_t[ix], adv[ix], ret[ix], logp_old[ix], v_old[ix], cfg, probs_param)

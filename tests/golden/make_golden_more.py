@@ -47,21 +47,30 @@ def _flat_params(ac) -> dict[str, np.ndarray]:
     }
 
 
-def gen_ppo() -> None:
+PPO_CASES = [
+    # R rows, T steps, O, H, nA, batch_size, repeat, probs-parameterisation, PPO kwargs
+    dict(R=24, T=16, O=18, H=64, nA=5, bs=128, repeat=2, probs=False, kw=dict()),
+    dict(R=12, T=25, O=18, H=64, nA=5, bs=64, repeat=3, probs=False,
+         kw=dict(max_grad_norm=0.5, value_clip=True, dual_clip=3.0, advantage_normalization=False, lr=1e-3)),
+    dict(R=8, T=13, O=16, H=64, nA=5, bs=40, repeat=2, probs=True, kw=dict(max_grad_norm=0.5, ent_coef=0.05, vf_coef=0.25)),
+    dict(R=6, T=12, O=60, H=128, nA=5, bs=36, repeat=2, probs=False, kw=dict(max_grad_norm=1.0, eps_clip=0.1)),
+]
+# recompute_advantage (ppo.py:174-178): returns / advantages / v_s re-evaluated with the current parameters before every epoch after the first
+PPO_RECOMPUTE_CASES = [
+    dict(R=16, T=20, O=18, H=64, nA=5, bs=80, repeat=3, probs=False, kw=dict(recompute_advantage=True, max_grad_norm=0.5, lr=1e-3)),
+    dict(R=10, T=15, O=18, H=64, nA=5, bs=50, repeat=2, probs=False,
+         kw=dict(recompute_advantage=True, value_clip=True, advantage_normalization=False, lr=1e-3)),
+]
+
+
+def gen_ppo(cases=None, fname: str = "ppo.npz") -> None:
     import torch
     from tianshou.data import Batch, VectorReplayBuffer
     from tianshou.data.stats import SequenceSummaryStats
     from tianshou.utils.torch_utils import policy_within_training_step, torch_train_mode
 
     out: dict[str, np.ndarray] = {}
-    cases = [
-        # R rows, T steps, O, H, nA, batch_size, repeat, probs-parameterisation, PPO kwargs
-        dict(R=24, T=16, O=18, H=64, nA=5, bs=128, repeat=2, probs=False, kw=dict()),
-        dict(R=12, T=25, O=18, H=64, nA=5, bs=64, repeat=3, probs=False,
-             kw=dict(max_grad_norm=0.5, value_clip=True, dual_clip=3.0, advantage_normalization=False, lr=1e-3)),
-        dict(R=8, T=13, O=16, H=64, nA=5, bs=40, repeat=2, probs=True, kw=dict(max_grad_norm=0.5, ent_coef=0.05, vf_coef=0.25)),
-        dict(R=6, T=12, O=60, H=128, nA=5, bs=36, repeat=2, probs=False, kw=dict(max_grad_norm=1.0, eps_clip=0.1)),
-    ]
+    cases = PPO_CASES if cases is None else cases
     for ci, c in enumerate(cases):
         R, T, O, H, nA = c["R"], c["T"], c["O"], c["H"], c["nA"]
         rng = np.random.default_rng(100 + ci)
@@ -121,7 +130,7 @@ def gen_ppo() -> None:
                                        float(kw.get("value_clip", False)), float(kw.get("advantage_normalization", True)),
                                        kw.get("max_grad_norm") or 0.0, kw.get("lr", 3e-4), 0.99, 0.95])
     out["n_cases"] = np.array(len(cases))
-    save("ppo.npz", **out)
+    save(fname, **out)
 
 
-GENS = {"ppo": gen_ppo}
+GENS = {"ppo": gen_ppo, "ppo_recompute": lambda: gen_ppo(PPO_RECOMPUTE_CASES, "ppo_recompute.npz")}

@@ -14,7 +14,7 @@ from _ppo_golden import load_case
 pytestmark = pytest.mark.gpu
 
 
-def _mk(c, order="numpy"):
+def _mk(c, order="numpy", **ppo_kw):
     from tianshou_marl_b200.algorithm import PPO, AdamOptimizerFactory, DiscreteActorPolicy
     from tianshou_marl_b200.data import Batch, VectorReplayBuffer
     from tianshou_marl_b200.utils import ActorCriticNet
@@ -24,7 +24,7 @@ def _mk(c, order="numpy"):
     k = c["cfg"]
     alg = PPO(policy=pol, critic=net, optim=AdamOptimizerFactory(lr=c["lr"]), eps_clip=k["eps_clip"], dual_clip=k["dual_clip"] or None,
               value_clip=k["value_clip"], advantage_normalization=k["adv_norm"], vf_coef=k["vf_coef"], ent_coef=k["ent_coef"],
-              max_grad_norm=c["max_norm"] or None, gamma=c["gamma"], gae_lambda=c["lam"], minibatch_order=order)
+              max_grad_norm=c["max_norm"] or None, gamma=c["gamma"], gae_lambda=c["lam"], minibatch_order=order, **ppo_kw)
     buf = VectorReplayBuffer(c["R"] * c["T"], c["R"], index_type="torch")
     for t in range(c["T"]):
         buf.add(Batch(obs=c["obs"][t], act=c["act"][t], rew=c["rew"][t], terminated=c["term"][t], truncated=c["trunc"][t],
@@ -264,3 +264,22 @@ def test_dedup_next_values_is_bit_identical(engine):
         res.append({k: alg._work[k].clone() for k in ("v_s", "v_n", "adv", "ret")})
     for k in res[0]:
         assert torch.equal(res[0][k], res[1][k]), k
+
+
+@pytest.mark.parametrize("ci", [0, 1])
+def test_recompute_advantage_matches_reference(golden, ci):
+    """PPO(recompute_advantage=True) (ppo.py:174-178) vs fixtures recorded from the reference: every minibatch loss of every
+    epoch (the later epochs use re-evaluated values / advantages) and the final parameters."""
+    c = load_case(golden("ppo_recompute.npz"), ci)
+    net, pol, alg, buf = _mk(c, "numpy", recompute_advantage=True)
+    pol.is_within_training_step = True
+    np.random.seed(c["seed"])
+    stats = alg.update(buf, c["bs"], c["repeat"])
+    seq = alg.last_sequences
+    assert stats.gradient_steps == len(c["loss_seq"])
+    for k, ref in (("loss", "loss_seq"), ("clip", "clip_seq"), ("vf", "vf_seq"), ("ent", "ent_seq")):
+        assert np.allclose(seq[k], c[ref], rtol=2e-4, atol=2e-5), (k, np.abs(seq[k] - c[ref]).max())
+    v = net.named_views()
+    for k in ("W1", "b1", "W2", "b2", "W3", "b3"):
+        err = np.abs(v[k].cpu().numpy() - c["after_" + k]).max()
+        assert err < 5e-5, (k, err)

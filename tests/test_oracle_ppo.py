@@ -34,3 +34,28 @@ def test_oracle_matches_reference_ppo(golden, ci):
         assert np.allclose(log[k], c[ref], rtol=1e-4, atol=1e-5), (k, np.abs(np.array(log[k]) - c[ref]).max())
     for k, p in zip(("W1", "b1", "W2", "b2", "W3", "b3"), net.p):
         assert np.allclose(p.detach().numpy(), c["after_" + k], rtol=0, atol=2e-5), (k, np.abs(p.detach().numpy() - c["after_" + k]).max())
+
+
+@pytest.mark.parametrize("ci", [0, 1])
+def test_oracle_matches_reference_ppo_recompute_advantage(golden, ci):
+    """recompute_advantage=True (ppo.py:174-178): fixtures from the reference in tests/golden/ppo_recompute.npz."""
+    c = load_case(golden("ppo_recompute.npz"), ci)
+    net = oppo.Net(c["W1"], c["b1"], c["W2"], c["b2"], c["W3"], c["b3"], c["nA"])
+    f = c["flat"]
+    v_s, ret, adv, logp_old = oppo.preprocess(net, f["obs"], f["obs_next"], f["act"], f["rew"], f["term"], f["trunc"], c["indices"],
+                                              c["unfinished"], c["gamma"], c["lam"], c["probs"])
+    assert np.allclose(v_s, c["v_s"], rtol=2e-5, atol=2e-6) and np.allclose(adv, c["adv"], rtol=2e-5, atol=2e-5)
+    rc = dict(obs_next=f["obs_next"], rew=f["rew"], term=f["term"], trunc=f["trunc"], indices=c["indices"], unfinished=c["unfinished"],
+              gamma=c["gamma"], lam=c["lam"])
+    log = oppo.update_with_orders(net, f["obs"], f["act"], c["adv"], c["returns"], c["logp_old"], c["v_s"], c["cfg"], c["orders"],
+                                  c["bs"], c["lr"], c["max_norm"], c["probs"], recompute=rc)
+    assert len(log["loss"]) == len(c["loss_seq"])
+    for k, ref in (("loss", "loss_seq"), ("clip", "clip_seq"), ("vf", "vf_seq"), ("ent", "ent_seq")):
+        assert np.allclose(log[k], c[ref], rtol=1e-4, atol=1e-5), (k, np.abs(np.array(log[k]) - c[ref]).max())
+    for k, p in zip(("W1", "b1", "W2", "b2", "W3", "b3"), net.p):
+        assert np.allclose(p.detach().numpy(), c["after_" + k], rtol=0, atol=2e-5), (k, np.abs(p.detach().numpy() - c["after_" + k]).max())
+    # and without recomputation the later epochs must NOT match (the fixture really exercises the option)
+    net2 = oppo.Net(c["W1"], c["b1"], c["W2"], c["b2"], c["W3"], c["b3"], c["nA"])
+    log2 = oppo.update_with_orders(net2, f["obs"], f["act"], c["adv"], c["returns"], c["logp_old"], c["v_s"], c["cfg"], c["orders"],
+                                   c["bs"], c["lr"], c["max_norm"], c["probs"])
+    assert not np.allclose(log2["loss"], c["loss_seq"], rtol=1e-4, atol=1e-5)

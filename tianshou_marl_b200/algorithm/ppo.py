@@ -210,19 +210,30 @@ class PPO:
         # slot, computed by the same forward kernel with the parameters this update starts from (buffer._policy_version), so
         # critic(obs) and logp_old need no second pass, and critic(obs_next[t]) = value[t + 1] wherever obs_next[t] is the
         # next stored obs; only rows whose episode ended at t and the last slot get a critic evaluation of obs_next.
+        # the rollout kernel wrote obs_next[t] and obs[t + 1] from the same registers wherever the episode went on: critic(obs_next[t])
+        # IS critic(obs[t + 1]) there; only rows that ended an episode at t, and the last slot, need an evaluation of obs_next
+        dedup_ok = bool(self.dedup_next_values and lockstep and rows is None and buffer._obs_chain is True)
+
+        def next_values(v_cur: torch.Tensor, dedup: bool) -> None:
+            """critic(obs_next) -> v_n, given critic(obs) = v_cur under the same parameters (a2c.py:124-127)."""
+            if dedup:
+                start0 = buffer._lockstep_ins if lock_len == size else 0
+                need = self._buf("need_list", (size * R,), torch.int64)
+                cnt = self._buf("need_count", (1,), torch.int64)
+                _lib.check(L.tsm_values_next_prepare(P(v_cur), P(st["done"]), size, R, start0, lock_len, P(v_n), P(need), P(cnt), S))
+                n_need = int(cnt.item())
+                if n_need > 0:
+                    net.forward(st["obs_next"].view(size * R, O), mode="raw", out={"value": v_n.view(-1)}, rows=need[:n_need], scatter=True)
+            else:
+                net.forward(st["obs_next"].view(size * R, O), mode="raw", out={"value": v_n.view(-1)}, rows=slots, scatter=slots is not None)
+
         reuse = (self.reuse_rollout and lockstep and rows is None and "value" in st and "logp" in st and net.value_index >= 0
                  and getattr(self.policy, "actor", None) is net and buffer._policy_version is not None
                  and buffer._policy_version == net.param_version)
         if reuse:
             tk = _lib.t_start("critic_forward")
             v_s, logp = st["value"], st["logp"]
-            start0 = buffer._lockstep_ins if lock_len == size else 0
-            need = self._buf("need_list", (size * R,), torch.int64)
-            cnt = self._buf("need_count", (1,), torch.int64)
-            _lib.check(L.tsm_values_next_prepare(P(v_s), P(st["done"]), size, R, start0, lock_len, P(v_n), P(need), P(cnt), S))
-            n_need = int(cnt.item())
-            if n_need > 0:
-                net.forward(st["obs_next"].view(size * R, O), mode="raw", out={"value": v_n.view(-1)}, rows=need[:n_need], scatter=True)
+            next_values(v_s, True)
             _lib.t_stop(tk)
         else:
             # critic(obs) (a2c.py:120-123) and logp_old = log pi(act | obs) (ppo.py:157-161) read the same rows through the
@@ -232,24 +243,28 @@ class PPO:
                         rows=slots, scatter=slots is not None)
             _lib.t_stop(tk)
             tk = _lib.t_start("critic_forward")
-            if self.dedup_next_values and lockstep and rows is None and buffer._obs_chain is True:
-                # the rollout kernel wrote obs_next[t] and obs[t + 1] from the same registers wherever the episode went on:
-                # critic(obs_next[t]) IS v_s[t + 1] there; only rows that ended an episode at t, and the last slot, are evaluated
-                start0 = buffer._lockstep_ins if lock_len == size else 0
-                need = self._buf("need_list", (size * R,), torch.int64)
-                cnt = self._buf("need_count", (1,), torch.int64)
-                _lib.check(L.tsm_values_next_prepare(P(v_s), P(st["done"]), size, R, start0, lock_len, P(v_n), P(need), P(cnt), S))
-                n_need = int(cnt.item())
-                if n_need > 0:
-                    net.forward(st["obs_next"].view(size * R, O), mode="raw", out={"value": v_n.view(-1)}, rows=need[:n_need], scatter=True)
-            else:
-                net.forward(st["obs_next"].view(size * R, O), mode="raw", out={"value": v_n.view(-1)}, rows=slots, scatter=slots is not None)
+            next_values(v_s, dedup_ok)
             _lib.t_stop(tk)
         tk = _lib.t_start("gae")
+        flat_ctx: dict[str, Any] = {}
+
+        def run_gae(v_cur: torch.Tensor) -> None:
+            """compute_episodic_return over the stored rollout -> adv, ret (algorithm_base.py:651-717)."""
+            if lockstep:
+                gae_time_major(v_cur, v_n, st["rew"], st["terminated"], st["truncated"], buffer._lockstep_ins if flat_ctx["full"] else 0,
+                               flat_ctx["len"], self.gamma, self.gae_lambda, adv, ret)
+            else:
+                g = lambda t: t.view(-1)[flat_ctx["slot"]]  # noqa: E731
+                r_f, a_f = gae_flat(g(v_cur), g(v_n), g(st["rew"]), g(st["terminated"]), g(st["truncated"]), flat_ctx["force"], 0,
+                                    self.gamma, self.gae_lambda)
+                adv.view(-1)[flat_ctx["slot"]] = a_f
+                ret.view(-1)[flat_ctx["slot"]] = r_f
+
         if lockstep:
             start = buffer._lockstep_ins if lock_len == size else 0
             B = lock_len * R
-            gae_time_major(v_s, v_n, st["rew"], st["terminated"], st["truncated"], start, lock_len, self.gamma, self.gae_lambda, adv, ret)
+            flat_ctx.update(full=lock_len == size, len=lock_len)
+            run_gae(v_s)
             idx_all = None
             if rows is not None:  # env-major buffer indices of the group's rows, in buffer.sample(0) order
                 tt = (start + torch.arange(lock_len, device=net.device, dtype=torch.int64)) % size
@@ -265,14 +280,11 @@ class PPO:
             if B == 0:
                 return A2CTrainingStats(*(SequenceSummaryStats.from_sequence([]) for _ in range(4)))
             slot = (idx_all % size) * R + idx_all // size
-            g = lambda t: t.view(-1)[slot]  # noqa: E731
             unf = buffer._unfinished_device()
             mask = torch.zeros(buffer.maxsize, dtype=torch.uint8, device=net.device)
             mask[unf] = 1
-            r_f, a_f = gae_flat(g(v_s), g(v_n), g(st["rew"]), g(st["terminated"]), g(st["truncated"]), mask[idx_all], 0,
-                                self.gamma, self.gae_lambda)
-            adv.view(-1)[slot] = a_f
-            ret.view(-1)[slot] = r_f
+            flat_ctx.update(slot=slot, force=mask[idx_all])
+            run_gae(v_s)
             start, lock_len = 0, size
         _lib.t_stop(tk)
         # ---- logp_old (ppo.py:157-161) ----
@@ -300,7 +312,16 @@ class PPO:
         keep = []  # keep explicit index tensors alive until the stream has consumed them
         for ep in range(repeat):
             if self.recompute_adv and ep > 0:
-                raise NotImplementedError("recompute_advantage is a next-tier row, not built yet")
+                # ppo.py:174-178 -> a2c.py:113-151 with the CURRENT parameters: v_s, returns and advantages (logp_old stays)
+                tk = _lib.t_start("recompute_advantage")
+                v_s = self._buf("v_s", (size, R))
+                net.forward(obs_all, mode="raw", out={"value": v_s.view(-1)}, rows=slots, scatter=slots is not None)
+                next_values(v_s, dedup_ok)
+                run_gae(v_s)
+                pb.v_old = P(v_s)
+                if net.engine == "tc":
+                    _lib.check(L.tsm_ppo_pack_records(net.desc, C.byref(pb), P(rec), S))
+                _lib.t_stop(tk)
             if self.minibatch_order == "numpy":
                 order = torch.as_tensor(np.random.permutation(B), device=net.device)  # batch.py:1219
                 explicit = order if idx_all is None and start == 0 and lock_len == size else (
