@@ -82,10 +82,25 @@ def split_bounds(length: int, size: int, merge_last: bool = True) -> list[tuple[
     return out
 
 
-def preprocess(net: Net, obs, obs_next, act_, rew, term, trunc, indices, unfinished, gamma, lam, probs_param=False):
-    """a2c.py:113-151 + ppo.py:146-162 over a flat batch in buffer.sample(0) order."""
+def rms_update(rms: dict, data: np.ndarray) -> None:
+    """RunningMeanStd.update (tianshou/utils/statistics.py:96-114) on rms = dict(mean, var, count)."""
+    b_mean, b_var, b_n = float(np.mean(data)), float(np.var(data)), len(data)
+    delta, tot = b_mean - rms["mean"], rms["count"] + b_n
+    m_2 = rms["var"] * rms["count"] + b_var * b_n + delta**2 * rms["count"] * b_n / tot
+    rms["mean"], rms["var"], rms["count"] = rms["mean"] + delta * b_n / tot, m_2 / tot, tot
+
+
+def preprocess(net: Net, obs, obs_next, act_, rew, term, trunc, indices, unfinished, gamma, lam, probs_param=False, ret_rms: dict | None = None):
+    """a2c.py:113-151 + ppo.py:146-162 over a flat batch in buffer.sample(0) order.  ret_rms = dict(mean, var, count):
+    return_scaling=True (a2c.py:132-146); the dict is updated like self.ret_rms."""
     v_s, v_n = values(net, obs), values(net, obs_next)
-    ret, adv = _gae(rew, term, trunc, indices, unfinished, v_n, v_s, gamma, lam)
+    if ret_rms is not None:
+        sc = np.sqrt(ret_rms["var"] + 1e-8)
+        ret_u, adv = _gae(rew, term, trunc, indices, unfinished, v_n * sc, v_s * sc, gamma, lam)
+        ret = ret_u / sc
+        rms_update(ret_rms, ret_u)
+    else:
+        ret, adv = _gae(rew, term, trunc, indices, unfinished, v_n, v_s, gamma, lam)
     with torch.no_grad():
         logits, _ = net.forward(torch.from_numpy(np.ascontiguousarray(obs, np.float32)))
         logp_old = log_softmax_dist(logits, probs_param).log_prob(torch.from_numpy(np.asarray(act_)).float()).numpy()

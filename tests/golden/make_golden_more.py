@@ -63,6 +63,14 @@ PPO_RECOMPUTE_CASES = [
 ]
 
 
+# return_scaling (a2c.py:132-146): one un-recorded _preprocess_batch first, so that ret_rms holds non-trivial statistics
+PPO_RETSCALE_CASES = [
+    dict(R=16, T=20, O=18, H=64, nA=5, bs=80, repeat=2, probs=False, warm_rms=True, kw=dict(return_scaling=True, max_grad_norm=0.5, lr=1e-3)),
+    dict(R=10, T=15, O=18, H=64, nA=5, bs=50, repeat=2, probs=False, warm_rms=True,
+         kw=dict(return_scaling=True, recompute_advantage=True, value_clip=True, lr=1e-3)),
+]
+
+
 def gen_ppo(cases=None, fname: str = "ppo.npz") -> None:
     import torch
     from tianshou.data import Batch, VectorReplayBuffer
@@ -111,8 +119,14 @@ def gen_ppo(cases=None, fname: str = "ppo.npz") -> None:
         try:
             np.random.seed(7 + ci)
             with policy_within_training_step(alg.policy):
+                if c.get("warm_rms"):
+                    b0, i0 = buf.sample(0)
+                    alg._preprocess_batch(b0, buf, i0)
+                    out[pre + "rms_before"] = np.array([float(alg.ret_rms.mean), float(alg.ret_rms.var), float(alg.ret_rms.count)])
                 batch, indices = buf.sample(0)
                 batch = alg._preprocess_batch(batch, buf, indices)
+                if c.get("warm_rms"):
+                    out[pre + "rms_after_preprocess"] = np.array([float(alg.ret_rms.mean), float(alg.ret_rms.var), float(alg.ret_rms.count)])
                 out[pre + "indices"] = np.asarray(indices)
                 for k in ("v_s", "returns", "adv", "logp_old"):
                     out[pre + k] = batch[k].detach().cpu().numpy().copy()
@@ -124,6 +138,8 @@ def gen_ppo(cases=None, fname: str = "ppo.npz") -> None:
         out[pre + "gradient_steps"] = np.array(stats.gradient_steps)
         for k, v in _flat_params(ac).items():
             out[pre + "after_" + k] = v
+        if c.get("warm_rms"):
+            out[pre + "rms_after"] = np.array([float(alg.ret_rms.mean), float(alg.ret_rms.var), float(alg.ret_rms.count)])
         kw = c["kw"]
         out[pre + "cfg"] = np.array([R, T, O, H, nA, c["bs"], c["repeat"], int(c["probs"]), 7 + ci], np.int64)
         out[pre + "hyper"] = np.array([kw.get("eps_clip", 0.2), kw.get("dual_clip") or 0.0, kw.get("vf_coef", 0.5), kw.get("ent_coef", 0.01),
@@ -133,4 +149,5 @@ def gen_ppo(cases=None, fname: str = "ppo.npz") -> None:
     save(fname, **out)
 
 
-GENS = {"ppo": gen_ppo, "ppo_recompute": lambda: gen_ppo(PPO_RECOMPUTE_CASES, "ppo_recompute.npz")}
+GENS = {"ppo": gen_ppo, "ppo_recompute": lambda: gen_ppo(PPO_RECOMPUTE_CASES, "ppo_recompute.npz"),
+        "ppo_retscale": lambda: gen_ppo(PPO_RETSCALE_CASES, "ppo_retscale.npz")}

@@ -283,3 +283,31 @@ def test_recompute_advantage_matches_reference(golden, ci):
     for k in ("W1", "b1", "W2", "b2", "W3", "b3"):
         err = np.abs(v[k].cpu().numpy() - c["after_" + k]).max()
         assert err < 5e-5, (k, err)
+
+
+@pytest.mark.parametrize("ci", [0, 1])
+def test_return_scaling_matches_reference(golden, ci):
+    """PPO(return_scaling=True) (a2c.py:132-146) vs fixtures recorded from the reference with a warmed-up ret_rms: normalised
+    returns, advantages, the running statistics after the update, every minibatch loss and the final parameters."""
+    g = golden("ppo_retscale.npz")
+    c = load_case(g, ci)
+    pre = f"p{ci}_"
+    net, pol, alg, buf = _mk(c, "numpy", return_scaling=True, recompute_advantage=(ci == 1))
+    alg.ret_rms.mean, alg.ret_rms.var, alg.ret_rms.count = (float(x) for x in g[pre + "rms_before"])
+    alg.ret_rms.count = int(alg.ret_rms.count)
+    pol.is_within_training_step = True
+    np.random.seed(c["seed"])
+    stats = alg.update(buf, c["bs"], c["repeat"])
+    em = lambda t: t.t().contiguous().view(-1).cpu().numpy()  # noqa: E731
+    if ci == 0:  # (with recompute_advantage the work arrays hold the LAST epoch's values)
+        assert np.allclose(em(alg._work["ret"]), c["returns"], rtol=2e-5, atol=2e-5)
+        assert np.allclose(em(alg._work["adv"]), c["adv"], rtol=2e-5, atol=2e-5)
+    assert np.allclose([alg.ret_rms.mean, alg.ret_rms.var, alg.ret_rms.count], g[pre + "rms_after"], rtol=1e-5)
+    seq = alg.last_sequences
+    assert stats.gradient_steps == len(c["loss_seq"])
+    for k, ref in (("loss", "loss_seq"), ("clip", "clip_seq"), ("vf", "vf_seq"), ("ent", "ent_seq")):
+        assert np.allclose(seq[k], c[ref], rtol=2e-4, atol=2e-5), (k, np.abs(seq[k] - c[ref]).max())
+    v = net.named_views()
+    for k in ("W1", "b1", "W2", "b2", "W3", "b3"):
+        err = np.abs(v[k].cpu().numpy() - c["after_" + k]).max()
+        assert err < 5e-5, (k, err)

@@ -59,3 +59,24 @@ def test_oracle_matches_reference_ppo_recompute_advantage(golden, ci):
     log2 = oppo.update_with_orders(net2, f["obs"], f["act"], c["adv"], c["returns"], c["logp_old"], c["v_s"], c["cfg"], c["orders"],
                                    c["bs"], c["lr"], c["max_norm"], c["probs"])
     assert not np.allclose(log2["loss"], c["loss_seq"], rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("ci", [0, 1])
+def test_oracle_matches_reference_ppo_return_scaling(golden, ci):
+    """return_scaling=True (a2c.py:132-146, RunningMeanStd statistics.py:96-114): fixtures from the reference in
+    tests/golden/ppo_retscale.npz (ret_rms warmed by one earlier preprocess; case 1 also recomputes advantages)."""
+    g = golden("ppo_retscale.npz")
+    c = load_case(g, ci)
+    pre = f"p{ci}_"
+    net = oppo.Net(c["W1"], c["b1"], c["W2"], c["b2"], c["W3"], c["b3"], c["nA"])
+    f = c["flat"]
+    rms = dict(zip(("mean", "var", "count"), (float(x) for x in g[pre + "rms_before"])))
+    v_s, ret, adv, logp_old = oppo.preprocess(net, f["obs"], f["obs_next"], f["act"], f["rew"], f["term"], f["trunc"], c["indices"],
+                                              c["unfinished"], c["gamma"], c["lam"], c["probs"], ret_rms=rms)
+    assert np.allclose(v_s, c["v_s"], rtol=2e-5, atol=2e-6)
+    assert np.allclose(ret, c["returns"], rtol=2e-5, atol=2e-5) and np.allclose(adv, c["adv"], rtol=2e-5, atol=2e-5)
+    assert np.allclose([rms["mean"], rms["var"], rms["count"]], g[pre + "rms_after_preprocess"], rtol=1e-5)
+    # scaling is really exercised: un-scaled returns differ
+    _, ret_plain, _, _ = oppo.preprocess(net, f["obs"], f["obs_next"], f["act"], f["rew"], f["term"], f["trunc"], c["indices"],
+                                         c["unfinished"], c["gamma"], c["lam"], c["probs"])
+    assert not np.allclose(ret_plain, c["returns"], rtol=1e-3, atol=1e-3)

@@ -101,8 +101,6 @@ class PPO:
                  grad_sync: str = "auto") -> None:
         assert dual_clip is None or dual_clip > 1.0, f"Dual-clip PPO parameter should greater than 1.0 but got {dual_clip}"  # ppo.py
         assert 0.0 <= gamma <= 1.0 and 0.0 <= gae_lambda <= 1.0
-        if return_scaling:
-            raise NotImplementedError("return_scaling (RunningMeanStd) is a next-tier row, not built yet")
         if critic is not None and critic is not policy.actor:
             raise NotImplementedError("separate critic network: use the CTDE path")
         if policy.actor.value_index < 0:
@@ -121,6 +119,10 @@ class PPO:
             raise ValueError("grad_sync must be 'auto', 'peer' or 'nccl'")
         self.grad_sync = grad_sync  # world > 1: "peer" = exchange fused into the optimizer kernel, "nccl" = all_reduce per minibatch
         self._peers = None
+        self.return_scaling = bool(return_scaling)  # a2c.py:110-111, :132-146
+        from ..utils.stats import RunningMeanStd
+
+        self.ret_rms = RunningMeanStd()
         self.reuse_rollout = reuse_rollout_policy_outputs
         self.dedup_next_values = dedup_next_values  # critic(obs_next[t]) = critic(obs[t + 1]) where the rollout kernel vouches for obs_next[t] == obs[t + 1]
         self._eps = 1e-8
@@ -250,7 +252,17 @@ class PPO:
 
         def run_gae(v_cur: torch.Tensor) -> None:
             """compute_episodic_return over the stored rollout -> adv, ret (algorithm_base.py:651-717)."""
-            if lockstep:
+            if lockstep and self.return_scaling:
+                scale = float(np.sqrt(self.ret_rms.var + self._eps))
+                sums_rs = self._buf("ret_sums", (2,), torch.float64)
+                gae_time_major(v_cur, v_n, st["rew"], st["terminated"], st["truncated"], buffer._lockstep_ins if flat_ctx["full"] else 0,
+                               flat_ctx["len"], self.gamma, self.gae_lambda, adv, ret, v_scale=scale, ret_sums=sums_rs)
+                s1, s2 = (float(x) for x in sums_rs.cpu().numpy())
+                n_el = flat_ctx["len"] * R
+                self.ret_rms.update_from_moments(s1 / n_el, max(s2 / n_el - (s1 / n_el) ** 2, 0.0), n_el)  # statistics.py:96-114
+            elif self.return_scaling:
+                raise NotImplementedError("return_scaling needs a lock-step rollout buffer (time-major GAE path)")
+            elif lockstep:
                 gae_time_major(v_cur, v_n, st["rew"], st["terminated"], st["truncated"], buffer._lockstep_ins if flat_ctx["full"] else 0,
                                flat_ctx["len"], self.gamma, self.gae_lambda, adv, ret)
             else:

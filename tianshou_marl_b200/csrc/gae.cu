@@ -247,14 +247,20 @@ __global__ void __launch_bounds__(THREADS) gae_flat_kernel(
 constexpr int TM_THREADS = 128;
 constexpr int TM_UNROLL = 8;
 
+// SCALED (return_scaling, a2c.py:132-146): values enter multiplied by v_scale = sqrt(ret_rms.var + eps), returns leave divided by
+// it, and the sum / sum of squares of the UNNORMALISED returns go to ret_sums[0..1] (what RunningMeanStd.update needs).
+template <bool SCALED>
 __global__ void __launch_bounds__(TM_THREADS) gae_tm_kernel(
     const float* __restrict__ v_s, const float* __restrict__ v_next, const float* __restrict__ rew,
     const uint8_t* __restrict__ term, const uint8_t* __restrict__ trunc, int64_t size, int64_t R, int64_t start,
-    int64_t len, double gamma, double gl, float* __restrict__ adv_out, float* __restrict__ ret_out) {
-    const int64_t r = (int64_t)blockIdx.x * TM_THREADS + threadIdx.x;
-    if (r >= R) return;
-    double g = 0.0;
-    int64_t j = len - 1;
+    int64_t len, double gamma, double gl, float* __restrict__ adv_out, float* __restrict__ ret_out, double v_scale,
+    double* __restrict__ ret_sums) {
+    const int64_t r_raw = (int64_t)blockIdx.x * TM_THREADS + threadIdx.x;
+    const bool live = r_raw < R;
+    if (!SCALED && !live) return;
+    const int64_t r = live ? r_raw : 0;
+    double g = 0.0, acc_s = 0.0, acc_q = 0.0;
+    int64_t j = live ? len - 1 : -1;
     int64_t tj = (start + j) % size;  // ring slot of element j; walks backwards with one wrap
     // main loop: TM_UNROLL independent loads in flight per array, then the dependent chain
     while (j >= 0) {
@@ -278,17 +284,37 @@ __global__ void __launch_bounds__(TM_THREADS) gae_tm_kernel(
         for (int u = 0; u < TM_UNROLL; ++u) {
             int64_t jj = j - u;
             if (jj < 0) break;
-            double vnm = a_te[u] ? 0.0 : (double)a_vn[u];
-            double delta = __dadd_rn(__dadd_rn((double)a_rw[u], __dmul_rn(vnm, gamma)), -(double)a_vs[u]);
+            double vs_d = (double)a_vs[u], vn_d = (double)a_vn[u];
+            if (SCALED) { vs_d = __dmul_rn(vs_d, v_scale); vn_d = __dmul_rn(vn_d, v_scale); }
+            double vnm = a_te[u] ? 0.0 : vn_d;
+            double delta = __dadd_rn(__dadd_rn((double)a_rw[u], __dmul_rn(vnm, gamma)), -vs_d);
             bool en = (a_te[u] | a_tr[u]) != 0 || jj == len - 1;
             double c = en ? 0.0 : gl;
             g = __dadd_rn(delta, __dmul_rn(c, g));
             if (adv_out) adv_out[off[u]] = (float)g;
-            if (ret_out) ret_out[off[u]] = (float)__dadd_rn(g, (double)a_vs[u]);
+            const double ru = __dadd_rn(g, vs_d);
+            if (SCALED) {
+                acc_s += ru;
+                acc_q = fma(ru, ru, acc_q);
+                if (ret_out) ret_out[off[u]] = (float)(ru / v_scale);
+            } else {
+                if (ret_out) ret_out[off[u]] = (float)ru;
+            }
         }
         j -= TM_UNROLL;
         tj -= TM_UNROLL;
         if (tj < 0) tj = ((tj % size) + size) % size;
+    }
+    if (SCALED && ret_sums) {
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            acc_s += __shfl_down_sync(0xffffffffu, acc_s, d);
+            acc_q += __shfl_down_sync(0xffffffffu, acc_q, d);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            atomicAdd(ret_sums, acc_s);
+            atomicAdd(ret_sums + 1, acc_q);
+        }
     }
 }
 
@@ -401,8 +427,27 @@ extern "C" int tsm_gae_tm(const float* v_s, const float* v_next, const float* re
     TSM_REQUIRE(adv_out != nullptr || ret_out != nullptr, "an output pointer");
     const int64_t blocks = ceil_div(n_rows, TM_THREADS);
     TSM_REQUIRE(blocks < (int64_t)INT32_MAX, "n_rows too large");
-    gae_tm_kernel<<<(unsigned)blocks, TM_THREADS, 0, as_stream(stream)>>>(
-        v_s, v_next, rew, terminated, truncated, size, n_rows, start, len, gamma, gamma * lam, adv_out, ret_out);
+    gae_tm_kernel<false><<<(unsigned)blocks, TM_THREADS, 0, as_stream(stream)>>>(
+        v_s, v_next, rew, terminated, truncated, size, n_rows, start, len, gamma, gamma * lam, adv_out, ret_out, 1.0, nullptr);
+    TSM_LAUNCH_CHECK();
+    return TSM_OK;
+}
+
+extern "C" int tsm_gae_tm_scaled(const float* v_s, const float* v_next, const float* rew, const uint8_t* terminated,
+                                 const uint8_t* truncated, int64_t size, int64_t n_rows, int64_t start, int64_t len,
+                                 double gamma, double lam, double v_scale, float* adv_out, float* ret_out, double* ret_sums,
+                                 tsm_stream_t stream) {
+    TSM_REQUIRE(size > 0 && n_rows >= 0, "size > 0, n_rows >= 0");
+    TSM_REQUIRE(len >= 0 && len <= size && start >= 0 && start < size, "0 <= len <= size, 0 <= start < size");
+    TSM_REQUIRE(v_scale > 0.0, "v_scale > 0");
+    if (ret_sums) TSM_CUDA(cudaMemsetAsync(ret_sums, 0, 2 * sizeof(double), as_stream(stream)));
+    if (n_rows == 0 || len == 0) return TSM_OK;
+    TSM_REQUIRE(rew && terminated && truncated, "rew/terminated/truncated != NULL");
+    TSM_REQUIRE(adv_out != nullptr || ret_out != nullptr, "an output pointer");
+    const int64_t blocks = ceil_div(n_rows, TM_THREADS);
+    TSM_REQUIRE(blocks < (int64_t)INT32_MAX, "n_rows too large");
+    gae_tm_kernel<true><<<(unsigned)blocks, TM_THREADS, 0, as_stream(stream)>>>(
+        v_s, v_next, rew, terminated, truncated, size, n_rows, start, len, gamma, gamma * lam, adv_out, ret_out, v_scale, ret_sums);
     TSM_LAUNCH_CHECK();
     return TSM_OK;
 }

@@ -63,3 +63,29 @@ class CollectStats:
         self.collect_time = t
         if update_collect_speed:
             self.collect_speed = self.n_collected_steps / t if t > 0 else 0.0
+
+
+class RunningMeanStd:
+    """Running mean / variance of a data stream (reference tianshou/utils/statistics.py:69-114; parallel-variance merge).
+    The device path feeds it batch moments (`update_from_moments`); `update` takes an array like the reference."""
+
+    def __init__(self, mean: float = 0.0, std: float = 1.0, clip_max: float | None = 10.0,
+                 epsilon: float = float(np.finfo(np.float32).eps)) -> None:
+        self.mean, self.var = mean, std  # (the reference initialises var with `std`, statistics.py:88)
+        self.clip_max, self.count, self.eps = clip_max, 0, epsilon
+
+    def norm(self, data_array: Any) -> Any:
+        data_array = (data_array - self.mean) / np.sqrt(self.var + self.eps)
+        if self.clip_max:
+            data_array = np.clip(data_array, -self.clip_max, self.clip_max)
+        return data_array
+
+    def update_from_moments(self, batch_mean: float, batch_var: float, batch_count: int) -> None:
+        delta = batch_mean - self.mean
+        total_count = self.count + batch_count
+        new_mean = self.mean + delta * batch_count / total_count
+        m_2 = self.var * self.count + batch_var * batch_count + delta**2 * self.count * batch_count / total_count
+        self.mean, self.var, self.count = new_mean, m_2 / total_count, total_count
+
+    def update(self, data_array: np.ndarray) -> None:
+        self.update_from_moments(np.mean(data_array, axis=0), np.var(data_array, axis=0), len(data_array))
