@@ -137,6 +137,11 @@ def minibatch_loss(net: Net, obs, act_, adv, ret, logp_old, v_old, cfg: dict, pr
     """ppo.py:181-211 for one minibatch (tensors)."""
     logits, value = net.forward(obs)
     dist = log_softmax_dist(logits, probs_param)
+    if cfg.get("a2c", False):  # A2C._update_with_batch (a2c.py:262-272)
+        actor_loss = -(dist.log_prob(act_) * adv).mean()
+        vf_loss = (ret - value).pow(2).mean()
+        ent = dist.entropy().mean()
+        return actor_loss + cfg.get("vf_coef", 0.5) * vf_loss - cfg.get("ent_coef", 0.01) * ent, actor_loss, vf_loss, ent
     if cfg.get("adv_norm", True):
         adv = (adv - adv.mean()) / (adv.std() + 1e-8)
     ratio = (dist.log_prob(act_) - logp_old).exp().float()

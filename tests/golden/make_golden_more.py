@@ -31,6 +31,10 @@ def _ref_ppo(O: int, H: int, nA: int, seed: int, softmax_probs: bool, **ppo_kw):
     else:
         policy = DiscreteActorPolicy(actor=actor, action_space=gym.spaces.Discrete(nA))
     lr = ppo_kw.pop("lr", 3e-4)
+    if ppo_kw.pop("algo", "ppo") == "a2c":
+        from tianshou.algorithm import A2C
+
+        return A2C(policy=policy, critic=critic, optim=AdamOptimizerFactory(lr=lr), **ppo_kw), ac
     alg = PPO(policy=policy, critic=critic, optim=AdamOptimizerFactory(lr=lr), **ppo_kw)
     return alg, ac
 
@@ -68,6 +72,14 @@ PPO_RETSCALE_CASES = [
     dict(R=16, T=20, O=18, H=64, nA=5, bs=80, repeat=2, probs=False, warm_rms=True, kw=dict(return_scaling=True, max_grad_norm=0.5, lr=1e-3)),
     dict(R=10, T=15, O=18, H=64, nA=5, bs=50, repeat=2, probs=False, warm_rms=True,
          kw=dict(return_scaling=True, recompute_advantage=True, value_clip=True, lr=1e-3)),
+]
+
+
+# A2C._update_with_batch (a2c.py:247-288)
+A2C_CASES = [
+    dict(R=16, T=20, O=18, H=64, nA=5, bs=80, repeat=2, probs=False, kw=dict(algo="a2c", max_grad_norm=0.5, lr=1e-3)),
+    dict(R=10, T=15, O=18, H=64, nA=5, bs=50, repeat=1, probs=False, warm_rms=True,
+         kw=dict(algo="a2c", return_scaling=True, vf_coef=0.25, ent_coef=0.02, lr=1e-3)),
 ]
 
 
@@ -129,7 +141,7 @@ def gen_ppo(cases=None, fname: str = "ppo.npz") -> None:
                     out[pre + "rms_after_preprocess"] = np.array([float(alg.ret_rms.mean), float(alg.ret_rms.var), float(alg.ret_rms.count)])
                 out[pre + "indices"] = np.asarray(indices)
                 for k in ("v_s", "returns", "adv", "logp_old"):
-                    out[pre + k] = batch[k].detach().cpu().numpy().copy()
+                    out[pre + k] = batch[k].detach().cpu().numpy().copy() if k in batch else np.zeros(len(indices), np.float32)  # (A2C: no logp_old)
                 with torch_train_mode(alg):
                     stats = alg._update_with_batch(batch, c["bs"], c["repeat"])
         finally:
@@ -150,4 +162,4 @@ def gen_ppo(cases=None, fname: str = "ppo.npz") -> None:
 
 
 GENS = {"ppo": gen_ppo, "ppo_recompute": lambda: gen_ppo(PPO_RECOMPUTE_CASES, "ppo_recompute.npz"),
-        "ppo_retscale": lambda: gen_ppo(PPO_RETSCALE_CASES, "ppo_retscale.npz")}
+        "ppo_retscale": lambda: gen_ppo(PPO_RETSCALE_CASES, "ppo_retscale.npz"), "a2c": lambda: gen_ppo(A2C_CASES, "a2c.npz")}

@@ -311,3 +311,40 @@ def test_return_scaling_matches_reference(golden, ci):
     for k in ("W1", "b1", "W2", "b2", "W3", "b3"):
         err = np.abs(v[k].cpu().numpy() - c["after_" + k]).max()
         assert err < 5e-5, (k, err)
+
+
+@pytest.mark.parametrize("ci", [0, 1])
+def test_a2c_matches_reference(golden, ci):
+    """A2C.update (a2c.py:247-288; case 1 with return_scaling) vs fixtures recorded from the reference A2C."""
+    from tianshou_marl_b200.algorithm import A2C, AdamOptimizerFactory, DiscreteActorPolicy
+    from tianshou_marl_b200.data import Batch, VectorReplayBuffer
+    from tianshou_marl_b200.utils import ActorCriticNet
+
+    g = golden("a2c.npz")
+    c = load_case(g, ci)
+    pre = f"p{ci}_"
+    net = ActorCriticNet(c["O"], c["H"], c["nA"]).load_arrays(c["W1"], c["b1"], c["W2"], c["b2"], c["W3"], c["b3"])
+    pol = DiscreteActorPolicy(actor=net)
+    alg = A2C(policy=pol, critic=net, optim=AdamOptimizerFactory(lr=c["lr"]), vf_coef=c["cfg"]["vf_coef"], ent_coef=c["cfg"]["ent_coef"],
+              max_grad_norm=c["max_norm"] or None, gamma=c["gamma"], gae_lambda=c["lam"], return_scaling=(ci == 1), minibatch_order="numpy")
+    if ci == 1:
+        alg.ret_rms.mean, alg.ret_rms.var = (float(x) for x in g[pre + "rms_before"][:2])
+        alg.ret_rms.count = int(g[pre + "rms_before"][2])
+    buf = VectorReplayBuffer(c["R"] * c["T"], c["R"], index_type="torch")
+    for t in range(c["T"]):
+        buf.add(Batch(obs=c["obs"][t], act=c["act"][t], rew=c["rew"][t], terminated=c["term"][t], truncated=c["trunc"][t],
+                      obs_next=c["obs_next"][t]))
+    pol.is_within_training_step = True
+    np.random.seed(c["seed"])
+    stats = alg.update(buf, c["bs"], c["repeat"])
+    em = lambda t: t.t().contiguous().view(-1).cpu().numpy()  # noqa: E731
+    assert np.allclose(em(alg._work["ret"]), c["returns"], rtol=2e-5, atol=2e-5)
+    assert np.allclose(em(alg._work["adv"]), c["adv"], rtol=2e-5, atol=2e-5)
+    seq = alg.last_sequences
+    assert stats.gradient_steps == len(c["loss_seq"])
+    for k, ref in (("loss", "loss_seq"), ("clip", "clip_seq"), ("vf", "vf_seq"), ("ent", "ent_seq")):
+        assert np.allclose(seq[k], c[ref], rtol=2e-4, atol=2e-5), (k, np.abs(seq[k] - c[ref]).max())
+    v = net.named_views()
+    for k in ("W1", "b1", "W2", "b2", "W3", "b3"):
+        err = np.abs(v[k].cpu().numpy() - c["after_" + k]).max()
+        assert err < 5e-5, (k, err)

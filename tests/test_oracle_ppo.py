@@ -80,3 +80,24 @@ def test_oracle_matches_reference_ppo_return_scaling(golden, ci):
     _, ret_plain, _, _ = oppo.preprocess(net, f["obs"], f["obs_next"], f["act"], f["rew"], f["term"], f["trunc"], c["indices"],
                                          c["unfinished"], c["gamma"], c["lam"], c["probs"])
     assert not np.allclose(ret_plain, c["returns"], rtol=1e-3, atol=1e-3)
+
+
+@pytest.mark.parametrize("ci", [0, 1])
+def test_oracle_matches_reference_a2c(golden, ci):
+    """A2C (a2c.py:247-288; case 1 with return_scaling): fixtures from the reference A2C in tests/golden/a2c.npz."""
+    g = golden("a2c.npz")
+    c = load_case(g, ci)
+    pre = f"p{ci}_"
+    net = oppo.Net(c["W1"], c["b1"], c["W2"], c["b2"], c["W3"], c["b3"], c["nA"])
+    f = c["flat"]
+    rms = dict(zip(("mean", "var", "count"), (float(x) for x in g[pre + "rms_before"]))) if ci == 1 else None
+    v_s, ret, adv, _ = oppo.preprocess(net, f["obs"], f["obs_next"], f["act"], f["rew"], f["term"], f["trunc"], c["indices"],
+                                       c["unfinished"], c["gamma"], c["lam"], c["probs"], ret_rms=rms)
+    assert np.allclose(ret, c["returns"], rtol=2e-5, atol=2e-5) and np.allclose(adv, c["adv"], rtol=2e-5, atol=2e-5)
+    cfg = dict(c["cfg"], a2c=True)
+    log = oppo.update_with_orders(net, f["obs"], f["act"], c["adv"], c["returns"], np.zeros_like(c["adv"]), c["v_s"], cfg, c["orders"],
+                                  c["bs"], c["lr"], c["max_norm"], c["probs"])
+    for k, ref in (("loss", "loss_seq"), ("clip", "clip_seq"), ("vf", "vf_seq"), ("ent", "ent_seq")):
+        assert np.allclose(log[k], c[ref], rtol=1e-4, atol=1e-5), (k, np.abs(np.array(log[k]) - c[ref]).max())
+    for k, p in zip(("W1", "b1", "W2", "b2", "W3", "b3"), net.p):
+        assert np.allclose(p.detach().numpy(), c["after_" + k], rtol=0, atol=2e-5), (k, np.abs(p.detach().numpy() - c["after_" + k]).max())

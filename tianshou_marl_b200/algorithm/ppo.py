@@ -420,3 +420,18 @@ def ppo_smoke() -> None:
         lg, v = onet.forward(obs.cpu())
     assert torch.allclose(o["logits"].cpu(), lg, rtol=1e-4, atol=1e-5), "policy forward mismatch"
     assert torch.allclose(o["value"].cpu(), v, rtol=1e-4, atol=1e-5), "value forward mismatch"
+
+
+class A2C(PPO):
+    """Advantage actor-critic (reference tianshou/algorithm/modelfree/a2c.py:154-288): the PPO machinery with the plain
+    policy-gradient epilogue of the fused minibatch kernels -- actor_loss = -mean(log pi(a | s) * adv), vf_loss =
+    mean((returns - value)^2), loss = actor_loss + vf_coef * vf_loss - ent_coef * entropy -- no ratio, no clipping, no
+    advantage normalisation, no logp_old.  Same preprocessing (critic values, GAE, optional return_scaling)."""
+
+    def __init__(self, *, policy: DiscreteActorPolicy, critic: Any = None, optim: AdamOptimizerFactory | None = None, vf_coef: float = 0.5,
+                 ent_coef: float = 0.01, max_grad_norm: float | None = None, gae_lambda: float = 0.95, max_batchsize: int = 256,
+                 gamma: float = 0.99, return_scaling: bool = False, **kwargs: Any) -> None:
+        super().__init__(policy=policy, critic=critic, optim=optim, vf_coef=vf_coef, ent_coef=ent_coef, max_grad_norm=max_grad_norm,
+                         gae_lambda=gae_lambda, max_batchsize=max_batchsize, gamma=gamma, return_scaling=return_scaling,
+                         advantage_normalization=False, value_clip=False, dual_clip=None, recompute_advantage=False, **kwargs)
+        self._cfg.plain_pg = 1
