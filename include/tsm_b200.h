@@ -85,15 +85,16 @@ int tsm_gae_tm(const float* v_s, const float* v_next, const float* rew,
                double gamma, double lam, float* adv_out, float* ret_out, tsm_stream_t stream);
 
 /* tsm_gae_tm with return scaling (A2C._add_returns_and_advantages with return_scaling=True, a2c.py:132-146): v_s and v_next
- * are multiplied by v_scale = sqrt(ret_rms.var + eps) on load, ret_out = unnormalised return / v_scale, adv_out is the
+ * are multiplied by v_scale = sqrt(ret_rms.var + eps) on load, ret_out = (unnormalised return - ret_shift) / v_scale (ret_shift
+ * = 0 for return_scaling, = ret_rms.mean for Reinforce's return_standardization, reinforce.py:305-309), adv_out is the
  * (unnormalised) advantage, and ret_sums[0..1] (device doubles, zeroed by the call) receive the sum and the sum of squares
  * of the unnormalised returns over all valid slots -- the batch moments RunningMeanStd.update needs
  * (tianshou/utils/statistics.py:96-114). */
 int tsm_gae_tm_scaled(const float* v_s, const float* v_next, const float* rew,
                       const uint8_t* terminated, const uint8_t* truncated,
                       int64_t size, int64_t n_rows, int64_t start, int64_t len,
-                      double gamma, double lam, double v_scale, float* adv_out, float* ret_out, double* ret_sums,
-                      tsm_stream_t stream);
+                      double gamma, double lam, double v_scale, double ret_shift, float* adv_out, float* ret_out,
+                      double* ret_sums, tsm_stream_t stream);
 
 /* critic(obs_next) from the values the policy forward stored at collect time (time-major [size][n_rows], valid slots
  * (start + j) % size, j < len): v_next[slot][row] = value[next slot][row] where obs_next IS the next stored obs (row not

@@ -36,7 +36,7 @@ class Net:
         h = F.relu(F.linear(x, W1, b1))
         h = F.relu(F.linear(h, W2, b2))
         o = F.linear(h, W3, b3)
-        return o[:, : self.n_act], o[:, self.n_act]
+        return o[:, : self.n_act], (o[:, self.n_act] if o.shape[1] > self.n_act else torch.zeros(o.shape[0]))  # (actor-only net: no value row)
 
     def flat(self) -> np.ndarray:
         return np.concatenate([x.detach().numpy().reshape(-1) for x in self.p])
@@ -198,3 +198,33 @@ def update(net: Net, store: dict, adv: np.ndarray, ret: np.ndarray, batch_size: 
     orders = [np.random.permutation(len(adv)) for _ in range(repeat)]
     update_with_orders(net, obs, store["act"], adv.astype(np.float32), ret.astype(np.float32), logp_old, v_old.numpy(),
                        dict(adv_norm=True), orders, batch_size, lr, 0.0)
+
+
+def reinforce_returns(rew, term, trunc, indices, unfinished, gamma, ret_rms: dict | None = None, standardize: bool = False):
+    """DiscountedReturnComputation.add_discounted_returns (reinforce.py:297-312): lambda = 1 returns whose truncated /
+    unfinished ends bootstrap with ret_rms.mean; v_s = roll(masked v_s_, 1) as in algorithm_base.py:710."""
+    mean = ret_rms["mean"] if ret_rms is not None else 0.0
+    v_n = np.full(len(rew), mean, np.float64)
+    v_s = np.roll(v_n * (1.0 - np.asarray(term, np.float64)), 1)
+    ret_u, _ = _gae(rew, term, trunc, indices, unfinished, v_n, v_s, gamma, 1.0)
+    if standardize:
+        ret = (ret_u - ret_rms["mean"]) / np.sqrt(ret_rms["var"] + 1e-8)
+        rms_update(ret_rms, ret_u)
+        return ret
+    return ret_u
+
+
+def reinforce_update(net: Net, obs, act_, ret, orders: list[np.ndarray], batch_size: int, lr: float) -> list[float]:
+    """Reinforce._update_with_batch (reinforce.py:362-382): loss = -(log pi(a | s) * return).mean(), Adam, no clipping."""
+    T = lambda a, dt=torch.float32: torch.from_numpy(np.ascontiguousarray(a)).to(dt)  # noqa: E731
+    obs, ret, act_t = T(obs), T(ret), T(act_)
+    losses = []
+    for order in orders:
+        for s_, e_ in split_bounds(len(ret), batch_size, True):
+            ix = torch.from_numpy(np.asarray(order[s_:e_], np.int64))
+            logits, _ = net.forward(obs[ix])
+            loss = -(log_softmax_dist(logits, False).log_prob(act_t[ix]) * ret[ix]).mean()
+            loss.backward()
+            adam_step(net, lr, 0.0)
+            losses.append(float(loss))
+    return losses

@@ -33,3 +33,22 @@ def load_case(g, ci):
     rs = np.random.RandomState(seed)
     c["orders"] = [rs.permutation(B) for _ in range(repeat)]
     return c
+
+
+def load_reinforce(g, ci):
+    pre = f"p{ci}_"
+    R, T, O, H, nA, bs, repeat, std, seed = (int(v) for v in g[pre + "cfg"])
+    lr, gamma = (float(v) for v in g[pre + "hyper"])
+    c = dict(R=R, T=T, O=O, H=H, nA=nA, bs=bs, repeat=repeat, std=bool(std), seed=seed, lr=lr, gamma=gamma)
+    for k in ("W1", "b1", "W2", "b2", "W3", "b3", "after_W1", "after_b1", "after_W2", "after_b2", "after_W3", "after_b3", "obs", "act", "rew",
+              "term", "trunc", "obs_next", "returns", "loss_seq", "rms_before", "rms_after"):
+        c[k] = g[pre + k]
+    B = R * T
+    em = lambda a: np.swapaxes(a, 0, 1).reshape(B, *a.shape[2:])  # noqa: E731
+    c["flat"] = {k: em(c[k]) for k in ("obs", "act", "rew", "term", "trunc")}
+    last = np.arange(R) * T + T - 1
+    done = c["flat"]["term"] | c["flat"]["trunc"]
+    c["unfinished"] = last[~done[last]]
+    rs = np.random.RandomState(seed)
+    c["orders"] = [rs.permutation(B) for _ in range(repeat)]
+    return c

@@ -163,3 +163,90 @@ def gen_ppo(cases=None, fname: str = "ppo.npz") -> None:
 
 GENS = {"ppo": gen_ppo, "ppo_recompute": lambda: gen_ppo(PPO_RECOMPUTE_CASES, "ppo_recompute.npz"),
         "ppo_retscale": lambda: gen_ppo(PPO_RETSCALE_CASES, "ppo_retscale.npz"), "a2c": lambda: gen_ppo(A2C_CASES, "a2c.npz")}
+
+
+def gen_reinforce() -> None:
+    """Reinforce (reinforce.py:249-382) with an actor-only net; case 1 with return_standardization and a warmed ret_rms."""
+    import gymnasium as gym
+    import torch
+    from tianshou.algorithm import Reinforce
+    from tianshou.algorithm.modelfree.reinforce import DiscreteActorPolicy
+    from tianshou.algorithm.optim import AdamOptimizerFactory
+    from tianshou.data import Batch, VectorReplayBuffer
+    from tianshou.data.stats import SequenceSummaryStats
+    from tianshou.utils.net.common import Net
+    from tianshou.utils.net.discrete import DiscreteActor
+    from tianshou.utils.torch_utils import policy_within_training_step, torch_train_mode
+
+    out: dict[str, np.ndarray] = {}
+    cases = [dict(R=16, T=20, O=18, H=64, nA=5, bs=80, repeat=2, std=False, lr=1e-3, gamma=0.99),
+             dict(R=10, T=15, O=18, H=64, nA=5, bs=50, repeat=2, std=True, lr=1e-3, gamma=0.95)]
+    for ci, c in enumerate(cases):
+        R, T, O, H, nA = c["R"], c["T"], c["O"], c["H"], c["nA"]
+        rng = np.random.default_rng(300 + ci)
+        torch.manual_seed(50 + ci)
+        actor = DiscreteActor(preprocess_net=Net(state_shape=(O,), hidden_sizes=[H, H]), action_shape=nA, softmax_output=False)
+        for m in actor.modules():
+            if isinstance(m, torch.nn.Linear):
+                torch.nn.init.orthogonal_(m.weight)
+                torch.nn.init.normal_(m.bias, std=0.1)
+        policy = DiscreteActorPolicy(actor=actor, action_space=gym.spaces.Discrete(nA))
+        alg = Reinforce(policy=policy, gamma=c["gamma"], return_standardization=c["std"], optim=AdamOptimizerFactory(lr=c["lr"]))
+        pre = f"p{ci}_"
+
+        def params(prefix):
+            sd = {k: v.detach().cpu().numpy().copy() for k, v in actor.state_dict().items()}
+            pick = lambda suf: next(v for k, v in sd.items() if k.endswith(suf))  # noqa: E731
+            for name, suf in (("W1", "model.model.0.weight"), ("b1", "model.model.0.bias"), ("W2", "model.model.2.weight"),
+                              ("b2", "model.model.2.bias"), ("W3", "last.model.0.weight"), ("b3", "last.model.0.bias")):
+                out[pre + prefix + name] = pick(suf)
+
+        params("")
+        buf = VectorReplayBuffer(R * T, R)
+        obs = rng.normal(size=(R, O)).astype(np.float32)
+        store = {k: [] for k in ("obs", "act", "rew", "term", "trunc", "obs_next")}
+        for t in range(T):
+            act = rng.integers(0, nA, R)
+            rew = rng.normal(size=R).astype(np.float32).astype(np.float64)
+            trunc = np.full(R, (t + 1) % 5 == 0) & (rng.random(R) < 0.9)
+            term = (rng.random(R) < 0.05) & ~trunc
+            obs_next = (obs + rng.normal(size=(R, O)) * 0.3).astype(np.float32)
+            buf.add(Batch(obs=obs, act=act, rew=rew, terminated=term, truncated=trunc, obs_next=obs_next, info={}))
+            for k, v in zip(store, (obs, act, rew, term, trunc, obs_next)):
+                store[k].append(np.array(v))
+            obs = np.where((term | trunc)[:, None], rng.normal(size=(R, O)).astype(np.float32), obs_next)
+        for k, v in store.items():
+            out[pre + k] = np.stack(v)
+        seqs: list[list[float]] = []
+        orig = SequenceSummaryStats.from_sequence.__func__
+
+        def spy(cls, seq, _orig=orig, _seqs=seqs):
+            _seqs.append([float(x) for x in seq])
+            return _orig(cls, seq)
+
+        SequenceSummaryStats.from_sequence = classmethod(spy)
+        try:
+            np.random.seed(17 + ci)
+            with policy_within_training_step(alg.policy):
+                rms = alg.discounted_return_computation.ret_rms
+                if c["std"]:
+                    b0, i0 = buf.sample(0)
+                    alg._preprocess_batch(b0, buf, i0)
+                out[pre + "rms_before"] = np.array([float(rms.mean), float(rms.var), float(rms.count)])
+                batch, indices = buf.sample(0)
+                batch = alg._preprocess_batch(batch, buf, indices)
+                out[pre + "returns"] = np.asarray(batch.returns, np.float64).copy()
+                out[pre + "rms_after"] = np.array([float(rms.mean), float(rms.var), float(rms.count)])
+                with torch_train_mode(alg):
+                    alg._update_with_batch(batch, c["bs"], c["repeat"])
+        finally:
+            SequenceSummaryStats.from_sequence = classmethod(orig)
+        out[pre + "loss_seq"] = np.array(seqs[0])
+        params("after_")
+        out[pre + "cfg"] = np.array([R, T, O, H, nA, c["bs"], c["repeat"], int(c["std"]), 17 + ci], np.int64)
+        out[pre + "hyper"] = np.array([c["lr"], c["gamma"]])
+    out["n_cases"] = np.array(len(cases))
+    save("reinforce.npz", **out)
+
+
+GENS["reinforce"] = gen_reinforce

@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 import torch
 
-from _ppo_golden import load_case
+from _ppo_golden import load_case, load_reinforce
 
 pytestmark = pytest.mark.gpu
 
@@ -344,6 +344,39 @@ def test_a2c_matches_reference(golden, ci):
     assert stats.gradient_steps == len(c["loss_seq"])
     for k, ref in (("loss", "loss_seq"), ("clip", "clip_seq"), ("vf", "vf_seq"), ("ent", "ent_seq")):
         assert np.allclose(seq[k], c[ref], rtol=2e-4, atol=2e-5), (k, np.abs(seq[k] - c[ref]).max())
+    v = net.named_views()
+    for k in ("W1", "b1", "W2", "b2", "W3", "b3"):
+        err = np.abs(v[k].cpu().numpy() - c["after_" + k]).max()
+        assert err < 5e-5, (k, err)
+
+
+@pytest.mark.parametrize("ci", [0, 1])
+def test_reinforce_matches_reference(golden, ci):
+    """Reinforce.update (reinforce.py:249-382; case 1 with return_standardization and a warmed ret_rms) vs fixtures recorded from
+    the reference: Monte-Carlo returns, running statistics, every minibatch loss, final parameters."""
+    from tianshou_marl_b200.algorithm import AdamOptimizerFactory, DiscreteActorPolicy, Reinforce
+    from tianshou_marl_b200.data import Batch, VectorReplayBuffer
+    from tianshou_marl_b200.utils import ActorCriticNet
+
+    c = load_reinforce(golden("reinforce.npz"), ci)
+    net = ActorCriticNet(c["O"], c["H"], c["nA"], with_value=False).load_arrays(c["W1"], c["b1"], c["W2"], c["b2"], c["W3"], c["b3"])
+    pol = DiscreteActorPolicy(actor=net)
+    alg = Reinforce(policy=pol, gamma=c["gamma"], return_standardization=c["std"], optim=AdamOptimizerFactory(lr=c["lr"]), minibatch_order="numpy")
+    alg.ret_rms.mean, alg.ret_rms.var = (float(x) for x in c["rms_before"][:2])
+    alg.ret_rms.count = int(c["rms_before"][2])
+    buf = VectorReplayBuffer(c["R"] * c["T"], c["R"], index_type="torch")
+    for t in range(c["T"]):
+        buf.add(Batch(obs=c["obs"][t], act=c["act"][t], rew=c["rew"][t], terminated=c["term"][t], truncated=c["trunc"][t],
+                      obs_next=c["obs_next"][t]))
+    pol.is_within_training_step = True
+    np.random.seed(c["seed"])
+    stats = alg.update(buf, c["bs"], c["repeat"])
+    em = lambda t: t.t().contiguous().view(-1).cpu().numpy()  # noqa: E731
+    assert np.allclose(em(alg._work["ret"]), c["returns"], rtol=2e-5, atol=2e-5)
+    if c["std"]:
+        assert np.allclose([alg.ret_rms.mean, alg.ret_rms.var, alg.ret_rms.count], c["rms_after"], rtol=1e-5)
+    assert stats.gradient_steps == len(c["loss_seq"])
+    assert np.allclose(alg.last_sequences["loss"], c["loss_seq"], rtol=2e-4, atol=2e-5), np.abs(alg.last_sequences["loss"] - c["loss_seq"]).max()
     v = net.named_views()
     for k in ("W1", "b1", "W2", "b2", "W3", "b3"):
         err = np.abs(v[k].cpu().numpy() - c["after_" + k]).max()

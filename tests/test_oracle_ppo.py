@@ -5,7 +5,7 @@ import numpy as np
 import pytest
 
 from oracle import ppo as oppo
-from _ppo_golden import load_case
+from _ppo_golden import load_case, load_reinforce
 
 
 @pytest.mark.parametrize("ci", [0, 1, 2, 3])
@@ -101,3 +101,20 @@ def test_oracle_matches_reference_a2c(golden, ci):
         assert np.allclose(log[k], c[ref], rtol=1e-4, atol=1e-5), (k, np.abs(np.array(log[k]) - c[ref]).max())
     for k, p in zip(("W1", "b1", "W2", "b2", "W3", "b3"), net.p):
         assert np.allclose(p.detach().numpy(), c["after_" + k], rtol=0, atol=2e-5), (k, np.abs(p.detach().numpy() - c["after_" + k]).max())
+
+
+@pytest.mark.parametrize("ci", [0, 1])
+def test_oracle_matches_reference_reinforce(golden, ci):
+    """Reinforce (reinforce.py:249-382; case 1 with return_standardization): fixtures from the reference in reinforce.npz."""
+    c = load_reinforce(golden("reinforce.npz"), ci)
+    f = c["flat"]
+    rms = dict(zip(("mean", "var", "count"), (float(x) for x in c["rms_before"])))
+    ret = oppo.reinforce_returns(f["rew"], f["term"], f["trunc"], np.arange(c["R"] * c["T"]), c["unfinished"], c["gamma"], rms, c["std"])
+    assert np.allclose(ret, c["returns"], rtol=1e-9, atol=1e-9)
+    if c["std"]:
+        assert np.allclose([rms["mean"], rms["var"], rms["count"]], c["rms_after"], rtol=1e-9)
+    net = oppo.Net(c["W1"], c["b1"], c["W2"], c["b2"], c["W3"], c["b3"], c["nA"])
+    losses = oppo.reinforce_update(net, f["obs"], f["act"], c["returns"], c["orders"], c["bs"], c["lr"])
+    assert np.allclose(losses, c["loss_seq"], rtol=1e-4, atol=1e-5), np.abs(np.array(losses) - c["loss_seq"]).max()
+    for k, p in zip(("W1", "b1", "W2", "b2", "W3", "b3"), net.p):
+        assert np.allclose(p.detach().numpy(), c["after_" + k], rtol=0, atol=2e-5), k

@@ -103,7 +103,7 @@ _SIGS = {
     "tsm_gae_flat": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_i64, c_i64, c_f64, c_f64,
                              c_vp, c_vp, c_vp, c_sz, c_vp]),
     "tsm_gae_tm": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_f64, c_f64, c_vp, c_vp, c_vp]),
-    "tsm_gae_tm_scaled": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_f64, c_f64, c_f64, c_vp, c_vp, c_vp, c_vp]),
+    "tsm_gae_tm_scaled": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_f64, c_f64, c_f64, c_f64, c_vp, c_vp, c_vp, c_vp]),
     "tsm_values_next_prepare": (c_i32, [c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp]),
     "tsm_buf_reset": (c_i32, [c_vp, c_i32, c_vp]),
     "tsm_buf_add": (c_i32, [c_vp] * 10 + [c_i64] + [c_vp] * 5),

@@ -103,7 +103,8 @@ class PPO:
         assert 0.0 <= gamma <= 1.0 and 0.0 <= gae_lambda <= 1.0
         if critic is not None and critic is not policy.actor:
             raise NotImplementedError("separate critic network: use the CTDE path")
-        if policy.actor.value_index < 0:
+        self._mc_returns = bool(getattr(self, "_mc_returns_flag", False))  # Reinforce: Monte-Carlo returns, no critic
+        if policy.actor.value_index < 0 and not self._mc_returns:
             raise ValueError("the shared actor-critic net needs a value head (with_value=True)")
         if minibatch_order not in ("device", "numpy"):
             raise ValueError("minibatch_order must be 'device' or 'numpy'")
@@ -232,7 +233,22 @@ class PPO:
         reuse = (self.reuse_rollout and lockstep and rows is None and "value" in st and "logp" in st and net.value_index >= 0
                  and getattr(self.policy, "actor", None) is net and buffer._policy_version is not None
                  and buffer._policy_version == net.param_version)
-        if reuse:
+        if self._mc_returns:
+            # Reinforce (reinforce.py:297-312): no critic.  The reference passes v_s_ = ret_rms.mean everywhere and v_s = roll(v_s_);
+            # in the lambda = 1 recurrence the two cancel except where an episode ends (done, or the last collected slot), where
+            # the return bootstraps with gamma * ret_rms.mean * (1 - terminated).  So: v_s = 0, v_n = mean at those slots only.
+            reuse = False
+            v_s.zero_()
+            boot = float(self.ret_rms.mean)
+            if self.return_scaling:  # the scaled GAE kernel multiplies the values by sqrt(var + eps) on load: pre-divide
+                boot /= float(np.sqrt(self.ret_rms.var + self._eps))
+            if boot == 0.0:
+                v_n.zero_()
+            else:
+                torch.mul(st["done"].to(torch.float32), boot, out=v_n)
+                v_n[((buffer._lockstep_ins if lock_len == size else 0) + lock_len - 1) % size].fill_(boot)
+            logp.zero_()
+        elif reuse:
             tk = _lib.t_start("critic_forward")
             v_s, logp = st["value"], st["logp"]
             next_values(v_s, True)
@@ -252,7 +268,15 @@ class PPO:
 
         def run_gae(v_cur: torch.Tensor) -> None:
             """compute_episodic_return over the stored rollout -> adv, ret (algorithm_base.py:651-717)."""
-            if lockstep and self.return_scaling:
+            if lockstep and self._mc_returns and self.return_scaling:  # return_standardization: (ret - mean) / sqrt(var + eps)
+                sums_rs = self._buf("ret_sums", (2,), torch.float64)
+                gae_time_major(v_cur, v_n, st["rew"], st["terminated"], st["truncated"], buffer._lockstep_ins if flat_ctx["full"] else 0,
+                               flat_ctx["len"], self.gamma, 1.0, adv, ret, v_scale=float(np.sqrt(self.ret_rms.var + self._eps)),
+                               ret_sums=sums_rs, ret_shift=float(self.ret_rms.mean))
+                s1, s2 = (float(x) for x in sums_rs.cpu().numpy())
+                n_el = flat_ctx["len"] * R
+                self.ret_rms.update_from_moments(s1 / n_el, max(s2 / n_el - (s1 / n_el) ** 2, 0.0), n_el)
+            elif lockstep and self.return_scaling:
                 scale = float(np.sqrt(self.ret_rms.var + self._eps))
                 sums_rs = self._buf("ret_sums", (2,), torch.float64)
                 gae_time_major(v_cur, v_n, st["rew"], st["terminated"], st["truncated"], buffer._lockstep_ins if flat_ctx["full"] else 0,
@@ -308,7 +332,7 @@ class PPO:
         stats = self._buf("mb_stats", (repeat * n_mb, 2))
         sums = self._buf("loss_sums", (repeat * n_mb, 4), torch.float64)
         sums.zero_()
-        pb = _lib.TsmPpoBatch(obs=P(st["obs"]), act=P(st["act"]), adv=P(adv), ret=P(ret), logp_old=P(logp), v_old=P(v_s),
+        pb = _lib.TsmPpoBatch(obs=P(st["obs"]), act=P(st["act"]), adv=P(ret if self._mc_returns else adv), ret=P(ret), logp_old=P(logp), v_old=P(v_s),
                               indices=None, size=size, n_rows=R, start=start, len=lock_len, perm_key=0, perm_n=0, records=None)
         if net.engine == "tc":  # one 96-byte record per stored row: the minibatch kernels gather 3 sectors / 1 page per row
             tk = _lib.t_start("pack_records")
@@ -434,4 +458,20 @@ class A2C(PPO):
         super().__init__(policy=policy, critic=critic, optim=optim, vf_coef=vf_coef, ent_coef=ent_coef, max_grad_norm=max_grad_norm,
                          gae_lambda=gae_lambda, max_batchsize=max_batchsize, gamma=gamma, return_scaling=return_scaling,
                          advantage_normalization=False, value_clip=False, dual_clip=None, recompute_advantage=False, **kwargs)
+        self._cfg.plain_pg = 1
+
+
+class Reinforce(PPO):
+    """REINFORCE (reference tianshou/algorithm/modelfree/reinforce.py:249-382): Monte-Carlo discounted returns (lambda = 1, no
+    critic; truncated / unfinished episodes bootstrap with ret_rms.mean, :297-304), optional return standardisation with the
+    running mean / std (:305-309), loss = -mean(log pi(a | s) * return) through the plain policy-gradient epilogue of the fused
+    minibatch kernels.  The net is actor-only (ActorCriticNet(..., with_value=False)).  Lock-step rollout buffers only."""
+
+    _mc_returns_flag = True
+
+    def __init__(self, *, policy: DiscreteActorPolicy, gamma: float = 0.99, return_standardization: bool = False,
+                 optim: AdamOptimizerFactory | None = None, **kwargs: Any) -> None:
+        super().__init__(policy=policy, critic=None, optim=optim, vf_coef=0.0, ent_coef=0.0, max_grad_norm=None, gae_lambda=1.0, gamma=gamma,
+                         return_scaling=return_standardization, advantage_normalization=False, value_clip=False, dual_clip=None,
+                         recompute_advantage=False, **kwargs)
         self._cfg.plain_pg = 1

@@ -60,7 +60,7 @@ def gae_flat(v_s: torch.Tensor | None, v_next: torch.Tensor | None, rew: torch.T
 def gae_time_major(v_s: torch.Tensor | None, v_next: torch.Tensor | None, rew: torch.Tensor, terminated: torch.Tensor,
                    truncated: torch.Tensor, start: int, length: int, gamma: float, gae_lambda: float,
                    adv_out: torch.Tensor | None = None, ret_out: torch.Tensor | None = None, v_scale: float | None = None,
-                   ret_sums: torch.Tensor | None = None) -> tuple[torch.Tensor, torch.Tensor]:
+                   ret_sums: torch.Tensor | None = None, ret_shift: float = 0.0) -> tuple[torch.Tensor, torch.Tensor]:
     """GAE over the device buffer's native [size][rows] float32 layout (tsm_gae_tm).  With v_scale (return_scaling,
     a2c.py:132-146) values are un-normalised on load, the returned returns are normalised again and ret_sums (2 device
     doubles) receives sum / sum of squares of the un-normalised returns (tsm_gae_tm_scaled)."""
@@ -71,8 +71,8 @@ def gae_time_major(v_s: torch.Tensor | None, v_next: torch.Tensor | None, rew: t
     u8 = lambda t: t.view(torch.uint8) if t.dtype == torch.bool else t  # noqa: E731
     if v_scale is not None:
         _lib.check(_lib.lib().tsm_gae_tm_scaled(P(v_s), P(v_next), P(rew), P(u8(terminated)), P(u8(truncated)), size, rows,
-                                                int(start), int(length), float(gamma), float(gae_lambda), float(v_scale), P(adv), P(ret),
-                                                P(ret_sums), _lib.stream_ptr()))
+                                                int(start), int(length), float(gamma), float(gae_lambda), float(v_scale), float(ret_shift), P(adv),
+                                                P(ret), P(ret_sums), _lib.stream_ptr()))
         return ret, adv
     _lib.check(_lib.lib().tsm_gae_tm(P(v_s), P(v_next), P(rew), P(u8(terminated)), P(u8(truncated)), size, rows,
                                      int(start), int(length), float(gamma), float(gae_lambda), P(adv), P(ret),

@@ -247,14 +247,14 @@ __global__ void __launch_bounds__(THREADS) gae_flat_kernel(
 constexpr int TM_THREADS = 128;
 constexpr int TM_UNROLL = 8;
 
-// SCALED (return_scaling, a2c.py:132-146): values enter multiplied by v_scale = sqrt(ret_rms.var + eps), returns leave divided by
-// it, and the sum / sum of squares of the UNNORMALISED returns go to ret_sums[0..1] (what RunningMeanStd.update needs).
+// SCALED (return_scaling, a2c.py:132-146; return_standardization, reinforce.py:297-312): values enter multiplied by v_scale =
+// sqrt(ret_rms.var + eps), returns leave as (return - ret_shift) / v_scale, and the sum / sum of squares of the UNNORMALISED returns go to ret_sums[0..1] (what RunningMeanStd.update needs).
 template <bool SCALED>
 __global__ void __launch_bounds__(TM_THREADS) gae_tm_kernel(
     const float* __restrict__ v_s, const float* __restrict__ v_next, const float* __restrict__ rew,
     const uint8_t* __restrict__ term, const uint8_t* __restrict__ trunc, int64_t size, int64_t R, int64_t start,
     int64_t len, double gamma, double gl, float* __restrict__ adv_out, float* __restrict__ ret_out, double v_scale,
-    double* __restrict__ ret_sums) {
+    double ret_shift, double* __restrict__ ret_sums) {
     const int64_t r_raw = (int64_t)blockIdx.x * TM_THREADS + threadIdx.x;
     const bool live = r_raw < R;
     if (!SCALED && !live) return;
@@ -296,7 +296,7 @@ __global__ void __launch_bounds__(TM_THREADS) gae_tm_kernel(
             if (SCALED) {
                 acc_s += ru;
                 acc_q = fma(ru, ru, acc_q);
-                if (ret_out) ret_out[off[u]] = (float)(ru / v_scale);
+                if (ret_out) ret_out[off[u]] = (float)((ru - ret_shift) / v_scale);
             } else {
                 if (ret_out) ret_out[off[u]] = (float)ru;
             }
@@ -428,15 +428,15 @@ extern "C" int tsm_gae_tm(const float* v_s, const float* v_next, const float* re
     const int64_t blocks = ceil_div(n_rows, TM_THREADS);
     TSM_REQUIRE(blocks < (int64_t)INT32_MAX, "n_rows too large");
     gae_tm_kernel<false><<<(unsigned)blocks, TM_THREADS, 0, as_stream(stream)>>>(
-        v_s, v_next, rew, terminated, truncated, size, n_rows, start, len, gamma, gamma * lam, adv_out, ret_out, 1.0, nullptr);
+        v_s, v_next, rew, terminated, truncated, size, n_rows, start, len, gamma, gamma * lam, adv_out, ret_out, 1.0, 0.0, nullptr);
     TSM_LAUNCH_CHECK();
     return TSM_OK;
 }
 
 extern "C" int tsm_gae_tm_scaled(const float* v_s, const float* v_next, const float* rew, const uint8_t* terminated,
                                  const uint8_t* truncated, int64_t size, int64_t n_rows, int64_t start, int64_t len,
-                                 double gamma, double lam, double v_scale, float* adv_out, float* ret_out, double* ret_sums,
-                                 tsm_stream_t stream) {
+                                 double gamma, double lam, double v_scale, double ret_shift, float* adv_out, float* ret_out,
+                                 double* ret_sums, tsm_stream_t stream) {
     TSM_REQUIRE(size > 0 && n_rows >= 0, "size > 0, n_rows >= 0");
     TSM_REQUIRE(len >= 0 && len <= size && start >= 0 && start < size, "0 <= len <= size, 0 <= start < size");
     TSM_REQUIRE(v_scale > 0.0, "v_scale > 0");
@@ -447,7 +447,7 @@ extern "C" int tsm_gae_tm_scaled(const float* v_s, const float* v_next, const fl
     const int64_t blocks = ceil_div(n_rows, TM_THREADS);
     TSM_REQUIRE(blocks < (int64_t)INT32_MAX, "n_rows too large");
     gae_tm_kernel<true><<<(unsigned)blocks, TM_THREADS, 0, as_stream(stream)>>>(
-        v_s, v_next, rew, terminated, truncated, size, n_rows, start, len, gamma, gamma * lam, adv_out, ret_out, v_scale, ret_sums);
+        v_s, v_next, rew, terminated, truncated, size, n_rows, start, len, gamma, gamma * lam, adv_out, ret_out, v_scale, ret_shift, ret_sums);
     TSM_LAUNCH_CHECK();
     return TSM_OK;
 }
