@@ -73,3 +73,44 @@ def test_ctde_per_row_advantage_differs_from_broadcast():
         assert np.isfinite(r["actor_loss"]) and np.isfinite(r["critic_loss"])
         res.append(actor.flat.detach().clone())
     assert not torch.equal(res[0], res[1])
+
+
+@pytest.mark.gpu
+def test_simultaneous_trainer_routes_joint_batch_to_ctde_policies():
+    """SimultaneousTrainer.train_step (training_coordinator.py:292-339) over real CTDEPolicy objects: each agent's policy learns
+    from its slice of the joint batch with the joint global state attached; result == calling learn() by hand."""
+    import types
+
+    from tianshou_marl_b200.algorithm import AdamOptimizerFactory
+    from tianshou_marl_b200.algorithm.ctde import CTDEPolicy, CentralizedCritic, DecentralizedActor
+    from tianshou_marl_b200.algorithm.training_coordinator import SimultaneousTrainer
+    from tianshou_marl_b200.data import Batch
+
+    n, O, A = 64, 18, 3
+    rng = np.random.default_rng(1)
+    g_obs = rng.normal(size=(n, A * O)).astype(np.float32)
+    g_next = rng.normal(size=(n, A * O)).astype(np.float32)
+
+    def mk():
+        pols = {}
+        for i in range(2):
+            actor, critic = DecentralizedActor(O, 5, 64, seed=10 + i, orthogonal=True), CentralizedCritic(A * O, A, 64, seed=20 + i, orthogonal=True)
+            pols[f"agent_{i}"] = CTDEPolicy(actor, critic, AdamOptimizerFactory(lr=1e-3), AdamOptimizerFactory(lr=1e-3), enable_global_info=True)
+        return pols
+
+    def agent_batch(i):
+        r = np.random.default_rng(100 + i)
+        return Batch(obs=r.normal(size=(n, O)).astype(np.float32), act=r.integers(0, 5, n), rew=r.normal(size=n).astype(np.float32),
+                     obs_next=r.normal(size=(n, O)).astype(np.float32), terminated=r.random(n) < 0.1)
+
+    pols = mk()
+    joint = Batch(agent_0=agent_batch(0), agent_1=agent_batch(1))
+    joint.__dict__["global_obs"], joint.__dict__["global_obs_next"] = g_obs, g_next
+    pm = types.SimpleNamespace(mode="independent", agents=list(pols), policies=pols)
+    out = SimultaneousTrainer(pm, agent_train_freq={"agent_1": 2}).train_step(joint)
+    assert set(out) == {"agent_0"} and set(out["agent_0"]) == {"actor_loss", "critic_loss"}
+    ref = mk()
+    b0 = agent_batch(0)
+    b0.__dict__["global_obs"], b0.__dict__["global_obs_next"] = g_obs, g_next
+    want = ref["agent_0"].learn(b0)
+    assert np.allclose([out["agent_0"]["actor_loss"], out["agent_0"]["critic_loss"]], [want["actor_loss"], want["critic_loss"]], rtol=1e-5)

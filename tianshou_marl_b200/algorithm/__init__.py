@@ -1,8 +1,9 @@
 from .ctde import CentralizedCritic, CTDEPolicy, DecentralizedActor, GlobalStateConstructor
 from .multiagent import FlexibleMultiAgentPolicyManager
 from .ppo import A2C, PPO, AdamOptimizerFactory, DiscreteActorPolicy, Reinforce, ppo_smoke
+from .training_coordinator import SimultaneousTrainer
 from .returns import compute_episodic_return, episode_mc_return_to_go, gae_flat, gae_time_major
 
 __all__ = ["compute_episodic_return", "episode_mc_return_to_go", "gae_flat", "gae_time_major", "PPO", "A2C", "Reinforce", "AdamOptimizerFactory",
            "DiscreteActorPolicy", "ppo_smoke", "FlexibleMultiAgentPolicyManager", "CTDEPolicy", "GlobalStateConstructor",
-           "DecentralizedActor", "CentralizedCritic"]
+           "DecentralizedActor", "CentralizedCritic", "SimultaneousTrainer"]
