@@ -95,6 +95,9 @@ __device__ __forceinline__ float adam_elem(float p, float g, float& m, float& v,
 // used by the tcgen05 engine's persistent epoch kernel, where every CTA steps all parameters.
 __device__ __forceinline__ float adam_elem_fast(float p, float g, float& m, float& v, float coef, float step_size, float inv_bc2_sqrt,
                                                 float beta1, float beta2, float eps) {
+#ifdef TSM_TC_EXACT_ADAM  // instrumented builds only (tools/tc_error_budget.py)
+    return adam_elem(p, g, m, v, coef, step_size, 1.f / inv_bc2_sqrt, beta1, beta2, eps);
+#endif
     const float gi = g * coef;
     m = m + (gi - m) * (1.f - beta1);
     v = fmaf(gi * gi, 1.f - beta2, v * beta2);

@@ -24,6 +24,14 @@
 // are coalesced.
 #pragma once
 
+// Instrumented builds only (tools/tc_error_budget.py separates the tcgen05 engine's error sources): -DTSM_TC_EXACT_LOSS keeps
+// the IEEE loss math of the fp32 engine, -DTSM_TC_EXACT_ADAM the IEEE optimizer arithmetic.  The shipped library has neither.
+#ifdef TSM_TC_EXACT_LOSS
+constexpr bool TC_FAST_LOSS = false;
+#else
+constexpr bool TC_FAST_LOSS = true;
+#endif
+
 constexpr int TC_THREADS = 128;
 constexpr int TC_ROWS = 128;
 constexpr int TC_H = 64;
@@ -373,7 +381,7 @@ __global__ void __launch_bounds__(TC_THREADS) tc_forward_kernel(TcFwdArgs a) {
                         if (j < a.out_dim) a.out[dst * a.out_dim + j] = z[j];
                 }
             } else {
-                const Soft sm = softmax_row<true>(z, a.n_act);
+                const Soft sm = softmax_row<TC_FAST_LOSS>(z, a.n_act);
                 int act = 0;
                 if (a.mode == 1) {
                     const int64_t key = dst + a.rng_row0;
@@ -601,7 +609,7 @@ __global__ void __launch_bounds__(TC_THREADS) tc_ppo_minibatch_kernel(TcPpoArgs 
 #pragma unroll
             for (int j = 0; j < OUTP; ++j) dz[j] = z[j] * inv_n;
         } else {
-            rl = row_loss<true>(z, a.n_act, a.value_index, d_act, d_adv, d_ret, d_logp_old, d_v_old, mean, rstd, a.cfg, inv_n, dz);
+            rl = row_loss<TC_FAST_LOSS>(z, a.n_act, a.value_index, d_act, d_adv, d_ret, d_logp_old, d_v_old, mean, rstd, a.cfg, inv_n, dz);
         }
         if (valid) {
             f_clip += rl.clip;
@@ -926,7 +934,7 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
             tc_forward_tile(smem, s, xoff, trow);
             float z[OUTP], dz[OUTP];
             tc_read_out(s, z);
-            const RowLoss rl = row_loss<true>(z, a.n_act, a.value_index, d_act, d_adv, d_ret, d_logp_old, d_v_old, mean, rstd, a.cfg, inv_n, dz);
+            const RowLoss rl = row_loss<TC_FAST_LOSS>(z, a.n_act, a.value_index, d_act, d_adv, d_ret, d_logp_old, d_v_old, mean, rstd, a.cfg, inv_n, dz);
             if (valid) { f_clip += rl.clip; f_vf += rl.vf; f_ent += rl.ent; }
             if ((it & 15) == 15) {
                 l_clip += (double)f_clip; l_vf += (double)f_vf; l_ent += (double)f_ent;
