@@ -52,3 +52,49 @@ def load_reinforce(g, ci):
     rs = np.random.RandomState(seed)
     c["orders"] = [rs.permutation(B) for _ in range(repeat)]
     return c
+
+
+def large_inputs(seed, R, T, O, nA):
+    """Synthetic rollout of the C2-scale fixtures (tests/golden/ppo_large.npz), regenerated from a frozen numpy RandomState
+    stream by both the generator (make_golden_large.py) and the tests, so that only the reference's OUTPUTS are committed.
+    MPE-like: every row truncates every 25 steps at its own phase, terminates with p = 0.01; returns [T][R] arrays."""
+    rs = np.random.RandomState(seed)
+    obs = rs.standard_normal((R, O)).astype(np.float32)
+    phase = rs.randint(0, 25, R)
+    out = {k: [] for k in ("obs", "act", "rew", "term", "trunc", "obs_next")}
+    for t in range(T):
+        act = rs.randint(0, nA, R)
+        rew = rs.standard_normal(R).astype(np.float32)
+        trunc = (t + phase) % 25 == 24
+        term = (rs.random_sample(R) < 0.01) & ~trunc
+        obs_next = (obs + 0.3 * rs.standard_normal((R, O))).astype(np.float32)
+        for k, v in zip(out, (obs, act, rew, term, trunc, obs_next)):
+            out[k].append(np.array(v))
+        fresh = rs.standard_normal((R, O)).astype(np.float32)
+        obs = np.where((term | trunc)[:, None], fresh, obs_next)
+    out = {k: np.stack(v) for k, v in out.items()}
+    out["checksum"] = np.array([float(out["obs"].astype(np.float64).sum()), float(out["act"].sum()), float(out["rew"].astype(np.float64).sum()),
+                                float(out["term"].sum()), float(out["trunc"].sum()), float(out["obs_next"].astype(np.float64).sum())])
+    return out
+
+
+def load_large(g, ci):
+    """One case of ppo_large.npz: reference outputs + the regenerated inputs (checksum-verified)."""
+    pre = f"p{ci}_"
+    R, T, O, H, nA, bs, repeat, seed, in_seed = (int(v) for v in g[pre + "cfg"])
+    eps_clip, dual_clip, vf_coef, ent_coef, value_clip, adv_norm, max_norm, lr, gamma, lam = (float(v) for v in g[pre + "hyper"])
+    c = dict(R=R, T=T, O=O, H=H, nA=nA, bs=bs, repeat=repeat, seed=seed, lr=lr, gamma=gamma, lam=lam, max_norm=max_norm,
+             cfg=dict(eps_clip=eps_clip, dual_clip=dual_clip, vf_coef=vf_coef, ent_coef=ent_coef, value_clip=bool(value_clip), adv_norm=bool(adv_norm)))
+    x = large_inputs(in_seed, R, T, O, nA)
+    assert np.array_equal(x["checksum"], g[pre + "checksum"]), "regenerated inputs differ from the recorded ones"
+    c.update({k: x[k] for k in ("obs", "act", "rew", "term", "trunc", "obs_next")})
+    for k in ("W1", "b1", "W2", "b2", "Wa", "ba", "Wv", "bv"):
+        c[k] = g[pre + k]
+        c["after_" + k] = g[pre + "after_" + k]
+    for k in ("loss_seq", "clip_seq", "vf_seq", "ent_seq", "sample_idx", "v_s", "returns", "adv", "logp_old"):
+        c[k] = g[pre + k]
+    c["W3"] = np.concatenate([c["Wa"], c["Wv"]], 0)
+    c["b3"] = np.concatenate([c["ba"], c["bv"]], 0)
+    c["after_W3"] = np.concatenate([c["after_Wa"], c["after_Wv"]], 0)
+    c["after_b3"] = np.concatenate([c["after_ba"], c["after_bv"]], 0)
+    return c
