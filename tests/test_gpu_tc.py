@@ -280,3 +280,66 @@ def test_epoch_slot_table_and_launch_chain_agree(n_mb, mb, monkeypatch):
         diff = (res[variant][0] - res["chain"][0]).abs()
         assert (diff < 2e-5).float().mean().item() > 0.995 and diff.max().item() < 2e-3 * n_mb + 1e-6, (variant, diff.max())
         assert np.allclose(res[variant][1], res["chain"][1], rtol=1e-4, atol=1e-3)
+
+
+# ---- the benched engine against the REFERENCE fixtures (tolerances: DESIGN.md 3.1 "error budget", profiles/r02_tc_error_budget.json) ----
+TC_REF_TOL = dict(loss_rel=2e-2, loss_abs=4e-3, param_abs=2.5e-3)
+
+
+def _mk_case(c, engine):
+    from tianshou_marl_b200.algorithm import PPO, AdamOptimizerFactory, DiscreteActorPolicy
+    from tianshou_marl_b200.data import Batch, VectorReplayBuffer
+    from tianshou_marl_b200.utils import ActorCriticNet
+
+    net = ActorCriticNet(c["O"], c["H"], c["nA"], engine=engine).load_arrays(c["W1"], c["b1"], c["W2"], c["b2"], c["W3"], c["b3"])
+    pol = DiscreteActorPolicy(actor=net)
+    k = c["cfg"]
+    alg = PPO(policy=pol, critic=net, optim=AdamOptimizerFactory(lr=c["lr"]), eps_clip=k["eps_clip"], dual_clip=k["dual_clip"] or None,
+              value_clip=k["value_clip"], advantage_normalization=k["adv_norm"], vf_coef=k["vf_coef"], ent_coef=k["ent_coef"],
+              max_grad_norm=c["max_norm"] or None, gamma=c["gamma"], gae_lambda=c["lam"], minibatch_order="numpy")
+    buf = VectorReplayBuffer(c["R"] * c["T"], c["R"], index_type="torch")
+    for t in range(c["T"]):
+        buf.add(Batch(obs=c["obs"][t], act=c["act"][t], rew=c["rew"][t], terminated=c["term"][t], truncated=c["trunc"][t], obs_next=c["obs_next"][t]))
+    pol.is_within_training_step = True
+    return net, alg, buf
+
+
+def _check_against_reference(c, net, alg, tol):
+    seq = alg.last_sequences
+    for k, ref in (("loss", "loss_seq"), ("clip", "clip_seq"), ("vf", "vf_seq"), ("ent", "ent_seq")):
+        assert np.allclose(seq[k], c[ref], rtol=tol["loss_rel"], atol=tol["loss_abs"]), (k, np.abs(seq[k] - c[ref]).max())
+    v = net.named_views()
+    for k in ("W1", "b1", "W2", "b2", "W3", "b3"):
+        err = np.abs(v[k].cpu().numpy() - c["after_" + k]).max()
+        assert err < tol["param_abs"], (k, err)
+
+
+@pytest.mark.parametrize("ci", [0, 1])
+def test_update_tc_matches_reference(golden, ci):
+    """PPO.update on the tcgen05 engine vs the fixtures recorded from the UNMODIFIED reference PPO (same minibatch index lists)."""
+    from _ppo_golden import load_case
+
+    c = load_case(golden("ppo.npz"), ci)
+    net, alg, buf = _mk_case(c, "tc")
+    np.random.seed(c["seed"])
+    alg.update(buf, c["bs"], c["repeat"])
+    _check_against_reference(c, net, alg, TC_REF_TOL)
+
+
+@pytest.mark.parametrize("engine", ["fp32", "tc"])
+@pytest.mark.parametrize("ci", [0, 1])
+def test_update_large_matches_reference(golden, ci, engine):
+    """C2-scale fixture (131 072 rows, minibatches of 4 096, 64 optimizer steps) recorded from the reference."""
+    from _ppo_golden import load_large
+
+    c = load_large(golden("ppo_large.npz"), ci)
+    net, alg, buf = _mk_case(c, engine)
+    np.random.seed(c["seed"])
+    alg.update(buf, c["bs"], c["repeat"])
+    em = lambda t: t.t().contiguous().view(-1).cpu().numpy()  # noqa: E731
+    si = c["sample_idx"]
+    pre_tol = 2e-5 if engine == "fp32" else 4e-3
+    for k, w in (("v_s", "v_s"), ("returns", "ret"), ("adv", "adv"), ("logp_old", "logp_old")):
+        assert np.allclose(em(alg._work[w])[si], c[k], rtol=pre_tol, atol=pre_tol * 4), (k, np.abs(em(alg._work[w])[si] - c[k]).max())
+    tol = dict(loss_rel=2e-4, loss_abs=2e-5, param_abs=1e-4) if engine == "fp32" else TC_REF_TOL
+    _check_against_reference(c, net, alg, tol)

@@ -1,9 +1,9 @@
 from .ctde import CentralizedCritic, CTDEPolicy, DecentralizedActor, GlobalStateConstructor
 from .multiagent import FlexibleMultiAgentPolicyManager
-from .ppo import A2C, PPO, AdamOptimizerFactory, DiscreteActorPolicy, Reinforce, ppo_smoke
+from .ppo import A2C, PPO, AdamOptimizerFactory, DiscreteActorPolicy, Reinforce
 from .training_coordinator import SimultaneousTrainer
 from .returns import compute_episodic_return, episode_mc_return_to_go, gae_flat, gae_time_major
 
 __all__ = ["compute_episodic_return", "episode_mc_return_to_go", "gae_flat", "gae_time_major", "PPO", "A2C", "Reinforce", "AdamOptimizerFactory",
-           "DiscreteActorPolicy", "ppo_smoke", "FlexibleMultiAgentPolicyManager", "CTDEPolicy", "GlobalStateConstructor",
+           "DiscreteActorPolicy", "FlexibleMultiAgentPolicyManager", "CTDEPolicy", "GlobalStateConstructor",
            "DecentralizedActor", "CentralizedCritic", "SimultaneousTrainer"]

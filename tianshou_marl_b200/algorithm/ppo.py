@@ -430,22 +430,6 @@ class PPO:
         return row * size + (start + j) % size
 
 
-def ppo_smoke() -> None:
-    """Used by __graft_entry__.smoke(): one tiny PPO minibatch update vs the torch-fp32 oracle."""
-    from oracle import ppo as oppo  # checker only (smoke is test infrastructure)
-
-    torch.manual_seed(0)
-    R, T, O, nA = 16, 8, 18, 5
-    onet = oppo.make_net(O, 64, nA, seed=1)
-    net = ActorCriticNet(O, 64, nA).load_arrays(*[p.detach().numpy() for p in onet.p])
-    obs = torch.randn(T * R, O, device="cuda")
-    o = net.forward(obs, mode="sample", seed=3, counter=0, want_logits=True)
-    with torch.no_grad():
-        lg, v = onet.forward(obs.cpu())
-    assert torch.allclose(o["logits"].cpu(), lg, rtol=1e-4, atol=1e-5), "policy forward mismatch"
-    assert torch.allclose(o["value"].cpu(), v, rtol=1e-4, atol=1e-5), "value forward mismatch"
-
-
 class A2C(PPO):
     """Advantage actor-critic (reference tianshou/algorithm/modelfree/a2c.py:154-288): the PPO machinery with the plain
     policy-gradient epilogue of the fused minibatch kernels -- actor_loss = -mean(log pi(a | s) * adv), vf_loss =
