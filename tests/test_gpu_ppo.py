@@ -266,6 +266,60 @@ def test_dedup_next_values_is_bit_identical(engine):
         assert torch.equal(res[0][k], res[1][k]), k
 
 
+def test_reset_env_between_collects_breaks_the_obs_chain():
+    """Collector.reset_env() while the lock-step buffer holds data: obs[t + 1] is a fresh reset observation although done[t] == 0,
+    so critic(obs_next[t]) must be evaluated on obs_next itself there (a2c.py:124-127).  The buffer is flagged and the update
+    with dedup_next_values=True equals the full second critic pass bit for bit."""
+    from tianshou_marl_b200.algorithm import PPO, AdamOptimizerFactory, DiscreteActorPolicy
+    from tianshou_marl_b200.data import Collector, VectorReplayBuffer
+    from tianshou_marl_b200.env import MPEVectorEnv
+    from tianshou_marl_b200.utils import ActorCriticNet
+
+    E, A, T = 64, 3, 20
+    res = []
+    for dedup in (False, True):
+        env = MPEVectorEnv("simple_spread_v3", n_envs=E, n_agents=A, seed=5)
+        buf = VectorReplayBuffer(T * E * A, E * A, index_type="torch")
+        net = ActorCriticNet(env.obs_dim, 64, 5, seed=3)
+        pol = DiscreteActorPolicy(actor=net, seed=11)
+        alg = PPO(policy=pol, critic=net, optim=AdamOptimizerFactory(lr=1e-3), minibatch_order="device", seed=2, dedup_next_values=dedup,
+                  reuse_rollout_policy_outputs=dedup)
+        col = Collector(alg, env, buf)
+        col.reset()
+        pol.is_within_training_step = True
+        col.collect(n_step=7 * E * A)
+        assert buf._obs_chain is True
+        col.reset_env()
+        assert buf._obs_chain is False and buf._policy_version is None
+        col.collect(n_step=(T - 7) * E * A)
+        assert buf._obs_chain is False
+        st = buf._store
+        assert not bool(st["done"][6].any()) and not torch.equal(st["obs"][7], st["obs_next"][6])  # the seam
+        alg.update(buf, 1024, 1)
+        res.append({k: alg._work[k].clone() for k in ("v_s", "v_n", "adv", "ret")})
+    for k in res[0]:
+        assert torch.equal(res[0][k], res[1][k]), k
+
+
+def test_return_scaling_with_row_subset_is_refused():
+    """ret_rms would be reduced over rows outside the group: refuse instead of contaminating the statistics."""
+    from tianshou_marl_b200.algorithm import PPO, AdamOptimizerFactory, DiscreteActorPolicy
+    from tianshou_marl_b200.data import Batch, VectorReplayBuffer
+    from tianshou_marl_b200.utils import ActorCriticNet
+
+    R, T, O = 8, 4, 6
+    net = ActorCriticNet(O, 64, 5, seed=1)
+    pol = DiscreteActorPolicy(actor=net)
+    alg = PPO(policy=pol, critic=net, optim=AdamOptimizerFactory(), return_scaling=True)
+    buf = VectorReplayBuffer(R * T, R, index_type="torch")
+    for t in range(T):
+        buf.add(Batch(obs=np.zeros((R, O), np.float32), act=np.zeros(R, np.int64), rew=np.ones(R), terminated=np.zeros(R, bool),
+                      truncated=np.zeros(R, bool), obs_next=np.zeros((R, O), np.float32)))
+    pol.is_within_training_step = True
+    with pytest.raises(NotImplementedError):
+        alg.update(buf, 8, 1, rows=torch.tensor([0, 2, 4], device="cuda"))
+
+
 @pytest.mark.parametrize("ci", [0, 1])
 def test_recompute_advantage_matches_reference(golden, ci):
     """PPO(recompute_advantage=True) (ppo.py:174-178) vs fixtures recorded from the reference: every minibatch loss of every

@@ -192,6 +192,10 @@ class PPO:
                 "If you want to update the policy without a Trainer, you will have to manage the above-mentioned flag yourself.")
         if buffer is None:
             return A2CTrainingStats(*(SequenceSummaryStats.from_sequence([]) for _ in range(4)))
+        if rows is not None and self.return_scaling:
+            # the scaled GAE kernel reduces the return moments over ALL rows of the buffer; with a row subset the other rows hold
+            # another group's (or no) values and would contaminate ret_rms
+            raise NotImplementedError("return_scaling / return_standardization with a row subset (policy groups) is not supported")
         t0 = time.time()
         net, L, P, S = self.net, _lib.lib(), _lib.ptr, _lib.stream_ptr()
         st = buffer._store

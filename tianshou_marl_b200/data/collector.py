@@ -95,6 +95,12 @@ class Collector:
         obs, info = self.env.reset(**(gym_reset_kwargs or {}))
         self._pre_collect_obs = obs
         self._carry = None
+        b = self.buffer
+        if b is not None and getattr(b, "_lockstep_len", None):
+            # the buffer holds a rollout whose last obs_next is NOT the next stored obs any more: PPO.update must evaluate
+            # critic(obs_next) itself at that seam (dedup_next_values / reuse_rollout_policy_outputs are off for this buffer)
+            b._obs_chain = False
+            b._policy_version = None
         return obs, info
 
     # -- collect ------------------------------------------------------------------------------

@@ -92,6 +92,11 @@ def one(engine: str) -> dict:
         r["param_abs"] = float(max(np.abs(v[kk].cpu().numpy() - c["after_" + kk]).max() for kk in names))
         moved = max(np.abs(c[kk] - c["after_" + kk]).max() for kk in names)
         r["param_vs_travel"] = r["param_abs"] / float(moved)  # error relative to how far the reference moved the parameters
+        err = np.concatenate([(v[kk].cpu().numpy() - c["after_" + kk]).reshape(-1) for kk in names])
+        trav = np.concatenate([(c[kk] - c["after_" + kk]).reshape(-1) for kk in names])
+        r["param_rms"] = float(np.sqrt((err ** 2).mean()))
+        r["param_rms_vs_travel_rms"] = float(np.sqrt((err ** 2).mean() / (trav ** 2).mean()))
+        r["param_abs_vs_lr_steps"] = r["param_abs"] / (c["lr"] * len(c["loss_seq"]))  # Adam moves an entry by at most ~lr per step
         em = lambda t: t.t().contiguous().view(-1).cpu().numpy()  # noqa: E731
         si = c["sample_idx"] if "sample_idx" in c else slice(None)
         for kk, w in (("v_s", "v_s"), ("returns", "ret"), ("adv", "adv"), ("logp_old", "logp_old")):
