@@ -102,6 +102,8 @@ _SIGS = {
     "tsm_gae_flat_workspace_bytes": (c_sz, [c_i64]),
     "tsm_gae_flat": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_i64, c_i64, c_f64, c_f64,
                              c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "tsm_gae_flat_static_max_n": (c_i64, []),
+    "tsm_gae_flat_static": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_i64, c_i64, c_f64, c_f64, c_vp, c_vp, c_vp]),
     "tsm_gae_tm": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_f64, c_f64, c_vp, c_vp, c_vp]),
     "tsm_gae_tm_scaled": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_f64, c_f64, c_f64, c_f64, c_vp, c_vp, c_vp, c_vp]),
     "tsm_values_next_prepare": (c_i32, [c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp]),

@@ -417,6 +417,71 @@ extern "C" int tsm_gae_flat(const void* v_s, const void* v_next, const void* rew
     return TSM_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// tsm_gae_flat_static: the same kernel with its scratch (tile counter + tile states) in a file-scope device array instead
+// of a caller-provided workspace, for callers that cannot allocate (CUDA graph capture, serving loops).  No counterpart in
+// the reference.  Every GPU that loads the library holds the array until
+// exit.  All calls share it: calls that overlap on one GPU (two streams) race; it is re-initialised on the caller's
+// stream at the start of every call (counter = 0, tile states = 0xFF), so nothing is assumed about its previous contents.
+constexpr int64_t STATIC_MAX_N = TSM_GAE_FLAT_STATIC_MAX_N;
+constexpr size_t STATIC_BYTES = 64 + (size_t)((STATIC_MAX_N + TILE - 1) / TILE) * sizeof(TileState);
+static __device__ __align__(256) unsigned char g_gae_flat_scratch[STATIC_BYTES];
+
+// In host code the array's name is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress,
+// once per device, with that device current.
+static int gae_flat_static_scratch(void** out, const char* fn) {
+    constexpr int MAX_DEV = 64;
+    static void* ptrs[MAX_DEV] = {nullptr};
+    int dev = 0;
+    TSM_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAX_DEV) return fail(TSM_ERR_UNSUPPORTED, "%s: device ordinal %d out of range", fn, dev);
+    if (!ptrs[dev]) {
+        void* p = nullptr;
+        TSM_CUDA(cudaGetSymbolAddress(&p, g_gae_flat_scratch));
+        if (!p) return fail(TSM_ERR_CUDA, "%s: cudaGetSymbolAddress returned NULL", fn);
+        ptrs[dev] = p;
+    }
+    *out = ptrs[dev];
+    return TSM_OK;
+}
+
+extern "C" int64_t tsm_gae_flat_static_max_n(void) { return STATIC_MAX_N; }
+
+extern "C" int tsm_gae_flat_static(const void* v_s, const void* v_next, const void* rew, int io_is_f64,
+                                   const uint8_t* terminated, const uint8_t* truncated, const uint8_t* force_end,
+                                   int64_t n, int64_t seg_len, double gamma, double lam, void* adv_out, void* ret_out,
+                                   tsm_stream_t stream) {
+    TSM_REQUIRE(n >= 0, "n >= 0");
+    if (n > STATIC_MAX_N)
+        return fail(TSM_ERR_INVALID, "%s: n = %lld exceeds the static scratch (TSM_GAE_FLAT_STATIC_MAX_N = %lld elements); use tsm_gae_flat",
+                    __func__, (long long)n, (long long)STATIC_MAX_N);
+    if (n == 0) return TSM_OK;
+    TSM_REQUIRE(rew != nullptr, "rew != NULL");
+    TSM_REQUIRE(terminated != nullptr && truncated != nullptr, "terminated/truncated != NULL");
+    TSM_REQUIRE(adv_out != nullptr || ret_out != nullptr, "an output pointer");
+    void* scratch = nullptr;
+    const int rc = gae_flat_static_scratch(&scratch, __func__);
+    if (rc) return rc;
+    cudaStream_t s = as_stream(stream);
+    const int num_tiles = (int)ceil_div(n, TILE);
+    const size_t used = 64 + (size_t)num_tiles * sizeof(TileState);
+    TSM_CUDA(cudaMemsetAsync(scratch, 0, 64, s));                                               // tile counter
+    TSM_CUDA(cudaMemsetAsync(reinterpret_cast<char*>(scratch) + 64, 0xFF, used - 64, s));       // tile states: empty
+    unsigned int* counter = reinterpret_cast<unsigned int*>(scratch);
+    TileState* tiles = reinterpret_cast<TileState*>(reinterpret_cast<char*>(scratch) + 64);
+    const double gl = gamma * lam;
+    if (io_is_f64)
+        gae_flat_kernel<double><<<num_tiles, THREADS, 0, s>>>(
+            (const double*)v_s, (const double*)v_next, (const double*)rew, terminated, truncated, force_end, n, seg_len,
+            gamma, gl, (double*)adv_out, (double*)ret_out, counter, tiles, num_tiles);
+    else
+        gae_flat_kernel<float><<<num_tiles, THREADS, 0, s>>>(
+            (const float*)v_s, (const float*)v_next, (const float*)rew, terminated, truncated, force_end, n, seg_len,
+            gamma, gl, (float*)adv_out, (float*)ret_out, counter, tiles, num_tiles);
+    TSM_LAUNCH_CHECK();
+    return TSM_OK;
+}
+
 extern "C" int tsm_gae_tm(const float* v_s, const float* v_next, const float* rew, const uint8_t* terminated,
                           const uint8_t* truncated, int64_t size, int64_t n_rows, int64_t start, int64_t len,
                           double gamma, double lam, float* adv_out, float* ret_out, tsm_stream_t stream) {
