@@ -2,7 +2,7 @@
 
 Run (only where /root/reference exists; never on the GPU box):
 
-    python tests/golden/make_golden.py [gae buffer collector ppo marl]
+    python tests/golden/make_golden.py [gae buffer ppo ppo_recompute ppo_retscale a2c reinforce ...]   (GENS lists the generators)
 
 The reference is imported from /root/reference through the import shims in oracle/shims/
 (stand-ins for gymnasium, pettingzoo, overrides, sensai, h5py, deepdiff, matplotlib, which
@@ -177,7 +177,7 @@ GENS = {"gae": gen_gae, "buffer": gen_buffer}
 
 if __name__ == "__main__":
     try:
-        from make_golden_more import GENS as MORE  # collector / ppo / marl fixtures
+        from make_golden_more import GENS as MORE  # ppo / a2c / reinforce fixtures
 
         GENS.update(MORE)
     except ImportError:

@@ -282,8 +282,16 @@ def test_epoch_slot_table_and_launch_chain_agree(n_mb, mb, monkeypatch):
         assert np.allclose(res[variant][1], res["chain"][1], rtol=1e-4, atol=1e-3)
 
 
-# ---- the benched engine against the REFERENCE fixtures (tolerances: DESIGN.md 3.1 "error budget", profiles/r02_tc_error_budget.json) ----
-TC_REF_TOL = dict(loss_rel=2e-2, loss_abs=4e-3, param_abs=2.5e-3)
+# ---- the benched engine against the REFERENCE fixtures ----
+# Tolerances = about 2x what tools/tc_error_budget.py measured on B200 (profiles/r02_tc_error_budget.json):
+#   per-minibatch loss / clip / vf / ent: |d| <= 1e-3 + 1e-3 * |ref|          (measured <= 4.5e-4 abs, 3e-4 rel)
+#   v_s, returns, adv, logp_old:          |d| <= 2e-3                          (measured <= 9.6e-4: fp16 operands)
+#   parameters after the whole update:    RMS error <= 10 % of the RMS distance the reference moved them (measured 1.3 - 5 %),
+#                                         and every entry within lr * steps (Adam moves an entry by at most ~lr per step; entries
+#                                         whose gradient is rounding noise take +-lr steps of either sign: measured <= 0.48)
+# The fp32 engine on the same C2-scale fixture: losses rtol 2e-5 / atol 3e-5, parameters RMS <= 0.5 % of the travel, max 5e-4.
+TC_REF_TOL = dict(loss_rel=1e-3, loss_abs=1e-3, pre_abs=2e-3, param_rms_frac=0.10, param_abs_lr_steps=1.0)
+FP32_LARGE_TOL = dict(loss_rel=2e-5, loss_abs=3e-5, pre_abs=4e-6, param_rms_frac=5e-3, param_abs=5e-4)
 
 
 def _mk_case(c, engine):
@@ -309,9 +317,13 @@ def _check_against_reference(c, net, alg, tol):
     for k, ref in (("loss", "loss_seq"), ("clip", "clip_seq"), ("vf", "vf_seq"), ("ent", "ent_seq")):
         assert np.allclose(seq[k], c[ref], rtol=tol["loss_rel"], atol=tol["loss_abs"]), (k, np.abs(seq[k] - c[ref]).max())
     v = net.named_views()
-    for k in ("W1", "b1", "W2", "b2", "W3", "b3"):
-        err = np.abs(v[k].cpu().numpy() - c["after_" + k]).max()
-        assert err < tol["param_abs"], (k, err)
+    names = ("W1", "b1", "W2", "b2", "W3", "b3")
+    err = np.concatenate([(v[k].cpu().numpy() - c["after_" + k]).reshape(-1) for k in names])
+    trav = np.concatenate([(c[k] - c["after_" + k]).reshape(-1) for k in names])
+    rms_frac = float(np.sqrt((err ** 2).mean() / (trav ** 2).mean()))
+    assert rms_frac < tol["param_rms_frac"], rms_frac
+    bound = tol["param_abs"] if "param_abs" in tol else tol["param_abs_lr_steps"] * c["lr"] * len(c["loss_seq"])
+    assert np.abs(err).max() < bound, (np.abs(err).max(), bound)
 
 
 @pytest.mark.parametrize("ci", [0, 1])
@@ -338,8 +350,7 @@ def test_update_large_matches_reference(golden, ci, engine):
     alg.update(buf, c["bs"], c["repeat"])
     em = lambda t: t.t().contiguous().view(-1).cpu().numpy()  # noqa: E731
     si = c["sample_idx"]
-    pre_tol = 2e-5 if engine == "fp32" else 4e-3
+    tol = FP32_LARGE_TOL if engine == "fp32" else TC_REF_TOL
     for k, w in (("v_s", "v_s"), ("returns", "ret"), ("adv", "adv"), ("logp_old", "logp_old")):
-        assert np.allclose(em(alg._work[w])[si], c[k], rtol=pre_tol, atol=pre_tol * 4), (k, np.abs(em(alg._work[w])[si] - c[k]).max())
-    tol = dict(loss_rel=2e-4, loss_abs=2e-5, param_abs=1e-4) if engine == "fp32" else TC_REF_TOL
+        assert np.abs(em(alg._work[w])[si] - c[k]).max() < tol["pre_abs"], (k, np.abs(em(alg._work[w])[si] - c[k]).max())
     _check_against_reference(c, net, alg, tol)
