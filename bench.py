@@ -57,6 +57,8 @@ def parse() -> argparse.Namespace:
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--cpu-envs", type=int, default=4096, help="reference arm: environments in the bounded sample")
     p.add_argument("--cpu-horizon", type=int, default=64)
+    p.add_argument("--ref-quick", action="store_true", help="--impl reference: only the C1 point of the reference classes (the cpu_baseline leg of the own arm)")
+    p.add_argument("--ref-port", action="store_true", help="--impl reference: time the oracle port even when baseline/_ref is installed")
     return p.parse_args()
 
 
@@ -195,17 +197,78 @@ def cpu_arm(args: argparse.Namespace, steps: int, warmup: int) -> dict:
                       f"oracle port (C/OpenMP MPE step + buffer add, serial f64 GAE, torch-fp32 CPU MLP)"}
 
 
+def reference_classes_arm(args: argparse.Namespace, steps: int, warmup: int, quick: bool) -> dict | None:
+    """The reference's own classes (baseline/_ref, installed by baseline/install_ref.py at build time) on the host cores:
+    BASELINE.json configs[0] exactly (DummyVectorEnv x8, A agents, T = --horizon) as the timed value, plus -- unless `quick` --
+    SubprocVectorEnv x8, a DummyVectorEnv x1024 scaling point (one step, T = 16) and the numba `_gae` at B = 2^24 on one core.
+    Returns None when baseline/_ref is absent (the caller then times the oracle port)."""
+    from baseline import ref_arm
+
+    if not ref_arm.available():
+        return None
+    bs = 256  # the reference's own PPO scripts use batch_size 64..256 at this scale (test/discrete/test_ppo_discrete.py:45)
+    r = ref_arm.run(8, args.agents, args.horizon, bs, args.repeat, args.hidden, steps, warmup, update=not args.no_update)
+    if not quick:
+        extra = {}
+        try:
+            s = ref_arm.run(8, args.agents, args.horizon, bs, args.repeat, args.hidden, max(1, steps // 2), 1, subproc=True, update=not args.no_update)
+            extra["subproc_x8"] = {k: s[k] for k in ("value", "ms_per_step", "collect_ms", "update_ms", "workers")}
+        except Exception as e:  # noqa: BLE001  (fork restrictions of the box must not lose the main number)
+            extra["subproc_x8"] = {"unavailable": repr(e)[:200]}
+        s = ref_arm.run(1024, args.agents, 16, bs, args.repeat, args.hidden, 1, 0, update=not args.no_update)
+        extra["dummy_x1024_T16"] = {k: s[k] for k in ("value", "ms_per_step", "collect_ms", "update_ms")}
+        extra["gae_numba_2p24"] = ref_arm.gae_numba(1 << 24)
+        r["extra"] = extra
+    return r
+
+
+def cpu_baseline_leg(args: argparse.Namespace) -> dict:
+    """cpu_baseline of the own arm (rank 0, N = 1): the reference classes in a fresh process (no CUDA context, own torch thread
+    pool), about 5 s; the oracle port beside it as cpu_baseline_port."""
+    out: dict = {}
+    try:
+        cmd = [sys.executable, os.path.abspath(__file__), "--impl", "reference", "--ref-quick", "--steps", "3", "--warmup", "1",
+               "--agents", str(args.agents), "--horizon", str(args.horizon), "--repeat", str(args.repeat), "--hidden", str(args.hidden)]
+        env = dict(os.environ)
+        for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+            env.pop(k, None)
+        p = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
+        ref = json.loads(p.stdout.strip().splitlines()[-1])["cpu_baseline"]
+    except Exception as e:  # noqa: BLE001
+        ref = None
+        print("cpu_baseline: reference process failed:", repr(e)[:300], file=sys.stderr)
+    r = cpu_arm(args, 3, 1)
+    port = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]}
+    if ref is not None and ref.get("kind") == "reference":
+        out["cpu_baseline"], out["cpu_baseline_port"] = ref, port
+    else:
+        out["cpu_baseline"] = port
+    return out
+
+
 def reference_main(args: argparse.Namespace) -> None:
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    r = cpu_arm(args, max(1, args.steps), max(0, args.warmup))
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
+    r = None if args.ref_port else reference_classes_arm(args, steps, warmup, args.ref_quick)
+    kind = "reference"
+    port = None
+    if r is None:
+        r, kind = cpu_arm(args, steps, warmup), "port"
+    elif not args.ref_quick:
+        port = cpu_arm(args, 2, 1)
     line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"C2 simple_spread_v3 A={args.agents}, bounded CPU sample: {r['sample']}"},
-            "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]},
+            "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": kind, "sample": r["sample"]},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    for k in ("collect_ms", "update_ms", "extra"):
+        if k in r:
+            line["cpu_baseline"][k] = r[k]
+    if port is not None:
+        line["cpu_baseline_port"] = {"value": port["value"], "unit": UNIT, "cores": port["cores"], "kind": "port", "sample": port["sample"]}
     print(json.dumps(line))
 
 
@@ -374,8 +437,7 @@ def main() -> None:
                         "h2d_bytes_per_step": wl.h2d_bytes, "d2h_bytes_per_step": wl.d2h_bytes},
                 "stages_ms": stages, "roofline": roof}
         if not args.no_cpu_baseline and world == 1:
-            r = cpu_arm(args, 3, 1)
-            line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]}
+            line.update(cpu_baseline_leg(args))
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
