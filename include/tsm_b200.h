@@ -281,7 +281,8 @@ int tsm_random_actions(int32_t* act, int64_t n, int n_act, uint64_t seed, uint64
 typedef struct tsm_net {
     int32_t in_dim, hidden, out_dim, n_act, value_index;
     int32_t engine;     /* 0: fp32 CUDA-core kernels (exact parity path); 1: tcgen05 kernels (fp16 operands, fp32 accumulate in
-                           TMEM; needs hidden == 64, in_dim <= 31, out_dim <= 8) */
+                           TMEM; needs hidden == 64, in_dim <= 31, out_dim <= 8); 2: the wide tcgen05 engine (tsm_tcw_*:
+                           hidden == 128, in_dim <= 1023, out_dim <= 16) */
     int64_t n_params;   /* == tsm_net_param_count(in_dim, hidden, out_dim) */
     float* params;      /* [n_params] */
     float* grads;       /* [n_params] accumulated by tsm_ppo_minibatch, zeroed by tsm_adam_step */
@@ -488,6 +489,58 @@ int tsm_rollout_step(const tsm_mpe* env, const tsm_buf* buf, const int32_t* act,
 int tsm_collect_lockstep(const tsm_net* net, const tsm_mpe* env, const tsm_buf* buf, const tsm_rollout* ro, int64_t n_steps,
                          int mode, uint64_t seed, uint64_t counter0, int64_t lockstep_len, int n_random_act,
                          int64_t* slot_out, int64_t* lockstep_len_out, int* obs_in_carry_out, tsm_stream_t stream);
+
+/* ---- engine 2: the "wide" tcgen05 engine (csrc/mlp_tcw.cu): in(<= 1023) -> 128 -> 128 -> out(<= 16) ---------------------
+ * The nets of the reference's CTDE path: DecentralizedActor (multiagent/ctde.py:346-379, obs -> 128 -> 128 -> n_act) and
+ * CentralizedCritic (ctde.py:382-414, global state -> 128 -> 128 -> one value per agent; 600 -> ... -> 10 at BASELINE.json
+ * configs[2]).  tsm_net.engine = 2, hidden = 128; tsm_net.tc_image holds tsm_tcw_image_bytes(in_dim) bytes (the fp16 operand
+ * image of the parameters: call tsm_net_pack after writing params from the host; tsm_tcw_adam keeps it current).
+ * Inputs are consumed as PACKED fp16 tile images (tsm_tcw_pack_x), 128 rows per tile; a minibatch is a set of whole tiles. */
+int64_t tsm_tcw_image_bytes(int in_dim);
+int64_t tsm_tcw_x_bytes(int in_dim, int64_t n_rows);
+/* x: [*][ld] float32 rows (ld >= in_dim; the centralized critic's global state of one world is A * obs_dim consecutive floats of
+ * the env-major obs block, GlobalStateConstructor "concatenate", ctde.py:291-294, so ld = in_dim = A * obs_dim needs no copy);
+ * idx: optional source row per packed row (a permuted / gathered batch, data/batch.py:1209-1226); ximg: tsm_tcw_x_bytes bytes. */
+int tsm_tcw_pack_x(const float* x, int64_t ld, int in_dim, const int64_t* idx, int64_t n_rows, void* ximg, tsm_stream_t stream);
+/* Forward over all rows of a packed image.  mode 0: out[n_rows][out_dim] raw head outputs (critic values / actor logits,
+ * discrete.py:67-89); 1 sample / 2 argmax / 3 evaluate `act`: act, logp, entropy (+ out = logits [n_rows][n_act]); the sampling
+ * key of row r is (seed, counter, rng_row0 + r) exactly as in tsm_net_forward. */
+int tsm_tcw_forward(const tsm_net* net, const void* ximg, int64_t n_rows, int mode, uint64_t seed, uint64_t counter, int64_t rng_row0,
+                    float* out, int32_t* act, float* logp, float* entropy, tsm_stream_t stream);
+typedef struct tsm_tcw_tiles {
+    const void* ximg;          /* packed input image */
+    int64_t n_rows;            /* rows behind ximg (the last tile may be ragged) */
+    const int32_t* super_ids;  /* optional device list: logical tile q -> physical tile super_ids[q / sub] * sub + q % sub
+                                  (a minibatch of "super-tiles": one critic tile of 128 worlds <-> `sub` = A actor tiles) */
+    int32_t sub;
+    int64_t tile0, n_tiles;    /* logical tiles [tile0, tile0 + n_tiles) of this launch */
+} tsm_tcw_tiles;
+typedef struct tsm_tcw_loss {
+    int32_t kind;              /* 0: PPO / policy-gradient term on the logits (modelfree/ppo.py:181-197, cfg.plain_pg as in
+                                     tsm_ppo_cfg) with entropy bonus; row scalars adv / logp_old / act indexed by physical row
+                                  1: value loss per head (ppo.py:199-208): target / v_old / weight are [n_rows][heads]
+                                  2: value = mean of the heads against one target per row (ctde.py:153-166) */
+    const int32_t* act;
+    const float* adv;
+    const float* logp_old;
+    const float* target;
+    const float* v_old;        /* kind 1 with cfg.value_clip */
+    const float* weight;       /* kind 1, optional 0/1 mask per head */
+    int32_t heads;
+} tsm_tcw_loss;
+/* Forward + loss + backward over the tiles of one minibatch; gradients are ADDED to net.grads, loss sums (clip, vf, ent, rows)
+ * to loss_sums[4].  inv_n = 1 / (rows of the minibatch), gscale = power of two >= rows (fp16 range of the output gradient). */
+int tsm_tcw_train(const tsm_net* net, const tsm_tcw_tiles* tiles, const tsm_tcw_loss* loss, const tsm_ppo_cfg* cfg, float inv_n,
+                  float gscale, const float* mb_stats, double* loss_sums, tsm_stream_t stream);
+/* clip_grad_norm_ over the parameters of ALL n_nets nets jointly (ActorCritic, a2c.py:102-105; algorithm_base.py:485-498) +
+ * Adam (optim.py:89-110) + fp16 image refresh + zeroed gradients.  step: 1-based number of this update; workspace: 64 zeroed
+ * device bytes kept by the caller, seq: number of earlier CLIPPING launches on it. */
+int tsm_tcw_adam(const tsm_net* nets, int n_nets, int64_t step, float lr, float beta1, float beta2, float eps, float max_grad_norm,
+                 float grad_scale, void* workspace, uint32_t seq, float* grad_norm_out, tsm_stream_t stream);
+/* advantage mean / 1 / (unbiased std + eps) of tile-ordered minibatches (ppo.py:184-186): minibatch m = super-tiles
+ * [m * mb_super, (m + 1) * mb_super) of super_ids (NULL: identity), one super-tile = rows_per_super consecutive rows. */
+int tsm_tcw_adv_stats(const float* adv, int64_t n_rows, const int32_t* super_ids, int64_t rows_per_super, int64_t n_super,
+                      int64_t mb_super, float eps, float* stats, tsm_stream_t stream);
 
 /* tcgen05 self test (tests only): D[128][n] = A * B with A / B given as shared-memory images
  * (float32 words, copied verbatim to smem) and explicit descriptor fields

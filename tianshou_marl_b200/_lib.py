@@ -93,6 +93,19 @@ class TsmPpoCfg(C.Structure):
     ]
 
 
+class TsmTcwTiles(C.Structure):
+    """struct tsm_tcw_tiles (include/tsm_b200.h)."""
+
+    _fields_ = [("ximg", c_vp), ("n_rows", c_i64), ("super_ids", c_vp), ("sub", C.c_int32), ("tile0", c_i64), ("n_tiles", c_i64)]
+
+
+class TsmTcwLoss(C.Structure):
+    """struct tsm_tcw_loss (include/tsm_b200.h)."""
+
+    _fields_ = [("kind", C.c_int32), ("act", c_vp), ("adv", c_vp), ("logp_old", c_vp), ("target", c_vp), ("v_old", c_vp), ("weight", c_vp),
+                ("heads", C.c_int32)]
+
+
 c_f32, c_u64 = C.c_float, C.c_uint64
 
 _SIGS = {
@@ -135,6 +148,13 @@ _SIGS = {
     "tsm_rollout_step": (c_i32, [c_vp] * 14 + [c_i64, c_i64, c_i64, c_vp]),
     "tsm_net_forward_range": (c_i32, [c_vp, c_vp, c_i64, c_i64, c_i32, C.c_uint64, C.c_uint64, c_vp, c_vp, c_vp, c_vp]),
     "tsm_tc_selftest": (c_i32, [c_vp, c_i32, c_vp, c_i32, c_vp, c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp]),
+    "tsm_tcw_image_bytes": (c_i64, [c_i32]),
+    "tsm_tcw_x_bytes": (c_i64, [c_i32, c_i64]),
+    "tsm_tcw_pack_x": (c_i32, [c_vp, c_i64, c_i32, c_vp, c_i64, c_vp, c_vp]),
+    "tsm_tcw_forward": (c_i32, [c_vp, c_vp, c_i64, c_i32, c_u64, c_u64, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "tsm_tcw_train": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_f32, c_f32, c_vp, c_vp, c_vp]),
+    "tsm_tcw_adam": (c_i32, [c_vp, c_i32, c_i64, c_f32, c_f32, c_f32, c_f32, c_f32, c_f32, c_vp, C.c_uint32, c_vp, c_vp]),
+    "tsm_tcw_adv_stats": (c_i32, [c_vp, c_i64, c_vp, c_i64, c_i64, c_i64, c_f32, c_vp, c_vp]),
     "tsm_buf_gather": (c_i32, [c_vp, c_vp, c_i64] + [c_vp] * 9 + [c_vp, c_vp, c_i32, c_vp]),
 }
 

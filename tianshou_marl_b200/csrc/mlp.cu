@@ -625,6 +625,7 @@ __global__ void __launch_bounds__(ADAM_THREADS) pack_image_kernel(const float* _
 }  // namespace tsm
 
 namespace tsm {
+int tcw_net_pack(const tsm_net* net, cudaStream_t s);  // engine 2 (mlp_tcw.cu)
 int tc_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int64_t n, int mode, int scatter, uint64_t seed,
                    uint64_t counter, float* out, int32_t* act, float* logp, float* value, float* entropy, int64_t rng_row0, cudaStream_t s);
 int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, int64_t mb_start, int64_t mb_len,
@@ -875,6 +876,7 @@ extern "C" int tsm_adam_step(const tsm_net* net, float lr, float beta1, float be
 }
 
 extern "C" int tsm_net_pack(const tsm_net* net, tsm_stream_t stream) {
+    if (net && net->engine == 2) return tcw_net_pack(net, as_stream(stream));
     int rc = check_net(net, __func__);
     if (rc) return rc;
     if (net->engine != 1) return TSM_OK;

@@ -28,10 +28,13 @@ class ActorCriticNet(nn.Module):
                  device: str | torch.device = "cuda", seed: int | None = None, orthogonal: bool = True,
                  engine: str = "fp32") -> None:
         """engine: "fp32" = exact CUDA-core kernels (csrc/mlp.cu); "tc" = tcgen05 tensor-core kernels with fp16 operands and
-        fp32 accumulation (csrc/mlp_tc.cu; hidden 64, in_dim <= 31, out_dim <= 8)."""
+        fp32 accumulation (csrc/mlp_tc.cu; hidden 64, in_dim <= 31, out_dim <= 8); "tcw" = the wide tcgen05 engine of the CTDE
+        nets (csrc/mlp_tcw.cu; hidden 128, in_dim <= 1023, out_dim <= 16, separate actor / value-only critic)."""
         super().__init__()
-        if engine not in ("fp32", "tc"):
-            raise ValueError("engine must be 'fp32' or 'tc'")
+        if engine not in ("fp32", "tc", "tcw"):
+            raise ValueError("engine must be 'fp32', 'tc' or 'tcw'")
+        if engine == "tcw" and (hidden != 128 or with_value and not n_value_only):
+            raise ValueError("engine 'tcw' (csrc/mlp_tcw.cu) runs separate hidden-128 nets: an actor (with_value=False) or a value-only critic")
         self.engine = engine
         self.in_dim, self.hidden, self.n_act = int(in_dim), int(hidden), int(n_act)
         if n_value_only:  # critic-only net: out_dim value heads, no logits
@@ -52,7 +55,8 @@ class ActorCriticNet(nn.Module):
         self.adam_step = torch.zeros(1, dtype=torch.int64, device=self.device)
         # engine "tc": fp16 operand image of the parameters, kept current by the optimizer kernels; any host-side
         # write to `flat` (tracked through its version counter) triggers tsm_net_pack before the next kernel call
-        self.tc_image = torch.zeros(_lib.TC_IMAGE_BYTES, dtype=torch.uint8, device=self.device) if engine == "tc" else None
+        self.tc_image = torch.zeros(self._image_bytes(), dtype=torch.uint8, device=self.device) if engine != "fp32" else None
+        self._ximg: torch.Tensor | None = None  # engine "tcw": packed fp16 input image of the last forward
         self._packed_version = -1
         self.kernel_updates = 0  # optimizer steps taken by kernels (they do not bump flat._version): see param_version
         H, I, O = self.hidden, self.in_dim, self.out_dim
@@ -74,22 +78,28 @@ class ActorCriticNet(nn.Module):
                     self.view(k).copy_(w)
 
     # -- plumbing ---------------------------------------------------------------------------
+    ENGINES = {"fp32": 0, "tc": 1, "tcw": 2}
+
+    def _image_bytes(self) -> int:
+        return _lib.TC_IMAGE_BYTES if self.engine == "tc" else int(_lib.lib().tsm_tcw_image_bytes(self.in_dim))
+
     def _fill_desc(self) -> None:
         d = self._desc
         d.in_dim, d.hidden, d.out_dim, d.n_act, d.value_index, d.n_params = (self.in_dim, self.hidden, self.out_dim, self.n_act,
                                                                            self.value_index, self.n_params)
-        d.engine = 1 if self.engine == "tc" else 0
+        d.engine = self.ENGINES[self.engine]
         d.params, d.grads = self.flat.data_ptr(), self.grads.data_ptr()
         d.adam_m, d.adam_v, d.adam_step = self.adam_m.data_ptr(), self.adam_v.data_ptr(), self.adam_step.data_ptr()
         d.tc_image = self.tc_image.data_ptr() if self.tc_image is not None else None
 
     @property
     def desc(self) -> Any:
-        if self._desc.params != self.flat.data_ptr() or self._desc.engine != (1 if self.engine == "tc" else 0):
+        if (self._desc.params != self.flat.data_ptr() or self._desc.grads != self.grads.data_ptr()
+                or self._desc.engine != self.ENGINES[self.engine]):
             self._fill_desc()
-        if self.engine == "tc" and self.flat._version != self._packed_version:
+        if self.engine != "fp32" and self.flat._version != self._packed_version:
             if self.tc_image is None:
-                self.tc_image = torch.zeros(_lib.TC_IMAGE_BYTES, dtype=torch.uint8, device=self.device)
+                self.tc_image = torch.zeros(self._image_bytes(), dtype=torch.uint8, device=self.device)
                 self._fill_desc()
             _lib.check(_lib.lib().tsm_net_pack(C.byref(self._desc), _lib.stream_ptr()))
             self._packed_version = self.flat._version
@@ -125,6 +135,24 @@ class ActorCriticNet(nn.Module):
     def reset_optimizer(self) -> None:
         self.grads.zero_(); self.adam_m.zero_(); self.adam_v.zero_(); self.adam_step.zero_()
 
+    # -- engine "tcw": packed fp16 tile images of the inputs (tsm_tcw_pack_x) -------------------------------------------------
+    def x_bytes(self, n_rows: int) -> int:
+        return int(_lib.lib().tsm_tcw_x_bytes(self.in_dim, int(n_rows)))
+
+    def pack_x(self, x: torch.Tensor, idx: torch.Tensor | None = None, out: torch.Tensor | None = None, n_rows: int | None = None) -> torch.Tensor:
+        """x: float32 [*, ld] rows on the device (ld >= in_dim); idx: optional int64 source row per packed row."""
+        assert x.is_cuda and x.dtype == torch.float32 and x.is_contiguous()
+        x2 = x.view(-1, x.shape[-1])
+        n = int(n_rows if n_rows is not None else (idx.numel() if idx is not None else x2.shape[0]))
+        need = self.x_bytes(n)
+        if out is None:
+            if self._ximg is None or self._ximg.numel() < need:
+                self._ximg = torch.empty(need, dtype=torch.uint8, device=self.device)
+            out = self._ximg
+        assert out.numel() >= need
+        _lib.check(_lib.lib().tsm_tcw_pack_x(_lib.ptr(x2), int(x2.shape[1]), self.in_dim, _lib.ptr(idx), n, _lib.ptr(out), _lib.stream_ptr()))
+        return out
+
     # -- forward ----------------------------------------------------------------------------
     def forward(self, obs: torch.Tensor, mode: str = "raw", act: torch.Tensor | None = None, seed: int = 0, counter: int = 0,
                 rows: torch.Tensor | None = None, scatter: bool = False, out: dict[str, torch.Tensor] | None = None,
@@ -156,6 +184,15 @@ class ActorCriticNet(nn.Module):
             if want_entropy and "entropy" not in o:
                 o["entropy"] = torch.empty(n_out, dtype=torch.float32, device=dev)
         P = _lib.ptr
+        if self.engine == "tcw":
+            if rows is not None:
+                raise NotImplementedError("engine 'tcw': row subsets are passed as the index list of pack_x")
+            ximg = self.pack_x(x)
+            _lib.check(_lib.lib().tsm_tcw_forward(self.desc, P(ximg), n, m, int(seed), int(counter), 0, P(o.get("out")), P(o.get("act")),
+                                                  P(o.get("logp")), P(o.get("entropy")), _lib.stream_ptr()))
+            if m != 0 and "out" in o:
+                o["logits"] = o["out"]
+            return o
         _lib.check(_lib.lib().tsm_net_forward(self.desc, P(x), P(rows), n, m, int(scatter), int(seed), int(counter),
                                               P(o.get("out")), P(o.get("act")), P(o.get("logp")), P(o.get("value")),
                                               P(o.get("entropy")), _lib.stream_ptr()))
