@@ -291,7 +291,10 @@ typedef struct tsm_net {
     int64_t* adam_step; /* [1] device step counter */
     void* tc_image;     /* engine 1 only: TSM_TC_IMAGE_BYTES device bytes, zero-initialised by the caller: the fp16 operand
                            image of params.  Refreshed by tsm_adam_step / tsm_ppo_epoch; call tsm_net_pack
-                           after writing params any other way. */
+                           after writing params any other way.  engine 2: tsm_tcw_image_bytes(in_dim) bytes. */
+    void* x_scratch;    /* engine 2 only, optional: device scratch for the packed fp16 image of the rows tsm_net_forward /
+                           tsm_net_forward_range / tsm_collect_lockstep evaluate (they take float32 rows like engines 0 / 1) */
+    int64_t x_scratch_bytes; /* >= tsm_tcw_x_bytes(in_dim, rows of the largest call) */
 } tsm_net;
 #define TSM_TC_IMAGE_BYTES 119552 /* 16 896 image + tsm_ppo_epoch's three more gradient-sized buffers of 7 168 floats + 256 bytes of barrier words + a 16 KB index table */
 
@@ -541,6 +544,38 @@ int tsm_tcw_adam(const tsm_net* nets, int n_nets, int64_t step, float lr, float 
  * [m * mb_super, (m + 1) * mb_super) of super_ids (NULL: identity), one super-tile = rows_per_super consecutive rows. */
 int tsm_tcw_adv_stats(const float* adv, int64_t n_rows, const int32_t* super_ids, int64_t rows_per_super, int64_t n_super,
                       int64_t mb_super, float eps, float* stats, tsm_stream_t stream);
+
+/* One PPO epoch over CTDE nets (the build's "MAPPO": reference PPO arithmetic, modelfree/ppo.py:164-224, with the
+ * DecentralizedActor on local observations and the CentralizedCritic on the concatenated global state, one value head per
+ * agent) as ONE C call: per minibatch m = super-tiles [m * mb_super, (m + 1) * mb_super) of super_ids -- critic
+ * forward/value-loss/backward over those tiles of ximg_critic (one row per world and step), actor forward/policy-loss/backward
+ * over the matching n_agents tiles each of ximg_actor (row = world * n_agents + agent), then tsm_tcw_adam over both nets with
+ * one gradient norm.  Single rank (across ranks the caller loops and all-reduces net.grads between tsm_tcw_train and
+ * tsm_tcw_adam). */
+typedef struct tsm_tcw_epoch {
+    const tsm_net* actor;
+    const tsm_net* critic;
+    const void* ximg_actor;     /* packed local observations, n_rows rows */
+    const void* ximg_critic;    /* packed global states, n_rows / n_agents rows */
+    int64_t n_rows;
+    int32_t n_agents;
+    const int32_t* super_ids;   /* device, [n_super] or NULL (identity) */
+    int64_t n_super, mb_super;
+    const int32_t* act;         /* [n_rows] */
+    const float* adv;           /* [n_rows] */
+    const float* logp_old;      /* [n_rows] */
+    const float* ret;           /* [n_rows] == [n_rows / n_agents][n_agents] */
+    const float* v_old;         /* [n_rows], read with cfg.value_clip */
+    const int64_t* h_mb_rows;   /* HOST: agent rows of each minibatch */
+    const float* mb_stats;      /* device [n_mb][2] (tsm_tcw_adv_stats) or NULL */
+    double* sums_actor;         /* device [n_mb][4] */
+    double* sums_critic;        /* device [n_mb][4] */
+    float lr, beta1, beta2, eps, max_grad_norm;
+    int64_t step0;              /* optimizer steps taken before this call */
+    void* adam_ws;              /* 64 zeroed device bytes */
+    uint32_t adam_seq0;         /* clipping launches on adam_ws before this call */
+} tsm_tcw_epoch;
+int tsm_tcw_ppo_epoch(const tsm_tcw_epoch* e, const tsm_ppo_cfg* cfg, tsm_stream_t stream);
 
 /* tcgen05 self test (tests only): D[128][n] = A * B with A / B given as shared-memory images
  * (float32 words, copied verbatim to smem) and explicit descriptor fields

@@ -8,14 +8,14 @@ import numpy as np
 from make_golden import save  # noqa: E402  (also sets sys.path for the reference + shims)
 
 
-def gen_ctde() -> dict:
+def gen_ctde(cases: list | None = None) -> dict:
     import gymnasium as gym
     import torch
     from tianshou.algorithm.multiagent.ctde import CTDEPolicy, CentralizedCritic, DecentralizedActor, GlobalStateConstructor
     from tianshou.data import Batch
 
     out: dict = {}
-    cases = [dict(A=3, O=18, H=64, nA=5, n_env=40, lr_a=1e-3, lr_c=2e-3, gamma=0.99, use_global=True, steps=3),
+    cases = cases or [dict(A=3, O=18, H=64, nA=5, n_env=40, lr_a=1e-3, lr_c=2e-3, gamma=0.99, use_global=True, steps=3),
              dict(A=3, O=18, H=128, nA=5, n_env=24, lr_a=5e-4, lr_c=1e-3, gamma=0.95, use_global=True, steps=2),
              dict(A=2, O=10, H=64, nA=4, n_env=33, lr_a=1e-3, lr_c=1e-3, gamma=0.9, use_global=False, steps=2)]
     out["n_cases"] = np.array(len(cases))

@@ -53,7 +53,7 @@ class TsmNet(C.Structure):
         ("in_dim", C.c_int32), ("hidden", C.c_int32), ("out_dim", C.c_int32), ("n_act", C.c_int32),
         ("value_index", C.c_int32), ("engine", C.c_int32), ("n_params", c_i64),
         ("params", c_vp), ("grads", c_vp), ("adam_m", c_vp), ("adam_v", c_vp), ("adam_step", c_vp),
-        ("tc_image", c_vp),
+        ("tc_image", c_vp), ("x_scratch", c_vp), ("x_scratch_bytes", c_i64),
     ]
 
 
@@ -106,6 +106,16 @@ class TsmTcwLoss(C.Structure):
                 ("heads", C.c_int32)]
 
 
+class TsmTcwEpoch(C.Structure):
+    """struct tsm_tcw_epoch (include/tsm_b200.h)."""
+
+    _fields_ = [("actor", c_vp), ("critic", c_vp), ("ximg_actor", c_vp), ("ximg_critic", c_vp), ("n_rows", c_i64), ("n_agents", C.c_int32),
+                ("super_ids", c_vp), ("n_super", c_i64), ("mb_super", c_i64), ("act", c_vp), ("adv", c_vp), ("logp_old", c_vp), ("ret", c_vp),
+                ("v_old", c_vp), ("h_mb_rows", c_vp), ("mb_stats", c_vp), ("sums_actor", c_vp), ("sums_critic", c_vp),
+                ("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float), ("max_grad_norm", C.c_float),
+                ("step0", c_i64), ("adam_ws", c_vp), ("adam_seq0", C.c_uint32)]
+
+
 c_f32, c_u64 = C.c_float, C.c_uint64
 
 _SIGS = {
@@ -154,6 +164,7 @@ _SIGS = {
     "tsm_tcw_forward": (c_i32, [c_vp, c_vp, c_i64, c_i32, c_u64, c_u64, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "tsm_tcw_train": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_f32, c_f32, c_vp, c_vp, c_vp]),
     "tsm_tcw_adam": (c_i32, [c_vp, c_i32, c_i64, c_f32, c_f32, c_f32, c_f32, c_f32, c_f32, c_vp, C.c_uint32, c_vp, c_vp]),
+    "tsm_tcw_ppo_epoch": (c_i32, [c_vp, c_vp, c_vp]),
     "tsm_tcw_adv_stats": (c_i32, [c_vp, c_i64, c_vp, c_i64, c_i64, c_i64, c_f32, c_vp, c_vp]),
     "tsm_buf_gather": (c_i32, [c_vp, c_vp, c_i64] + [c_vp] * 9 + [c_vp, c_vp, c_i32, c_vp]),
 }

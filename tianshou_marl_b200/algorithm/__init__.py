@@ -1,4 +1,5 @@
 from .ctde import CentralizedCritic, CTDEPolicy, DecentralizedActor, GlobalStateConstructor
+from .mappo import MAPPO
 from .multiagent import FlexibleMultiAgentPolicyManager
 from .ppo import A2C, PPO, AdamOptimizerFactory, DiscreteActorPolicy, Reinforce
 from .training_coordinator import SimultaneousTrainer
@@ -6,4 +7,4 @@ from .returns import compute_episodic_return, episode_mc_return_to_go, gae_flat,
 
 __all__ = ["compute_episodic_return", "episode_mc_return_to_go", "gae_flat", "gae_time_major", "PPO", "A2C", "Reinforce", "AdamOptimizerFactory",
            "DiscreteActorPolicy", "FlexibleMultiAgentPolicyManager", "CTDEPolicy", "GlobalStateConstructor",
-           "DecentralizedActor", "CentralizedCritic", "SimultaneousTrainer"]
+           "DecentralizedActor", "CentralizedCritic", "SimultaneousTrainer", "MAPPO"]

@@ -169,6 +169,22 @@ class CTDEPolicy:
     def _minibatch(self, net: ActorCriticNet, pb: Any, cfg: Any, n: int, stats: torch.Tensor | None, sums: torch.Tensor,
                    opt: AdamOptimizerFactory) -> None:
         L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr()
+        if net.engine == "tcw":  # the wide tcgen05 engine (csrc/mlp_tcw.cu): packed input image, one launch pair
+            x = pb.obs  # device address of the [n, in_dim] float32 rows (kept alive by the caller)
+            ximg = self._buf("ximg_%d" % id(net), (net.x_bytes(n),), torch.uint8)
+            _lib.check(L.tsm_tcw_pack_x(x, net.in_dim, net.in_dim, None, n, P(ximg), S))
+            tiles = _lib.TsmTcwTiles(ximg=P(ximg), n_rows=n, super_ids=None, sub=1, tile0=0, n_tiles=(n + 127) // 128)
+            if cfg.value_heads:  # critic: mse(mean over heads, td) (ctde.py:153-166)
+                loss = _lib.TsmTcwLoss(kind=2, act=None, adv=None, logp_old=None, target=pb.ret, v_old=None, weight=None, heads=cfg.value_heads)
+            else:
+                loss = _lib.TsmTcwLoss(kind=0, act=pb.act, adv=pb.adv, logp_old=None, target=None, v_old=None, weight=None, heads=0)
+            gs = float(min(2 ** int(np.ceil(np.log2(max(n, 2)))), 1048576))
+            _lib.check(L.tsm_tcw_train(net.desc, C.byref(tiles), C.byref(loss), C.byref(cfg), 1.0 / n, gs, P(stats), P(sums), S))
+            step = int(getattr(net, "_tcw_steps", 0)) + 1
+            net._tcw_steps = step
+            _lib.check(L.tsm_tcw_adam(net.desc, 1, step, opt.lr, opt.betas[0], opt.betas[1], opt.eps, 0.0, 1.0, None, 0, None, S))
+            net.kernel_updates += 1
+            return
         if net.engine == "tc":
             rec = self._buf("rec_%d" % id(net), (n, _lib.PPO_RECORD_BYTES), torch.uint8)
             _lib.check(L.tsm_ppo_pack_records(net.desc, C.byref(pb), P(rec), S))

@@ -62,7 +62,11 @@ extern "C" int tsm_collect_lockstep(const tsm_net* net, const tsm_mpe* env, cons
         const bool to_carry = (k == n_steps - 1) || (len + 1 >= size);
         float* carry = to_carry ? ro->carry : ro->obs + nxt * R * O;
         for (int p = 0; p < parts; ++p) {
-            const int64_t e0 = E * p / parts, e1 = E * (p + 1) / parts, r0 = e0 * A, nr = (e1 - e0) * A;
+            // engine 2 packs each range's rows into 128-row tiles of the net's scratch image: ranges start on a tile boundary
+            const int64_t al = (net && net->engine == 2) ? 128 : 1;
+            const int64_t e0 = p == 0 ? 0 : E * p / parts / al * al, e1 = p == parts - 1 ? E : E * (p + 1) / parts / al * al;
+            const int64_t r0 = e0 * A, nr = (e1 - e0) * A;
+            if (nr <= 0) continue;
             cudaStream_t ps = parts > 1 ? part_stream[p] : s;
             tsm_stream_t pst = parts > 1 ? reinterpret_cast<tsm_stream_t>(ps) : stream;
             if (in_carry)

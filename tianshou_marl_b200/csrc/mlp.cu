@@ -626,6 +626,8 @@ __global__ void __launch_bounds__(ADAM_THREADS) pack_image_kernel(const float* _
 
 namespace tsm {
 int tcw_net_pack(const tsm_net* net, cudaStream_t s);  // engine 2 (mlp_tcw.cu)
+int tcw_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int64_t n, int mode, int scatter, uint64_t seed, uint64_t counter,
+                    float* out, int32_t* act, float* logp, float* value, float* entropy, int64_t rng_row0, cudaStream_t s);
 int tc_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int64_t n, int mode, int scatter, uint64_t seed,
                    uint64_t counter, float* out, int32_t* act, float* logp, float* value, float* entropy, int64_t rng_row0, cudaStream_t s);
 int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_ppo_cfg* cfg, int64_t mb_start, int64_t mb_len,
@@ -675,6 +677,8 @@ extern "C" int64_t tsm_net_param_count(int in_dim, int hidden, int out_dim) { re
 static int net_forward_impl(const tsm_net* net, const float* x, const int64_t* rows, int64_t n, int mode, int scatter,
                             uint64_t seed, uint64_t counter, float* out, int32_t* act, float* logp, float* value,
                             float* entropy, int64_t rng_row0, tsm_stream_t stream) {
+    if (net && net->engine == 2)
+        return tcw_net_forward(net, x, rows, n, mode, scatter, seed, counter, out, act, logp, value, entropy, rng_row0, as_stream(stream));
     int rc = check_net(net, __func__);
     if (rc) return rc;
     TSM_REQUIRE(n >= 0 && mode >= 0 && mode <= 3, "n >= 0, 0 <= mode <= 3");

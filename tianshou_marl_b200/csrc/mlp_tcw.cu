@@ -129,7 +129,6 @@ __device__ __forceinline__ uint32_t pack_relu_h2(float a, float b) {
 }
 constexpr int BAR_READY = 1;                   // named barrier: 256 epilogue arrivals + the issuer warp
 constexpr int READY_COUNT = EPI_THREADS + 32;
-constexpr int BAR_EPI = 2;                     // named barrier among the 256 epilogue threads
 
 __device__ __forceinline__ uint64_t desc_at(uint32_t sb4, uint32_t off_bytes, uint32_t lbo, uint32_t sbo) {
     const uint32_t lo = sb4 + ((off_bytes >> 4) + ((lbo >> 4) << 16));
@@ -939,10 +938,11 @@ static int tcw_check_net(const tsm_net* n, const char* fn) {
 
 extern "C" int64_t tsm_tcw_image_bytes(int in_dim) { return in_dim >= 1 ? (int64_t)tcw::img_of(tcw::pad_in(in_dim)).total : 0; }
 
-extern "C" int64_t tsm_tcw_x_bytes(int in_dim, int64_t n_rows) {
+static int64_t tcw_x_bytes_impl(int in_dim, int64_t n_rows) {
     if (in_dim < 1 || n_rows < 0) return 0;
     return ceil_div(n_rows, tcw::ROWS) * (int64_t)(tcw::pad_in(in_dim) / 8) * tcw::CH;
 }
+extern "C" int64_t tsm_tcw_x_bytes(int in_dim, int64_t n_rows) { return tcw_x_bytes_impl(in_dim, n_rows); }
 
 namespace tsm {
 int tcw_net_pack(const tsm_net* net, cudaStream_t s) {
@@ -1006,6 +1006,28 @@ extern "C" int tsm_tcw_forward(const tsm_net* net, const void* ximg, int64_t n_r
     a.out = out; a.act = act; a.logp = logp; a.entropy = entropy;
     return a.KP <= tcw::RES_KP ? tcw_launch<false, false>(a, as_stream(stream)) : tcw_launch<true, false>(a, as_stream(stream));
 }
+
+namespace tsm {
+// engines 0 / 1 signature (float32 rows in, tsm_net_forward / tsm_net_forward_range / tsm_collect_lockstep): pack into the net's
+// scratch image, then the forward kernel.  Outputs are indexed like the input rows [0, n) (row lists gather; no scatter).
+int tcw_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int64_t n, int mode, int scatter, uint64_t seed, uint64_t counter,
+                    float* out, int32_t* act, float* logp, float* value, float* entropy, int64_t rng_row0, cudaStream_t s) {
+    int rc = tcw_check_net(net, __func__);
+    if (rc) return rc;
+    TSM_REQUIRE(n >= 0 && mode >= 0 && mode <= 3, "n >= 0, 0 <= mode <= 3");
+    if (n == 0) return TSM_OK;
+    TSM_REQUIRE(x != nullptr && !scatter, "x != NULL; engine 2 has no scatter mode");
+    TSM_REQUIRE(value == nullptr || (mode == 0 && net->n_act == 0 && net->out_dim == 1), "engine 2 nets are separate: no value head beside the logits");
+    TSM_REQUIRE(rng_row0 % tcw::ROWS == 0, "engine 2: a row range starts on a 128-row tile boundary");
+    const int64_t off = tcw_x_bytes_impl(net->in_dim, rng_row0);
+    TSM_REQUIRE(net->x_scratch && net->x_scratch_bytes >= off + tcw_x_bytes_impl(net->in_dim, n), "engine 2: net.x_scratch too small for this call");
+    unsigned char* ximg = reinterpret_cast<unsigned char*>(net->x_scratch) + off;
+    rc = tsm_tcw_pack_x(x, net->in_dim, net->in_dim, rows, n, ximg, reinterpret_cast<tsm_stream_t>(s));
+    if (rc) return rc;
+    return tsm_tcw_forward(net, ximg, n, mode, seed, counter, rng_row0, mode == 0 && value ? value : out, act, logp, entropy,
+                           reinterpret_cast<tsm_stream_t>(s));
+}
+}  // namespace tsm
 
 extern "C" int tsm_tcw_train(const tsm_net* net, const tsm_tcw_tiles* t, const tsm_tcw_loss* l, const tsm_ppo_cfg* cfg, float inv_n, float gscale,
                              const float* mb_stats, double* loss_sums, tsm_stream_t stream) {
@@ -1073,5 +1095,40 @@ extern "C" int tsm_tcw_adv_stats(const float* adv, int64_t n_rows, const int32_t
     const int64_t n_mb = ceil_div(n_super, mb_super);
     tcw::adv_stats_kernel<<<(unsigned)n_mb, 512, 0, as_stream(stream)>>>(adv, n_rows, super_ids, rows_per_super, n_super, mb_super, eps, stats);
     TSM_LAUNCH_CHECK();
+    return TSM_OK;
+}
+
+extern "C" int tsm_tcw_ppo_epoch(const tsm_tcw_epoch* e, const tsm_ppo_cfg* cfg, tsm_stream_t stream) {
+    TSM_REQUIRE(e && cfg && e->actor && e->critic && e->ximg_actor && e->ximg_critic, "epoch / cfg / nets / images != NULL");
+    TSM_REQUIRE(e->n_agents >= 1 && e->n_rows > 0 && e->n_rows % e->n_agents == 0, "n_rows = worlds x n_agents");
+    TSM_REQUIRE(e->n_super > 0 && e->mb_super > 0 && e->h_mb_rows && e->sums_actor && e->sums_critic, "n_super, mb_super > 0; h_mb_rows / sums != NULL");
+    TSM_REQUIRE(e->act && e->adv && e->logp_old && e->ret, "act / adv / logp_old / ret != NULL");
+    TSM_REQUIRE(e->critic->out_dim >= e->n_agents, "the critic needs one value head per agent");
+    const int A = e->n_agents;
+    const int64_t n_mb = ceil_div(e->n_super, e->mb_super);
+    tsm_net nets[2] = {*e->actor, *e->critic};
+    tsm_ppo_cfg ccfg = *cfg;
+    uint32_t seq = e->adam_seq0;
+    for (int64_t m = 0; m < n_mb; ++m) {
+        const int64_t s0 = m * e->mb_super, cnt = std::min(e->mb_super, e->n_super - s0);
+        const int64_t rows = e->h_mb_rows[m];
+        TSM_REQUIRE(rows > 0, "h_mb_rows > 0");
+        float gs = 1.f;
+        while (gs < (float)rows && gs < 1048576.f) gs *= 2.f;
+        const float inv_n = 1.0f / (float)rows;
+        tsm_tcw_tiles tc{e->ximg_critic, e->n_rows / A, e->super_ids, 1, s0, cnt};
+        tsm_tcw_loss lc{};
+        lc.kind = 1; lc.target = e->ret; lc.v_old = e->v_old; lc.weight = nullptr; lc.heads = A;
+        int rc = tsm_tcw_train(&nets[1], &tc, &lc, &ccfg, inv_n, gs, nullptr, e->sums_critic + 4 * m, stream);
+        if (rc) return rc;
+        tsm_tcw_tiles ta{e->ximg_actor, e->n_rows, e->super_ids, A, s0 * A, cnt * A};
+        tsm_tcw_loss la{};
+        la.kind = 0; la.act = e->act; la.adv = e->adv; la.logp_old = e->logp_old;
+        rc = tsm_tcw_train(&nets[0], &ta, &la, &ccfg, inv_n, gs, e->mb_stats ? e->mb_stats + 2 * m : nullptr, e->sums_actor + 4 * m, stream);
+        if (rc) return rc;
+        rc = tsm_tcw_adam(nets, 2, e->step0 + m + 1, e->lr, e->beta1, e->beta2, e->eps, e->max_grad_norm, 1.0f, e->adam_ws, seq, nullptr, stream);
+        if (rc) return rc;
+        if (e->max_grad_norm > 0.f) ++seq;
+    }
     return TSM_OK;
 }

@@ -232,6 +232,8 @@ class Collector:
         else:
             pol = self.policy
             mode = 2 if (pol.deterministic_eval and not pol.is_within_training_step) else 1
+            if pol.actor.engine == "tcw":
+                pol.actor.ensure_scratch(R)
             _lib.check(L.tsm_collect_lockstep(pol.actor.desc, C.byref(env._desc), C.byref(buf._desc), C.byref(ro), n_vec, mode, pol.seed,
                                               pol._counter, buf._lockstep_len, 0, C.byref(slot_o), C.byref(len_o), C.byref(carry_o), S))
             pol._counter += n_vec

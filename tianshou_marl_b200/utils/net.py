@@ -91,6 +91,8 @@ class ActorCriticNet(nn.Module):
         d.params, d.grads = self.flat.data_ptr(), self.grads.data_ptr()
         d.adam_m, d.adam_v, d.adam_step = self.adam_m.data_ptr(), self.adam_v.data_ptr(), self.adam_step.data_ptr()
         d.tc_image = self.tc_image.data_ptr() if self.tc_image is not None else None
+        xs = getattr(self, "_x_scratch", None)
+        d.x_scratch, d.x_scratch_bytes = (xs.data_ptr(), xs.numel()) if xs is not None else (None, 0)
 
     @property
     def desc(self) -> Any:
@@ -134,6 +136,14 @@ class ActorCriticNet(nn.Module):
 
     def reset_optimizer(self) -> None:
         self.grads.zero_(); self.adam_m.zero_(); self.adam_v.zero_(); self.adam_step.zero_()
+
+    def ensure_scratch(self, n_rows: int) -> None:
+        """engine "tcw": scratch image for calls that hand the library float32 rows (tsm_collect_lockstep, tsm_net_forward)."""
+        need = self.x_bytes(n_rows + 128)
+        xs = getattr(self, "_x_scratch", None)
+        if xs is None or xs.numel() < need:
+            self._x_scratch = torch.zeros(need, dtype=torch.uint8, device=self.device)
+            self._fill_desc()
 
     # -- engine "tcw": packed fp16 tile images of the inputs (tsm_tcw_pack_x) -------------------------------------------------
     def x_bytes(self, n_rows: int) -> int:
