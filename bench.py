@@ -52,8 +52,9 @@ def parse() -> argparse.Namespace:
     p.add_argument("--no-update", action="store_true", help="collect + GAE only")
     p.add_argument("--reuse-rollout", action="store_true",
                    help="PPO(reuse_rollout_policy_outputs=True): critic(obs) / logp_old come from the collect-time forward (off in the headline run)")
-    p.add_argument("--workload", default="c2", choices=["c2", "c5"],
-                   help="c2: the headline collect+GAE+PPO step; c5: GAE + buffer add/sample microbench (T=128, 1M rows), one GPU")
+    p.add_argument("--workload", default="c2", choices=["c2", "c3", "c5"],
+                   help="c2: the headline collect+GAE+PPO step; c3: MAPPO / CTDE, N = 10 agents, 32 768 worlds per GPU (BASELINE.json "
+                        "configs[2]); c5: GAE + buffer add/sample microbench (T=128, 1M rows), one GPU")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--cpu-envs", type=int, default=4096, help="reference arm: environments in the bounded sample")
     p.add_argument("--cpu-horizon", type=int, default=64)
@@ -367,7 +368,7 @@ def main() -> None:
     import torch.distributed as dist
 
     from tianshou_marl_b200 import _lib
-    from tianshou_marl_b200.bench_workload import Workload
+    from tianshou_marl_b200.bench_workload import Workload, WorkloadC3
 
     rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -383,7 +384,12 @@ def main() -> None:
     hbm_peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
     tf_peak = peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1590.0))
 
-    wl = Workload(args, rank, world)
+    if args.workload == "c3":
+        if args.envs == 65536 and args.agents == 3:  # the c2 defaults: switch to configs[2]
+            args.envs, args.agents = 32768, 10
+        wl = WorkloadC3(args, rank, world)
+    else:
+        wl = Workload(args, rank, world)
 
     def barrier() -> None:
         if world > 1:
@@ -436,7 +442,9 @@ def main() -> None:
                 "e2e": {"value": units / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                         "h2d_bytes_per_step": wl.h2d_bytes, "d2h_bytes_per_step": wl.d2h_bytes},
                 "stages_ms": stages, "roofline": roof}
-        if not args.no_cpu_baseline and world == 1:
+        if args.workload == "c3":
+            line["metric"] = "agent-steps/sec collect+MAPPO update, simple_spread N=10 (centralized critic)"
+        if not args.no_cpu_baseline and world == 1 and args.workload == "c2":
             line.update(cpu_baseline_leg(args))
         print(json.dumps(line))
     if world > 1:

@@ -144,3 +144,90 @@ class Workload:
                 "horizon": self.T, "rows_per_gpu": self.R, "batch_size": a.batch_size, "repeat": a.repeat, "hidden": a.hidden, "engine": a.engine, "reuse_rollout_policy_outputs": bool(getattr(a, "reuse_rollout", False)),
                 "minibatches_per_epoch": self.n_mb,
                 "l2": "inputs larger than L2: per-step working set %.0f MB > 126 MB" % (self.R * self.T * (8 * self.O + 30) / 1e6)}
+
+
+class WorkloadC3(Workload):
+    """BASELINE.json configs[2]: MAPPO / CTDE on simple_spread with N = 10 agents (obs 60), 262 144 worlds over 8 GPUs = 32 768 per
+    GPU: DecentralizedActor 60 -> 128 -> 128 -> 5 on every agent row, CentralizedCritic 600 -> 128 -> 128 -> 10 on every
+    (step, world) pair, engine "tcw" (csrc/mlp_tcw.cu).  One step = collect T vector steps + MAPPO.update + reset_buffer."""
+
+    def __init__(self, args: Any, rank: int, world: int) -> None:
+        from .algorithm.ctde import CentralizedCritic, DecentralizedActor
+        from .algorithm.mappo import MAPPO, TILE
+
+        self.args, self.rank, self.world = args, rank, world
+        self.E, self.A, self.T = args.envs, args.agents, args.horizon
+        self.R = self.E * self.A
+        self.env = MPEVectorEnv("simple_spread_v3", n_envs=self.E, n_agents=self.A, seed=1000 + rank)
+        self.O = self.env.obs_dim
+        self.buf = VectorReplayBuffer(self.T * self.R, self.R, index_type="torch")
+        self.net = DecentralizedActor(self.O, 5, 128, engine="tcw", orthogonal=True, seed=0)  # same init on every rank
+        self.critic = CentralizedCritic(self.A * self.O, self.A, 128, engine="tcw", orthogonal=True, seed=1)
+        self.policy = DiscreteActorPolicy(actor=self.net, seed=77 + rank)
+        self.alg = MAPPO(policy=self.policy, critic=self.critic, n_agents=self.A, optim=AdamOptimizerFactory(lr=3e-4), max_grad_norm=0.5)
+        self.collector = Collector(self.alg, self.env, self.buf, episode_list=False)
+        self.collector.reset()
+        self.policy.is_within_training_step = True
+        self.update = not args.no_update
+        self.agent_steps_per_step = self.R * self.T
+        self.dtype = "f16 operands / f32 accumulate (tcgen05)"
+        n_super = (self.T * self.E + TILE - 1) // TILE
+        self.mb_super = max(1, int(round(args.batch_size / (TILE * self.A))))
+        self.n_mb = (n_super + self.mb_super - 1) // self.mb_super
+        parts = 2 if self.E >= 8192 else 1
+        self.launches_per_step = self.T * parts * (2 * K_POLICY + K_ROLLOUT_STEP) + 1  # pack + forward + rollout step per range
+        if self.update:
+            # pack x2, critic forward, values_next + pack + critic on ended worlds, logp_old, gae; per epoch adv stats + 3 launches per minibatch
+            self.launches_per_step += 8 + args.repeat * (1 + 3 * self.n_mb)
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+        self.last_stats = None
+
+    def step_e2e(self) -> None:
+        super().step_e2e()
+        n_super = self.n_mb * self.mb_super
+        self.h2d_bytes = (4 * n_super + 8 * self.n_mb) * (self.args.repeat if self.update else 0)  # super-tile order + rows per minibatch
+        if self.update:
+            self.d2h_bytes += self.last_stats.gradient_steps * 4 * 8  # second loss-sum array (critic)
+
+    def roofline(self, stages: dict, hbm_peak: float, peak_src: str, tf_peak: float) -> dict:
+        O, A, H = self.O, self.A, 128
+        mac_a, mac_a_dx = O * H + H * H + H * 5, H * H + H * 5          # actor: forward MACs; data-gradient MACs (no dX of layer 1)
+        mac_c, mac_c_dx = A * O * H + H * H + H * A, H * H + H * A      # critic, per (step, world) pair
+        flop_row = 2.0 * (2 * mac_a + mac_a_dx) + 2.0 * (2 * mac_c + mac_c_dx) / A  # forward + weight gradients + data gradients, per agent row
+        B = self.R * self.T
+        if not stages:
+            return {}
+        dom = max(stages, key=lambda k: stages[k]["ms_per_step"])
+        out: dict[str, Any] = {"kernel": dom, "peak_source": peak_src}
+        if dom == "ppo_epoch":
+            t = stages[dom]["launch_ms"] * 1e-3  # one epoch: n_mb x (critic launch, actor launch, optimizer launch)
+            ach = flop_row * B / t / 1e12
+            bytes_row = 2.0 * (O + 4) + 12.0 + (2.0 * (A * O + 8) + 8.0 * A) / A  # packed fp16 inputs + row scalars, per agent row
+            out.update({"kernel": "tcw_kernel<resident|streaming, train> (actor + centralized critic) + tcw_adam_kernel", "bound": "tensor",
+                        "achieved": ach, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach / tf_peak, "traffic": None,
+                        "flop_per_unit": flop_row, "bytes_per_unit": bytes_row, "units_per_launch": B, "launch_us": t * 1e6,
+                        "minibatch_us": t * 1e6 / self.n_mb, "hbm_gbs": bytes_row * B / t / 1e9,
+                        "note": "per minibatch: critic tiles (K = 608 streamed, W1 gradient flushed per tile), actor tiles (weights resident), "
+                                "joint-clip Adam over both nets; %d minibatches of %d super-tiles per epoch" % (self.n_mb, self.mb_super)})
+        else:
+            per_unit_bytes = {"collect": (16 * A * 2 + 8 * A + 4 * A + 8 * A * O + 6 * A) / A + 4.0 * O + 12.0 + 8.0, "gae": 22.0,
+                              "pack_inputs": 4.0 * O + 2.0 * (O + 4) + (4.0 * O * A + 2.0 * (A * O + 8)) / A,
+                              "critic_forward": 2.0 * (A * O + 8) / A + 4.0, "logp_old_forward": 2.0 * (O + 4) + 8.0, "adv_stats": 4.0}
+            ach = per_unit_bytes.get(dom, 0.0) * B / (stages[dom]["launch_ms"] * 1e-3) / 1e9
+            out.update({"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak, "traffic": None,
+                        "bytes_per_unit": per_unit_bytes.get(dom), "units_per_launch": B})
+        if "gae" in stages:
+            g = 22.0 * B / (stages["gae"]["launch_ms"] * 1e-3) / 1e9
+            out["gae"] = {"achieved": g, "frac": g / hbm_peak, "unit": "GB/s", "peak": hbm_peak}
+        return out
+
+    def config(self) -> dict:
+        a = self.args
+        what = "collect+GAE+MAPPO update" if self.update else "collect+buffer write (no update)"
+        return {"workload": f"C3 simple_spread N={self.A} agents E={self.E}/GPU T={self.T}: {what}; DecentralizedActor {self.O}->128->128->5, "
+                            f"CentralizedCritic {self.A * self.O}->128->128->{self.A} on the concatenated global state",
+                "envs_per_gpu": self.E, "agents": self.A, "horizon": self.T, "rows_per_gpu": self.R, "batch_size": a.batch_size,
+                "rows_per_minibatch": self.mb_super * 128 * self.A, "repeat": a.repeat, "hidden": 128, "engine": "tcw",
+                "minibatches_per_epoch": self.n_mb,
+                "l2": "inputs larger than L2: per-step working set %.0f MB > 126 MB" % (self.R * self.T * (8 * self.O + 30) / 1e6)}
