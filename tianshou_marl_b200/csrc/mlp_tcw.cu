@@ -70,7 +70,7 @@ constexpr int SM_STR_TOTAL = SM_RING + STAGES * 2 * SLICE_B;
 static_assert(SM_RES_TOTAL <= 227 * 1024 && SM_STR_TOTAL <= 227 * 1024, "shared-memory map exceeds an SM");
 
 // mbarrier slots
-enum { B_MAIN = 0, B_XFULL = 1 /*2*/, B_XEMPTY = 3 /*2*/, B_FULL = 5 /*STAGES*/, B_EMPTY = 7 /*STAGES*/, B_DONE = 9 /*2*/, B_FREE = 11 /*2*/ };
+enum { B_MAIN = 0, B_XFULL = 1 /*2*/, B_XEMPTY = 3 /*2*/, B_FULL = 5 /*STAGES*/, B_EMPTY = 7 /*STAGES*/, B_DONE = 9 /*2*/, B_FREE = 11 /*2*/, B_W = 13 };
 
 // TMEM columns (fp32, 128 lanes)
 constexpr uint32_t TM_SCR = 0;     // 128: H1pre / H2pre / DH2 / DH1 in turn
@@ -110,6 +110,27 @@ __host__ __device__ inline int64_t image_index(int64_t i, const Offsets& o, int 
         return im.w3 / 2 + ((int64_t)(in >> 3) * OP + out) * 8 + (in & 7);
     }
     return im.w3 / 2 + ((int64_t)(H >> 3) * OP + (i - o.b3)) * 8;
+}
+
+// the same with 32-bit arithmetic (device hot path of the optimizer kernel; n_params < 2^31)
+__device__ __forceinline__ int image_index32(int i, const Offsets& o, int in_dim, int KP) {
+    const int b1 = (int)o.b1, w2 = (int)o.w2, b2 = (int)o.b2, w3 = (int)o.w3, b3 = (int)o.b3;
+    const int iw2 = KP * H, iw3 = iw2 + W2_BYTES / 2;  // halves offsets of the W2 / W3 images
+    if (i < b1) {
+        const int out = i / in_dim, in = i - out * in_dim;
+        return ((in >> 3) * H + out) * 8 + (in & 7);
+    }
+    if (i < w2) return (((KP - 1) >> 3) * H + (i - b1)) * 8 + ((KP - 1) & 7);
+    if (i < b2) {
+        const int rel = i - w2, out = rel >> 7, in = rel & 127;
+        return iw2 + ((in >> 3) * H + out) * 8 + (in & 7);
+    }
+    if (i < w3) return iw2 + ((H >> 3) * H + (i - b2)) * 8;
+    if (i < b3) {
+        const int rel = i - w3, out = rel >> 7, in = rel & 127;
+        return iw3 + ((in >> 3) * OP + out) * 8 + (in & 7);
+    }
+    return iw3 + ((H >> 3) * OP + (i - b3)) * 8;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -176,6 +197,15 @@ struct Args {
     const float* mb_stats;        // optional (mean, rstd) of the minibatch advantages
     double* loss_sums;            // [4]: clip, vf, ent, rows
 };
+
+// Instrumented builds only (tools/tcw_trace.py, -DTSM_TCW_TRACE): clock64 stamps of CTA 0 -- slots 0..63 by the first epilogue
+// thread, 64..127 by the MMA issuer lane, 128..191 by the producer lane.
+#ifdef TSM_TCW_TRACE
+__device__ long long g_tcw_trace[192];
+#define TCW_TRACE(slot) do { if (blockIdx.x == 0 && (slot) < 192) g_tcw_trace[slot] = clock64(); } while (0)
+#else
+#define TCW_TRACE(slot) do { } while (0)
+#endif
 
 struct Ctx {
     unsigned char* smem;
@@ -257,6 +287,7 @@ __device__ __forceinline__ Ctx setup(unsigned char* smem, const Args& a) {
     if (c.warp == 0) tc::tmem_alloc(tmem_s, TM_COLS);
     if (c.tid == 32) {
         tc::mbar_init(c.bar + B_MAIN, 1);
+        tc::mbar_init(c.bar + B_W, 1);
         for (int i = 0; i < 2; ++i) {
             tc::mbar_init(c.bar + B_XFULL + i, 1);
             tc::mbar_init(c.bar + B_XEMPTY + i, 1);
@@ -266,18 +297,15 @@ __device__ __forceinline__ Ctx setup(unsigned char* smem, const Args& a) {
             tc::mbar_init(c.bar + B_FREE + i, EPI_THREADS);
         }
         tc::fence_barrier_init();
-    }
-    const Img im = img_of(a.KP);
-    // W2 | W3 are adjacent in the image and in shared memory
-    {
-        const uint4* src = reinterpret_cast<const uint4*>(a.image + im.w2);
-        uint4* dst = reinterpret_cast<uint4*>(smem + SM_W2);
-        for (int i = c.tid; i < (W2_BYTES + W3_BYTES) / 16; i += THREADS) dst[i] = __ldg(src + i);
-    }
-    if (!STREAM) {
-        const uint4* src = reinterpret_cast<const uint4*>(a.image + im.w1);
-        uint4* dst = reinterpret_cast<uint4*>(smem + SM_RW1);
-        for (int i = c.tid; i < a.KP * H * 2 / 16; i += THREADS) dst[i] = __ldg(src + i);
+        tc::fence_async_smem();
+        // weight images by TMA bulk copies (W2 | W3 are adjacent in the image and in shared memory; W1 when resident): the
+        // issuer warp waits for B_W before its first MMA, nobody else reads them.  (Per-thread 16-byte copy loops cost 4.4 k
+        // cycles of dependent L2 round trips here.)
+        const Img im = img_of(a.KP);
+        const uint32_t w1b = STREAM ? 0u : (uint32_t)(a.KP * H * 2);
+        tc::mbar_expect_tx(c.bar + B_W, (uint32_t)(W2_BYTES + W3_BYTES) + w1b);
+        tc::bulk_g2s(smem + SM_W2, a.image + im.w2, (uint32_t)(W2_BYTES + W3_BYTES), c.bar + B_W);
+        if (!STREAM) tc::bulk_g2s(smem + SM_RW1, a.image + im.w1, w1b, c.bar + B_W);
     }
     // ones feature (index 128 = element 0 of chunk 16) of H1 and H2, chunk 17 zero; G zero
     for (int i = c.tid; i < 2 * ROWS; i += THREADS) {
@@ -461,40 +489,44 @@ __device__ __forceinline__ void output_stage(const Ctx& c, const Args& a, int64_
 }
 
 // ---------------------------------------------------------------------------------------------
-// flush of the TMEM-resident gradient accumulators (after the last tile of the CTA): 16-byte reductions into the flat
-// gradient buffer where the row stride allows, scalar ones otherwise
-__device__ __forceinline__ void red_row(float* base, const float* v, int n, float s) {  // n values to consecutive addresses
-    if ((reinterpret_cast<uintptr_t>(base) & 15) == 0) {
-        int k = 0;
-        for (; k + 4 <= n; k += 4) red_add_v4(base + k, v[k] * s, v[k + 1] * s, v[k + 2] * s, v[k + 3] * s);
-        for (; k < n; ++k) atomicAdd(base + k, v[k] * s);
-    } else {
-        for (int k = 0; k < n; ++k) atomicAdd(base + k, v[k] * s);
-    }
-}
+// flush of the TMEM-resident gradient accumulators (after the last tile of the CTA, all MMAs complete: shared memory is free).
+// The accumulators are laid down in shared memory at their FLAT gradient positions, then added to the global gradient with
+// fully coalesced 16-byte reductions (a warp instruction = 512 contiguous bytes = four L2 lines).  Measured on B200 before
+// this staging (per-thread row-strided reductions straight from TMEM registers): 43 k of the actor kernel's 79 k cycles.
+// The W2 block (lane = row, 32 float4 per row) is stored with its float4 column XORed by (row & 7): conflict-free on both sides.
+__device__ __forceinline__ void epi_sync() { asm volatile("bar.sync 2, 256;" ::: "memory"); }
 
 template <bool STREAM>
 __device__ __forceinline__ void flush_grads(const Ctx& c, const Args& a, const LossAcc& acc) {
     const Offsets o = offsets(a.in_dim, H, a.out_dim);
     const float s = a.inv_gscale;
+    const int64_t base = STREAM ? o.w2 : 0;  // the streaming path has flushed the W1 / b1 part tile by tile
+    float* stg = reinterpret_cast<float*>(c.smem);
+    float4* stg4 = reinterpret_cast<float4*>(c.smem);
+    const int w2q = (int)((o.w2 - base) >> 2);  // float4 index of the W2 block
     // W2 gradient: lane = out, columns = in (0..127), column 128 = b2
 #pragma unroll
     for (int q = 0; q < 2; ++q) {
         float v[32];
         tc::tmem_ld32(c.lane_base + TM_GW2 + 64 * c.half + 32 * q, v);
-        red_row(a.grads + o.w2 + (int64_t)c.row * H + 64 * c.half + 32 * q, v, 32, s);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int c4 = 16 * c.half + 8 * q + j;
+            stg4[w2q + c.row * 32 + (c4 ^ (c.row & 7))] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        }
     }
     if (c.half == 1) {
         float v[8];
         tc::tmem_ld8(c.lane_base + TM_GW2 + H, v);
-        atomicAdd(a.grads + o.b2 + c.row, v[0] * s);
+        stg[o.b2 - base + c.row] = v[0];
+        if (c.row < a.out_dim) stg[o.b3 - base + c.row] = 0.f;  // b3 goes straight to global memory below
     } else {
         // W3 gradient: lane = in (H2 feature), column = output j
         float v[16];
         tc::tmem_ld16(c.lane_base + TM_GW3, v);
 #pragma unroll
         for (int j = 0; j < OP; ++j)
-            if (j < a.out_dim) atomicAdd(a.grads + o.w3 + (int64_t)j * H + c.row, v[j] * s);
+            if (j < a.out_dim) stg[o.w3 - base + j * H + c.row] = v[j];
         // b3 gradient: fp32 register sums of the loss stage (unscaled), reduced over the warp
 #pragma unroll
         for (int j = 0; j < OP; ++j) {
@@ -514,11 +546,25 @@ __device__ __forceinline__ void flush_grads(const Ctx& c, const Args& a, const L
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 const int k = col + j;
-                if (k < a.in_dim) atomicAdd(a.grads + o.w1 + (int64_t)c.row * a.in_dim + k, v[j] * s);
-                else if (k == a.KP - 1) atomicAdd(a.grads + o.b1 + c.row, v[j] * s);
+                if (k < a.in_dim) stg[c.row * a.in_dim + k] = v[j];
+                else if (k == a.KP - 1) stg[o.b1 + c.row] = v[j];
             }
         }
     }
+    epi_sync();
+    const int total = (int)(o.total - base), n4 = total >> 2;
+    float* g = a.grads + base;
+    for (int F = c.tid; F < n4; F += EPI_THREADS) {
+        int idx = F;
+        const int rel = F - w2q;
+        if (rel >= 0 && rel < H * H / 4) {
+            const int r = rel >> 5, c4 = rel & 31;
+            idx = w2q + r * 32 + (c4 ^ (r & 7));
+        }
+        const float4 v = stg4[idx];
+        red_add_v4(g + 4 * F, v.x * s, v.y * s, v.z * s, v.w * s);
+    }
+    for (int i = 4 * n4 + c.tid; i < total; i += EPI_THREADS) atomicAdd(g + i, stg[i] * s);
 }
 
 __device__ __forceinline__ void flush_losses(const Ctx& c, const Args& a, const LossAcc& acc) {
@@ -538,7 +584,9 @@ __device__ __forceinline__ void flush_losses(const Ctx& c, const Args& a, const 
 template <bool STREAM, bool TRAIN>
 __global__ void __launch_bounds__(THREADS, 1) tcw_kernel(Args a) {
     extern __shared__ __align__(1024) unsigned char smem[];
+    if (threadIdx.x == 0) TCW_TRACE(0);
     Ctx c = setup<STREAM>(smem, a);
+    if (threadIdx.x == 0) TCW_TRACE(1);
     const int KP = a.KP;
     const int n_slices = (KP + SLICE - 1) / SLICE;
     const int64_t tile_bytes = (int64_t)(KP / 8) * CH;
@@ -585,7 +633,11 @@ __global__ void __launch_bounds__(THREADS, 1) tcw_kernel(Args a) {
         // ================= MMA issuer =================
         constexpr uint32_t ID_H = tc::make_idesc_f16(128, H, 0, 0, 0, 0);
         uint32_t it = 0, blk = 0;
+        tc::mbar_wait(c.bar + B_W, 0);  // weight images have landed
         for (int64_t i = 0; i < my_tiles; ++i) {
+            const int ib = 64 + 12 * (int)i;
+            (void)ib;
+            if ((threadIdx.x & 31) == 0) TCW_TRACE(ib);
             // ---- layer 1 ----
             if (!STREAM) {
                 const int b = (int)(i & 1);
@@ -614,16 +666,21 @@ __global__ void __launch_bounds__(THREADS, 1) tcw_kernel(Args a) {
                     __syncwarp();
                 }
             }
+            if ((threadIdx.x & 31) == 0) TCW_TRACE(ib + 1);  // layer 1 issued
             // ---- layer 2 ----
             bar_sync(BAR_READY, READY_COUNT);
             tc::fence_after_sync();
+            if ((threadIdx.x & 31) == 0) TCW_TRACE(ib + 2);  // H1 ready seen
             if (tc::elect_one()) { issue_l2(c); tc::commit(c.bar + B_MAIN); }
             __syncwarp();
+            if ((threadIdx.x & 31) == 0) TCW_TRACE(ib + 3);  // layer 2 issued
             // ---- layer 3 ----
             bar_sync(BAR_READY, READY_COUNT);
             tc::fence_after_sync();
+            if ((threadIdx.x & 31) == 0) TCW_TRACE(ib + 4);
             if (tc::elect_one()) { issue_l3(c); tc::commit(c.bar + B_MAIN); }
             __syncwarp();
+            if ((threadIdx.x & 31) == 0) TCW_TRACE(ib + 5);
             if (!TRAIN) {
                 bar_sync(BAR_READY, READY_COUNT);  // OUT has been read: the next tile may overwrite SCR / OUT
                 tc::fence_after_sync();
@@ -646,9 +703,11 @@ __global__ void __launch_bounds__(THREADS, 1) tcw_kernel(Args a) {
                 issue_gw2(c, i == 0);
             }
             __syncwarp();
+            if ((threadIdx.x & 31) == 0) TCW_TRACE(ib + 6);  // W3 gradient, DH1, W2 gradient issued
             // ---- D1 ready: W1 gradient ----
             bar_sync(BAR_READY, READY_COUNT);
             tc::fence_after_sync();
+            if ((threadIdx.x & 31) == 0) TCW_TRACE(ib + 7);
             if (!STREAM) {
                 if (tc::elect_one()) {
                     const int b = (int)(i & 1);
@@ -679,6 +738,7 @@ __global__ void __launch_bounds__(THREADS, 1) tcw_kernel(Args a) {
                 }
             }
         }
+        if ((threadIdx.x & 31) == 0) TCW_TRACE(127);
         if (TRAIN) {  // everything issued: one last commit the epilogue threads wait for before the flush
             if (tc::elect_one()) tc::commit(c.bar + B_MAIN);
             __syncwarp();
@@ -702,13 +762,21 @@ __global__ void __launch_bounds__(THREADS, 1) tcw_kernel(Args a) {
                 side[1] = a.logp_old ? __ldg(a.logp_old + prow) : 0.f;
                 act_reg = __ldg(a.act + prow);
             }
+            const int tb = 2 + 12 * (int)i;  // trace slots of this tile (first 5 tiles)
+            (void)tb;
+            if (c.tid == 0) TCW_TRACE(tb);
             wait_main(c);  // layer 1 done
+            if (c.tid == 0) TCW_TRACE(tb + 1);
             epi_relu(c, SM_H1);
             ready(c);
+            if (c.tid == 0) TCW_TRACE(tb + 2);
             wait_main(c);  // layer 2 done
+            if (c.tid == 0) TCW_TRACE(tb + 3);
             epi_relu(c, SM_H2);
             ready(c);
+            if (c.tid == 0) TCW_TRACE(tb + 4);
             wait_main(c);  // layer 3 done
+            if (c.tid == 0) TCW_TRACE(tb + 5);
             if (!TRAIN) {
                 if (c.half == 0) output_stage(c, a, prow, valid);
                 ready(c);
@@ -716,12 +784,17 @@ __global__ void __launch_bounds__(THREADS, 1) tcw_kernel(Args a) {
             }
             if (c.half == 0) loss_stage(c, a, prow, valid, acc, side, act_reg);
             ready(c);
+            if (c.tid == 0) TCW_TRACE(tb + 6);
             wait_main(c);  // DH2 done
+            if (c.tid == 0) TCW_TRACE(tb + 7);
             epi_mask(c, SM_H2, SM_D2);
             ready(c);
+            if (c.tid == 0) TCW_TRACE(tb + 8);
             wait_main(c);  // W3 gradient + DH1 done: H2 may be overwritten by D1
+            if (c.tid == 0) TCW_TRACE(tb + 9);
             epi_mask(c, SM_H1, SM_D1);
             ready(c);
+            if (c.tid == 0) TCW_TRACE(tb + 10);
             if (STREAM) {
                 // W1 gradient of this tile, 64 input features per TMEM block: flush straight to the gradient buffer
                 for (int sl = 0; sl < n_slices; ++sl, ++blk) {
@@ -734,26 +807,44 @@ __global__ void __launch_bounds__(THREADS, 1) tcw_kernel(Args a) {
                     if (mine) tc::tmem_ld32(c.lane_base + TM_GW1 + 64 * bk + 32 * c.half, v);
                     tc::fence_before_sync();
                     mbar_arrive(c.bar + B_FREE + bk);
+                    // stage the block (row = out, 16 float4 slots per row, column XORed by row & 7), then coalesced reductions.
+                    // Two staging buffers (H1's first 16 chunks / D2: both free once the first block is done, because every MMA
+                    // that read them was issued before it): the barrier of block b + 1 also fences the readers of block b.
+                    float4* st4 = reinterpret_cast<float4*>(smem + (bk ? SM_D2 : SM_H1));
                     if (mine) {
-                        const int k0 = sl * SLICE + 32 * c.half;
-                        float* dst = a.grads + o.w1 + (int64_t)c.row * a.in_dim + k0;
-                        if (k0 + 32 <= a.in_dim && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+                        const float s = a.inv_gscale;
 #pragma unroll
-                            for (int k = 0; k < 32; k += 4) red_add_v4(dst + k, v[k] * a.inv_gscale, v[k + 1] * a.inv_gscale, v[k + 2] * a.inv_gscale, v[k + 3] * a.inv_gscale);
+                        for (int j = 0; j < 8; ++j)
+                            st4[c.row * 16 + ((8 * c.half + j) ^ (c.row & 7))] = make_float4(v[4 * j] * s, v[4 * j + 1] * s, v[4 * j + 2] * s, v[4 * j + 3] * s);
+                    }
+                    epi_sync();
+                    const int q4 = nk >> 2;
+                    const bool vec = (a.in_dim & 3) == 0;
+                    for (int F = c.tid; F < ROWS * q4; F += EPI_THREADS) {
+                        const int r = F / q4, c4 = F - r * q4;
+                        const float4 val = st4[r * 16 + (c4 ^ (r & 7))];
+                        const int k0 = sl * SLICE + 4 * c4;
+                        float* dst = a.grads + o.w1 + (int64_t)r * a.in_dim + k0;
+                        if (vec && k0 + 4 <= a.in_dim) {
+                            red_add_v4(dst, val.x, val.y, val.z, val.w);
                         } else {
+                            const float e[4] = {val.x, val.y, val.z, val.w};
 #pragma unroll
-                            for (int k = 0; k < 32; ++k) {
-                                if (k0 + k < a.in_dim) atomicAdd(dst + k, v[k] * a.inv_gscale);
-                                else if (k0 + k == KP - 1) atomicAdd(a.grads + o.b1 + c.row, v[k] * a.inv_gscale);
+                            for (int u = 0; u < 4; ++u) {
+                                if (k0 + u < a.in_dim) atomicAdd(dst + u, e[u]);
+                                else if (k0 + u == KP - 1) atomicAdd(a.grads + o.b1 + r, e[u]);
                             }
                         }
                     }
                 }
+                epi_sync();  // the staging buffers alias H1 / D2: nobody writes the next tile's activations while a block is being read
             }
         }
         if (TRAIN) {
+            if (c.tid == 0) TCW_TRACE(62);
             if (my_tiles > 0) {
                 wait_main(c);  // all MMAs of this CTA have completed
+                if (c.tid == 0) TCW_TRACE(63);
                 flush_grads<STREAM>(c, a, acc);
             }
             flush_losses(c, a, acc);
@@ -761,6 +852,7 @@ __global__ void __launch_bounds__(THREADS, 1) tcw_kernel(Args a) {
     }
     tc::fence_before_sync();
     __syncthreads();
+    if (threadIdx.x == 0) TCW_TRACE(191);
     if (c.warp == 0) tc::tmem_dealloc(c.tmem, TM_COLS);
 }
 
@@ -836,9 +928,13 @@ __global__ void __launch_bounds__(256) tcw_adam_kernel(AdamJob j) {
         double acc = 0.0;
         for (int t = 0; t < j.n_nets; ++t) {
             const AdamNet& n = j.net[t];
-            for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n.n; i += (int64_t)gridDim.x * blockDim.x) {
-                const float g = __ldcg(n.g + i) * j.grad_scale;
-                acc += (double)g * (double)g;
+            const int cnt = (int)n.n, stride = (int)(gridDim.x * blockDim.x);
+            for (int i0 = (int)(blockIdx.x * blockDim.x + threadIdx.x); i0 < cnt; i0 += 4 * stride) {
+                float g[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) g[u] = i0 + u * stride < cnt ? __ldcg(n.g + i0 + u * stride) * j.grad_scale : 0.f;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) acc += (double)g[u] * (double)g[u];
             }
         }
 #pragma unroll
@@ -869,14 +965,28 @@ __global__ void __launch_bounds__(256) tcw_adam_kernel(AdamJob j) {
     }
     const double bc1 = 1.0 - opt::ipow((double)j.beta1, j.step), bc2 = 1.0 - opt::ipow((double)j.beta2, j.step);
     const float step_size = (float)((double)j.lr / bc1), bc2_sqrt = (float)sqrt(bc2);
+    const int stride = (int)(gridDim.x * blockDim.x);
     for (int t = 0; t < j.n_nets; ++t) {
         const AdamNet& n = j.net[t];
         const Offsets o = offsets(n.in_dim, H, n.out_dim);
-        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n.n; i += (int64_t)gridDim.x * blockDim.x) {
-            float m = n.m[i], v = n.v[i];
-            const float pn = opt::adam_elem(n.p[i], __ldcg(n.g + i), m, v, coef, step_size, bc2_sqrt, j.beta1, j.beta2, j.eps);
-            n.p[i] = pn; n.m[i] = m; n.v[i] = v; n.g[i] = 0.f;
-            if (n.image) n.image[image_index(i, o, n.in_dim, n.KP)] = __float2half_rn(pn);
+        const int cnt = (int)n.n;
+        // four independent elements per thread and pass: the loads of all four are in flight together
+        for (int i0 = (int)(blockIdx.x * blockDim.x + threadIdx.x); i0 < cnt; i0 += 4 * stride) {
+            float p[4], g[4], m[4], v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int i = i0 + u * stride;
+                if (i < cnt) { p[u] = n.p[i]; g[u] = __ldcg(n.g + i); m[u] = n.m[i]; v[u] = n.v[i]; }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int i = i0 + u * stride;
+                if (i < cnt) {
+                    const float pn = opt::adam_elem(p[u], g[u], m[u], v[u], coef, step_size, bc2_sqrt, j.beta1, j.beta2, j.eps);
+                    n.p[i] = pn; n.m[i] = m[u]; n.v[i] = v[u]; n.g[i] = 0.f;
+                    if (n.image) n.image[image_index32(i, o, n.in_dim, n.KP)] = __float2half_rn(pn);
+                }
+            }
         }
         if (blockIdx.x == 0 && threadIdx.x == 0 && n.step_out) *n.step_out = j.step;
     }
@@ -971,14 +1081,14 @@ extern "C" int tsm_tcw_pack_x(const float* x, int64_t ld, int in_dim, const int6
 }
 
 template <bool STREAM, bool TRAIN>
-static int tcw_launch(const tcw::Args& a, cudaStream_t s) {
+static int tcw_launch(const tcw::Args& a, cudaStream_t s, int max_ctas = 0) {
     const size_t smem = STREAM ? tcw::SM_STR_TOTAL : tcw::SM_RES_TOTAL;
     static bool attr = false;
     if (!attr) {
         TSM_CUDA(cudaFuncSetAttribute(tcw::tcw_kernel<STREAM, TRAIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr = true;
     }
-    const unsigned grid = (unsigned)std::min<int64_t>(a.n_tiles, (int64_t)sm_count());
+    const unsigned grid = (unsigned)std::min<int64_t>(a.n_tiles, (int64_t)(max_ctas > 0 ? max_ctas : sm_count()));
     tcw::tcw_kernel<STREAM, TRAIN><<<grid, tcw::THREADS, smem, s>>>(a);
     TSM_LAUNCH_CHECK();
     return TSM_OK;
@@ -1029,8 +1139,16 @@ int tcw_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int
 }
 }  // namespace tsm
 
+static int tcw_train_impl(const tsm_net* net, const tsm_tcw_tiles* t, const tsm_tcw_loss* l, const tsm_ppo_cfg* cfg, float inv_n, float gscale,
+                          const float* mb_stats, double* loss_sums, cudaStream_t stream, int max_ctas);
+
 extern "C" int tsm_tcw_train(const tsm_net* net, const tsm_tcw_tiles* t, const tsm_tcw_loss* l, const tsm_ppo_cfg* cfg, float inv_n, float gscale,
                              const float* mb_stats, double* loss_sums, tsm_stream_t stream) {
+    return tcw_train_impl(net, t, l, cfg, inv_n, gscale, mb_stats, loss_sums, as_stream(stream), 0);
+}
+
+static int tcw_train_impl(const tsm_net* net, const tsm_tcw_tiles* t, const tsm_tcw_loss* l, const tsm_ppo_cfg* cfg, float inv_n, float gscale,
+                          const float* mb_stats, double* loss_sums, cudaStream_t stream, int max_ctas) {
     int rc = tcw_check_net(net, __func__);
     if (rc) return rc;
     TSM_REQUIRE(t && l && cfg && net->grads, "tiles / loss / cfg / net.grads != NULL");
@@ -1040,6 +1158,7 @@ extern "C" int tsm_tcw_train(const tsm_net* net, const tsm_tcw_tiles* t, const t
     if (l->kind != 0) TSM_REQUIRE(l->target && l->heads >= 1 && l->heads <= net->out_dim, "value loss needs target and 1 <= heads <= out_dim");
     if (l->kind == 1 && cfg->value_clip) TSM_REQUIRE(l->v_old != nullptr, "value_clip needs v_old");
     TSM_REQUIRE(gscale > 0.f && inv_n > 0.f, "gscale > 0, inv_n > 0");
+    TSM_REQUIRE((reinterpret_cast<uintptr_t>(net->grads) & 15) == 0, "net.grads must be 16-byte aligned");
     if (t->n_tiles == 0) return TSM_OK;
     tcw::Args a{};
     tcw_fill_net(a, net);
@@ -1052,7 +1171,7 @@ extern "C" int tsm_tcw_train(const tsm_net* net, const tsm_tcw_tiles* t, const t
     a.cfg.value_clip = cfg->value_clip; a.cfg.adv_norm = cfg->adv_norm; a.cfg.plain_pg = cfg->plain_pg; a.cfg.value_heads = 0;
     a.inv_n = inv_n; a.gscale = gscale; a.inv_gscale = 1.0f / gscale;
     a.mb_stats = mb_stats; a.loss_sums = loss_sums;
-    return a.KP <= tcw::RES_KP ? tcw_launch<false, true>(a, as_stream(stream)) : tcw_launch<true, true>(a, as_stream(stream));
+    return a.KP <= tcw::RES_KP ? tcw_launch<false, true>(a, stream, max_ctas) : tcw_launch<true, true>(a, stream, max_ctas);
 }
 
 extern "C" int tsm_tcw_adam(const tsm_net* nets, int n_nets, int64_t step, float lr, float beta1, float beta2, float eps, float max_grad_norm,
@@ -1109,6 +1228,23 @@ extern "C" int tsm_tcw_ppo_epoch(const tsm_tcw_epoch* e, const tsm_ppo_cfg* cfg,
     tsm_net nets[2] = {*e->actor, *e->critic};
     tsm_ppo_cfg ccfg = *cfg;
     uint32_t seq = e->adam_seq0;
+    cudaStream_t s = as_stream(stream);
+    // The critic's tiles of a minibatch (one per 128 worlds) occupy a third of the SMs for about as long as the actor's tiles
+    // occupy the rest: the two launches run side by side, the critic on a forked stream, and join before the optimizer.
+    static const bool two = !(getenv("TSM_TCW_STREAMS") && atoi(getenv("TSM_TCW_STREAMS")) == 1);
+    static cudaStream_t side = nullptr;
+    static cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    static int ev_device = -1;
+    if (two) {
+        int dev = 0;
+        TSM_CUDA(cudaGetDevice(&dev));
+        if (ev_device != dev) {  // (one device per process)
+            TSM_CUDA(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
+            TSM_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+            TSM_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+            ev_device = dev;
+        }
+    }
     for (int64_t m = 0; m < n_mb; ++m) {
         const int64_t s0 = m * e->mb_super, cnt = std::min(e->mb_super, e->n_super - s0);
         const int64_t rows = e->h_mb_rows[m];
@@ -1116,19 +1252,35 @@ extern "C" int tsm_tcw_ppo_epoch(const tsm_tcw_epoch* e, const tsm_ppo_cfg* cfg,
         float gs = 1.f;
         while (gs < (float)rows && gs < 1048576.f) gs *= 2.f;
         const float inv_n = 1.0f / (float)rows;
+        const bool split = two && cnt * 2 <= sm_count();  // critic CTAs + actor CTAs fit side by side
         tsm_tcw_tiles tc{e->ximg_critic, e->n_rows / A, e->super_ids, 1, s0, cnt};
         tsm_tcw_loss lc{};
         lc.kind = 1; lc.target = e->ret; lc.v_old = e->v_old; lc.weight = nullptr; lc.heads = A;
-        int rc = tsm_tcw_train(&nets[1], &tc, &lc, &ccfg, inv_n, gs, nullptr, e->sums_critic + 4 * m, stream);
+        if (split) {
+            TSM_CUDA(cudaEventRecord(ev_fork, s));
+            TSM_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
+        }
+        int rc = tcw_train_impl(&nets[1], &tc, &lc, &ccfg, inv_n, gs, nullptr, e->sums_critic + 4 * m, split ? side : s, 0);
         if (rc) return rc;
+        if (split) TSM_CUDA(cudaEventRecord(ev_join, side));
         tsm_tcw_tiles ta{e->ximg_actor, e->n_rows, e->super_ids, A, s0 * A, cnt * A};
         tsm_tcw_loss la{};
         la.kind = 0; la.act = e->act; la.adv = e->adv; la.logp_old = e->logp_old;
-        rc = tsm_tcw_train(&nets[0], &ta, &la, &ccfg, inv_n, gs, e->mb_stats ? e->mb_stats + 2 * m : nullptr, e->sums_actor + 4 * m, stream);
+        rc = tcw_train_impl(&nets[0], &ta, &la, &ccfg, inv_n, gs, e->mb_stats ? e->mb_stats + 2 * m : nullptr, e->sums_actor + 4 * m, s,
+                            split ? sm_count() - (int)cnt : 0);
         if (rc) return rc;
+        if (split) TSM_CUDA(cudaStreamWaitEvent(s, ev_join, 0));
         rc = tsm_tcw_adam(nets, 2, e->step0 + m + 1, e->lr, e->beta1, e->beta2, e->eps, e->max_grad_norm, 1.0f, e->adam_ws, seq, nullptr, stream);
         if (rc) return rc;
         if (e->max_grad_norm > 0.f) ++seq;
     }
     return TSM_OK;
 }
+
+#ifdef TSM_TCW_TRACE
+extern "C" int tsm_tcw_trace_read(long long* h_out /*[192]*/) {
+    TSM_CUDA(cudaDeviceSynchronize());
+    TSM_CUDA(cudaMemcpyFromSymbol(h_out, tcw::g_tcw_trace, sizeof(long long) * 192));
+    return TSM_OK;
+}
+#endif
