@@ -536,8 +536,9 @@ typedef struct tsm_tcw_loss {
 int tsm_tcw_train(const tsm_net* net, const tsm_tcw_tiles* tiles, const tsm_tcw_loss* loss, const tsm_ppo_cfg* cfg, float inv_n,
                   float gscale, const float* mb_stats, double* loss_sums, tsm_stream_t stream);
 /* clip_grad_norm_ over the parameters of ALL n_nets nets jointly (ActorCritic, a2c.py:102-105; algorithm_base.py:485-498) +
- * Adam (optim.py:89-110) + fp16 image refresh + zeroed gradients.  step: 1-based number of this update; workspace: 64 zeroed
- * device bytes kept by the caller, seq: number of earlier CLIPPING launches on it. */
+ * Adam (optim.py:89-110) + fp16 image refresh + zeroed gradients.  step: 1-based number of this update; workspace:
+ * TSM_TCW_ADAM_WS_BYTES zeroed device bytes kept by the caller, seq: number of earlier CLIPPING launches on it. */
+#define TSM_TCW_ADAM_WS_BYTES 2048
 int tsm_tcw_adam(const tsm_net* nets, int n_nets, int64_t step, float lr, float beta1, float beta2, float eps, float max_grad_norm,
                  float grad_scale, void* workspace, uint32_t seq, float* grad_norm_out, tsm_stream_t stream);
 /* advantage mean / 1 / (unbiased std + eps) of tile-ordered minibatches (ppo.py:184-186): minibatch m = super-tiles
@@ -572,7 +573,7 @@ typedef struct tsm_tcw_epoch {
     double* sums_critic;        /* device [n_mb][4] */
     float lr, beta1, beta2, eps, max_grad_norm;
     int64_t step0;              /* optimizer steps taken before this call */
-    void* adam_ws;              /* 64 zeroed device bytes */
+    void* adam_ws;              /* TSM_TCW_ADAM_WS_BYTES zeroed device bytes */
     uint32_t adam_seq0;         /* clipping launches on adam_ws before this call */
 } tsm_tcw_epoch;
 int tsm_tcw_ppo_epoch(const tsm_tcw_epoch* e, const tsm_ppo_cfg* cfg, tsm_stream_t stream);

@@ -270,7 +270,7 @@ def test_adam_joint_clip_matches_torch(max_norm):
     nets = (_lib.TsmNet * 2)()
     tp = [torch.nn.Parameter(n.flat.detach().clone()) for n in (actor, critic)]
     opt = torch.optim.Adam(tp, lr=1e-3)
-    ws = torch.zeros(64, dtype=torch.uint8, device="cuda")
+    ws = torch.zeros(2048, dtype=torch.uint8, device="cuda")  # TSM_TCW_ADAM_WS_BYTES
     gn = torch.zeros(1, device="cuda")
     seq = 0
     for step in range(1, 4):

@@ -72,7 +72,7 @@ class MAPPO:
         na = (actor.n_params + 3) // 4 * 4
         self._grads = torch.zeros(na + critic.n_params, dtype=torch.float32, device=dev)
         actor.grads, critic.grads = self._grads[: actor.n_params], self._grads[na:]
-        self._adam_ws = torch.zeros(64, dtype=torch.uint8, device=dev)
+        self._adam_ws = torch.zeros(2048, dtype=torch.uint8, device=dev)  # TSM_TCW_ADAM_WS_BYTES
         self._adam_seq = 0
         self._steps = 0
         self.last_sequences: dict[str, np.ndarray] = {}

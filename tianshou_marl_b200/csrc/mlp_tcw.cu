@@ -554,7 +554,11 @@ __device__ __forceinline__ void flush_grads(const Ctx& c, const Args& a, const L
     epi_sync();
     const int total = (int)(o.total - base), n4 = total >> 2;
     float* g = a.grads + base;
-    for (int F = c.tid; F < n4; F += EPI_THREADS) {
+    // every CTA adds to the same addresses: start each CTA at its own offset so that they do not queue on the same L2 lines
+    const int rot = (int)((blockIdx.x * 1031u) % (unsigned)max(n4, 1));
+    for (int F0 = c.tid; F0 < n4; F0 += EPI_THREADS) {
+        int F = F0 + rot;
+        if (F >= n4) F -= n4;
         int idx = F;
         const int rel = F - w2q;
         if (rel >= 0 && rel < H * H / 4) {
@@ -757,6 +761,12 @@ __global__ void __launch_bounds__(THREADS, 1) tcw_kernel(Args a) {
             const bool valid = prow < a.n_rows;
             float side[2] = {0.f, 0.f};
             int act_reg = 0;
+            if (TRAIN && c.half == 0 && valid && a.loss_kind == 1) {  // pull the row's targets towards L1 while the forward runs
+                const float* tg = a.target + prow * a.heads;
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(tg));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(tg + a.heads - 1));
+                if (a.v_old) asm volatile("prefetch.global.L1 [%0];" ::"l"(a.v_old + prow * a.heads));
+            }
             if (TRAIN && c.half == 0 && valid && a.loss_kind == 0) {  // the loss stage's row scalars: in flight during the forward
                 side[0] = __ldg(a.adv + prow);
                 side[1] = a.logp_old ? __ldg(a.logp_old + prow) : 0.f;
@@ -820,8 +830,10 @@ __global__ void __launch_bounds__(THREADS, 1) tcw_kernel(Args a) {
                     epi_sync();
                     const int q4 = nk >> 2;
                     const bool vec = (a.in_dim & 3) == 0;
+                    const int rrot = (int)(blockIdx.x * 37u) & (ROWS - 1);  // CTAs walk the rows from different starting points
                     for (int F = c.tid; F < ROWS * q4; F += EPI_THREADS) {
-                        const int r = F / q4, c4 = F - r * q4;
+                        const int r0 = q4 == 16 ? F >> 4 : (q4 == 8 ? F >> 3 : F / q4);
+                        const int c4 = F - r0 * q4, r = (r0 + rrot) & (ROWS - 1);
                         const float4 val = st4[r * 16 + (c4 ^ (r & 7))];
                         const int k0 = sl * SLICE + 4 * c4;
                         float* dst = a.grads + o.w1 + (int64_t)r * a.in_dim + k0;
@@ -905,10 +917,10 @@ struct AdamNet {
     int in_dim, out_dim, KP;
     int64_t* step_out;
 };
-struct AdamWs {      // 64 bytes, zeroed once by the caller
-    double sumsq[2];
-    unsigned int count;
-    unsigned int pad[11];
+struct AdamWs {      // TSM_TCW_ADAM_WS_BYTES, zeroed once by the caller
+    unsigned int count;      // arrivals of all launches so far (the grid barrier counts monotonically)
+    unsigned int pad[3];
+    double partial[254];     // one squared-norm partial per CTA: plain stores, summed in CTA order by everybody after the barrier
 };
 struct AdamJob {
     AdamNet net[2];
@@ -944,20 +956,26 @@ __global__ void __launch_bounds__(256) tcw_adam_kernel(AdamJob j) {
         if (threadIdx.x == 0) {
             double t = 0.0;
             for (int w = 0; w < 8; ++w) t += s_part[w];
-            atomicAdd(&j.ws->sumsq[j.seq & 1], t);
+            // (148 atomicAdd(double) on one address serialise in L2 for ~3 us; a slot per CTA costs one store)
+            *reinterpret_cast<volatile double*>(&j.ws->partial[blockIdx.x]) = t;
             __threadfence();
             atomicAdd(&j.ws->count, 1u);
             const unsigned int target = (j.seq + 1u) * gridDim.x;
             while ((int)(*reinterpret_cast<volatile unsigned int*>(&j.ws->count) - target) < 0) {
             }
             __threadfence();
-            const double total = *reinterpret_cast<volatile double*>(&j.ws->sumsq[j.seq & 1]);
-            const float norm = (float)sqrt(total);
-            const float cc = j.max_norm / (norm + 1e-6f);  // clip_grad_norm_: clip_coef = max_norm / (total_norm + 1e-6), clamped to 1
-            s_coef = j.grad_scale * (cc < 1.f ? cc : 1.f);
-            if (blockIdx.x == 0) {
-                j.ws->sumsq[(j.seq + 1) & 1] = 0.0;
-                if (j.gnorm_out) *j.gnorm_out = norm;
+        }
+        __syncthreads();
+        if (threadIdx.x < 32) {  // the same sum in the same order in every CTA: one clip coefficient, bit for bit
+            double t = 0.0;
+            for (unsigned int b = threadIdx.x; b < gridDim.x; b += 32) t += __ldcg(&j.ws->partial[b]);
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) t += __shfl_xor_sync(0xffffffffu, t, d);
+            if (threadIdx.x == 0) {
+                const float norm = (float)sqrt(t);
+                const float cc = j.max_norm / (norm + 1e-6f);  // clip_grad_norm_: clip_coef = max_norm / (total_norm + 1e-6), clamped to 1
+                s_coef = j.grad_scale * (cc < 1.f ? cc : 1.f);
+                if (blockIdx.x == 0 && j.gnorm_out) *j.gnorm_out = norm;
             }
         }
         __syncthreads();
@@ -1177,7 +1195,7 @@ static int tcw_train_impl(const tsm_net* net, const tsm_tcw_tiles* t, const tsm_
 extern "C" int tsm_tcw_adam(const tsm_net* nets, int n_nets, int64_t step, float lr, float beta1, float beta2, float eps, float max_grad_norm,
                             float grad_scale, void* workspace, uint32_t seq, float* grad_norm_out, tsm_stream_t stream) {
     TSM_REQUIRE(nets && n_nets >= 1 && n_nets <= 2 && step >= 1, "1 <= n_nets <= 2, step >= 1");
-    TSM_REQUIRE(max_grad_norm <= 0.f || workspace != nullptr, "clipping needs the 64-byte workspace");
+    TSM_REQUIRE(max_grad_norm <= 0.f || workspace != nullptr, "clipping needs the workspace (TSM_TCW_ADAM_WS_BYTES)");
     tcw::AdamJob j{};
     int64_t total = 0;
     for (int t = 0; t < n_nets; ++t) {
@@ -1192,7 +1210,8 @@ extern "C" int tsm_tcw_adam(const tsm_net* nets, int n_nets, int64_t step, float
     }
     j.n_nets = n_nets; j.step = step; j.lr = lr; j.beta1 = beta1; j.beta2 = beta2; j.eps = eps; j.max_norm = max_grad_norm;
     j.grad_scale = grad_scale; j.ws = reinterpret_cast<tcw::AdamWs*>(workspace); j.seq = seq; j.gnorm_out = grad_norm_out;
-    static_assert(sizeof(tcw::AdamWs) == 64, "workspace layout");
+    static_assert(sizeof(tcw::AdamWs) == TSM_TCW_ADAM_WS_BYTES, "workspace layout");
+    TSM_REQUIRE(sm_count() <= 254, "optimizer grid exceeds the workspace's partial slots");
     // fixed grid (the grid barrier counts arrivals monotonically across launches on one workspace); all CTAs must be
     // co-resident: 148 CTAs of 256 threads always are when the kernel runs alone on its stream's turn, and the
     // cooperative launch makes the driver guarantee it
