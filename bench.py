@@ -432,6 +432,14 @@ def main() -> None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_e2e = float(t.item())
 
+    ident = None
+    if world > 1:  # the correctness claim of the data-parallel update travels with the line (costs one small all_gather)
+        flat = torch.cat([n.flat.detach().view(-1) for n in wl.nets()]).contiguous()
+        got = [torch.empty_like(flat) for _ in range(world)]
+        dist.all_gather(got, flat)
+        ident = {"params_identical_across_ranks": bool(all(torch.equal(got[0], g) for g in got[1:])),
+                 "params_max_abs_diff_across_ranks": float(max((got[0] - g).abs().max().item() for g in got[1:])),
+                 "grad_sync": wl.grad_sync()}
     if rank == 0:
         units = wl.agent_steps_per_step * world
         roof = wl.roofline(stages, hbm_peak, peak_src, tf_peak)
@@ -442,6 +450,8 @@ def main() -> None:
                 "e2e": {"value": units / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                         "h2d_bytes_per_step": wl.h2d_bytes, "d2h_bytes_per_step": wl.d2h_bytes},
                 "stages_ms": stages, "roofline": roof}
+        if ident is not None:
+            line.update(ident)
         if args.workload == "c3":
             line["metric"] = "agent-steps/sec collect+MAPPO update, simple_spread N=10 (centralized critic)"
         if not args.no_cpu_baseline and world == 1 and args.workload == "c2":

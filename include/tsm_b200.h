@@ -546,13 +546,30 @@ int tsm_tcw_adam(const tsm_net* nets, int n_nets, int64_t step, float lr, float 
 int tsm_tcw_adv_stats(const float* adv, int64_t n_rows, const int32_t* super_ids, int64_t rows_per_super, int64_t n_super,
                       int64_t mb_super, float eps, float* stats, tsm_stream_t stream);
 
+/* Data-parallel ranks of one node for engine 2: every rank's gradient arena and flag pad live in symmetric
+ * memory (torch.distributed._symmetric_memory: rendezvous only).  tsm_tcw_adam_peers = tsm_tcw_adam with the all-reduce inside:
+ * one flag store per peer ("my gradient of exchange xseq is complete"), wait for all ranks, coalesced NVLink LOADS of every
+ * rank's gradient summed in rank order (bit-identical parameters on all ranks), clip, Adam; grad_scale = 1 / world.  Backward
+ * launches of exchange xseq accumulate into parity (xseq & 1) of the arena; the other parity is zeroed by the optimizer. */
+typedef struct tsm_tcw_peers {
+    int32_t world, rank;
+    float* arena[8];      /* rank q's arena: [2 parities][stride] floats, zero-initialised */
+    uint32_t* flags[8];   /* rank q's flag pad: >= world uint32, zero-initialised; slot r is written by rank r */
+    int64_t stride;       /* floats per parity block */
+    int64_t net_off[2];   /* offset of each net's flat gradient inside a parity block (multiples of 4) */
+    float* gsum;          /* local scratch, stride floats */
+    int32_t* status;      /* local: set to 1 if a peer did not arrive within ~3 s */
+} tsm_tcw_peers;
+int tsm_tcw_adam_peers(const tsm_net* nets, int n_nets, int64_t step, float lr, float beta1, float beta2, float eps,
+                       float max_grad_norm, void* workspace, uint32_t seq, const tsm_tcw_peers* peers, uint32_t xseq,
+                       tsm_stream_t stream);
+
 /* One PPO epoch over CTDE nets (the build's "MAPPO": reference PPO arithmetic, modelfree/ppo.py:164-224, with the
  * DecentralizedActor on local observations and the CentralizedCritic on the concatenated global state, one value head per
  * agent) as ONE C call: per minibatch m = super-tiles [m * mb_super, (m + 1) * mb_super) of super_ids -- critic
  * forward/value-loss/backward over those tiles of ximg_critic (one row per world and step), actor forward/policy-loss/backward
  * over the matching n_agents tiles each of ximg_actor (row = world * n_agents + agent), then tsm_tcw_adam over both nets with
- * one gradient norm.  Single rank (across ranks the caller loops and all-reduces net.grads between tsm_tcw_train and
- * tsm_tcw_adam). */
+ * one gradient norm (tsm_tcw_adam_peers when `peers` is set). */
 typedef struct tsm_tcw_epoch {
     const tsm_net* actor;
     const tsm_net* critic;
@@ -575,6 +592,9 @@ typedef struct tsm_tcw_epoch {
     int64_t step0;              /* optimizer steps taken before this call */
     void* adam_ws;              /* TSM_TCW_ADAM_WS_BYTES zeroed device bytes */
     uint32_t adam_seq0;         /* clipping launches on adam_ws before this call */
+    const tsm_tcw_peers* peers; /* NULL on one rank; else the exchange runs inside the optimizer launch (every rank passes the
+                                   same number of minibatches) */
+    uint32_t xseq0;             /* exchanges done before this call */
 } tsm_tcw_epoch;
 int tsm_tcw_ppo_epoch(const tsm_tcw_epoch* e, const tsm_ppo_cfg* cfg, tsm_stream_t stream);
 

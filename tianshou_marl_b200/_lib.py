@@ -113,7 +113,14 @@ class TsmTcwEpoch(C.Structure):
                 ("super_ids", c_vp), ("n_super", c_i64), ("mb_super", c_i64), ("act", c_vp), ("adv", c_vp), ("logp_old", c_vp), ("ret", c_vp),
                 ("v_old", c_vp), ("h_mb_rows", c_vp), ("mb_stats", c_vp), ("sums_actor", c_vp), ("sums_critic", c_vp),
                 ("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float), ("max_grad_norm", C.c_float),
-                ("step0", c_i64), ("adam_ws", c_vp), ("adam_seq0", C.c_uint32)]
+                ("step0", c_i64), ("adam_ws", c_vp), ("adam_seq0", C.c_uint32), ("peers", c_vp), ("xseq0", C.c_uint32)]
+
+
+class TsmTcwPeers(C.Structure):
+    """struct tsm_tcw_peers (include/tsm_b200.h)."""
+
+    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("arena", c_vp * 8), ("flags", c_vp * 8), ("stride", c_i64), ("net_off", c_i64 * 2),
+                ("gsum", c_vp), ("status", c_vp)]
 
 
 c_f32, c_u64 = C.c_float, C.c_uint64
@@ -164,6 +171,7 @@ _SIGS = {
     "tsm_tcw_forward": (c_i32, [c_vp, c_vp, c_i64, c_i32, c_u64, c_u64, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "tsm_tcw_train": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_f32, c_f32, c_vp, c_vp, c_vp]),
     "tsm_tcw_adam": (c_i32, [c_vp, c_i32, c_i64, c_f32, c_f32, c_f32, c_f32, c_f32, c_f32, c_vp, C.c_uint32, c_vp, c_vp]),
+    "tsm_tcw_adam_peers": (c_i32, [c_vp, c_i32, c_i64, c_f32, c_f32, c_f32, c_f32, c_f32, c_vp, C.c_uint32, c_vp, C.c_uint32, c_vp]),
     "tsm_tcw_ppo_epoch": (c_i32, [c_vp, c_vp, c_vp]),
     "tsm_tcw_adv_stats": (c_i32, [c_vp, c_i64, c_vp, c_i64, c_i64, c_i64, c_f32, c_vp, c_vp]),
     "tsm_buf_gather": (c_i32, [c_vp, c_vp, c_i64] + [c_vp] * 9 + [c_vp, c_vp, c_i32, c_vp]),

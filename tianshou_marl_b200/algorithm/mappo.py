@@ -44,7 +44,7 @@ class MAPPO:
     def __init__(self, *, policy: DiscreteActorPolicy, critic: ActorCriticNet, n_agents: int, optim: AdamOptimizerFactory | None = None,
                  eps_clip: float = 0.2, dual_clip: float | None = None, value_clip: bool = False, advantage_normalization: bool = True,
                  vf_coef: float = 0.5, ent_coef: float = 0.01, max_grad_norm: float | None = None, gae_lambda: float = 0.95,
-                 gamma: float = 0.99, minibatch_order: str = "numpy", dedup_next_values: bool = True) -> None:
+                 gamma: float = 0.99, minibatch_order: str = "numpy", dedup_next_values: bool = True, grad_sync: str = "auto") -> None:
         assert dual_clip is None or dual_clip > 1.0, f"Dual-clip PPO parameter should greater than 1.0 but got {dual_clip}"  # ppo.py
         actor = policy.actor
         if actor.engine != "tcw" or critic.engine != "tcw":
@@ -55,6 +55,10 @@ class MAPPO:
             raise ValueError("the centralized critic reads the concatenated global state: in_dim == n_agents * obs_dim")
         if minibatch_order not in ("numpy", "sequential"):
             raise ValueError("minibatch_order must be 'numpy' or 'sequential'")
+        if grad_sync not in ("auto", "peer", "nccl"):
+            raise ValueError("grad_sync must be 'auto', 'peer' or 'nccl'")
+        self.grad_sync = grad_sync  # world > 1: "peer" = exchange inside the optimizer kernel over NVLink peer loads; "nccl" = all_reduce per minibatch
+        self._peers = None
         self.policy, self.actor, self.critic, self.n_agents = policy, actor, critic, int(n_agents)
         self.optim = optim or AdamOptimizerFactory()
         self.eps_clip, self.dual_clip, self.value_clip = eps_clip, dual_clip, value_clip
@@ -205,15 +209,26 @@ class MAPPO:
                 _lib.t_stop(tk)
             tk = _lib.t_start("ppo_epoch")
             h_rows = (C.c_int64 * n_mb)(*[int(x) for x in mb_rows])
-            if world == 1:
+            if world > 1 and self.grad_sync != "nccl" and self._peers is None:
+                try:
+                    self._peers = _TcwPeers(self)
+                except Exception:  # no symmetric memory on this system: per-minibatch NCCL all-reduce
+                    if self.grad_sync == "peer":
+                        raise
+                    self.grad_sync = "nccl"
+            if world == 1 or self._peers is not None:
                 actor.desc, critic.desc  # (refresh the descriptors: parameter image current, pointers valid)
                 e = _lib.TsmTcwEpoch(actor=C.addressof(actor._desc), critic=C.addressof(critic._desc), ximg_actor=P(xa), ximg_critic=P(xc),
                                      n_rows=n_rows, n_agents=A, super_ids=P(ids), n_super=n_super, mb_super=mb_super, act=P(act), adv=P(adv),
                                      logp_old=P(logp), ret=P(ret), v_old=P(v_s), h_mb_rows=C.cast(h_rows, C.c_void_p),
                                      mb_stats=P(st_ep) if self.advantage_normalization else None, sums_actor=P(sa), sums_critic=P(sc),
                                      lr=o.lr, beta1=o.betas[0], beta2=o.betas[1], eps=o.eps, max_grad_norm=mgn, step0=self._steps,
-                                     adam_ws=P(self._adam_ws), adam_seq0=self._adam_seq)
+                                     adam_ws=P(self._adam_ws), adam_seq0=self._adam_seq,
+                                     peers=C.addressof(self._peers.desc) if self._peers is not None else None,
+                                     xseq0=self._peers.xseq if self._peers is not None else 0)
                 _lib.check(L.tsm_tcw_ppo_epoch(C.byref(e), C.byref(self._cfg), S))
+                if self._peers is not None:
+                    self._peers.xseq += n_mb
             else:
                 self._epoch_across_ranks(xa, xc, n_rows, ids, n_super, mb_super, mb_rows, act, adv, logp, ret, v_s,
                                          st_ep if self.advantage_normalization else None, sa, sc, world)
@@ -224,6 +239,8 @@ class MAPPO:
         actor.kernel_updates += repeat * n_mb
         critic.kernel_updates += repeat * n_mb
         ha, hc = sums_a.cpu().numpy(), sums_c.cpu().numpy()
+        if self._peers is not None:
+            self._peers.check()
         del keep
         n_per = np.concatenate(rows_seq).astype(np.float64)
         clip_l, ent_l, vf_l = ha[:, 0] / n_per, ha[:, 2] / n_per, hc[:, 1] / n_per
@@ -258,3 +275,45 @@ class MAPPO:
             torch.distributed.all_reduce(self._grads)
             _lib.check(L.tsm_tcw_adam(nets, 2, self._steps + m + 1, o.lr, o.betas[0], o.betas[1], o.eps, mgn, 1.0 / world, P(self._adam_ws),
                                       self._adam_seq + (m if mgn > 0 else 0), None, S))
+
+
+class _TcwPeers:
+    """Symmetric-memory gradient arenas ([2 parities][stride] floats) + flag pads of all ranks as a tsm_tcw_peers struct
+    (csrc/mlp_tcw.cu tcw_adam_kernel reads every rank's gradient over NVLink; torch.distributed only does the rendezvous)."""
+
+    FLAG_WORDS = 64
+
+    def __init__(self, alg: MAPPO) -> None:
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+
+        actor, critic = alg.actor, alg.critic
+        dev = actor.device
+        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+        if self.world > 8:
+            raise _lib.TsmError("the fused gradient exchange covers one node (<= 8 ranks)")
+        na = (actor.n_params + 3) // 4 * 4
+        self.stride = (na + critic.n_params + 3) // 4 * 4
+        self.block = symm_mem.empty(2 * self.stride + self.FLAG_WORDS, dtype=torch.float32, device=dev)
+        self.block.zero_()
+        self.handle = symm_mem.rendezvous(self.block, group=dist.group.WORLD.group_name)
+        self.gsum = torch.zeros(self.stride, dtype=torch.float32, device=dev)
+        self.status = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.xseq = 0  # exchanges done
+        p = _lib.TsmTcwPeers()
+        p.world, p.rank, p.stride = self.world, self.rank, self.stride
+        p.net_off[0], p.net_off[1] = 0, na
+        for q in range(self.world):
+            base = int(self.handle.buffer_ptrs[q])
+            p.arena[q] = base
+            p.flags[q] = base + 4 * 2 * self.stride
+        p.gsum, p.status = self.gsum.data_ptr(), self.status.data_ptr()
+        self.desc = p
+        # the nets' gradient views point into parity 0 of the local arena (the epoch call selects the parity per minibatch)
+        actor.grads, critic.grads = self.block[: actor.n_params], self.block[na: na + critic.n_params]
+        torch.cuda.synchronize(dev)
+        dist.barrier()  # every rank has zeroed its block before anyone's kernels touch it
+
+    def check(self) -> None:
+        if int(self.status.item()) != 0:
+            raise _lib.TsmError("cross-rank gradient barrier timed out (a peer rank did not reach the optimizer step)")

@@ -75,6 +75,12 @@ class Workload:
         self.h2d_bytes = (self.n_mb + 1) * 8 * (self.args.repeat if self.update else 0)  # minibatch bounds
 
     # -- reporting ------------------------------------------------------------------------------
+    def nets(self) -> list:
+        return [self.net] + ([self.critic] if getattr(self, "critic", None) is not None and self.critic is not self.net else [])
+
+    def grad_sync(self) -> str:
+        return "peer (inside the optimizer / epoch kernel over NVLink)" if getattr(self.alg, "_peers", None) is not None else "nccl all_reduce per minibatch"
+
     def reset_timers(self) -> None:
         _lib.timer = _lib.StageTimer()
 

@@ -925,6 +925,18 @@ struct AdamWs {      // TSM_TCW_ADAM_WS_BYTES, zeroed once by the caller
 struct AdamJob {
     AdamNet net[2];
     int n_nets;
+    // data-parallel ranks of one node (world == 1: unused).  Every rank's gradient arena ([2 parities][stride] floats) and
+    // flag pad live in symmetric memory: rank r announces "my gradient of exchange xseq is complete" with one flag store per
+    // peer, waits for all ranks' flags, and then READS the gradients of all ranks over NVLink (coalesced peer loads, summed
+    // in rank order: the same bits everywhere).  The arena of the other parity is zeroed here for the minibatch after next.
+    int world, rank;
+    const float* peer_g[8];   // rank q's arena of this exchange's parity
+    uint32_t* peer_flag[8];   // rank q's flag pad
+    int64_t goff[2];          // offset of each net's gradient inside a parity block
+    float* gsum;              // local scratch [stride]: the rank-summed gradient (phase 1 -> phase 2)
+    float* zero_next;         // local arena of the other parity
+    uint32_t xseq;
+    int* status;
     int64_t step;            // 1-based step number of THIS update
     float lr, beta1, beta2, eps, max_norm, grad_scale;
     AdamWs* ws;
@@ -936,15 +948,65 @@ __global__ void __launch_bounds__(256) tcw_adam_kernel(AdamJob j) {
     __shared__ double s_part[8];
     __shared__ float s_coef;
     float coef = j.grad_scale;
+    const bool multi = j.world > 1;
+    if (multi) {
+        // (a) announce; (b) wait for every rank (bounded: a missing peer sets *status instead of hanging the GPU)
+        if (blockIdx.x == 0 && (int)threadIdx.x < j.world)
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(j.peer_flag[threadIdx.x] + j.rank), "r"(j.xseq) : "memory");
+        if ((int)threadIdx.x < j.world) {
+            const uint32_t* f = j.peer_flag[j.rank] + threadIdx.x;
+            const long long t0 = clock64();
+            uint32_t v;
+            do {
+                asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+                if ((int)(v - j.xseq) >= 0) break;
+                if (clock64() - t0 > 6000000000LL) { *j.status = 1; break; }  // ~3 s
+            } while (true);
+        }
+        __syncthreads();
+        // (c) rank-ordered sum of the peers' gradients -> gsum (and the other parity's arena zeroed for the minibatch after next)
+        for (int t = 0; t < j.n_nets; ++t) {
+            const AdamNet& n = j.net[t];
+            const int cnt = (int)n.n, stride = (int)(gridDim.x * blockDim.x);
+            const int64_t off = j.goff[t];
+            for (int i0 = (int)(blockIdx.x * blockDim.x + threadIdx.x); i0 < cnt; i0 += 4 * stride) {
+                // all ranks' loads are issued before the first add (in-order issue: an add behind each rank's loads would cost
+                // one NVLink round trip per rank instead of one in total)
+                float v[8][4];
+#pragma unroll
+                for (int r = 0; r < 8; ++r) {
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        v[r][u] = 0.f;
+                        if (r < j.world && i0 + u * stride < cnt)
+                            asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v[r][u]) : "l"(j.peer_g[r] + off + i0 + u * stride));
+                    }
+                }
+                float g[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int r = 0; r < 8; ++r) {
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) g[u] += v[r][u];  // rank order; absent ranks add +0
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    if (i0 + u * stride < cnt) {
+                        j.gsum[off + i0 + u * stride] = g[u];
+                        j.zero_next[off + i0 + u * stride] = 0.f;
+                    }
+            }
+        }
+    }
     if (j.max_norm > 0.f) {
         double acc = 0.0;
         for (int t = 0; t < j.n_nets; ++t) {
             const AdamNet& n = j.net[t];
             const int cnt = (int)n.n, stride = (int)(gridDim.x * blockDim.x);
+            const float* gp = multi ? j.gsum + j.goff[t] : n.g;  // (each thread re-reads only what it wrote itself)
             for (int i0 = (int)(blockIdx.x * blockDim.x + threadIdx.x); i0 < cnt; i0 += 4 * stride) {
                 float g[4];
 #pragma unroll
-                for (int u = 0; u < 4; ++u) g[u] = i0 + u * stride < cnt ? __ldcg(n.g + i0 + u * stride) * j.grad_scale : 0.f;
+                for (int u = 0; u < 4; ++u) g[u] = i0 + u * stride < cnt ? __ldcg(gp + i0 + u * stride) * j.grad_scale : 0.f;
 #pragma unroll
                 for (int u = 0; u < 4; ++u) acc += (double)g[u] * (double)g[u];
             }
@@ -988,20 +1050,22 @@ __global__ void __launch_bounds__(256) tcw_adam_kernel(AdamJob j) {
         const AdamNet& n = j.net[t];
         const Offsets o = offsets(n.in_dim, H, n.out_dim);
         const int cnt = (int)n.n;
+        const float* gp = multi ? j.gsum + j.goff[t] : n.g;
         // four independent elements per thread and pass: the loads of all four are in flight together
         for (int i0 = (int)(blockIdx.x * blockDim.x + threadIdx.x); i0 < cnt; i0 += 4 * stride) {
             float p[4], g[4], m[4], v[4];
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 const int i = i0 + u * stride;
-                if (i < cnt) { p[u] = n.p[i]; g[u] = __ldcg(n.g + i); m[u] = n.m[i]; v[u] = n.v[i]; }
+                if (i < cnt) { p[u] = n.p[i]; g[u] = __ldcg(gp + i); m[u] = n.m[i]; v[u] = n.v[i]; }
             }
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 const int i = i0 + u * stride;
                 if (i < cnt) {
                     const float pn = opt::adam_elem(p[u], g[u], m[u], v[u], coef, step_size, bc2_sqrt, j.beta1, j.beta2, j.eps);
-                    n.p[i] = pn; n.m[i] = m[u]; n.v[i] = v[u]; n.g[i] = 0.f;
+                    n.p[i] = pn; n.m[i] = m[u]; n.v[i] = v[u];
+                    if (!multi) n.g[i] = 0.f;  // (multi: peers may still be reading this parity; the other one was zeroed above)
                     if (n.image) n.image[image_index32(i, o, n.in_dim, n.KP)] = __float2half_rn(pn);
                 }
             }
@@ -1192,8 +1256,26 @@ static int tcw_train_impl(const tsm_net* net, const tsm_tcw_tiles* t, const tsm_
     return a.KP <= tcw::RES_KP ? tcw_launch<false, true>(a, stream, max_ctas) : tcw_launch<true, true>(a, stream, max_ctas);
 }
 
+static int tcw_adam_impl(const tsm_net* nets, int n_nets, int64_t step, float lr, float beta1, float beta2, float eps, float max_grad_norm,
+                         float grad_scale, void* workspace, uint32_t seq, float* grad_norm_out, const tsm_tcw_peers* peers, uint32_t xseq,
+                         tsm_stream_t stream);
+
 extern "C" int tsm_tcw_adam(const tsm_net* nets, int n_nets, int64_t step, float lr, float beta1, float beta2, float eps, float max_grad_norm,
                             float grad_scale, void* workspace, uint32_t seq, float* grad_norm_out, tsm_stream_t stream) {
+    return tcw_adam_impl(nets, n_nets, step, lr, beta1, beta2, eps, max_grad_norm, grad_scale, workspace, seq, grad_norm_out, nullptr, 0, stream);
+}
+
+extern "C" int tsm_tcw_adam_peers(const tsm_net* nets, int n_nets, int64_t step, float lr, float beta1, float beta2, float eps,
+                                  float max_grad_norm, void* workspace, uint32_t seq, const tsm_tcw_peers* peers, uint32_t xseq,
+                                  tsm_stream_t stream) {
+    TSM_REQUIRE(peers != nullptr && peers->world >= 1, "peers != NULL");
+    return tcw_adam_impl(nets, n_nets, step, lr, beta1, beta2, eps, max_grad_norm, 1.0f / (float)peers->world, workspace, seq, nullptr, peers, xseq,
+                         stream);
+}
+
+static int tcw_adam_impl(const tsm_net* nets, int n_nets, int64_t step, float lr, float beta1, float beta2, float eps, float max_grad_norm,
+                         float grad_scale, void* workspace, uint32_t seq, float* grad_norm_out, const tsm_tcw_peers* peers, uint32_t xseq,
+                         tsm_stream_t stream) {
     TSM_REQUIRE(nets && n_nets >= 1 && n_nets <= 2 && step >= 1, "1 <= n_nets <= 2, step >= 1");
     TSM_REQUIRE(max_grad_norm <= 0.f || workspace != nullptr, "clipping needs the workspace (TSM_TCW_ADAM_WS_BYTES)");
     tcw::AdamJob j{};
@@ -1207,6 +1289,24 @@ extern "C" int tsm_tcw_adam(const tsm_net* nets, int n_nets, int64_t step, float
         n.image = reinterpret_cast<__half*>(nets[t].tc_image); n.in_dim = nets[t].in_dim; n.out_dim = nets[t].out_dim;
         n.KP = tcw::pad_in(nets[t].in_dim); n.step_out = nets[t].adam_step;
         total += n.n;
+    }
+    if (peers && peers->world > 1) {
+        TSM_REQUIRE(peers->world <= 8 && peers->rank >= 0 && peers->rank < peers->world && xseq >= 1, "1 < world <= 8, 0 <= rank < world, xseq >= 1");
+        TSM_REQUIRE(peers->gsum && peers->status && peers->stride > 0, "peers: gsum / status / stride");
+        const int64_t par = (int64_t)(xseq & 1u);
+        j.world = peers->world; j.rank = peers->rank; j.xseq = xseq; j.gsum = peers->gsum; j.status = peers->status;
+        for (int q = 0; q < peers->world; ++q) {
+            TSM_REQUIRE(peers->arena[q] && peers->flags[q], "peers: arena / flags of every rank");
+            j.peer_g[q] = peers->arena[q] + par * peers->stride;
+            j.peer_flag[q] = peers->flags[q];
+        }
+        j.zero_next = peers->arena[peers->rank] + (par ^ 1) * peers->stride;
+        for (int t = 0; t < n_nets; ++t) {
+            j.goff[t] = peers->net_off[t];
+            TSM_REQUIRE(nets[t].grads == peers->arena[peers->rank] + par * peers->stride + peers->net_off[t], "net.grads must be this parity's arena slice");
+        }
+    } else {
+        j.world = 1;
     }
     j.n_nets = n_nets; j.step = step; j.lr = lr; j.beta1 = beta1; j.beta2 = beta2; j.eps = eps; j.max_norm = max_grad_norm;
     j.grad_scale = grad_scale; j.ws = reinterpret_cast<tcw::AdamWs*>(workspace); j.seq = seq; j.gnorm_out = grad_norm_out;
@@ -1248,6 +1348,7 @@ extern "C" int tsm_tcw_ppo_epoch(const tsm_tcw_epoch* e, const tsm_ppo_cfg* cfg,
     tsm_ppo_cfg ccfg = *cfg;
     uint32_t seq = e->adam_seq0;
     cudaStream_t s = as_stream(stream);
+    const bool multi = e->peers != nullptr && e->peers->world > 1;
     // The critic's tiles of a minibatch (one per 128 worlds) occupy a third of the SMs for about as long as the actor's tiles
     // occupy the rest: the two launches run side by side, the critic on a forked stream, and join before the optimizer.
     static const bool two = !(getenv("TSM_TCW_STREAMS") && atoi(getenv("TSM_TCW_STREAMS")) == 1);
@@ -1272,6 +1373,12 @@ extern "C" int tsm_tcw_ppo_epoch(const tsm_tcw_epoch* e, const tsm_ppo_cfg* cfg,
         while (gs < (float)rows && gs < 1048576.f) gs *= 2.f;
         const float inv_n = 1.0f / (float)rows;
         const bool split = two && cnt * 2 <= sm_count();  // critic CTAs + actor CTAs fit side by side
+        const uint32_t xseq = e->xseq0 + (uint32_t)m + 1u;
+        if (multi) {  // this exchange's parity of the symmetric gradient arena
+            float* blockp = e->peers->arena[e->peers->rank] + (int64_t)(xseq & 1u) * e->peers->stride;
+            nets[0].grads = blockp + e->peers->net_off[0];
+            nets[1].grads = blockp + e->peers->net_off[1];
+        }
         tsm_tcw_tiles tc{e->ximg_critic, e->n_rows / A, e->super_ids, 1, s0, cnt};
         tsm_tcw_loss lc{};
         lc.kind = 1; lc.target = e->ret; lc.v_old = e->v_old; lc.weight = nullptr; lc.heads = A;
@@ -1289,7 +1396,10 @@ extern "C" int tsm_tcw_ppo_epoch(const tsm_tcw_epoch* e, const tsm_ppo_cfg* cfg,
                             split ? sm_count() - (int)cnt : 0);
         if (rc) return rc;
         if (split) TSM_CUDA(cudaStreamWaitEvent(s, ev_join, 0));
-        rc = tsm_tcw_adam(nets, 2, e->step0 + m + 1, e->lr, e->beta1, e->beta2, e->eps, e->max_grad_norm, 1.0f, e->adam_ws, seq, nullptr, stream);
+        if (multi)
+            rc = tsm_tcw_adam_peers(nets, 2, e->step0 + m + 1, e->lr, e->beta1, e->beta2, e->eps, e->max_grad_norm, e->adam_ws, seq, e->peers, xseq, stream);
+        else
+            rc = tsm_tcw_adam(nets, 2, e->step0 + m + 1, e->lr, e->beta1, e->beta2, e->eps, e->max_grad_norm, 1.0f, e->adam_ws, seq, nullptr, stream);
         if (rc) return rc;
         if (e->max_grad_norm > 0.f) ++seq;
     }
