@@ -56,6 +56,7 @@ def parse() -> argparse.Namespace:
                    help="c2: the headline collect+GAE+PPO step; c3: MAPPO / CTDE, N = 10 agents, 32 768 worlds per GPU (BASELINE.json "
                         "configs[2]); c5: GAE + buffer add/sample microbench (T=128, 1M rows), one GPU")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-c5", action="store_true", help="skip the configs[4] microbench that rides on the default N = 1 line")
     p.add_argument("--cpu-envs", type=int, default=4096, help="reference arm: environments in the bounded sample")
     p.add_argument("--cpu-horizon", type=int, default=64)
     p.add_argument("--ref-quick", action="store_true", help="--impl reference: only the C1 point of the reference classes (the cpu_baseline leg of the own arm)")
@@ -275,6 +276,11 @@ def reference_main(args: argparse.Namespace) -> None:
 
 # ------------------------------------------------------------------------------------------
 def c5_main(args: argparse.Namespace) -> None:
+    line = c5_measure(args.steps, max(args.warmup, 3))
+    print(json.dumps(line))
+
+
+def c5_measure(steps: int, warmup: int) -> dict:
     """BASELINE.json configs[4]: GAE + buffer add / sample at T = 128, envs x agents = 1 048 576, gamma 0.99, lambda 0.95.
     One step = T vector adds of R rows (obs dim 18) through VectorReplayBuffer.add, GAE over the [T, R] block in place,
     sample_indices(0) over the full buffer.  Inputs per SURVEY 8(d): done every 25th step with a per-row phase, 1 % terminated."""
@@ -323,27 +329,29 @@ def c5_main(args: argparse.Namespace) -> None:
             for k, (a, b) in zip(tot, ((0, 1), (1, 2), (2, 3))):
                 tot[k] += e[a].elapsed_time(e[b])
 
-    for _ in range(max(args.warmup, 3)):
+    for _ in range(warmup):
         step(False)
     with Clocks(0) as clk:
-        for _ in range(args.steps):
+        for _ in range(steps):
             step(True)
     n = T * R
-    ms = {k: v / args.steps for k, v in tot.items()}
+    ms = {k: v / steps for k, v in tot.items()}
     gbs = {"gae": GAE_BYTES_PER_ELT * n / ms["gae"] / 1e6, "add": (2 * 4 * O + 4 + 4 + 3) * n / ms["add"] / 1e6,
            "sample_indices": 8 * n / ms["sample_indices"] / 1e6}
-    line = {"metric": "GAE GB/s vs HBM peak", "value": gbs["gae"], "unit": "GB/s", "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3),
+    line = {"metric": "GAE GB/s vs HBM peak", "value": gbs["gae"], "unit": "GB/s", "n_gpus": 1, "steps": steps, "warmup": warmup,
             "ms_per_step": sum(ms.values()), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 I/O, f64 carry",
             "data": "synthetic", "config": {"workload": "C5 GAE + buffer add/sample microbench T=128 rows=1048576 gamma=0.99 lambda=0.95 obs_dim=18",
                                             "l2": "inputs larger than L2: 2.95 GB per GAE call, 20.8 GB per 128 adds"},
-            "clocks": clk.summary(), "gpu_launches": args.steps * (1 + 2 * T + 1 + 1),
+            "clocks": clk.summary(), "gpu_launches": steps * (1 + 2 * T + 1 + 1),
             "stages_ms": ms,
             "roofline": {"kernel": "gae_tm_kernel", "bound": "hbm", "achieved": gbs["gae"], "peak": hbm_peak, "peak_source": src, "unit": "GB/s",
                          "frac": gbs["gae"] / hbm_peak, "traffic": None, "bytes_per_unit": GAE_BYTES_PER_ELT, "units_per_launch": n,
                          "buffer_add": {"achieved": gbs["add"], "frac": gbs["add"] / hbm_peak, "bytes_per_unit": 2 * 4 * O + 11,
                                         "note": "128 VectorReplayBuffer.add calls of 1M rows (payload copy + counters kernel each)"},
                          "sample_indices": {"achieved": gbs["sample_indices"], "frac": gbs["sample_indices"] / hbm_peak, "bytes_per_unit": 8}}}
-    print(json.dumps(line))
+    del buf, obs, obs2, v_s, v_n, adv, ret
+    torch.cuda.empty_cache()
+    return line
 
 
 def main() -> None:
@@ -454,6 +462,16 @@ def main() -> None:
             line.update(ident)
         if args.workload == "c3":
             line["metric"] = "agent-steps/sec collect+MAPPO update, simple_spread N=10 (centralized critic)"
+        if world == 1 and args.workload == "c2" and not args.no_c5:
+            # BASELINE.json configs[4] (GAE + buffer add / sample microbench, T = 128, 1 048 576 rows) rides on the default line so
+            # that the driver's record carries its HBM fractions too (python bench.py --workload c5 prints it alone)
+            del wl
+            torch.cuda.empty_cache()
+            c5 = c5_measure(2, 3)
+            r5 = c5["roofline"]
+            line["roofline"]["c5"] = {"gae": {"achieved": r5["achieved"], "frac": r5["frac"], "unit": "GB/s", "bytes_per_unit": r5["bytes_per_unit"]},
+                                      "buffer_add": r5["buffer_add"], "sample_indices": r5["sample_indices"], "peak": r5["peak"],
+                                      "workload": c5["config"]["workload"], "stages_ms": c5["stages_ms"]}
         if not args.no_cpu_baseline and world == 1 and args.workload == "c2":
             line.update(cpu_baseline_leg(args))
         print(json.dumps(line))

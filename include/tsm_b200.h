@@ -295,6 +295,8 @@ typedef struct tsm_net {
     void* x_scratch;    /* engine 2 only, optional: device scratch for the packed fp16 image of the rows tsm_net_forward /
                            tsm_net_forward_range / tsm_collect_lockstep evaluate (they take float32 rows like engines 0 / 1) */
     int64_t x_scratch_bytes; /* >= tsm_tcw_x_bytes(in_dim, rows of the largest call) */
+    int32_t probs_param; /* 1: the actor is DiscreteActor(softmax_output=True) feeding Categorical(probs=...) (utils/net/discrete.py:41,85-86):
+                            log-probabilities / entropy are log(clamp(softmax(logits), eps, 1 - eps)) as torch computes them */
 } tsm_net;
 #define TSM_TC_IMAGE_BYTES 119552 /* 16 896 image + tsm_ppo_epoch's three more gradient-sized buffers of 7 168 floats + 256 bytes of barrier words + a 16 KB index table */
 

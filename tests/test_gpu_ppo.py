@@ -19,7 +19,7 @@ def _mk(c, order="numpy", **ppo_kw):
     from tianshou_marl_b200.data import Batch, VectorReplayBuffer
     from tianshou_marl_b200.utils import ActorCriticNet
 
-    net = ActorCriticNet(c["O"], c["H"], c["nA"]).load_arrays(c["W1"], c["b1"], c["W2"], c["b2"], c["W3"], c["b3"])
+    net = ActorCriticNet(c["O"], c["H"], c["nA"], softmax_output=c["probs"]).load_arrays(c["W1"], c["b1"], c["W2"], c["b2"], c["W3"], c["b3"])
     pol = DiscreteActorPolicy(actor=net)
     k = c["cfg"]
     alg = PPO(policy=pol, critic=net, optim=AdamOptimizerFactory(lr=c["lr"]), eps_clip=k["eps_clip"], dual_clip=k["dual_clip"] or None,
@@ -32,11 +32,18 @@ def _mk(c, order="numpy", **ppo_kw):
     return net, pol, alg, buf
 
 
-@pytest.mark.parametrize("ci", [0, 1, 3])
+@pytest.mark.parametrize("ci", [0, 1, 2, 3])
 def test_forward_matches_reference(golden, ci):
     c = load_case(golden("ppo.npz"), ci)
     net, *_ = _mk(c)
     o = net.forward(torch.as_tensor(c["obs"][0], device="cuda"), mode="mode", want_logits=True)
+    if c["probs"]:  # case 2: DiscreteActor(softmax_output=True) returns probabilities (utils/net/discrete.py:85-86)
+        assert np.allclose(torch.softmax(o["logits"], -1).cpu().numpy(), c["fwd_actor_out"], rtol=2e-5, atol=2e-6)
+        assert np.allclose(o["value"].cpu().numpy(), c["fwd_value"], rtol=2e-5, atol=2e-6)
+        a = c["fwd_actor_out"].argmax(-1)
+        assert np.array_equal(o["act"].cpu().numpy(), a)
+        assert np.allclose(o["logp"].cpu().numpy(), np.log(c["fwd_actor_out"][np.arange(len(a)), a]), rtol=2e-5, atol=2e-6)
+        return
     assert np.allclose(o["logits"].cpu().numpy(), c["fwd_actor_out"], rtol=2e-5, atol=2e-6)
     assert np.allclose(o["value"].cpu().numpy(), c["fwd_value"], rtol=2e-5, atol=2e-6)
     assert np.array_equal(o["act"].cpu().numpy(), c["fwd_actor_out"].argmax(-1))
@@ -44,7 +51,7 @@ def test_forward_matches_reference(golden, ci):
     assert np.allclose(o["logp"].cpu().numpy(), lp[np.arange(len(lp)), c["fwd_actor_out"].argmax(-1)], rtol=2e-5, atol=2e-6)
 
 
-@pytest.mark.parametrize("ci", [0, 1, 3])
+@pytest.mark.parametrize("ci", [0, 1, 2, 3])
 def test_update_matches_reference(golden, ci):
     """Whole PPO.update vs the reference: v_s, returns, adv, logp_old, every minibatch loss, final parameters."""
     c = load_case(golden("ppo.npz"), ci)
@@ -91,9 +98,18 @@ def test_single_minibatch_gradient_vs_oracle():
         ret = rng.normal(size=n).astype(np.float32)
         logp_old = (np.log(0.2) + 0.3 * rng.normal(size=n)).astype(np.float32)
         v_old = rng.normal(size=n).astype(np.float32)
-        for cfg in (dict(adv_norm=True), dict(adv_norm=False, value_clip=True, dual_clip=2.0, eps_clip=0.1, vf_coef=0.3, ent_coef=0.02)):
+        for cfg in (dict(adv_norm=True), dict(adv_norm=False, value_clip=True, dual_clip=2.0, eps_clip=0.1, vf_coef=0.3, ent_coef=0.02),
+                    dict(adv_norm=True, probs=True, ent_coef=0.05), dict(adv_norm=True, probs=True, peaked=True, ent_coef=0.05)):
             T = lambda a: torch.from_numpy(a)  # noqa: E731
-            loss, cl, vf, en = oppo.minibatch_loss(onet, T(obs), T(act).float(), T(adv), T(ret), T(logp_old), T(v_old), cfg)
+            if cfg.get("probs"):  # Categorical(probs=softmax(logits)), discrete.py:85-86; peaked: probabilities below 2^-23, where
+                #                   torch's probs_to_logits clamps the log and stops the gradient
+                if cfg.get("peaked"):
+                    onet.p[4].data[:5] *= 60.0
+                    with torch.no_grad():
+                        pr = torch.softmax(onet.forward(T(obs))[0], -1)
+                    assert float((pr < 1.19e-7).float().mean()) > 0.02
+                net = ActorCriticNet(O, H, 5, softmax_output=True).load_arrays(*[p.detach().numpy() for p in onet.p])
+            loss, cl, vf, en = oppo.minibatch_loss(onet, T(obs), T(act).float(), T(adv), T(ret), T(logp_old), T(v_old), cfg, bool(cfg.get("probs")))
             for p in onet.p:
                 p.grad = None
             loss.backward()

@@ -53,7 +53,7 @@ class TsmNet(C.Structure):
         ("in_dim", C.c_int32), ("hidden", C.c_int32), ("out_dim", C.c_int32), ("n_act", C.c_int32),
         ("value_index", C.c_int32), ("engine", C.c_int32), ("n_params", c_i64),
         ("params", c_vp), ("grads", c_vp), ("adam_m", c_vp), ("adam_v", c_vp), ("adam_step", c_vp),
-        ("tc_image", c_vp), ("x_scratch", c_vp), ("x_scratch_bytes", c_i64),
+        ("tc_image", c_vp), ("x_scratch", c_vp), ("x_scratch_bytes", c_i64), ("probs_param", C.c_int32),
     ]
 
 

@@ -251,7 +251,7 @@ struct FwdArgs {
     const float* x;          // [.][in_dim] rows addressed through `rows` (NULL = identity)
     const int64_t* rows;     // optional gather list of x rows (also the scatter target when scatter != 0)
     int64_t n;
-    int in_dim, out_dim, n_act, value_index, mode, scatter;
+    int in_dim, out_dim, n_act, value_index, mode, scatter, probs;
     uint64_t seed, counter;
     int64_t rng_row0;        // added to the row index in the sampling key
     float* out;              // mode 0: [n][out_dim]
@@ -299,7 +299,7 @@ __global__ void __launch_bounds__(THREADS) forward_kernel(FwdArgs a) {
                         if (j < a.out_dim) a.out[dst * a.out_dim + j] = z[j];
                 }
             } else {
-                const Soft s = softmax_row(z, a.n_act);
+                const Soft s = softmax_row(z, a.n_act, a.probs != 0);
                 int act = 0;
                 if (a.mode == 1) {
                     const int64_t key = dst + a.rng_row0;
@@ -691,7 +691,7 @@ static int net_forward_impl(const tsm_net* net, const float* x, const int64_t* r
     FwdArgs a{};
     a.params = net->params; a.x = x; a.rows = rows; a.n = n;
     a.in_dim = net->in_dim; a.out_dim = net->out_dim; a.n_act = net->n_act; a.value_index = net->value_index;
-    a.mode = mode; a.scatter = scatter; a.seed = seed; a.counter = counter; a.rng_row0 = rng_row0;
+    a.mode = mode; a.scatter = scatter; a.seed = seed; a.counter = counter; a.rng_row0 = rng_row0; a.probs = net->probs_param;
     a.out = out; a.act = act; a.logp = logp; a.value = value; a.entropy = entropy;
     cudaStream_t s = as_stream(stream);
     int occ = 1;
@@ -817,7 +817,7 @@ extern "C" int tsm_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch,
     a.mb_start = mb_start; a.mb_len = mb_len; a.mb_stats = mb_stats;
     a.cfg.eps_clip = cfg->eps_clip; a.cfg.dual_clip = cfg->dual_clip; a.cfg.vf_coef = cfg->vf_coef; a.cfg.ent_coef = cfg->ent_coef;
     a.cfg.value_clip = cfg->value_clip; a.cfg.adv_norm = cfg->adv_norm;
-    a.cfg.plain_pg = cfg->plain_pg; a.cfg.value_heads = cfg->value_heads;
+    a.cfg.plain_pg = cfg->plain_pg; a.cfg.value_heads = cfg->value_heads; a.cfg.probs_param = net->probs_param;
     a.in_dim = net->in_dim; a.out_dim = net->out_dim; a.n_act = net->n_act; a.value_index = net->value_index;
     a.loss_sums = loss_sums;
     return net->hidden == 64 ? launch_ppo<64>(a, as_stream(stream)) : launch_ppo<128>(a, as_stream(stream));

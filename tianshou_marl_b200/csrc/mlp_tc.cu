@@ -170,7 +170,7 @@ int tc_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int6
     mlptc::TcFwdArgs a{};
     a.image = reinterpret_cast<const unsigned char*>(net->tc_image); a.x = x; a.rows = rows; a.n = n;
     a.in_dim = net->in_dim; a.out_dim = net->out_dim; a.n_act = net->n_act; a.value_index = net->value_index;
-    a.mode = mode; a.scatter = scatter; a.seed = seed; a.counter = counter; a.rng_row0 = rng_row0;
+    a.mode = mode; a.scatter = scatter; a.seed = seed; a.counter = counter; a.rng_row0 = rng_row0; a.probs = net->probs_param;
     a.out = out; a.act = act; a.logp = logp; a.value = value; a.entropy = entropy;
     const size_t smem = mlptc::SM_FWD_TOTAL + 128;  // ~69 KB: three CTAs per SM (3 x 128 TMEM columns)
     static bool attr = false;
@@ -227,7 +227,7 @@ int tc_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch, const tsm_p
     a.mb_start = mb_start; a.mb_len = mb_len; a.mb_stats = mb_stats;
     a.cfg.eps_clip = cfg->eps_clip; a.cfg.dual_clip = cfg->dual_clip; a.cfg.vf_coef = cfg->vf_coef; a.cfg.ent_coef = cfg->ent_coef;
     a.cfg.value_clip = cfg->value_clip; a.cfg.adv_norm = cfg->adv_norm;
-    a.cfg.plain_pg = cfg->plain_pg; a.cfg.value_heads = cfg->value_heads;
+    a.cfg.plain_pg = cfg->plain_pg; a.cfg.value_heads = cfg->value_heads; a.cfg.probs_param = net->probs_param;
     a.in_dim = net->in_dim; a.out_dim = net->out_dim; a.n_act = net->n_act; a.value_index = net->value_index;
     float sc = 1.0f;  // S = 2^ceil(log2(mb_len)), capped, so that S / mb_len is in (0.5, 1]
     while (sc < (float)mb_len && sc < 1048576.0f) sc *= 2.0f;
@@ -304,7 +304,7 @@ int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, cons
     a.mb_start = start; a.mb_len = mb_size; a.mb_stats = nullptr;
     a.cfg.eps_clip = cfg->eps_clip; a.cfg.dual_clip = cfg->dual_clip; a.cfg.vf_coef = cfg->vf_coef; a.cfg.ent_coef = cfg->ent_coef;
     a.cfg.value_clip = cfg->value_clip; a.cfg.adv_norm = cfg->adv_norm;
-    a.cfg.plain_pg = cfg->plain_pg; a.cfg.value_heads = cfg->value_heads;
+    a.cfg.plain_pg = cfg->plain_pg; a.cfg.value_heads = cfg->value_heads; a.cfg.probs_param = net->probs_param;
     a.in_dim = net->in_dim; a.out_dim = net->out_dim; a.n_act = net->n_act; a.value_index = net->value_index;
     a.gscale = 1.f; a.inv_gscale = 1.f; a.loss_sums = nullptr;
     a.debug = getenv("TSM_TC_DEBUG") ? atoi(getenv("TSM_TC_DEBUG")) : 0;

@@ -201,7 +201,7 @@ struct TcFwdArgs {
     const float* x;
     const int64_t* rows;
     int64_t n;
-    int in_dim, out_dim, n_act, value_index, mode, scatter;
+    int in_dim, out_dim, n_act, value_index, mode, scatter, probs;
     uint64_t seed, counter;
     int64_t rng_row0;  // added to the row index in the sampling key (a launch over rows [row0, row0 + n) of a larger batch)
     float* out;
@@ -381,7 +381,7 @@ __global__ void __launch_bounds__(TC_THREADS) tc_forward_kernel(TcFwdArgs a) {
                         if (j < a.out_dim) a.out[dst * a.out_dim + j] = z[j];
                 }
             } else {
-                const Soft sm = softmax_row<TC_FAST_LOSS>(z, a.n_act);
+                const Soft sm = softmax_row<TC_FAST_LOSS>(z, a.n_act, a.probs != 0);
                 int act = 0;
                 if (a.mode == 1) {
                     const int64_t key = dst + a.rng_row0;

@@ -450,7 +450,7 @@ __device__ __forceinline__ void output_stage(const Ctx& c, const Args& a, int64_
     float z[OUTP];
 #pragma unroll
     for (int j = 0; j < OUTP; ++j) z[j] = o[j];
-    const Soft sm = softmax_row<true>(z, a.n_act);
+    const Soft sm = softmax_row<true>(z, a.n_act, a.cfg.probs_param != 0);
     int act = 0;
     if (a.mode == 1) {
         const int64_t key = prow + a.rng_row0;
@@ -1194,7 +1194,7 @@ extern "C" int tsm_tcw_forward(const tsm_net* net, const void* ximg, int64_t n_r
     tcw_fill_net(a, net);
     a.ximg = reinterpret_cast<const unsigned char*>(ximg); a.n_rows = n_rows; a.super_ids = nullptr; a.sub = 1; a.tile0 = 0;
     a.n_tiles = ceil_div(n_rows, tcw::ROWS);
-    a.mode = mode; a.seed = seed; a.counter = counter; a.rng_row0 = rng_row0;
+    a.mode = mode; a.seed = seed; a.counter = counter; a.rng_row0 = rng_row0; a.cfg.probs_param = net->probs_param;
     a.out = out; a.act = act; a.logp = logp; a.entropy = entropy;
     return a.KP <= tcw::RES_KP ? tcw_launch<false, false>(a, as_stream(stream)) : tcw_launch<true, false>(a, as_stream(stream));
 }
@@ -1250,7 +1250,7 @@ static int tcw_train_impl(const tsm_net* net, const tsm_tcw_tiles* t, const tsm_
     a.loss_kind = l->kind; a.adv = l->adv; a.logp_old = l->logp_old; a.act = const_cast<int32_t*>(l->act);
     a.target = l->target; a.v_old = l->v_old; a.weight = l->weight; a.heads = l->heads;
     a.cfg.eps_clip = cfg->eps_clip; a.cfg.dual_clip = cfg->dual_clip; a.cfg.vf_coef = cfg->vf_coef; a.cfg.ent_coef = cfg->ent_coef;
-    a.cfg.value_clip = cfg->value_clip; a.cfg.adv_norm = cfg->adv_norm; a.cfg.plain_pg = cfg->plain_pg; a.cfg.value_heads = 0;
+    a.cfg.value_clip = cfg->value_clip; a.cfg.adv_norm = cfg->adv_norm; a.cfg.plain_pg = cfg->plain_pg; a.cfg.value_heads = 0; a.cfg.probs_param = net->probs_param;
     a.inv_n = inv_n; a.gscale = gscale; a.inv_gscale = 1.0f / gscale;
     a.mb_stats = mb_stats; a.loss_sums = loss_sums;
     return a.KP <= tcw::RES_KP ? tcw_launch<false, true>(a, stream, max_ctas) : tcw_launch<true, true>(a, stream, max_ctas);

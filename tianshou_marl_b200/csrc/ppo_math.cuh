@@ -69,6 +69,7 @@ struct Soft {
     float logp[OUTP];
     float p[OUTP];
     float ent;
+    unsigned clamped;  // probs parameterisation only: bit j set where log p_j hit a clamp (no gradient flows through it)
 };
 // FAST: hardware exp2 / log2 / reciprocal approximations (about 2 ulp), used by the tcgen05 engine whose
 // GEMM operands are already rounded to fp16; the fp32 engine keeps the IEEE library versions.
@@ -76,8 +77,14 @@ template <bool FAST> __device__ __forceinline__ float exp_t(float x) { return FA
 template <bool FAST> __device__ __forceinline__ float log_t(float x) { return FAST ? __logf(x) : logf(x); }
 template <bool FAST> __device__ __forceinline__ float div_t(float a, float b) { return FAST ? __fdividef(a, b) : a / b; }
 
+// probs: the reference's DiscreteActor(softmax_output=True) + Categorical(probs=softmax(z)) (utils/net/discrete.py:85-86,
+// test/discrete/test_ppo_discrete.py:97-113).  torch turns the probabilities back into logits with
+// log(clamp(p, eps, 1 - eps)), eps = 2^-23 (torch.distributions.utils.probs_to_logits); log is monotonic, so that is
+// clamp(log p, log eps, log(1 - eps)).  Entropy and log-probabilities use the clamped logs; a clamped entry has no gradient.
+constexpr float PROBS_LOG_LO = -15.942385f;      // log(2^-23)
+constexpr float PROBS_LOG_HI = -1.1920930e-7f;   // log(1 - 2^-23)
 template <bool FAST = false>
-__device__ __forceinline__ Soft softmax_row(const float* z, int n_act) {
+__device__ __forceinline__ Soft softmax_row(const float* z, int n_act, bool probs = false) {
     Soft s;
     float m = -INFINITY;
 #pragma unroll
@@ -92,9 +99,16 @@ __device__ __forceinline__ Soft softmax_row(const float* z, int n_act) {
     const float lse = log_t<FAST>(sum);
     const float inv_sum = div_t<FAST>(1.f, sum);
     s.ent = 0.f;
+    s.clamped = 0u;
 #pragma unroll
     for (int j = 0; j < OUTP; ++j) {
-        s.logp[j] = j < n_act ? (z[j] - m) - lse : 0.f;
+        float lp = (z[j] - m) - lse;
+        if (probs && j < n_act) {
+            const float c = fminf(fmaxf(lp, PROBS_LOG_LO), PROBS_LOG_HI);
+            if (c != lp) s.clamped |= 1u << j;
+            lp = c;
+        }
+        s.logp[j] = j < n_act ? lp : 0.f;
         s.p[j] = j < n_act ? (FAST ? s.p[j] * inv_sum : s.p[j] / sum) : 0.f;
         if (j < n_act) s.ent -= s.p[j] * s.logp[j];
     }
@@ -108,6 +122,7 @@ struct PpoCfg {
                       // 2: the reference's literal CTDEPolicy.learn, where logp [n] * adv [n,1] broadcasts to [n,n]
                       //    (ctde.py:181-183): every row is weighted by the minibatch MEAN advantage (mb_stats[0])
     int value_heads;  // > 1: the value is the mean of that many head outputs from value_index on (ctde.py:153-156)
+    int probs_param;  // the net's softmax_output flag (tsm_net.probs_param): Categorical(probs = softmax(logits))
 };
 
 
@@ -123,7 +138,7 @@ __device__ __forceinline__ RowLoss row_loss(const float (&z)[OUTP], int n_act, i
 #pragma unroll
     for (int j = 0; j < OUTP; ++j) dz[j] = 0.f;
     if (n_act > 0) {
-        const Soft sm = softmax_row<FAST>(z, n_act);
+        const Soft sm = softmax_row<FAST>(z, n_act, cfg.probs_param != 0);
         float lp = 0.f;
 #pragma unroll
         for (int j = 0; j < OUTP; ++j)
@@ -152,9 +167,25 @@ __device__ __forceinline__ RowLoss row_loss(const float (&z)[OUTP], int n_act, i
         out.clip = li;
         out.ent = sm.ent;
         const float ec = cfg.ent_coef * inv_n;
+        if (sm.clamped == 0u) {
 #pragma unroll
-        for (int j = 0; j < OUTP; ++j)
-            if (j < n_act) dz[j] = dlp * ((j == act ? 1.f : 0.f) - sm.p[j]) + ec * sm.p[j] * (sm.logp[j] + sm.ent);
+            for (int j = 0; j < OUTP; ++j)
+                if (j < n_act) dz[j] = dlp * ((j == act ? 1.f : 0.f) - sm.p[j]) + ec * sm.p[j] * (sm.logp[j] + sm.ent);
+        } else {
+            // some log p_j sit on a clamp: d logp(act) = 0 if act is clamped; d(-ent)/dz_k = p_k (L_k + ent + u_k - U) with
+            // u_k = [k unclamped], U = sum of the unclamped p_j
+            float U = 0.f;
+#pragma unroll
+            for (int j = 0; j < OUTP; ++j)
+                if (j < n_act && !((sm.clamped >> j) & 1u)) U += sm.p[j];
+            const float dl = ((sm.clamped >> act) & 1u) ? 0.f : dlp;
+#pragma unroll
+            for (int j = 0; j < OUTP; ++j)
+                if (j < n_act) {
+                    const float u = ((sm.clamped >> j) & 1u) ? 0.f : 1.f;
+                    dz[j] = dl * ((j == act ? 1.f : 0.f) - sm.p[j]) + ec * sm.p[j] * (sm.logp[j] + sm.ent + u - U);
+                }
+        }
     }
     if (value_index >= 0) {
         const int nh = cfg.value_heads > 1 ? cfg.value_heads : 1;

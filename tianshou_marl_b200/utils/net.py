@@ -26,7 +26,7 @@ MODES = {"raw": 0, "sample": 1, "mode": 2, "eval": 3}
 class ActorCriticNet(nn.Module):
     def __init__(self, in_dim: int, hidden: int = 64, n_act: int = 5, with_value: bool = True, n_value_only: int = 0,
                  device: str | torch.device = "cuda", seed: int | None = None, orthogonal: bool = True,
-                 engine: str = "fp32") -> None:
+                 engine: str = "fp32", softmax_output: bool = False) -> None:
         """engine: "fp32" = exact CUDA-core kernels (csrc/mlp.cu); "tc" = tcgen05 tensor-core kernels with fp16 operands and
         fp32 accumulation (csrc/mlp_tc.cu; hidden 64, in_dim <= 31, out_dim <= 8); "tcw" = the wide tcgen05 engine of the CTDE
         nets (csrc/mlp_tcw.cu; hidden 128, in_dim <= 1023, out_dim <= 16, separate actor / value-only critic)."""
@@ -36,6 +36,9 @@ class ActorCriticNet(nn.Module):
         if engine == "tcw" and (hidden != 128 or with_value and not n_value_only):
             raise ValueError("engine 'tcw' (csrc/mlp_tcw.cu) runs separate hidden-128 nets: an actor (with_value=False) or a value-only critic")
         self.engine = engine
+        # DiscreteActor(softmax_output=True) + Categorical(probs=...) (utils/net/discrete.py:41,85-86): the kernels keep working on
+        # logits and evaluate log-probabilities / entropy as torch does for the probs parameterisation
+        self.softmax_output = bool(softmax_output)
         self.in_dim, self.hidden, self.n_act = int(in_dim), int(hidden), int(n_act)
         if n_value_only:  # critic-only net: out_dim value heads, no logits
             self.n_act, self.out_dim, self.value_index = 0, int(n_value_only), 0
@@ -93,6 +96,7 @@ class ActorCriticNet(nn.Module):
         d.tc_image = self.tc_image.data_ptr() if self.tc_image is not None else None
         xs = getattr(self, "_x_scratch", None)
         d.x_scratch, d.x_scratch_bytes = (xs.data_ptr(), xs.numel()) if xs is not None else (None, 0)
+        d.probs_param = int(self.softmax_output)
 
     @property
     def desc(self) -> Any:
