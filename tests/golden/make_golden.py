@@ -3,6 +3,7 @@
 Run (only where /root/reference exists; never on the GPU box):
 
     python tests/golden/make_golden.py [gae buffer ppo ppo_recompute ppo_retscale a2c reinforce ...]   (GENS lists the generators)
+    python tests/golden/make_golden_{ctde,large,mappo,collector,marl}.py                                (one fixture file each)
 
 The reference is imported from /root/reference through the import shims in oracle/shims/
 (stand-ins for gymnasium, pettingzoo, overrides, sensai, h5py, deepdiff, matplotlib, which

@@ -104,3 +104,59 @@ def test_shared_mode_equals_plain_ppo():
         res.append((buf._store["act"].clone(), net.flat.detach().clone()))
     assert torch.equal(res[0][0], res[1][0])  # same actions through the manager's generic collect loop
     assert torch.allclose(res[0][1], res[1][1], atol=1e-6)
+
+
+def test_manager_forward_matches_reference_fixture():
+    """tests/golden/marl.npz (make_golden_marl.py): the reference FlexibleMultiAgentPolicyManager.forward with copied weights and
+    deterministic policies.  independent mode: holder.act, the agent keys of out / state and every agent's own out.act are the
+    reference's.  shared / grouped: the reference's forward raises with real policies (recorded as found: `shared_error`,
+    `grouped_error` -- MultiAgentPolicy.forward iterates self.policies, which FlexibleMultiAgentPolicyManager re-keys by group
+    name, marl.py:141-150 / flexible_policy.py:93-105; _forward_shared drops batch.info); the build routes rows by the reference's
+    own policy_map, checked against the mapped reference policies evaluated per agent (`*_routed_act`)."""
+    import os
+
+    from tianshou_marl_b200.algorithm import DiscreteActorPolicy, FlexibleMultiAgentPolicyManager
+    from tianshou_marl_b200.data import Batch
+    from tianshou_marl_b200.utils import ActorCriticNet
+
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "marl.npz"))
+    A, O, H, nA, E = (int(x) for x in z["dims"])
+    agents = [str(a) for a in z["agents"]]
+
+    class Env:
+        pass
+
+    env = Env()
+    env.agents = agents
+    obs = torch.as_tensor(z["obs"], device="cuda")
+    assert int(z["independent_ok"]) == 1 and int(z["shared_ok"]) == 0 and int(z["grouped_ok"]) == 0  # as found in the reference
+    for mode in ("independent", "shared", "grouped"):
+        pof = z[f"{mode}_policy_of_agent"]
+        pols = []
+        for i in range(int(pof.max()) + 1):
+            net = ActorCriticNet(O, H, nA, with_value=False).load_arrays(*[z[f"{mode}_p{i}_{k}"] for k in ("W1", "b1", "W2", "b2", "W3", "b3")])
+            pols.append(DiscreteActorPolicy(actor=net, deterministic_eval=True))
+        if mode == "independent":
+            man = FlexibleMultiAgentPolicyManager([pols[int(i)] for i in pof], env, mode="independent")
+        elif mode == "shared":
+            man = FlexibleMultiAgentPolicyManager(pols[0], env, mode="shared")
+        else:
+            man = FlexibleMultiAgentPolicyManager({"adv": pols[0], "good": pols[1]}, env, mode="grouped",
+                                                  agent_groups={"adv": agents[:3], "good": agents[3:]})
+        assert [str(k) for k in z[f"{mode}_policies_keys"]] == list(man.policies.keys())
+        h = man.forward(Batch(obs=obs))
+        act = h.act.cpu().numpy()
+        # logits within 1e-5 of the reference's; an argmax may only differ where the two best logits are that close
+        want, lg = z[f"{mode}_routed_act"], z[f"{mode}_routed_logits"]
+        top2 = np.sort(lg, axis=1)[:, -2:]
+        clear = (top2[:, 1] - top2[:, 0]) > 1e-4
+        assert np.array_equal(act[clear], want[clear]) and clear.mean() > 0.95
+        assert list(h.out.keys()) == agents and list(h.state.keys()) == agents
+        if mode == "independent":
+            assert np.array_equal(z["independent_act"][clear], want[clear])  # the reference holder.act is the routed act
+            assert [str(k) for k in z["independent_out_keys"]] == agents and [str(k) for k in z["independent_state_keys"]] == agents
+            for ai, a in enumerate(agents):
+                rows = np.arange(ai, E * A, A)
+                got = h.out[a].act.cpu().numpy()
+                assert got.shape == z[f"independent_out_{a}_act"].shape
+                assert np.array_equal(got[clear[rows]], z[f"independent_out_{a}_act"][clear[rows]])

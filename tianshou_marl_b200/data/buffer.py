@@ -332,8 +332,31 @@ class VectorReplayBuffer:
                 v = self._finish(k, g[k], host)
                 pol.__dict__[k] = v[0] if scalar else v
             out.__dict__["policy"] = pol
+        for k, t in self.__dict__.get("_extra", {}).items():
+            v = t[idx]
+            v = v.cpu().numpy() if host else v
+            out.__dict__[k] = v[0] if scalar else v
         out.__dict__.setdefault("info", Batch())
         return out
+
+    def set_array_at_key(self, seq: Any, key: str, index: Any = None, default_value: float | None = None) -> None:
+        """buffer_base.py:637-644 / batch.py set_array_at_key: write `seq` into the extra key `key` at env-major `index` (None: the
+        whole key); a key that does not exist yet is created for all slots, filled with default_value (NaN when None) -- what
+        the collector's episode hooks use to attach per-transition results such as MC returns (collector.py:1000-1011)."""
+        if key in _RESERVED:
+            raise ValueError(f"{key!r} is a reserved buffer key")
+        extra = self.__dict__.setdefault("_extra", {})
+        arr = torch.as_tensor(np.asarray(seq) if not isinstance(seq, torch.Tensor) else seq).to(device=self.device, dtype=torch.float64)
+        if index is None:
+            if arr.shape[0] != self.maxsize:
+                raise ValueError("a whole-key assignment must cover every slot")
+            extra[key] = arr.clone()
+            return
+        if key not in extra:
+            fill = float("nan") if default_value is None else float(default_value)
+            extra[key] = torch.full((self.maxsize, *arr.shape[1:]), fill, dtype=torch.float64, device=self.device)
+        idx = self._dev(np.atleast_1d(index) if _is_host(index) else index, torch.int64).reshape(-1)
+        extra[key][idx] = arr
 
     def sample(self, batch_size: int | None) -> tuple[Batch, Any]:
         """buffer_base.py:533-541."""
@@ -344,6 +367,9 @@ class VectorReplayBuffer:
         """buf.obs / buf.done / ... (buffer_base.py:237-241): the whole stored array, numbered
         env-major like the reference.  This is a gathered COPY of the time-major device storage."""
         store = self.__dict__.get("_store")
+        extra = self.__dict__.get("_extra")
+        if extra is not None and key in extra:
+            return extra[key].cpu().numpy() if self.index_type == "numpy" else extra[key]
         if store is None or key not in _RESERVED or key not in store:
             raise AttributeError(key)
         t = store[key]

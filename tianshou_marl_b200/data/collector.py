@@ -21,6 +21,7 @@ from __future__ import annotations
 import ctypes as C
 import os
 import time
+import warnings
 from typing import Any
 
 import numpy as np
@@ -48,9 +49,9 @@ class Collector:
                 f"Buffer has only {buffer.buffer_num} buffers, but at least {self.env_num=} are needed.")
         self.buffer = buffer
         self.exploration_noise = exploration_noise
+        # hooks (collector.py:583-689): accepted; a collector with hooks runs the reference's per-step host loop (_reference_loop)
+        # instead of the fused device loop, because the hooks are Python callables that see every step / episode batch
         self.on_episode_done_hook, self.on_step_hook = on_episode_done_hook, on_step_hook
-        if on_episode_done_hook is not None or on_step_hook is not None:
-            raise NotImplementedError("per-step / per-episode Python hooks are not on the device path")
         self.raise_on_nan_in_buffer = raise_on_nan_in_buffer
         self.collect_stats_class = collect_stats_class
         self.episode_list = episode_list
@@ -162,6 +163,11 @@ class Collector:
                 self._list_len = torch.zeros(cap, dtype=torch.int64, device=dev)
                 self._list_cap = cap
         fused = self._fused_ok(random)
+        hooks = self.on_episode_done_hook is not None or self.on_step_hook is not None
+        if hooks or not isinstance(self.env, MPEVectorEnv):
+            # any other vector env, or Python hooks: the reference's loop itself (ready-env subset, surplus-env rule, episode
+            # extraction, hooks, end-of-collect reset), one host iteration per vector step
+            return self._reference_loop(n_step, n_episode, random)
         steps = 0
         if fused and n_vec is not None and not os.environ.get("TSM_COLLECT_PY"):
             self._fused_run(n_vec, random)  # the whole loop in one C call (csrc/collect.cu)
@@ -299,6 +305,118 @@ class Collector:
         _lib.t_stop(tk)
         self._pre_collect_obs = carry
 
+    # -- the reference's loop (collector.py:770-1098), step numbers as in its docstring -------------------------------------
+    def run_on_episode_done(self, episode_batch: Any) -> dict | None:
+        """collector.py:663-675."""
+        return self.on_episode_done_hook(episode_batch) if self.on_episode_done_hook is not None else None
+
+    def run_on_step_hook(self, action_batch: Any, rollout_batch: Any) -> None:
+        """collector.py:677-689."""
+        if self.on_step_hook is not None:
+            self.on_step_hook(action_batch, rollout_batch)
+
+    def _reference_loop(self, n_step: int | None, n_episode: int | None, random: bool) -> CollectStats:
+        env, buf, N = self.env, self.buffer, self.env_num
+        if getattr(env, "is_async", False):  # collector.py:804-809
+            raise ValueError(f"Please use AsyncCollector for asynchronous environments. Env class: {env.__class__.__name__}.")
+        whole = isinstance(env, MPEVectorEnv)  # a batched world steps all rows at once
+        if n_step is not None:
+            ready = np.arange(N)
+        else:
+            if N > n_episode:  # collector.py:816-822 (a warning, not an error)
+                warnings.warn(f"Number of episodes ({n_episode}) is smaller than the number of environments ({N}). This means that "
+                              f"{N - n_episode} environments (or, equivalently, parallel workers) will not be used!")
+            ready = np.arange(min(N, n_episode))
+        if whole and len(ready) != N:
+            raise NotImplementedError("MPEVectorEnv steps whole worlds: n_episode must be >= the number of rows")
+        to_host = lambda x: x.detach().cpu().numpy() if isinstance(x, torch.Tensor) else np.asarray(x)  # noqa: E731
+        take = lambda x, ids: x[torch.as_tensor(ids, device=x.device)] if isinstance(x, torch.Tensor) else np.asarray(x)[ids]  # noqa: E731
+        step_count, n_ep = 0, 0
+        returns: list[float] = []
+        lens: list[int] = []
+        last_obs = take(self._pre_collect_obs, ready)
+        while True:
+            # Step 2: actions for the R ready envs (collector.py:704-767)
+            if random:
+                act = np.array([env.action_space[int(i)].sample() for i in ready])
+                pol_out = Batch(act=act)
+            else:
+                pol_out = self.policy(Batch(obs=last_obs, info=Batch()), None)
+                act = pol_out.act
+            act_env = self.policy.map_action(act) if hasattr(self.policy, "map_action") else act
+            # Step 3
+            if whole:
+                obs_next, rew, term, trunc, info = env.step(act_env)
+            else:
+                obs_next, rew, term, trunc, info = env.step(to_host(act_env), ready)
+            done = to_host(term).astype(bool) | to_host(trunc).astype(bool)
+            step_b = Batch(obs=last_obs, act=act, rew=rew, terminated=term, truncated=trunc, obs_next=obs_next)
+            step_b.__dict__["done"] = done
+            # Step 4
+            self.run_on_step_hook(pol_out, step_b)
+            # Step 5
+            n_done = int(done.sum())
+            n_ep += n_done
+            step_count += len(ready)
+            # Step 6
+            add_b = Batch(obs=last_obs, act=act, rew=rew, terminated=term, truncated=trunc, obs_next=obs_next)
+            if "logp" in pol_out and "value" in pol_out:
+                add_b.__dict__["policy"] = Batch(logp=pol_out.logp, value=pol_out.value)
+            idx, ep_ret, ep_len, ep_start = buf.add(add_b, buffer_ids=None if (len(ready) == buf.buffer_num) else ready)
+            last_obs = obs_next.clone() if isinstance(obs_next, torch.Tensor) else np.array(obs_next, copy=True)
+            if n_done > 0:
+                # Steps 7-8: the D envs that ended an episode, reset them
+                d_local = np.where(done)[0]
+                idx_h, ret_h, len_h, start_h = to_host(idx), to_host(ep_ret), to_host(ep_len), to_host(ep_start)
+                lens.extend(int(x) for x in len_h[d_local])
+                returns.extend(float(x) for x in ret_h[d_local])
+                d_global = ready[d_local]
+                obs_reset, _ = env.reset(torch.as_tensor(d_global, device=self.device) if whole else d_global)
+                # Steps 9-11: the episode batch of every finished episode, hook, additions written back (n_episode only)
+                if self.on_episode_done_hook is not None:
+                    for li in d_local:
+                        ep_idx = buf.get_buffer_indices(int(start_h[li]), int(idx_h[li]) + 1)
+                        ep_batch = buf[np.asarray(ep_idx)]
+                        add = self.run_on_episode_done(ep_batch)
+                        if add is not None:
+                            if n_episode is None:
+                                raise ValueError(
+                                    "An on_episode_done_hook with non-empty returns is not supported for n_step collection."
+                                    "Such hooks should only be used when collecting full episodes. Got a on_episode_done_hook "
+                                    f"that would add the following fields to the buffer: {list(add)}.")
+                            for key, arr in add.items():
+                                buf.set_array_at_key(arr, key, index=np.asarray(ep_idx))
+                # Step 12
+                if isinstance(last_obs, torch.Tensor):
+                    last_obs[torch.as_tensor(d_local, device=last_obs.device)] = torch.as_tensor(obs_reset, device=last_obs.device)
+                else:
+                    last_obs[d_local] = to_host(obs_reset)
+                # Step 13: surplus envs leave the ready set (only envs that just finished an episode can be removed)
+                if n_episode:
+                    surplus = len(ready) - (n_episode - n_ep)
+                    if surplus > 0:
+                        if whole:
+                            raise NotImplementedError("MPEVectorEnv steps whole worlds: rows cannot leave the ready set")
+                        keep = np.ones(len(ready), dtype=bool)
+                        keep[d_local[:surplus]] = False
+                        ready = ready[keep]
+                        last_obs = take(last_obs, np.where(keep)[0])
+            if (n_step and step_count >= n_step) or (n_episode and n_ep >= n_episode):
+                break
+        st = self.collect_stats_class(n_collected_episodes=n_ep, n_collected_steps=step_count)
+        if n_ep > 0:
+            st.returns, st.lens = np.asarray(returns, dtype=float), np.asarray(lens, dtype=int)
+        r, l = np.asarray(returns, dtype=float), np.asarray(lens, dtype=float)
+        self.last_episode_summary = {"count": n_ep, "ret_sum": r.sum(), "ret_sqsum": (r * r).sum(), "ret_min": r.min() if n_ep else np.inf,
+                                     "ret_max": r.max() if n_ep else -np.inf, "len_sum": l.sum(), "len_sqsum": (l * l).sum(),
+                                     "len_min": l.min() if n_ep else np.inf, "len_max": l.max() if n_ep else -np.inf}
+        # Step 15
+        if n_step:
+            self._pre_collect_obs = last_obs
+        else:
+            self.reset_env()
+        return st
+
     # -- one vector step, generic (reference loop) ---------------------------------------------
     def _generic_step(self, random: bool) -> None:
         env, buf = self.env, self.buffer
@@ -338,3 +456,25 @@ class Collector:
                 obs_next = np.array(obs_next, copy=True)
                 obs_next[ids_h] = obs_reset
         self._pre_collect_obs = obs_next
+
+
+class EpisodeRolloutHookMCReturn:
+    """collector.py:1480-1509: adds the discounted Monte-Carlo return to go and the full-episode return to every transition of
+    a finished episode (an on_episode_done_hook; n_episode collection).  The return to go is K3 with lambda = 1 and zero values
+    (algorithm.returns.episode_mc_return_to_go -> csrc/gae.cu)."""
+
+    MC_RETURN_TO_GO_KEY = "mc_return_to_go"
+    FULL_EPISODE_MC_RETURN_KEY = "full_episode_mc_return"
+
+    def __init__(self, gamma: float = 0.99) -> None:
+        if not 0 <= gamma <= 1:
+            raise ValueError(f"Expected 0 <= gamma <= 1, but got {gamma=}.")
+        self.gamma = gamma
+
+    def __call__(self, episode_batch: Any) -> dict[str, np.ndarray]:
+        from ..algorithm.returns import episode_mc_return_to_go
+
+        rew = episode_batch.rew
+        rew = rew.detach().cpu().numpy() if isinstance(rew, torch.Tensor) else np.asarray(rew)
+        to_go = np.asarray(episode_mc_return_to_go(rew.astype(np.float64), self.gamma), dtype=np.float64)
+        return {self.MC_RETURN_TO_GO_KEY: to_go, self.FULL_EPISODE_MC_RETURN_KEY: np.full_like(to_go, to_go[0])}
