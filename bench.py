@@ -52,9 +52,9 @@ def parse() -> argparse.Namespace:
     p.add_argument("--no-update", action="store_true", help="collect + GAE only")
     p.add_argument("--reuse-rollout", action="store_true",
                    help="PPO(reuse_rollout_policy_outputs=True): critic(obs) / logp_old come from the collect-time forward (off in the headline run)")
-    p.add_argument("--workload", default="c2", choices=["c2", "c3", "c5"],
+    p.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5"],
                    help="c2: the headline collect+GAE+PPO step; c3: MAPPO / CTDE, N = 10 agents, 32 768 worlds per GPU (BASELINE.json "
-                        "configs[2]); c5: GAE + buffer add/sample microbench (T=128, 1M rows), one GPU")
+                        "configs[2]); c4: simple_tag grouped policies, 131 072 worlds in total over the ranks (configs[3], strong scaling); c5: GAE + buffer add/sample microbench (T=128, 1M rows), one GPU")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-c5", action="store_true", help="skip the configs[4] microbench that rides on the default N = 1 line")
     p.add_argument("--cpu-envs", type=int, default=4096, help="reference arm: environments in the bounded sample")
@@ -376,7 +376,7 @@ def main() -> None:
     import torch.distributed as dist
 
     from tianshou_marl_b200 import _lib
-    from tianshou_marl_b200.bench_workload import Workload, WorkloadC3
+    from tianshou_marl_b200.bench_workload import Workload, WorkloadC3, WorkloadC4
 
     rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -396,6 +396,10 @@ def main() -> None:
         if args.envs == 65536 and args.agents == 3:  # the c2 defaults: switch to configs[2]
             args.envs, args.agents = 32768, 10
         wl = WorkloadC3(args, rank, world)
+    elif args.workload == "c4":
+        if args.envs == 65536 and args.agents == 3:  # the c2 defaults: switch to configs[3]
+            args.envs = 131072
+        wl = WorkloadC4(args, rank, world)
     else:
         wl = Workload(args, rank, world)
 
@@ -460,6 +464,9 @@ def main() -> None:
                 "stages_ms": stages, "roofline": roof}
         if ident is not None:
             line.update(ident)
+        if args.workload == "c4":
+            line["metric"] = "agent-steps/sec collect+PPO update, simple_tag grouped policies"
+            line["scaling"] = "strong"
         if args.workload == "c3":
             line["metric"] = "agent-steps/sec collect+MAPPO update, simple_spread N=10 (centralized critic)"
         if world == 1 and args.workload == "c2" and not args.no_c5:

@@ -600,6 +600,15 @@ typedef struct tsm_tcw_epoch {
 } tsm_tcw_epoch;
 int tsm_tcw_ppo_epoch(const tsm_tcw_epoch* e, const tsm_ppo_cfg* cfg, tsm_stream_t stream);
 
+/* tsm_collect_lockstep for GROUPED policies (FlexibleMultiAgentPolicyManager.forward inside the rollout loop,
+ * multiagent/flexible_policy.py:189-231 -> marl.py:108-185): group g = (nets[g], rows[g][0..n_rows[g]) device row list, policy
+ * seed seeds[g], first sampling counter counters0[g]); one fused forward launch per group and vector step (row gather, act /
+ * logp / value scattered into buffer slot t, sampling key = global row) + one tsm_rollout_step over all worlds. */
+int tsm_collect_lockstep_groups(const tsm_net* const* nets, const int64_t* const* rows, const int64_t* n_rows, const uint64_t* seeds,
+                                const uint64_t* counters0, int n_groups, const tsm_mpe* env, const tsm_buf* buf, const tsm_rollout* ro,
+                                int64_t n_steps, int mode, int64_t lockstep_len, int64_t* slot_out, int64_t* lockstep_len_out,
+                                int* obs_in_carry_out, tsm_stream_t stream);
+
 /* tcgen05 self test (tests only): D[128][n] = A * B with A / B given as shared-memory images
  * (float32 words, copied verbatim to smem) and explicit descriptor fields
  * h_desc = {a_lbo, a_sbo, a_kstep_bytes, b_lbo, b_sbo, b_kstep_bytes}; kind::tf32, M = 128,

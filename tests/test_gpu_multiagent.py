@@ -160,3 +160,27 @@ def test_manager_forward_matches_reference_fixture():
                 got = h.out[a].act.cpu().numpy()
                 assert got.shape == z[f"independent_out_{a}_act"].shape
                 assert np.array_equal(got[clear[rows]], z[f"independent_out_{a}_act"][clear[rows]])
+
+
+@pytest.mark.parametrize("engine", ["fp32", "tc"])
+def test_fused_grouped_rollout_equals_generic_loop(engine, monkeypatch):
+    """tsm_collect_lockstep_groups (one forward launch per policy group and step inside the C loop) writes the same buffer,
+    bit for bit, as the per-step Python loop through FlexibleMultiAgentPolicyManager.forward."""
+    res = {}
+    for py in (True, False):
+        if py:
+            monkeypatch.setenv("TSM_COLLECT_PY", "1")
+        else:
+            monkeypatch.delenv("TSM_COLLECT_PY", raising=False)
+        env, algs, man, buf, Collector, A, O = _setup(E=96, T=12, engine=engine)
+        col = Collector(man, env, buf)
+        col.reset()
+        for a in algs.values():
+            a.policy.is_within_training_step = True
+        man.is_within_training_step = True
+        st = col.collect(n_step=12 * 96 * A)
+        res[py] = ({k: v.clone() for k, v in buf._store.items() if v is not None}, st.n_collected_episodes, [a.policy._counter for a in algs.values()])
+    (sa, ea, ca), (sb, eb, cb) = res[True], res[False]
+    assert ea == eb and ca == cb
+    for k in sa:
+        assert torch.equal(sa[k], sb[k]), k

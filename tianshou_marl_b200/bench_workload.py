@@ -237,3 +237,80 @@ class WorkloadC3(Workload):
                 "rows_per_minibatch": self.mb_super * 128 * self.A, "repeat": a.repeat, "hidden": 128, "engine": "tcw",
                 "minibatches_per_epoch": self.n_mb,
                 "l2": "inputs larger than L2: per-step working set %.0f MB > 126 MB" % (self.R * self.T * (8 * self.O + 30) / 1e6)}
+
+
+class WorkloadC4(Workload):
+    """BASELINE.json configs[3]: simple_tag_v3 with grouped policies (three adversaries share one PPO policy, the good agent has its
+    own), 131 072 worlds IN TOTAL at 1 / 2 / 4 / 8 GPUs (strong scaling: --envs is the total, each rank takes total / world).
+    FlexibleMultiAgentPolicyManager inside the fused rollout loop (tsm_collect_lockstep_groups: one forward launch per policy
+    group and step), then one PPO.update per group over its strided row set (persistent epoch kernel with explicit row lists)."""
+
+    def __init__(self, args: Any, rank: int, world: int) -> None:
+        from .algorithm import FlexibleMultiAgentPolicyManager
+
+        self.args, self.rank, self.world = args, rank, world
+        self.E, self.T = args.envs // world, args.horizon
+        self.env = MPEVectorEnv("simple_tag_v3", n_envs=self.E, seed=1000 + rank)
+        self.A, self.O = self.env.n_agents, self.env.obs_dim
+        self.R = self.E * self.A
+        self.buf = VectorReplayBuffer(self.T * self.R, self.R, index_type="torch")
+        self.algs = {}
+        for name, seed in (("adversaries", 1), ("good", 2)):
+            net = ActorCriticNet(self.O, args.hidden, 5, seed=seed, engine=args.engine)  # same init on every rank
+            pol = DiscreteActorPolicy(actor=net, seed=77 + 10 * seed + rank)
+            self.algs[name] = PPO(policy=pol, critic=net, optim=AdamOptimizerFactory(lr=3e-4), max_grad_norm=0.5, minibatch_order="device", seed=rank)
+        ag = self.env.agents
+        groups = {"adversaries": [a for a in ag if a.startswith("adversary")], "good": [a for a in ag if a.startswith("agent")]}
+        self.manager = FlexibleMultiAgentPolicyManager(self.algs, self.env, mode="grouped", agent_groups=groups)
+        self.net = self.algs["adversaries"].net
+        self.critic = None
+        self.alg = self.algs["adversaries"]
+        self.collector = Collector(self.manager, self.env, self.buf, episode_list=False)
+        self.collector.reset()
+        for a in self.algs.values():
+            a.policy.is_within_training_step = True
+        self.manager.is_within_training_step = True
+        self.update = not args.no_update
+        self.agent_steps_per_step = self.R * self.T
+        self.dtype = "f16 operands / f32 accumulate (tcgen05)" if args.engine == "tc" else "f32"
+        n_adv = len(groups["adversaries"])
+        self.n_mb = sum(len(PPO.split_bounds(self.E * k * self.T, args.batch_size)) - 1 for k in (n_adv, self.A - n_adv))
+        self.launches_per_step = self.T * (2 * K_POLICY + K_ROLLOUT_STEP) + 1
+        if self.update:
+            per_epoch = 2 if args.engine == "tc" else 1 + 2 * self.n_mb
+            self.launches_per_step += 2 * (3 + 1 + 1) + args.repeat * 2 * per_epoch
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+        self.last_stats = None
+
+    def nets(self) -> list:
+        return [a.net for a in self.algs.values()]
+
+    def grad_sync(self) -> str:
+        return "peer (inside the epoch kernel over NVLink)" if all(getattr(a, "_peers", None) is not None for a in self.algs.values()) else "nccl all_reduce per minibatch"
+
+    def step(self, timed: bool = False) -> None:
+        self.collector.collect(n_step=self.R * self.T)
+        if self.update:
+            self.last_stats = self.manager.update(self.buf, self.args.batch_size, self.args.repeat)
+        self.collector.reset_buffer(keep_statistics=True)
+
+    def step_e2e(self) -> None:
+        self.collector.episode_list = True
+        cs = self.collector.collect(n_step=self.R * self.T)
+        self.d2h_bytes = 9 * 8 + cs.returns.nbytes + cs.lens.nbytes
+        if self.update:
+            ts = self.manager.update(self.buf, self.args.batch_size, self.args.repeat)
+            self.d2h_bytes += sum(t.gradient_steps for t in ts.values()) * 4 * 8
+            self.last_stats = ts
+        self.collector.reset_buffer(keep_statistics=True)
+        self.collector.episode_list = False
+        self.h2d_bytes = (self.n_mb + 2) * 8 * (self.args.repeat if self.update else 0)
+
+    def config(self) -> dict:
+        a = self.args
+        return {"workload": f"C4 simple_tag_v3 grouped policies (3 adversaries share one PPO policy + 1 good agent) {a.envs} worlds in total, "
+                            f"{self.E}/GPU, T={self.T}: collect+GAE+PPO update per group; MLP {self.O}->{a.hidden}->{a.hidden}->(5 logits, 1 value) per group",
+                "envs_total": a.envs, "envs_per_gpu": self.E, "agents": self.A, "horizon": self.T, "rows_per_gpu": self.R, "batch_size": a.batch_size,
+                "repeat": a.repeat, "hidden": a.hidden, "engine": a.engine, "minibatches_per_epoch": self.n_mb,
+                "l2": "inputs larger than L2: per-step working set %.0f MB > 126 MB" % (self.R * self.T * (8 * self.O + 30) / 1e6)}

@@ -103,3 +103,51 @@ extern "C" int tsm_collect_lockstep(const tsm_net* net, const tsm_mpe* env, cons
     if (obs_in_carry_out) *obs_in_carry_out = in_carry ? 1 : 0;
     return TSM_OK;
 }
+
+// The same loop for GROUPED policies (FlexibleMultiAgentPolicyManager.forward inside the rollout, reference
+// multiagent/flexible_policy.py:189-231 -> marl.py:108-185): with rows flattened as row = world * A + agent the rows of a policy
+// group are a fixed strided set, so every vector step is one fused forward launch PER POLICY GROUP (row gather + scatter of
+// act / logp / value straight into buffer slot t; sampling key = the global row, seed and counter of the group's policy) and one
+// tsm_rollout_step over all worlds.  No Python per step.
+extern "C" int tsm_collect_lockstep_groups(const tsm_net* const* nets, const int64_t* const* rows, const int64_t* n_rows, const uint64_t* seeds,
+                                           const uint64_t* counters0, int n_groups, const tsm_mpe* env, const tsm_buf* buf, const tsm_rollout* ro,
+                                           int64_t n_steps, int mode, int64_t lockstep_len, int64_t* slot_out, int64_t* lockstep_len_out,
+                                           int* obs_in_carry_out, tsm_stream_t stream) {
+    TSM_REQUIRE(nets && rows && n_rows && seeds && counters0 && n_groups >= 1 && n_groups <= 64, "group arrays != NULL, 1 <= n_groups <= 64");
+    TSM_REQUIRE(env && buf && ro, "env / buf / rollout != NULL");
+    TSM_REQUIRE(n_steps >= 0 && ro->size > 0 && ro->slot >= 0 && ro->slot < ro->size, "n_steps >= 0, 0 <= slot < size");
+    TSM_REQUIRE(ro->obs && ro->act && ro->rew && ro->terminated && ro->truncated && ro->obs_next && ro->carry, "payload pointers != NULL");
+    TSM_REQUIRE(ro->ep_ret && ro->ep_len && ro->acc, "episode scratch != NULL");
+    TSM_REQUIRE(mode == 1 || mode == 2, "mode: 1 sample, 2 argmax");
+    const int64_t R = ro->n_rows, O = ro->obs_dim, size = ro->size;
+    TSM_REQUIRE(R > 0 && O > 0, "n_rows, obs_dim > 0");
+    for (int g = 0; g < n_groups; ++g) TSM_REQUIRE(nets[g] && rows[g] && n_rows[g] > 0, "every group needs a net and a row list");
+    int64_t slot = ro->slot, len = lockstep_len;
+    bool in_carry = false;
+    cudaStream_t s = as_stream(stream);
+    for (int64_t k = 0; k < n_steps; ++k) {
+        float* obs_slot = ro->obs + slot * R * O;
+        int32_t* act_slot = ro->act + slot * R;
+        const int64_t nxt = (slot + 1) % size;
+        const bool to_carry = (k == n_steps - 1) || (len + 1 >= size);
+        float* carry = to_carry ? ro->carry : ro->obs + nxt * R * O;
+        if (in_carry) TSM_CUDA(cudaMemcpyAsync(obs_slot, ro->carry, sizeof(float) * R * O, cudaMemcpyDeviceToDevice, s));
+        for (int g = 0; g < n_groups; ++g) {
+            int rc = tsm_net_forward(nets[g], obs_slot, rows[g], n_rows[g], mode, 1, seeds[g], counters0[g] + (uint64_t)k, nullptr, act_slot,
+                                     ro->logp ? ro->logp + slot * R : nullptr,
+                                     (ro->value && nets[g]->value_index >= 0) ? ro->value + slot * R : nullptr, nullptr, stream);
+            if (rc) return rc;
+        }
+        int rc = tsm_rollout_step(env, buf, act_slot, ro->obs_next + slot * R * O, ro->rew + slot * R, ro->terminated + slot * R,
+                                  ro->truncated + slot * R, carry, ro->ep_ret, ro->ep_len, ro->acc, ro->list_ret, ro->list_len, ro->list_count,
+                                  ro->list_cap, 0, env->n_envs, stream);
+        if (rc) return rc;
+        len = len + 1 < size ? len + 1 : size;
+        slot = nxt;
+        in_carry = to_carry;
+    }
+    if (slot_out) *slot_out = slot;
+    if (lockstep_len_out) *lockstep_len_out = len;
+    if (obs_in_carry_out) *obs_in_carry_out = in_carry ? 1 : 0;
+    return TSM_OK;
+}

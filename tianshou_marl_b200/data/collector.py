@@ -146,8 +146,28 @@ class Collector:
         from ..algorithm.ppo import DiscreteActorPolicy
 
         b = self.buffer
+        if not random and self._manager_groups() is not None:
+            return isinstance(self.env, MPEVectorEnv) and b._lockstep_len is not None and b.buffer_num == self.env_num and b._save_obs_next
         return (isinstance(self.env, MPEVectorEnv) and (random or isinstance(self.policy, DiscreteActorPolicy))
                 and b._lockstep_len is not None and b.buffer_num == self.env_num and b._save_obs_next)
+
+    def _manager_groups(self) -> list | None:
+        """[(DiscreteActorPolicy, rows)] when the policy is a FlexibleMultiAgentPolicyManager over fused-capable policies."""
+        from ..algorithm.multiagent import FlexibleMultiAgentPolicyManager
+        from ..algorithm.ppo import DiscreteActorPolicy
+
+        man = self.policy
+        if not isinstance(man, FlexibleMultiAgentPolicyManager):
+            return None
+        out = []
+        for p, rows in man.groups(self.env_num, self.device):
+            pol = man._actor_policy(p)
+            if not isinstance(pol, DiscreteActorPolicy) or getattr(pol.actor, "engine", None) == "tcw":
+                return None
+            if rows is None:
+                rows = torch.arange(self.env_num, device=self.device, dtype=torch.int64)
+            out.append((pol, rows))
+        return out
 
     def _collect(self, n_step: int | None, n_episode: int | None, random: bool) -> CollectStats:
         R = self.env_num
@@ -173,7 +193,7 @@ class Collector:
             self._fused_run(n_vec, random)  # the whole loop in one C call (csrc/collect.cu)
             steps = n_vec
         while steps == 0 or n_vec is None or steps < n_vec:
-            if fused:
+            if fused and (random or hasattr(self.policy, "actor")):
                 self._fused_step(random, last=(n_vec is not None and steps == n_vec - 1) or n_vec is None)
             else:
                 self._generic_step(random)
@@ -225,7 +245,8 @@ class Collector:
                              list_len=P(self._list_len) if self.episode_list else None,
                              list_count=P(self._list_count) if self.episode_list else None, list_cap=self._list_cap)
         # which parameters produced the stored logp / value (PPO's reuse_rollout_policy_outputs checks this)
-        ver = None if random or st.get("value") is None or self.policy.actor.value_index < 0 else self.policy.actor.param_version
+        single = hasattr(self.policy, "actor")
+        ver = None if random or not single or st.get("value") is None or self.policy.actor.value_index < 0 else self.policy.actor.param_version
         buf._policy_version = ver if (buf._lockstep_len == 0 or buf._policy_version == ver) else None
         buf._obs_chain = bool(buf._lockstep_len == 0 or buf._obs_chain)  # the kernel writes obs_next[t] and obs[t + 1] from the same registers
         slot_o, len_o, carry_o = C.c_int64(0), C.c_int64(0), C.c_int(0)
@@ -235,6 +256,23 @@ class Collector:
                                               self._random_counter, buf._lockstep_len, int(env.single_action_space.n),
                                               C.byref(slot_o), C.byref(len_o), C.byref(carry_o), S))
             self._random_counter += n_vec
+        elif self._manager_groups() is not None:
+            # grouped policies: one fused forward launch per policy group and step, no Python per step (csrc/collect.cu)
+            man, groups = self.policy, self._manager_groups()
+            G = len(groups)
+            det = all(p.deterministic_eval and not (p.is_within_training_step or man.is_within_training_step) for p, _ in groups)
+            nets = (C.c_void_p * G)(*[C.addressof(p.actor._desc) for p, _ in groups])
+            for p, _ in groups:
+                p.actor.desc  # refresh (packs the fp16 image when the parameters changed)
+            rows_a = (C.c_void_p * G)(*[r.data_ptr() for _, r in groups])
+            n_rows = (C.c_int64 * G)(*[int(r.numel()) for _, r in groups])
+            seeds = (C.c_uint64 * G)(*[int(p.seed) for p, _ in groups])
+            ctrs = (C.c_uint64 * G)(*[int(p._counter) for p, _ in groups])
+            buf._policy_version = None
+            _lib.check(L.tsm_collect_lockstep_groups(nets, rows_a, n_rows, seeds, ctrs, G, C.byref(env._desc), C.byref(buf._desc), C.byref(ro), n_vec,
+                                                     2 if det else 1, buf._lockstep_len, C.byref(slot_o), C.byref(len_o), C.byref(carry_o), S))
+            for p, _ in groups:
+                p._counter += n_vec
         else:
             pol = self.policy
             mode = 2 if (pol.deterministic_eval and not pol.is_within_training_step) else 1
