@@ -109,7 +109,8 @@ class OnPolicyTrainer:
             p.train_collector.reset(reset_buffer=reset_collector_buffers)
             if p.test_collector is not None:
                 p.test_collector.reset(reset_buffer=reset_collector_buffers)
-        self._best_score = self._best_reward = float("-inf")
+        # without test steps the reference reports 0.0 for the best score / reward (trainer.py:367-368; tests/golden/trainer.npz "no_test")
+        self._best_score = self._best_reward = float("-inf") if p.test_collector is not None else 0.0
         self._best_reward_std, self._best_epoch = 0.0, 0
         if p.test_collector is not None:  # initial test step fixes the "best" baseline (:460-468)
             self._test_step(force_update_best=True)
