@@ -219,12 +219,14 @@ int tsm_episode_stats(const double* ep_ret, const int64_t* ep_len, int64_t n, do
  * ========================================================================================= */
 #define TSM_MPE_SPREAD 0
 #define TSM_MPE_TAG 1
+#define TSM_MPE_ADVERSARY 2 /* simple_adversary_v3: 1 adversary + N good agents, N landmarks one of which is the goal; nothing
+                               collides; obs = [goal - p (good agents only), landmarks - p, others - p], the adversary zero-padded */
 typedef struct tsm_mpe {
-    int32_t scenario;      /* TSM_MPE_SPREAD / TSM_MPE_TAG */
+    int32_t scenario;      /* TSM_MPE_SPREAD / TSM_MPE_TAG / TSM_MPE_ADVERSARY */
     int32_t n_agents;      /* A (tag: adversaries first, then good agents) */
     int32_t n_landmarks;   /* L */
     int32_t n_adversaries; /* tag only */
-    int32_t obs_dim;       /* spread 6A; tag 4 + 2L + 2(A-1) + 2*n_good (good agents zero-padded) */
+    int32_t obs_dim;       /* spread 6A; tag 4 + 2L + 2(A-1) + 2*n_good (good agents zero-padded); adversary 2 + 2L + 2(A-1) */
     int32_t max_cycles;    /* truncation horizon (25) */
     int32_t pos_first;     /* 1: p += v*dt before the velocity update (pettingzoo 1.24) ; 0: after */
     float local_ratio;     /* spread: reward = global*(1-lr) + local*lr */

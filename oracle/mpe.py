@@ -29,7 +29,7 @@ DAMPING = 0.25
 CONTACT_FORCE = 1e2
 CONTACT_MARGIN = 1e-3
 
-SPREAD, TAG = 0, 1
+SPREAD, TAG, ADVERSARY = 0, 1, 2
 
 
 class OracleMPE:
@@ -59,6 +59,18 @@ class OracleMPE:
             n_good = num_good
             # adversary obs: 4 + 2L + 2(A-1) + 2*n_good ; good agent: 4 + 2L + 2(A-1) + 2*(n_good-1)
             self.obs_dim = 4 + 2 * L + 2 * (A - 1) + 2 * n_good
+        elif scenario == ADVERSARY:
+            # scenarios/simple_adversary.py: 1 adversary first, then N good agents; N landmarks, one of them the goal; nothing collides
+            A, L = num_adversaries + num_good, num_good
+            self.adversary = np.arange(A) < num_adversaries
+            self.size = np.array([0.15] * A + [0.08] * L)
+            self.collide = np.array([False] * (A + L))
+            self.accel = np.full(A, 5.0)
+            self.max_speed = np.full(A, np.inf)
+            self.local_ratio = None
+            self.lm_lo, self.lm_hi = -1.0, 1.0
+            self.obs_dim = 2 + 2 * L + 2 * (A - 1)
+            self.goal = np.zeros(n_envs, np.int64)
         else:
             raise ValueError(scenario)
         self.A, self.L = A, L
@@ -90,12 +102,25 @@ class OracleMPE:
                 out[:, e, 1] = lo32 + w32 * u[2 * j + 1]
         return out
 
+    def draw_goal(self, env_ids, episode) -> np.ndarray:
+        """simple_adversary reset_world: goal = np_random.choice(landmarks); here the Philox draw of the entity slot behind the
+        last landmark (same counter layout as draw_positions), floor(u * L)."""
+        env_ids = np.asarray(env_ids, dtype=np.uint64)
+        ent = self.A + self.L
+        r = philox.philox4x32(env_ids & 0xFFFFFFFF, env_ids >> np.uint64(32), np.asarray(episode, np.uint64) & 0xFFFFFFFF,
+                              np.uint32(ent >> 1), np.uint32(self.seed & 0xFFFFFFFF),
+                              np.uint32(((self.seed >> 32) & 0xFFFFFFFF) ^ philox.STREAM_RESET))
+        u = philox.u01(r[2] if ent & 1 else r[0])
+        return np.minimum((u * np.float32(self.L)).astype(np.int64), self.L - 1)
+
     def reset(self, env_ids=None, init_pos=None) -> np.ndarray:
         """reset_world (simple_spread.py / simple_tag.py): agents then landmarks, zero velocity.
         Returns obs (n, A, obs_dim) float32."""
         env_ids = np.arange(self.E) if env_ids is None else np.asarray(env_ids, dtype=np.int64)
         if init_pos is None:
             init_pos = self.draw_positions(env_ids, self.episode[env_ids])
+        if self.scenario == ADVERSARY:
+            self.goal[env_ids] = self.draw_goal(env_ids, self.episode[env_ids])
         self.pos[env_ids] = np.asarray(init_pos, dtype=np.float64)
         self.vel[env_ids] = 0.0
         self.steps[env_ids] = 0
@@ -173,6 +198,15 @@ class OracleMPE:
             return g[:, None] * (1 - self.local_ratio) + rew * self.local_ratio
         adv = np.nonzero(self.adversary)[0]
         good = np.nonzero(~self.adversary)[0]
+        if self.scenario == ADVERSARY:
+            # simple_adversary.reward, shaped: adversary_reward = -|p - goal|; agent_reward = sum_adv |p_adv - goal| - min_good |p_good - goal|
+            gp = self.pos[np.arange(self.E), A + self.goal]
+            dg = np.sqrt(np.sum(np.square(self.pos[:, :A] - gp[:, None]), axis=-1))  # (E, A)
+            adv_rew = dg[:, adv].sum(axis=1)
+            pos_rew = -dg[:, good].min(axis=1)
+            rew[:, adv] = -dg[:, adv]
+            rew[:, good] = (pos_rew + adv_rew)[:, None]
+            return rew
         # adversary_reward: +10 per (good, adversary) pair in collision, shared
         ar = np.zeros(self.E)
         for ag in good:
@@ -198,6 +232,17 @@ class OracleMPE:
         A, L = self.A, self.L
         n = pos.shape[0]
         obs = np.zeros((n, A, self.obs_dim))
+        if self.scenario == ADVERSARY:
+            # simple_adversary.observation: good [goal - p, landmarks - p, others - p]; adversary [landmarks - p, others - p] (zero-padded)
+            goal = self.goal[sl]
+            gp = pos[np.arange(n), A + goal]
+            for i in range(A):
+                parts = [] if self.adversary[i] else [gp - pos[:, i]]
+                parts += [pos[:, A + l] - pos[:, i] for l in range(L)]
+                parts += [pos[:, j] - pos[:, i] for j in range(A) if j != i]
+                row = np.concatenate(parts, axis=-1)
+                obs[:, i, : row.shape[1]] = row
+            return obs.astype(np.float32)
         for i in range(A):
             parts = [vel[:, i], pos[:, i]]
             parts += [pos[:, A + l] - pos[:, i] for l in range(L)]

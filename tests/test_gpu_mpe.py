@@ -18,7 +18,8 @@ from oracle.mpe import OracleMPE
 pytestmark = pytest.mark.gpu
 
 CASES = [("simple_spread_v3", 0, dict(n_agents=3)), ("simple_spread_v3", 0, dict(n_agents=10)),
-         ("simple_tag_v3", 1, dict()), ("simple_spread_v3", 0, dict(n_agents=5, pos_first=False))]
+         ("simple_tag_v3", 1, dict()), ("simple_spread_v3", 0, dict(n_agents=5, pos_first=False)),
+         ("simple_adversary_v3", 2, dict(num_good=2, num_adversaries=1)), ("simple_adversary_v3", 2, dict(num_good=4, num_adversaries=1))]
 
 
 def _mk(name, scen, kw, E, seed=0):

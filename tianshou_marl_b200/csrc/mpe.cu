@@ -1,4 +1,4 @@
-// mpe.cu -- K1: batched MPE simple_spread / simple_tag world step (sm_100a).
+// mpe.cu -- K1: batched MPE simple_spread / simple_tag / simple_adversary world step (sm_100a).
 //
 // Restates pettingzoo 1.24.2 mpe (core.World.step, simple_env._set_action /
 // _execute_world_step, scenarios/simple_spread.py, scenarios/simple_tag.py), which the
@@ -19,15 +19,15 @@ constexpr float DT = 0.1f, DAMPING = 0.25f, CONTACT_FORCE = 1e2f, CONTACT_MARGIN
 constexpr int THREADS = 256;
 
 __device__ __forceinline__ float agent_size(const tsm_mpe& e, int j) {
-    if (e.scenario == TSM_MPE_SPREAD) return 0.15f;
+    if (e.scenario != TSM_MPE_TAG) return 0.15f;  // simple_spread and simple_adversary: every agent 0.15
     return j < e.n_adversaries ? 0.075f : 0.05f;
 }
 __device__ __forceinline__ float agent_accel(const tsm_mpe& e, int j) {
-    if (e.scenario == TSM_MPE_SPREAD) return 5.0f;  // simple_env._set_action default sensitivity
+    if (e.scenario != TSM_MPE_TAG) return 5.0f;  // simple_env._set_action default sensitivity (accel None)
     return j < e.n_adversaries ? 3.0f : 4.0f;
 }
 __device__ __forceinline__ float agent_max_speed(const tsm_mpe& e, int j) {
-    if (e.scenario == TSM_MPE_SPREAD) return INFINITY;
+    if (e.scenario != TSM_MPE_TAG) return INFINITY;
     return j < e.n_adversaries ? 1.0f : 1.3f;
 }
 __device__ __forceinline__ float landmark_size(const tsm_mpe& e) { return e.scenario == TSM_MPE_SPREAD ? 0.05f : 0.2f; }
@@ -78,10 +78,21 @@ __device__ __forceinline__ float2 draw_entity(const tsm_mpe& e, int64_t env_id, 
     return make_float2(__fadd_rn(lo, __fmul_rn(w, u0)), __fadd_rn(lo, __fmul_rn(w, u1)));
 }
 
+// simple_adversary: the goal landmark of episode `episode` of env `env_id` (scenario.reset_world: np_random.choice(landmarks)).
+// Not stored: it is a pure function of (seed, env, episode) -- the Philox draw of the entity slot behind the last landmark.
+__device__ __forceinline__ int goal_index(const tsm_mpe& e, int64_t env_id, int64_t episode) {
+    const int ent = e.n_agents + e.n_landmarks;
+    const Philox4 r = philox4x32((uint32_t)env_id, (uint32_t)((uint64_t)env_id >> 32), (uint32_t)episode, (uint32_t)(ent >> 1),
+                                 (uint32_t)e.seed, (uint32_t)(e.seed >> 32) ^ STREAM_RESET);
+    const float u = u01((ent & 1) ? r.z : r.x);
+    const int g = (int)(u * (float)e.n_landmarks);
+    return g < e.n_landmarks ? g : e.n_landmarks - 1;
+}
+
 // scenario.observation for agent j (lane j); all lanes of the group must call (shuffles inside)
 template <int G>
 __device__ __forceinline__ void write_obs(const tsm_mpe& e, int j, bool valid, float2 p, float2 v, float2 lm,
-                                          float* __restrict__ dst0, float* __restrict__ dst1) {
+                                          float* __restrict__ dst0, float* __restrict__ dst1, int goal = 0) {
     const int A = e.n_agents, L = e.n_landmarks;
     float2* o0 = reinterpret_cast<float2*>(dst0);
     float2* o1 = reinterpret_cast<float2*>(dst1);
@@ -93,6 +104,23 @@ __device__ __forceinline__ void write_obs(const tsm_mpe& e, int j, bool valid, f
         }
         ++q;
     };
+    if (e.scenario == TSM_MPE_ADVERSARY) {
+        // simple_adversary.observation: good agents [goal - p, landmarks - p, others - p]; the adversary [landmarks - p, others - p]
+        // (no velocities, no own position); the adversary's 2 + 2L + 2(A-1) - 2 values are zero-padded to the common obs_dim
+        const float2 pg = shfl2<G>(lm, goal);
+        if (j >= e.n_adversaries) put(make_float2(pg.x - p.x, pg.y - p.y));
+        for (int l = 0; l < L; ++l) {
+            const float2 pl = shfl2<G>(lm, l);
+            put(make_float2(pl.x - p.x, pl.y - p.y));
+        }
+        for (int k = 0; k < A; ++k) {
+            const float2 pk = shfl2<G>(p, k);
+            if (k != j) put(make_float2(pk.x - p.x, pk.y - p.y));
+        }
+        const int O2 = e.obs_dim / 2;
+        while (q < O2) put(make_float2(0.f, 0.f));
+        return;
+    }
     put(v);
     put(p);
     for (int l = 0; l < L; ++l) {
@@ -137,8 +165,9 @@ __global__ void __launch_bounds__(THREADS) reset_kernel(tsm_mpe e, const int64_t
             reinterpret_cast<float2*>(e.lm)[env * L + j] = lm;
         }
     }
+    const int goal = (live && e.scenario == TSM_MPE_ADVERSARY) ? goal_index(e, env, e.episode[env]) : 0;
     write_obs<G>(e, j, live && j < A && obs_out != nullptr, p, v, lm,
-                 obs_out ? obs_out + (gid * A + j) * e.obs_dim : nullptr, nullptr);
+                 obs_out ? obs_out + (gid * A + j) * e.obs_dim : nullptr, nullptr, goal);
     if (live && j == 0) {
         e.steps[env] = 0;
         e.episode[env] += 1;
@@ -206,8 +235,9 @@ __global__ void __launch_bounds__(THREADS) step_kernel(tsm_mpe e, const int32_t*
     const float sens = agent_accel(e, j);
     float fx = (a == 1 ? -1.f : (a == 2 ? 1.f : 0.f)) * sens;
     float fy = (a == 3 ? -1.f : (a == 4 ? 1.f : 0.f)) * sens;
-    // World.apply_environment_force: partners in ascending entity order (agents, then landmarks)
-    for (int k = 0; k < A; ++k) {
+    // World.apply_environment_force: partners in ascending entity order (agents, then landmarks); simple_adversary has no
+    // collidable entity at all (collide = False everywhere)
+    for (int k = 0; k < (e.scenario == TSM_MPE_ADVERSARY ? 0 : A); ++k) {
         const float2 pk = shfl2<G>(p, k);
         if (k != j) {
             const float2 f = collision_force(p, pk, my_size + agent_size(e, k));
@@ -243,6 +273,7 @@ __global__ void __launch_bounds__(THREADS) step_kernel(tsm_mpe e, const int32_t*
 
     // rewards on the post-step state
     float r = 0.f;
+    int goal = 0;  // simple_adversary: goal landmark of the running episode
     if (e.scenario == TSM_MPE_SPREAD) {
         float local = 0.f;
         for (int k = 0; k < A; ++k) {
@@ -258,6 +289,18 @@ __global__ void __launch_bounds__(THREADS) step_kernel(tsm_mpe e, const int32_t*
         float g = 0.f;
         for (int l = 0; l < L; ++l) g -= shfl1<G>(mind, l);
         r = __fadd_rn(__fmul_rn(g, 1.f - e.local_ratio), __fmul_rn(local, e.local_ratio));
+    } else if (e.scenario == TSM_MPE_ADVERSARY) {
+        // simple_adversary.reward (shaped): adversary -|p - goal|; good agents sum_adv |p_adv - goal| - min_good |p_good - goal|
+        goal = live ? goal_index(e, env, e.episode[env] - 1) : 0;
+        const float2 pg = shfl2<G>(lm, goal);
+        const float dg = dist2d(p, pg);
+        float adv_rew = 0.f, mind = INFINITY;
+        for (int k = 0; k < A; ++k) {
+            const float dk = shfl1<G>(dg, k);
+            if (k < e.n_adversaries) adv_rew += dk;
+            else mind = fminf(mind, dk);
+        }
+        r = j < e.n_adversaries ? -dg : __fadd_rn(-mind, adv_rew);
     } else {
         const bool adv = j < e.n_adversaries;
         // number of adversaries in collision with me (meaningful on good-agent lanes)
@@ -296,7 +339,7 @@ __global__ void __launch_bounds__(THREADS) step_kernel(tsm_mpe e, const int32_t*
     // observation of the post-step state goes to obs_next (terminal obs for done envs) and, when
     // the env keeps running, also straight to the carry slot the next policy forward reads
     write_obs<G>(e, j, is_agent, p, v, lm, obs_next ? obs_next + row * e.obs_dim : nullptr,
-                 (obs_carry && !do_reset) ? obs_carry + row * e.obs_dim : nullptr);
+                 (obs_carry && !do_reset) ? obs_carry + row * e.obs_dim : nullptr, goal);
     if (do_reset) {
         const int64_t ep = e.episode[env];
         v = make_float2(0.f, 0.f);
@@ -308,7 +351,8 @@ __global__ void __launch_bounds__(THREADS) step_kernel(tsm_mpe e, const int32_t*
     }
     // the whole group takes the same branch (tr is per env); shuffles inside use the group mask
     if (do_reset)
-        write_obs<G>(e, j, is_agent, p, v, lm, obs_carry ? obs_carry + row * e.obs_dim : nullptr, nullptr);
+        write_obs<G>(e, j, is_agent, p, v, lm, obs_carry ? obs_carry + row * e.obs_dim : nullptr, nullptr,
+                     e.scenario == TSM_MPE_ADVERSARY ? goal_index(e, env, e.episode[env]) : 0);
     if (is_agent) {
         reinterpret_cast<float2*>(e.pos)[row] = p;
         reinterpret_cast<float2*>(e.vel)[row] = v;
@@ -398,13 +442,16 @@ using namespace tsm::mpe;
 
 static int check_env(const tsm_mpe* e, const char* fn) {
     if (!e) return fail(TSM_ERR_INVALID, "%s: env is NULL", fn);
-    if (e->scenario != TSM_MPE_SPREAD && e->scenario != TSM_MPE_TAG) return fail(TSM_ERR_INVALID, "%s: unknown scenario", fn);
+    if (e->scenario != TSM_MPE_SPREAD && e->scenario != TSM_MPE_TAG && e->scenario != TSM_MPE_ADVERSARY)
+        return fail(TSM_ERR_INVALID, "%s: unknown scenario", fn);
     if (e->n_envs <= 0 || e->n_agents <= 0 || e->n_agents > 32 || e->n_landmarks < 0 || e->n_landmarks > 32)
         return fail(TSM_ERR_INVALID, "%s: need n_envs > 0, 1 <= n_agents <= 32, 0 <= n_landmarks <= 32", fn);
-    if (e->scenario == TSM_MPE_TAG && (e->n_adversaries < 0 || e->n_adversaries > e->n_agents))
+    if (e->scenario != TSM_MPE_SPREAD && (e->n_adversaries < 0 || e->n_adversaries > e->n_agents))
         return fail(TSM_ERR_INVALID, "%s: bad n_adversaries", fn);
-    const int want = e->scenario == TSM_MPE_SPREAD ? 6 * e->n_agents
-                                                   : 4 + 2 * e->n_landmarks + 2 * (e->n_agents - 1) + 2 * (e->n_agents - e->n_adversaries);
+    if (e->scenario == TSM_MPE_ADVERSARY && e->n_landmarks < 1) return fail(TSM_ERR_INVALID, "%s: simple_adversary needs a landmark", fn);
+    const int want = e->scenario == TSM_MPE_SPREAD      ? 6 * e->n_agents
+                     : e->scenario == TSM_MPE_ADVERSARY ? 2 + 2 * e->n_landmarks + 2 * (e->n_agents - 1)
+                                                        : 4 + 2 * e->n_landmarks + 2 * (e->n_agents - 1) + 2 * (e->n_agents - e->n_adversaries);
     if (e->obs_dim != want) return fail(TSM_ERR_INVALID, "%s: obs_dim does not match the scenario (want %lld)", fn, want);
     if (!e->pos || !e->vel || !e->steps || !e->episode || (e->n_landmarks > 0 && !e->lm))
         return fail(TSM_ERR_INVALID, "%s: state arrays must not be NULL", fn);

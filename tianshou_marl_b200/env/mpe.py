@@ -18,8 +18,9 @@ import torch
 
 from .. import _lib
 
-SPREAD, TAG = 0, 1
-_SCENARIOS = {"simple_spread": SPREAD, "simple_spread_v3": SPREAD, "simple_tag": TAG, "simple_tag_v3": TAG, 0: SPREAD, 1: TAG}
+SPREAD, TAG, ADVERSARY = 0, 1, 2
+_SCENARIOS = {"simple_spread": SPREAD, "simple_spread_v3": SPREAD, "simple_tag": TAG, "simple_tag_v3": TAG, "simple_adversary": ADVERSARY,
+              "simple_adversary_v3": ADVERSARY, 0: SPREAD, 1: TAG, 2: ADVERSARY}
 
 
 class Discrete:
@@ -84,6 +85,12 @@ class MPEVectorEnv:
             A, L, n_adv = n_agents, n_agents, 0
             O = 6 * A
             self.agents = [f"agent_{i}" for i in range(A)]
+        elif self.scenario == ADVERSARY:
+            # simple_adversary_v3(N = 2): one adversary, N good agents, N landmarks (one is the goal)
+            n_good = n_agents - 1 if n_agents >= 2 and num_good == 1 and num_adversaries == 3 else num_good  # MPEVectorEnv("simple_adversary_v3", n_agents=3)
+            A, L, n_adv = 1 + n_good, n_good, 1
+            O = 2 + 2 * L + 2 * (A - 1)
+            self.agents = ["adversary_0"] + [f"agent_{i}" for i in range(n_good)]
         else:
             A, L, n_adv = num_adversaries + num_good, num_obstacles, num_adversaries
             O = 4 + 2 * L + 2 * (A - 1) + 2 * num_good
