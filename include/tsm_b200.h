@@ -602,6 +602,12 @@ typedef struct tsm_tcw_epoch {
 } tsm_tcw_epoch;
 int tsm_tcw_ppo_epoch(const tsm_tcw_epoch* e, const tsm_ppo_cfg* cfg, tsm_stream_t stream);
 
+/* Policy.map_action for Box action spaces (algorithm_base.py:255-288): bound_method 0 none / 1 clip to [-1, 1] / 2 tanh, then (scaling)
+ * low + (high - low) * (a + 1) / 2 per action dimension; act, out: [n][dim]; *out_of_range (optional) is set to 1 where the
+ * reference's range assertion would fire. */
+int tsm_map_action(const float* act, int64_t n, int dim, int bound_method, int scaling, const float* low, const float* high,
+                   float* out, int* out_of_range, tsm_stream_t stream);
+
 /* tsm_collect_lockstep for GROUPED policies (FlexibleMultiAgentPolicyManager.forward inside the rollout loop,
  * multiagent/flexible_policy.py:189-231 -> marl.py:108-185): group g = (nets[g], rows[g][0..n_rows[g]) device row list, policy
  * seed seeds[g], first sampling counter counters0[g]); one fused forward launch per group and vector step (row gather, act /

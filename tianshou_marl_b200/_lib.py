@@ -148,6 +148,7 @@ _SIGS = {
     "tsm_mpe_step": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
     "tsm_random_actions": (c_i32, [c_vp, c_i64, c_i32, C.c_uint64, C.c_uint64, c_vp]),
     "tsm_collect_lockstep": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, C.c_uint64, C.c_uint64, c_i64, c_i32, c_vp, c_vp, c_vp, c_vp]),
+    "tsm_map_action": (c_i32, [c_vp, c_i64, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "tsm_collect_lockstep_groups": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_i64, c_i32, c_i64, c_vp, c_vp, c_vp, c_vp]),
     "tsm_adam_step_dist": (c_i32, [c_vp, c_vp, C.c_uint32, c_f32, c_f32, c_f32, c_f32, c_f32, c_vp, c_vp]),
     "tsm_ppo_epoch_dist": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_f32, c_f32, c_f32, c_f32, c_f32, c_vp, c_vp, C.c_uint32, c_vp]),

@@ -1,3 +1,4 @@
+from .actions import BoxActionMapper
 from .ctde import CentralizedCritic, CTDEPolicy, DecentralizedActor, GlobalStateConstructor
 from .mappo import MAPPO
 from .multiagent import FlexibleMultiAgentPolicyManager
@@ -7,4 +8,4 @@ from .returns import compute_episodic_return, episode_mc_return_to_go, gae_flat,
 
 __all__ = ["compute_episodic_return", "episode_mc_return_to_go", "gae_flat", "gae_time_major", "PPO", "A2C", "Reinforce", "AdamOptimizerFactory",
            "DiscreteActorPolicy", "FlexibleMultiAgentPolicyManager", "CTDEPolicy", "GlobalStateConstructor",
-           "DecentralizedActor", "CentralizedCritic", "SimultaneousTrainer", "MAPPO"]
+           "DecentralizedActor", "CentralizedCritic", "SimultaneousTrainer", "MAPPO", "BoxActionMapper"]

@@ -9,6 +9,7 @@
 // touches shared memory.  State is SoA per field with float2 elements, indexed by row
 // (env*A + agent), so consecutive lanes read consecutive 8-byte words: every state load and
 // store of a warp is one contiguous segment.
+#include <cstdlib>
 #include "common.cuh"
 #include "philox.cuh"
 
@@ -207,7 +208,11 @@ __device__ __forceinline__ void atomic_max_f64(double* a, double v) {
     }
 }
 
-template <int G, bool TAIL>
+// STAGE: observations are laid down in shared memory by their owner lanes and copied out by the whole block as one
+// contiguous range (the worlds of a block are consecutive, so their rows are too).  Direct per-lane writes put consecutive
+// lanes obs_dim * 4 bytes apart: every 8-byte store is its own 32-byte sector (N = 10: 60 such stores per lane and
+// destination, 102 us per 163 840 rows before this change).
+template <int G, bool TAIL, bool STAGE>
 __global__ void __launch_bounds__(THREADS) step_kernel(tsm_mpe e, const int32_t* __restrict__ act,
                                                       float* __restrict__ obs_next, float* __restrict__ rew,
                                                       uint8_t* __restrict__ term, uint8_t* __restrict__ trunc, int autoreset,
@@ -338,8 +343,27 @@ __global__ void __launch_bounds__(THREADS) step_kernel(tsm_mpe e, const int32_t*
     const bool do_reset = autoreset && tr;
     // observation of the post-step state goes to obs_next (terminal obs for done envs) and, when
     // the env keeps running, also straight to the carry slot the next policy forward reads
-    write_obs<G>(e, j, is_agent, p, v, lm, obs_next ? obs_next + row * e.obs_dim : nullptr,
-                 (obs_carry && !do_reset) ? obs_carry + row * e.obs_dim : nullptr, goal);
+    extern __shared__ float2 s_obs[];                 // STAGE: [worlds of the block][A * obs_dim / 2]
+    __shared__ unsigned char s_reset[THREADS / 4];    // STAGE: the world's carry observation comes from the reset
+    constexpr int W = THREADS / G;
+    const int wl = (int)(threadIdx.x / G), row_f2 = e.obs_dim / 2, world_f2 = A * row_f2;
+    const int64_t first_local = (int64_t)blockIdx.x * W;
+    const int total_f2 = (int)min((int64_t)W, n_sub - first_local) * world_f2;  // (<= 0 for a block past the range)
+    float2* blk_next = obs_next ? reinterpret_cast<float2*>(obs_next) + (env0 + first_local) * world_f2 : nullptr;
+    float2* blk_carry = obs_carry ? reinterpret_cast<float2*>(obs_carry) + (env0 + first_local) * world_f2 : nullptr;
+    if constexpr (STAGE) {
+        write_obs<G>(e, j, is_agent, p, v, lm, reinterpret_cast<float*>(s_obs + wl * world_f2 + j * row_f2), nullptr, goal);
+        if (j == 0) s_reset[wl] = do_reset ? 1 : 0;
+        __syncthreads();
+        for (int i = threadIdx.x; i < total_f2; i += THREADS) {
+            const float2 val = s_obs[i];
+            if (blk_next) blk_next[i] = val;
+            if (blk_carry && !s_reset[i / world_f2]) blk_carry[i] = val;
+        }
+    } else {
+        write_obs<G>(e, j, is_agent, p, v, lm, obs_next ? obs_next + row * e.obs_dim : nullptr,
+                     (obs_carry && !do_reset) ? obs_carry + row * e.obs_dim : nullptr, goal);
+    }
     if (do_reset) {
         const int64_t ep = e.episode[env];
         v = make_float2(0.f, 0.f);
@@ -350,9 +374,20 @@ __global__ void __launch_bounds__(THREADS) step_kernel(tsm_mpe e, const int32_t*
         }
     }
     // the whole group takes the same branch (tr is per env); shuffles inside use the group mask
-    if (do_reset)
+    if constexpr (STAGE) {
+        if (__syncthreads_or(do_reset ? 1 : 0)) {  // (also orders the copy loop above before the staging area is reused)
+            if (do_reset)
+                write_obs<G>(e, j, is_agent, p, v, lm, reinterpret_cast<float*>(s_obs + wl * world_f2 + j * row_f2), nullptr,
+                             e.scenario == TSM_MPE_ADVERSARY ? goal_index(e, env, e.episode[env]) : 0);
+            __syncthreads();
+            if (blk_carry)
+                for (int i = threadIdx.x; i < total_f2; i += THREADS)
+                    if (s_reset[i / world_f2]) blk_carry[i] = s_obs[i];
+        }
+    } else if (do_reset) {
         write_obs<G>(e, j, is_agent, p, v, lm, obs_carry ? obs_carry + row * e.obs_dim : nullptr, nullptr,
                      e.scenario == TSM_MPE_ADVERSARY ? goal_index(e, env, e.episode[env]) : 0);
+    }
     if (is_agent) {
         reinterpret_cast<float2*>(e.pos)[row] = p;
         reinterpret_cast<float2*>(e.vel)[row] = v;
@@ -490,12 +525,20 @@ static int launch_step(const tsm_mpe* e, const int32_t* act, float* obs_next, fl
                        int autoreset, float* obs_carry, const RolloutTail& t, int64_t env0, int64_t n_sub, cudaStream_t s) {
     const int G = group_width(e);
     const unsigned grid = (unsigned)ceil_div(n_sub * G, THREADS);
+    // staging area: the observations of the block's worlds; direct per-lane writes when it would not fit the default 48 KB
+    const size_t stage = (size_t)(THREADS / G) * e->n_agents * e->obs_dim * sizeof(float);
+    static const bool no_stage = getenv("TSM_MPE_NO_STAGE") != nullptr;
+    const bool st = stage <= 48 * 1024 - 2048 && (e->obs_dim % 2) == 0 && !no_stage;
+#define TSM_STEP(GG)                                                                                                                          \
+    if (st) step_kernel<GG, TAIL, true><<<grid, THREADS, stage, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t, env0, n_sub); \
+    else step_kernel<GG, TAIL, false><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t, env0, n_sub);
     switch (G) {
-        case 4: step_kernel<4, TAIL><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t, env0, n_sub); break;
-        case 8: step_kernel<8, TAIL><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t, env0, n_sub); break;
-        case 16: step_kernel<16, TAIL><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t, env0, n_sub); break;
-        default: step_kernel<32, TAIL><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t, env0, n_sub); break;
+        case 4: TSM_STEP(4) break;
+        case 8: TSM_STEP(8) break;
+        case 16: TSM_STEP(16) break;
+        default: TSM_STEP(32) break;
     }
+#undef TSM_STEP
     TSM_LAUNCH_CHECK();
     return TSM_OK;
 }
