@@ -300,7 +300,7 @@ typedef struct tsm_net {
     int32_t probs_param; /* 1: the actor is DiscreteActor(softmax_output=True) feeding Categorical(probs=...) (utils/net/discrete.py:41,85-86):
                             log-probabilities / entropy are log(clamp(softmax(logits), eps, 1 - eps)) as torch computes them */
 } tsm_net;
-#define TSM_TC_IMAGE_BYTES 119552 /* 16 896 image + tsm_ppo_epoch's three more gradient-sized buffers of 7 168 floats + 256 bytes of barrier words + a 16 KB index table */
+#define TSM_TC_IMAGE_BYTES 123648 /* 16 896 image + tsm_ppo_epoch's three more gradient-sized buffers of 7 168 floats + 256 bytes of barrier words + a 20 KB index table */
 
 int64_t tsm_net_param_count(int in_dim, int hidden, int out_dim);
 

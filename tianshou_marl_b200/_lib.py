@@ -42,7 +42,7 @@ class TsmMpe(C.Structure):
     ]
 
 
-TC_IMAGE_BYTES = 119552  # TSM_TC_IMAGE_BYTES
+TC_IMAGE_BYTES = 123648  # TSM_TC_IMAGE_BYTES
 PPO_RECORD_BYTES = 96  # TSM_PPO_RECORD_BYTES
 
 

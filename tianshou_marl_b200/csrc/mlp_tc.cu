@@ -285,16 +285,22 @@ int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, cons
     if (!batch->records) return fail(TSM_ERR_INVALID, "%s: engine 1 needs batch.records (tsm_ppo_pack_records)", __func__);
     if (reinterpret_cast<uintptr_t>(net->grads) & 15) return fail(TSM_ERR_INVALID, "%s: grads must be 16-byte aligned", __func__);
     if (adam.n > (int64_t)mlptc::EP_G_STRIDE) return 1;
-    static int coop = -1, occ = 0;
+    static int coop = -1, occ = 0, hv = mlptc::EP_HV;
     const size_t smem = mlptc::SM_EP_TOTAL;
     if (coop < 0) {
         int dev = 0;
         TSM_CUDA(cudaGetDevice(&dev));
         TSM_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
-        TSM_CUDA(cudaFuncSetAttribute(mlptc::tc_ppo_epoch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        TSM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mlptc::tc_ppo_epoch_kernel, mlptc::EP_THREADS, smem));
+        if (const char* h = getenv("TSM_TC_EPOCH_HALVES")) hv = atoi(h) == 1 ? 1 : 2;  // 1: one thread per tile row (round-1 shape)
+        int occ1 = 0, occ2 = 0;
+        TSM_CUDA(cudaFuncSetAttribute(mlptc::tc_ppo_epoch_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        TSM_CUDA(cudaFuncSetAttribute(mlptc::tc_ppo_epoch_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        TSM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, mlptc::tc_ppo_epoch_kernel<1>, mlptc::EP_THREADS, smem));
+        TSM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, mlptc::tc_ppo_epoch_kernel<2>, 2 * mlptc::EP_THREADS, smem));
+        occ = hv == 1 ? occ1 : occ2;
         if (occ > 1) occ = 1;  // one CTA owns the SM's 512 TMEM columns
     }
+    void* const kernel = hv == 1 ? reinterpret_cast<void*>(mlptc::tc_ppo_epoch_kernel<1>) : reinterpret_cast<void*>(mlptc::tc_ppo_epoch_kernel<2>);
     if (!coop || occ < 1) return 1;
     mlptc::TcEpochArgs e{};
     mlptc::TcPpoArgs& a = e.p;
@@ -309,13 +315,13 @@ int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, cons
     a.gscale = 1.f; a.inv_gscale = 1.f; a.loss_sums = nullptr;
     a.debug = getenv("TSM_TC_DEBUG") ? atoi(getenv("TSM_TC_DEBUG")) : 0;
     // workspace behind the image (TSM_TC_IMAGE_BYTES): two more gradient buffers
-    static_assert(TSM_TC_IMAGE_BYTES >= opt::IMG_BYTES + 2 * mlptc::EP_G_STRIDE * 4 + 256 + mlptc::EP_THREADS * (mlptc::EP_OPT + 1) * 8 + mlptc::EP_G_STRIDE * 4,
+    static_assert(TSM_TC_IMAGE_BYTES >= opt::IMG_BYTES + 2 * mlptc::EP_G_STRIDE * 4 + 256 + mlptc::EP_Q_WORDS * 8 + mlptc::EP_G_STRIDE * 4,
                   "TSM_TC_IMAGE_BYTES too small for the epoch kernel's workspace");
     e.grads1 = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(net->tc_image) + opt::IMG_BYTES);
     e.grads2 = e.grads1 + mlptc::EP_G_STRIDE;
     e.sync_words = reinterpret_cast<uint32_t*>(e.grads2 + mlptc::EP_G_STRIDE);
     e.q_table = reinterpret_cast<uint2*>(e.sync_words + 64);
-    e.g_total = reinterpret_cast<float*>(e.q_table + mlptc::EP_THREADS * (mlptc::EP_OPT + 1));
+    e.g_total = reinterpret_cast<float*>(e.q_table + mlptc::EP_Q_WORDS);
     e.n_mb = n_mb; e.mb_size = mb_size; e.total = total; e.mb_stats = mb_stats; e.loss_sums = loss_sums; e.adam = adam;
     const int64_t tiles = ceil_div(n_mb > 1 ? mb_size : total, mlptc::TC_ROWS);
     const unsigned grid = (unsigned)std::min<int64_t>(ceil_div(tiles, (int64_t)mlptc::TC_GROUPS), (int64_t)sm_count() * occ);
@@ -323,8 +329,7 @@ int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, cons
     rc = record_map(batch->records, batch->size * batch->n_rows, &rec_map, __func__);
     if (rc) return rc;
     void* args[] = {&e, &rec_map};
-    const cudaError_t err = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(mlptc::tc_ppo_epoch_kernel), dim3(grid),
-                                                        dim3(mlptc::EP_THREADS), args, smem, s);
+    const cudaError_t err = cudaLaunchCooperativeKernel(kernel, dim3(grid), dim3(hv * mlptc::EP_THREADS), args, smem, s);
     if (err == cudaErrorCooperativeLaunchTooLarge) {
         cudaGetLastError();
         return 1;
@@ -342,8 +347,8 @@ int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, cons
         }
         {
             cudaFuncAttributes fa;
-            cudaFuncGetAttributes(&fa, mlptc::tc_ppo_epoch_kernel);
-            printf("grid %u x %d threads, occ %d, smem %zu, regs %d\n", grid, mlptc::EP_THREADS, occ, smem, fa.numRegs);
+            cudaFuncGetAttributes(&fa, kernel);
+            printf("grid %u x %d threads, occ %d, smem %zu, regs %d\n", grid, hv * mlptc::EP_THREADS, occ, smem, fa.numRegs);
         }
         for (int row = 0; row < 3; ++row)
             printf("tile row %d: store_rec %lld prefetch-issue %lld to-forward %lld\n", row, h[row][24] - h[row][0], h[row][25] - h[row][24],

@@ -79,10 +79,15 @@ __device__ __forceinline__ int tc_grp() { return (int)(threadIdx.x / TC_THREADS)
 // broadcast, so the branch is warp-uniform for the compiler, and TcSetup::tmem / sbase are broadcast values too: the
 // descriptors are then built in uniform registers.  (With `if (tid == 0)` every operand went through R2UR inside an
 // elect loop: ~15 dependent instructions = 85 cycles per MMA, 3.9k of a tile's 10.3k cycles.)
-__device__ __forceinline__ int tc_warp_u() { return __shfl_sync(0xffffffffu, (int)((threadIdx.x >> 5) & (TC_THREADS / 32 - 1)), 0); }
+// HV ("halves"): threads per tile row.  1 everywhere except the persistent epoch kernel, which runs a group as 2 x 128
+// threads: thread t of a group works on row t & 127 and on half (t >> 7) of that row's columns (warps 0-3 and 4-7 of a
+// group see the same TMEM lane quarters), so every CUDA-core stage between two MMAs is half as long.
+template <int HV = 1>
+__device__ __forceinline__ int tc_warp_u() { return __shfl_sync(0xffffffffu, (int)((threadIdx.x >> 5) & (HV * TC_THREADS / 32 - 1)), 0); }
 __device__ __forceinline__ bool tc_issuer(bool w0) { return w0 && tc::elect_one(); }  // w0 = TcSetup::w0 (warp-uniform, computed once)
+template <int HV = 1>
 __device__ __forceinline__ void tc_group_sync() {
-    asm volatile("bar.sync %0, %1;" ::"r"(1 + tc_grp()), "n"(TC_THREADS) : "memory");
+    asm volatile("bar.sync %0, %1;" ::"r"(1 + (int)(threadIdx.x / (HV * TC_THREADS))), "n"(HV * TC_THREADS) : "memory");
 }
 
 __device__ __forceinline__ uint32_t h2_bits(__half2 h) { return *reinterpret_cast<const uint32_t*>(&h); }
@@ -128,9 +133,11 @@ __device__ __forceinline__ void tc_load_row(const float* __restrict__ x, int64_t
 }
 
 // relu(SCR accumulator, 64 cols of this thread's lane) -> fp16 image at smem + dst
-__device__ __forceinline__ void tc_epilogue_relu(unsigned char* smem, uint32_t tmem_lane_base, int dst) {
+template <int HV = 1>
+__device__ __forceinline__ void tc_epilogue_relu(unsigned char* smem, uint32_t tmem_lane_base, int dst, int half = 0) {
 #pragma unroll
-    for (int q = 0; q < 2; ++q) {
+    for (int q0 = 0; q0 < 2 / HV; ++q0) {
+        const int q = HV == 1 ? q0 : half;
         float v[32];
         tc::tmem_ld32(tmem_lane_base + TM_SCR + 32 * q, v);
 #pragma unroll
@@ -146,10 +153,12 @@ __device__ __forceinline__ void tc_epilogue_relu(unsigned char* smem, uint32_t t
 }
 
 // SCR accumulator masked by (activation image at `img` > 0) -> fp16 image at `dst`
-__device__ __forceinline__ void tc_epilogue_mask(unsigned char* smem, uint32_t tmem_lane_base, int img, int dst) {
+template <int HV = 1>
+__device__ __forceinline__ void tc_epilogue_mask(unsigned char* smem, uint32_t tmem_lane_base, int img, int dst, int half = 0) {
     const __half2 zero = __float2half2_rn(0.f);
 #pragma unroll
-    for (int q = 0; q < 2; ++q) {
+    for (int q0 = 0; q0 < 2 / HV; ++q0) {
+        const int q = HV == 1 ? q0 : half;
         float v[32];
         tc::tmem_ld32(tmem_lane_base + TM_SCR + 32 * q, v);
 #pragma unroll
@@ -188,10 +197,11 @@ __device__ __forceinline__ uint64_t desc_w_mn(uint32_t sb4, int off, int n_out, 
 }
 
 // publish generic-proxy smem writes + TMEM reads to the MMA-issuing thread
+template <int HV = 1>
 __device__ __forceinline__ void tc_sync_for_mma() {
     tc::fence_async_smem();
     tc::fence_before_sync();
-    tc_group_sync();
+    tc_group_sync<HV>();
     tc::fence_after_sync();
 }
 
@@ -226,13 +236,14 @@ struct TcSetup {
 
 // part A: nothing here depends on the parameters (runs ahead of pdl_wait()).  `smem` is the group's own map; TMEM is
 // allocated once per CTA by its first warp (tmem_cols covers every group) into group 0's slot.
+template <int HV = 1>
 __device__ __forceinline__ void tc_setup_begin(unsigned char* smem, uint32_t tmem_cols) {
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem + SM_BAR);
     uint32_t* tmem_s = reinterpret_cast<uint32_t*>(smem + SM_BAR + 16);
     for (int i = tc_tid(); i < 2 * CHUNK_B / 16; i += TC_THREADS)  // G image (chunk 1 stays zero forever)
         *reinterpret_cast<uint4*>(smem + SM_G + i * 16) = make_uint4(0, 0, 0, 0);
     if ((threadIdx.x >> 5) == 0) tc::tmem_alloc(tmem_s, tmem_cols);
-    if (tc_tid() == 0) {
+    if ((threadIdx.x & (HV * TC_THREADS - 1)) == 0) {
         tc::mbar_init(bar, 1);
         tc::mbar_init(bar + 1, 1);
         tc::mbar_init(bar + 3, 1);
@@ -261,19 +272,20 @@ __device__ __forceinline__ void tc_load_image(unsigned char* smem, const unsigne
 // part B: weight image (straight 16-byte copies; the image is rebuilt by the optimizer step, not here), then publish.
 // tmem_slot: where the CTA's TMEM base was written (the group's own map for one-group kernels); this group owns
 // TM_COLS_BWD columns from base + tmem_col0.
+template <int HV = 1>
 __device__ __forceinline__ TcSetup tc_setup_finish(unsigned char* smem, const unsigned char* image, const uint32_t* tmem_slot = nullptr,
                                                    uint32_t tmem_col0 = 0) {
     TcSetup s;
     s.bar = reinterpret_cast<uint64_t*>(smem + SM_BAR);
     if (!tmem_slot) tmem_slot = reinterpret_cast<const uint32_t*>(smem + SM_BAR + 16);
     const int warp = tc_tid() >> 5;
-    tc_load_image(smem, image);
-    tc_sync_for_mma();
+    tc_load_image(smem, image);  // (HV = 2: both halves store the same values)
+    tc_sync_for_mma<HV>();
     s.tmem = __shfl_sync(0xffffffffu, *tmem_slot + tmem_col0, 0);
     s.lane_base = s.tmem + ((uint32_t)(warp * 32) << 16);
     s.sbase = __shfl_sync(0xffffffffu, tc::smem_u32(smem) >> 4, 0);  // descriptor units
     s.phase = 0;
-    s.w0 = tc_warp_u() == 0;
+    s.w0 = tc_warp_u<HV>() == 0;
     return s;
 }
 
@@ -284,11 +296,16 @@ __device__ __forceinline__ void tc_wait(TcSetup& s) {
 }
 
 // [X|1] -> H1 -> H2 -> OUT for the tile in the X image at xoff; leaves OUT in TMEM (waited)
-__device__ __forceinline__ void tc_forward_tile(unsigned char* smem, TcSetup& s, int xoff, int trow = -1) {
+struct TcNoHook { __device__ __forceinline__ void operator()() const {} };
+// after_sync: run by every thread right after the first group barrier (the X image is complete and every thread is past
+// its reads of the record staging area: the epoch kernel issues the next tile's record gather there)
+template <int HV = 1, typename Hook = TcNoHook>
+__device__ __forceinline__ void tc_forward_tile(unsigned char* smem, TcSetup& s, int xoff, int trow = -1, int half = 0, Hook after_sync = Hook()) {
     constexpr uint32_t ID64 = tc::make_idesc_f16(128, 64, 0, 0, 0, 0);
     constexpr uint32_t ID16 = tc::make_idesc_f16(128, 16, 0, 0, 0, 0);
     TRACE(trow, 1);
-    tc_sync_for_mma();
+    tc_sync_for_mma<HV>();
+    after_sync();
     TRACE(trow, 2);
     if (tc_issuer(s.w0)) {
 #pragma unroll
@@ -299,9 +316,9 @@ __device__ __forceinline__ void tc_forward_tile(unsigned char* smem, TcSetup& s,
     TRACE(trow, 3);
     tc_wait(s);
     TRACE(trow, 4);
-    tc_epilogue_relu(smem, s.lane_base, SM_H1);
+    tc_epilogue_relu<HV>(smem, s.lane_base, SM_H1, half);
     TRACE(trow, 5);
-    tc_sync_for_mma();
+    tc_sync_for_mma<HV>();
     TRACE(trow, 6);
     if (tc_issuer(s.w0)) {
 #pragma unroll
@@ -313,9 +330,9 @@ __device__ __forceinline__ void tc_forward_tile(unsigned char* smem, TcSetup& s,
     TRACE(trow, 7);
     tc_wait(s);
     TRACE(trow, 8);
-    tc_epilogue_relu(smem, s.lane_base, SM_H2);
+    tc_epilogue_relu<HV>(smem, s.lane_base, SM_H2, half);
     TRACE(trow, 9);
-    tc_sync_for_mma();
+    tc_sync_for_mma<HV>();
     TRACE(trow, 10);
     if (tc_issuer(s.w0)) {
 #pragma unroll
@@ -472,22 +489,27 @@ __device__ __forceinline__ void tc_gather_issue(unsigned char* smem, const CUten
 
 // take: wait for the tile's records, move this thread's row into the X image at xoff (fp16 chunks, as packed) and its scalars
 // into registers.  Afterwards the thread's staging row is free for the next issue (it is only ever touched by this thread).
-__device__ __forceinline__ void tc_gather_take(unsigned char* smem, int xoff, bool valid, uint32_t& rphase, RowScalars& d) {
+// HV = 2: half h moves chunks 2h, 2h + 1 of the row; only half 0 reads the scalars.  The staging row is then shared by two
+// threads: the next issue has to come after a group barrier (tc_forward_tile's after_sync hook).
+template <int HV = 1>
+__device__ __forceinline__ void tc_gather_take(unsigned char* smem, int xoff, bool valid, uint32_t& rphase, RowScalars& d, int half = 0) {
     uint64_t* rbar = reinterpret_cast<uint64_t*>(smem + SM_BAR) + 3;
     tc::mbar_wait(rbar, rphase);
     rphase ^= 1;
     const uint4* rec = reinterpret_cast<const uint4*>(smem + SM_REC + tc_tid() * REC_BYTES);
     const uint4 zero = make_uint4(0, 0, 0, 0);
-    uint4 x[4], sc = zero;
+    constexpr int NC = 4 / HV;
+    const int c0 = HV == 1 ? 0 : NC * half;
+    uint4 x[NC], sc = zero;
     uint32_t vo = 0;
 #pragma unroll
-    for (int c = 0; c < 4; ++c) x[c] = valid ? rec[c] : zero;
-    if (valid) {
+    for (int c = 0; c < NC; ++c) x[c] = valid ? rec[c0 + c] : zero;
+    if (valid && half == 0) {
         sc = rec[4];
         vo = *reinterpret_cast<const uint32_t*>(rec + 5);
     }
 #pragma unroll
-    for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4*>(smem + xoff + c * CHUNK_B + tc_tid() * 16) = x[c];
+    for (int c = 0; c < NC; ++c) *reinterpret_cast<uint4*>(smem + xoff + (c0 + c) * CHUNK_B + tc_tid() * 16) = x[c];
     d.adv = __uint_as_float(sc.x); d.ret = __uint_as_float(sc.y); d.logp_old = __uint_as_float(sc.z);
     d.act = (int)sc.w;
     d.v_old = __uint_as_float(vo);
@@ -505,9 +527,39 @@ __device__ __forceinline__ int stage_pos4(int i, int w2_lo, int w2_hi) {  // i =
 }
 
 // TMEM weight-gradient accumulators of this group -> its staging copy
-__device__ __forceinline__ void tc_stage_grads(unsigned char* smem, const TcSetup& s, const Offsets& o, int in_dim, int out_dim) {
+template <int HV = 1>
+__device__ __forceinline__ void tc_stage_grads(unsigned char* smem, const TcSetup& s, const Offsets& o, int in_dim, int out_dim, int half = 0) {
     float* stage = reinterpret_cast<float*>(smem + SM_STAGE);
     const int r = tc_tid();
+    if constexpr (HV == 2) {  // the same map, each half of a row's columns by its own thread
+        if (r < TC_H) {
+            float v[32];
+            tc::tmem_ld32(s.lane_base + TM_GW2 + 32 * half, v);  // dW2[r][32 half ..]
+#pragma unroll
+            for (int h = 0; h < 8; ++h)
+                *reinterpret_cast<float4*>(stage + o.w2 + (r << 6) + (((8 * half + h) ^ (r & 15)) << 2)) =
+                    make_float4(v[4 * h], v[4 * h + 1], v[4 * h + 2], v[4 * h + 3]);
+            float w[16];
+            if (half == 0) {
+                tc::tmem_ld16(s.lane_base + TM_GW3, w);  // dW3^T[r][o]
+#pragma unroll
+                for (int k = 0; k < OUTP; ++k)
+                    if (k < out_dim) stage[o.w3 + k * TC_H + r] = w[k];
+            } else {
+                tc::tmem_ld16(s.lane_base + TM_GW1 + 16, w);  // D2^T [X|1], column 31 = db2[r]
+                stage[o.b2 + r] = w[15];
+            }
+        } else {
+            float v[16];
+            tc::tmem_ld16(s.lane_base + TM_GW1 + 16 * half, v);  // dW1[r-64][16 half ..], db1[r-64] (column 31)
+            const int rr = r - TC_H;
+#pragma unroll
+            for (int k = 0; k < 16; ++k)
+                if (16 * half + k < in_dim) stage[o.w1 + rr * in_dim + 16 * half + k] = v[k];
+            if (half == 1) stage[o.b1 + rr] = v[15];
+        }
+        return;
+    }
     if (r < TC_H) {
 #pragma unroll
         for (int q = 0; q < 2; ++q) {  // dW2[r][32q..]
@@ -750,7 +802,7 @@ struct TcEpochArgs {
     TcPpoArgs p;           // mb_start = first batch position of the epoch; grads = gradient buffer 0
     float* grads1;         // gradient buffers 1 and 2 (minibatch m reduces into buffer m % 3; all zero on entry and on exit)
     float* grads2;
-    uint2* q_table;        // [EP_THREADS][EP_OPT + 1] scratch (see the kernel)
+    uint2* q_table;        // [threads][float4 per thread + 1] scratch (see the kernel): EP_Q_WORDS entries
     float* g_total;        // [EP_G_STRIDE] sum over ranks (world > 1 only)
     uint32_t* sync_words;  // [0], [1] arrival counters of the in-kernel grid barriers (zero between launches)
     int64_t n_mb, mb_size, total;  // minibatch m = [m * mb_size, (m + 1) * mb_size), the last one runs to `total`
@@ -759,15 +811,21 @@ struct TcEpochArgs {
     opt::AdamArgs adam;
 };
 
-constexpr int EP_THREADS = TC_THREADS * TC_GROUPS;
+constexpr int EP_THREADS = TC_THREADS * TC_GROUPS;  // HV = 1; the kernel runs HV * EP_THREADS threads
+constexpr int EP_HV = 2;                            // threads per tile row of the default instantiation
 constexpr int SM_GROUP = (SM_TOTAL + 1023) & ~1023;   // stride between the groups' maps
 constexpr int SM_EP_SHARED = TC_GROUPS * SM_GROUP;    // CTA-wide scratch: 8 norm partials, 3 coefficients, TC_GROUPS flags
 constexpr int SM_EP_TOTAL = SM_EP_SHARED + 128;
 constexpr int EP_G_STRIDE = 7168;                     // floats per gradient buffer (largest net: 6 728 parameters)
-constexpr int EP_OPT = EP_G_STRIDE / 4 / EP_THREADS;  // 7 float4 of the flat parameter vector per thread: j = t + u * EP_THREADS
-constexpr uint32_t TM_OPT_M = 208;                    // exp_avg: 28 columns (of 32)
-constexpr uint32_t TM_OPT_V0 = 240, TM_OPT_V1 = 80;   // exp_avg_sq: 16 + 12 (of 16) columns
+constexpr int EP_OPT = EP_G_STRIDE / 4 / EP_THREADS;  // HV = 1: 7 float4 of the flat parameter vector per thread: j = t + u * EP_THREADS
+constexpr int EP_OPT2 = 4;                            // HV = 2: 4 float4 per thread (512 threads; entries past n are dead)
+constexpr int EP_Q_WORDS = 2 * EP_THREADS * (EP_OPT2 + 1) > EP_THREADS * (EP_OPT + 1) ? 2 * EP_THREADS * (EP_OPT2 + 1) : EP_THREADS * (EP_OPT + 1);  // q_table entries
+// Spare TMEM columns of a group (lanes = the thread's row).  HV = 1: exp_avg in 28 of the 32 columns at TM_OPT_M, exp_avg_sq in
+// 16 + 12 columns at V0 / V1.  HV = 2: 16 + 16 columns per thread: half 0 exp_avg at M, exp_avg_sq at V0; half 1 at M + 16 / V1.
+constexpr uint32_t TM_OPT_M = 208;
+constexpr uint32_t TM_OPT_V0 = 240, TM_OPT_V1 = 80;
 static_assert(EP_OPT == 7, "column map below is for 7 float4 per thread");
+static_assert(4 * EP_OPT2 * 2 * EP_THREADS >= EP_G_STRIDE, "HV = 2 must cover the whole gradient buffer");
 
 // 32-bit opt::image_index
 __device__ __forceinline__ int ep_image_index(int i, const Offsets& o, int in_dim) {
@@ -798,27 +856,38 @@ __device__ __forceinline__ void ep_st4(uint32_t taddr, const float4& v) {
     asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(taddr), "r"(__float_as_uint(v.x)),
                  "r"(__float_as_uint(v.y)), "r"(__float_as_uint(v.z)), "r"(__float_as_uint(v.w)) : "memory");
 }
-__device__ __forceinline__ uint32_t ep_m_col(int u) { return TM_OPT_M + 4 * u; }
-__device__ __forceinline__ uint32_t ep_v_col(int u) { return u < 4 ? TM_OPT_V0 + 4 * u : TM_OPT_V1 + 4 * (u - 4); }
+template <int HV>
+__device__ __forceinline__ uint32_t ep_m_col(int u, int half) { return HV == 1 ? TM_OPT_M + 4 * u : TM_OPT_M + 16 * half + 4 * u; }
+template <int HV>
+__device__ __forceinline__ uint32_t ep_v_col(int u, int half) {
+    if (HV == 1) return u < 4 ? TM_OPT_V0 + 4 * u : TM_OPT_V1 + 4 * (u - 4);
+    return (half ? TM_OPT_V1 : TM_OPT_V0) + 4 * u;
+}
 
-__global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs e, const __grid_constant__ CUtensorMap rec_map) {
+template <int HV>
+__global__ void __launch_bounds__(HV * EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs e, const __grid_constant__ CUtensorMap rec_map) {
     extern __shared__ __align__(1024) unsigned char smem_all[];
     namespace cg = cooperative_groups;
     cg::grid_group grid = cg::this_grid();
+    constexpr int EPT = HV * EP_THREADS;           // threads of the CTA
+    constexpr int OPT = HV == 1 ? EP_OPT : EP_OPT2;  // float4 of the flat parameter vector per thread: j = t + u * EPT
     const TcPpoArgs& a = e.p;  // (never written: the argument struct stays in the constant bank)
-    const int grp = tc_grp(), r = tc_tid(), rc = (int)threadIdx.x;
+    const int grp = (int)(threadIdx.x / (HV * TC_THREADS)), r = tc_tid(), rc = (int)threadIdx.x;
+    const int half = HV == 1 ? 0 : (int)((threadIdx.x >> 7) & 1);  // warp-uniform
     unsigned char* smem = smem_all + grp * SM_GROUP;
     float* s_red = reinterpret_cast<float*>(smem_all + SM_EP_SHARED);
-    float* s_coef = s_red + 8;
-    int* s_has = reinterpret_cast<int*>(s_red + 12);
+    float* s_coef = s_red + EPT / 32;
+    int* s_has = reinterpret_cast<int*>(s_coef + 4);
+    static_assert(EPT / 32 + 4 + TC_GROUPS <= 32, "CTA-wide scratch is 128 bytes");
     const int64_t vb = (int64_t)blockIdx.x * TC_GROUPS + grp, vg = (int64_t)gridDim.x * TC_GROUPS;  // virtual CTA = group
-    tc_setup_begin(smem, TM_COLS_BWD * TC_GROUPS);
+    tc_setup_begin<HV>(smem, TM_COLS_BWD * TC_GROUPS);
     constexpr uint32_t ID_DH = tc::make_idesc_f16(128, 64, 0, 0, 0, 1);
     constexpr uint32_t ID_G64 = tc::make_idesc_f16(128, 64, 0, 0, 1, 1);
     constexpr uint32_t ID_G32 = tc::make_idesc_f16(128, 32, 0, 0, 1, 1);
     constexpr uint32_t ID_G16 = tc::make_idesc_f16(128, 16, 0, 0, 1, 1);
     const Offsets o = offsets(a.in_dim, TC_H, a.out_dim);
     const int64_t epoch_start = a.mb_start;
+    const bool simple_loss = a.cfg.probs_param == 0 && a.cfg.value_heads <= 1 && a.cfg.plain_pg == 0 && a.n_act > 0 && a.value_index >= 0;
     const opt::AdamArgs& ad = e.adam;
     const int64_t n = ad.n;
     const int64_t step0 = *ad.step;  // rewritten by CTA 0 only after the last grid barrier
@@ -840,7 +909,10 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
     int64_t nm = 0, nt = vb;       // the tile whose records are in flight
     bool n_ok = vb * TC_ROWS < len_of(0);
     if (!n_ok) n_ok = advance(nm, nt);
-    if (n_ok) {
+    // HV = 2: the record prefetch (tile bookkeeping, slot loads -- whose issue stalls on address translation -- and the
+    // gather itself) belongs to the half-1 warps, which run it while the half-0 warps are in the loss stage
+    const bool pf = HV == 1 || half == 1;
+    if (n_ok && pf) {
         bool v;
         const int64_t p = pos_of(nm, nt, v);
         tc_gather_issue(smem, &rec_map, v ? tc_slot(a, p) : 0);
@@ -849,27 +921,27 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
     bool a_ok = n_ok && advance(am, at);
     int32_t sl_next = 0;
     bool v_next = false;
-    if (a.slots && a_ok) {
+    if (a.slots && a_ok && pf) {
         const int64_t p = pos_of(am, at, v_next);
         if (v_next) sl_next = __ldg(a.slots + p);
     }
     tc::fence_before_sync();
     __syncthreads();  // the CTA's TMEM base (group 0's slot) is visible to every group
     tc::fence_after_sync();
-    TcSetup s = tc_setup_finish(smem, a.image, reinterpret_cast<const uint32_t*>(smem_all + SM_BAR + 16), grp * TM_COLS_BWD);
+    TcSetup s = tc_setup_finish<HV>(smem, a.image, reinterpret_cast<const uint32_t*>(smem_all + SM_BAR + 16), grp * TM_COLS_BWD);
     uint32_t xb = 0, wg_commits = 0;  // X buffer toggle and number of commits to bar[1] so far (its phase parity)
     // ---- this CTA's copy of the optimizer state: fp32 masters in registers, moments in the group's spare TMEM columns ----
-    float4 Pr[EP_OPT];
+    float4 Pr[OPT];
     // image positions of each float4's four parameters (0xffff: none) and, in word EP_OPT, bit u = "four consecutive
     // positions" (W2 / W3 rows: one 8-byte store).  Computed once and parked in global memory (the same values from
     // every CTA; a thread only reads back what it wrote itself): 15 registers less across the tile loop.
-    uint2* q_tab = e.q_table + (size_t)rc * (EP_OPT + 1);
+    uint2* q_tab = e.q_table + (size_t)rc * (OPT + 1);
     {
-    uint2 Q[EP_OPT];
+    uint2 Q[OPT];
     uint32_t q_contig = 0;
 #pragma unroll
-    for (int u = 0; u < EP_OPT; ++u) {
-        const int i = 4 * (rc + u * EP_THREADS);
+    for (int u = 0; u < OPT; ++u) {
+        const int i = 4 * (rc + u * EPT);
         {
             uint32_t q[4];
 #pragma unroll
@@ -879,12 +951,12 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
         }
         auto get = [&](const float* src, int k) { return i + k < n ? __ldcg(src + i + k) : 0.f; };
         Pr[u] = make_float4(get(ad.p, 0), get(ad.p, 1), get(ad.p, 2), get(ad.p, 3));
-        ep_st4(s.lane_base + ep_m_col(u), make_float4(get(ad.m, 0), get(ad.m, 1), get(ad.m, 2), get(ad.m, 3)));
-        ep_st4(s.lane_base + ep_v_col(u), make_float4(get(ad.v, 0), get(ad.v, 1), get(ad.v, 2), get(ad.v, 3)));
+        ep_st4(s.lane_base + ep_m_col<HV>(u, half), make_float4(get(ad.m, 0), get(ad.m, 1), get(ad.m, 2), get(ad.m, 3)));
+        ep_st4(s.lane_base + ep_v_col<HV>(u, half), make_float4(get(ad.v, 0), get(ad.v, 1), get(ad.v, 2), get(ad.v, 3)));
     }
 #pragma unroll
-    for (int u = 0; u < EP_OPT; ++u) q_tab[u] = Q[u];
-    q_tab[EP_OPT] = make_uint2(q_contig, 0u);
+    for (int u = 0; u < OPT; ++u) q_tab[u] = Q[u];
+    q_tab[OPT] = make_uint2(q_contig, 0u);
     }
     tc::tmem_st_wait();
 
@@ -913,28 +985,36 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
             [[maybe_unused]] const int trow = (erow >= 0 && it < 2) ? erow + (int)it : -1;
             TRACE(trow, 0);
             RowScalars d;
-            tc_gather_take(smem, xoff, valid, rphase, d);
+            tc_gather_take<HV>(smem, xoff, valid, rphase, d, half);
             const float d_adv = d.adv, d_ret = d.ret, d_logp_old = d.logp_old, d_v_old = d.v_old;
             const int d_act = d.act;
             TRACE(trow, 24);
             // gather of this group's next tile (possibly the first one of a later minibatch: it then overlaps the flush and
-            // the barriers); with a slot table its entries were fetched a tile ago and the ones after are fetched now
-            nm = am; nt = at; n_ok = a_ok;
-            if (n_ok) {
-                bool v;
-                const int64_t p = pos_of(nm, nt, v);
-                tc_gather_issue(smem, &rec_map, !v ? 0 : (a.slots ? sl_next : tc_slot(a, p)));
-                a_ok = advance(am, at);
-                if (a.slots && a_ok) {
-                    const int64_t p2 = pos_of(am, at, v_next);
-                    if (v_next) sl_next = __ldg(a.slots + p2);
+            // the barriers); with a slot table its entries were fetched a tile ago and the ones after are fetched now.
+            // HV = 1: here, ahead of the forward.  HV = 2: by the half-1 warps after the forward (every thread of the group
+            // is then long done with the staging rows), in the shadow of the loss stage.
+            auto prefetch_next = [&]() {
+                nm = am; nt = at; n_ok = a_ok;
+                if (n_ok) {
+                    bool v;
+                    const int64_t p = pos_of(nm, nt, v);
+                    tc_gather_issue(smem, &rec_map, !v ? 0 : (a.slots ? sl_next : tc_slot(a, p)));
+                    a_ok = advance(am, at);
+                    if (a.slots && a_ok) {
+                        const int64_t p2 = pos_of(am, at, v_next);
+                        if (v_next) sl_next = __ldg(a.slots + p2);
+                    }
                 }
-            }
+            };
+            if (HV == 1) prefetch_next();
             TRACE(trow, 25);
-            tc_forward_tile(smem, s, xoff, trow);
+            tc_forward_tile<HV>(smem, s, xoff, trow, half);
+            if (HV == 2 && half == 1) prefetch_next();
+            if (half == 0) {  // the loss stage: one thread per row
             float z[OUTP], dz[OUTP];
             tc_read_out(s, z);
-            const RowLoss rl = row_loss<TC_FAST_LOSS>(z, a.n_act, a.value_index, d_act, d_adv, d_ret, d_logp_old, d_v_old, mean, rstd, a.cfg, inv_n, dz);
+            const RowLoss rl = simple_loss ? row_loss<TC_FAST_LOSS, true>(z, a.n_act, a.value_index, d_act, d_adv, d_ret, d_logp_old, d_v_old, mean, rstd, a.cfg, inv_n, dz)
+                                           : row_loss<TC_FAST_LOSS>(z, a.n_act, a.value_index, d_act, d_adv, d_ret, d_logp_old, d_v_old, mean, rstd, a.cfg, inv_n, dz);
             if (valid) { f_clip += rl.clip; f_vf += rl.vf; f_ent += rl.ent; }
             if ((it & 15) == 15) {
                 l_clip += (double)f_clip; l_vf += (double)f_vf; l_ent += (double)f_ent;
@@ -952,8 +1032,9 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
                 w.x = pack_h2(g[0], g[1]); w.y = pack_h2(g[2], g[3]); w.z = pack_h2(g[4], g[5]); w.w = pack_h2(g[6], g[7]);
                 *reinterpret_cast<uint4*>(smem + SM_G + r * 16) = w;
             }
+            }
             TRACE(trow, 13);
-            tc_sync_for_mma();
+            tc_sync_for_mma<HV>();
             TRACE(trow, 14);
             if (tc_issuer(s.w0)) {
                 tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase, SM_G, 0), desc_w_mn(s.sbase, SM_W3, TC_OF, 0), ID_DH, 0);
@@ -962,9 +1043,9 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
             TRACE(trow, 15);
             tc_wait(s);
             TRACE(trow, 16);
-            tc_epilogue_mask(smem, s.lane_base, SM_H2, SM_D2);
+            tc_epilogue_mask<HV>(smem, s.lane_base, SM_H2, SM_D2, half);
             TRACE(trow, 17);
-            tc_sync_for_mma();
+            tc_sync_for_mma<HV>();
             TRACE(trow, 18);
             if (tc_issuer(s.w0)) {
 #pragma unroll
@@ -975,9 +1056,9 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
             TRACE(trow, 19);
             tc_wait(s);
             TRACE(trow, 20);
-            tc_epilogue_mask(smem, s.lane_base, SM_H1, SM_D1);
+            tc_epilogue_mask<HV>(smem, s.lane_base, SM_H1, SM_D1, half);
             TRACE(trow, 21);
-            tc_sync_for_mma();
+            tc_sync_for_mma<HV>();
             TRACE(trow, 22);
             if (tc_issuer(s.w0)) {
                 const uint32_t acc0 = it > 0;
@@ -1010,18 +1091,18 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
                 l_vf += __shfl_down_sync(0xffffffffu, l_vf, dlt);
                 l_ent += __shfl_down_sync(0xffffffffu, l_ent, dlt);
             }
-            if ((r & 31) == 0) {
+            if ((r & 31) == 0 && half == 0) {
                 const int w = r >> 5;
 #pragma unroll
                 for (int j = 0; j < OUTP; ++j) red_f[w * OUTP + j] = gb3[j];
                 red_d[w * 3 + 0] = l_clip; red_d[w * 3 + 1] = l_vf; red_d[w * 3 + 2] = l_ent;
             }
-            if (r == 0) s_has[grp] = it > 0;
+            if (r == 0 && half == 0) s_has[grp] = it > 0;
         }
         if (it > 0) {
             tc::mbar_wait(s.bar + 1, (wg_commits - 1) & 1);
             tc::fence_after_sync();
-            tc_stage_grads(smem, s, o, a.in_dim, a.out_dim);
+            tc_stage_grads<HV>(smem, s, o, a.in_dim, a.out_dim, half);
         }
         tc::fence_before_sync();
         __syncthreads();
@@ -1033,7 +1114,7 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
 #pragma unroll
             for (int g = 0; g < TC_GROUPS; ++g) { has[g] = s_has[g] != 0; any |= has[g]; }
             if (any) {
-                for (int i = 4 * rc; i < n_stage; i += 4 * EP_THREADS) {
+                for (int i = 4 * rc; i < n_stage; i += 4 * EPT) {
                     const int pos = stage_pos4(i, w2_lo, w2_hi);
                     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
@@ -1077,10 +1158,10 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
         // polls the pairs of its slice from every peer.  Receive areas are double buffered by step parity: a peer
         // overwrites parity b at step seq + 2, after it has finished step seq + 1, which needed this rank's data of step
         // seq + 1, pushed only after every CTA here was done with step seq.
-        uint2 Q[EP_OPT];  // (in flight across the barrier)
+        uint2 Q[OPT];  // (in flight across the barrier)
 #pragma unroll
-        for (int u = 0; u < EP_OPT; ++u) Q[u] = q_tab[u];
-        const uint32_t q_contig = q_tab[EP_OPT].x;
+        for (int u = 0; u < OPT; ++u) Q[u] = q_tab[u];
+        const uint32_t q_contig = q_tab[OPT].x;
         const uint32_t seq = ad.seq + (uint32_t)m;
         __threadfence();
         __syncthreads();
@@ -1111,7 +1192,7 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
             // CTAs read the whole slot, +1 us for one slice each); the extra barrier costs ~1.3 us.
             const int64_t n4s = ad.n_stride / 4, per4 = (n4s + gridDim.x - 1) / gridDim.x;
             const int64_t lo4 = (int64_t)blockIdx.x * per4, hi4 = lo4 + per4 < n4s ? lo4 + per4 : n4s;
-            for (int64_t j = lo4 + rc; j < hi4; j += EP_THREADS) {
+            for (int64_t j = lo4 + rc; j < hi4; j += EPT) {
                 float4 own;
                 if (4 * j + 3 < n) {
                     own = __ldcg(reinterpret_cast<const float4*>(g_cur) + j);
@@ -1171,14 +1252,14 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
             g_src = e.g_total;
         }
         TRACE(erow, 48);
-        float4 G[EP_OPT];  // all loads first (one L2 round trip)
+        float4 G[OPT];  // all loads first (one L2 round trip)
         {
             const float gs = ad.grad_scale;
 #pragma unroll
-            for (int u = 0; u < EP_OPT; ++u) {
-                const int i = 4 * (rc + u * EP_THREADS);
+            for (int u = 0; u < OPT; ++u) {
+                const int i = 4 * (rc + u * EPT);
                 if (i + 3 < n) {
-                    G[u] = __ldcg(reinterpret_cast<const float4*>(g_src) + rc + u * EP_THREADS);
+                    G[u] = __ldcg(reinterpret_cast<const float4*>(g_src) + rc + u * EPT);
                 } else {  // (buffer 0 is the net's own gradient array: exactly n floats)
                     auto get = [&](int k) { return i + k < n ? __ldcg(g_src + i + k) : 0.f; };
                     G[u] = make_float4(get(0), get(1), get(2), get(3));
@@ -1186,7 +1267,7 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
             }
             float sq = 0.f;
 #pragma unroll
-            for (int u = 0; u < EP_OPT; ++u) {
+            for (int u = 0; u < OPT; ++u) {
                 sq = fmaf(G[u].x * gs, G[u].x * gs, sq); sq = fmaf(G[u].y * gs, G[u].y * gs, sq);
                 sq = fmaf(G[u].z * gs, G[u].z * gs, sq); sq = fmaf(G[u].w * gs, G[u].w * gs, sq);
             }
@@ -1196,7 +1277,7 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
             __syncthreads();
             if (rc == 0) {
                 float t = 0.f;
-                for (int w = 0; w < EP_THREADS / 32; ++w) t += s_red[w];
+                for (int w = 0; w < EPT / 32; ++w) t += s_red[w];
                 const float norm = sqrtf(t);
                 float c = 1.f;
                 if (ad.max_norm > 0.f) c = fminf(ad.max_norm / (norm + 1e-6f), 1.f);
@@ -1212,19 +1293,23 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
         {
             const float c0 = s_coef[0], c1 = s_coef[1], c2 = s_coef[2];
             const bool last = m == e.n_mb - 1 && blockIdx.x == 0;
-            float Mo[32], Vo[32];  // one TMEM round trip for all moments of this thread (entries 28..31 unused)
-            {
+            constexpr int NMV = HV == 1 ? 32 : 16;
+            float Mo[NMV], Vo[NMV];  // one TMEM round trip for all moments of this thread (HV = 1: entries 28..31 unused)
+            tc::tmem_st_wait();  // the previous step's stores of these columns (waited here, not there)
+            if constexpr (HV == 1) {
                 float v0[16], v1[16];
-                tc::tmem_st_wait();  // the previous step's stores of these columns (waited here, not there)
                 tc::tmem_ld32(s.lane_base + TM_OPT_M, Mo);
                 tc::tmem_ld16(s.lane_base + TM_OPT_V0, v0);
                 tc::tmem_ld16(s.lane_base + TM_OPT_V1, v1);
 #pragma unroll
                 for (int k = 0; k < 16; ++k) { Vo[k] = v0[k]; Vo[16 + k] = v1[k]; }
+            } else {
+                tc::tmem_ld16(s.lane_base + ep_m_col<HV>(0, half), Mo);
+                tc::tmem_ld16(s.lane_base + ep_v_col<HV>(0, half), Vo);
             }
 #pragma unroll
-            for (int u = 0; u < EP_OPT; ++u) {
-                const int i = 4 * (rc + u * EP_THREADS);
+            for (int u = 0; u < OPT; ++u) {
+                const int i = 4 * (rc + u * EPT);
                 const bool live = i < n;  // TMEM traffic stays warp-uniform: dead entries are all-zero and stay so
                 float4 mm = make_float4(Mo[4 * u], Mo[4 * u + 1], Mo[4 * u + 2], Mo[4 * u + 3]);
                 float4 vv = make_float4(Vo[4 * u], Vo[4 * u + 1], Vo[4 * u + 2], Vo[4 * u + 3]);
@@ -1260,14 +1345,14 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
                 }
             }
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
+            for (int c = 0; c < NMV / 8; ++c) {
                 float t8[8];
 #pragma unroll
                 for (int k = 0; k < 8; ++k) t8[k] = Mo[8 * c + k];
-                tc::tmem_st8(s.lane_base + TM_OPT_M + 8 * c, t8);
+                tc::tmem_st8(s.lane_base + ep_m_col<HV>(0, half) + 8 * c, t8);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) t8[k] = Vo[8 * c + k];
-                tc::tmem_st8(s.lane_base + (c < 2 ? TM_OPT_V0 + 8 * c : TM_OPT_V1 + 8 * (c - 2)), t8);
+                tc::tmem_st8(s.lane_base + (HV == 1 ? (c < 2 ? TM_OPT_V0 + 8 * c : TM_OPT_V1 + 8 * (c - 2)) : ep_v_col<HV>(0, half) + 8 * c), t8);
             }
         }
         TRACE(erow, 45);
@@ -1275,7 +1360,7 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
             float* g_old = ((m + 2) % 3 == 0) ? a.grads : ((m + 2) % 3 == 1 ? e.grads1 : e.grads2);
             const int64_t per = (n + gridDim.x - 1) / gridDim.x;
             const int64_t lo = (int64_t)blockIdx.x * per, hi = lo + per < n ? lo + per : n;
-            for (int64_t i = lo + rc; i < hi; i += EP_THREADS) g_old[i] = 0.f;
+            for (int64_t i = lo + rc; i < hi; i += EPT) g_old[i] = 0.f;
         }
         TRACE(erow, 46);
         tc::fence_async_smem();  // the image entries written above are read by both groups' MMAs
@@ -1288,7 +1373,7 @@ __global__ void __launch_bounds__(EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpochArgs
         float* g_last = ((e.n_mb - 1) % 3 == 0) ? a.grads : ((e.n_mb - 1) % 3 == 1 ? e.grads1 : e.grads2);
         const int64_t per = (n + gridDim.x - 1) / gridDim.x;
         const int64_t lo = (int64_t)blockIdx.x * per, hi = lo + per < n ? lo + per : n;
-        for (int64_t i = lo + rc; i < hi; i += EP_THREADS) g_last[i] = 0.f;
+        for (int64_t i = lo + rc; i < hi; i += EPT) g_last[i] = 0.f;
         if (blockIdx.x == 0 && rc == 0) *ad.step = step0 + e.n_mb;
         if (blockIdx.x == 0 && rc < 2) e.sync_words[rc] = 0u;  // arrival counters: zero between launches
     }

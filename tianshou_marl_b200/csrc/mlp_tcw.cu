@@ -596,6 +596,9 @@ __global__ void __launch_bounds__(THREADS, 1) tcw_kernel(Args a) {
     const int64_t tile_bytes = (int64_t)(KP / 8) * CH;
     const int64_t my_tiles = a.n_tiles > (int64_t)blockIdx.x ? (a.n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
     const Img im = img_of(KP);
+    // streaming path, W1-gradient pass: every CTA walks the 64-column slices from its own starting slice, so that the CTAs
+    // of a minibatch do not all reduce into the same 32 KB of the gradient at the same time
+    const int rot = (int)(blockIdx.x % (unsigned)n_slices);
 
     if (c.warp == 8) {
         // ================= TMA producer =================
@@ -614,7 +617,8 @@ __global__ void __launch_bounds__(THREADS, 1) tcw_kernel(Args a) {
                     const int64_t pt = phys_tile(a, blockIdx.x + i * gridDim.x);
                     const unsigned char* xt = a.ximg + pt * tile_bytes;
                     for (int pass = 0; pass < (TRAIN ? 2 : 1); ++pass) {
-                        for (int sl = 0; sl < n_slices; ++sl, ++it) {
+                        for (int sl0 = 0; sl0 < n_slices; ++sl0, ++it) {
+                            const int sl = pass == 1 ? (sl0 + rot) % n_slices : sl0;  // W1-gradient pass: rotated slice order
                             const int s = (int)(it % STAGES);
                             if (it >= STAGES) tc::mbar_wait(c.bar + B_EMPTY + s, (uint32_t)((it / STAGES - 1) & 1));
                             const int nk = min(SLICE, KP - sl * SLICE);
@@ -723,12 +727,15 @@ __global__ void __launch_bounds__(THREADS, 1) tcw_kernel(Args a) {
                 }
                 __syncwarp();
             } else {
-                for (int sl = 0; sl < n_slices; ++sl, ++it, ++blk) {
+                for (int sl0 = 0; sl0 < n_slices; ++sl0, ++it, ++blk) {
+                    const int sl = (sl0 + rot) % n_slices;
                     const int s = (int)(it % STAGES);
                     const int bk = (int)(blk & 1);
                     tc::mbar_wait(c.bar + B_FULL + s, (uint32_t)((it / STAGES) & 1));
+                    if ((threadIdx.x & 31) == 0 && i == 0) TCW_TRACE(160 + 3 * sl0);
                     if (blk >= 2) tc::mbar_wait(c.bar + B_FREE + bk, (uint32_t)(((blk >> 1) - 1) & 1));
                     tc::fence_after_sync();
+                    if ((threadIdx.x & 31) == 0 && i == 0) TCW_TRACE(161 + 3 * sl0);
                     if (tc::elect_one()) {
                         const int off = SM_RING + s * 2 * SLICE_B;
                         const int nk = min(SLICE, KP - sl * SLICE);
@@ -739,6 +746,7 @@ __global__ void __launch_bounds__(THREADS, 1) tcw_kernel(Args a) {
                         tc::commit(c.bar + B_DONE + bk);
                     }
                     __syncwarp();
+                    if ((threadIdx.x & 31) == 0 && i == 0) TCW_TRACE(162 + 3 * sl0);
                 }
             }
         }
@@ -807,10 +815,12 @@ __global__ void __launch_bounds__(THREADS, 1) tcw_kernel(Args a) {
             if (c.tid == 0) TCW_TRACE(tb + 10);
             if (STREAM) {
                 // W1 gradient of this tile, 64 input features per TMEM block: flush straight to the gradient buffer
-                for (int sl = 0; sl < n_slices; ++sl, ++blk) {
+                for (int sl0 = 0; sl0 < n_slices; ++sl0, ++blk) {
+                    const int sl = (sl0 + rot) % n_slices;
                     const int bk = (int)(blk & 1);
                     tc::mbar_wait(c.bar + B_DONE + bk, (uint32_t)((blk >> 1) & 1));
                     tc::fence_after_sync();
+                    if (c.tid == 0 && i == 0) TCW_TRACE(128 + 3 * sl0);
                     const int nk = min(SLICE, KP - sl * SLICE);
                     float v[32];
                     const bool mine = 32 * c.half < nk;
@@ -828,6 +838,7 @@ __global__ void __launch_bounds__(THREADS, 1) tcw_kernel(Args a) {
                             st4[c.row * 16 + ((8 * c.half + j) ^ (c.row & 7))] = make_float4(v[4 * j] * s, v[4 * j + 1] * s, v[4 * j + 2] * s, v[4 * j + 3] * s);
                     }
                     epi_sync();
+                    if (c.tid == 0 && i == 0) TCW_TRACE(129 + 3 * sl0);
                     const int q4 = nk >> 2;
                     const bool vec = (a.in_dim & 3) == 0;
                     const int rrot = (int)(blockIdx.x * 37u) & (ROWS - 1);  // CTAs walk the rows from different starting points
@@ -838,7 +849,11 @@ __global__ void __launch_bounds__(THREADS, 1) tcw_kernel(Args a) {
                         const int k0 = sl * SLICE + 4 * c4;
                         float* dst = a.grads + o.w1 + (int64_t)r * a.in_dim + k0;
                         if (vec && k0 + 4 <= a.in_dim) {
+#ifdef TSM_TCW_EXPERIMENT_STORE
+                            *reinterpret_cast<float4*>(dst + (int64_t)blockIdx.x * 0) = val;  // timing experiment only: plain stores
+#else
                             red_add_v4(dst, val.x, val.y, val.z, val.w);
+#endif
                         } else {
                             const float e[4] = {val.x, val.y, val.z, val.w};
 #pragma unroll
@@ -848,6 +863,7 @@ __global__ void __launch_bounds__(THREADS, 1) tcw_kernel(Args a) {
                             }
                         }
                     }
+                    if (c.tid == 0 && i == 0) TCW_TRACE(130 + 3 * sl0);
                 }
                 epi_sync();  // the staging buffers alias H1 / D2: nobody writes the next tile's activations while a block is being read
             }

@@ -130,10 +130,16 @@ struct PpoCfg {
 struct RowLoss {
     float clip, vf, ent;
 };
-template <bool FAST = false>
+// SIMPLE: the caller has checked (once, on uniform values) that cfg.probs_param == 0, cfg.value_heads <= 1 and
+// cfg.plain_pg == 0 -- plain PPO on a logits head with one value output.  The same arithmetic with those three folded in
+// as constants: the loss stage of the tcgen05 engine is a dependent chain of one warp per scheduler, so its length is
+// its instruction count (570 -> 300 SASS instructions per row).
+template <bool FAST = false, bool SIMPLE = false>
 __device__ __forceinline__ RowLoss row_loss(const float (&z)[OUTP], int n_act, int value_index, int act, float adv, float ret,
-                                            float logp_old, float v_old, float mean, float rstd, const PpoCfg& cfg, float inv_n,
+                                            float logp_old, float v_old, float mean, float rstd, const PpoCfg& cfg_in, float inv_n,
                                             float (&dz)[OUTP]) {
+    PpoCfg cfg = cfg_in;
+    if (SIMPLE) { cfg.probs_param = 0; cfg.value_heads = 1; cfg.plain_pg = 0; }
     RowLoss out{0.f, 0.f, 0.f};
 #pragma unroll
     for (int j = 0; j < OUTP; ++j) dz[j] = 0.f;
@@ -190,10 +196,16 @@ __device__ __forceinline__ RowLoss row_loss(const float (&z)[OUTP], int n_act, i
     if (value_index >= 0) {
         const int nh = cfg.value_heads > 1 ? cfg.value_heads : 1;
         float v = 0.f;
+        if (SIMPLE) {
 #pragma unroll
-        for (int j = 0; j < OUTP; ++j)
-            if (j >= value_index && j < value_index + nh) v += z[j];
-        v /= (float)nh;
+            for (int j = 0; j < OUTP; ++j)
+                if (j == value_index) v = z[j];
+        } else {
+#pragma unroll
+            for (int j = 0; j < OUTP; ++j)
+                if (j >= value_index && j < value_index + nh) v += z[j];
+            v /= (float)nh;
+        }
         float vf = (ret - v) * (ret - v), dv = 2.f * (v - ret);
         if (cfg.value_clip) {
             const float d = v - v_old;
@@ -205,10 +217,10 @@ __device__ __forceinline__ RowLoss row_loss(const float (&z)[OUTP], int n_act, i
             }
         }
         out.vf = vf;
-        const float dvs = cfg.vf_coef * inv_n * dv / (float)nh;
+        const float dvs = SIMPLE ? cfg.vf_coef * inv_n * dv : cfg.vf_coef * inv_n * dv / (float)nh;
 #pragma unroll
         for (int j = 0; j < OUTP; ++j)
-            if (j >= value_index && j < value_index + nh) dz[j] = dvs;
+            if (SIMPLE ? j == value_index : (j >= value_index && j < value_index + nh)) dz[j] = dvs;
     }
     return out;
 }

@@ -218,7 +218,9 @@ class Collector:
         n = t.numel()
         h = self._pinned.get(name)
         if h is None or h.numel() < n or h.dtype != t.dtype:
-            h = torch.empty(max(n, 1), dtype=t.dtype, pin_memory=True)
+            # sized for the whole episode list: the number of episodes differs from call to call, and a pinned allocation
+            # costs milliseconds
+            h = torch.empty(max(n, self._list_cap, 1), dtype=t.dtype, pin_memory=True)
             self._pinned[name] = h
         h[:n].copy_(t, non_blocking=True)
         return h[:n].numpy()

@@ -12,7 +12,7 @@ VLIB = os.path.join(ROOT, "tools", "_variants", "libtsm_tcw_trace.so")
 if sys.argv[1] == "build":
     os.makedirs(os.path.dirname(VLIB), exist_ok=True)
     subprocess.check_call(["make", "-C", os.path.join(ROOT, "tianshou_marl_b200", "csrc"), "-j8", "BUILD=build_tcwtrace", f"OUT={VLIB}",
-                           "EXTRA=-DTSM_TCW_TRACE"])
+                           "EXTRA=-DTSM_TCW_TRACE" + (" -DTSM_TCW_EXPERIMENT_STORE" if len(sys.argv) > 2 and sys.argv[2] == "store" else "")])
     sys.exit(0)
 
 os.environ["TSM_B200_LIB"] = VLIB
@@ -62,3 +62,7 @@ for i in range(5):
         break
     print(f"issuer tile {i}: start +{t[b] - t0}: " + " ".join(f"{inames[k + 1]} {t[b + k + 1] - t[b + k]}" for k in range(7)))
 print("issuer done +", t[127] - t0)
+if which == "critic":
+    for k in range(10):
+        e, q = 128 + 3 * k, 160 + 3 * k
+        print(f"W1-gradient block {k}: issuer full seen +{t[q] - t0} free seen +{t[q + 1] - t0} issued +{t[q + 2] - t0} | epilogue done seen +{t[e] - t0} staged +{t[e + 1] - t0} reduced +{t[e + 2] - t0}")
