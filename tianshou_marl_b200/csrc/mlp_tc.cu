@@ -285,6 +285,7 @@ int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, cons
     if (!batch->records) return fail(TSM_ERR_INVALID, "%s: engine 1 needs batch.records (tsm_ppo_pack_records)", __func__);
     if (reinterpret_cast<uintptr_t>(net->grads) & 15) return fail(TSM_ERR_INVALID, "%s: grads must be 16-byte aligned", __func__);
     if (adam.n > (int64_t)mlptc::EP_G_STRIDE) return 1;
+    if (mb_size >= (int64_t)1 << 30 || total - (n_mb - 1) * mb_size >= (int64_t)1 << 30) return 1;  // in-minibatch row numbers are 32-bit in the kernel
     static int coop = -1, occ = 0, hv = mlptc::EP_HV;
     const size_t smem = mlptc::SM_EP_TOTAL;
     if (coop < 0) {
@@ -350,6 +351,8 @@ int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, cons
             cudaFuncGetAttributes(&fa, kernel);
             printf("grid %u x %d threads, occ %d, smem %zu, regs %d\n", grid, hv * mlptc::EP_THREADS, occ, smem, fa.numRegs);
         }
+        printf("half-1 prefetch (tile 0): pos/slot %lld gather issue %lld advance %lld slot load issue %lld | start at +%lld of the tile\n", h[3][51] - h[3][50],
+               h[3][52] - h[3][51], h[3][53] - h[3][52], h[3][54] - h[3][53], h[3][50] - h[0][0]);
         for (int row = 0; row < 3; ++row)
             printf("tile row %d: store_rec %lld prefetch-issue %lld to-forward %lld\n", row, h[row][24] - h[row][0], h[row][25] - h[row][24],
                    h[row][1] - h[row][25]);

@@ -224,8 +224,10 @@ struct TcFwdArgs {
 #ifdef TSM_TC_TRACE
 __device__ long long g_trace[4][64];
 #define TRACE(row, slot) do { if (threadIdx.x == 0 && (row) >= 0) g_trace[row][slot] = clock64(); } while (0)
+#define TRACE_H1(on, slot) do { if (threadIdx.x == 128 && (on)) g_trace[3][slot] = clock64(); } while (0)  // first half-1 thread of group 0
 #else
 #define TRACE(row, slot) do { } while (0)
+#define TRACE_H1(on, slot) do { } while (0)
 #endif
 
 struct TcSetup {
@@ -296,16 +298,15 @@ __device__ __forceinline__ void tc_wait(TcSetup& s) {
 }
 
 // [X|1] -> H1 -> H2 -> OUT for the tile in the X image at xoff; leaves OUT in TMEM (waited)
-struct TcNoHook { __device__ __forceinline__ void operator()() const {} };
-// after_sync: run by every thread right after the first group barrier (the X image is complete and every thread is past
-// its reads of the record staging area: the epoch kernel issues the next tile's record gather there)
+struct TcNoHook { __device__ __forceinline__ void operator()(int) const {} };
+// in_wait(stage): run by every thread between the issue of layer `stage`'s MMAs and the wait for them (the epoch kernel
+// slips the next tile's record gather into these waits)
 template <int HV = 1, typename Hook = TcNoHook>
-__device__ __forceinline__ void tc_forward_tile(unsigned char* smem, TcSetup& s, int xoff, int trow = -1, int half = 0, Hook after_sync = Hook()) {
+__device__ __forceinline__ void tc_forward_tile(unsigned char* smem, TcSetup& s, int xoff, int trow = -1, int half = 0, Hook in_wait = Hook()) {
     constexpr uint32_t ID64 = tc::make_idesc_f16(128, 64, 0, 0, 0, 0);
     constexpr uint32_t ID16 = tc::make_idesc_f16(128, 16, 0, 0, 0, 0);
     TRACE(trow, 1);
     tc_sync_for_mma<HV>();
-    after_sync();
     TRACE(trow, 2);
     if (tc_issuer(s.w0)) {
 #pragma unroll
@@ -314,6 +315,7 @@ __device__ __forceinline__ void tc_forward_tile(unsigned char* smem, TcSetup& s,
         tc::commit(s.bar);
     }
     TRACE(trow, 3);
+    in_wait(0);
     tc_wait(s);
     TRACE(trow, 4);
     tc_epilogue_relu<HV>(smem, s.lane_base, SM_H1, half);
@@ -328,6 +330,7 @@ __device__ __forceinline__ void tc_forward_tile(unsigned char* smem, TcSetup& s,
         tc::commit(s.bar);
     }
     TRACE(trow, 7);
+    in_wait(1);
     tc_wait(s);
     TRACE(trow, 8);
     tc_epilogue_relu<HV>(smem, s.lane_base, SM_H2, half);
@@ -342,6 +345,7 @@ __device__ __forceinline__ void tc_forward_tile(unsigned char* smem, TcSetup& s,
         tc::commit(s.bar);
     }
     TRACE(trow, 11);
+    in_wait(2);
     tc_wait(s);
     TRACE(trow, 12);
 }
@@ -888,29 +892,34 @@ __global__ void __launch_bounds__(HV * EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpoc
     const Offsets o = offsets(a.in_dim, TC_H, a.out_dim);
     const int64_t epoch_start = a.mb_start;
     const bool simple_loss = a.cfg.probs_param == 0 && a.cfg.value_heads <= 1 && a.cfg.plain_pg == 0 && a.n_act > 0 && a.value_index >= 0;
+    const bool simple5 = simple_loss && a.n_act == 5 && a.value_index == 5;
     const opt::AdamArgs& ad = e.adam;
     const int64_t n = ad.n;
     const int64_t step0 = *ad.step;  // rewritten by CTA 0 only after the last grid barrier
-    // this group's tile sequence over the whole epoch: (m, tile) -> next (m, tile); false at the end
-    auto len_of = [&](int64_t m_) { return m_ == e.n_mb - 1 ? e.total - m_ * e.mb_size : e.mb_size; };
+    // this group's tile sequence over the whole epoch: (m, tile) -> next (m, tile); false at the end.  Tile counts and
+    // in-minibatch row numbers in 32 bits (this bookkeeping sits on the tile's dependent chain); positions in 64.
+    const int n_mb32 = (int)e.n_mb, vb32 = (int)vb, vg32 = (int)vg;
+    const int len_full = (int)e.mb_size, len_last = (int)(e.total - (e.n_mb - 1) * e.mb_size);
+    const int tiles_full = (len_full + TC_ROWS - 1) / TC_ROWS, tiles_last = (len_last + TC_ROWS - 1) / TC_ROWS;
     auto advance = [&](int64_t& m_, int64_t& t_) -> bool {
-        if ((t_ + vg) * TC_ROWS < len_of(m_)) { t_ += vg; return true; }
-        for (int64_t mm = m_ + 1; mm < e.n_mb; ++mm)
-            if (vb * TC_ROWS < len_of(mm)) { m_ = mm; t_ = vb; return true; }
+        const int m32 = (int)m_, t32 = (int)t_ + vg32;
+        if (t32 < (m32 == n_mb32 - 1 ? tiles_last : tiles_full)) { t_ = t32; return true; }
+        for (int mm = m32 + 1; mm < n_mb32; ++mm)
+            if (vb32 < (mm == n_mb32 - 1 ? tiles_last : tiles_full)) { m_ = mm; t_ = vb32; return true; }
         return false;
     };
     auto pos_of = [&](int64_t m_, int64_t t_, bool& valid) -> int64_t {  // batch position of this thread's row
-        const int64_t q = t_ * TC_ROWS + r;
-        valid = q < len_of(m_);
+        const int q = (int)t_ * TC_ROWS + r;
+        valid = q < ((int)m_ == n_mb32 - 1 ? len_last : len_full);
         return epoch_start + m_ * e.mb_size + q;
     };
+    auto len_of = [&](int64_t m_) { return m_ == e.n_mb - 1 ? e.total - m_ * e.mb_size : e.mb_size; };
     uint32_t rphase = 0;
     __syncthreads();  // barriers initialised before any thread's bulk copy names them
     int64_t nm = 0, nt = vb;       // the tile whose records are in flight
     bool n_ok = vb * TC_ROWS < len_of(0);
     if (!n_ok) n_ok = advance(nm, nt);
-    // HV = 2: the record prefetch (tile bookkeeping, slot loads -- whose issue stalls on address translation -- and the
-    // gather itself) belongs to the half-1 warps, which run it while the half-0 warps are in the loss stage
+    // HV = 2: the record prefetch (tile bookkeeping, slot loads and the gather itself) belongs to the half-1 warps
     const bool pf = HV == 1 || half == 1;
     if (n_ok && pf) {
         bool v;
@@ -992,18 +1001,25 @@ __global__ void __launch_bounds__(HV * EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpoc
             // gather of this group's next tile (possibly the first one of a later minibatch: it then overlaps the flush and
             // the barriers); with a slot table its entries were fetched a tile ago and the ones after are fetched now.
             // HV = 1: here, ahead of the forward.  HV = 2: by the half-1 warps after the forward (every thread of the group
-            // is then long done with the staging rows), in the shadow of the loss stage.
+            // is then long done with the staging rows), in the shadow of the loss stage.  (The 32 gather4 copies of a tile
+            // keep the SM's TMA unit busy for ~900 cycles and block their issuing warps that long: spreading them over the
+            // MMA waits of the other stages, one warp each, measured slower -- the late warp delays its stage.)
             auto prefetch_next = [&]() {
+                TRACE_H1(trow == 0, 50);
                 nm = am; nt = at; n_ok = a_ok;
                 if (n_ok) {
                     bool v;
                     const int64_t p = pos_of(nm, nt, v);
+                    TRACE_H1(trow == 0, 51);
                     tc_gather_issue(smem, &rec_map, !v ? 0 : (a.slots ? sl_next : tc_slot(a, p)));
+                    TRACE_H1(trow == 0, 52);
                     a_ok = advance(am, at);
+                    TRACE_H1(trow == 0, 53);
                     if (a.slots && a_ok) {
                         const int64_t p2 = pos_of(am, at, v_next);
                         if (v_next) sl_next = __ldg(a.slots + p2);
                     }
+                    TRACE_H1(trow == 0, 54);
                 }
             };
             if (HV == 1) prefetch_next();
@@ -1013,7 +1029,10 @@ __global__ void __launch_bounds__(HV * EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpoc
             if (half == 0) {  // the loss stage: one thread per row
             float z[OUTP], dz[OUTP];
             tc_read_out(s, z);
-            const RowLoss rl = simple_loss ? row_loss<TC_FAST_LOSS, true>(z, a.n_act, a.value_index, d_act, d_adv, d_ret, d_logp_old, d_v_old, mean, rstd, a.cfg, inv_n, dz)
+            // (three instantiations of the same arithmetic behind uniform branches: five actions + value, the shape of every
+            // discrete MPE scenario; plain PPO of any shape; everything else)
+            const RowLoss rl = simple5 ? row_loss<TC_FAST_LOSS, true, 5>(z, 5, 5, d_act, d_adv, d_ret, d_logp_old, d_v_old, mean, rstd, a.cfg, inv_n, dz)
+                             : simple_loss ? row_loss<TC_FAST_LOSS, true>(z, a.n_act, a.value_index, d_act, d_adv, d_ret, d_logp_old, d_v_old, mean, rstd, a.cfg, inv_n, dz)
                                            : row_loss<TC_FAST_LOSS>(z, a.n_act, a.value_index, d_act, d_adv, d_ret, d_logp_old, d_v_old, mean, rstd, a.cfg, inv_n, dz);
             if (valid) { f_clip += rl.clip; f_vf += rl.vf; f_ent += rl.ent; }
             if ((it & 15) == 15) {
@@ -1036,9 +1055,16 @@ __global__ void __launch_bounds__(HV * EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpoc
             TRACE(trow, 13);
             tc_sync_for_mma<HV>();
             TRACE(trow, 14);
+            // The three weight-gradient products are issued as soon as their operands exist, each behind the waited MMA of
+            // its stage (commit first: the wait does not cover them): the issuing lane spends the time it would otherwise
+            // wait, instead of 24 MMA issues at the end of the tile with the rest of the group idle.
+            const uint32_t acc0 = it > 0;
             if (tc_issuer(s.w0)) {
                 tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase, SM_G, 0), desc_w_mn(s.sbase, SM_W3, TC_OF, 0), ID_DH, 0);
                 tc::commit(s.bar);
+#pragma unroll
+                for (int ks = 0; ks < TC_ROWS / 16; ++ks)  // [H2; H1]^T G: rows 0..63 = dW3^T
+                    tc::mma_f16(s.tmem + TM_GW3, desc_act_mn(s.sbase, SM_H2, ks), desc_act_mn(s.sbase, SM_G, ks), ID_G16, ks > 0 ? 1u : acc0);
             }
             TRACE(trow, 15);
             tc_wait(s);
@@ -1052,6 +1078,11 @@ __global__ void __launch_bounds__(HV * EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpoc
                 for (int ks = 0; ks < TC_H / 16; ++ks)
                     tc::mma_f16(s.tmem + TM_SCR, desc_act_k(s.sbase, SM_D2, ks), desc_w_mn(s.sbase, SM_W2, TC_H, ks), ID_DH, ks > 0);
                 tc::commit(s.bar);
+                // [D2; D1]^T H1: rows 0..63 = dW2.  Rows 64..127 (the D1 half of the stacked operand, which the next stage is
+                // about to write) land in accumulator lanes nobody reads.
+#pragma unroll
+                for (int ks = 0; ks < TC_ROWS / 16; ++ks)
+                    tc::mma_f16(s.tmem + TM_GW2, desc_act_mn(s.sbase, SM_D2, ks), desc_act_mn(s.sbase, SM_H1, ks), ID_G64, ks > 0 ? 1u : acc0);
             }
             TRACE(trow, 19);
             tc_wait(s);
@@ -1061,13 +1092,6 @@ __global__ void __launch_bounds__(HV * EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpoc
             tc_sync_for_mma<HV>();
             TRACE(trow, 22);
             if (tc_issuer(s.w0)) {
-                const uint32_t acc0 = it > 0;
-#pragma unroll
-                for (int ks = 0; ks < TC_ROWS / 16; ++ks)
-                    tc::mma_f16(s.tmem + TM_GW3, desc_act_mn(s.sbase, SM_H2, ks), desc_act_mn(s.sbase, SM_G, ks), ID_G16, ks > 0 ? 1u : acc0);
-#pragma unroll
-                for (int ks = 0; ks < TC_ROWS / 16; ++ks)
-                    tc::mma_f16(s.tmem + TM_GW2, desc_act_mn(s.sbase, SM_D2, ks), desc_act_mn(s.sbase, SM_H1, ks), ID_G64, ks > 0 ? 1u : acc0);
 #pragma unroll
                 for (int ks = 0; ks < TC_ROWS / 16; ++ks)
                     tc::mma_f16(s.tmem + TM_GW1, desc_act_mn(s.sbase, SM_D2, ks), desc_act_mn(s.sbase, xoff, ks), ID_G32, ks > 0 ? 1u : acc0);

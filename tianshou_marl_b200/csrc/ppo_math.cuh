@@ -83,8 +83,11 @@ template <bool FAST> __device__ __forceinline__ float div_t(float a, float b) { 
 // clamp(log p, log eps, log(1 - eps)).  Entropy and log-probabilities use the clamped logs; a clamped entry has no gradient.
 constexpr float PROBS_LOG_LO = -15.942385f;      // log(2^-23)
 constexpr float PROBS_LOG_HI = -1.1920930e-7f;   // log(1 - 2^-23)
-template <bool FAST = false>
-__device__ __forceinline__ Soft softmax_row(const float* z, int n_act, bool probs = false) {
+// NA > 0: the number of actions as a compile-time constant (the caller has checked n_act == NA): the same operations in the
+// same order on entries 0..NA-1, none of the predication on the others
+template <bool FAST = false, int NA = 0>
+__device__ __forceinline__ Soft softmax_row(const float* z, int n_act_in, bool probs = false) {
+    const int n_act = NA ? NA : n_act_in;
     Soft s;
     float m = -INFINITY;
 #pragma unroll
@@ -94,7 +97,7 @@ __device__ __forceinline__ Soft softmax_row(const float* z, int n_act, bool prob
 #pragma unroll
     for (int j = 0; j < OUTP; ++j) {
         s.p[j] = j < n_act ? exp_t<FAST>(z[j] - m) : 0.f;
-        sum += s.p[j];
+        if (!NA || j < NA) sum += s.p[j];
     }
     const float lse = log_t<FAST>(sum);
     const float inv_sum = div_t<FAST>(1.f, sum);
@@ -134,17 +137,20 @@ struct RowLoss {
 // cfg.plain_pg == 0 -- plain PPO on a logits head with one value output.  The same arithmetic with those three folded in
 // as constants: the loss stage of the tcgen05 engine is a dependent chain of one warp per scheduler, so its length is
 // its instruction count (570 -> 300 SASS instructions per row).
-template <bool FAST = false, bool SIMPLE = false>
-__device__ __forceinline__ RowLoss row_loss(const float (&z)[OUTP], int n_act, int value_index, int act, float adv, float ret,
+// NA > 0 (with SIMPLE): additionally n_act == NA and value_index == NA, checked by the caller.
+template <bool FAST = false, bool SIMPLE = false, int NA = 0>
+__device__ __forceinline__ RowLoss row_loss(const float (&z)[OUTP], int n_act_in, int value_index_in, int act, float adv, float ret,
                                             float logp_old, float v_old, float mean, float rstd, const PpoCfg& cfg_in, float inv_n,
                                             float (&dz)[OUTP]) {
+    static_assert(NA == 0 || (SIMPLE && NA < OUTP), "NA needs SIMPLE and room for the value output");
+    const int n_act = NA ? NA : n_act_in, value_index = NA ? NA : value_index_in;
     PpoCfg cfg = cfg_in;
     if (SIMPLE) { cfg.probs_param = 0; cfg.value_heads = 1; cfg.plain_pg = 0; }
     RowLoss out{0.f, 0.f, 0.f};
 #pragma unroll
     for (int j = 0; j < OUTP; ++j) dz[j] = 0.f;
     if (n_act > 0) {
-        const Soft sm = softmax_row<FAST>(z, n_act, cfg.probs_param != 0);
+        const Soft sm = softmax_row<FAST, NA>(z, n_act, cfg.probs_param != 0);
         float lp = 0.f;
 #pragma unroll
         for (int j = 0; j < OUTP; ++j)
