@@ -1191,6 +1191,11 @@ __global__ void __launch_bounds__(HV * EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpoc
         __syncthreads();
         const uint32_t arrivals = (uint32_t)(m + 1) * gridDim.x;  // counter value once every CTA has arrived at this barrier
         if (rc == 0) atomicAdd(e.sync_words, 1u);
+        if (rc == 64) {  // the bias corrections of this step (double-precision powers): in the shadow of the barrier wait
+            const int64_t step = step0 + m + 1;
+            s_coef[1] = ad.lr / (float)(1.0 - opt::ipow((double)ad.beta1, step));
+            s_coef[2] = (float)(1.0 / sqrt(1.0 - opt::ipow((double)ad.beta2, step)));
+        }
         if (rc == 0) {
             const uint32_t* w = e.sync_words;
             const uint32_t want = arrivals;
@@ -1305,10 +1310,7 @@ __global__ void __launch_bounds__(HV * EP_THREADS, 1) tc_ppo_epoch_kernel(TcEpoc
                 const float norm = sqrtf(t);
                 float c = 1.f;
                 if (ad.max_norm > 0.f) c = fminf(ad.max_norm / (norm + 1e-6f), 1.f);
-                const int64_t step = step0 + m + 1;
                 s_coef[0] = c * gs;
-                s_coef[1] = ad.lr / (float)(1.0 - opt::ipow((double)ad.beta1, step));
-                s_coef[2] = (float)(1.0 / sqrt(1.0 - opt::ipow((double)ad.beta2, step)));
                 if (ad.gnorm_out && blockIdx.x == 0) *ad.gnorm_out = norm;
             }
             __syncthreads();
