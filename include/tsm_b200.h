@@ -353,10 +353,11 @@ typedef struct tsm_ppo_batch {
                                 indices change.  NULL: computed in the kernels.  Needs size * n_rows < 2^31. */
 } tsm_ppo_batch;
 
-/* Engine 1 gathers each minibatch row as ONE 96-byte record (3 sectors, one page) instead of 7-8 sectors spread over
- * five arrays: halves x[32] (obs as fp16, zero padded, x[31] = 1) | float adv, ret, logp_old | int32 act | float v_old |
- * 12 bytes pad.  Packs every slot of the buffer ([size][n_rows], storage order); NULL source arrays pack as zeros. */
-#define TSM_PPO_RECORD_BYTES 96
+/* Engine 1 gathers each minibatch row as ONE 96-byte record (3 sectors of one 128-byte line) instead of 7-8 sectors spread
+ * over five arrays: halves x[32] (obs as fp16, zero padded, x[31] = 1) | float adv, ret, logp_old | int32 act | float v_old |
+ * 12 bytes pad; records sit at a 128-byte pitch (TSM_PPO_RECORD_BYTES per slot, the last 32 bytes unused) in a 128-byte
+ * aligned array.  Packs every slot of the buffer ([size][n_rows], storage order); NULL source arrays pack as zeros. */
+#define TSM_PPO_RECORD_BYTES 128
 int tsm_ppo_pack_records(const tsm_net* net, const tsm_ppo_batch* batch, void* records, tsm_stream_t stream);
 
 typedef struct tsm_ppo_cfg {

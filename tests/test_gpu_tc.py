@@ -120,7 +120,7 @@ def test_ppo_minibatch_tc_vs_fp32(O, n):
 
 
 def test_pack_records_bit_exact():
-    """tsm_ppo_pack_records: 96-byte rows = fp16(obs) zero padded with x[31] = 1 | adv ret logp_old | act | v_old | pad."""
+    """tsm_ppo_pack_records: 96-byte rows at a 128-byte pitch = fp16(obs) zero padded with x[31] = 1 | adv ret logp_old | act | v_old | pad."""
     from tianshou_marl_b200 import _lib
     from tianshou_marl_b200.utils import ActorCriticNet
 
@@ -149,7 +149,7 @@ def test_pack_records_bit_exact():
             assert np.array_equal(sc[:, 0], adv) and np.array_equal(sc[:, 1], ret) and np.array_equal(sc[:, 2], lp)
             assert np.array_equal(h[:, 76:80].copy().view(np.int32)[:, 0], act)
             assert np.array_equal(h[:, 80:84].copy().view(np.float32)[:, 0], vo if with_vo else np.zeros(n, np.float32))
-            assert not h[:, 84:].any()
+            assert not h[:, 84:96].any()  # (bytes 96..127 of the 128-byte pitch are never written)
 
 
 def test_minibatch_tc_needs_records():

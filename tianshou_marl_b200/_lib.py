@@ -43,7 +43,7 @@ class TsmMpe(C.Structure):
 
 
 TC_IMAGE_BYTES = 123648  # TSM_TC_IMAGE_BYTES
-PPO_RECORD_BYTES = 96  # TSM_PPO_RECORD_BYTES
+PPO_RECORD_BYTES = 128  # TSM_PPO_RECORD_BYTES (96 used, 128-byte pitch)
 
 
 class TsmNet(C.Structure):

@@ -118,8 +118,9 @@ class Workload:
             out.update({"kernel": "tc_ppo_epoch_kernel" if persistent else "ppo_minibatch_kernel",
                         "bound": "tensor", "achieved": ach, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach / tf_peak,
                         # dram__bytes_read.sum + dram__bytes_write.sum of one tc_ppo_epoch_kernel launch over 25 165 824 rows,
-                        # profiles/r01_ncu_full_v4.csv (ncu --set full); null for other shapes / engines
-                        "traffic": 4.848e9 if (persistent and rows == 25165824 and O == 18) else None,
+                        # profiles/r02_ncu_full_epoch.csv (ncu --set full; records at a 128-byte pitch: 1.38x the 96 algorithmic
+                        # bytes, 2.0x at the 96-byte pitch of round 1); null for other shapes / engines
+                        "traffic": 3.326e9 if (persistent and rows == 25165824 and O == 18) else None,
                         "flop_per_unit": 3.0 * fwd_flop, "bytes_per_unit": rec_bytes, "units_per_launch": rows,
                         "launch_us": t * 1e6, "minibatch_us": stages[dom]["launch_ms"] * 1e3 / self.n_mb,
                         "hbm_gbs": rec_bytes * rows / t / 1e9,

@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(256) pack_records_kernel(const float* __restri
             if (k < in_dim) x[k] = __ldcs(p + k);
     }
     x[TC_XF - 1] = 1.0f;
-    uint4* out = records + s * (REC_BYTES / 16);
+    uint4* out = records + s * (REC_PITCH / 16);
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
         uint4 v;
@@ -202,8 +202,8 @@ static int record_map(const void* records, int64_t n_slots, CUtensorMap* out, co
     static CUtensorMap c_map;
     if (records != c_rec || n_slots != c_n) {
         if (n_slots <= 0 || n_slots >= (int64_t)1 << 31) return fail(TSM_ERR_UNSUPPORTED, "%s: engine 1 needs size * n_rows < 2^31", fn);
-        if (reinterpret_cast<uintptr_t>(records) & 15) return fail(TSM_ERR_INVALID, "%s: records must be 16-byte aligned", fn);
-        const cuuint64_t dim[2] = {mlptc::REC_BYTES / 4, (cuuint64_t)n_slots}, stride[1] = {mlptc::REC_BYTES};
+        if (reinterpret_cast<uintptr_t>(records) & 127) return fail(TSM_ERR_INVALID, "%s: records must be 128-byte aligned", fn);
+        const cuuint64_t dim[2] = {mlptc::REC_BYTES / 4, (cuuint64_t)n_slots}, stride[1] = {mlptc::REC_PITCH};
         const cuuint32_t box[2] = {mlptc::REC_BYTES / 4, 1}, estr[2] = {1, 1};
         const CUresult r = encode(&c_map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void*>(records), dim, stride, box, estr,
                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,

@@ -56,6 +56,8 @@ constexpr int SM_FWD_TOTAL = SM_BAR + 64;        // the forward kernel stops her
 constexpr int SM_D2 = SM_FWD_TOTAL;              // 16 KB  (backward only)
 constexpr int SM_D1 = SM_D2 + 8 * CHUNK_B;       // 16 KB
 constexpr int REC_BYTES = 96;  // halves x[32] | float adv, ret, logp_old | int32 act | float v_old | 12 bytes pad
+constexpr int REC_PITCH = 128; // distance between records in device memory: a record never straddles a 128-byte line (at a 96-byte
+                               // pitch the gather moved 2.0x the record bytes through DRAM); the TMA box is the first 96 bytes
 constexpr int SM_REC = (SM_D1 + 8 * CHUNK_B + 127) & ~127;  // 12 KB: the next tile's batch records, landed by TMA gather4 (128-byte aligned)
 constexpr int SM_TOTAL = SM_REC + TC_ROWS * REC_BYTES;  // 115,712 B: still two CTAs per SM (2 x (this + 1 KB) = 228 KB exactly)
 constexpr int SM_STAGE = SM_H2;                  // flush staging: fp32 copy of the flat gradient (<= 32 KB)
