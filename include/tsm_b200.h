@@ -299,6 +299,11 @@ typedef struct tsm_net {
     int64_t x_scratch_bytes; /* >= tsm_tcw_x_bytes(in_dim, rows of the largest call) */
     int32_t probs_param; /* 1: the actor is DiscreteActor(softmax_output=True) feeding Categorical(probs=...) (utils/net/discrete.py:41,85-86):
                             log-probabilities / entropy are log(clamp(softmax(logits), eps, 1 - eps)) as torch computes them */
+    int32_t n_sigma;     /* 0, or n_act: the n_act head outputs are the MEANS of a diagonal Gaussian whose log standard deviations are
+                            n_sigma more parameters stored behind b3 (n_params = tsm_net_param_count + n_sigma) --
+                            ContinuousActorProbabilistic(unbounded=True, conditioned_sigma=False) with Independent(Normal, 1)
+                            (utils/net/continuous.py:222,229-247).  Engine 0 only; tsm_ppo_minibatch then reads tsm_ppo_batch.act_f,
+                            and tsm_net_forward serves mode 0 only (sampling / log-probabilities are elementwise host-side ops) */
 } tsm_net;
 #define TSM_TC_IMAGE_BYTES 123648 /* 16 896 image + tsm_ppo_epoch's three more gradient-sized buffers of 7 168 floats + 256 bytes of barrier words + a 20 KB index table */
 
@@ -351,6 +356,7 @@ typedef struct tsm_ppo_batch {
                                 visits; engine 1's tsm_ppo_minibatch / tsm_ppo_epoch then read it instead of evaluating the
                                 permutation per row.  The caller refills it whenever perm_key / perm_n / start / len /
                                 indices change.  NULL: computed in the kernels.  Needs size * n_rows < 2^31. */
+    const float* act_f;      /* Gaussian nets (tsm_net.n_sigma > 0): [size][n_rows][n_act] float actions as stored (before map_action) */
 } tsm_ppo_batch;
 
 /* Engine 1 gathers each minibatch row as ONE 96-byte record (3 sectors of one 128-byte line) instead of 7-8 sectors spread

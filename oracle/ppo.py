@@ -11,6 +11,9 @@ Restates, for the shared-trunk actor-critic  in -> H -> H -> (n_act logits, 1 va
   tianshou/algorithm/algorithm_base.py:485-498   zero_grad / backward / clip_grad_norm_ / Adam
 PINNED: tests/test_oracle_ppo.py checks it against tests/golden/ppo.npz, recorded from the
 unmodified reference PPO (tests/golden/make_golden_more.py).
+Continuous actions (Net(log_sigma=...)): the head's n_act outputs are the means and log_sigma the state-independent log
+standard deviations of Independent(Normal, 1) -- ContinuousActorProbabilistic(unbounded=True, conditioned_sigma=False),
+tianshou/utils/net/continuous.py:196-247, test/continuous/test_ppo.py:104-110; pinned to tests/golden/ppo_gauss.npz.
 """
 from __future__ import annotations
 
@@ -24,15 +27,17 @@ from . import gae as ogae
 class Net:
     """Parameters in torch.nn.Linear convention; W3/b3 stack the actor rows then the critic row."""
 
-    def __init__(self, W1, b1, W2, b2, W3, b3, n_act: int) -> None:
-        self.p = [torch.tensor(np.asarray(a), dtype=torch.float32).clone().requires_grad_(True) for a in (W1, b1, W2, b2, W3, b3)]
+    def __init__(self, W1, b1, W2, b2, W3, b3, n_act: int, log_sigma=None) -> None:
+        arrs = (W1, b1, W2, b2, W3, b3) + ((np.asarray(log_sigma).reshape(-1),) if log_sigma is not None else ())
+        self.p = [torch.tensor(np.asarray(a), dtype=torch.float32).clone().requires_grad_(True) for a in arrs]
         self.n_act = n_act
+        self.gaussian = log_sigma is not None
         self.m = [torch.zeros_like(x) for x in self.p]
         self.v = [torch.zeros_like(x) for x in self.p]
         self.t = 0
 
     def forward(self, x: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
-        W1, b1, W2, b2, W3, b3 = self.p
+        W1, b1, W2, b2, W3, b3 = self.p[:6]
         h = F.relu(F.linear(x, W1, b1))
         h = F.relu(F.linear(h, W2, b2))
         o = F.linear(h, W3, b3)
@@ -60,6 +65,15 @@ def values(net: Net, obs: np.ndarray, chunk: int = 1 << 16) -> np.ndarray:
         for i in range(0, len(obs), chunk):
             out.append(net.forward(torch.from_numpy(np.ascontiguousarray(obs[i:i + chunk], np.float32)))[1])
     return torch.cat(out).numpy()
+
+
+def policy_dist(net: Net, logits: torch.Tensor, probs_param: bool):
+    """dist_fn of the policy: Categorical for discrete heads, Independent(Normal(mu, sigma), 1) for a Gaussian net
+    (sigma = exp(sigma_param) broadcast over the rows, continuous.py:244-246)."""
+    if net.gaussian:
+        sigma = (net.p[6].view(1, -1) + torch.zeros_like(logits)).exp()
+        return torch.distributions.Independent(torch.distributions.Normal(logits, sigma), 1)
+    return log_softmax_dist(logits, probs_param)
 
 
 def log_softmax_dist(logits: torch.Tensor, probs_param: bool) -> torch.distributions.Categorical:
@@ -103,7 +117,7 @@ def preprocess(net: Net, obs, obs_next, act_, rew, term, trunc, indices, unfinis
         ret, adv = _gae(rew, term, trunc, indices, unfinished, v_n, v_s, gamma, lam)
     with torch.no_grad():
         logits, _ = net.forward(torch.from_numpy(np.ascontiguousarray(obs, np.float32)))
-        logp_old = log_softmax_dist(logits, probs_param).log_prob(torch.from_numpy(np.asarray(act_)).float()).numpy()
+        logp_old = policy_dist(net, logits, probs_param).log_prob(torch.from_numpy(np.asarray(act_)).float()).numpy()
     return v_s, ret.astype(np.float32), adv.astype(np.float32), logp_old
 
 
@@ -136,7 +150,7 @@ def adam_step(net: Net, lr: float, max_grad_norm: float, b1=0.9, b2=0.999, eps=1
 def minibatch_loss(net: Net, obs, act_, adv, ret, logp_old, v_old, cfg: dict, probs_param=False):
     """ppo.py:181-211 for one minibatch (tensors)."""
     logits, value = net.forward(obs)
-    dist = log_softmax_dist(logits, probs_param)
+    dist = policy_dist(net, logits, probs_param)
     if cfg.get("a2c", False):  # A2C._update_with_batch (a2c.py:262-272)
         actor_loss = -(dist.log_prob(act_) * adv).mean()
         vf_loss = (ret - value).pow(2).mean()

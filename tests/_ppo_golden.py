@@ -35,6 +35,35 @@ def load_case(g, ci):
     return c
 
 
+def load_gauss(g, ci):
+    """tests/golden/ppo_gauss.npz (make_golden_gauss.py): load_case with float actions [T][R][A] and the log_sigma parameter."""
+    pre = f"p{ci}_"
+    R, T, O, H, A, bs, repeat, _, seed = (int(v) for v in g[pre + "cfg"])
+    eps_clip, dual_clip, vf_coef, ent_coef, value_clip, adv_norm, max_norm, lr, gamma, lam = (float(v) for v in g[pre + "hyper"])
+    c = dict(R=R, T=T, O=O, H=H, nA=A, bs=bs, repeat=repeat, probs=False, seed=seed, lr=lr, gamma=gamma, lam=lam, max_norm=max_norm,
+             cfg=dict(eps_clip=eps_clip, dual_clip=dual_clip, vf_coef=vf_coef, ent_coef=ent_coef, value_clip=bool(value_clip),
+                      adv_norm=bool(adv_norm)))
+    for k in ("W1", "b1", "W2", "b2", "Wa", "ba", "Wv", "bv", "log_sigma"):
+        c[k] = g[pre + k]
+        c["after_" + k] = g[pre + "after_" + k]
+    for k in ("obs", "act", "rew", "term", "trunc", "obs_next", "indices", "v_s", "returns", "adv", "logp_old",
+              "loss_seq", "clip_seq", "vf_seq", "ent_seq", "fwd_mu", "fwd_sigma", "fwd_value"):
+        c[k] = g[pre + k]
+    for a in ("", "after_"):
+        c[a + "W3"] = np.concatenate([c[a + "Wa"], c[a + "Wv"]], 0)
+        c[a + "b3"] = np.concatenate([c[a + "ba"], c[a + "bv"]], 0)
+    B = R * T
+    assert np.array_equal(c["indices"], np.arange(B))
+    em = lambda a: np.swapaxes(a, 0, 1).reshape(B, *a.shape[2:])  # noqa: E731  [T][R] -> env-major flat
+    c["flat"] = {k: em(c[k]) for k in ("obs", "act", "rew", "term", "trunc", "obs_next")}
+    last = np.arange(R) * T + T - 1
+    done = c["flat"]["term"] | c["flat"]["trunc"]
+    c["unfinished"] = last[~done[last]]
+    rs = np.random.RandomState(seed)
+    c["orders"] = [rs.permutation(B) for _ in range(repeat)]
+    return c
+
+
 def load_reinforce(g, ci):
     pre = f"p{ci}_"
     R, T, O, H, nA, bs, repeat, std, seed = (int(v) for v in g[pre + "cfg"])

@@ -53,7 +53,7 @@ class TsmNet(C.Structure):
         ("in_dim", C.c_int32), ("hidden", C.c_int32), ("out_dim", C.c_int32), ("n_act", C.c_int32),
         ("value_index", C.c_int32), ("engine", C.c_int32), ("n_params", c_i64),
         ("params", c_vp), ("grads", c_vp), ("adam_m", c_vp), ("adam_v", c_vp), ("adam_step", c_vp),
-        ("tc_image", c_vp), ("x_scratch", c_vp), ("x_scratch_bytes", c_i64), ("probs_param", C.c_int32),
+        ("tc_image", c_vp), ("x_scratch", c_vp), ("x_scratch_bytes", c_i64), ("probs_param", C.c_int32), ("n_sigma", C.c_int32),
     ]
 
 
@@ -80,7 +80,7 @@ class TsmPpoBatch(C.Structure):
     _fields_ = [
         ("obs", c_vp), ("act", c_vp), ("adv", c_vp), ("ret", c_vp), ("logp_old", c_vp), ("v_old", c_vp), ("indices", c_vp),
         ("size", c_i64), ("n_rows", c_i64), ("start", c_i64), ("len", c_i64), ("perm_key", C.c_uint64), ("perm_n", c_i64),
-        ("records", c_vp), ("slots", c_vp),
+        ("records", c_vp), ("slots", c_vp), ("act_f", c_vp),
     ]
 
 

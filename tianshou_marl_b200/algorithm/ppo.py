@@ -91,6 +91,62 @@ class DiscreteActorPolicy:
     __call__ = forward
 
 
+class ContinuousActorPolicy(DiscreteActorPolicy):
+    """ProbabilisticActorPolicy over a Box action space (reinforce.py:118-215) with the reference's standard continuous head:
+    ContinuousActorProbabilistic(unbounded=True, conditioned_sigma=False) (utils/net/continuous.py:196-247) and
+    dist_fn = Independent(Normal(mu, sigma), 1) (test/continuous/test_ppo.py:104-110).  `actor` is an ActorCriticNet(gaussian=True):
+    its n_act outputs are the means, `log_sigma` the state-independent log standard deviations.  forward samples
+    mu + sigma * N(0, 1) (the mean when deterministic_eval and not in a training step); map_action clips / scales like
+    Policy.map_action (algorithm_base.py:255-288, tsm_map_action).  The network pass is the library's forward kernel; the
+    sampling and the log-density are elementwise device ops on its [n, A] output."""
+
+    def __init__(self, *, actor: ActorCriticNet, action_space: Any = None, action_scaling: bool = True,
+                 action_bound_method: str | None = "clip", **kwargs: Any) -> None:
+        if not getattr(actor, "gaussian", False):
+            raise ValueError("ContinuousActorPolicy needs ActorCriticNet(gaussian=True)")
+        super().__init__(actor=actor, action_space=action_space, **kwargs)
+        self._mapper = None
+        if action_space is not None and hasattr(action_space, "low"):
+            from .actions import BoxActionMapper
+
+            self._mapper = BoxActionMapper(action_space.low, action_space.high, action_scaling=action_scaling,
+                                           action_bound_method=action_bound_method, device=actor.device)
+        self._gen = torch.Generator(device=actor.device).manual_seed(int(kwargs.get("seed", 0)))
+
+    def map_action(self, act: Any) -> Any:
+        return act if self._mapper is None else self._mapper.map_action(act)
+
+    @staticmethod
+    def log_prob(mu: torch.Tensor, log_sigma: torch.Tensor, act: torch.Tensor) -> torch.Tensor:
+        """torch.distributions.Normal.log_prob summed over the action dimensions (Independent(..., 1))."""
+        var = (2.0 * log_sigma).exp()
+        return (-((act - mu) ** 2) / (2.0 * var) - log_sigma - 0.9189385332046727).sum(-1)
+
+    def forward(self, batch: Any, state: Any = None, **kwargs: Any) -> Batch:
+        obs = batch.obs if hasattr(batch, "obs") else batch["obs"]
+        if isinstance(obs, Batch):
+            obs = obs["obs"]
+        if not (isinstance(obs, torch.Tensor) and obs.is_cuda):
+            obs = torch.as_tensor(np.ascontiguousarray(obs), dtype=torch.float32, device=self.actor.device)
+        net = self.actor
+        o = net.forward(obs.to(torch.float32).contiguous(), mode="raw")["out"]
+        mu = o[:, : net.n_act]
+        ls = net.view("log_sigma")
+        if self.deterministic_eval and not self.is_within_training_step:
+            act = mu.clone()
+        else:
+            act = mu + ls.exp() * torch.randn(mu.shape, device=mu.device, generator=self._gen)
+        out = Batch()
+        out.__dict__.update(logits=(mu, ls.exp().expand_as(mu)), act=act, state=None, logp=self.log_prob(mu, ls, act))
+        if net.value_index >= 0:
+            out.__dict__["value"] = o[:, net.value_index]
+        out.__dict__["dist"] = (torch.distributions.Independent(torch.distributions.Normal(mu, ls.exp().expand_as(mu)), 1)
+                                if kwargs.get("want_dist") else None)
+        return out
+
+    __call__ = forward
+
+
 class PPO:
     def __init__(self, *, policy: DiscreteActorPolicy, critic: ActorCriticNet | None = None,
                  optim: AdamOptimizerFactory | None = None, eps_clip: float = 0.2, dual_clip: float | None = None,
@@ -257,6 +313,20 @@ class PPO:
             v_s, logp = st["value"], st["logp"]
             next_values(v_s, True)
             _lib.t_stop(tk)
+        elif net.gaussian:
+            # the same single pass for a Gaussian head: the kernel yields [mu | value]; the log-density of the stored float
+            # actions is elementwise (Independent(Normal(mu, sigma), 1).log_prob, ppo.py:157-161)
+            if rows is not None or "act_f" not in st:
+                raise NotImplementedError("Gaussian policies: whole-buffer updates over float action vectors (buffer key act_f)")
+            tk = _lib.t_start("logp_old_forward")
+            raw = net.forward(obs_all, mode="raw")["out"]
+            v_s.view(-1).copy_(raw[:, net.value_index])
+            A_ = net.n_act
+            logp.view(-1).copy_(ContinuousActorPolicy.log_prob(raw[:, :A_], net.view("log_sigma"), st["act_f"].view(-1, A_)))
+            _lib.t_stop(tk)
+            tk = _lib.t_start("critic_forward")
+            next_values(v_s, dedup_ok)
+            _lib.t_stop(tk)
         else:
             # critic(obs) (a2c.py:120-123) and logp_old = log pi(act | obs) (ppo.py:157-161) read the same rows through the
             # same trunk: ONE evaluation pass yields both (the reference runs the network twice)
@@ -338,6 +408,8 @@ class PPO:
         sums.zero_()
         pb = _lib.TsmPpoBatch(obs=P(st["obs"]), act=P(st["act"]), adv=P(ret if self._mc_returns else adv), ret=P(ret), logp_old=P(logp), v_old=P(v_s),
                               indices=None, size=size, n_rows=R, start=start, len=lock_len, perm_key=0, perm_n=0, records=None)
+        if net.gaussian:
+            pb.act, pb.act_f = None, P(st["act_f"])
         if net.engine == "tc":  # one 96-byte record per stored row: the minibatch kernels gather 3 sectors / 1 page per row
             tk = _lib.t_start("pack_records")
             rec = self._buf("records", (size * R, _lib.PPO_RECORD_BYTES), torch.uint8)

@@ -231,5 +231,83 @@ __device__ __forceinline__ RowLoss row_loss(const float (&z)[OUTP], int n_act_in
     return out;
 }
 
+// The same row for a diagonal Gaussian policy with state-independent scale: the reference's ContinuousActorProbabilistic(unbounded
+// = True, conditioned_sigma = False) feeding Independent(Normal(mu, sigma), 1) (utils/net/continuous.py:229-247,
+// test/continuous/test_ppo.py:104-110).  z[0..n_act) = mu, log_sigma[0..n_act) = the actor's sigma_param, a[0..n_act) = the
+// stored action (before map_action).  torch.distributions.Normal: log_prob = -(a - mu)^2 / (2 sigma^2) - log sigma - log sqrt(2 pi),
+// entropy = 0.5 + 0.5 log(2 pi) + log sigma, both summed over the action dimensions.  dz as in row_loss; dls[j] += d(mean loss) /
+// d log_sigma[j] of this row (the caller reduces it over the rows of the minibatch).
+__device__ __forceinline__ RowLoss row_loss_gauss(const float (&z)[OUTP], int n_act, int value_index, const float* __restrict__ a,
+                                                  const float* __restrict__ log_sigma, float adv, float ret, float logp_old, float v_old,
+                                                  float mean, float rstd, const PpoCfg& cfg, float inv_n, float (&dz)[OUTP], float (&dls)[OUTP]) {
+    RowLoss out{0.f, 0.f, 0.f};
+#pragma unroll
+    for (int j = 0; j < OUTP; ++j) dz[j] = 0.f;
+    float lp = 0.f, ent = 0.f;
+    float dmu[OUTP], dsg[OUTP];  // d logp / d mu_j, d logp / d log_sigma_j
+#pragma unroll
+    for (int j = 0; j < OUTP; ++j) {
+        dmu[j] = dsg[j] = 0.f;
+        if (j < n_act) {
+            const float ls = log_sigma[j], sg = expf(ls), var = sg * sg, d = a[j] - z[j];
+            lp += -(d * d) / (2.f * var) - ls - 0.9189385332046727f;  // log sqrt(2 pi)
+            ent += 0.5f + 0.9189385332046727f + ls;                   // 0.5 + 0.5 log(2 pi) + log sigma
+            dmu[j] = d / var;
+            dsg[j] = d * d / var - 1.f;
+        }
+    }
+    float advn = adv;
+    if (cfg.adv_norm) advn = (advn - mean) * rstd;
+    float li, dlp;
+    if (cfg.plain_pg) {
+        li = -lp * advn;
+        dlp = -advn * inv_n;
+    } else {
+        const float ratio = expf(lp - logp_old);
+        const float lo = 1.f - cfg.eps_clip, hi = 1.f + cfg.eps_clip;
+        const float s1 = ratio * advn, s2 = fminf(fmaxf(ratio, lo), hi) * advn;
+        const bool inside = ratio >= lo && ratio <= hi;
+        const float clip1 = fminf(s1, s2);
+        float g_ratio = (inside || s1 < s2) ? advn : 0.f;
+        li = -clip1;
+        if (cfg.dual_clip > 0.f && advn < 0.f) {
+            const float c2 = cfg.dual_clip * advn;
+            if (c2 > clip1) { li = -c2; g_ratio = 0.f; }
+        }
+        dlp = -g_ratio * ratio * inv_n;
+    }
+    out.clip = li;
+    out.ent = ent;
+    const float ec = cfg.ent_coef * inv_n;
+#pragma unroll
+    for (int j = 0; j < OUTP; ++j)
+        if (j < n_act) {
+            dz[j] = dlp * dmu[j];
+            dls[j] += dlp * dsg[j] - ec;
+        }
+    if (value_index >= 0) {
+        float v = 0.f;
+#pragma unroll
+        for (int j = 0; j < OUTP; ++j)
+            if (j == value_index) v = z[j];
+        float vf = (ret - v) * (ret - v), dv = 2.f * (v - ret);
+        if (cfg.value_clip) {
+            const float d = v - v_old;
+            const float vc = v_old + fminf(fmaxf(d, -cfg.eps_clip), cfg.eps_clip);
+            const float vf2 = (ret - vc) * (ret - vc);
+            if (vf2 > vf) {
+                vf = vf2;
+                dv = (d >= -cfg.eps_clip && d <= cfg.eps_clip) ? 2.f * (vc - ret) : 0.f;
+            }
+        }
+        out.vf = vf;
+        const float dvs = cfg.vf_coef * inv_n * dv;
+#pragma unroll
+        for (int j = 0; j < OUTP; ++j)
+            if (j == value_index) dz[j] = dvs;
+    }
+    return out;
+}
+
 }  // namespace ppo
 }  // namespace tsm

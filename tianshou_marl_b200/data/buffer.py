@@ -158,7 +158,15 @@ class VectorReplayBuffer:
                 self._act_dtype = np.asarray(act).dtype
         obs_t = obs_t.reshape(n, -1)
         on_t = self._dev(obs_next, torch.float32).reshape(n, -1) if (obs_next is not None and self._save_obs_next) else None
-        act_t = self._dev(act, torch.int32).reshape(n)
+        # continuous (Box) actions: float vectors per row.  They live in their own time-major array `act_f` [size][rows][A]
+        # (what the Gaussian PPO kernels read, tsm_ppo_batch.act_f); the integer action array then holds zeros.
+        act_f_t = None
+        a_probe = act if isinstance(act, torch.Tensor) else np.asarray(act)
+        if a_probe.ndim >= 2 and (a_probe.dtype.is_floating_point if isinstance(a_probe, torch.Tensor) else np.issubdtype(a_probe.dtype, np.floating)):
+            act_f_t = self._dev(act, torch.float32).reshape(n, -1)
+            act_t = torch.zeros(n, dtype=torch.int32, device=self.device)
+        else:
+            act_t = self._dev(act, torch.int32).reshape(n)
         rew_t = self._dev(rew, torch.float32).reshape(n)
         te_t = self._dev(term, torch.bool).view(torch.uint8).reshape(n) if not (isinstance(term, torch.Tensor) and term.dtype == torch.uint8) else term.reshape(n)
         tr_t = self._dev(trunc, torch.bool).view(torch.uint8).reshape(n) if not (isinstance(trunc, torch.Tensor) and trunc.dtype == torch.uint8) else trunc.reshape(n)
@@ -181,6 +189,11 @@ class VectorReplayBuffer:
         _lib.check(_lib.lib().tsm_buf_add(
             C.byref(self._desc), P(obs_t), P(act_t), P(rew_t), P(te_t), P(tr_t), P(on_t), P(logp_t), P(value_t),
             P(ids_t), n, P(idx), P(ep_ret), P(ep_len), P(ep_start), _lib.stream_ptr()))
+        if act_f_t is not None:
+            A = int(act_f_t.shape[1])
+            if "act_f" not in self._store or self._store["act_f"].shape[2] != A:
+                self._store["act_f"] = torch.zeros(self._size, self.buffer_num, A, dtype=torch.float32, device=self.device)
+            self._store["act_f"].view(-1, A)[(idx % self._size) * self.buffer_num + idx // self._size] = act_f_t
         self._policy_version = None  # generic adds: stored logp / value (if any) are not known to cover every slot
         self._obs_chain = False  # nor is obs[t + 1] known to repeat obs_next[t]
         if buffer_ids is None and self._lockstep_len is not None:
@@ -322,6 +335,11 @@ class VectorReplayBuffer:
                 continue
             v = self._finish(k, g[k], host)
             out.__dict__[k] = v[0] if scalar else v
+        if "act_f" in self._store:  # continuous actions (see add)
+            af = self._store["act_f"]
+            v = af.view(-1, af.shape[2])[(idx % self._size) * self.buffer_num + idx // self._size]
+            v = v.cpu().numpy() if host else v
+            out.__dict__["act"] = v[0] if scalar else v
         if not self._save_obs_next and "obs" in g:
             nxt = self._dev(self.next(idx), torch.int64)
             v = self._finish("obs", self._gather(nxt, ("obs",))["obs"], host)

@@ -26,13 +26,19 @@ MODES = {"raw": 0, "sample": 1, "mode": 2, "eval": 3}
 class ActorCriticNet(nn.Module):
     def __init__(self, in_dim: int, hidden: int = 64, n_act: int = 5, with_value: bool = True, n_value_only: int = 0,
                  device: str | torch.device = "cuda", seed: int | None = None, orthogonal: bool = True,
-                 engine: str = "fp32", softmax_output: bool = False) -> None:
+                 engine: str = "fp32", softmax_output: bool = False, gaussian: bool = False) -> None:
         """engine: "fp32" = exact CUDA-core kernels (csrc/mlp.cu); "tc" = tcgen05 tensor-core kernels with fp16 operands and
         fp32 accumulation (csrc/mlp_tc.cu; hidden 64, in_dim <= 31, out_dim <= 8); "tcw" = the wide tcgen05 engine of the CTDE
         nets (csrc/mlp_tcw.cu; hidden 128, in_dim <= 1023, out_dim <= 16, separate actor / value-only critic)."""
         super().__init__()
         if engine not in ("fp32", "tc", "tcw"):
             raise ValueError("engine must be 'fp32', 'tc' or 'tcw'")
+        # gaussian: the n_act outputs are the means of a diagonal Gaussian and `log_sigma` (n_act more parameters behind b3, zero
+        # initialised) its state-independent log standard deviations: ContinuousActorProbabilistic(unbounded=True,
+        # conditioned_sigma=False) (utils/net/continuous.py:196-247).  Exact fp32 kernels only.
+        if gaussian and (engine != "fp32" or softmax_output or n_value_only):
+            raise ValueError("gaussian=True needs engine 'fp32', an actor head and no softmax_output")
+        self.gaussian = bool(gaussian)
         if engine == "tcw" and (hidden != 128 or with_value and not n_value_only):
             raise ValueError("engine 'tcw' (csrc/mlp_tcw.cu) runs separate hidden-128 nets: an actor (with_value=False) or a value-only critic")
         self.engine = engine
@@ -49,7 +55,8 @@ class ActorCriticNet(nn.Module):
         if self.device.type != "cuda":
             raise _lib.TsmError("ActorCriticNet needs a CUDA device (no CPU fallback)")
         L = _lib.lib()
-        n = int(L.tsm_net_param_count(self.in_dim, self.hidden, self.out_dim))
+        self.n_sigma = self.n_act if self.gaussian else 0
+        n = int(L.tsm_net_param_count(self.in_dim, self.hidden, self.out_dim)) + self.n_sigma
         self.n_params = n
         self.flat = nn.Parameter(torch.zeros(n, dtype=torch.float32, device=self.device))
         self.grads = torch.zeros(n, dtype=torch.float32, device=self.device)
@@ -64,6 +71,8 @@ class ActorCriticNet(nn.Module):
         self.kernel_updates = 0  # optimizer steps taken by kernels (they do not bump flat._version): see param_version
         H, I, O = self.hidden, self.in_dim, self.out_dim
         sizes = [("W1", (H, I)), ("b1", (H,)), ("W2", (H, H)), ("b2", (H,)), ("W3", (O, H)), ("b3", (O,))]
+        if self.n_sigma:
+            sizes.append(("log_sigma", (self.n_sigma,)))
         self._views: dict[str, tuple[int, tuple[int, ...]]] = {}
         off = 0
         for k, shp in sizes:
@@ -97,6 +106,7 @@ class ActorCriticNet(nn.Module):
         xs = getattr(self, "_x_scratch", None)
         d.x_scratch, d.x_scratch_bytes = (xs.data_ptr(), xs.numel()) if xs is not None else (None, 0)
         d.probs_param = int(self.softmax_output)
+        d.n_sigma = int(self.n_sigma)
 
     @property
     def desc(self) -> Any:
