@@ -21,6 +21,7 @@ namespace mlptc {
 using namespace tsm::ppo;
 
 #include "mlp_tc_kernels.cuh"
+#include "mlp_tc_epoch4.cuh"
 
 // ---------------------------------------------------------------------------------------------
 // self test: one GEMM D[128][N] = A * B from caller-prepared shared-memory images and caller-chosen
@@ -48,6 +49,34 @@ __global__ void __launch_bounds__(128) selftest_kernel(SelfArgs a) {
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tmem_base = tmem_base_s;
+    if (a.kind == 3) {
+        // kind 3: FOUR issuing threads (one elected lane per warp) accumulate the same fp16 GEMM 16 times each into ONE TMEM
+        // accumulator, concurrently: D = 64 * A * B if accumulating tcgen05.mma from different threads of a CTA do not race
+        // (the question behind sharing weight-gradient accumulators between tile groups)
+        __shared__ uint64_t bars[4];
+        if (threadIdx.x == 0) { for (int i = 0; i < 4; ++i) tc::mbar_init(&bars[i], 1); tc::fence_barrier_init(); }
+        for (int c = 0; c < a.N; c += 8) {
+            float z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            tc::tmem_st8(tmem_base + ((uint32_t)(warp * 32) << 16) + c, z);
+        }
+        tc::tmem_st_wait();
+        tc::fence_before_sync();
+        __syncthreads();
+        tc::fence_after_sync();
+        if (tc::elect_one()) {
+            const uint32_t idesc = tc::make_idesc_f16(128, a.N, 0, 0, a.a_mn, a.b_mn);
+            for (int rep = 0; rep < 16; ++rep)
+                for (int ks = 0; ks < a.ksteps; ++ks) {
+                    const uint64_t da = tc::make_desc(tc::smem_u32(sA) + ks * a.a_step, a.a_lbo, a.a_sbo);
+                    const uint64_t db = tc::make_desc(tc::smem_u32(sB) + ks * a.b_step, a.b_lbo, a.b_sbo);
+                    tc::mma_f16(tmem_base, da, db, idesc, 1);
+                }
+            tc::commit(&bars[warp]);
+        }
+        __syncwarp();
+        for (int i = 0; i < 4; ++i) tc::mbar_wait(&bars[i], 0);
+        tc::fence_after_sync();
+    } else {
     if (threadIdx.x == 0) {
         const uint32_t idesc = a.kind == 0 ? tc::make_idesc_tf32(128, a.N, a.a_mn, a.b_mn)
                                            : tc::make_idesc_f16(128, a.N, a.a_bf16, a.b_bf16, a.a_mn, a.b_mn);
@@ -61,6 +90,7 @@ __global__ void __launch_bounds__(128) selftest_kernel(SelfArgs a) {
     }
     tc::mbar_wait(&bar, 0);
     tc::fence_after_sync();
+    }
     for (int c = 0; c < a.N; c += 16) {
         float v[16];
         tc::tmem_ld16(tmem_base + ((uint32_t)(warp * 32) << 16) + c, v);
@@ -286,8 +316,8 @@ int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, cons
     if (reinterpret_cast<uintptr_t>(net->grads) & 15) return fail(TSM_ERR_INVALID, "%s: grads must be 16-byte aligned", __func__);
     if (adam.n > (int64_t)mlptc::EP_G_STRIDE) return 1;
     if (mb_size >= (int64_t)1 << 30 || total - (n_mb - 1) * mb_size >= (int64_t)1 << 30) return 1;  // in-minibatch row numbers are 32-bit in the kernel
-    static int coop = -1, occ = 0, hv = mlptc::EP_HV;
-    const size_t smem = mlptc::SM_EP_TOTAL;
+    static int coop = -1, occ = 0, hv = mlptc::EP_HV, groups = 4;
+    static size_t smem = mlptc::SM_EP_TOTAL;
     if (coop < 0) {
         int dev = 0;
         TSM_CUDA(cudaGetDevice(&dev));
@@ -299,9 +329,23 @@ int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, cons
         TSM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, mlptc::tc_ppo_epoch_kernel<1>, mlptc::EP_THREADS, smem));
         TSM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, mlptc::tc_ppo_epoch_kernel<2>, 2 * mlptc::EP_THREADS, smem));
         occ = hv == 1 ? occ1 : occ2;
+        // four tile groups per SM (mlp_tc_epoch4.cuh) unless TSM_TC_EPOCH_GROUPS=2 or TSM_TC_EPOCH_HALVES asks for the two-group kernels
+        if (const char* g = getenv("TSM_TC_EPOCH_GROUPS")) groups = atoi(g) == 2 ? 2 : 4;
+        else if (getenv("TSM_TC_EPOCH_HALVES")) groups = 2;
+        if (groups == 4) {
+            int occ4 = 0;
+            TSM_CUDA(cudaFuncSetAttribute(mlptc::tc_ppo_epoch4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mlptc::G4_TOTAL));
+            TSM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ4, mlptc::tc_ppo_epoch4_kernel, mlptc::G4_THREADS, (size_t)mlptc::G4_TOTAL));
+            if (occ4 >= 1) { occ = occ4; smem = mlptc::G4_TOTAL; } else groups = 2;
+        }
         if (occ > 1) occ = 1;  // one CTA owns the SM's 512 TMEM columns
     }
-    void* const kernel = hv == 1 ? reinterpret_cast<void*>(mlptc::tc_ppo_epoch_kernel<1>) : reinterpret_cast<void*>(mlptc::tc_ppo_epoch_kernel<2>);
+    void* const kernel = groups == 4 ? reinterpret_cast<void*>(mlptc::tc_ppo_epoch4_kernel)
+                         : hv == 1   ? reinterpret_cast<void*>(mlptc::tc_ppo_epoch_kernel<1>)
+                                     : reinterpret_cast<void*>(mlptc::tc_ppo_epoch_kernel<2>);
+    const int cta_threads = groups == 4 ? mlptc::G4_THREADS : hv * mlptc::EP_THREADS;
+    static const bool verbose = getenv("TSM_TC_EPOCH_VERBOSE") != nullptr;
+    if (verbose) fprintf(stderr, "tsm_ppo_epoch: %d tile groups per SM, %d threads per CTA, %zu bytes of shared memory, occupancy %d\n", groups, cta_threads, smem, occ);
     if (!coop || occ < 1) return 1;
     mlptc::TcEpochArgs e{};
     mlptc::TcPpoArgs& a = e.p;
@@ -325,12 +369,14 @@ int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, cons
     e.g_total = reinterpret_cast<float*>(e.q_table + mlptc::EP_Q_WORDS);
     e.n_mb = n_mb; e.mb_size = mb_size; e.total = total; e.mb_stats = mb_stats; e.loss_sums = loss_sums; e.adam = adam;
     const int64_t tiles = ceil_div(n_mb > 1 ? mb_size : total, mlptc::TC_ROWS);
-    const unsigned grid = (unsigned)std::min<int64_t>(ceil_div(tiles, (int64_t)mlptc::TC_GROUPS), (int64_t)sm_count() * occ);
+    // (four groups: one CTA per tile until the SMs run out, so that small minibatches spread over the SMs)
+    unsigned grid = (unsigned)std::min<int64_t>(groups == 4 ? tiles : ceil_div(tiles, (int64_t)groups), (int64_t)sm_count() * occ);
+    if (const char* gmax = getenv("TSM_TC_EPOCH_GRID")) grid = std::max(1u, std::min(grid, (unsigned)atoi(gmax)));  // experiments: fewer CTAs
     CUtensorMap rec_map;
     rc = record_map(batch->records, batch->size * batch->n_rows, &rec_map, __func__);
     if (rc) return rc;
     void* args[] = {&e, &rec_map};
-    const cudaError_t err = cudaLaunchCooperativeKernel(kernel, dim3(grid), dim3(hv * mlptc::EP_THREADS), args, smem, s);
+    const cudaError_t err = cudaLaunchCooperativeKernel(kernel, dim3(grid), dim3(cta_threads), args, smem, s);
     if (err == cudaErrorCooperativeLaunchTooLarge) {
         cudaGetLastError();
         return 1;
@@ -349,7 +395,7 @@ int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, cons
         {
             cudaFuncAttributes fa;
             cudaFuncGetAttributes(&fa, kernel);
-            printf("grid %u x %d threads, occ %d, smem %zu, regs %d\n", grid, hv * mlptc::EP_THREADS, occ, smem, fa.numRegs);
+            printf("grid %u x %d threads, occ %d, smem %zu, regs %d\n", grid, cta_threads, occ, smem, fa.numRegs);
         }
         printf("half-1 prefetch (tile 0): pos/slot %lld gather issue %lld advance %lld slot load issue %lld | start at +%lld of the tile\n", h[3][51] - h[3][50],
                h[3][52] - h[3][51], h[3][53] - h[3][52], h[3][54] - h[3][53], h[3][50] - h[0][0]);
@@ -358,6 +404,21 @@ int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, cons
                    h[row][1] - h[row][25]);
         printf("abs offsets from slot40 (CTA0): tile0 start %lld end %lld | tile1 start %lld end %lld | loop end %lld\n", h[0][0] - h[0][40],
                h[0][23] - h[0][40], h[1][0] - h[0][40], h[1][23] - h[0][40], h[0][41] - h[0][40]);
+        if (groups == 4) {
+            unsigned long long hc[160][8];
+            cudaMemcpyFromSymbol(hc, mlptc::g_trace_cta, sizeof(hc));
+            unsigned long long t0 = ~0ull;
+            for (unsigned c = 0; c < grid; ++c) t0 = hc[c][0] < t0 ? hc[c][0] : t0;
+            printf("minibatch 2, ns after the first CTA's start: CTA: start tiles-done flush-done arrive passed end\n");
+            for (unsigned c = 0; c < grid; c += (grid > 24 ? grid / 24 : 1))
+                printf("  CTA %3u: %5llu %5llu %5llu %5llu %5llu %5llu\n", c, hc[c][0] - t0, hc[c][1] - t0, hc[c][2] - t0, hc[c][3] - t0, hc[c][4] - t0, hc[c][5] - t0);
+            unsigned long long mx[6] = {0, 0, 0, 0, 0, 0};
+            for (unsigned c = 0; c < grid; ++c) for (int k = 0; k < 6; ++k) mx[k] = hc[c][k] - t0 > mx[k] ? hc[c][k] - t0 : mx[k];
+            printf("  max    : %5llu %5llu %5llu %5llu %5llu %5llu\n", mx[0], mx[1], mx[2], mx[3], mx[4], mx[5]);
+            printf("four-group kernel, CTA 0, cycles per minibatch:");
+            for (int k = 1; k < 16 && h[1][k] > 0; ++k) printf(" %lld", h[1][k] - h[1][k - 1]);
+            printf("\n");
+        }
         for (int row = 0; row < 4; row += 2)
             printf("epoch row %d (minibatch 2): tiles %lld flush %lld grid-barrier %lld rank-exchange %lld norm %lld adam %lld clear+publish %lld | total %lld\n",
                    row, h[row][41] - h[row][40], h[row][42] - h[row][41], h[row][43] - h[row][42], h[row][48] - h[row][43], h[row][44] - h[row][48],
