@@ -304,7 +304,6 @@ __global__ void __launch_bounds__(G4_THREADS, 1) tc_ppo_epoch4_kernel(TcEpochArg
             n_ok = advance(nm, nt);
             need_issue = n_ok;
             const bool same_mb = n_ok && nm == (int)m;
-            if (n_ok) sl_next = slot_at(nm, nt);
             TRACE(trow, 1);
             g4_sync_for_mma(grp);  // X complete; every thread is past its reads of the staging rows (= H1)
             TRACE(trow, 2);
@@ -315,6 +314,7 @@ __global__ void __launch_bounds__(G4_THREADS, 1) tc_ppo_epoch4_kernel(TcEpochArg
                     tc::mma_f16(dacc, desc_act_k(sb4, G4_X, ks), desc_w_k(wb4, G4_W1, TC_H, ks), ID64, ks > 0);
                 tc::commit(bar);
             }
+            if (n_ok) sl_next = slot_at(nm, nt);  // (the load's issue stalls on address translation: inside the wait for layer 1)
             TRACE(trow, 3);
             wait_mma();
             TRACE(trow, 4);
