@@ -108,14 +108,14 @@ class Workload:
         if dom == "ppo_epoch":
             # algorithmic FLOPs fwd + 2x bwd = 33.8 kFLOP/row, algorithmic bytes = one 96-byte record per row (tc engine) or
             # 4*O + 20 gathered bytes (fp32 engine).  tc engine, uniform minibatches: ONE persistent launch (tc_ppo_epoch_kernel)
-            # per epoch = per stage call, optimizer steps and grid barriers inside; fp32 engine: a launch pair per minibatch.
+            # per epoch = per stage call, optimizer steps and grid barriers inside (mlp_tc_epoch4.cuh); fp32 engine: a launch pair per minibatch.
             persistent = self.args.engine == "tc" and B % self.args.batch_size == 0
             rows = B if persistent else min(self.args.batch_size, B)
             t = stages[dom]["launch_ms"] * 1e-3 / (1 if persistent else self.n_mb)
             flop = 3.0 * fwd_flop * rows
             ach = flop / t / 1e12
             rec_bytes = 96.0 if self.args.engine == "tc" else 4.0 * O + 20.0
-            out.update({"kernel": "tc_ppo_epoch_kernel" if persistent else "ppo_minibatch_kernel",
+            out.update({"kernel": "tc_ppo_epoch4_kernel" if persistent else "ppo_minibatch_kernel",
                         "bound": "tensor", "achieved": ach, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach / tf_peak,
                         # dram__bytes_read.sum + dram__bytes_write.sum of one tc_ppo_epoch_kernel launch over 25 165 824 rows,
                         # profiles/r02_ncu_full_epoch.csv (ncu --set full; records at a 128-byte pitch: 1.38x the 96 algorithmic
@@ -124,8 +124,8 @@ class Workload:
                         "flop_per_unit": 3.0 * fwd_flop, "bytes_per_unit": rec_bytes, "units_per_launch": rows,
                         "launch_us": t * 1e6, "minibatch_us": stages[dom]["launch_ms"] * 1e3 / self.n_mb,
                         "hbm_gbs": rec_bytes * rows / t / 1e9,
-                        "note": "engine=%s; latency bound: per minibatch two rounds of 128-row tiles per SM tile group (5 dependent "
-                                "tcgen05 GEMM stages + loss each), gradient flush, one grid barrier, optimizer step in every CTA; "
+                        "note": "engine=%s; latency bound: per minibatch one round of three or four 128-row tiles per SM (four tile groups, "
+                                "5 dependent tcgen05 GEMM stages + loss each), gradient flush, one grid barrier, optimizer step in every CTA; "
                                 "%d minibatches per launch" % (self.args.engine, self.n_mb if persistent else 1)})
         elif dom in ("policy_forward", "critic_forward", "logp_old_forward"):
             flop = fwd_flop * units[dom]
