@@ -627,7 +627,9 @@ int tsm_collect_lockstep_groups(const tsm_net* const* nets, const int64_t* const
 /* tcgen05 self test (tests only): D[128][n] = A * B with A / B given as shared-memory images
  * (float32 words, copied verbatim to smem) and explicit descriptor fields
  * h_desc = {a_lbo, a_sbo, a_kstep_bytes, b_lbo, b_sbo, b_kstep_bytes}; kind::tf32, M = 128,
- * `ksteps` MMAs of K = 8 (tf32) or 16 (f16/bf16).  Pins the operand-layout semantics csrc/mlp_tc.cu relies on. */
+ * `ksteps` MMAs of K = 8 (tf32) or 16 (f16/bf16).  Pins the operand-layout semantics csrc/mlp_tc.cu relies on.
+ * kind 0: tf32, 1: f16 / bf16, 3: the f16 GEMM accumulated 16 times by each of FOUR concurrently issuing threads into one
+ * accumulator (D = 64 A B): accumulating tcgen05.mma from different threads of a CTA do not race (tools/tc_shared_acc_probe.py). */
 int tsm_tc_selftest(const float* a_img, int a_floats, const float* b_img, int b_floats, const uint32_t* h_desc,
                     int a_mn_major, int b_mn_major, int n, int ksteps, int kind /*0 tf32 (K=8), 1 f16 (K=16)*/, int a_bf16,
                     int b_bf16, float* d_out, tsm_stream_t stream);

@@ -415,6 +415,12 @@ int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, cons
             unsigned long long mx[6] = {0, 0, 0, 0, 0, 0};
             for (unsigned c = 0; c < grid; ++c) for (int k = 0; k < 6; ++k) mx[k] = hc[c][k] - t0 > mx[k] ? hc[c][k] - t0 : mx[k];
             printf("  max    : %5llu %5llu %5llu %5llu %5llu %5llu\n", mx[0], mx[1], mx[2], mx[3], mx[4], mx[5]);
+            unsigned long long hg[4][8];
+            cudaMemcpyFromSymbol(hg, mlptc::g_trace_grp, sizeof(hg));
+            printf("CTA 0, groups (ns after the first CTA's start): tile start, records taken, last product issued, products done, all groups done, staged, flushed\n");
+            for (int g = 0; g < 4; ++g)
+                printf("  group %d: %5llu %5llu %5llu %5llu %5llu %5llu %5llu\n", g, hg[g][0] - t0, hg[g][1] - t0, hg[g][2] - t0, hg[g][3] - t0, hg[g][4] - t0,
+                       hg[g][5] - t0, hg[g][6] - t0);
             printf("four-group kernel, CTA 0, cycles per minibatch:");
             for (int k = 1; k < 16 && h[1][k] > 0; ++k) printf(" %lld", h[1][k] - h[1][k - 1]);
             printf("\n");

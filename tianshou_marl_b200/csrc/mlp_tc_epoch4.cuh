@@ -135,8 +135,11 @@ __device__ __forceinline__ void g4_epilogue_mask_inplace(unsigned char* smem, ui
 __device__ unsigned long long g_trace_cta[160][8];  // globaltimer (ns) stamps of every CTA in minibatch 2
 __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 #define TRACE_CTA(m, k) do { if (threadIdx.x == 0 && (m) == 2 && blockIdx.x < 160) g_trace_cta[blockIdx.x][k] = gtime(); } while (0)
+__device__ unsigned long long g_trace_grp[4][8];  // the four groups of CTA 0 in minibatch 2
+#define TRACE_GRP(m, k) do { if ((threadIdx.x & 127) == 0 && (m) == 2 && blockIdx.x == 0) g_trace_grp[threadIdx.x >> 7][k] = gtime(); } while (0)
 #else
 #define TRACE_CTA(m, k) do { } while (0)
+#define TRACE_GRP(m, k) do { } while (0)
 #endif
 
 __global__ void __launch_bounds__(G4_THREADS, 1) tc_ppo_epoch4_kernel(TcEpochArgs e, const __grid_constant__ CUtensorMap rec_map) {
@@ -295,6 +298,7 @@ __global__ void __launch_bounds__(G4_THREADS, 1) tc_ppo_epoch4_kernel(TcEpochArg
             const bool valid = (int64_t)tile * TC_ROWS + r < mb_len;
             [[maybe_unused]] const int trow = (erow >= 0 && it < 2) ? erow + (int)it : -1;
             TRACE(trow, 0);
+            TRACE_GRP(m, 0);
             if (gw_pending) { wait_gw(); gw_pending = false; }  // (only when the gather of this tile could not be issued earlier)
             RowScalars d;
             g4_gather_take(smem, valid, rphase, d);
@@ -305,6 +309,7 @@ __global__ void __launch_bounds__(G4_THREADS, 1) tc_ppo_epoch4_kernel(TcEpochArg
             need_issue = n_ok;
             const bool same_mb = n_ok && nm == (int)m;
             TRACE(trow, 1);
+            TRACE_GRP(m, 1);
             g4_sync_for_mma(grp);  // X complete; every thread is past its reads of the staging rows (= H1)
             TRACE(trow, 2);
             // ---- layer 1 ----
@@ -421,6 +426,7 @@ __global__ void __launch_bounds__(G4_THREADS, 1) tc_ppo_epoch4_kernel(TcEpochArg
             }
             gw_pending = true;
             TRACE(trow, 23);
+            TRACE_GRP(m, 2);
             if (same_mb) {  // more tiles of this minibatch for this group (minibatch > 4 tiles per SM): the gather waits for H1
                 wait_gw();
                 gw_pending = false;
@@ -452,9 +458,11 @@ __global__ void __launch_bounds__(G4_THREADS, 1) tc_ppo_epoch4_kernel(TcEpochArg
             if (r == 0) s_has[grp] = it > 0;
         }
         if (gw_pending) { wait_gw(); gw_pending = false; }  // this group's weight-gradient MMAs have completed
+        TRACE_GRP(m, 3);
         tc::fence_before_sync();
         __syncthreads();  // ... and so have every group's
         tc::fence_after_sync();
+        TRACE_GRP(m, 4);
         const bool any = (s_has[0] | s_has[1] | s_has[2] | s_has[3]) != 0;
         if (any) {
             // staging copy (fp32, flat gradient layout, W2 block XOR-swizzled: stage_pos4) in group 0's H2 + H1.  Lanes 0..63:
@@ -488,6 +496,7 @@ __global__ void __launch_bounds__(G4_THREADS, 1) tc_ppo_epoch4_kernel(TcEpochArg
             tc::fence_before_sync();
             __syncthreads();
             tc::fence_after_sync();
+            TRACE_GRP(m, 5);
             {   // the accumulators restart at zero for the next minibatch (their columns were all read above)
                 float z8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
@@ -521,6 +530,7 @@ __global__ void __launch_bounds__(G4_THREADS, 1) tc_ppo_epoch4_kernel(TcEpochArg
         }
         TRACE(erow, 42);
         TRACE_CTA(m, 2);
+        TRACE_GRP(m, 6);
         // ---- grid barrier with the cross-rank gradient exchange folded into it (tc_ppo_epoch_kernel's, see there) ----
         uint2 Q[OPT];  // (in flight across the barrier)
 #pragma unroll
