@@ -359,3 +359,20 @@ def test_update_large_matches_reference(golden, ci, engine):
     for k, w in (("v_s", "v_s"), ("returns", "ret"), ("adv", "adv"), ("logp_old", "logp_old")):
         assert np.abs(em(alg._work[w])[si] - c[k]).max() < tol["pre_abs"], (k, np.abs(em(alg._work[w])[si] - c[k]).max())
     _check_against_reference(c, net, alg, tol)
+
+
+@pytest.mark.parametrize("env", [{"TSM_TC_EPOCH_GROUPS": "2"}, {"TSM_TC_EPOCH_GROUPS": "2", "TSM_TC_EPOCH_HALVES": "1"}])
+def test_two_group_epoch_kernels_still_agree(env):
+    """The default persistent kernel keeps four tile groups per SM (mlp_tc_epoch4.cuh); the two-group kernels (two threads per row,
+    and the round-1 shape with one) stay selectable.  The choice is read once per process, so they run in a child process:
+    the chain-agreement and reference-fixture tests of this file under the given environment."""
+    import os
+    import subprocess
+    import sys
+
+    e = dict(os.environ)
+    e.update(env)
+    r = subprocess.run([sys.executable, "-m", "pytest", __file__, "-q", "-x", "-k", "launch_chain_agree or update_tc_matches_reference"],
+                       env=e, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-1000:]
+    assert " passed" in r.stdout
