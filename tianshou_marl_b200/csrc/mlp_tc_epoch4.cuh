@@ -177,7 +177,7 @@ __global__ void __launch_bounds__(G4_THREADS, 1) tc_ppo_epoch4_kernel(TcEpochArg
         if ((threadIdx.x >> 5) == 0) tc::tmem_alloc(tmem_slot, 512);
         if (r == 0) {
             tc::mbar_init(bar, 1);
-            tc::mbar_init(bar + 1, 1);
+            tc::mbar_init(bar + 1, 4);  // every warp of the group issues (and commits) a quarter of each weight-gradient product
             tc::mbar_init(bar + 3, 1);
             tc::fence_barrier_init();
         }
@@ -219,7 +219,8 @@ __global__ void __launch_bounds__(G4_THREADS, 1) tc_ppo_epoch4_kernel(TcEpochArg
     const uint32_t dacc = tmem + G4_TM_GRP * grp;        // the same accumulator as an MMA destination
     const uint32_t sb4 = __shfl_sync(0xffffffffu, tc::smem_u32(smem) >> 4, 0);      // group map, descriptor units
     const uint32_t wb4 = __shfl_sync(0xffffffffu, tc::smem_u32(smem_all) >> 4, 0);  // CTA map (weight image)
-    const bool w0 = __shfl_sync(0xffffffffu, (int)((threadIdx.x >> 5) & 3), 0) == 0;
+    const int wq = __shfl_sync(0xffffffffu, (int)((threadIdx.x >> 5) & 3), 0);  // warp of the group (a broadcast: uniform for the compiler)
+    const bool w0 = wq == 0;
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem + G4_BAR);
     uint32_t phase = 0;
     auto wait_mma = [&]() { tc::mbar_wait(bar, phase); phase ^= 1; tc::fence_after_sync(); };
@@ -387,11 +388,16 @@ __global__ void __launch_bounds__(G4_THREADS, 1) tc_ppo_epoch4_kernel(TcEpochArg
             if (tc_issuer(w0)) {
                 tc::mma_f16(dacc, desc_act_k(sb4, G4_G, 0), desc_w_mn(wb4, G4_W3, TC_OF, 0), ID_DH, 0);
                 tc::commit(bar);
+            }
+            // The weight-gradient products accumulate (order does not matter) and accumulating MMAs of different threads do not
+            // race: every warp issues two of the eight K-steps, so no warp is late for the epilogue by a whole product's issue.
+            if (tc::elect_one()) {
 #pragma unroll
-                for (int ks = 0; ks < TC_ROWS / 16; ++ks)
-                    tc::mma_f16(tmem + G4_TM_GW3, desc_act_mn(sb4, G4_H2, ks), desc_act_mn(sb4, G4_G, ks), ID_G16, 1);
+                for (int k2 = 0; k2 < 2; ++k2)
+                    tc::mma_f16(tmem + G4_TM_GW3, desc_act_mn(sb4, G4_H2, 2 * wq + k2), desc_act_mn(sb4, G4_G, 2 * wq + k2), ID_G16, 1);
                 tc::commit(bar + 1);
             }
+            __syncwarp();
             TRACE(trow, 15);
             wait_mma();
             TRACE(trow, 16);
@@ -405,11 +411,14 @@ __global__ void __launch_bounds__(G4_THREADS, 1) tc_ppo_epoch4_kernel(TcEpochArg
                 for (int ks = 0; ks < TC_H / 16; ++ks)
                     tc::mma_f16(dacc, desc_act_k(sb4, G4_H2, ks), desc_w_mn(wb4, G4_W2, TC_H, ks), ID_DH, ks > 0);
                 tc::commit(bar);
+            }
+            if (tc::elect_one()) {
 #pragma unroll
-                for (int ks = 0; ks < TC_ROWS / 16; ++ks)
-                    tc::mma_f16(tmem + G4_TM_GW2, desc_act_mn(sb4, G4_H2, ks), desc_act_mn(sb4, G4_H1, ks), ID_G64, 1);
+                for (int k2 = 0; k2 < 2; ++k2)
+                    tc::mma_f16(tmem + G4_TM_GW2, desc_act_mn(sb4, G4_H2, 2 * wq + k2), desc_act_mn(sb4, G4_H1, 2 * wq + k2), ID_G64, 1);
                 tc::commit(bar + 1);
             }
+            __syncwarp();
             TRACE(trow, 19);
             wait_mma();
             TRACE(trow, 20);
@@ -418,12 +427,13 @@ __global__ void __launch_bounds__(G4_THREADS, 1) tc_ppo_epoch4_kernel(TcEpochArg
             g4_sync_for_mma(grp);
             TRACE(trow, 22);
             // ---- [D2;D1]^T [X|1] ----
-            if (tc_issuer(w0)) {
+            if (tc::elect_one()) {
 #pragma unroll
-                for (int ks = 0; ks < TC_ROWS / 16; ++ks)
-                    tc::mma_f16(tmem + G4_TM_GW1, desc_act_mn(sb4, G4_H2, ks), desc_act_mn(sb4, G4_X, ks), ID_G32, 1);
+                for (int k2 = 0; k2 < 2; ++k2)
+                    tc::mma_f16(tmem + G4_TM_GW1, desc_act_mn(sb4, G4_H2, 2 * wq + k2), desc_act_mn(sb4, G4_X, 2 * wq + k2), ID_G32, 1);
                 tc::commit(bar + 1);
             }
+            __syncwarp();
             gw_pending = true;
             TRACE(trow, 23);
             TRACE_GRP(m, 2);
