@@ -421,6 +421,8 @@ int tc_ppo_epoch_persistent(const tsm_net* net, const tsm_ppo_batch* batch, cons
             for (int g = 0; g < 4; ++g)
                 printf("  group %d: %5llu %5llu %5llu %5llu %5llu %5llu %5llu\n", g, hg[g][0] - t0, hg[g][1] - t0, hg[g][2] - t0, hg[g][3] - t0, hg[g][4] - t0,
                        hg[g][5] - t0, hg[g][6] - t0);
+            printf("CTA 0 group 0, tile 0 (cycles): tile start -> records landed %lld -> taken %lld -> bookkeeping %lld\n", h[0][26] - h[0][0], h[0][27] - h[0][26], h[0][1] - h[0][27]);
+            printf("CTA 0 group 0 (cycles): last product issued -> flush prologue done %lld -> products done %lld\n", h[0][49] - h[0][41], h[0][50] - h[0][49]);
             printf("four-group kernel, CTA 0, cycles per minibatch:");
             for (int k = 1; k < 16 && h[1][k] > 0; ++k) printf(" %lld", h[1][k] - h[1][k - 1]);
             printf("\n");

@@ -302,7 +302,12 @@ __global__ void __launch_bounds__(G4_THREADS, 1) tc_ppo_epoch4_kernel(TcEpochArg
             TRACE_GRP(m, 0);
             if (gw_pending) { wait_gw(); gw_pending = false; }  // (only when the gather of this tile could not be issued earlier)
             RowScalars d;
+#ifdef TSM_TC_TRACE
+            tc::mbar_wait(reinterpret_cast<uint64_t*>(smem + G4_BAR) + 3, rphase);  // (stamp only: the wait inside the take then returns at once)
+            TRACE(trow, 26);
+#endif
             g4_gather_take(smem, valid, rphase, d);
+            TRACE(trow, 27);
             const float d_adv = d.adv, d_ret = d.ret, d_logp_old = d.logp_old, d_v_old = d.v_old;
             const int d_act = d.act;
             // the group's next tile: its slot now (the load's issue stalls on address translation), its gather once H1 is free
@@ -467,7 +472,9 @@ __global__ void __launch_bounds__(G4_THREADS, 1) tc_ppo_epoch4_kernel(TcEpochArg
             }
             if (r == 0) s_has[grp] = it > 0;
         }
+        TRACE(erow, 49);
         if (gw_pending) { wait_gw(); gw_pending = false; }  // this group's weight-gradient MMAs have completed
+        TRACE(erow, 50);
         TRACE_GRP(m, 3);
         tc::fence_before_sync();
         __syncthreads();  // ... and so have every group's

@@ -19,7 +19,8 @@ if not os.environ.get("NO_SLOTS"):
     slots = torch.empty(B, dtype=torch.int32, device=dev); b.slots = P(slots)
     _lib.check(L.tsm_ppo_slot_table(C.byref(b), 0, B, st))
 n_mb = 16
-bounds = np.arange(0, 65536 * (n_mb + 1), 65536, dtype=np.int64); hb = bounds.ctypes.data_as(C.c_void_p)
+MB = int(os.environ.get("TRACE_MB", "65536"))
+bounds = np.arange(0, MB * (n_mb + 1), MB, dtype=np.int64); hb = bounds.ctypes.data_as(C.c_void_p)
 for i in range(3):
     if i == 2: os.environ["TSM_TC_TRACE_DUMP"] = "1"
     _lib.check(L.tsm_ppo_epoch(net.desc, C.byref(b), C.byref(cfg), hb, n_mb, None, 3e-4, 0.9, 0.999, 1e-8, 0.5, None, st))
