@@ -287,7 +287,7 @@ def c5_measure(steps: int, warmup: int) -> dict:
     import torch
 
     from tianshou_marl_b200 import _lib
-    from tianshou_marl_b200.algorithm import gae_time_major
+    from tianshou_marl_b200.algorithm import gae_flat, gae_time_major
     from tianshou_marl_b200.data import Batch, VectorReplayBuffer
 
     torch.cuda.set_device(0)
@@ -309,11 +309,14 @@ def c5_measure(steps: int, warmup: int) -> dict:
     v_s, v_n = torch.randn(T, R, device="cuda", generator=g), torch.randn(T, R, device="cuda", generator=g)
     adv, ret = torch.empty_like(v_s), torch.empty_like(v_s)
     ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
-    tot = {"add": 0.0, "gae": 0.0, "sample_indices": 0.0}
+    tot = {"add": 0.0, "gae": 0.0, "sample_indices": 0.0, "gae_flat": 0.0}
+    # what compute_episodic_return passes for a flat index list: no segment length, the unfinished slots as force_end
+    fe = torch.zeros(T * R, dtype=torch.uint8, device="cuda")
+    fe[T - 1::T] = 1
 
     def step(timed: bool) -> None:
         buf.reset()
-        e = [ev() for _ in range(4)]
+        e = [ev() for _ in range(5)]
         e[0].record()
         for t in range(T):
             buf.add(Batch(obs=obs, act=act, rew=rew, terminated=term, truncated=trunc[t % 25], obs_next=obs2))
@@ -323,10 +326,13 @@ def c5_measure(steps: int, warmup: int) -> dict:
         e[2].record()
         idx = buf.sample_indices(0)
         e[3].record()
+        # the same 134 M elements as one flat array of 128-element episodes (the layout compute_episodic_return receives)
+        gae_flat(v_s.view(-1), v_n.view(-1), st["rew"].view(-1), st["terminated"].view(-1), st["truncated"].view(-1), fe, 0, 0.99, 0.95)
+        e[4].record()
         torch.cuda.synchronize()
         assert idx.numel() == T * R
         if timed:
-            for k, (a, b) in zip(tot, ((0, 1), (1, 2), (2, 3))):
+            for k, (a, b) in zip(tot, ((0, 1), (1, 2), (2, 3), (3, 4))):
                 tot[k] += e[a].elapsed_time(e[b])
 
     for _ in range(warmup):
@@ -337,17 +343,23 @@ def c5_measure(steps: int, warmup: int) -> dict:
     n = T * R
     ms = {k: v / steps for k, v in tot.items()}
     gbs = {"gae": GAE_BYTES_PER_ELT * n / ms["gae"] / 1e6, "add": (2 * 4 * O + 4 + 4 + 3) * n / ms["add"] / 1e6,
-           "sample_indices": 8 * n / ms["sample_indices"] / 1e6}
+           "sample_indices": 8 * n / ms["sample_indices"] / 1e6, "gae_flat": (GAE_BYTES_PER_ELT + 1) * n / ms["gae_flat"] / 1e6,
+           "add_moved": (2 * (2 * 4 * O + 11) + 80) * n / ms["add"] / 1e6}
     line = {"metric": "GAE GB/s vs HBM peak", "value": gbs["gae"], "unit": "GB/s", "n_gpus": 1, "steps": steps, "warmup": warmup,
             "ms_per_step": sum(ms.values()), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 I/O, f64 carry",
             "data": "synthetic", "config": {"workload": "C5 GAE + buffer add/sample microbench T=128 rows=1048576 gamma=0.99 lambda=0.95 obs_dim=18",
                                             "l2": "inputs larger than L2: 2.95 GB per GAE call, 20.8 GB per 128 adds"},
-            "clocks": clk.summary(), "gpu_launches": steps * (1 + 2 * T + 1 + 1),
+            "clocks": clk.summary(), "gpu_launches": steps * (1 + 2 * T + 1 + 1 + 1),
             "stages_ms": ms,
             "roofline": {"kernel": "gae_tm_kernel", "bound": "hbm", "achieved": gbs["gae"], "peak": hbm_peak, "peak_source": src, "unit": "GB/s",
                          "frac": gbs["gae"] / hbm_peak, "traffic": None, "bytes_per_unit": GAE_BYTES_PER_ELT, "units_per_launch": n,
                          "buffer_add": {"achieved": gbs["add"], "frac": gbs["add"] / hbm_peak, "bytes_per_unit": 2 * 4 * O + 11,
-                                        "note": "128 VectorReplayBuffer.add calls of 1M rows (payload copy + counters kernel each)"},
+                                        "moved_bytes_per_unit": 2 * (2 * 4 * O + 11) + 80, "moved_frac": gbs["add_moved"] / hbm_peak,
+                                        "note": "128 VectorReplayBuffer.add calls of 1M rows (payload copy + counters kernel each); bytes_per_unit is "
+                                                "SURVEY 8(d)'s write-only figure, moved_bytes_per_unit adds the reads of the caller's arrays and the "
+                                                "five 8-byte per-row counters read and written"},
+                         "gae_flat": {"kernel": "gae_flat_kernel", "achieved": gbs["gae_flat"], "frac": gbs["gae_flat"] / hbm_peak,
+                                      "bytes_per_unit": GAE_BYTES_PER_ELT + 1, "note": "flat layout with force_end flags, output allocation included"},
                          "sample_indices": {"achieved": gbs["sample_indices"], "frac": gbs["sample_indices"] / hbm_peak, "bytes_per_unit": 8}}}
     del buf, obs, obs2, v_s, v_n, adv, ret
     torch.cuda.empty_cache()
@@ -477,7 +489,7 @@ def main() -> None:
             c5 = c5_measure(2, 3)
             r5 = c5["roofline"]
             line["roofline"]["c5"] = {"gae": {"achieved": r5["achieved"], "frac": r5["frac"], "unit": "GB/s", "bytes_per_unit": r5["bytes_per_unit"]},
-                                      "buffer_add": r5["buffer_add"], "sample_indices": r5["sample_indices"], "peak": r5["peak"],
+                                      "gae_flat": r5["gae_flat"], "buffer_add": r5["buffer_add"], "sample_indices": r5["sample_indices"], "peak": r5["peak"],
                                       "workload": c5["config"]["workload"], "stages_ms": c5["stages_ms"]}
         if not args.no_cpu_baseline and world == 1 and args.workload == "c2":
             line.update(cpu_baseline_leg(args))

@@ -75,10 +75,10 @@ int tsm_gae_flat(const void* v_s, const void* v_next, const void* rew, int io_is
                  void* adv_out, void* ret_out,
                  void* workspace, size_t workspace_bytes, tsm_stream_t stream);
 
-/* tsm_gae_flat without a workspace argument and without any allocation: the scratch (tile counter + tile states) is a
+/* tsm_gae_flat without a workspace argument and without any allocation: the scratch (tile states) is a
  * file-scope device array inside the library.  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot call cudaMalloc (CUDA graph capture, serving loops, harnesses that forbid it).  Limit:
- * n <= TSM_GAE_FLAT_STATIC_MAX_N elements (the scratch is 64 + ceil(n_max / 2048) * 32 bytes = 262 208 bytes, held by every
+ * n <= TSM_GAE_FLAT_STATIC_MAX_N elements (the scratch is 64 + ceil(n_max / 1024) * 32 bytes = 524 352 bytes, held by every
  * GPU that loads the library until exit); larger n returns TSM_ERR_INVALID with a message naming the limit.  All calls on
  * one GPU share the array: it is re-initialised on `stream` at the start of every call, and calls that overlap on the GPU
  * (different streams) race -- serialise them.  Same arguments, arithmetic and results as tsm_gae_flat otherwise. */

@@ -21,8 +21,12 @@
 namespace tsm {
 namespace gae {
 
+// 128 threads x 8 elements per tile and ten CTAs per SM (48 registers, 48 bytes of spills): the kernel is one dependent chain
+// per tile (loads -> scan -> neighbour state -> stores), so what matters is how many tiles an SM holds.  Measured at 134 M
+// elements: 256 threads / 3 CTAs per SM 4.07 TB/s, 256 / 4 4.74, 128 / 8 4.92, 128 / 10 5.08 (0.78 of the measured HBM peak),
+// 128 / 12 3.99 (spills), 64 / 20 4.87.
 #ifndef TSM_GAE_THREADS
-#define TSM_GAE_THREADS 256
+#define TSM_GAE_THREADS 128
 #endif
 #ifndef TSM_GAE_ITEMS
 #define TSM_GAE_ITEMS 8
@@ -106,22 +110,23 @@ __device__ __forceinline__ void store_items(T* __restrict__ p, int64_t base, int
 
 // T in {float,double}: dtype of v_s, v_next, rew and of both outputs (float64 = the numpy path
 // of the reference, float32 = device-resident rollouts); the carry is float64 either way
+#ifndef TSM_GAE_MIN_BLOCKS
+#define TSM_GAE_MIN_BLOCKS 10
+#endif
 template <typename T>
-__global__ void __launch_bounds__(THREADS) gae_flat_kernel(
+__global__ void __launch_bounds__(THREADS, (sizeof(T) == 8 ? (TSM_GAE_MIN_BLOCKS * 3) / 5 : TSM_GAE_MIN_BLOCKS)) gae_flat_kernel(
     const T* __restrict__ v_s, const T* __restrict__ v_next, const T* __restrict__ rew,
     const uint8_t* __restrict__ term, const uint8_t* __restrict__ trunc, const uint8_t* __restrict__ force_end,
     int64_t n, int64_t seg_len, double gamma, double gl, T* __restrict__ adv_out, T* __restrict__ ret_out,
-    unsigned int* __restrict__ tile_counter, TileState* __restrict__ tiles, int num_tiles) {
-    __shared__ int s_tile;
+    TileState* __restrict__ tiles, int num_tiles) {
     __shared__ Map s_warp[WARPS];
     __shared__ double s_carry;
 
-    // tiles are handed out right-to-left in launch order, so a tile only ever waits on tiles
-    // that already started (forward progress without co-residency assumptions).  (Persistent CTAs that claim the next
-    // tile one iteration ahead were measured slower: 3.80 vs 4.08 TB/s.)
-    if (threadIdx.x == 0) s_tile = num_tiles - 1 - (int)atomicAdd(tile_counter, 1u);
-    __syncthreads();
-    const int tile = s_tile;
+    // Tiles run right to left in block order: a tile only ever waits on tiles of lower block index, and the hardware hands
+    // out the blocks of a one-dimensional grid in increasing index order, so those have started (the assumption CUB's
+    // decoupled look-back makes as well).  Claiming the tile with an atomic counter instead put an L2 round trip in front
+    // of every tile's loads (4.71 against 4.92 TB/s), and persistent CTAs claiming one tile ahead were slower still.
+    const int tile = num_tiles - 1 - (int)blockIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     // the right neighbour started earlier: probe its state now, so that the round trip overlaps this tile's loads
     double nb_incl = 0.0, nb_a = 0.0, nb_b = 0.0;
@@ -400,29 +405,27 @@ extern "C" int tsm_gae_flat(const void* v_s, const void* v_next, const void* rew
     TSM_REQUIRE((reinterpret_cast<uintptr_t>(workspace) % 32) == 0, "workspace 32-byte aligned");
     cudaStream_t s = as_stream(stream);
     const int num_tiles = (int)ceil_div(n, TILE);
-    TSM_CUDA(cudaMemsetAsync(workspace, 0, 64, s));                                                                   // tile counter
     TSM_CUDA(cudaMemsetAsync(reinterpret_cast<char*>(workspace) + 64, 0xFF, tsm_gae_flat_workspace_bytes(n) - 64, s));  // tile states: empty
-    unsigned int* counter = reinterpret_cast<unsigned int*>(workspace);
     TileState* tiles = reinterpret_cast<TileState*>(reinterpret_cast<char*>(workspace) + 64);
     const double gl = gamma * lam;
     if (io_is_f64)
         gae_flat_kernel<double><<<num_tiles, THREADS, 0, s>>>(
             (const double*)v_s, (const double*)v_next, (const double*)rew, terminated, truncated, force_end, n, seg_len,
-            gamma, gl, (double*)adv_out, (double*)ret_out, counter, tiles, num_tiles);
+            gamma, gl, (double*)adv_out, (double*)ret_out, tiles, num_tiles);
     else
         gae_flat_kernel<float><<<num_tiles, THREADS, 0, s>>>(
             (const float*)v_s, (const float*)v_next, (const float*)rew, terminated, truncated, force_end, n, seg_len,
-            gamma, gl, (float*)adv_out, (float*)ret_out, counter, tiles, num_tiles);
+            gamma, gl, (float*)adv_out, (float*)ret_out, tiles, num_tiles);
     TSM_LAUNCH_CHECK();
     return TSM_OK;
 }
 
 // ---------------------------------------------------------------------------------------------
-// tsm_gae_flat_static: the same kernel with its scratch (tile counter + tile states) in a file-scope device array instead
+// tsm_gae_flat_static: the same kernel with its scratch (64 reserved bytes + tile states) in a file-scope device array instead
 // of a caller-provided workspace, for callers that cannot allocate (CUDA graph capture, serving loops).  No counterpart in
 // the reference.  Every GPU that loads the library holds the array until
 // exit.  All calls share it: calls that overlap on one GPU (two streams) race; it is re-initialised on the caller's
-// stream at the start of every call (counter = 0, tile states = 0xFF), so nothing is assumed about its previous contents.
+// stream at the start of every call (tile states = 0xFF), so nothing is assumed about its previous contents.
 constexpr int64_t STATIC_MAX_N = TSM_GAE_FLAT_STATIC_MAX_N;
 constexpr size_t STATIC_BYTES = 64 + (size_t)((STATIC_MAX_N + TILE - 1) / TILE) * sizeof(TileState);
 static __device__ __align__(256) unsigned char g_gae_flat_scratch[STATIC_BYTES];
@@ -465,19 +468,17 @@ extern "C" int tsm_gae_flat_static(const void* v_s, const void* v_next, const vo
     cudaStream_t s = as_stream(stream);
     const int num_tiles = (int)ceil_div(n, TILE);
     const size_t used = 64 + (size_t)num_tiles * sizeof(TileState);
-    TSM_CUDA(cudaMemsetAsync(scratch, 0, 64, s));                                               // tile counter
     TSM_CUDA(cudaMemsetAsync(reinterpret_cast<char*>(scratch) + 64, 0xFF, used - 64, s));       // tile states: empty
-    unsigned int* counter = reinterpret_cast<unsigned int*>(scratch);
     TileState* tiles = reinterpret_cast<TileState*>(reinterpret_cast<char*>(scratch) + 64);
     const double gl = gamma * lam;
     if (io_is_f64)
         gae_flat_kernel<double><<<num_tiles, THREADS, 0, s>>>(
             (const double*)v_s, (const double*)v_next, (const double*)rew, terminated, truncated, force_end, n, seg_len,
-            gamma, gl, (double*)adv_out, (double*)ret_out, counter, tiles, num_tiles);
+            gamma, gl, (double*)adv_out, (double*)ret_out, tiles, num_tiles);
     else
         gae_flat_kernel<float><<<num_tiles, THREADS, 0, s>>>(
             (const float*)v_s, (const float*)v_next, (const float*)rew, terminated, truncated, force_end, n, seg_len,
-            gamma, gl, (float*)adv_out, (float*)ret_out, counter, tiles, num_tiles);
+            gamma, gl, (float*)adv_out, (float*)ret_out, tiles, num_tiles);
     TSM_LAUNCH_CHECK();
     return TSM_OK;
 }
