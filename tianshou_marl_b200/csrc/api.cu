@@ -3,6 +3,7 @@
 
 namespace tsm {
 thread_local char g_err[512] = "";
+thread_local bool g_pdl_hint = false;
 }
 
 extern "C" int tsm_abi_version(void) { return TSM_ABI_VERSION; }

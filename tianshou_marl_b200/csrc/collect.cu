@@ -33,6 +33,8 @@ extern "C" int tsm_collect_lockstep(const tsm_net* net, const tsm_mpe* env, cons
     // its own stream (forked from / joined into the caller's stream), and the GPU overlaps one range's latency-bound
     // tensor-core forward with the other's CUDA-core world step.  Sampling keys use the global row index
     // (tsm_net_forward_range), so the actions are those of the unsplit loop.
+    static const bool pdl_on = !getenv("TSM_COLLECT_NO_PDL");
+    const bool pdl = pdl_on && net && net->engine == 1;
     static const int want_parts = getenv("TSM_COLLECT_STREAMS") ? atoi(getenv("TSM_COLLECT_STREAMS")) : 2;
     constexpr int MAX_PARTS = 4;
     const int64_t E = env->n_envs, A = env->n_agents;
@@ -73,6 +75,9 @@ extern "C" int tsm_collect_lockstep(const tsm_net* net, const tsm_mpe* env, cons
                 TSM_CUDA(cudaMemcpyAsync(obs_slot + r0 * O, ro->carry + r0 * O, sizeof(float) * nr * O, cudaMemcpyDeviceToDevice, ps));
             int rc;
             if (net) {
+                // engine 1's forward starts under the tail of the previous world step of this range (k > 0: the predecessor in
+                // this stream is that launch; before it comes whatever the caller enqueued, e.g. the optimizer's image write)
+                g_pdl_hint = pdl && k > 0 && !in_carry;
                 rc = tsm_net_forward_range(net, obs_slot, r0, nr, mode, seed, counter0 + (uint64_t)k, act_slot,
                                            ro->logp ? ro->logp + slot * R : nullptr,
                                            (ro->value && net->value_index >= 0) ? ro->value + slot * R : nullptr, pst);
@@ -81,11 +86,14 @@ extern "C" int tsm_collect_lockstep(const tsm_net* net, const tsm_mpe* env, cons
                 if (!rc && ro->logp) TSM_CUDA(cudaMemsetAsync(ro->logp + slot * R, 0, sizeof(float) * R, s));
                 if (!rc && ro->value) TSM_CUDA(cudaMemsetAsync(ro->value + slot * R, 0, sizeof(float) * R, s));
             }
+            g_pdl_hint = false;
             if (rc) return rc;
-            // world step + ring counters + episode statistics: one launch
+            // world step + ring counters + episode statistics: one launch (its loads of the world state run under the forward's tail)
+            g_pdl_hint = pdl && net != nullptr;
             rc = tsm_rollout_step(env, buf, act_slot, ro->obs_next + slot * R * O, ro->rew + slot * R, ro->terminated + slot * R,
                                   ro->truncated + slot * R, carry, ro->ep_ret, ro->ep_len, ro->acc, ro->list_ret, ro->list_len,
                                   ro->list_count, ro->list_cap, e0, e1 - e0, pst);
+            g_pdl_hint = false;
             if (rc) return rc;
         }
         len = len + 1 < size ? len + 1 : size;

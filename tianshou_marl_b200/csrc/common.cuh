@@ -54,6 +54,20 @@ static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 // Programmatic dependent launch (sm_90+): a kernel launched with the programmatic-stream-serialization attribute may start
 // while its predecessor in the stream is still running; pdl_wait() blocks until the predecessor has completed and its
 // writes are visible (no-op for a normal launch); pdl_launch_dependents() lets the successor start its prologue.
+// Host side: the lock-step rollout loop (collect.cu) sets g_pdl_hint around the launches whose predecessor in the stream is the
+// other kernel of its forward -> world step chain; launch sites that understand it (tc_net_forward, launch_step) then launch
+// with the attribute.  Everything else launches normally (the device-side calls are no-ops then).
+extern thread_local bool g_pdl_hint;
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(bool pdl, void (*kernel)(KArgs...), unsigned grid, unsigned block, size_t smem, cudaStream_t s, Args&&... args) {
+    cudaLaunchConfig_t lc{};
+    lc.gridDim = dim3(grid); lc.blockDim = dim3(block); lc.dynamicSmemBytes = smem; lc.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = at; lc.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&lc, kernel, static_cast<KArgs>(args)...);
+}
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 

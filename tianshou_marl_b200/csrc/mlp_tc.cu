@@ -210,7 +210,7 @@ int tc_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int6
     }
     const int64_t tiles = ceil_div(n, mlptc::TC_ROWS);
     const unsigned grid = (unsigned)std::min<int64_t>(tiles, (int64_t)sm_count() * 3);
-    mlptc::tc_forward_kernel<<<grid, mlptc::TC_THREADS, smem, s>>>(a);
+    TSM_CUDA(launch_pdl(g_pdl_hint, mlptc::tc_forward_kernel, grid, mlptc::TC_THREADS, smem, s, a));
     TSM_LAUNCH_CHECK();
     return TSM_OK;
 }

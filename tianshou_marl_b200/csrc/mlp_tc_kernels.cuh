@@ -363,6 +363,12 @@ __global__ void __launch_bounds__(TC_THREADS) tc_forward_kernel(TcFwdArgs a) {
     extern __shared__ __align__(1024) unsigned char smem[];
     tc_setup_begin(smem, TM_COLS_FWD);
     TcSetup s = tc_setup_finish(smem, a.image);
+    // Rollout chain (collect.cu): launched with programmatic stream serialization behind the world step that writes this
+    // step's observations, so TMEM allocation, barrier setup and the weight image load above run under that kernel's tail.
+    // The successor (the world step reading the actions) may be scheduled from here on: its own prologue reads state that the
+    // PREVIOUS world step wrote, which has completed once this wait returns.
+    pdl_wait();
+    pdl_launch_dependents();
     const int64_t n_tiles = (a.n + TC_ROWS - 1) / TC_ROWS;
     const int r = threadIdx.x;
     float xr[TC_XF];

@@ -231,9 +231,14 @@ __global__ void __launch_bounds__(THREADS) step_kernel(tsm_mpe e, const int32_t*
     if (is_agent) {
         p = reinterpret_cast<const float2*>(e.pos)[row];
         v = reinterpret_cast<const float2*>(e.vel)[row];
-        a = act[row];
     }
     if (live && j < L) lm = reinterpret_cast<const float2*>(e.lm)[env * L + j];
+    // Rollout chain (collect.cu): launched with programmatic stream serialization behind the policy forward that writes `act`.
+    // The world state loaded above was written by the previous world step, which completed before that forward passed its own
+    // wait (and only then let this kernel be scheduled).  No-ops for a normal launch.
+    pdl_wait();
+    pdl_launch_dependents();
+    if (is_agent) a = act[row];
     const float my_size = agent_size(e, j);
 
     // simple_env._set_action (discrete) + World.apply_action_force
@@ -530,8 +535,8 @@ static int launch_step(const tsm_mpe* e, const int32_t* act, float* obs_next, fl
     static const bool no_stage = getenv("TSM_MPE_NO_STAGE") != nullptr;
     const bool st = stage <= 48 * 1024 - 2048 && (e->obs_dim % 2) == 0 && !no_stage;
 #define TSM_STEP(GG)                                                                                                                          \
-    if (st) step_kernel<GG, TAIL, true><<<grid, THREADS, stage, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t, env0, n_sub); \
-    else step_kernel<GG, TAIL, false><<<grid, THREADS, 0, s>>>(*e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t, env0, n_sub);
+    if (st) TSM_CUDA(launch_pdl(g_pdl_hint, step_kernel<GG, TAIL, true>, grid, THREADS, stage, s, *e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t, env0, n_sub)); \
+    else TSM_CUDA(launch_pdl(g_pdl_hint, step_kernel<GG, TAIL, false>, grid, THREADS, 0, s, *e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t, env0, n_sub));
     switch (G) {
         case 4: TSM_STEP(4) break;
         case 8: TSM_STEP(8) break;
