@@ -254,6 +254,13 @@ int tsm_mpe_step(const tsm_mpe* env, const int32_t* act, float* obs_next, float*
                  uint8_t* terminated, uint8_t* truncated, int autoreset, float* obs_carry,
                  tsm_stream_t stream);
 
+/* The same step for continuous_actions=True (pettingzoo mpe simple_env._set_action): act [n_envs * n_agents][5] float32, the
+ * Box(0, 1, (5,)) action of every row; values outside the box are clipped first (the ClipOutOfBoundsWrapper that mpe's make_env
+ * puts around continuous environments), then u = (act[2] - act[1], act[4] - act[3]) * sensitivity.  A one-hot act equals the
+ * discrete action of that index bit for bit.  Everything else as tsm_mpe_step. */
+int tsm_mpe_step_continuous(const tsm_mpe* e, const float* act, float* obs_next, float* rew, uint8_t* terminated,
+                            uint8_t* truncated, int autoreset, float* obs_carry, tsm_stream_t stream);
+
 /* =========================================================================================
  * Policy side of the rollout
  * ========================================================================================= */

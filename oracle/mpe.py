@@ -130,13 +130,22 @@ class OracleMPE:
     # -- step -------------------------------------------------------------------------------
     def step(self, act):
         """One parallel cycle (simple_env.step with all agents' actions -> _execute_world_step).
-        act: (E, A) ints in 0..4.  Returns obs (E,A,O) f32, rew (E,A) f64, terminated, truncated (E,A) bool."""
-        act = np.asarray(act).reshape(self.E, self.A)
+        act: (E, A) ints in 0..4, or (E, A, 5) floats (continuous_actions=True).  Returns obs (E,A,O) f32, rew (E,A) f64, terminated, truncated (E,A) bool."""
+        act = np.asarray(act)
         A, L = self.A, self.L
-        # simple_env._set_action (discrete): u in {-1,0,1}^2 times sensitivity
         u = np.zeros((self.E, A, 2))
-        u[..., 0] = np.where(act == 1, -1.0, np.where(act == 2, 1.0, 0.0))
-        u[..., 1] = np.where(act == 3, -1.0, np.where(act == 4, 1.0, 0.0))
+        if np.issubdtype(act.dtype, np.floating):
+            # continuous_actions=True: Box(0, 1, (5,)) per agent, clipped to the box by ClipOutOfBoundsWrapper (mpe make_env wraps
+            # continuous environments with it), then simple_env._set_action: u[0] += a[2] - a[1]; u[1] += a[4] - a[3] (float32
+            # differences added to float64 zeros; the order keeps the directions of discrete actions 1..4)
+            a = np.clip(act.reshape(self.E, A, 5).astype(np.float32), np.float32(0.0), np.float32(1.0))
+            u[..., 0] = a[..., 2] - a[..., 1]
+            u[..., 1] = a[..., 4] - a[..., 3]
+        else:
+            # simple_env._set_action (discrete): u in {-1,0,1}^2 times sensitivity
+            act = act.reshape(self.E, A)
+            u[..., 0] = np.where(act == 1, -1.0, np.where(act == 2, 1.0, 0.0))
+            u[..., 1] = np.where(act == 3, -1.0, np.where(act == 4, 1.0, 0.0))
         u *= self.accel[None, :, None]
         # core.World.apply_action_force (u_noise None) then apply_environment_force
         force = np.zeros((self.E, A + L, 2))

@@ -121,3 +121,91 @@ def test_autoreset_carry():
             assert int(env.steps.max().item()) == 0
         else:
             assert torch.equal(carry, obs)
+
+
+CONT_CASES = [CASES[0], CASES[2], CASES[4]]
+
+
+@pytest.mark.parametrize("name,scen,kw", CONT_CASES)
+def test_continuous_actions_teacher_forced(name, scen, kw):
+    """continuous_actions=True (tsm_mpe_step_continuous): Box(0, 1, (5,)) action vectors, values outside the box included."""
+    from tianshou_marl_b200.env import MPEVectorEnv
+
+    E = 2048
+    env = MPEVectorEnv(name, n_envs=E, seed=3, continuous_actions=True, **kw)
+    orc = OracleMPE(scen, E, seed=3, **kw)
+    assert env.single_action_space.shape == (5,) and env.single_action_space.low == 0.0 and env.single_action_space.high == 1.0
+    env.reset()
+    orc.reset()
+    rng = np.random.default_rng(11)
+    A = orc.A
+    for t in range(20):
+        if t % 5 == 0:
+            orc.pos[: E // 4] *= 0.25
+        env.pos.copy_(torch.as_tensor(orc.pos[:, :A].reshape(-1, 2), dtype=torch.float32))
+        env.vel.copy_(torch.as_tensor(orc.vel.reshape(-1, 2), dtype=torch.float32))
+        env.lm.copy_(torch.as_tensor(orc.pos[:, A:].reshape(-1, 2), dtype=torch.float32))
+        orc.pos[:] = np.concatenate([env.pos.cpu().numpy().reshape(E, A, 2), env.lm.cpu().numpy().reshape(E, -1, 2)], 1)
+        orc.vel[:] = env.vel.cpu().numpy().reshape(E, A, 2)
+        act = rng.uniform(-0.25, 1.25, (E, A, 5)).astype(np.float32)  # a quarter of the entries get clipped
+        obs, rew, term, trunc, _ = env.step(act.reshape(-1, 5))
+        o_w, r_w, _, tr_w = orc.step(act)
+        assert np.allclose(env.pos.cpu().numpy().reshape(E, A, 2), orc.pos[:, :A], rtol=1e-5, atol=1e-5)
+        assert np.allclose(env.vel.cpu().numpy().reshape(E, A, 2), orc.vel, rtol=1e-5, atol=1e-5)
+        assert np.allclose(obs.cpu().numpy().reshape(E, A, -1), o_w, rtol=1e-5, atol=1e-5)
+        bad = ~np.isclose(rew.cpu().numpy().reshape(E, A), r_w, rtol=1e-5, atol=1e-5)
+        assert bad.mean() < 1e-4, bad.mean()
+        assert np.array_equal(trunc.cpu().numpy().reshape(E, A), tr_w)
+        if tr_w.any():
+            env.reset()
+            orc.reset()
+
+
+@pytest.mark.parametrize("name,scen,kw", CONT_CASES)
+def test_one_hot_continuous_equals_discrete(name, scen, kw):
+    """simple_env._set_action: the continuous ordering keeps the directions of discrete actions 1..4, so a one-hot vector moves
+    the world exactly like the discrete action of that index: bit-equal state, observations and rewards."""
+    from tianshou_marl_b200.env import MPEVectorEnv
+
+    E = 512
+    d = MPEVectorEnv(name, n_envs=E, seed=9, **kw)
+    c = MPEVectorEnv(name, n_envs=E, seed=9, continuous_actions=True, **kw)
+    od, _ = d.reset()
+    oc, _ = c.reset()
+    assert torch.equal(od, oc)
+    g = torch.Generator(device="cuda").manual_seed(2)
+    for _ in range(25):
+        a = torch.randint(0, 5, (d.n_rows,), device="cuda", generator=g)
+        od, rd, _, td, _ = d.step(a)
+        oc, rc, _, tc, _ = c.step(torch.nn.functional.one_hot(a, 5).to(torch.float32))
+        assert torch.equal(od, oc) and torch.equal(rd, rc) and torch.equal(td, tc)
+        assert torch.equal(d.pos, c.pos) and torch.equal(d.vel, c.vel)
+
+
+def test_continuous_policy_collects_and_updates_on_mpe():
+    """Box actions end to end: ContinuousActorPolicy (Gaussian head, Policy.map_action scaling [-1, 1] -> [0, 1]) acting in
+    MPEVectorEnv(continuous_actions=True) through the Collector, float action vectors in the buffer, one PPO update."""
+    from tianshou_marl_b200.algorithm import PPO, AdamOptimizerFactory, ContinuousActorPolicy
+    from tianshou_marl_b200.data import Collector, VectorReplayBuffer
+    from tianshou_marl_b200.env import MPEVectorEnv
+    from tianshou_marl_b200.utils import ActorCriticNet
+
+    E, T = 64, 25
+    env = MPEVectorEnv("simple_spread_v3", n_envs=E, seed=1, continuous_actions=True)
+    net = ActorCriticNet(env.obs_dim, 64, 5, seed=0, gaussian=True)
+    before = net.flat.detach().clone()
+    pol = ContinuousActorPolicy(actor=net, action_space=env.single_action_space)
+    pol.is_within_training_step = True  # (what the trainer sets around collect + update)
+    alg = PPO(policy=pol, critic=net, optim=AdamOptimizerFactory(lr=1e-3), max_grad_norm=0.5)
+    buf = VectorReplayBuffer(T * env.n_rows, env.n_rows, index_type="torch")
+    col = Collector(pol, env, buf)
+    col.reset()
+    st = col.collect(n_step=T * env.n_rows)
+    assert st.n_collected_steps == T * env.n_rows and st.n_collected_episodes == env.n_rows
+    act_f = buf._store["act_f"]
+    assert act_f.shape == (T, env.n_rows, 5) and bool(torch.isfinite(act_f).all()) and float(act_f.std()) > 0.1
+    ts = alg.update(buf, 1024, 2)
+    assert ts.gradient_steps == 2 * len(alg.split_bounds(T * env.n_rows, 1024)) - 2
+    assert np.isfinite(ts.loss.mean) and np.isfinite(ts.vf_loss.mean)
+    assert not torch.equal(before, net.flat.detach())
+    assert float((net.view("log_sigma").detach() - 0.0).abs().max()) > 0.0  # the scale parameters moved too

@@ -146,6 +146,7 @@ _SIGS = {
     "tsm_buf_unfinished": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
     "tsm_mpe_reset": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_vp, c_vp]),
     "tsm_mpe_step": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
+    "tsm_mpe_step_continuous": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
     "tsm_random_actions": (c_i32, [c_vp, c_i64, c_i32, C.c_uint64, C.c_uint64, c_vp]),
     "tsm_collect_lockstep": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, C.c_uint64, C.c_uint64, c_i64, c_i32, c_vp, c_vp, c_vp, c_vp]),
     "tsm_map_action": (c_i32, [c_vp, c_i64, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp]),

@@ -209,7 +209,8 @@ int tc_net_forward(const tsm_net* net, const float* x, const int64_t* rows, int6
         attr = true;
     }
     const int64_t tiles = ceil_div(n, mlptc::TC_ROWS);
-    const unsigned grid = (unsigned)std::min<int64_t>(tiles, (int64_t)sm_count() * 3);
+    static const int ctas = getenv("TSM_TC_FWD_CTAS") ? atoi(getenv("TSM_TC_FWD_CTAS")) : 3;  // experiments: CTAs per SM the grid is sized for
+    const unsigned grid = (unsigned)std::min<int64_t>(tiles, (int64_t)sm_count() * ctas);
     TSM_CUDA(launch_pdl(g_pdl_hint, mlptc::tc_forward_kernel, grid, mlptc::TC_THREADS, smem, s, a));
     TSM_LAUNCH_CHECK();
     return TSM_OK;

@@ -216,7 +216,8 @@ template <int G, bool TAIL, bool STAGE>
 __global__ void __launch_bounds__(THREADS) step_kernel(tsm_mpe e, const int32_t* __restrict__ act,
                                                       float* __restrict__ obs_next, float* __restrict__ rew,
                                                       uint8_t* __restrict__ term, uint8_t* __restrict__ trunc, int autoreset,
-                                                      float* __restrict__ obs_carry, RolloutTail t, int64_t env0, int64_t n_sub) {
+                                                      float* __restrict__ obs_carry, RolloutTail t, int64_t env0, int64_t n_sub,
+                                                      const float* __restrict__ act_f) {
     // the launch covers environments [env0, env0 + n_sub) (all arrays stay indexed by the global env / row)
     const int64_t local = ((int64_t)blockIdx.x * THREADS + threadIdx.x) / G;
     const int64_t env = env0 + local;
@@ -238,13 +239,28 @@ __global__ void __launch_bounds__(THREADS) step_kernel(tsm_mpe e, const int32_t*
     // wait (and only then let this kernel be scheduled).  No-ops for a normal launch.
     pdl_wait();
     pdl_launch_dependents();
-    if (is_agent) a = act[row];
+    // continuous_actions=True (simple_env._set_action): a row's action is a Box(0, 1, (5,)) vector, u = (a[2] - a[1], a[4] - a[3])
+    // in float32, after ClipOutOfBoundsWrapper (mpe make_env wraps continuous envs with it) clipped it to the box
+    float ux = 0.f, uy = 0.f;
+    if (is_agent) {
+        if (act_f) {
+            const float* af = act_f + row * 5;
+            const float a1 = fminf(fmaxf(af[1], 0.f), 1.f), a2 = fminf(fmaxf(af[2], 0.f), 1.f);
+            const float a3 = fminf(fmaxf(af[3], 0.f), 1.f), a4 = fminf(fmaxf(af[4], 0.f), 1.f);
+            ux = __fsub_rn(a2, a1);
+            uy = __fsub_rn(a4, a3);
+        } else {
+            a = act[row];
+            ux = a == 1 ? -1.f : (a == 2 ? 1.f : 0.f);
+            uy = a == 3 ? -1.f : (a == 4 ? 1.f : 0.f);
+        }
+    }
     const float my_size = agent_size(e, j);
 
     // simple_env._set_action (discrete) + World.apply_action_force
     const float sens = agent_accel(e, j);
-    float fx = (a == 1 ? -1.f : (a == 2 ? 1.f : 0.f)) * sens;
-    float fy = (a == 3 ? -1.f : (a == 4 ? 1.f : 0.f)) * sens;
+    float fx = __fmul_rn(ux, sens);
+    float fy = __fmul_rn(uy, sens);
     // World.apply_environment_force: partners in ascending entity order (agents, then landmarks); simple_adversary has no
     // collidable entity at all (collide = False everywhere)
     for (int k = 0; k < (e.scenario == TSM_MPE_ADVERSARY ? 0 : A); ++k) {
@@ -527,7 +543,8 @@ extern "C" int tsm_mpe_reset(const tsm_mpe* e, const int64_t* env_ids, int64_t n
 
 template <bool TAIL>
 static int launch_step(const tsm_mpe* e, const int32_t* act, float* obs_next, float* rew, uint8_t* terminated, uint8_t* truncated,
-                       int autoreset, float* obs_carry, const RolloutTail& t, int64_t env0, int64_t n_sub, cudaStream_t s) {
+                       int autoreset, float* obs_carry, const RolloutTail& t, int64_t env0, int64_t n_sub, cudaStream_t s,
+                       const float* act_f = nullptr) {
     const int G = group_width(e);
     const unsigned grid = (unsigned)ceil_div(n_sub * G, THREADS);
     // staging area: the observations of the block's worlds; direct per-lane writes when it would not fit the default 48 KB
@@ -535,8 +552,8 @@ static int launch_step(const tsm_mpe* e, const int32_t* act, float* obs_next, fl
     static const bool no_stage = getenv("TSM_MPE_NO_STAGE") != nullptr;
     const bool st = stage <= 48 * 1024 - 2048 && (e->obs_dim % 2) == 0 && !no_stage;
 #define TSM_STEP(GG)                                                                                                                          \
-    if (st) TSM_CUDA(launch_pdl(g_pdl_hint, step_kernel<GG, TAIL, true>, grid, THREADS, stage, s, *e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t, env0, n_sub)); \
-    else TSM_CUDA(launch_pdl(g_pdl_hint, step_kernel<GG, TAIL, false>, grid, THREADS, 0, s, *e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t, env0, n_sub));
+    if (st) TSM_CUDA(launch_pdl(g_pdl_hint, step_kernel<GG, TAIL, true>, grid, THREADS, stage, s, *e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t, env0, n_sub, act_f)); \
+    else TSM_CUDA(launch_pdl(g_pdl_hint, step_kernel<GG, TAIL, false>, grid, THREADS, 0, s, *e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, t, env0, n_sub, act_f));
     switch (G) {
         case 4: TSM_STEP(4) break;
         case 8: TSM_STEP(8) break;
@@ -554,6 +571,14 @@ extern "C" int tsm_mpe_step(const tsm_mpe* e, const int32_t* act, float* obs_nex
     if (rc) return rc;
     TSM_REQUIRE(act && rew && terminated && truncated, "act/rew/terminated/truncated != NULL");
     return launch_step<false>(e, act, obs_next, rew, terminated, truncated, autoreset, obs_carry, RolloutTail{}, 0, e->n_envs, as_stream(stream));
+}
+
+extern "C" int tsm_mpe_step_continuous(const tsm_mpe* e, const float* act, float* obs_next, float* rew, uint8_t* terminated,
+                                       uint8_t* truncated, int autoreset, float* obs_carry, tsm_stream_t stream) {
+    int rc = check_env(e, __func__);
+    if (rc) return rc;
+    TSM_REQUIRE(act && rew && terminated && truncated, "act/rew/terminated/truncated != NULL");
+    return launch_step<false>(e, nullptr, obs_next, rew, terminated, truncated, autoreset, obs_carry, RolloutTail{}, 0, e->n_envs, as_stream(stream), act);
 }
 
 extern "C" int tsm_rollout_step(const tsm_mpe* e, const tsm_buf* buf, const int32_t* act, float* obs_next, float* rew,

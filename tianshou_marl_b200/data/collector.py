@@ -146,6 +146,8 @@ class Collector:
         from ..algorithm.ppo import DiscreteActorPolicy
 
         b = self.buffer
+        if getattr(self.env, "continuous_actions", False) or getattr(getattr(self.policy, "actor", None), "gaussian", False):
+            return False  # Box actions: the generic step (float action vectors, Policy.map_action); the fused kernels sample Categorical
         if not random and self._manager_groups() is not None:
             return isinstance(self.env, MPEVectorEnv) and b._lockstep_len is not None and b.buffer_num == self.env_num and b._save_obs_next
         return (isinstance(self.env, MPEVectorEnv) and (random or isinstance(self.policy, DiscreteActorPolicy))

@@ -44,8 +44,16 @@ class Discrete:
 
 
 class Box:
-    def __init__(self, low: float, high: float, shape: tuple[int, ...], dtype: Any = np.float32) -> None:
+    def __init__(self, low: float, high: float, shape: tuple[int, ...], dtype: Any = np.float32, seed: int | None = None) -> None:
         self.low, self.high, self.shape, self.dtype = low, high, tuple(shape), dtype
+        self._rng = np.random.default_rng(seed)
+
+    def sample(self, mask: Any = None) -> np.ndarray:
+        """Uniform over a bounded box (gymnasium.spaces.Box.sample for finite bounds)."""
+        return self._rng.uniform(self.low, self.high, self.shape).astype(self.dtype)
+
+    def seed(self, seed: int | None = None) -> None:
+        self._rng = np.random.default_rng(seed)
 
     def __repr__(self) -> str:
         return f"Box({self.low}, {self.high}, {self.shape}, {self.dtype})"
@@ -75,7 +83,8 @@ class MPEVectorEnv:
 
     def __init__(self, scenario: str | int = "simple_spread_v3", n_envs: int = 1, n_agents: int = 3, max_cycles: int = 25,
                  local_ratio: float = 0.5, pos_first: bool = True, seed: int = 0, num_good: int = 1,
-                 num_adversaries: int = 3, num_obstacles: int = 2, device: str | torch.device = "cuda") -> None:
+                 num_adversaries: int = 3, num_obstacles: int = 2, device: str | torch.device = "cuda",
+                 continuous_actions: bool = False) -> None:
         self.scenario = _SCENARIOS[scenario]
         self.device = torch.device(device)
         if self.device.type != "cuda":
@@ -111,7 +120,9 @@ class MPEVectorEnv:
         d.max_cycles, d.pos_first, d.local_ratio, d.n_envs, d.seed = max_cycles, int(pos_first), local_ratio, n_envs, seed
         d.pos, d.vel, d.lm = self.pos.data_ptr(), self.vel.data_ptr(), self.lm.data_ptr()
         d.steps, d.episode = self.steps.data_ptr(), self.episode.data_ptr()
-        self.single_action_space = Discrete(5, seed)
+        # continuous_actions=True: Box(0, 1, (5,)) per agent (simple_env: space_dim = dim_p * 2 + 1, every agent here is silent)
+        self.continuous_actions = bool(continuous_actions)
+        self.single_action_space = Box(0.0, 1.0, (5,), seed=seed) if self.continuous_actions else Discrete(5, seed)
         self.single_observation_space = Box(-np.inf, np.inf, (O,))
         self.action_space = _SpaceList(self.single_action_space, self.n_rows)
         self.observation_space = _SpaceList(self.single_observation_space, self.n_rows)
@@ -152,12 +163,15 @@ class MPEVectorEnv:
 
     def step(self, action: Any, id: Any = None, autoreset: bool = False,
              out: dict[str, torch.Tensor] | None = None) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor, Any]:
-        """venvs.py:237-322.  `action` (R,) ints.  Returns (obs_next, rew, terminated, truncated, info)
+        """venvs.py:237-322.  `action` (R,) ints, or (R, 5) floats with continuous_actions=True.  Returns (obs_next, rew, terminated, truncated, info)
         as device tensors.  `id` must be None or all rows (a batched world cannot step a subset)."""
         if id is not None and len(id) != self.n_rows:
             raise ValueError("MPEVectorEnv steps all rows at once")
         R, O, dev = self.n_rows, self.obs_dim, self.device
-        act = torch.as_tensor(action, device=dev).to(torch.int32).reshape(R).contiguous()
+        if self.continuous_actions:
+            act = torch.as_tensor(action, device=dev).to(torch.float32).reshape(R, 5).contiguous()
+        else:
+            act = torch.as_tensor(action, device=dev).to(torch.int32).reshape(R).contiguous()
         o = out or {}
         obs_next = o.get("obs_next", None)
         if obs_next is None:
@@ -166,8 +180,9 @@ class MPEVectorEnv:
         term = o["terminated"] if "terminated" in o else torch.empty(R, dtype=torch.uint8, device=dev)
         trunc = o["truncated"] if "truncated" in o else torch.empty(R, dtype=torch.uint8, device=dev)
         carry = o.get("obs_carry", None)
-        _lib.check(_lib.lib().tsm_mpe_step(C.byref(self._desc), _lib.ptr(act), _lib.ptr(obs_next), _lib.ptr(rew),
-                                           _lib.ptr(term), _lib.ptr(trunc), int(autoreset), _lib.ptr(carry), _lib.stream_ptr()))
+        fn = _lib.lib().tsm_mpe_step_continuous if self.continuous_actions else _lib.lib().tsm_mpe_step
+        _lib.check(fn(C.byref(self._desc), _lib.ptr(act), _lib.ptr(obs_next), _lib.ptr(rew),
+                      _lib.ptr(term), _lib.ptr(trunc), int(autoreset), _lib.ptr(carry), _lib.stream_ptr()))
         return obs_next, rew, term.view(torch.bool), trunc.view(torch.bool), EmptyInfo(R)
 
 
