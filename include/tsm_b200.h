@@ -311,6 +311,9 @@ typedef struct tsm_net {
                             ContinuousActorProbabilistic(unbounded=True, conditioned_sigma=False) with Independent(Normal, 1)
                             (utils/net/continuous.py:222,229-247).  Engine 0 only; tsm_ppo_minibatch then reads tsm_ppo_batch.act_f,
                             and tsm_net_forward serves mode 0 only (sampling / log-probabilities are elementwise host-side ops) */
+    float mu_bound;      /* Gaussian nets: 0 = the head outputs are the means (unbounded=True); > 0: mean = mu_bound * tanh(output),
+                            the reference's default unbounded=False with max_action = mu_bound (continuous.py:239-241).
+                            tsm_net_forward (mode 0) returns the raw outputs either way */
 } tsm_net;
 #define TSM_TC_IMAGE_BYTES 123648 /* 16 896 image + tsm_ppo_epoch's three more gradient-sized buffers of 7 168 floats + 256 bytes of barrier words + a 20 KB index table */
 

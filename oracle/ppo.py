@@ -27,11 +27,12 @@ from . import gae as ogae
 class Net:
     """Parameters in torch.nn.Linear convention; W3/b3 stack the actor rows then the critic row."""
 
-    def __init__(self, W1, b1, W2, b2, W3, b3, n_act: int, log_sigma=None) -> None:
+    def __init__(self, W1, b1, W2, b2, W3, b3, n_act: int, log_sigma=None, mu_bound: float = 0.0) -> None:
         arrs = (W1, b1, W2, b2, W3, b3) + ((np.asarray(log_sigma).reshape(-1),) if log_sigma is not None else ())
         self.p = [torch.tensor(np.asarray(a), dtype=torch.float32).clone().requires_grad_(True) for a in arrs]
         self.n_act = n_act
         self.gaussian = log_sigma is not None
+        self.mu_bound = float(mu_bound)  # > 0: unbounded=False, mu = max_action * tanh(head output) (continuous.py:239-241)
         self.m = [torch.zeros_like(x) for x in self.p]
         self.v = [torch.zeros_like(x) for x in self.p]
         self.t = 0
@@ -41,7 +42,10 @@ class Net:
         h = F.relu(F.linear(x, W1, b1))
         h = F.relu(F.linear(h, W2, b2))
         o = F.linear(h, W3, b3)
-        return o[:, : self.n_act], (o[:, self.n_act] if o.shape[1] > self.n_act else torch.zeros(o.shape[0]))  # (actor-only net: no value row)
+        head = o[:, : self.n_act]
+        if self.gaussian and self.mu_bound > 0:
+            head = self.mu_bound * torch.tanh(head)
+        return head, (o[:, self.n_act] if o.shape[1] > self.n_act else torch.zeros(o.shape[0]))  # (actor-only net: no value row)
 
     def flat(self) -> np.ndarray:
         return np.concatenate([x.detach().numpy().reshape(-1) for x in self.p])

@@ -43,6 +43,7 @@ def load_gauss(g, ci):
     c = dict(R=R, T=T, O=O, H=H, nA=A, bs=bs, repeat=repeat, probs=False, seed=seed, lr=lr, gamma=gamma, lam=lam, max_norm=max_norm,
              cfg=dict(eps_clip=eps_clip, dual_clip=dual_clip, vf_coef=vf_coef, ent_coef=ent_coef, value_clip=bool(value_clip),
                       adv_norm=bool(adv_norm)))
+    c["mu_bound"] = float(g[pre + "mu_bound"]) if pre + "mu_bound" in g.files else 0.0  # > 0: unbounded=False, max_action
     for k in ("W1", "b1", "W2", "b2", "Wa", "ba", "Wv", "bv", "log_sigma"):
         c[k] = g[pre + k]
         c["after_" + k] = g[pre + "after_" + k]

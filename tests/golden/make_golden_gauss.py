@@ -1,5 +1,5 @@
 """Golden fixture `ppo_gauss.npz`: the UNMODIFIED reference PPO with a continuous (diagonal Gaussian) actor --
-ContinuousActorProbabilistic(unbounded=True, conditioned_sigma=False) + ContinuousCritic on a shared Net trunk,
+ContinuousActorProbabilistic(conditioned_sigma=False; unbounded=True, and unbounded=False with max_action 1 and 2) + ContinuousCritic on a shared Net trunk,
 dist_fn = Independent(Normal(mu, sigma), 1), as test/continuous/test_ppo.py:85-124 builds it -- on synthetic rollouts with
 float actions.  Same recording points as make_golden_more.gen_ppo (PPO._preprocess_batch outputs, per-minibatch loss terms,
 parameters after the update, sigma_param included).  Run in the build container:  cd tests/golden && python make_golden_gauss.py"""
@@ -15,10 +15,13 @@ CASES = [
     dict(R=10, T=15, O=11, H=64, A=3, bs=50, repeat=3,
          kw=dict(value_clip=True, dual_clip=3.0, advantage_normalization=False, ent_coef=0.02, vf_coef=0.25, lr=1e-3)),
     dict(R=8, T=12, O=24, H=128, A=5, bs=32, repeat=2, kw=dict(max_grad_norm=1.0, eps_clip=0.1, lr=3e-4)),
+    # unbounded=False (the reference's default): mu = max_action * tanh(head output)
+    dict(R=12, T=16, O=18, H=64, A=2, bs=64, repeat=2, bound=1.0, kw=dict(max_grad_norm=0.5, lr=1e-3)),
+    dict(R=10, T=14, O=11, H=64, A=3, bs=48, repeat=3, bound=2.0, kw=dict(value_clip=True, dual_clip=2.0, ent_coef=0.02, lr=1e-3)),
 ]
 
 
-def _ref(O: int, H: int, A: int, seed: int, **kw):
+def _ref(O: int, H: int, A: int, seed: int, bound: float = 0.0, **kw):
     import gymnasium as gym
     import torch
     from tianshou.algorithm import PPO
@@ -30,7 +33,8 @@ def _ref(O: int, H: int, A: int, seed: int, **kw):
 
     torch.manual_seed(seed)
     net = Net(state_shape=(O,), hidden_sizes=[H, H])
-    actor = ContinuousActorProbabilistic(preprocess_net=net, action_shape=(A,), unbounded=True)
+    actor = (ContinuousActorProbabilistic(preprocess_net=net, action_shape=(A,), unbounded=False, max_action=bound) if bound > 0
+             else ContinuousActorProbabilistic(preprocess_net=net, action_shape=(A,), unbounded=True))
     critic = ContinuousCritic(preprocess_net=net)
     ac = ActorCritic(actor, critic)
     for m in ac.modules():  # test/continuous/test_ppo.py:95-99 (orthogonal weights), biases non-zero so that their paths are exercised
@@ -73,7 +77,7 @@ def gen() -> None:
     for ci, c in enumerate(CASES):
         R, T, O, H, A = c["R"], c["T"], c["O"], c["H"], c["A"]
         rng = np.random.default_rng(300 + ci)
-        alg, ac = _ref(O, H, A, seed=40 + ci, **dict(c["kw"]))
+        alg, ac = _ref(O, H, A, seed=40 + ci, bound=c.get("bound", 0.0), **dict(c["kw"]))
         pre = f"p{ci}_"
         for k, v in _flat(ac).items():
             out[pre + k] = v
@@ -125,6 +129,7 @@ def gen() -> None:
             out[pre + "after_" + k] = v
         kw = c["kw"]
         out[pre + "cfg"] = np.array([R, T, O, H, A, c["bs"], c["repeat"], 0, 70 + ci], np.int64)
+        out[pre + "mu_bound"] = np.array(c.get("bound", 0.0))
         out[pre + "hyper"] = np.array([kw.get("eps_clip", 0.2), kw.get("dual_clip") or 0.0, kw.get("vf_coef", 0.5), kw.get("ent_coef", 0.01),
                                        float(kw.get("value_clip", False)), float(kw.get("advantage_normalization", True)),
                                        kw.get("max_grad_norm") or 0.0, kw.get("lr", 3e-4), 0.99, 0.95])

@@ -1,5 +1,6 @@
 """Continuous-action PPO (diagonal Gaussian head) on the GPU against fixtures recorded from the reference's
-ContinuousActorProbabilistic(unbounded=True) + ProbabilisticActorPolicy + PPO (tests/golden/ppo_gauss.npz <- make_golden_gauss.py).
+ContinuousActorProbabilistic (unbounded, and tanh-bounded with max_action 1 and 2) + ProbabilisticActorPolicy + PPO
+(tests/golden/ppo_gauss.npz <- make_golden_gauss.py).
 fp32 engine: same tolerances as the discrete reference test (tests/test_gpu_ppo.py)."""
 import numpy as np
 import pytest
@@ -15,7 +16,8 @@ def _mk(c):
     from tianshou_marl_b200.data import Batch, VectorReplayBuffer
     from tianshou_marl_b200.utils import ActorCriticNet
 
-    net = ActorCriticNet(c["O"], c["H"], c["nA"], gaussian=True).load_arrays(c["W1"], c["b1"], c["W2"], c["b2"], c["W3"], c["b3"])
+    net = ActorCriticNet(c["O"], c["H"], c["nA"], gaussian=True, unbounded=c["mu_bound"] == 0.0,
+                         max_action=c["mu_bound"] or 1.0).load_arrays(c["W1"], c["b1"], c["W2"], c["b2"], c["W3"], c["b3"])
     with torch.no_grad():
         net.view("log_sigma").copy_(torch.as_tensor(c["log_sigma"]))
     pol = ContinuousActorPolicy(actor=net)
@@ -30,7 +32,7 @@ def _mk(c):
     return net, pol, alg, buf
 
 
-@pytest.mark.parametrize("ci", [0, 1, 2])
+@pytest.mark.parametrize("ci", [0, 1, 2, 3, 4])
 def test_gaussian_update_matches_reference(golden, ci):
     """Whole PPO.update vs the reference: v_s, returns, adv, logp_old, every minibatch loss, final parameters incl. log sigma."""
     c = load_gauss(golden("ppo_gauss.npz"), ci)
@@ -38,8 +40,10 @@ def test_gaussian_update_matches_reference(golden, ci):
     # the buffer hands the float action vectors back (buffer_base.py:591-635)
     got = buf[np.arange(c["R"] * c["T"])]
     assert np.array_equal(np.asarray(got.act), c["flat"]["act"])
-    o = net.forward(torch.as_tensor(c["obs"][0], device="cuda"), mode="raw")["out"].cpu().numpy()
-    assert np.allclose(o[:, : c["nA"]], c["fwd_mu"], rtol=2e-5, atol=2e-6) and np.allclose(o[:, c["nA"]], c["fwd_value"], rtol=2e-5, atol=2e-6)
+    raw = net.forward(torch.as_tensor(c["obs"][0], device="cuda"), mode="raw")["out"]
+    o = raw.cpu().numpy()
+    assert np.allclose(net.gaussian_mean(raw).cpu().numpy(), c["fwd_mu"], rtol=2e-5, atol=2e-6)  # cases 3, 4: max_action * tanh(head)
+    assert np.allclose(o[:, c["nA"]], c["fwd_value"], rtol=2e-5, atol=2e-6)
     pol.is_within_training_step = True
     np.random.seed(c["seed"])
     stats = alg.update(buf, c["bs"], c["repeat"])

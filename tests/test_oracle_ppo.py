@@ -120,14 +120,14 @@ def test_oracle_matches_reference_reinforce(golden, ci):
         assert np.allclose(p.detach().numpy(), c["after_" + k], rtol=0, atol=2e-5), k
 
 
-@pytest.mark.parametrize("ci", [0, 1, 2])
+@pytest.mark.parametrize("ci", [0, 1, 2, 3, 4])
 def test_oracle_matches_reference_ppo_gaussian(golden, ci):
     """Continuous actions: Independent(Normal(mu, exp(sigma_param)), 1) (tests/golden/ppo_gauss.npz, recorded from the reference's
-    ContinuousActorProbabilistic(unbounded=True) + PPO)."""
+    ContinuousActorProbabilistic + PPO; cases 3 and 4: unbounded=False, mu = max_action * tanh(head) with max_action 1 and 2)."""
     import torch
 
     c = load_gauss(golden("ppo_gauss.npz"), ci)
-    net = oppo.Net(c["W1"], c["b1"], c["W2"], c["b2"], c["W3"], c["b3"], c["nA"], log_sigma=c["log_sigma"])
+    net = oppo.Net(c["W1"], c["b1"], c["W2"], c["b2"], c["W3"], c["b3"], c["nA"], log_sigma=c["log_sigma"], mu_bound=c["mu_bound"])
     f = c["flat"]
     with torch.no_grad():
         mu, value = net.forward(torch.from_numpy(c["obs"][0]))

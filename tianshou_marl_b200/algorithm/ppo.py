@@ -93,7 +93,7 @@ class DiscreteActorPolicy:
 
 class ContinuousActorPolicy(DiscreteActorPolicy):
     """ProbabilisticActorPolicy over a Box action space (reinforce.py:118-215) with the reference's standard continuous head:
-    ContinuousActorProbabilistic(unbounded=True, conditioned_sigma=False) (utils/net/continuous.py:196-247) and
+    ContinuousActorProbabilistic(conditioned_sigma=False), unbounded or tanh-bounded means (utils/net/continuous.py:196-247), and
     dist_fn = Independent(Normal(mu, sigma), 1) (test/continuous/test_ppo.py:104-110).  `actor` is an ActorCriticNet(gaussian=True):
     its n_act outputs are the means, `log_sigma` the state-independent log standard deviations.  forward samples
     mu + sigma * N(0, 1) (the mean when deterministic_eval and not in a training step); map_action clips / scales like
@@ -130,7 +130,7 @@ class ContinuousActorPolicy(DiscreteActorPolicy):
             obs = torch.as_tensor(np.ascontiguousarray(obs), dtype=torch.float32, device=self.actor.device)
         net = self.actor
         o = net.forward(obs.to(torch.float32).contiguous(), mode="raw")["out"]
-        mu = o[:, : net.n_act]
+        mu = net.gaussian_mean(o)
         ls = net.view("log_sigma")
         if self.deterministic_eval and not self.is_within_training_step:
             act = mu.clone()
@@ -322,7 +322,7 @@ class PPO:
             raw = net.forward(obs_all, mode="raw")["out"]
             v_s.view(-1).copy_(raw[:, net.value_index])
             A_ = net.n_act
-            logp.view(-1).copy_(ContinuousActorPolicy.log_prob(raw[:, :A_], net.view("log_sigma"), st["act_f"].view(-1, A_)))
+            logp.view(-1).copy_(ContinuousActorPolicy.log_prob(net.gaussian_mean(raw), net.view("log_sigma"), st["act_f"].view(-1, A_)))
             _lib.t_stop(tk)
             tk = _lib.t_start("critic_forward")
             next_values(v_s, dedup_ok)

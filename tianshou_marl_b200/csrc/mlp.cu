@@ -375,6 +375,7 @@ struct PpoArgs {
     const int32_t* act;     // [size][n_rows]
     const float* act_f;     // Gaussian nets: [size][n_rows][n_act]
     int n_sigma;            // > 0: Gaussian policy, log sigma at params[offsets.total ...]
+    float mu_bound;         // Gaussian policy: > 0 = mean is mu_bound * tanh(output)
     const float* adv;
     const float* ret;
     const float* logp_old;
@@ -445,7 +446,7 @@ __global__ void __launch_bounds__(THREADS) ppo_minibatch_kernel(PpoArgs a) {
             const float ret_s = a.value_index >= 0 ? a.ret[s] : 0.f;
             const float vo = (a.value_index >= 0 && a.cfg.value_clip) ? a.v_old[s] : 0.f;
             const RowLoss rl = a.n_sigma ? row_loss_gauss(z, a.n_act, a.value_index, a.act_f + s * a.n_act, a.params + sigma_off, adv_s, ret_s, lpo, vo,
-                                                          mean, rstd, a.cfg, inv_n, dz, dls)
+                                                          mean, rstd, a.cfg, inv_n, dz, dls, a.mu_bound)
                                          : row_loss<false>(z, a.n_act, a.value_index, act, adv_s, ret_s, lpo, vo, mean, rstd, a.cfg, inv_n, dz);
             l_clip += (double)rl.clip;
             l_ent += (double)rl.ent;
@@ -670,6 +671,8 @@ static int check_net(const tsm_net* n, const char* fn) {
     if (n->engine == 1 && !n->tc_image) return fail(TSM_ERR_INVALID, "%s: engine 1 needs tc_image", fn);
     if (n->n_sigma != 0 && (n->n_sigma != n->n_act || n->engine != 0 || n->probs_param))
         return fail(TSM_ERR_INVALID, "%s: n_sigma must be 0 or n_act, on engine 0, without probs_param", fn);
+    if (!(n->mu_bound >= 0.f) || (n->mu_bound > 0.f && n->n_sigma == 0))
+        return fail(TSM_ERR_INVALID, "%s: mu_bound must be >= 0, and 0 unless the net is Gaussian (n_sigma > 0)", fn);
     if (n->n_params != offsets(n->in_dim, n->hidden, n->out_dim).total + n->n_sigma)
         return fail(TSM_ERR_INVALID, "%s: n_params does not match the layout (want %lld)", fn,
                     (long long)offsets(n->in_dim, n->hidden, n->out_dim).total + n->n_sigma);
@@ -834,7 +837,7 @@ extern "C" int tsm_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch,
     PpoArgs a{};
     a.params = net->params; a.grads = net->grads;
     a.obs = batch->obs; a.act = batch->act; a.adv = batch->adv; a.ret = batch->ret; a.logp_old = batch->logp_old; a.v_old = batch->v_old;
-    a.act_f = batch->act_f; a.n_sigma = net->n_sigma;
+    a.act_f = batch->act_f; a.n_sigma = net->n_sigma; a.mu_bound = net->mu_bound;
     a.view = make_view(batch);
     a.mb_start = mb_start; a.mb_len = mb_len; a.mb_stats = mb_stats;
     a.cfg.eps_clip = cfg->eps_clip; a.cfg.dual_clip = cfg->dual_clip; a.cfg.vf_coef = cfg->vf_coef; a.cfg.ent_coef = cfg->ent_coef;

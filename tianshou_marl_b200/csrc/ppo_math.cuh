@@ -239,7 +239,8 @@ __device__ __forceinline__ RowLoss row_loss(const float (&z)[OUTP], int n_act_in
 // d log_sigma[j] of this row (the caller reduces it over the rows of the minibatch).
 __device__ __forceinline__ RowLoss row_loss_gauss(const float (&z)[OUTP], int n_act, int value_index, const float* __restrict__ a,
                                                   const float* __restrict__ log_sigma, float adv, float ret, float logp_old, float v_old,
-                                                  float mean, float rstd, const PpoCfg& cfg, float inv_n, float (&dz)[OUTP], float (&dls)[OUTP]) {
+                                                  float mean, float rstd, const PpoCfg& cfg, float inv_n, float (&dz)[OUTP], float (&dls)[OUTP],
+                                                  float mu_bound = 0.f) {
     RowLoss out{0.f, 0.f, 0.f};
 #pragma unroll
     for (int j = 0; j < OUTP; ++j) dz[j] = 0.f;
@@ -249,10 +250,13 @@ __device__ __forceinline__ RowLoss row_loss_gauss(const float (&z)[OUTP], int n_
     for (int j = 0; j < OUTP; ++j) {
         dmu[j] = dsg[j] = 0.f;
         if (j < n_act) {
-            const float ls = log_sigma[j], sg = expf(ls), var = sg * sg, d = a[j] - z[j];
+            // unbounded=False (continuous.py:239-241): mu = max_action * tanh(z), d mu / d z = max_action * (1 - tanh^2 z)
+            const float th = mu_bound > 0.f ? tanhf(z[j]) : 0.f;
+            const float mu = mu_bound > 0.f ? mu_bound * th : z[j], dmu_dz = mu_bound > 0.f ? mu_bound * (1.f - th * th) : 1.f;
+            const float ls = log_sigma[j], sg = expf(ls), var = sg * sg, d = a[j] - mu;
             lp += -(d * d) / (2.f * var) - ls - 0.9189385332046727f;  // log sqrt(2 pi)
             ent += 0.5f + 0.9189385332046727f + ls;                   // 0.5 + 0.5 log(2 pi) + log sigma
-            dmu[j] = d / var;
+            dmu[j] = d / var * dmu_dz;
             dsg[j] = d * d / var - 1.f;
         }
     }

@@ -26,7 +26,8 @@ MODES = {"raw": 0, "sample": 1, "mode": 2, "eval": 3}
 class ActorCriticNet(nn.Module):
     def __init__(self, in_dim: int, hidden: int = 64, n_act: int = 5, with_value: bool = True, n_value_only: int = 0,
                  device: str | torch.device = "cuda", seed: int | None = None, orthogonal: bool = True,
-                 engine: str = "fp32", softmax_output: bool = False, gaussian: bool = False) -> None:
+                 engine: str = "fp32", softmax_output: bool = False, gaussian: bool = False, unbounded: bool = True,
+                 max_action: float = 1.0) -> None:
         """engine: "fp32" = exact CUDA-core kernels (csrc/mlp.cu); "tc" = tcgen05 tensor-core kernels with fp16 operands and
         fp32 accumulation (csrc/mlp_tc.cu; hidden 64, in_dim <= 31, out_dim <= 8); "tcw" = the wide tcgen05 engine of the CTDE
         nets (csrc/mlp_tcw.cu; hidden 128, in_dim <= 1023, out_dim <= 16, separate actor / value-only critic)."""
@@ -34,11 +35,16 @@ class ActorCriticNet(nn.Module):
         if engine not in ("fp32", "tc", "tcw"):
             raise ValueError("engine must be 'fp32', 'tc' or 'tcw'")
         # gaussian: the n_act outputs are the means of a diagonal Gaussian and `log_sigma` (n_act more parameters behind b3, zero
-        # initialised) its state-independent log standard deviations: ContinuousActorProbabilistic(unbounded=True,
-        # conditioned_sigma=False) (utils/net/continuous.py:196-247).  Exact fp32 kernels only.
+        # initialised) its state-independent log standard deviations: ContinuousActorProbabilistic(conditioned_sigma=False)
+        # (utils/net/continuous.py:196-247; `unbounded` / `max_action` as there, except that unbounded defaults to True here).
+        # Exact fp32 kernels only.
         if gaussian and (engine != "fp32" or softmax_output or n_value_only):
             raise ValueError("gaussian=True needs engine 'fp32', an actor head and no softmax_output")
         self.gaussian = bool(gaussian)
+        # unbounded=False (the reference's default, continuous.py:222,239-241): mean = max_action * tanh(head output)
+        self.mu_bound = float(max_action) if (self.gaussian and not unbounded) else 0.0
+        if self.gaussian and not unbounded and not max_action > 0:
+            raise ValueError("max_action must be > 0")
         if engine == "tcw" and (hidden != 128 or with_value and not n_value_only):
             raise ValueError("engine 'tcw' (csrc/mlp_tcw.cu) runs separate hidden-128 nets: an actor (with_value=False) or a value-only critic")
         self.engine = engine
@@ -89,6 +95,11 @@ class ActorCriticNet(nn.Module):
                     nn.init.orthogonal_(w, generator=g)  # test_ppo_discrete.py:101-105
                     self.view(k).copy_(w)
 
+    def gaussian_mean(self, raw: torch.Tensor) -> torch.Tensor:
+        """Means of the Gaussian head from the raw outputs [n, >= n_act] of forward(mode="raw") (continuous.py:239-241)."""
+        mu = raw[:, : self.n_act]
+        return self.mu_bound * torch.tanh(mu) if self.mu_bound > 0 else mu
+
     # -- plumbing ---------------------------------------------------------------------------
     ENGINES = {"fp32": 0, "tc": 1, "tcw": 2}
 
@@ -107,6 +118,7 @@ class ActorCriticNet(nn.Module):
         d.x_scratch, d.x_scratch_bytes = (xs.data_ptr(), xs.numel()) if xs is not None else (None, 0)
         d.probs_param = int(self.softmax_output)
         d.n_sigma = int(self.n_sigma)
+        d.mu_bound = float(self.mu_bound)
 
     @property
     def desc(self) -> Any:
