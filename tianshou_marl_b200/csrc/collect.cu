@@ -130,6 +130,8 @@ extern "C" int tsm_collect_lockstep_groups(const tsm_net* const* nets, const int
     const int64_t R = ro->n_rows, O = ro->obs_dim, size = ro->size;
     TSM_REQUIRE(R > 0 && O > 0, "n_rows, obs_dim > 0");
     for (int g = 0; g < n_groups; ++g) TSM_REQUIRE(nets[g] && rows[g] && n_rows[g] > 0, "every group needs a net and a row list");
+    bool pdl = !getenv("TSM_COLLECT_NO_PDL");
+    for (int g = 0; g < n_groups; ++g) pdl = pdl && nets[g]->engine == 1;  // (engine 1's forward is the kernel that knows the protocol)
     int64_t slot = ro->slot, len = lockstep_len;
     bool in_carry = false;
     cudaStream_t s = as_stream(stream);
@@ -141,14 +143,20 @@ extern "C" int tsm_collect_lockstep_groups(const tsm_net* const* nets, const int
         float* carry = to_carry ? ro->carry : ro->obs + nxt * R * O;
         if (in_carry) TSM_CUDA(cudaMemcpyAsync(obs_slot, ro->carry, sizeof(float) * R * O, cudaMemcpyDeviceToDevice, s));
         for (int g = 0; g < n_groups; ++g) {
+            // the chain forward(group 0) -> ... -> forward(group n-1) -> world step runs under programmatic dependent launch like
+            // the single-policy loop above (every kernel waits for its predecessor before it touches what that one wrote)
+            g_pdl_hint = pdl && (g > 0 || (k > 0 && !in_carry));
             int rc = tsm_net_forward(nets[g], obs_slot, rows[g], n_rows[g], mode, 1, seeds[g], counters0[g] + (uint64_t)k, nullptr, act_slot,
                                      ro->logp ? ro->logp + slot * R : nullptr,
                                      (ro->value && nets[g]->value_index >= 0) ? ro->value + slot * R : nullptr, nullptr, stream);
+            g_pdl_hint = false;
             if (rc) return rc;
         }
+        g_pdl_hint = pdl;
         int rc = tsm_rollout_step(env, buf, act_slot, ro->obs_next + slot * R * O, ro->rew + slot * R, ro->terminated + slot * R,
                                   ro->truncated + slot * R, carry, ro->ep_ret, ro->ep_len, ro->acc, ro->list_ret, ro->list_len, ro->list_count,
                                   ro->list_cap, 0, env->n_envs, stream);
+        g_pdl_hint = false;
         if (rc) return rc;
         len = len + 1 < size ? len + 1 : size;
         slot = nxt;
