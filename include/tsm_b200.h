@@ -376,6 +376,12 @@ typedef struct tsm_ppo_batch {
 #define TSM_PPO_RECORD_BYTES 128
 int tsm_ppo_pack_records(const tsm_net* net, const tsm_ppo_batch* batch, void* records, tsm_stream_t stream);
 
+/* The same for the sub-buffers listed in rows [n_sel] (device int64, each in [0, n_rows)) only -- the rows of one policy group
+ * (FlexibleMultiAgentPolicyManager: one update per group over its strided row set): records of every other row are left as they
+ * are.  The record of slot (t, row) sits where tsm_ppo_pack_records puts it. */
+int tsm_ppo_pack_records_rows(const tsm_net* net, const tsm_ppo_batch* batch, void* records, const int64_t* rows, int64_t n_sel,
+                              tsm_stream_t stream);
+
 typedef struct tsm_ppo_cfg {
     float eps_clip;   /* ppo.py:25 (0.2) */
     float dual_clip;  /* <= 0: off (ppo.py:26) */

@@ -150,6 +150,14 @@ def test_pack_records_bit_exact():
             assert np.array_equal(h[:, 76:80].copy().view(np.int32)[:, 0], act)
             assert np.array_equal(h[:, 80:84].copy().view(np.float32)[:, 0], vo if with_vo else np.zeros(n, np.float32))
             assert not h[:, 84:96].any()  # (bytes 96..127 of the 128-byte pitch are never written)
+            # tsm_ppo_pack_records_rows: the same records for the listed sub-buffers, everything else untouched
+            sel = np.sort(rng.choice(R, size=max(1, R // 3), replace=False)).astype(np.int64)
+            rec2 = torch.full((n, _lib.PPO_RECORD_BYTES), 0xAB, dtype=torch.uint8, device="cuda")
+            _lib.check(_lib.lib().tsm_ppo_pack_records_rows(net.desc, C.byref(pb), P(rec2), P(d(sel)), len(sel), _lib.stream_ptr()))
+            h2 = rec2.cpu().numpy().reshape(size, R, -1)
+            mask = np.zeros(R, bool)
+            mask[sel] = True
+            assert np.array_equal(h2[:, mask], h.reshape(size, R, -1)[:, mask]) and (h2[:, ~mask] == 0xAB).all()
 
 
 def test_minibatch_tc_needs_records():

@@ -159,6 +159,7 @@ _SIGS = {
     "tsm_net_param_count": (c_i64, [c_i32, c_i32, c_i32]),
     "tsm_net_pack": (c_i32, [c_vp, c_vp]),
     "tsm_ppo_pack_records": (c_i32, [c_vp, c_vp, c_vp, c_vp]),
+    "tsm_ppo_pack_records_rows": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp]),
     "tsm_net_forward": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_u64, c_u64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "tsm_ppo_slot_table": (c_i32, [c_vp, c_i64, c_i64, c_vp]),
     "tsm_ppo_adv_stats": (c_i32, [c_vp, c_vp, c_i64, c_f32, c_vp, c_vp]),

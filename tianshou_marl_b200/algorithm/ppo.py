@@ -413,7 +413,14 @@ class PPO:
         if net.engine == "tc":  # one 96-byte record per stored row: the minibatch kernels gather 3 sectors / 1 page per row
             tk = _lib.t_start("pack_records")
             rec = self._buf("records", (size * R, _lib.PPO_RECORD_BYTES), torch.uint8)
-            _lib.check(L.tsm_ppo_pack_records(net.desc, C.byref(pb), P(rec), S))
+
+            def pack() -> None:
+                if rows is not None:  # a policy group: only its sub-buffers (the rest of the array is never gathered)
+                    _lib.check(L.tsm_ppo_pack_records_rows(net.desc, C.byref(pb), P(rec), P(rows), int(rows.numel()), S))
+                else:
+                    _lib.check(L.tsm_ppo_pack_records(net.desc, C.byref(pb), P(rec), S))
+
+            pack()
             pb.records = P(rec)
             _lib.t_stop(tk)
             if size * R < 2**31:  # slot table of the epoch's permutation: filled by adv_stats as a by-product, read by the tiles
@@ -432,7 +439,7 @@ class PPO:
                 run_gae(v_s)
                 pb.v_old = P(v_s)
                 if net.engine == "tc":
-                    _lib.check(L.tsm_ppo_pack_records(net.desc, C.byref(pb), P(rec), S))
+                    pack()
                 _lib.t_stop(tk)
             if self.minibatch_order == "numpy":
                 order = torch.as_tensor(np.random.permutation(B), device=net.device)  # batch.py:1219

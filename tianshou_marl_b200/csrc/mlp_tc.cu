@@ -131,9 +131,14 @@ namespace mlptc {
 __global__ void __launch_bounds__(256) pack_records_kernel(const float* __restrict__ obs, const int32_t* __restrict__ act,
                                                           const float* __restrict__ adv, const float* __restrict__ ret,
                                                           const float* __restrict__ logp_old, const float* __restrict__ v_old,
-                                                          int64_t n_slots, int in_dim, uint4* __restrict__ records) {
-    const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+                                                          int64_t n_slots, int in_dim, uint4* __restrict__ records,
+                                                          const int64_t* __restrict__ rows, int64_t n_sel, int64_t n_rows) {
+    int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n_slots) return;
+    if (rows) {  // only the sub-buffers in `rows` (a policy group): thread (t, i) packs slot t * n_rows + rows[i]
+        const int64_t t = s / n_sel;
+        s = t * n_rows + rows[s - t * n_sel];
+    }
     float x[TC_XF];
 #pragma unroll
     for (int k = 0; k < TC_XF; ++k) x[k] = 0.f;
@@ -178,7 +183,24 @@ extern "C" int tsm_ppo_pack_records(const tsm_net* net, const tsm_ppo_batch* bat
     TSM_REQUIRE((reinterpret_cast<uintptr_t>(records) & 15) == 0, "records must be 16-byte aligned");
     const int64_t n = batch->size * batch->n_rows;
     mlptc::pack_records_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, as_stream(stream)>>>(
-        batch->obs, batch->act, batch->adv, batch->ret, batch->logp_old, batch->v_old, n, net->in_dim, reinterpret_cast<uint4*>(records));
+        batch->obs, batch->act, batch->adv, batch->ret, batch->logp_old, batch->v_old, n, net->in_dim, reinterpret_cast<uint4*>(records),
+        nullptr, 0, batch->n_rows);
+    TSM_LAUNCH_CHECK();
+    return TSM_OK;
+}
+
+extern "C" int tsm_ppo_pack_records_rows(const tsm_net* net, const tsm_ppo_batch* batch, void* records, const int64_t* rows, int64_t n_sel,
+                                         tsm_stream_t stream) {
+    TSM_REQUIRE(net && batch && records && rows, "net / batch / records / rows != NULL");
+    TSM_REQUIRE(net->in_dim >= 1 && net->in_dim <= 31, "1 <= in_dim <= 31");
+    TSM_REQUIRE(batch->obs != nullptr && batch->size > 0 && batch->n_rows > 0, "batch.obs / size / n_rows");
+    TSM_REQUIRE((reinterpret_cast<uintptr_t>(records) & 15) == 0, "records must be 16-byte aligned");
+    TSM_REQUIRE(n_sel >= 0 && n_sel <= batch->n_rows, "0 <= n_sel <= n_rows");
+    if (n_sel == 0) return TSM_OK;
+    const int64_t n = batch->size * n_sel;
+    mlptc::pack_records_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, as_stream(stream)>>>(
+        batch->obs, batch->act, batch->adv, batch->ret, batch->logp_old, batch->v_old, n, net->in_dim, reinterpret_cast<uint4*>(records),
+        rows, n_sel, batch->n_rows);
     TSM_LAUNCH_CHECK();
     return TSM_OK;
 }
