@@ -451,3 +451,52 @@ def test_reinforce_matches_reference(golden, ci):
     for k in ("W1", "b1", "W2", "b2", "W3", "b3"):
         err = np.abs(v[k].cpu().numpy() - c["after_" + k]).max()
         assert err < 5e-5, (k, err)
+
+
+_STATS_SNIPPET = r"""
+import ctypes as C, sys, numpy as np, torch
+from tianshou_marl_b200 import _lib
+L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr()
+out = {}
+for size, R, start, ln, mb in ((16, 5000, 0, 16, 8192), (8, 1237, 5, 6, 1000), (1, 70001, 0, 1, 70001), (4, 33, 1, 4, 7)):
+    g = torch.Generator(device="cuda").manual_seed(size * 100 + R)
+    adv = torch.randn(size, R, device="cuda", generator=g) * 3 + 0.5
+    B = ln * R
+    bounds = list(range(0, B, mb)) + [B]
+    n_mb = len(bounds) - 1
+    slots = torch.full((B,), -1, dtype=torch.int32, device="cuda")
+    pb = _lib.TsmPpoBatch(obs=None, act=None, adv=P(adv), ret=None, logp_old=None, v_old=None, indices=None, size=size, n_rows=R,
+                          start=start, len=ln, perm_key=0xC0FFEE1234 + R, perm_n=B, slots=P(slots))
+    st = torch.zeros(n_mb, 2, device="cuda")
+    _lib.check(L.tsm_ppo_adv_stats(C.byref(pb), P(torch.as_tensor(bounds, dtype=torch.int64, device="cuda")), n_mb, 1e-8, P(st), S))
+    out[f"st_{R}"] = st.cpu().numpy()
+    out[f"sl_{R}"] = slots.cpu().numpy()
+np.savez(sys.argv[1], **out)
+"""
+
+
+@pytest.mark.gpu
+def test_adv_stats_walk_kernel_is_bit_identical_to_the_plain_gather(tmp_path):
+    """tsm_ppo_adv_stats over a keyed permutation runs adv_stats_walk_kernel (cycle walk with lane refill); TSM_ADV_STATS_PLAIN=1
+    (read once per process) selects the plain per-element loop.  Same permutation, same accumulation order: equal bits, and the
+    slot table written as a by-product is the same permutation of the view's slots."""
+    import os
+    import subprocess
+    import sys
+
+    res = []
+    for k, env in enumerate(({}, {"TSM_ADV_STATS_PLAIN": "1"})):
+        e = dict(os.environ)
+        e.update(env)
+        e["PYTHONPATH"] = os.path.dirname(os.path.dirname(os.path.abspath(__file__))) + os.pathsep + e.get("PYTHONPATH", "")
+        f = str(tmp_path / f"s{k}.npz")
+        r = subprocess.run([sys.executable, "-c", _STATS_SNIPPET, f], env=e, capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-2000:]
+        res.append(np.load(f))
+    assert sorted(res[0].files) == sorted(res[1].files) and len(res[0].files) == 8
+    for k in res[0].files:
+        assert np.array_equal(res[0][k].view(np.uint32) if res[0][k].dtype == np.float32 else res[0][k],
+                              res[1][k].view(np.uint32) if res[1][k].dtype == np.float32 else res[1][k]), k
+    sl = res[0]["sl_1237"]  # view: 6 of 8 ring slots per row from slot 5 on
+    t, row = sl // 1237, sl % 1237
+    assert len(np.unique(sl)) == len(sl) == 6 * 1237 and set(np.unique(t)) == {5, 6, 7, 0, 1, 2} and row.max() == 1236
