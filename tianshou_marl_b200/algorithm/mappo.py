@@ -191,6 +191,8 @@ class MAPPO:
         mgn = float(self.max_grad_norm) if self.max_grad_norm else 0.0
         rows_seq: list[np.ndarray] = []
         keep = []
+        # what it takes to undo the update if the in-kernel gradient exchange loses a peer (checked after the epochs)
+        snaps = (actor.snapshot(), critic.snapshot(), (self._steps, self._adam_seq)) if world > 1 and self.grad_sync != "nccl" else None
         for ep in range(repeat):
             if self.minibatch_order == "numpy" and n_mb > 1:
                 ids_h = np.random.permutation(n_super).astype(np.int32)  # the epoch's order of super-tiles (global numpy RNG, batch.py:1219)
@@ -240,7 +242,15 @@ class MAPPO:
         critic.kernel_updates += repeat * n_mb
         ha, hc = sums_a.cpu().numpy(), sums_c.cpu().numpy()
         if self._peers is not None:
-            self._peers.check()
+            try:
+                self._peers.check()
+            except _lib.TsmError:  # the exchange lost a peer: the update is void (see PPO.update)
+                if snaps is None:
+                    raise
+                actor.restore(snaps[0])
+                critic.restore(snaps[1])
+                self._steps, self._adam_seq = snaps[2]
+                raise
         del keep
         n_per = np.concatenate(rows_seq).astype(np.float64)
         clip_l, ent_l, vf_l = ha[:, 0] / n_per, ha[:, 2] / n_per, hc[:, 1] / n_per

@@ -433,7 +433,7 @@ class PPO:
         # (a hung device would be worse); the update is then void.  Keep what it takes to undo it (4 x 23 KB for the C2 net).
         snap = None
         if world > 1 and self.grad_sync != "nccl":
-            snap = (net.flat.detach().clone(), net.adam_m.clone(), net.adam_v.clone(), net.adam_step.clone(), net.kernel_updates)
+            snap = net.snapshot()
         for ep in range(repeat):
             if self.recompute_adv and ep > 0:
                 # ppo.py:174-178 -> a2c.py:113-151 with the CURRENT parameters: v_s, returns and advantages (logp_old stays)
@@ -503,13 +503,7 @@ class PPO:
                 self._peers.check()
             except _lib.TsmError:
                 if snap is not None:  # parameters and optimizer state as they were before this update; the error still reaches the caller
-                    with torch.no_grad():
-                        net.flat.copy_(snap[0])
-                        net.adam_m.copy_(snap[1])
-                        net.adam_v.copy_(snap[2])
-                        net.adam_step.copy_(snap[3])
-                        net.grads.zero_()
-                    net.kernel_updates = snap[4]  # (the write to `flat` makes the next kernel call rebuild the fp16 image)
+                    net.restore(snap)
                 raise
         n_per = np.tile(np.diff(np.asarray(bounds)), repeat).astype(np.float64)
         clip_l, vf_l, ent_l = h[:, 0] / n_per, h[:, 1] / n_per, h[:, 2] / n_per

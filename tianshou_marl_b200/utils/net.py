@@ -133,6 +133,20 @@ class ActorCriticNet(nn.Module):
             self._packed_version = self.flat._version
         return C.byref(self._desc)
 
+    def snapshot(self) -> tuple:
+        """Parameters and optimizer state as device copies (what restore() takes): data-parallel updates keep one so that an
+        update whose gradient exchange lost a peer can be undone."""
+        return (self.flat.detach().clone(), self.adam_m.clone(), self.adam_v.clone(), self.adam_step.clone(), self.kernel_updates)
+
+    def restore(self, snap: tuple) -> None:
+        with torch.no_grad():
+            self.flat.copy_(snap[0])  # (bumps flat's version: the next kernel call rebuilds the fp16 operand image)
+            self.adam_m.copy_(snap[1])
+            self.adam_v.copy_(snap[2])
+            self.adam_step.copy_(snap[3])
+            self.grads.zero_()
+        self.kernel_updates = snap[4]
+
     @property
     def param_version(self) -> tuple[int, int]:
         """Changes whenever the parameters do: host-side writes (torch's version counter) or kernel optimizer steps."""
