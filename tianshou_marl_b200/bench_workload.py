@@ -7,7 +7,6 @@ from __future__ import annotations
 
 from typing import Any
 
-
 from . import _lib
 from .algorithm import PPO, AdamOptimizerFactory, DiscreteActorPolicy
 from .data import Collector, VectorReplayBuffer
