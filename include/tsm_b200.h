@@ -314,6 +314,10 @@ typedef struct tsm_net {
     float mu_bound;      /* Gaussian nets: 0 = the head outputs are the means (unbounded=True); > 0: mean = mu_bound * tanh(output),
                             the reference's default unbounded=False with max_action = mu_bound (continuous.py:239-241).
                             tsm_net_forward (mode 0) returns the raw outputs either way */
+    int32_t cond_sigma;  /* 1: Gaussian net with a state-dependent scale (conditioned_sigma=True, continuous.py:228-233,242): head
+                            outputs [0, n_act) are the means, [n_act, 2 n_act) the log standard deviations before
+                            clamp(-20, 2) (SIGMA_MIN / SIGMA_MAX), the value head (if any) follows at value_index = 2 n_act;
+                            n_sigma stays 0.  Engine 0 only, 2 n_act + 1 <= 8 */
 } tsm_net;
 #define TSM_TC_IMAGE_BYTES 123648 /* 16 896 image + tsm_ppo_epoch's three more gradient-sized buffers of 7 168 floats + 256 bytes of barrier words + a 20 KB index table */
 

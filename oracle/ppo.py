@@ -27,11 +27,14 @@ from . import gae as ogae
 class Net:
     """Parameters in torch.nn.Linear convention; W3/b3 stack the actor rows then the critic row."""
 
-    def __init__(self, W1, b1, W2, b2, W3, b3, n_act: int, log_sigma=None, mu_bound: float = 0.0) -> None:
+    def __init__(self, W1, b1, W2, b2, W3, b3, n_act: int, log_sigma=None, mu_bound: float = 0.0, cond_sigma: bool = False) -> None:
         arrs = (W1, b1, W2, b2, W3, b3) + ((np.asarray(log_sigma).reshape(-1),) if log_sigma is not None else ())
         self.p = [torch.tensor(np.asarray(a), dtype=torch.float32).clone().requires_grad_(True) for a in arrs]
         self.n_act = n_act
-        self.gaussian = log_sigma is not None
+        # cond_sigma (conditioned_sigma=True, continuous.py:228-233,242): head rows [mu | log sigma | value], sigma = exp(clamp(., -20, 2))
+        self.cond_sigma = bool(cond_sigma)
+        self._ls = None  # per-row log sigma of the last forward (cond_sigma)
+        self.gaussian = log_sigma is not None or self.cond_sigma
         self.mu_bound = float(mu_bound)  # > 0: unbounded=False, mu = max_action * tanh(head output) (continuous.py:239-241)
         self.m = [torch.zeros_like(x) for x in self.p]
         self.v = [torch.zeros_like(x) for x in self.p]
@@ -45,7 +48,10 @@ class Net:
         head = o[:, : self.n_act]
         if self.gaussian and self.mu_bound > 0:
             head = self.mu_bound * torch.tanh(head)
-        return head, (o[:, self.n_act] if o.shape[1] > self.n_act else torch.zeros(o.shape[0]))  # (actor-only net: no value row)
+        vi = self.n_act * (2 if self.cond_sigma else 1)
+        if self.cond_sigma:
+            self._ls = torch.clamp(o[:, self.n_act: vi], min=-20.0, max=2.0)
+        return head, (o[:, vi] if o.shape[1] > vi else torch.zeros(o.shape[0]))  # (actor-only net: no value row)
 
     def flat(self) -> np.ndarray:
         return np.concatenate([x.detach().numpy().reshape(-1) for x in self.p])
@@ -75,7 +81,7 @@ def policy_dist(net: Net, logits: torch.Tensor, probs_param: bool):
     """dist_fn of the policy: Categorical for discrete heads, Independent(Normal(mu, sigma), 1) for a Gaussian net
     (sigma = exp(sigma_param) broadcast over the rows, continuous.py:244-246)."""
     if net.gaussian:
-        sigma = (net.p[6].view(1, -1) + torch.zeros_like(logits)).exp()
+        sigma = net._ls.exp() if net.cond_sigma else (net.p[6].view(1, -1) + torch.zeros_like(logits)).exp()
         return torch.distributions.Independent(torch.distributions.Normal(logits, sigma), 1)
     return log_softmax_dist(logits, probs_param)
 

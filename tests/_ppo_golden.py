@@ -44,15 +44,21 @@ def load_gauss(g, ci):
              cfg=dict(eps_clip=eps_clip, dual_clip=dual_clip, vf_coef=vf_coef, ent_coef=ent_coef, value_clip=bool(value_clip),
                       adv_norm=bool(adv_norm)))
     c["mu_bound"] = float(g[pre + "mu_bound"]) if pre + "mu_bound" in g.files else 0.0  # > 0: unbounded=False, max_action
-    for k in ("W1", "b1", "W2", "b2", "Wa", "ba", "Wv", "bv", "log_sigma"):
+    c["cond_sigma"] = bool(int(g[pre + "cond_sigma"])) if pre + "cond_sigma" in g.files else False  # conditioned_sigma=True
+    for k in ("W1", "b1", "W2", "b2", "Wa", "ba", "Wv", "bv") + (() if c["cond_sigma"] else ("log_sigma",)):
         c[k] = g[pre + k]
         c["after_" + k] = g[pre + "after_" + k]
+    if c["cond_sigma"]:  # the sigma head (fixture keys Ws / bs; "bs" is the batch size in this dict)
+        for a in ("", "after_"):
+            c[a + "Wsig"], c[a + "bsig"] = g[pre + a + "Ws"], g[pre + a + "bs"]
     for k in ("obs", "act", "rew", "term", "trunc", "obs_next", "indices", "v_s", "returns", "adv", "logp_old",
               "loss_seq", "clip_seq", "vf_seq", "ent_seq", "fwd_mu", "fwd_sigma", "fwd_value"):
         c[k] = g[pre + k]
-    for a in ("", "after_"):
-        c[a + "W3"] = np.concatenate([c[a + "Wa"], c[a + "Wv"]], 0)
-        c[a + "b3"] = np.concatenate([c[a + "ba"], c[a + "bv"]], 0)
+    for a in ("", "after_"):  # head rows: [mu | log sigma (conditioned_sigma) | value]
+        mid_w, mid_b = ([c[a + "Wsig"]], [c[a + "bsig"]]) if c["cond_sigma"] else ([], [])
+        c[a + "W3"] = np.concatenate([c[a + "Wa"]] + mid_w + [c[a + "Wv"]], 0)
+        c[a + "b3"] = np.concatenate([c[a + "ba"]] + mid_b + [c[a + "bv"]], 0)
+    c["param_names"] = ("W1", "b1", "W2", "b2", "W3", "b3") + (() if c["cond_sigma"] else ("log_sigma",))
     B = R * T
     assert np.array_equal(c["indices"], np.arange(B))
     em = lambda a: np.swapaxes(a, 0, 1).reshape(B, *a.shape[2:])  # noqa: E731  [T][R] -> env-major flat

@@ -18,10 +18,13 @@ CASES = [
     # unbounded=False (the reference's default): mu = max_action * tanh(head output)
     dict(R=12, T=16, O=18, H=64, A=2, bs=64, repeat=2, bound=1.0, kw=dict(max_grad_norm=0.5, lr=1e-3)),
     dict(R=10, T=14, O=11, H=64, A=3, bs=48, repeat=3, bound=2.0, kw=dict(value_clip=True, dual_clip=2.0, ent_coef=0.02, lr=1e-3)),
+    # conditioned_sigma=True: sigma = exp(clamp(Linear(features), -20, 2)); case 6 with the bounded mean as well
+    dict(R=12, T=16, O=18, H=64, A=2, bs=64, repeat=2, cond=True, kw=dict(max_grad_norm=0.5, lr=1e-3)),
+    dict(R=10, T=14, O=11, H=64, A=3, bs=48, repeat=3, cond=True, bound=1.5, kw=dict(value_clip=True, ent_coef=0.03, lr=1e-3)),
 ]
 
 
-def _ref(O: int, H: int, A: int, seed: int, bound: float = 0.0, **kw):
+def _ref(O: int, H: int, A: int, seed: int, bound: float = 0.0, cond: bool = False, **kw):
     import gymnasium as gym
     import torch
     from tianshou.algorithm import PPO
@@ -33,8 +36,8 @@ def _ref(O: int, H: int, A: int, seed: int, bound: float = 0.0, **kw):
 
     torch.manual_seed(seed)
     net = Net(state_shape=(O,), hidden_sizes=[H, H])
-    actor = (ContinuousActorProbabilistic(preprocess_net=net, action_shape=(A,), unbounded=False, max_action=bound) if bound > 0
-             else ContinuousActorProbabilistic(preprocess_net=net, action_shape=(A,), unbounded=True))
+    actor = (ContinuousActorProbabilistic(preprocess_net=net, action_shape=(A,), unbounded=False, max_action=bound, conditioned_sigma=cond)
+             if bound > 0 else ContinuousActorProbabilistic(preprocess_net=net, action_shape=(A,), unbounded=True, conditioned_sigma=cond))
     critic = ContinuousCritic(preprocess_net=net)
     ac = ActorCritic(actor, critic)
     for m in ac.modules():  # test/continuous/test_ppo.py:95-99 (orthogonal weights), biases non-zero so that their paths are exercised
@@ -42,7 +45,13 @@ def _ref(O: int, H: int, A: int, seed: int, bound: float = 0.0, **kw):
             torch.nn.init.orthogonal_(m.weight)
             torch.nn.init.normal_(m.bias, std=0.1)
     with torch.no_grad():
-        actor.sigma_param.copy_(torch.linspace(-0.5, 0.3, A).view(A, 1))  # distinct scales per action dimension
+        if cond:  # a wide spread of log sigma over the rows: part of them beyond the clamp at 2 (no gradient there)
+            for m in actor.sigma.modules():
+                if isinstance(m, torch.nn.Linear):
+                    m.weight.mul_(3.0)
+                    m.bias.add_(1.3)
+        else:
+            actor.sigma_param.copy_(torch.linspace(-0.5, 0.3, A).view(A, 1))  # distinct scales per action dimension
 
     def dist(loc_scale):  # test_ppo.py:104-106
         loc, scale = loc_scale
@@ -63,7 +72,8 @@ def _flat(ac) -> dict[str, np.ndarray]:
         "W2": pick("model.model.2.weight", "actor.preprocess"), "b2": pick("model.model.2.bias", "actor.preprocess"),
         "Wa": pick("mu.model.0.weight", "actor"), "ba": pick("mu.model.0.bias", "actor"),
         "Wv": pick("last.model.0.weight", "critic"), "bv": pick("last.model.0.bias", "critic"),
-        "log_sigma": pick("sigma_param", "actor").reshape(-1),
+        **({"Ws": pick("sigma.model.0.weight", "actor"), "bs": pick("sigma.model.0.bias", "actor")} if any(k.startswith("actor.sigma.") for k in sd)
+           else {"log_sigma": pick("sigma_param", "actor").reshape(-1)}),
     }
 
 
@@ -77,7 +87,7 @@ def gen() -> None:
     for ci, c in enumerate(CASES):
         R, T, O, H, A = c["R"], c["T"], c["O"], c["H"], c["A"]
         rng = np.random.default_rng(300 + ci)
-        alg, ac = _ref(O, H, A, seed=40 + ci, bound=c.get("bound", 0.0), **dict(c["kw"]))
+        alg, ac = _ref(O, H, A, seed=40 + ci, bound=c.get("bound", 0.0), cond=c.get("cond", False), **dict(c["kw"]))
         pre = f"p{ci}_"
         for k, v in _flat(ac).items():
             out[pre + k] = v
@@ -103,6 +113,10 @@ def gen() -> None:
             out[pre + "fwd_mu"] = mu.numpy().copy()
             out[pre + "fwd_sigma"] = sigma.numpy().copy()
             out[pre + "fwd_value"] = alg.critic(x).flatten().numpy().copy()
+            if c.get("cond", False):  # how much of the batch sits beyond the clamp (those rows pass no gradient to the sigma head)
+                feats, _ = alg.policy.actor.preprocess(torch.from_numpy(np.concatenate(store["obs"])))
+                raw = alg.policy.actor.sigma(feats)
+                out[pre + "ls_clamped_frac"] = np.array(float(((raw > 2.0) | (raw < -20.0)).float().mean()))
         seqs: list[list[float]] = []
         orig = SequenceSummaryStats.from_sequence.__func__
 
@@ -130,6 +144,7 @@ def gen() -> None:
         kw = c["kw"]
         out[pre + "cfg"] = np.array([R, T, O, H, A, c["bs"], c["repeat"], 0, 70 + ci], np.int64)
         out[pre + "mu_bound"] = np.array(c.get("bound", 0.0))
+        out[pre + "cond_sigma"] = np.array(int(c.get("cond", False)))
         out[pre + "hyper"] = np.array([kw.get("eps_clip", 0.2), kw.get("dual_clip") or 0.0, kw.get("vf_coef", 0.5), kw.get("ent_coef", 0.01),
                                        float(kw.get("value_clip", False)), float(kw.get("advantage_normalization", True)),
                                        kw.get("max_grad_norm") or 0.0, kw.get("lr", 3e-4), 0.99, 0.95])

@@ -16,10 +16,11 @@ def _mk(c):
     from tianshou_marl_b200.data import Batch, VectorReplayBuffer
     from tianshou_marl_b200.utils import ActorCriticNet
 
-    net = ActorCriticNet(c["O"], c["H"], c["nA"], gaussian=True, unbounded=c["mu_bound"] == 0.0,
-                         max_action=c["mu_bound"] or 1.0).load_arrays(c["W1"], c["b1"], c["W2"], c["b2"], c["W3"], c["b3"])
-    with torch.no_grad():
-        net.view("log_sigma").copy_(torch.as_tensor(c["log_sigma"]))
+    net = ActorCriticNet(c["O"], c["H"], c["nA"], gaussian=True, unbounded=c["mu_bound"] == 0.0, max_action=c["mu_bound"] or 1.0,
+                         conditioned_sigma=c["cond_sigma"]).load_arrays(c["W1"], c["b1"], c["W2"], c["b2"], c["W3"], c["b3"])
+    if not c["cond_sigma"]:
+        with torch.no_grad():
+            net.view("log_sigma").copy_(torch.as_tensor(c["log_sigma"]))
     pol = ContinuousActorPolicy(actor=net)
     k = c["cfg"]
     alg = PPO(policy=pol, critic=net, optim=AdamOptimizerFactory(lr=c["lr"]), eps_clip=k["eps_clip"], dual_clip=k["dual_clip"] or None,
@@ -32,7 +33,7 @@ def _mk(c):
     return net, pol, alg, buf
 
 
-@pytest.mark.parametrize("ci", [0, 1, 2, 3, 4])
+@pytest.mark.parametrize("ci", [0, 1, 2, 3, 4, 5, 6])
 def test_gaussian_update_matches_reference(golden, ci):
     """Whole PPO.update vs the reference: v_s, returns, adv, logp_old, every minibatch loss, final parameters incl. log sigma."""
     c = load_gauss(golden("ppo_gauss.npz"), ci)
@@ -43,7 +44,9 @@ def test_gaussian_update_matches_reference(golden, ci):
     raw = net.forward(torch.as_tensor(c["obs"][0], device="cuda"), mode="raw")["out"]
     o = raw.cpu().numpy()
     assert np.allclose(net.gaussian_mean(raw).cpu().numpy(), c["fwd_mu"], rtol=2e-5, atol=2e-6)  # cases 3, 4: max_action * tanh(head)
-    assert np.allclose(o[:, c["nA"]], c["fwd_value"], rtol=2e-5, atol=2e-6)
+    assert np.allclose(o[:, net.value_index], c["fwd_value"], rtol=2e-5, atol=2e-6)
+    if c["cond_sigma"]:  # cases 5, 6: per-row sigma = exp(clamp(head, -20, 2)), 7-18 % of the entries on the clamp
+        assert np.allclose(net.gaussian_log_sigma(raw).exp().cpu().numpy(), c["fwd_sigma"], rtol=2e-5)
     pol.is_within_training_step = True
     np.random.seed(c["seed"])
     stats = alg.update(buf, c["bs"], c["repeat"])
@@ -57,10 +60,14 @@ def test_gaussian_update_matches_reference(golden, ci):
     for k, ref in (("loss", "loss_seq"), ("clip", "clip_seq"), ("vf", "vf_seq"), ("ent", "ent_seq")):
         assert np.allclose(seq[k], c[ref], rtol=2e-4, atol=2e-5), (k, np.abs(seq[k] - c[ref]).max())
     v = net.named_views()
-    for k in ("W1", "b1", "W2", "b2", "W3", "b3", "log_sigma"):
+    for k in c["param_names"]:
         err = np.abs(v[k].cpu().numpy() - c["after_" + k]).max()
         assert err < 5e-5, (k, err)
-    assert np.abs(v["log_sigma"].cpu().numpy() - c["log_sigma"]).max() > 1e-4  # sigma really moved
+    if c["cond_sigma"]:
+        A = c["nA"]
+        assert np.abs(v["W3"].cpu().numpy()[A: 2 * A] - c["Wsig"]).max() > 1e-4  # the sigma head really moved
+    else:
+        assert np.abs(v["log_sigma"].cpu().numpy() - c["log_sigma"]).max() > 1e-4  # sigma really moved
     assert float(net.grads.abs().max().item()) == 0.0
 
 

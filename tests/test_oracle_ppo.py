@@ -120,19 +120,23 @@ def test_oracle_matches_reference_reinforce(golden, ci):
         assert np.allclose(p.detach().numpy(), c["after_" + k], rtol=0, atol=2e-5), k
 
 
-@pytest.mark.parametrize("ci", [0, 1, 2, 3, 4])
+@pytest.mark.parametrize("ci", [0, 1, 2, 3, 4, 5, 6])
 def test_oracle_matches_reference_ppo_gaussian(golden, ci):
     """Continuous actions: Independent(Normal(mu, exp(sigma_param)), 1) (tests/golden/ppo_gauss.npz, recorded from the reference's
     ContinuousActorProbabilistic + PPO; cases 3 and 4: unbounded=False, mu = max_action * tanh(head) with max_action 1 and 2)."""
     import torch
 
     c = load_gauss(golden("ppo_gauss.npz"), ci)
-    net = oppo.Net(c["W1"], c["b1"], c["W2"], c["b2"], c["W3"], c["b3"], c["nA"], log_sigma=c["log_sigma"], mu_bound=c["mu_bound"])
+    net = oppo.Net(c["W1"], c["b1"], c["W2"], c["b2"], c["W3"], c["b3"], c["nA"], log_sigma=None if c["cond_sigma"] else c["log_sigma"],
+                   mu_bound=c["mu_bound"], cond_sigma=c["cond_sigma"])
     f = c["flat"]
     with torch.no_grad():
         mu, value = net.forward(torch.from_numpy(c["obs"][0]))
     assert np.allclose(mu.numpy(), c["fwd_mu"], rtol=1e-5, atol=1e-6) and np.allclose(value.numpy(), c["fwd_value"], rtol=1e-5, atol=1e-6)
-    assert np.allclose(np.exp(c["log_sigma"])[None, :].repeat(len(c["fwd_sigma"]), 0), c["fwd_sigma"], rtol=1e-6)
+    if c["cond_sigma"]:  # cases 5, 6: sigma = exp(clamp(head, -20, 2)) per row; part of the rows sit on the clamp
+        assert np.allclose(net._ls.exp().numpy(), c["fwd_sigma"], rtol=1e-5) and abs(float(c["fwd_sigma"].max()) - float(np.exp(2.0))) < 1e-5
+    else:
+        assert np.allclose(np.exp(c["log_sigma"])[None, :].repeat(len(c["fwd_sigma"]), 0), c["fwd_sigma"], rtol=1e-6)
     v_s, ret, adv, logp_old = oppo.preprocess(net, f["obs"], f["obs_next"], f["act"], f["rew"], f["term"], f["trunc"], c["indices"],
                                               c["unfinished"], c["gamma"], c["lam"])
     assert np.allclose(v_s, c["v_s"], rtol=2e-5, atol=2e-6) and np.allclose(ret, c["returns"], rtol=2e-5, atol=2e-5)
@@ -142,6 +146,7 @@ def test_oracle_matches_reference_ppo_gaussian(golden, ci):
     assert len(log["loss"]) == len(c["loss_seq"])
     for k, ref in (("loss", "loss_seq"), ("clip", "clip_seq"), ("vf", "vf_seq"), ("ent", "ent_seq")):
         assert np.allclose(log[k], c[ref], rtol=1e-4, atol=1e-5), (k, np.abs(np.array(log[k]) - c[ref]).max())
-    for k, p in zip(("W1", "b1", "W2", "b2", "W3", "b3", "log_sigma"), net.p):
+    for k, p in zip(c["param_names"], net.p):
         assert np.allclose(p.detach().numpy(), c["after_" + k], rtol=0, atol=2e-5), (k, np.abs(p.detach().numpy() - c["after_" + k]).max())
-    assert np.abs(c["after_log_sigma"] - c["log_sigma"]).max() > 1e-4  # the fixture really moves sigma
+    moved = (c["after_Wsig"] - c["Wsig"]) if c["cond_sigma"] else (c["after_log_sigma"] - c["log_sigma"])
+    assert np.abs(moved).max() > 1e-4  # the fixture really moves sigma

@@ -54,7 +54,7 @@ class TsmNet(C.Structure):
         ("value_index", C.c_int32), ("engine", C.c_int32), ("n_params", c_i64),
         ("params", c_vp), ("grads", c_vp), ("adam_m", c_vp), ("adam_v", c_vp), ("adam_step", c_vp),
         ("tc_image", c_vp), ("x_scratch", c_vp), ("x_scratch_bytes", c_i64), ("probs_param", C.c_int32), ("n_sigma", C.c_int32),
-        ("mu_bound", C.c_float),
+        ("mu_bound", C.c_float), ("cond_sigma", C.c_int32),
     ]
 
 

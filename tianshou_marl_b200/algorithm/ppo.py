@@ -95,7 +95,8 @@ class ContinuousActorPolicy(DiscreteActorPolicy):
     """ProbabilisticActorPolicy over a Box action space (reinforce.py:118-215) with the reference's standard continuous head:
     ContinuousActorProbabilistic(conditioned_sigma=False), unbounded or tanh-bounded means (utils/net/continuous.py:196-247), and
     dist_fn = Independent(Normal(mu, sigma), 1) (test/continuous/test_ppo.py:104-110).  `actor` is an ActorCriticNet(gaussian=True):
-    its n_act outputs are the means, `log_sigma` the state-independent log standard deviations.  forward samples
+    its n_act outputs are the means, `log_sigma` the state-independent log standard deviations (or, with conditioned_sigma=True,
+    n_act more head outputs per row).  forward samples
     mu + sigma * N(0, 1) (the mean when deterministic_eval and not in a training step); map_action clips / scales like
     Policy.map_action (algorithm_base.py:255-288, tsm_map_action).  The network pass is the library's forward kernel; the
     sampling and the log-density are elementwise device ops on its [n, A] output."""
@@ -131,7 +132,7 @@ class ContinuousActorPolicy(DiscreteActorPolicy):
         net = self.actor
         o = net.forward(obs.to(torch.float32).contiguous(), mode="raw")["out"]
         mu = net.gaussian_mean(o)
-        ls = net.view("log_sigma")
+        ls = net.gaussian_log_sigma(o)
         if self.deterministic_eval and not self.is_within_training_step:
             act = mu.clone()
         else:
@@ -322,7 +323,7 @@ class PPO:
             raw = net.forward(obs_all, mode="raw")["out"]
             v_s.view(-1).copy_(raw[:, net.value_index])
             A_ = net.n_act
-            logp.view(-1).copy_(ContinuousActorPolicy.log_prob(net.gaussian_mean(raw), net.view("log_sigma"), st["act_f"].view(-1, A_)))
+            logp.view(-1).copy_(ContinuousActorPolicy.log_prob(net.gaussian_mean(raw), net.gaussian_log_sigma(raw), st["act_f"].view(-1, A_)))
             _lib.t_stop(tk)
             tk = _lib.t_start("critic_forward")
             next_values(v_s, dedup_ok)

@@ -376,6 +376,7 @@ struct PpoArgs {
     const float* act_f;     // Gaussian nets: [size][n_rows][n_act]
     int n_sigma;            // > 0: Gaussian policy, log sigma at params[offsets.total ...]
     float mu_bound;         // Gaussian policy: > 0 = mean is mu_bound * tanh(output)
+    int cond_sigma;         // Gaussian policy with per-row log sigma in head outputs [n_act, 2 n_act)
     const float* adv;
     const float* ret;
     const float* logp_old;
@@ -441,12 +442,12 @@ __global__ void __launch_bounds__(THREADS) ppo_minibatch_kernel(PpoArgs a) {
             const float4 z1 = *reinterpret_cast<const float4*>(sDOT + r * OUTP + 4);
             z[0] = z0.x; z[1] = z0.y; z[2] = z0.z; z[3] = z0.w; z[4] = z1.x; z[5] = z1.y; z[6] = z1.z; z[7] = z1.w;
             // the loss itself is shared with the tcgen05 engine (ppo_math.cuh); IEEE exp / log / division here
-            const int act = (a.n_act > 0 && !a.n_sigma) ? a.act[s] : 0;
+            const int act = (a.n_act > 0 && !a.n_sigma && !a.cond_sigma) ? a.act[s] : 0;
             const float adv_s = a.n_act > 0 ? a.adv[s] : 0.f, lpo = a.n_act > 0 ? a.logp_old[s] : 0.f;
             const float ret_s = a.value_index >= 0 ? a.ret[s] : 0.f;
             const float vo = (a.value_index >= 0 && a.cfg.value_clip) ? a.v_old[s] : 0.f;
-            const RowLoss rl = a.n_sigma ? row_loss_gauss(z, a.n_act, a.value_index, a.act_f + s * a.n_act, a.params + sigma_off, adv_s, ret_s, lpo, vo,
-                                                          mean, rstd, a.cfg, inv_n, dz, dls, a.mu_bound)
+            const RowLoss rl = (a.n_sigma || a.cond_sigma) ? row_loss_gauss(z, a.n_act, a.value_index, a.act_f + s * a.n_act, a.params + sigma_off, adv_s, ret_s, lpo, vo,
+                                                          mean, rstd, a.cfg, inv_n, dz, dls, a.mu_bound, a.cond_sigma != 0)
                                          : row_loss<false>(z, a.n_act, a.value_index, act, adv_s, ret_s, lpo, vo, mean, rstd, a.cfg, inv_n, dz);
             l_clip += (double)rl.clip;
             l_ent += (double)rl.ent;
@@ -747,8 +748,11 @@ static int check_net(const tsm_net* n, const char* fn) {
     if (n->engine == 1 && !n->tc_image) return fail(TSM_ERR_INVALID, "%s: engine 1 needs tc_image", fn);
     if (n->n_sigma != 0 && (n->n_sigma != n->n_act || n->engine != 0 || n->probs_param))
         return fail(TSM_ERR_INVALID, "%s: n_sigma must be 0 or n_act, on engine 0, without probs_param", fn);
-    if (!(n->mu_bound >= 0.f) || (n->mu_bound > 0.f && n->n_sigma == 0))
-        return fail(TSM_ERR_INVALID, "%s: mu_bound must be >= 0, and 0 unless the net is Gaussian (n_sigma > 0)", fn);
+    if (n->cond_sigma != 0 && (n->cond_sigma != 1 || n->n_sigma != 0 || n->engine != 0 || n->probs_param || n->n_act < 1 ||
+                               n->out_dim < 2 * n->n_act || (n->value_index >= 0 && n->value_index < 2 * n->n_act)))
+        return fail(TSM_ERR_INVALID, "%s: cond_sigma needs engine 0, n_sigma == 0, no probs_param, out_dim >= 2 n_act and the value head behind the sigma outputs", fn);
+    if (!(n->mu_bound >= 0.f) || (n->mu_bound > 0.f && n->n_sigma == 0 && n->cond_sigma == 0))
+        return fail(TSM_ERR_INVALID, "%s: mu_bound must be >= 0, and 0 unless the net is Gaussian (n_sigma > 0 or cond_sigma)", fn);
     if (n->n_params != offsets(n->in_dim, n->hidden, n->out_dim).total + n->n_sigma)
         return fail(TSM_ERR_INVALID, "%s: n_params does not match the layout (want %lld)", fn,
                     (long long)offsets(n->in_dim, n->hidden, n->out_dim).total + n->n_sigma);
@@ -784,7 +788,7 @@ static int net_forward_impl(const tsm_net* net, const float* x, const int64_t* r
     TSM_REQUIRE(x != nullptr, "x != NULL");
     TSM_REQUIRE(mode == 0 || net->n_act > 0, "sampling / evaluation needs n_act > 0");
     TSM_REQUIRE(mode != 3 || act != nullptr, "mode 3 (evaluate) needs act");
-    TSM_REQUIRE(net->n_sigma == 0 || mode == 0, "Gaussian nets (n_sigma > 0): mode 0 only");
+    TSM_REQUIRE((net->n_sigma == 0 && net->cond_sigma == 0) || mode == 0, "Gaussian nets (n_sigma > 0 or cond_sigma): mode 0 only");
     if (net->engine == 1)
         return tc_net_forward(net, x, rows, n, mode, scatter, seed, counter, out, act, logp, value, entropy, rng_row0, as_stream(stream));
     FwdArgs a{};
@@ -919,14 +923,14 @@ extern "C" int tsm_ppo_minibatch(const tsm_net* net, const tsm_ppo_batch* batch,
     TSM_REQUIRE(!(cfg->adv_norm || cfg->plain_pg == 2) || mb_stats, "advantage normalisation / plain_pg 2 need mb_stats");
     if (net->engine == 1) return tc_ppo_minibatch(net, batch, cfg, mb_start, mb_len, mb_stats, loss_sums, 0, as_stream(stream));
     TSM_REQUIRE(batch->obs != nullptr, "batch.obs != NULL");
-    TSM_REQUIRE(net->n_act == 0 || ((net->n_sigma ? (const void*)batch->act_f : (const void*)batch->act) && batch->adv && batch->logp_old),
+    TSM_REQUIRE(net->n_act == 0 || (((net->n_sigma || net->cond_sigma) ? (const void*)batch->act_f : (const void*)batch->act) && batch->adv && batch->logp_old),
                 "policy loss needs act (act_f for Gaussian nets) / adv / logp_old");
     TSM_REQUIRE(net->value_index < 0 || batch->ret, "value loss needs ret");
     TSM_REQUIRE(!cfg->value_clip || batch->v_old, "value_clip needs v_old");
     PpoArgs a{};
     a.params = net->params; a.grads = net->grads;
     a.obs = batch->obs; a.act = batch->act; a.adv = batch->adv; a.ret = batch->ret; a.logp_old = batch->logp_old; a.v_old = batch->v_old;
-    a.act_f = batch->act_f; a.n_sigma = net->n_sigma; a.mu_bound = net->mu_bound;
+    a.act_f = batch->act_f; a.n_sigma = net->n_sigma; a.mu_bound = net->mu_bound; a.cond_sigma = net->cond_sigma;
     a.view = make_view(batch);
     a.mb_start = mb_start; a.mb_len = mb_len; a.mb_stats = mb_stats;
     a.cfg.eps_clip = cfg->eps_clip; a.cfg.dual_clip = cfg->dual_clip; a.cfg.vf_coef = cfg->vf_coef; a.cfg.ent_coef = cfg->ent_coef;

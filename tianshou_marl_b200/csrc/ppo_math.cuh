@@ -3,6 +3,7 @@
 // loss with its gradient w.r.t. the head outputs (tianshou/algorithm/modelfree/ppo.py:181-211).
 #pragma once
 #include <stdint.h>
+#include <math_constants.h>
 #include "feistel.cuh"
 
 namespace tsm {
@@ -240,7 +241,7 @@ __device__ __forceinline__ RowLoss row_loss(const float (&z)[OUTP], int n_act_in
 __device__ __forceinline__ RowLoss row_loss_gauss(const float (&z)[OUTP], int n_act, int value_index, const float* __restrict__ a,
                                                   const float* __restrict__ log_sigma, float adv, float ret, float logp_old, float v_old,
                                                   float mean, float rstd, const PpoCfg& cfg, float inv_n, float (&dz)[OUTP], float (&dls)[OUTP],
-                                                  float mu_bound = 0.f) {
+                                                  float mu_bound = 0.f, bool cond_sigma = false) {
     RowLoss out{0.f, 0.f, 0.f};
 #pragma unroll
     for (int j = 0; j < OUTP; ++j) dz[j] = 0.f;
@@ -253,11 +254,20 @@ __device__ __forceinline__ RowLoss row_loss_gauss(const float (&z)[OUTP], int n_
             // unbounded=False (continuous.py:239-241): mu = max_action * tanh(z), d mu / d z = max_action * (1 - tanh^2 z)
             const float th = mu_bound > 0.f ? tanhf(z[j]) : 0.f;
             const float mu = mu_bound > 0.f ? mu_bound * th : z[j], dmu_dz = mu_bound > 0.f ? mu_bound * (1.f - th * th) : 1.f;
-            const float ls = log_sigma[j], sg = expf(ls), var = sg * sg, d = a[j] - mu;
+            // conditioned_sigma=True (continuous.py:242): log sigma = clamp(head output n_act + j, -20, 2), per row
+            float ls_raw = 0.f;
+            if (cond_sigma) {
+#pragma unroll
+                for (int k = 0; k < OUTP; ++k)
+                    if (k == n_act + j) ls_raw = z[k];
+            }
+            const float ls = cond_sigma ? fminf(fmaxf(ls_raw, -20.f), 2.f) : log_sigma[j];
+            const float sg = expf(ls), var = sg * sg, d = a[j] - mu;
             lp += -(d * d) / (2.f * var) - ls - 0.9189385332046727f;  // log sqrt(2 pi)
             ent += 0.5f + 0.9189385332046727f + ls;                   // 0.5 + 0.5 log(2 pi) + log sigma
             dmu[j] = d / var * dmu_dz;
             dsg[j] = d * d / var - 1.f;
+            if (cond_sigma && (ls_raw < -20.f || ls_raw > 2.f)) dsg[j] = CUDART_NAN_F;  // marks "clamped": no gradient (below)
         }
     }
     float advn = adv;
@@ -287,7 +297,13 @@ __device__ __forceinline__ RowLoss row_loss_gauss(const float (&z)[OUTP], int n_
     for (int j = 0; j < OUTP; ++j)
         if (j < n_act) {
             dz[j] = dlp * dmu[j];
-            dls[j] += dlp * dsg[j] - ec;
+            if (!cond_sigma) {
+                dls[j] += dlp * dsg[j] - ec;
+            } else if (dsg[j] == dsg[j]) {  // inside the clamp: d loss / d (head output n_act + j); the entropy term is per row here
+#pragma unroll
+                for (int k = 0; k < OUTP; ++k)
+                    if (k == n_act + j) dz[k] = dlp * dsg[j] - ec;
+            }
         }
     if (value_index >= 0) {
         float v = 0.f;

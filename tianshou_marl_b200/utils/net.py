@@ -27,7 +27,7 @@ class ActorCriticNet(nn.Module):
     def __init__(self, in_dim: int, hidden: int = 64, n_act: int = 5, with_value: bool = True, n_value_only: int = 0,
                  device: str | torch.device = "cuda", seed: int | None = None, orthogonal: bool = True,
                  engine: str = "fp32", softmax_output: bool = False, gaussian: bool = False, unbounded: bool = True,
-                 max_action: float = 1.0) -> None:
+                 max_action: float = 1.0, conditioned_sigma: bool = False) -> None:
         """engine: "fp32" = exact CUDA-core kernels (csrc/mlp.cu); "tc" = tcgen05 tensor-core kernels with fp16 operands and
         fp32 accumulation (csrc/mlp_tc.cu; hidden 64, in_dim <= 31, out_dim <= 8); "tcw" = the wide tcgen05 engine of the CTDE
         nets (csrc/mlp_tcw.cu; hidden 128, in_dim <= 1023, out_dim <= 16, separate actor / value-only critic)."""
@@ -41,6 +41,11 @@ class ActorCriticNet(nn.Module):
         if gaussian and (engine != "fp32" or softmax_output or n_value_only):
             raise ValueError("gaussian=True needs engine 'fp32', an actor head and no softmax_output")
         self.gaussian = bool(gaussian)
+        # conditioned_sigma=True (continuous.py:228-233,242): n_act more head outputs are the per-row log standard deviations
+        # (clamped to [-20, 2]); there is no log_sigma parameter then.  Head rows: [mu | log sigma | value].
+        self.cond_sigma = bool(conditioned_sigma)
+        if self.cond_sigma and not gaussian:
+            raise ValueError("conditioned_sigma=True needs gaussian=True")
         # unbounded=False (the reference's default, continuous.py:222,239-241): mean = max_action * tanh(head output)
         self.mu_bound = float(max_action) if (self.gaussian and not unbounded) else 0.0
         if self.gaussian and not unbounded and not max_action > 0:
@@ -55,13 +60,14 @@ class ActorCriticNet(nn.Module):
         if n_value_only:  # critic-only net: out_dim value heads, no logits
             self.n_act, self.out_dim, self.value_index = 0, int(n_value_only), 0
         else:
-            self.out_dim = self.n_act + (1 if with_value else 0)
-            self.value_index = self.n_act if with_value else -1
+            heads = self.n_act * (2 if conditioned_sigma else 1)
+            self.out_dim = heads + (1 if with_value else 0)
+            self.value_index = heads if with_value else -1
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise _lib.TsmError("ActorCriticNet needs a CUDA device (no CPU fallback)")
         L = _lib.lib()
-        self.n_sigma = self.n_act if self.gaussian else 0
+        self.n_sigma = self.n_act if (self.gaussian and not self.cond_sigma) else 0
         n = int(L.tsm_net_param_count(self.in_dim, self.hidden, self.out_dim)) + self.n_sigma
         self.n_params = n
         self.flat = nn.Parameter(torch.zeros(n, dtype=torch.float32, device=self.device))
@@ -100,6 +106,13 @@ class ActorCriticNet(nn.Module):
         mu = raw[:, : self.n_act]
         return self.mu_bound * torch.tanh(mu) if self.mu_bound > 0 else mu
 
+    def gaussian_log_sigma(self, raw: torch.Tensor) -> torch.Tensor:
+        """Log standard deviations of the Gaussian head: the state-independent parameter [n_act], or per row [n, n_act] from the
+        raw outputs with conditioned_sigma=True (clamped like continuous.py:242)."""
+        if self.cond_sigma:
+            return raw[:, self.n_act: 2 * self.n_act].clamp(-20.0, 2.0)
+        return self.view("log_sigma")
+
     # -- plumbing ---------------------------------------------------------------------------
     ENGINES = {"fp32": 0, "tc": 1, "tcw": 2}
 
@@ -119,6 +132,7 @@ class ActorCriticNet(nn.Module):
         d.probs_param = int(self.softmax_output)
         d.n_sigma = int(self.n_sigma)
         d.mu_bound = float(self.mu_bound)
+        d.cond_sigma = int(self.cond_sigma)
 
     @property
     def desc(self) -> Any:
