@@ -96,7 +96,8 @@ def _oracle_rows(rew, v_s, v_n, term, trunc, gamma, lam):
     return ogae.gae(v_s.reshape(-1), (v_n * ~term).reshape(-1), rew.reshape(-1).astype(np.float64), end.reshape(-1), gamma, lam)
 
 
-@pytest.mark.parametrize("n_rows,T", [(1, 1), (3, 7), (257, 128), (4099, 128), (1000, 25), (5, 5000), (1, 300000)])
+@pytest.mark.parametrize("n_rows,T", [(1, 1), (3, 7), (257, 128), (4099, 128), (1000, 25), (5, 5000), (1, 300000),
+                                        (1, 1023), (1, 1024), (1, 1025), (2, 1024), (1, 2049), (3, 1024)])  # around the 1024-element tile
 @pytest.mark.parametrize("mode", ["seg_len", "force_end"])
 def test_flat_vs_oracle(n_rows, T, mode):
     from tianshou_marl_b200.algorithm import gae_flat
