@@ -45,6 +45,7 @@ def load_gauss(g, ci):
                       adv_norm=bool(adv_norm)))
     c["mu_bound"] = float(g[pre + "mu_bound"]) if pre + "mu_bound" in g.files else 0.0  # > 0: unbounded=False, max_action
     c["cond_sigma"] = bool(int(g[pre + "cond_sigma"])) if pre + "cond_sigma" in g.files else False  # conditioned_sigma=True
+    c["a2c"] = bool(int(g[pre + "a2c"])) if pre + "a2c" in g.files else False  # recorded from A2C instead of PPO (no logp_old)
     for k in ("W1", "b1", "W2", "b2", "Wa", "ba", "Wv", "bv") + (() if c["cond_sigma"] else ("log_sigma",)):
         c[k] = g[pre + k]
         c["after_" + k] = g[pre + "after_" + k]

@@ -21,10 +21,12 @@ CASES = [
     # conditioned_sigma=True: sigma = exp(clamp(Linear(features), -20, 2)); case 6 with the bounded mean as well
     dict(R=12, T=16, O=18, H=64, A=2, bs=64, repeat=2, cond=True, kw=dict(max_grad_norm=0.5, lr=1e-3)),
     dict(R=10, T=14, O=11, H=64, A=3, bs=48, repeat=3, cond=True, bound=1.5, kw=dict(value_clip=True, ent_coef=0.03, lr=1e-3)),
+    # A2C (a2c.py:247-288) over the same continuous actor: the plain policy-gradient loss with the Gaussian log-density
+    dict(R=12, T=16, O=18, H=64, A=2, bs=64, repeat=2, algo="a2c", kw=dict(max_grad_norm=0.5, vf_coef=0.25, ent_coef=0.02, lr=1e-3)),
 ]
 
 
-def _ref(O: int, H: int, A: int, seed: int, bound: float = 0.0, cond: bool = False, **kw):
+def _ref(O: int, H: int, A: int, seed: int, bound: float = 0.0, cond: bool = False, algo: str = "ppo", **kw):
     import gymnasium as gym
     import torch
     from tianshou.algorithm import PPO
@@ -60,6 +62,10 @@ def _ref(O: int, H: int, A: int, seed: int, bound: float = 0.0, cond: bool = Fal
     space = gym.spaces.Box(low=-2.0, high=2.0, shape=(A,))
     policy = ProbabilisticActorPolicy(actor=actor, dist_fn=dist, action_space=space)
     lr = kw.pop("lr", 3e-4)
+    if algo == "a2c":
+        from tianshou.algorithm import A2C
+
+        return A2C(policy=policy, critic=critic, optim=AdamOptimizerFactory(lr=lr), **kw), ac
     alg = PPO(policy=policy, critic=critic, optim=AdamOptimizerFactory(lr=lr), **kw)
     return alg, ac
 
@@ -87,7 +93,7 @@ def gen() -> None:
     for ci, c in enumerate(CASES):
         R, T, O, H, A = c["R"], c["T"], c["O"], c["H"], c["A"]
         rng = np.random.default_rng(300 + ci)
-        alg, ac = _ref(O, H, A, seed=40 + ci, bound=c.get("bound", 0.0), cond=c.get("cond", False), **dict(c["kw"]))
+        alg, ac = _ref(O, H, A, seed=40 + ci, bound=c.get("bound", 0.0), cond=c.get("cond", False), algo=c.get("algo", "ppo"), **dict(c["kw"]))
         pre = f"p{ci}_"
         for k, v in _flat(ac).items():
             out[pre + k] = v
@@ -132,7 +138,7 @@ def gen() -> None:
                 batch = alg._preprocess_batch(batch, buf, indices)
                 out[pre + "indices"] = np.asarray(indices)
                 for k in ("v_s", "returns", "adv", "logp_old"):
-                    out[pre + k] = batch[k].detach().cpu().numpy().copy()
+                    out[pre + k] = batch[k].detach().cpu().numpy().copy() if k in batch else np.zeros(len(indices), np.float32)  # (A2C: no logp_old)
                 with torch_train_mode(alg):
                     stats = alg._update_with_batch(batch, c["bs"], c["repeat"])
         finally:
@@ -145,6 +151,7 @@ def gen() -> None:
         out[pre + "cfg"] = np.array([R, T, O, H, A, c["bs"], c["repeat"], 0, 70 + ci], np.int64)
         out[pre + "mu_bound"] = np.array(c.get("bound", 0.0))
         out[pre + "cond_sigma"] = np.array(int(c.get("cond", False)))
+        out[pre + "a2c"] = np.array(int(c.get("algo", "ppo") == "a2c"))
         out[pre + "hyper"] = np.array([kw.get("eps_clip", 0.2), kw.get("dual_clip") or 0.0, kw.get("vf_coef", 0.5), kw.get("ent_coef", 0.01),
                                        float(kw.get("value_clip", False)), float(kw.get("advantage_normalization", True)),
                                        kw.get("max_grad_norm") or 0.0, kw.get("lr", 3e-4), 0.99, 0.95])

@@ -120,7 +120,7 @@ def test_oracle_matches_reference_reinforce(golden, ci):
         assert np.allclose(p.detach().numpy(), c["after_" + k], rtol=0, atol=2e-5), k
 
 
-@pytest.mark.parametrize("ci", [0, 1, 2, 3, 4, 5, 6])
+@pytest.mark.parametrize("ci", [0, 1, 2, 3, 4, 5, 6, 7])
 def test_oracle_matches_reference_ppo_gaussian(golden, ci):
     """Continuous actions: Independent(Normal(mu, exp(sigma_param)), 1) (tests/golden/ppo_gauss.npz, recorded from the reference's
     ContinuousActorProbabilistic + PPO; cases 3 and 4: unbounded=False, mu = max_action * tanh(head) with max_action 1 and 2)."""
@@ -140,8 +140,9 @@ def test_oracle_matches_reference_ppo_gaussian(golden, ci):
     v_s, ret, adv, logp_old = oppo.preprocess(net, f["obs"], f["obs_next"], f["act"], f["rew"], f["term"], f["trunc"], c["indices"],
                                               c["unfinished"], c["gamma"], c["lam"])
     assert np.allclose(v_s, c["v_s"], rtol=2e-5, atol=2e-6) and np.allclose(ret, c["returns"], rtol=2e-5, atol=2e-5)
-    assert np.allclose(adv, c["adv"], rtol=2e-5, atol=2e-5) and np.allclose(logp_old, c["logp_old"], rtol=2e-5, atol=2e-5)
-    log = oppo.update_with_orders(net, f["obs"], f["act"], c["adv"], c["returns"], c["logp_old"], c["v_s"], c["cfg"], c["orders"],
+    assert np.allclose(adv, c["adv"], rtol=2e-5, atol=2e-5) and (c["a2c"] or np.allclose(logp_old, c["logp_old"], rtol=2e-5, atol=2e-5))
+    cfg = dict(c["cfg"], a2c=True) if c["a2c"] else c["cfg"]  # case 7: A2C over the Gaussian actor (a2c.py:262-272)
+    log = oppo.update_with_orders(net, f["obs"], f["act"], c["adv"], c["returns"], c["logp_old"], c["v_s"], cfg, c["orders"],
                                   c["bs"], c["lr"], c["max_norm"])
     assert len(log["loss"]) == len(c["loss_seq"])
     for k, ref in (("loss", "loss_seq"), ("clip", "clip_seq"), ("vf", "vf_seq"), ("ent", "ent_seq")):
