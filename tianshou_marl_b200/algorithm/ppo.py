@@ -549,6 +549,8 @@ class Reinforce(PPO):
 
     def __init__(self, *, policy: DiscreteActorPolicy, gamma: float = 0.99, return_standardization: bool = False,
                  optim: AdamOptimizerFactory | None = None, **kwargs: Any) -> None:
+        if getattr(policy.actor, "gaussian", False):
+            raise NotImplementedError("Reinforce over a Gaussian actor: not recorded against the reference (PPO and A2C are: ppo_gauss.npz)")
         super().__init__(policy=policy, critic=None, optim=optim, vf_coef=0.0, ent_coef=0.0, max_grad_norm=None, gae_lambda=1.0, gamma=gamma,
                          return_scaling=return_standardization, advantage_normalization=False, value_clip=False, dual_clip=None,
                          recompute_advantage=False, **kwargs)
