@@ -128,50 +128,88 @@ extern "C" int tsm_tc_selftest(const float* a_img, int a_floats, const float* b_
 // batch records (include/tsm_b200.h: TSM_PPO_RECORD_BYTES): one thread per storage slot, streaming
 namespace tsm {
 namespace mlptc {
+// Block = 256 consecutive slots (or 256 (t, row) pairs of a row list).  The observations of consecutive slots are one contiguous
+// range and so are their records up to the 32-byte tail of the pitch, so both sides go through shared memory: the block loads the
+// range with coalesced 16-byte accesses, every thread builds its record from its row, and the block writes the records out with
+// consecutive lanes on consecutive 16-byte pieces (a thread per record would touch 32 lines per instruction with 16 bytes each).
 __global__ void __launch_bounds__(256) pack_records_kernel(const float* __restrict__ obs, const int32_t* __restrict__ act,
                                                           const float* __restrict__ adv, const float* __restrict__ ret,
                                                           const float* __restrict__ logp_old, const float* __restrict__ v_old,
                                                           int64_t n_slots, int in_dim, uint4* __restrict__ records,
                                                           const int64_t* __restrict__ rows, int64_t n_sel, int64_t n_rows) {
-    int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= n_slots) return;
-    if (rows) {  // only the sub-buffers in `rows` (a policy group): thread (t, i) packs slot t * n_rows + rows[i]
-        const int64_t t = s / n_sel;
-        s = t * n_rows + rows[s - t * n_sel];
+    __shared__ __align__(16) float s_buf[256 * TC_XF];  // 32 KB: the block's observations, then its records (256 x 96 bytes)
+    const int64_t s_first = (int64_t)blockIdx.x * 256;
+    const int64_t s_lin = s_first + threadIdx.x;
+    const int n_here = (int)min((int64_t)256, n_slots - s_first);
+    const bool valid = threadIdx.x < n_here;
+    int64_t s = s_lin;
+    if (rows && valid) {  // only the sub-buffers in `rows` (a policy group): thread (t, i) packs slot t * n_rows + rows[i]
+        const int64_t t = s_lin / n_sel;
+        s = t * n_rows + rows[s_lin - t * n_sel];
     }
     float x[TC_XF];
 #pragma unroll
     for (int k = 0; k < TC_XF; ++k) x[k] = 0.f;
-    const float* p = obs + s * in_dim;
-    if ((in_dim & 1) == 0 && (reinterpret_cast<uintptr_t>(p) & 7) == 0) {
+    const bool staged = rows == nullptr && (((uintptr_t)(obs + s_first * in_dim)) & 15) == 0;
+    if (staged) {
+        const int n_f = n_here * in_dim, n4 = n_f >> 2;
+        const float4* src = reinterpret_cast<const float4*>(obs + s_first * in_dim);
+        for (int i = threadIdx.x; i < n4; i += 256) reinterpret_cast<float4*>(s_buf)[i] = __ldcs(src + i);
+        for (int i = (n4 << 2) + threadIdx.x; i < n_f; i += 256) s_buf[i] = __ldcs(obs + s_first * in_dim + i);
+        __syncthreads();
+        if (valid) {
 #pragma unroll
-        for (int k = 0; k < TC_XF / 2; ++k)
-            if (2 * k < in_dim) {
-                const float2 v = __ldcs(reinterpret_cast<const float2*>(p + 2 * k));
-                x[2 * k] = v.x;
-                x[2 * k + 1] = v.y;
-            }
-    } else {
+            for (int k = 0; k < TC_XF; ++k)
+                if (k < in_dim) x[k] = s_buf[threadIdx.x * in_dim + k];
+        }
+        __syncthreads();  // the staging area is reused for the records
+    } else if (valid) {
+        const float* p = obs + s * in_dim;
+        if ((in_dim & 1) == 0 && (reinterpret_cast<uintptr_t>(p) & 7) == 0) {
 #pragma unroll
-        for (int k = 0; k < TC_XF; ++k)
-            if (k < in_dim) x[k] = __ldcs(p + k);
+            for (int k = 0; k < TC_XF / 2; ++k)
+                if (2 * k < in_dim) {
+                    const float2 v = __ldcs(reinterpret_cast<const float2*>(p + 2 * k));
+                    x[2 * k] = v.x;
+                    x[2 * k + 1] = v.y;
+                }
+        } else {
+#pragma unroll
+            for (int k = 0; k < TC_XF; ++k)
+                if (k < in_dim) x[k] = __ldcs(p + k);
+        }
     }
     x[TC_XF - 1] = 1.0f;
-    uint4* out = records + s * (REC_PITCH / 16);
+    uint4 rec[6];
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
-        uint4 v;
-        v.x = pack_h2(x[8 * c + 0], x[8 * c + 1]); v.y = pack_h2(x[8 * c + 2], x[8 * c + 3]);
-        v.z = pack_h2(x[8 * c + 4], x[8 * c + 5]); v.w = pack_h2(x[8 * c + 6], x[8 * c + 7]);
-        out[c] = v;
+        rec[c].x = pack_h2(x[8 * c + 0], x[8 * c + 1]); rec[c].y = pack_h2(x[8 * c + 2], x[8 * c + 3]);
+        rec[c].z = pack_h2(x[8 * c + 4], x[8 * c + 5]); rec[c].w = pack_h2(x[8 * c + 6], x[8 * c + 7]);
     }
-    uint4 sc;
-    sc.x = __float_as_uint(adv ? adv[s] : 0.f);
-    sc.y = __float_as_uint(ret ? ret[s] : 0.f);
-    sc.z = __float_as_uint(logp_old ? logp_old[s] : 0.f);
-    sc.w = (uint32_t)(act ? act[s] : 0);
-    out[4] = sc;
-    out[5] = make_uint4(__float_as_uint(v_old ? v_old[s] : 0.f), 0, 0, 0);
+    rec[4] = make_uint4(0, 0, 0, 0);
+    rec[5] = make_uint4(0, 0, 0, 0);
+    if (valid) {
+        rec[4].x = __float_as_uint(adv ? adv[s] : 0.f);
+        rec[4].y = __float_as_uint(ret ? ret[s] : 0.f);
+        rec[4].z = __float_as_uint(logp_old ? logp_old[s] : 0.f);
+        rec[4].w = (uint32_t)(act ? act[s] : 0);
+        rec[5].x = __float_as_uint(v_old ? v_old[s] : 0.f);
+    }
+    if (rows == nullptr) {  // consecutive slots: records leave through shared memory, 16-byte pieces in order
+        uint4* s_rec = reinterpret_cast<uint4*>(s_buf);  // [256][6]
+#pragma unroll
+        for (int c = 0; c < 6; ++c) s_rec[threadIdx.x * 6 + c] = rec[c];
+        __syncthreads();
+        uint4* out = records + s_first * (REC_PITCH / 16);
+        for (int i = threadIdx.x; i < n_here * 6; i += 256) {
+            const int r = i / 6, c = i - r * 6;
+            out[r * (REC_PITCH / 16) + c] = s_rec[i];
+        }
+    } else if (valid) {
+        uint4* out = records + s * (REC_PITCH / 16);
+#pragma unroll
+        for (int c = 0; c < 6; ++c) out[c] = rec[c];
+    }
 }
 }  // namespace mlptc
 }  // namespace tsm
