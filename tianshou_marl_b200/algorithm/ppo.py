@@ -402,8 +402,11 @@ class PPO:
         # ---- minibatch loop (ppo.py:173-216) ----
         bounds = self.split_bounds(B, batch_size)
         n_mb = len(bounds) - 1
-        bounds_dev = torch.tensor(bounds, dtype=torch.int64, device=net.device)
-        h_bounds = (C.c_int64 * len(bounds))(*bounds)
+        cached = self._work.get("bounds_cache")  # (the same B / batch_size every update: no host -> device copy per call)
+        if cached is None or cached[0] != (B, batch_size):
+            cached = ((B, batch_size), torch.tensor(bounds, dtype=torch.int64, device=net.device), (C.c_int64 * len(bounds))(*bounds))
+            self._work["bounds_cache"] = cached
+        bounds_dev, h_bounds = cached[1], cached[2]
         stats = self._buf("mb_stats", (repeat * n_mb, 2))
         sums = self._buf("loss_sums", (repeat * n_mb, 4), torch.float64)
         sums.zero_()

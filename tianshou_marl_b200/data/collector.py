@@ -174,7 +174,9 @@ class Collector:
     def _collect(self, n_step: int | None, n_episode: int | None, random: bool) -> CollectStats:
         R = self.env_num
         dev = self.device
-        self._acc.copy_(torch.tensor([0, 0, 0, np.inf, -np.inf, 0, 0, np.inf, -np.inf], dtype=torch.float64))
+        if getattr(self, "_acc_init", None) is None:  # (a device copy instead of a host tensor + pageable H2D on every call)
+            self._acc_init = torch.tensor([0, 0, 0, np.inf, -np.inf, 0, 0, np.inf, -np.inf], dtype=torch.float64, device=dev)
+        self._acc.copy_(self._acc_init)
         self._list_count.zero_()
         n_vec = None if n_step is None else -(-n_step // R)  # ceil(n_step / R) vector steps (collector.py:917,1066)
         if self.episode_list:
