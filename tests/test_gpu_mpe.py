@@ -209,3 +209,24 @@ def test_continuous_policy_collects_and_updates_on_mpe():
     assert np.isfinite(ts.loss.mean) and np.isfinite(ts.vf_loss.mean)
     assert not torch.equal(before, net.flat.detach())
     assert float((net.view("log_sigma").detach() - 0.0).abs().max()) > 0.0  # the scale parameters moved too
+
+
+def test_kernel_contact_forces_cancel_at_full_size():
+    """A property that needs no oracle (MPE parity is unpinned): contact forces come in opposite pairs, so with no-op actions the
+    summed velocity of a world's agents only decays by the damping -- sum(v') = 0.75 * sum(v) -- however hard the agents overlap.
+    65 536 simple_spread worlds (BASELINE.json configs[1] size), all agents piled up near the origin."""
+    from tianshou_marl_b200.env import MPEVectorEnv
+
+    E, A = 65536, 3
+    env = MPEVectorEnv("simple_spread_v3", n_envs=E, n_agents=A, seed=5)
+    env.reset()
+    g = torch.Generator(device="cuda").manual_seed(1)
+    env.pos.copy_(torch.randn(E * A, 2, device="cuda", generator=g) * 0.1)
+    env.vel.copy_(torch.randn(E * A, 2, device="cuda", generator=g))
+    before = env.vel.view(E, A, 2).sum(1).double()
+    speed_before = float(env.vel.abs().max())
+    env.step(torch.zeros(E * A, dtype=torch.int32, device="cuda"))
+    after = env.vel.view(E, A, 2).sum(1).double()
+    assert float(env.vel.abs().max()) > 2.0 * speed_before / 3.0 and float(env.vel.abs().max()) > 5.0  # the contacts did push
+    # pairs cancel exactly in IEEE arithmetic (same formula on negated differences); what is left is the rounding of each agent's sum
+    assert float((after - 0.75 * before).abs().max()) < 2e-3
